@@ -1,0 +1,339 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes/numpy access to the CPU oracle.
+
+Loads oracle/_build/liboracle.so (the plain-C restatement, tp_oracle.c) and,
+when present, oracle/_ref/libtp_ref.so (the reference's own
+time_optimal_path_timing.cc compiled verbatim, see oracle/Makefile).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import this module.  The product never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_ORACLE_SO = os.path.join(HERE, "_build", "liboracle.so")
+_REF_SO = os.path.join(HERE, "_ref", "libtp_ref.so")
+
+c_double_p = C.POINTER(C.c_double)
+c_ubyte_p = C.POINTER(C.c_ubyte)
+
+ORC_OK = 0
+
+
+def build(force: bool = False) -> None:
+    """Compile the oracle (and oracle/_ref when /root/reference exists)."""
+    need = force or not os.path.exists(_ORACLE_SO)
+    if os.path.isdir("/root/reference/trajectory_planning") and not os.path.exists(_REF_SO):
+        need = True
+    if need:
+        subprocess.run(["make", "-C", HERE, "all"], check=True,
+                       stdout=subprocess.DEVNULL)
+
+
+def _dp(a):
+    if a is None:
+        return None
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(c_double_p)
+
+
+class _Solution(C.Structure):
+    _fields_ = [(n, c_double_p) for n in
+                ("time", "s", "sd", "sdd", "sd2", "b_sd2_max", "b_sdd_max",
+                 "b_sdd_min", "b_sd2_zero")] + [
+        ("b_type", c_ubyte_p), ("last_extremal_index", C.c_int),
+        ("extra", C.c_int)]
+
+
+class _PlanCfg(C.Structure):
+    _fields_ = [("N", C.c_int), ("dim", C.c_int), ("W", C.c_int),
+                ("rounding", C.c_double), ("safety", C.c_double),
+                ("delta", C.c_double), ("start_sec", C.c_double),
+                ("dt", C.c_double)]
+
+
+class _PlanOut(C.Structure):
+    _fields_ = [(n, c_double_p) for n in
+                ("time", "s", "sd", "sdd", "q", "dq", "ddq", "vel", "acc")] + [
+        ("duration", C.c_double), ("delta_used", C.c_double),
+        ("knot_end", C.c_double), ("last_extremal_index", C.c_int),
+        ("M_cap", C.c_int), ("M", C.c_int)] + [(n, c_double_p) for n in
+        ("r_t", "r_pos", "r_vel", "r_acc", "r_s", "r_sd", "r_sdd")]
+
+
+_lib = None
+_ref = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_ORACLE_SO):
+            build()
+        L = C.CDLL(_ORACLE_SO)
+        L.orc_knot_span.restype = C.c_int
+        L.orc_knot_span.argtypes = [c_double_p, C.c_int, C.c_int, C.c_double]
+        L.orc_basis.argtypes = [c_double_p, C.c_int, C.c_int, C.c_double, c_double_p]
+        L.orc_basis_ders.argtypes = [c_double_p, C.c_int, C.c_int, C.c_int,
+                                     C.c_double, c_double_p]
+        L.orc_eval_curve.restype = C.c_int
+        L.orc_eval_curve.argtypes = [c_double_p, C.c_int, c_double_p, C.c_int,
+                                     C.c_int, C.c_double, c_double_p]
+        L.orc_eval_curve_ders.restype = C.c_int
+        L.orc_eval_curve_ders.argtypes = [c_double_p, C.c_int, c_double_p, C.c_int,
+                                          C.c_int, C.c_int, C.c_double, c_double_p]
+        L.orc_make_uniform_knots.restype = C.c_int
+        L.orc_make_uniform_knots.argtypes = [C.c_int, C.c_int, C.c_double,
+                                             C.c_double, c_double_p]
+        L.orc_polyline_to_bspline3.restype = C.c_int
+        L.orc_polyline_to_bspline3.argtypes = [c_double_p, C.c_int, C.c_int,
+                                               C.c_double, c_double_p]
+        L.orc_joint_fit.restype = C.c_int
+        L.orc_joint_fit.argtypes = [c_double_p, C.c_int, C.c_int, C.c_double,
+                                    c_double_p, c_double_p]
+        L.orc_joint_sample.argtypes = [c_double_p, C.c_int, c_double_p, C.c_int,
+                                       C.c_int, C.c_double, C.c_double,
+                                       c_double_p, c_double_p, c_double_p]
+        L.orc_joint_constraints.argtypes = [c_double_p, c_double_p, C.c_int,
+                                            C.c_int, c_double_p, c_double_p,
+                                            C.c_double, c_double_p]
+        L.orc_find_max_sd2_simplex.argtypes = [c_double_p, C.c_int, c_double_p,
+                                               c_double_p, c_double_p]
+        L.orc_solve.restype = C.c_int
+        L.orc_solve.argtypes = [C.c_int, C.c_int, c_double_p] + [C.c_double] * 5 + [
+            C.c_int, C.POINTER(_Solution)]
+        L.orc_count_violations.restype = C.c_int
+        L.orc_count_violations.argtypes = [C.c_int, C.c_int, c_double_p,
+                                           c_double_p, c_double_p]
+        L.orc_query.restype = C.c_int
+        L.orc_query.argtypes = [C.c_int] + [c_double_p] * 4 + [C.c_double] * 3 + [
+            c_double_p] * 3
+        L.orc_time_from_sec.restype = C.c_int64
+        L.orc_time_from_sec.argtypes = [C.c_double]
+        L.orc_time_to_sec.restype = C.c_double
+        L.orc_time_to_sec.argtypes = [C.c_int64]
+        L.orc_assemble.argtypes = [c_double_p] * 5 + [C.c_int, C.c_int,
+                                                      c_double_p, c_double_p]
+        L.orc_resample_count.restype = C.c_int
+        L.orc_resample_count.argtypes = [C.c_double] * 3
+        L.orc_resample_uniform.argtypes = [C.c_int, C.c_int] + [c_double_p] * 8 + [
+            C.c_double, C.c_double, C.c_int] + [c_double_p] * 7
+        L.orc_plan_joint.restype = C.c_int
+        L.orc_plan_joint.argtypes = [C.POINTER(_PlanCfg), c_double_p, c_double_p,
+                                     c_double_p, C.POINTER(_PlanOut)]
+        _lib = L
+    return _lib
+
+
+def have_ref() -> bool:
+    return os.path.exists(_REF_SO)
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        R = C.CDLL(_REF_SO)
+        R.tpref_solve.restype = C.c_int
+        R.tpref_solve.argtypes = [C.c_int, C.c_int, c_double_p] + [C.c_double] * 5 + [
+            C.c_int, C.POINTER(_Solution)]
+        R.tpref_find_max_sd2.argtypes = [C.c_int, c_double_p, C.c_int, c_double_p]
+        R.tpref_query.restype = C.c_int
+        R.tpref_query.argtypes = [C.c_int, C.c_int, c_double_p] + [C.c_double] * 5 + [
+            C.c_int, c_double_p, c_double_p, c_double_p, c_double_p]
+        R.tpref_solve_batch.argtypes = [C.c_int, C.c_int, C.c_int, c_double_p,
+                                        c_double_p, C.c_int, C.c_int, c_double_p,
+                                        c_double_p, c_double_p, c_double_p]
+        R.tpref_plan_joint.restype = C.c_int
+        R.tpref_plan_joint.argtypes = [C.POINTER(_PlanCfg), c_double_p, c_double_p,
+                                       c_double_p, C.POINTER(_PlanOut)]
+        _ref = R
+    return _ref
+
+
+# ----------------------------------------------------------------- stage A
+def knot_span(knots, degree, u):
+    knots = np.ascontiguousarray(knots, np.float64)
+    return lib().orc_knot_span(_dp(knots), len(knots), degree, float(u))
+
+
+def basis(knots, span, p, u):
+    knots = np.ascontiguousarray(knots, np.float64)
+    out = np.zeros(p + 1)
+    lib().orc_basis(_dp(knots), span, p, float(u), _dp(out))
+    return out
+
+
+def basis_ders(knots, span, p, der, u):
+    knots = np.ascontiguousarray(knots, np.float64)
+    out = np.zeros((der + 1, p + 1))
+    lib().orc_basis_ders(_dp(knots), span, p, der, float(u), _dp(out))
+    return out
+
+
+def eval_curve(knots, ctrl, degree, u):
+    knots = np.ascontiguousarray(knots, np.float64)
+    ctrl = np.ascontiguousarray(ctrl, np.float64)
+    out = np.zeros(ctrl.shape[1])
+    st = lib().orc_eval_curve(_dp(knots), len(knots), _dp(ctrl), ctrl.shape[1],
+                              degree, float(u), _dp(out))
+    return st, out
+
+
+def eval_curve_ders(knots, ctrl, degree, nder, us):
+    """Evaluate at many parameters; returns (status[n], values[n][nder+1][dim])."""
+    knots = np.ascontiguousarray(knots, np.float64)
+    ctrl = np.ascontiguousarray(ctrl, np.float64)
+    us = np.atleast_1d(np.asarray(us, np.float64))
+    dim = ctrl.shape[1]
+    out = np.zeros((len(us), nder + 1, dim))
+    st = np.zeros(len(us), np.int32)
+    L = lib()
+    for i, u in enumerate(us):
+        st[i] = L.orc_eval_curve_ders(_dp(knots), len(knots), _dp(ctrl), dim,
+                                      degree, nder, float(u), _dp(out[i]))
+    return st, out
+
+
+def make_uniform_knots(num_points, degree, lo=0.0, hi=1.0):
+    k = np.zeros(num_points + degree + 1)
+    st = lib().orc_make_uniform_knots(num_points, degree, lo, hi, _dp(k))
+    assert st == 0
+    return k
+
+
+# ----------------------------------------------------------------- stage B
+def polyline_to_bspline3(corners, radius):
+    corners = np.ascontiguousarray(corners, np.float64)
+    W, D = corners.shape
+    out = np.zeros((max(3 * W - 2, 4), D))
+    n = lib().orc_polyline_to_bspline3(_dp(corners), W, D, float(radius), _dp(out))
+    return out[:n].copy()
+
+
+def joint_fit(waypoints, rounding):
+    wp = np.ascontiguousarray(waypoints, np.float64)
+    W, D = wp.shape
+    ctrl = np.zeros((max(3 * W - 2, 4), D))
+    knots = np.zeros(max(3 * W - 2, 4) + 3)
+    n = lib().orc_joint_fit(_dp(wp), W, D, float(rounding), _dp(ctrl), _dp(knots))
+    return ctrl[:n].copy(), knots[:n + 3].copy()
+
+
+def joint_sample(knots, ctrl, N, path_start, delta):
+    knots = np.ascontiguousarray(knots, np.float64)
+    ctrl = np.ascontiguousarray(ctrl, np.float64)
+    D = ctrl.shape[1]
+    q, dq, ddq = np.zeros((N, D)), np.zeros((N, D)), np.zeros((N, D))
+    lib().orc_joint_sample(_dp(knots), len(knots), _dp(ctrl), D, N,
+                           float(path_start), float(delta), _dp(q), _dp(dq), _dp(ddq))
+    return q, dq, ddq
+
+
+def joint_constraints(dq, ddq, vmax, amax, safety):
+    dq = np.ascontiguousarray(dq, np.float64)
+    ddq = np.ascontiguousarray(ddq, np.float64)
+    vmax = np.ascontiguousarray(vmax, np.float64)
+    amax = np.ascontiguousarray(amax, np.float64)
+    N, D = dq.shape
+    cons = np.zeros((N, 2 * D, 4))
+    lib().orc_joint_constraints(_dp(dq), _dp(ddq), N, D, _dp(vmax), _dp(amax),
+                                float(safety), _dp(cons))
+    return cons
+
+
+# ----------------------------------------------------------------- stage C
+def find_max_sd2(cons_row, impl="port"):
+    cons_row = np.ascontiguousarray(cons_row, np.float64)
+    Cn = cons_row.shape[0]
+    if impl == "port":
+        a, b, c = C.c_double(), C.c_double(), C.c_double()
+        lib().orc_find_max_sd2_simplex(_dp(cons_row), Cn, C.byref(a), C.byref(b),
+                                       C.byref(c))
+        return np.array([a.value, b.value, c.value])
+    out = np.zeros(3)
+    ref().tpref_find_max_sd2(Cn, _dp(cons_row), 1 if impl == "ref_brute" else 0,
+                             _dp(out))
+    return out
+
+
+def solve(cons, s_start, s_end, sd_start=0.0, sdd_start=0.0, time_start=0.0,
+          max_loops=100, impl="port"):
+    """Returns dict(status_ok, status, time, s, sd, sdd, sd2, b_*, last_extremal_index)."""
+    cons = np.ascontiguousarray(cons, np.float64)
+    N, Cn, four = cons.shape
+    assert four == 4
+    arrs = {k: np.full(N, np.nan) for k in
+            ("time", "s", "sd", "sdd", "sd2", "b_sd2_max", "b_sdd_max",
+             "b_sdd_min", "b_sd2_zero")}
+    btype = np.zeros(N, np.uint8)
+    sol = _Solution(**{k: _dp(v) for k, v in arrs.items()},
+                    b_type=btype.ctypes.data_as(c_ubyte_p))
+    if impl == "port":
+        st = lib().orc_solve(N, Cn, _dp(cons), s_start, s_end, sd_start, sdd_start,
+                             time_start, max_loops, C.byref(sol))
+        ok = st == ORC_OK
+    else:
+        r = ref().tpref_solve(N, Cn, _dp(cons), s_start, s_end, sd_start, sdd_start,
+                              time_start, max_loops, C.byref(sol))
+        st = 0 if r == 1 else (1 if r == -1 else 2)
+        ok = r == 1
+    out = dict(arrs)
+    out.update(ok=ok, status=st, b_type=btype,
+               last_extremal_index=sol.last_extremal_index, extra=sol.extra)
+    return out
+
+
+def count_violations(cons, sd2, sdd):
+    cons = np.ascontiguousarray(cons, np.float64)
+    N, Cn, _ = cons.shape
+    return lib().orc_count_violations(N, Cn, _dp(cons), _dp(np.ascontiguousarray(sd2)),
+                                      _dp(np.ascontiguousarray(sdd)))
+
+
+def query(sol, s_start, s_end, t):
+    N = len(sol["time"])
+    a, b, c = C.c_double(), C.c_double(), C.c_double()
+    ok = lib().orc_query(N, _dp(sol["time"]), _dp(sol["s"]), _dp(sol["sd"]),
+                         _dp(sol["sd2"]), s_start, s_end, float(t), C.byref(a),
+                         C.byref(b), C.byref(c))
+    return ok, a.value, b.value, c.value
+
+
+# ----------------------------------------------------------------- stage D
+def plan_joint(waypoints, vmax, amax, N, rounding=0.2, safety=0.8, delta=-1.0,
+               start_sec=0.0, dt=0.0, M_cap=0, impl="port"):
+    """One fresh joint path, single window.  impl: 'port' | 'ref'."""
+    wp = np.ascontiguousarray(waypoints, np.float64)
+    vmax = np.ascontiguousarray(vmax, np.float64)
+    amax = np.ascontiguousarray(amax, np.float64)
+    W, D = wp.shape
+    cfg = _PlanCfg(N, D, W, rounding, safety, delta, start_sec, dt)
+    o = {k: np.full(N, np.nan) for k in ("time", "s", "sd", "sdd")}
+    o.update({k: np.zeros((N, D)) for k in ("q", "dq", "ddq", "vel", "acc")})
+    r = {"r_t": np.zeros(M_cap), "r_s": np.zeros(M_cap), "r_sd": np.zeros(M_cap),
+         "r_sdd": np.zeros(M_cap), "r_pos": np.zeros((M_cap, D)),
+         "r_vel": np.zeros((M_cap, D)), "r_acc": np.zeros((M_cap, D))}
+    out = _PlanOut(**{k: _dp(v) for k, v in o.items()}, M_cap=M_cap,
+                   **{k: (_dp(v) if M_cap > 0 else None) for k, v in r.items()})
+    fn = lib().orc_plan_joint if impl == "port" else ref().tpref_plan_joint
+    st = fn(C.byref(cfg), _dp(wp), _dp(vmax), _dp(amax), C.byref(out))
+    res = dict(o)
+    M = out.M
+    res.update({k: v[:M] for k, v in r.items()})
+    res.update(status=st, ok=(st == ORC_OK), duration=out.duration,
+               delta=out.delta_used, knot_end=out.knot_end, M=M,
+               last_extremal_index=out.last_extremal_index)
+    return res
+
+
+def time_from_sec(x):
+    return lib().orc_time_from_sec(float(x))
+
+
+def time_to_sec(ns):
+    return lib().orc_time_to_sec(int(ns))

@@ -1,0 +1,141 @@
+/* TEST INFRASTRUCTURE ONLY -- the CPU oracle.  Never linked into, imported by,
+ * or called from the product (libtpb.so / the host C++ layer).  Only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+ * may use it, and only as the checker or the timed CPU baseline.
+ *
+ * A plain-C restatement of the reference's algorithm for the hot path
+ * (theteamatx/x-edr-trajectory-planning), each function citing the reference
+ * file:line it follows.  Parity pin: see the header comment of tp_oracle.c.
+ *
+ * Layout conventions (all double, row-major):
+ *   knots   [num_knots]
+ *   ctrl    [num_points][dim]
+ *   cons    [N][C][4]  with columns (A, B, lower, upper) of
+ *           lower <= A*sdd + B*sd^2 <= upper
+ *   q/dq/ddq [N][dim]
+ */
+#ifndef ORACLE_TP_ORACLE_H_
+#define ORACLE_TP_ORACLE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* status codes of orc_solve (0 == success; the reference only has bool). */
+enum {
+  ORC_OK = 0,
+  ORC_FAIL_SETUP = 1,    /* SetupProblem / IsSetupValid returned false */
+  ORC_FAIL_CONNECT = 2,  /* iback_lo > icrit_lo */
+  ORC_FAIL_NAN = 3,      /* sd2 still NaN after the extremal loop */
+  ORC_FAIL_TERMINAL = 4, /* non-zero terminal velocity */
+  ORC_FAIL_INDEX = 5     /* reference would index sd2_max[-1] (UB there) */
+};
+
+/* ---- stage A: B-splines ------------------------------------------------ */
+int orc_knot_span(const double* knots, int num_knots, int degree, double u);
+void orc_basis(const double* knots, int span, int p, double u, double* basis);
+void orc_basis_ders(const double* knots, int span, int p, int der, double u,
+                    double* ders /* [(der+1)][(p+1)] */);
+/* returns 0 ok, 11 (kOutOfRange) if u outside [knots[0], knots[last]]. */
+int orc_eval_curve(const double* knots, int num_knots, const double* ctrl,
+                   int dim, int degree, double u, double* value /* [dim] */);
+int orc_eval_curve_ders(const double* knots, int num_knots, const double* ctrl,
+                        int dim, int degree, int nder, double u,
+                        double* values /* [(nder+1)][dim] */);
+int orc_make_uniform_knots(int num_points, int degree, double lo, double hi,
+                           double* knots /* [num_points+degree+1] */);
+
+/* ---- stage B: joint-space timeable path -------------------------------- */
+/* returns number of control points written (3W-2, or 4 if W==1). */
+int orc_polyline_to_bspline3(const double* corners, int W, int dim,
+                             double radius, double* ctrl);
+/* FitSplineToWaypoints: ctrl [3W-2][dim], knots [3W-2+3]; returns num ctrl. */
+int orc_joint_fit(const double* waypoints, int W, int dim, double rounding,
+                  double* ctrl, double* knots);
+void orc_joint_sample(const double* knots, int num_knots, const double* ctrl,
+                      int dim, int N, double path_start, double delta,
+                      double* q, double* dq, double* ddq);
+void orc_joint_constraints(const double* dq, const double* ddq, int N, int dim,
+                           const double* vmax, const double* amax,
+                           double safety, double* cons /* [N][2dim][4] */);
+
+/* ---- stage C: Pfeiffer-Johanni time-optimal timing ---------------------- */
+void orc_find_max_sd2_simplex(const double* cons_row /* [C][4] */, int C,
+                              double* sd2max, double* sddmax, double* sd2zero);
+typedef struct {
+  /* outputs, all [N] and caller-allocated; any may be NULL */
+  double* time;
+  double* s;
+  double* sd;
+  double* sdd;
+  double* sd2;
+  /* limit curve after CalculateBoundary */
+  double* b_sd2_max;
+  double* b_sdd_max;
+  double* b_sdd_min;
+  double* b_sd2_zero;
+  unsigned char* b_type;
+  int last_extremal_index;
+  int num_loops; /* switching-point loop iterations executed */
+} orc_solution;
+int orc_solve(int N, int C, const double* cons, double s_start, double s_end,
+              double sd_start, double sdd_start, double time_start,
+              int max_loops, orc_solution* out);
+/* SolutionSatisfiesConstraints: number of violated rows. */
+int orc_count_violations(int N, int C, const double* cons, const double* sd2,
+                         const double* sdd);
+/* GetPathParameterAndDerivatives on a solved profile; returns 1 on success. */
+int orc_query(int N, const double* time, const double* s, const double* sd,
+              const double* sd2, double s_start, double s_end, double t,
+              double* s_out, double* sd_out, double* sdd_out);
+
+/* ---- stage D: trajectory assembly + time resampling --------------------- */
+int64_t orc_time_from_sec(double seconds);
+double orc_time_to_sec(int64_t ns);
+/* per-sample joint velocity / clamped acceleration. */
+void orc_assemble(const double* dq, const double* ddq, const double* sd,
+                  const double* sdd, const double* amax, int N, int dim,
+                  double* vel, double* acc);
+/* number of uniform samples ResampleEquidistantlyInTime would produce. */
+int orc_resample_count(double t_end, double start_sec, double dt);
+/* outputs: t[M], pos/vel/acc [M][dim], s/sd/sdd [M] */
+void orc_resample_uniform(int N, int dim, const double* time_ps,
+                          const double* s_ps, const double* sd_ps,
+                          const double* sdd_ps, const double* pos_ps,
+                          const double* vel_ps, const double* acc_ps,
+                          const double* amax, double start_sec, double dt,
+                          int M, double* t, double* pos, double* vel,
+                          double* acc, double* s, double* sd, double* sdd);
+
+/* Whole pipeline for one fresh joint path in a single window
+ * (TimeableJointSplinePath::SetWaypoints + PathTimingTrajectory::Plan with a
+ * path whose parameter range fits one window).  Caller provides scratch of
+ * the sizes documented in tp_oracle.c.  Returns an ORC_* status. */
+typedef struct {
+  int N, dim, W;
+  double rounding, safety, delta; /* delta <= 0: use knots.back()/(N-1) */
+  double start_sec;
+  double dt; /* <= 0: skip resampling */
+} orc_plan_cfg;
+typedef struct {
+  /* [N] */
+  double *time, *s, *sd, *sdd;
+  /* [N][dim] */
+  double *q, *dq, *ddq, *vel, *acc;
+  double duration;
+  double delta_used;
+  double knot_end;
+  int last_extremal_index;
+  /* resampled, capacity M_cap rows; M written */
+  int M_cap, M;
+  double *r_t, *r_pos, *r_vel, *r_acc, *r_s, *r_sd, *r_sdd;
+} orc_plan_out;
+int orc_plan_joint(const orc_plan_cfg* cfg, const double* waypoints,
+                   const double* vmax, const double* amax, orc_plan_out* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORACLE_TP_ORACLE_H_ */
