@@ -1,0 +1,243 @@
+/* tpb.h -- C ABI of the B200-native batched path-timing engine.
+ *
+ * This is the drop-in boundary for the hot path of
+ * theteamatx/x-edr-trajectory-planning (B-spline evaluation with derivatives,
+ * joint-space timeable-path sampling, Pfeiffer-Johanni time-optimal path
+ * timing, trajectory assembly / time resampling), batched over many
+ * independent paths.  The reference has no FFI of its own: its seam is the C++
+ * virtual interface TimeablePath (trajectory_planning/timeable_path.h:92-166)
+ * plus the concrete classes named below.  The host C++ layer in
+ * x-edr-trajectory-planning_b200/host/ re-creates those classes on top of
+ * exactly these entry points; nothing else crosses the boundary.
+ *
+ * Conventions
+ *  - All functions return an int32 equal to absl::StatusCode's numeric value
+ *    (0 kOk, 3 kInvalidArgument, 9 kFailedPrecondition, 11 kOutOfRange,
+ *    13 kInternal, ...), like the absl::Status the reference returns.
+ *  - Every array argument is plain double / int32 memory, row-major.  The
+ *    `on_device` flag says whether the pointer is a CUDA device pointer
+ *    (consumed in place or copied device-to-device) or host memory (copied
+ *    with cudaMemcpyAsync on the engine's stream; pinned memory makes that
+ *    copy truly asynchronous).
+ *  - An engine owns one device and one stream; all work is stream ordered and
+ *    asynchronous until tpb_sync / a host-side getter.  Not thread safe; use
+ *    one engine per thread / per GPU.
+ *  - A failing path never poisons the batch: per-path results carry an int32
+ *    status (TPB_PATH_*), the call itself still returns kOk.
+ *  - There is no CPU fallback: if no CUDA device is usable every call fails
+ *    with kFailedPrecondition / kInternal.
+ */
+#ifndef TPB_H_
+#define TPB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TPB_ABI_VERSION 1
+
+/* absl::StatusCode values used by this library. */
+enum {
+  TPB_OK = 0,
+  TPB_INVALID_ARGUMENT = 3,
+  TPB_DEADLINE_EXCEEDED = 4,
+  TPB_NOT_FOUND = 5,
+  TPB_FAILED_PRECONDITION = 9,
+  TPB_OUT_OF_RANGE = 11,
+  TPB_UNIMPLEMENTED = 12,
+  TPB_INTERNAL = 13
+};
+
+/* Per-path solver status (TimeOptimalPathProfile::OptimizePathParameter
+ * returns only bool; time_optimal_path_timing.cc:287-490 shows the causes). */
+enum {
+  TPB_PATH_OK = 0,
+  TPB_PATH_FAIL_SETUP = 1,    /* SetupProblem/IsSetupValid false (:161-203, :554-576) */
+  TPB_PATH_FAIL_CONNECT = 2,  /* iback_lo > icrit_lo (:383-391) */
+  TPB_PATH_FAIL_NAN = 3,      /* sd2 still NaN after the loop (:400-403) */
+  TPB_PATH_FAIL_TERMINAL = 4, /* non-zero terminal velocity (:422-428) */
+  TPB_PATH_FAIL_INDEX = 5,    /* reference would read sd2_max[-1] (:372, UB there) */
+  TPB_PATH_NOT_RUN = 100
+};
+
+/* Arrays that tpb_get / tpb_devptr can address.  B = current batch size,
+ * N = num_samples, D = num_dofs, n = control points of a path. */
+typedef enum {
+  /* spline of each path: TimeableJointSplinePath::control_points_/knots_ */
+  TPB_ARR_NUM_POINTS = 1, /* int32 [B] */
+  TPB_ARR_CTRL = 2,       /* double [B][max_points][D] */
+  TPB_ARR_KNOTS = 3,      /* double [B][max_points + 3] */
+  TPB_ARR_DELTA = 4,      /* double [B] path sampling distance actually used */
+  /* SamplePath outputs: GetPathPositionAt / GetFirst.. / GetSecond.. */
+  TPB_ARR_Q = 10,   /* double [B][N][D] */
+  TPB_ARR_DQ = 11,  /* double [B][N][D] */
+  TPB_ARR_DDQ = 12, /* double [B][N][D] */
+  /* TimeOptimalPathProfile outputs (time_optimal_path_timing.h:152-159) */
+  TPB_ARR_TIME = 20, /* double [B][N] */
+  TPB_ARR_S = 21,    /* double [B][N] */
+  TPB_ARR_SD = 22,   /* double [B][N] */
+  TPB_ARR_SDD = 23,  /* double [B][N] */
+  TPB_ARR_SD2 = 24,  /* double [B][N] */
+  /* limit curve (TimeOptimalPathProfile::Boundary, .h:225-255) */
+  TPB_ARR_B_SD2_MAX = 30,  /* double [B][N] */
+  TPB_ARR_B_SDD_MAX = 31,  /* double [B][N] */
+  TPB_ARR_B_SDD_MIN = 32,  /* double [B][N] */
+  TPB_ARR_B_SD2_ZERO = 33, /* double [B][N] */
+  TPB_ARR_B_TYPE = 34,     /* uint8  [B][N]  (1 source, 2 sink, 4 trajectory) */
+  /* per-path scalars */
+  TPB_ARR_STATUS = 40,        /* int32  [B] TPB_PATH_* */
+  TPB_ARR_DURATION = 41,      /* double [B] GetTotalDuration (NaN if failed) */
+  TPB_ARR_LAST_EXTREMAL = 42, /* int32  [B] GetLastExtremalIndex */
+  TPB_ARR_KNOT_END = 43,      /* double [B] knots.back() */
+  /* resampled trajectory (TrajectoryPlanner getters, trajectory_planner.h:86-108),
+   * ragged and packed: path b owns rows [R_OFFSET[b], R_OFFSET[b+1]) */
+  TPB_ARR_R_OFFSET = 50, /* int64  [B+1] */
+  TPB_ARR_R_TIME = 51,   /* double [total] */
+  TPB_ARR_R_POS = 52,    /* double [total][D] */
+  TPB_ARR_R_VEL = 53,    /* double [total][D] */
+  TPB_ARR_R_ACC = 54,    /* double [total][D] */
+  TPB_ARR_R_S = 55,      /* double [total] */
+  TPB_ARR_R_SD = 56,     /* double [total] */
+  TPB_ARR_R_SDD = 57     /* double [total] */
+} tpb_array;
+
+typedef struct tpb_engine tpb_engine;
+
+typedef struct {
+  int32_t device;          /* CUDA device ordinal */
+  int32_t max_paths;       /* batch capacity B */
+  int32_t num_dofs;        /* D (JointPathOptions::num_dofs); 0 for constraint-only use */
+  int32_t max_waypoints;   /* per path; 0 for constraint-only use */
+  int32_t num_samples;     /* N (num_path_samples) */
+  int32_t max_constraints; /* C capacity for tpb_set_constraints; 0 -> 2*D only */
+  int64_t max_time_samples_total; /* capacity of the packed resampled output; 0 -> none */
+} tpb_config;
+
+/* ---- life cycle ---------------------------------------------------------- */
+int32_t tpb_abi_version(void);
+int32_t tpb_create(const tpb_config* cfg, tpb_engine** out);
+int32_t tpb_destroy(tpb_engine* e);
+/* Human-readable text of the last non-OK return on this engine ("" if none). */
+const char* tpb_last_error(const tpb_engine* e);
+/* Use an existing cudaStream_t (e.g. torch's current stream); NULL = own stream. */
+int32_t tpb_set_stream(tpb_engine* e, void* cuda_stream);
+int32_t tpb_sync(tpb_engine* e);
+/* Number of kernels this engine has launched since creation (for accounting). */
+int64_t tpb_kernel_launches(const tpb_engine* e);
+
+/* ---- joint-space paths: TimeableJointSplinePath -------------------------- */
+/* PathOptions::constraint_safety / rounding (timeable_path.h:44-90; defaults
+ * 0.8 / 0.2). */
+int32_t tpb_set_path_options(tpb_engine* e, double constraint_safety, double rounding);
+/* SetWaypoints (timeable_path_joint_spline.cc:200-207) for `num_paths` paths.
+ * waypoints: [num_paths][max_waypoints][D]; num_waypoints: [num_paths] or NULL
+ * (all paths use max_waypoints).  Fits the degree-2 spline (FitSplineToWaypoints
+ * :252-292).  Sets the batch size B = num_paths. */
+int32_t tpb_set_joint_waypoints(tpb_engine* e, int32_t num_paths,
+                                const int32_t* num_waypoints,
+                                const double* waypoints, int32_t on_device);
+/* SetMaxJointVelocity / SetMaxJointAcceleration (:84-108).  per_path = 1:
+ * [B][D] each; per_path = 0: one [D] row shared by all paths. */
+int32_t tpb_set_joint_limits(tpb_engine* e, const double* max_velocity,
+                             const double* max_acceleration, int32_t per_path,
+                             int32_t on_device);
+/* PathOptions::delta_parameter per path.  delta == NULL: every path uses
+ * knots.back() / (N - 1), i.e. the whole path is one planning window. */
+int32_t tpb_set_sampling(tpb_engine* e, const double* delta, int32_t on_device);
+/* SamplePath(path_start) + ConstraintSetup (:294-343) + the per-sample part of
+ * CalculateBoundary (time_optimal_path_timing.cc:1366-1377).  path_start: [B]
+ * or NULL (0). */
+int32_t tpb_sample_paths(tpb_engine* e, const double* path_start, int32_t on_device);
+
+/* ---- explicit constraints: TimeOptimalPathProfile ------------------------ */
+/* InitSolver + SetupProblem (time_optimal_path_timing.cc:135-203) for
+ * `num_paths` problems of N samples and C rows each.
+ * constraints: [num_paths][N][C][4] = (A, B, lower, upper) of
+ * lower <= A*sdd + B*sd^2 <= upper.  s_start/s_end: [num_paths].
+ * Also evaluates the per-sample limit curve. */
+int32_t tpb_set_constraints(tpb_engine* e, int32_t num_paths, int32_t num_constraints,
+                            const double* constraints, const double* s_start,
+                            const double* s_end, int32_t on_device);
+
+/* ---- stage C: OptimizePathParameter (:287-490) --------------------------- */
+/* sd_start, sdd_start, time_start: [B] each or NULL (0).  max_loops <= 0:
+ * max(100, 10 N) as PathTimingTrajectory sets it (path_timing_trajectory.cc:398-400). */
+int32_t tpb_optimize(tpb_engine* e, const double* sd_start, const double* sdd_start,
+                     const double* time_start, int32_t max_loops, int32_t on_device);
+
+/* ---- stage D: trajectory assembly + ResampleEquidistantlyInTime ---------- */
+/* (path_timing_trajectory.cc:458-472, :755-783).  start_sec = TimeToSec(start),
+ * time_step_sec = the planner's time step.  Writes the packed TPB_ARR_R_* arrays;
+ * *total_samples (may be NULL) receives R_OFFSET[B] (this synchronises). */
+int32_t tpb_resample(tpb_engine* e, double start_sec, double time_step_sec,
+                     int64_t* total_samples);
+
+/* Whole pipeline for a batch of fresh joint paths with HOST buffers in and out:
+ * set waypoints+limits, sample, optimize, resample, copy back durations,
+ * status and (if out_* non-NULL) the packed resampled trajectory.  This is the
+ * call a user of PathTimingTrajectory::Plan makes for a batch. */
+typedef struct {
+  int32_t num_paths;
+  const int32_t* num_waypoints; /* [B] or NULL */
+  const double* waypoints;      /* [B][max_waypoints][D] */
+  const double* max_velocity;   /* [B][D] */
+  const double* max_acceleration;
+  double start_sec;
+  double time_step_sec; /* <= 0: no resampling */
+  /* outputs (host); any may be NULL */
+  double* duration;      /* [B] */
+  int32_t* status;       /* [B] */
+  int64_t* r_offset;     /* [B+1] */
+  double* r_pos;         /* [cap][D] */
+  double* r_vel;         /* [cap][D] */
+  double* r_acc;         /* [cap][D] */
+  double* r_s;           /* [cap] */
+  double* r_sd;          /* [cap] */
+  double* r_sdd;         /* [cap] */
+  int64_t r_capacity;    /* rows available in r_* */
+  int64_t r_total;       /* out: rows written */
+} tpb_plan_io;
+int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io);
+
+/* ---- results ------------------------------------------------------------- */
+/* Copy array `what` (current batch) to dst (host or device); bytes must be at
+ * least the array's size.  Host copies synchronise the stream. */
+int32_t tpb_get(tpb_engine* e, tpb_array what, void* dst, size_t bytes, int32_t to_device);
+/* Device pointer + size of array `what` for zero-copy consumers. */
+int32_t tpb_devptr(tpb_engine* e, tpb_array what, void** ptr, size_t* bytes);
+
+/* ---- stage A stand-alone: dense B-spline evaluation ---------------------- */
+/* BSplineT::EvalCurveAndDerivatives (splines/bspline.h:539-568) for
+ * num_splines splines that share degree / num_points / dim, evals_per_spline
+ * parameters each.  u == NULL: implicit grid u0[s] + i * du[s].
+ * out: [num_splines][evals_per_spline][nder+1][dim].
+ * status (may be NULL): int32 [num_splines][evals_per_spline], 0 or
+ * kOutOfRange (11) when u is outside [knots.front(), knots.back()] (then the
+ * output row is left untouched, like the reference).
+ * exact != 0: NURBS-book A2.3 operation order (bit-identical to the oracle);
+ * exact == 0: per-span polynomial form (<= 1e-12 absolute, faster). */
+typedef struct {
+  int32_t degree, num_points, dim, nder;
+  int32_t num_splines;
+  int64_t evals_per_spline;
+  const double* knots; /* [num_splines][num_points + degree + 1] */
+  const double* ctrl;  /* [num_splines][num_points][dim] */
+  const double* u;     /* [num_splines][evals_per_spline] or NULL */
+  const double* u0;    /* [num_splines] (grid mode) */
+  const double* du;    /* [num_splines] (grid mode) */
+  double* out;
+  int32_t* status;
+  int32_t exact;
+} tpb_spline_eval_desc;
+/* All pointers are device pointers; cuda_stream may be NULL (default stream). */
+int32_t tpb_spline_eval_device(const tpb_spline_eval_desc* d, void* cuda_stream);
+/* Same with host pointers (allocates, copies in, evaluates, copies out). */
+int32_t tpb_spline_eval_host(const tpb_spline_eval_desc* d, int32_t device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TPB_H_ */

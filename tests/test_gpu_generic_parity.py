@@ -1,0 +1,111 @@
+"""GPU parity: explicit-constraint problems (the TimeOptimalPathProfile API)
+through the C ABI vs the CPU oracle, on the reference's own test scenarios
+(time_optimal_path_timing_test.cc:440-701) and seeded random problems."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+KEYS = (("TIME", "time"), ("S", "s"), ("SD", "sd"), ("SDD", "sdd"), ("SD2", "sd2"),
+        ("B_SD2_MAX", "b_sd2_max"), ("B_SDD_MAX", "b_sdd_max"), ("B_SDD_MIN", "b_sdd_min"),
+        ("B_SD2_ZERO", "b_sd2_zero"), ("B_TYPE", "b_type"))
+
+
+def _solve_batch(pkg, cons, s0, s1, sd0=None, sdd0=None, t0=None, max_loops=100):
+    B, N, C, _ = cons.shape
+    eng = pkg.Engine(max_paths=B, num_samples=N, max_constraints=C)
+    eng.set_constraints(cons, s0, s1)
+    eng.optimize(sd0, sdd0, t0, max_loops=max_loops)
+    A = pkg.ARR
+    res = {k: eng.get(getattr(A, k)) for k, _ in KEYS}
+    for k in ("STATUS", "DURATION", "LAST_EXTREMAL"):
+        res[k] = eng.get(getattr(A, k))
+    eng.close()
+    return res
+
+
+def _compare(po, res, cons, s0, s1, sd0=None, sdd0=None, t0=None, max_loops=100,
+             expect_all_ok=False):
+    B = cons.shape[0]
+    for b in range(B):
+        o = po.solve(cons[b], s0[b], s1[b], 0.0 if sd0 is None else sd0[b],
+                     0.0 if sdd0 is None else sdd0[b], 0.0 if t0 is None else t0[b],
+                     max_loops=max_loops)
+        assert (res["STATUS"][b] == 0) == o["ok"], (b, res["STATUS"][b], o["status"])
+        assert res["STATUS"][b] == o["status"], (b, res["STATUS"][b], o["status"])
+        if expect_all_ok:
+            assert o["ok"]
+        if not o["ok"]:
+            continue
+        assert res["LAST_EXTREMAL"][b] == o["last_extremal_index"]
+        assert abs(res["DURATION"][b] - (o["time"][-1] - o["time"][0])) <= 1e-6 * abs(o["time"][-1] - o["time"][0]) + 1e-300
+        for k, ok in KEYS:
+            # integer/bit-exact: same operation order, no FMA contraction
+            assert np.array_equal(res[k][b], o[ok], equal_nan=True), (b, k)
+        assert po.count_violations(cons[b], res["SD2"][b], res["SDD"][b]) == \
+            po.count_violations(cons[b], o["sd2"], o["sdd"])
+
+
+def test_circle_scenarios(pkg, po):
+    W = pkg.workloads
+    for N in (50, 51, 1000, 2048):
+        cons = np.stack([W.circle_constraints(N), W.circle_constraints(N)])
+        s0, s1 = np.zeros(2), np.full(2, np.pi)
+        sd0 = np.array([0.0, 0.1])
+        res = _solve_batch(pkg, cons, s0, s1, sd0)
+        _compare(po, res, cons, s0, s1, sd0, expect_all_ok=True)
+    # golden duration of the reference itself (tests/golden, N=50, sd_start=0)
+    cons = W.circle_constraints(50)[None]
+    res = _solve_batch(pkg, cons, np.zeros(1), np.full(1, np.pi))
+    assert abs(res["DURATION"][0] - 6.0003326777697756) <= 1e-6 * 6.0
+
+
+def test_sine_scenarios(pkg, po):
+    W = pkg.workloads
+    for N in (30, 31, 100, 111):
+        offs = np.array([0.0, np.pi / 2, np.pi / 4])
+        cons = np.stack([W.sine_constraints(N, o, np.pi + o) for o in offs])
+        res = _solve_batch(pkg, cons, offs, offs + np.pi)
+        _compare(po, res, cons, offs, offs + np.pi, expect_all_ok=True)
+
+
+def test_line_scalar_scenarios(pkg, po):
+    W = pkg.workloads
+    cons = W.line_constraints(30)[None]
+    res = _solve_batch(pkg, cons, np.zeros(1), np.full(1, np.pi))
+    _compare(po, res, cons, np.zeros(1), np.full(1, np.pi), expect_all_ok=True)
+    cons = W.scalar_straight_constraints(30)[None]
+    res = _solve_batch(pkg, cons, np.zeros(1), np.ones(1))
+    _compare(po, res, cons, np.zeros(1), np.ones(1), expect_all_ok=True)
+    cons = W.scalar_curved_constraints(100)[None]
+    res = _solve_batch(pkg, cons, np.full(1, -3.0), np.ones(1))
+    _compare(po, res, cons, np.full(1, -3.0), np.ones(1), expect_all_ok=True)
+
+
+@pytest.mark.parametrize("N,C", [(64, 2), (200, 6), (333, 14), (128, 32), (2, 3), (3, 4)])
+def test_random_problems(pkg, po, N, C):
+    rng = np.random.default_rng(100 * N + C)
+    B = 24
+    cons = np.stack([pkg.workloads.random_constraints(rng, N, C) for _ in range(B)])
+    s0 = rng.uniform(-1, 1, B)
+    s1 = s0 + rng.uniform(0.5, 5, B)
+    sd0 = rng.uniform(0, 0.3, B) * (rng.random(B) < 0.5)
+    sdd0 = rng.uniform(-0.5, 0.5, B)
+    t0 = rng.uniform(0, 10, B)
+    res = _solve_batch(pkg, cons, s0, s1, sd0, sdd0, t0)
+    _compare(po, res, cons, s0, s1, sd0, sdd0, t0)
+
+
+def test_setup_failures_are_per_path(pkg, po):
+    """SetupProblem failures (lower >= upper, s_start >= s_end, sd_start < 0)
+    mark only the offending path (time_optimal_path_timing.cc:161-203, :554-576)."""
+    N = 50
+    cons = np.stack([pkg.workloads.circle_constraints(N) for _ in range(4)])
+    cons[1, 10, 2, 2] = cons[1, 10, 2, 3]            # lower == upper
+    s0, s1 = np.zeros(4), np.full(4, np.pi)
+    s1[2] = 0.0                                       # s_start >= s_end
+    sd0 = np.array([0.0, 0.0, 0.0, -0.1])             # negative start velocity
+    res = _solve_batch(pkg, cons, s0, s1, sd0)
+    assert list(res["STATUS"]) == [0, 1, 1, 1]
+    assert np.isnan(res["DURATION"][1:]).all()
+    _compare(po, res, cons, s0, s1, sd0)

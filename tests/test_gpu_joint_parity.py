@@ -1,0 +1,164 @@
+"""GPU parity: joint-space paths through the C ABI vs the CPU oracle.
+
+Tolerances from BASELINE.json: spline positions/derivatives 1e-12 absolute,
+durations 1e-6 relative, resampled joint positions 1e-9 rad.  Because the CUDA
+build uses the oracle's operation order without FMA contraction, the
+intermediate arrays are in fact expected to be bit-identical; that stronger
+property is asserted where it holds by construction.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL_SPLINE = 1e-12
+TOL_DURATION_REL = 1e-6
+TOL_RESAMPLED = 1e-9
+
+
+def _run_engine(pkg, wp, vmax, amax, N, dt=0.004, num_waypoints=None, delta=None,
+                options=None):
+    B, W, D = wp.shape
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * 16384)
+    if options:
+        eng.set_path_options(*options)
+    if delta is not None:
+        eng.set_joint_waypoints(wp, num_waypoints)
+        eng.set_sampling(delta)
+    else:
+        eng.set_joint_waypoints(wp, num_waypoints)
+    eng.set_joint_limits(vmax, amax)
+    eng.sample_paths()
+    eng.optimize()
+    total = eng.resample(0.0, dt)
+    A = pkg.ARR
+    res = {k: eng.get(getattr(A, k)) for k in
+           ("CTRL", "KNOTS", "NUM_POINTS", "Q", "DQ", "DDQ", "TIME", "S", "SD", "SDD", "SD2",
+            "B_SD2_MAX", "B_SDD_MAX", "B_SDD_MIN", "B_SD2_ZERO", "B_TYPE", "STATUS",
+            "DURATION", "LAST_EXTREMAL", "KNOT_END", "DELTA", "R_OFFSET", "R_TIME", "R_POS",
+            "R_VEL", "R_ACC", "R_S", "R_SD", "R_SDD")}
+    res["total"] = total
+    eng.close()
+    return res
+
+
+def _check_against_oracle(po, res, wp, vmax, amax, N, dt=0.004, nw=None, rounding=0.2,
+                          safety=0.8, delta=None):
+    B = wp.shape[0]
+    exact = 0
+    for b in range(B):
+        W = wp.shape[1] if nw is None else int(nw[b])
+        o = po.plan_joint(wp[b, :W], vmax[b], amax[b], N, rounding=rounding, safety=safety,
+                          delta=-1.0 if delta is None else float(delta[b]), dt=dt,
+                          M_cap=16384)
+        n = res["NUM_POINTS"][b]
+        ctrl, knots = po.joint_fit(wp[b, :W], rounding)
+        assert n == len(ctrl)
+        assert np.max(np.abs(res["CTRL"][b, :n] - ctrl)) <= TOL_SPLINE
+        assert np.max(np.abs(res["KNOTS"][b, :n + 3] - knots)) <= TOL_SPLINE
+        for k, ok in (("Q", "q"), ("DQ", "dq"), ("DDQ", "ddq")):
+            err = np.max(np.abs(res[k][b] - o[ok]))
+            assert err <= TOL_SPLINE, (b, k, err)
+        assert (res["STATUS"][b] == 0) == o["ok"], (b, res["STATUS"][b], o["status"])
+        if not o["ok"]:
+            assert np.isnan(res["DURATION"][b])
+            continue
+        assert abs(res["DURATION"][b] - o["duration"]) <= TOL_DURATION_REL * o["duration"]
+        assert res["LAST_EXTREMAL"][b] == o["last_extremal_index"]
+        for k, ok in (("TIME", "time"), ("SD", "sd"), ("SDD", "sdd"), ("S", "s")):
+            np.testing.assert_allclose(res[k][b], o[ok], rtol=1e-9, atol=1e-9, err_msg=f"{b} {k}")
+        lo, hi = res["R_OFFSET"][b], res["R_OFFSET"][b + 1]
+        assert hi - lo == o["M"], (b, hi - lo, o["M"])
+        assert np.max(np.abs(res["R_POS"][lo:hi] - o["r_pos"])) <= TOL_RESAMPLED
+        assert np.max(np.abs(res["R_VEL"][lo:hi] - o["r_vel"])) <= 1e-8
+        assert np.max(np.abs(res["R_ACC"][lo:hi] - o["r_acc"])) <= 1e-7
+        assert np.max(np.abs(res["R_TIME"][lo:hi] - o["r_t"])) == 0.0
+        bit = all(np.array_equal(res[k][b], o[ok]) for k, ok in
+                  (("Q", "q"), ("DQ", "dq"), ("DDQ", "ddq"), ("TIME", "time"), ("SD", "sd"),
+                   ("SDD", "sdd"))) and np.array_equal(res["R_POS"][lo:hi], o["r_pos"])
+        exact += bit
+    return exact
+
+
+def test_cfg2_shape_small_batch(pkg, po):
+    """cfg2 shape (D=7, W=10, N=2048), 48 paths."""
+    wp, vmax, amax = pkg.workloads.joint_paths(48, 10, 7, seed=1000)
+    res = _run_engine(pkg, wp, vmax, amax, 2048)
+    exact = _check_against_oracle(po, res, wp, vmax, amax, 2048)
+    assert exact == 48, f"only {exact}/48 paths bit-identical to the oracle"
+
+
+def test_cfg1_single_path(pkg, po):
+    wp, vmax, amax = pkg.workloads.single_path_cfg1()
+    res = _run_engine(pkg, wp, vmax, amax, 1000)
+    assert _check_against_oracle(po, res, wp, vmax, amax, 1000) == 1
+
+
+@pytest.mark.parametrize("D,W,N", [(6, 4, 257), (3, 3, 1000), (7, 2, 64), (1, 5, 100),
+                                   (16, 3, 128)])
+def test_other_shapes(pkg, po, D, W, N):
+    wp, vmax, amax = pkg.workloads.joint_paths(16, W, D, seed=5 + D)
+    res = _run_engine(pkg, wp, vmax, amax, N)
+    assert _check_against_oracle(po, res, wp, vmax, amax, N) == 16
+
+
+def test_ragged_waypoint_counts_and_single_waypoint(pkg, po):
+    """Ragged batches; W == 1 is PolyLineToBspline3Waypoints' special case
+    (spline_utils.cc:55-60): a point path, zero duration."""
+    B, W, D, N = 12, 8, 7, 300
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=77)
+    nw = np.array([8, 2, 3, 1, 5, 8, 4, 2, 7, 6, 1, 3], np.int32)
+    res = _run_engine(pkg, wp, vmax, amax, N, num_waypoints=nw)
+    _check_against_oracle(po, res, wp, vmax, amax, N, nw=nw)
+
+
+def test_short_segments_and_duplicate_waypoints(pkg, po):
+    """Segments shorter than 4*rounding (offset = norm/4) and zero-length
+    segments (norm <= kMinNorm), spline_utils.cc:28-43."""
+    B, W, D, N = 6, 5, 7, 400
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=9)
+    wp[0, 2] = wp[0, 1]                     # duplicate waypoint
+    wp[1, 1:] = wp[1, :1] + 0.01 * wp[1, 1:]  # tiny path
+    wp[2, 3] = wp[2, 2] + 1e-8              # below kMinNorm
+    res = _run_engine(pkg, wp, vmax, amax, N)
+    _check_against_oracle(po, res, wp, vmax, amax, N)
+
+
+def test_explicit_delta_with_tail_beyond_path_end(pkg, po):
+    """delta larger than knots.back()/(N-1): samples beyond the path end take the
+    tail branch (timeable_path_joint_spline.cc:309-313), zero rows -> kMaxSd2."""
+    B, W, D, N = 8, 6, 7, 500
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=21)
+    ctrl_len = np.array([po.joint_fit(wp[b], 0.2)[1][-1] for b in range(B)])
+    delta = ctrl_len / (N - 1) * np.linspace(1.0, 1.3, B)
+    res = _run_engine(pkg, wp, vmax, amax, N, delta=delta)
+    _check_against_oracle(po, res, wp, vmax, amax, N, delta=delta)
+
+
+def test_options_safety_rounding(pkg, po):
+    B, W, D, N = 8, 6, 7, 300
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=33)
+    res = _run_engine(pkg, wp, vmax, amax, N, options=(0.5, 0.05))
+    _check_against_oracle(po, res, wp, vmax, amax, N, rounding=0.05, safety=0.5)
+
+
+def test_plan_joint_host_matches_staged_calls(pkg, po):
+    B, W, D, N = 16, 10, 7, 512
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=4)
+    res = _run_engine(pkg, wp, vmax, amax, N)
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * 16384)
+    cap = int(res["total"])
+    out = {"duration": np.zeros(B), "status": np.zeros(B, np.int32),
+           "r_offset": np.zeros(B + 1, np.int64), "r_pos": np.zeros((cap, D)),
+           "r_vel": np.zeros((cap, D)), "r_acc": np.zeros((cap, D)), "r_s": np.zeros(cap),
+           "r_sd": np.zeros(cap), "r_sdd": np.zeros(cap)}
+    total = eng.plan_joint_host(wp, vmax, amax, 0.0, 0.004, out=out)
+    eng.close()
+    assert total == res["total"]
+    np.testing.assert_array_equal(out["duration"], res["DURATION"])
+    np.testing.assert_array_equal(out["r_offset"], res["R_OFFSET"])
+    np.testing.assert_array_equal(out["r_pos"], res["R_POS"])
+    np.testing.assert_array_equal(out["r_acc"], res["R_ACC"])
+    np.testing.assert_array_equal(out["r_sdd"], res["R_SDD"])

@@ -1,0 +1,16 @@
+"""B200-native batched path-timing engine (drop-in for the hot path of
+theteamatx/x-edr-trajectory-planning).
+
+The product is ``lib/libtpb.so`` (hand-written sm_100a CUDA kernels behind the C
+ABI of ``include/tpb.h``) plus the host-side mirrors of the reference's classes:
+C++ in ``host/`` (same names as the reference) and this thin ctypes layer used by
+the tests and ``bench.py``.  There is no CPU fallback: if the library is missing
+or no CUDA device is present, construction fails loudly.
+
+The directory name contains hyphens, so import it through
+``__graft_entry__.load_package()`` (module name ``x_edr_trajectory_planning_b200``).
+"""
+from .binding import (  # noqa: F401
+    ARR, PATH_OK, Engine, TpbError, lib, lib_path, spline_eval_device, spline_eval_host,
+)
+from . import workloads  # noqa: F401

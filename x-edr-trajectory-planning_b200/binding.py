@@ -1,0 +1,336 @@
+"""ctypes binding of include/tpb.h (the C ABI of lib/libtpb.so).
+
+Host arrays are numpy; device arrays are anything with ``data_ptr()`` (torch
+tensors) or raw integer device pointers.  No computation happens in Python.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "lib", "libtpb.so")
+
+PATH_OK = 0
+
+
+class ARR:
+    NUM_POINTS, CTRL, KNOTS, DELTA = 1, 2, 3, 4
+    Q, DQ, DDQ = 10, 11, 12
+    TIME, S, SD, SDD, SD2 = 20, 21, 22, 23, 24
+    B_SD2_MAX, B_SDD_MAX, B_SDD_MIN, B_SD2_ZERO, B_TYPE = 30, 31, 32, 33, 34
+    STATUS, DURATION, LAST_EXTREMAL, KNOT_END = 40, 41, 42, 43
+    R_OFFSET, R_TIME, R_POS, R_VEL, R_ACC, R_S, R_SD, R_SDD = 50, 51, 52, 53, 54, 55, 56, 57
+
+
+class TpbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"tpb status {code}: {msg}")
+        self.code = code
+
+
+class _Config(C.Structure):
+    _fields_ = [("device", C.c_int32), ("max_paths", C.c_int32), ("num_dofs", C.c_int32),
+                ("max_waypoints", C.c_int32), ("num_samples", C.c_int32),
+                ("max_constraints", C.c_int32), ("max_time_samples_total", C.c_int64)]
+
+
+class _PlanIO(C.Structure):
+    _fields_ = [("num_paths", C.c_int32), ("num_waypoints", C.c_void_p),
+                ("waypoints", C.c_void_p), ("max_velocity", C.c_void_p),
+                ("max_acceleration", C.c_void_p), ("start_sec", C.c_double),
+                ("time_step_sec", C.c_double), ("duration", C.c_void_p),
+                ("status", C.c_void_p), ("r_offset", C.c_void_p), ("r_pos", C.c_void_p),
+                ("r_vel", C.c_void_p), ("r_acc", C.c_void_p), ("r_s", C.c_void_p),
+                ("r_sd", C.c_void_p), ("r_sdd", C.c_void_p), ("r_capacity", C.c_int64),
+                ("r_total", C.c_int64)]
+
+
+class _SplineDesc(C.Structure):
+    _fields_ = [("degree", C.c_int32), ("num_points", C.c_int32), ("dim", C.c_int32),
+                ("nder", C.c_int32), ("num_splines", C.c_int32),
+                ("evals_per_spline", C.c_int64), ("knots", C.c_void_p), ("ctrl", C.c_void_p),
+                ("u", C.c_void_p), ("u0", C.c_void_p), ("du", C.c_void_p),
+                ("out", C.c_void_p), ("status", C.c_void_p), ("exact", C.c_int32)]
+
+
+_lib = None
+
+
+def lib_path() -> str:
+    return _LIB
+
+
+def lib():
+    """Load libtpb.so; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB):
+            raise FileNotFoundError(
+                f"{_LIB} is missing: run __graft_entry__.build() (nvcc, sm_100a). "
+                "There is no CPU fallback.")
+        L = C.CDLL(_LIB)
+        vp, i32, i64, f64 = C.c_void_p, C.c_int32, C.c_int64, C.c_double
+        L.tpb_abi_version.restype = i32
+        L.tpb_create.restype = i32
+        L.tpb_create.argtypes = [C.POINTER(_Config), C.POINTER(vp)]
+        L.tpb_destroy.restype = i32
+        L.tpb_destroy.argtypes = [vp]
+        L.tpb_last_error.restype = C.c_char_p
+        L.tpb_last_error.argtypes = [vp]
+        L.tpb_set_stream.restype = i32
+        L.tpb_set_stream.argtypes = [vp, vp]
+        L.tpb_sync.restype = i32
+        L.tpb_sync.argtypes = [vp]
+        L.tpb_kernel_launches.restype = i64
+        L.tpb_kernel_launches.argtypes = [vp]
+        L.tpb_set_path_options.restype = i32
+        L.tpb_set_path_options.argtypes = [vp, f64, f64]
+        L.tpb_set_joint_waypoints.restype = i32
+        L.tpb_set_joint_waypoints.argtypes = [vp, i32, vp, vp, i32]
+        L.tpb_set_joint_limits.restype = i32
+        L.tpb_set_joint_limits.argtypes = [vp, vp, vp, i32, i32]
+        L.tpb_set_sampling.restype = i32
+        L.tpb_set_sampling.argtypes = [vp, vp, i32]
+        L.tpb_sample_paths.restype = i32
+        L.tpb_sample_paths.argtypes = [vp, vp, i32]
+        L.tpb_set_constraints.restype = i32
+        L.tpb_set_constraints.argtypes = [vp, i32, i32, vp, vp, vp, i32]
+        L.tpb_optimize.restype = i32
+        L.tpb_optimize.argtypes = [vp, vp, vp, vp, i32, i32]
+        L.tpb_resample.restype = i32
+        L.tpb_resample.argtypes = [vp, f64, f64, C.POINTER(i64)]
+        L.tpb_plan_joint_host.restype = i32
+        L.tpb_plan_joint_host.argtypes = [vp, C.POINTER(_PlanIO)]
+        L.tpb_get.restype = i32
+        L.tpb_get.argtypes = [vp, i32, vp, C.c_size_t, i32]
+        L.tpb_devptr.restype = i32
+        L.tpb_devptr.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(C.c_size_t)]
+        L.tpb_spline_eval_device.restype = i32
+        L.tpb_spline_eval_device.argtypes = [C.POINTER(_SplineDesc), vp]
+        L.tpb_spline_eval_host.restype = i32
+        L.tpb_spline_eval_host.argtypes = [C.POINTER(_SplineDesc), i32]
+        _lib = L
+    return _lib
+
+
+def _ptr(x):
+    """(pointer, on_device) of a numpy array / torch tensor / None."""
+    if x is None:
+        return None, 0
+    if isinstance(x, np.ndarray):
+        assert x.flags["C_CONTIGUOUS"]
+        return x.ctypes.data, 0
+    if hasattr(x, "data_ptr"):
+        assert x.is_contiguous()
+        return x.data_ptr(), 1 if x.is_cuda else 0
+    raise TypeError(type(x))
+
+
+def _f64(x):
+    if x is None or hasattr(x, "data_ptr"):
+        return x
+    return np.ascontiguousarray(x, dtype=np.float64)
+
+
+_DTYPES = {ARR.NUM_POINTS: np.int32, ARR.STATUS: np.int32, ARR.LAST_EXTREMAL: np.int32,
+           ARR.B_TYPE: np.uint8, ARR.R_OFFSET: np.int64}
+
+
+class Engine:
+    """One engine = one GPU + one stream (tpb_engine)."""
+
+    def __init__(self, max_paths, num_samples, num_dofs=0, max_waypoints=0,
+                 max_constraints=0, max_time_samples_total=0, device=0):
+        self._h = C.c_void_p()
+        self.max_paths, self.N, self.D = max_paths, num_samples, num_dofs
+        self.Wmax = max_waypoints
+        self.max_points = max(3 * max_waypoints - 2, 4) if num_dofs else 0
+        self.B = 0
+        self.C = 0
+        cfg = _Config(device, max_paths, num_dofs, max_waypoints, num_samples,
+                      max_constraints, max_time_samples_total)
+        rc = lib().tpb_create(C.byref(cfg), C.byref(self._h))
+        if rc != 0:
+            self._h = C.c_void_p()
+            raise TpbError(rc, "tpb_create failed (no CUDA device / bad config / out of memory)")
+
+    def close(self):
+        if self._h:
+            lib().tpb_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise TpbError(rc, lib().tpb_last_error(self._h).decode())
+
+    # -- configuration -------------------------------------------------------
+    def set_stream(self, cuda_stream_ptr):
+        self._ck(lib().tpb_set_stream(self._h, cuda_stream_ptr))
+
+    def sync(self):
+        self._ck(lib().tpb_sync(self._h))
+
+    @property
+    def kernel_launches(self):
+        return lib().tpb_kernel_launches(self._h)
+
+    def set_path_options(self, constraint_safety=0.8, rounding=0.2):
+        self._ck(lib().tpb_set_path_options(self._h, constraint_safety, rounding))
+
+    # -- joint paths ---------------------------------------------------------
+    def set_joint_waypoints(self, waypoints, num_waypoints=None):
+        waypoints = _f64(waypoints)
+        B = waypoints.shape[0]
+        assert tuple(waypoints.shape[1:]) == (self.Wmax, self.D), waypoints.shape
+        wp, dev = _ptr(waypoints)
+        if num_waypoints is not None and not hasattr(num_waypoints, "data_ptr"):
+            num_waypoints = np.ascontiguousarray(num_waypoints, np.int32)
+        nw, dev2 = _ptr(num_waypoints)
+        assert num_waypoints is None or dev == dev2
+        self._ck(lib().tpb_set_joint_waypoints(self._h, B, nw, wp, dev))
+        self.B, self.C = B, 2 * self.D
+
+    def set_joint_limits(self, vmax, amax):
+        vmax, amax = _f64(vmax), _f64(amax)
+        per_path = 1 if vmax.ndim == 2 else 0
+        pv, dev = _ptr(vmax)
+        pa, dev2 = _ptr(amax)
+        assert dev == dev2
+        self._ck(lib().tpb_set_joint_limits(self._h, pv, pa, per_path, dev))
+
+    def set_sampling(self, delta=None):
+        delta = _f64(delta)
+        p, dev = _ptr(delta)
+        self._ck(lib().tpb_set_sampling(self._h, p, dev))
+
+    def sample_paths(self, path_start=None):
+        path_start = _f64(path_start)
+        p, dev = _ptr(path_start)
+        self._ck(lib().tpb_sample_paths(self._h, p, dev))
+
+    # -- explicit constraints --------------------------------------------------
+    def set_constraints(self, cons, s_start, s_end):
+        cons, s_start, s_end = _f64(cons), _f64(s_start), _f64(s_end)
+        B, N, Cn, four = cons.shape
+        assert N == self.N and four == 4
+        pc, dev = _ptr(cons)
+        p0, _ = _ptr(s_start)
+        p1, _ = _ptr(s_end)
+        self._ck(lib().tpb_set_constraints(self._h, B, Cn, pc, p0, p1, dev))
+        self.B, self.C = B, Cn
+
+    # -- stages ----------------------------------------------------------------
+    def optimize(self, sd_start=None, sdd_start=None, time_start=None, max_loops=0):
+        ptrs, dev = [], 0
+        for x in (sd_start, sdd_start, time_start):
+            p, d = _ptr(_f64(x))
+            ptrs.append(p)
+            dev = dev or d
+        self._ck(lib().tpb_optimize(self._h, *ptrs, max_loops, dev))
+
+    def resample(self, start_sec, time_step_sec, want_total=True):
+        total = C.c_int64(0)
+        self._ck(lib().tpb_resample(self._h, start_sec, time_step_sec,
+                                    C.byref(total) if want_total else None))
+        return total.value
+
+    def plan_joint_host(self, waypoints, vmax, amax, start_sec=0.0, time_step_sec=0.0,
+                        num_waypoints=None, out=None):
+        """tpb_plan_joint_host.  `out`: dict of preallocated (ideally pinned) host
+        arrays keyed duration,status,r_offset,r_pos,r_vel,r_acc,r_s,r_sd,r_sdd."""
+        B = waypoints.shape[0]
+        out = out or {}
+        io = _PlanIO()
+        io.num_paths = B
+        io.num_waypoints = _ptr(num_waypoints)[0]
+        io.waypoints = _ptr(waypoints)[0]
+        io.max_velocity = _ptr(vmax)[0]
+        io.max_acceleration = _ptr(amax)[0]
+        io.start_sec, io.time_step_sec = start_sec, time_step_sec
+        cap = None
+        for k in ("duration", "status", "r_offset", "r_pos", "r_vel", "r_acc", "r_s",
+                  "r_sd", "r_sdd"):
+            v = out.get(k)
+            setattr(io, k, _ptr(v)[0] if v is not None else None)
+            if v is not None and k in ("r_pos", "r_vel", "r_acc", "r_s", "r_sd", "r_sdd"):
+                rows = v.shape[0]
+                cap = rows if cap is None else min(cap, rows)
+        io.r_capacity = cap or 0
+        self._ck(lib().tpb_plan_joint_host(self._h, C.byref(io)))
+        self.B, self.C = B, 2 * self.D
+        return io.r_total
+
+    # -- results ---------------------------------------------------------------
+    def devptr(self, what):
+        p, n = C.c_void_p(), C.c_size_t()
+        self._ck(lib().tpb_devptr(self._h, what, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def get(self, what):
+        """Copy array `what` to a new numpy array shaped like the reference's getter."""
+        _, nbytes = self.devptr(what)
+        dt = np.dtype(_DTYPES.get(what, np.float64))
+        out = np.empty(nbytes // dt.itemsize, dt)
+        if nbytes:
+            self._ck(lib().tpb_get(self._h, what, out.ctypes.data, nbytes, 0))
+        B, N, D = self.B, self.N, self.D
+        if what in (ARR.Q, ARR.DQ, ARR.DDQ):
+            return out.reshape(B, N, D)
+        if what == ARR.CTRL:
+            return out.reshape(B, self.max_points, D)
+        if what == ARR.KNOTS:
+            return out.reshape(B, self.max_points + 3)
+        if what in (ARR.R_POS, ARR.R_VEL, ARR.R_ACC):
+            return out.reshape(-1, D)
+        if ARR.TIME <= what <= ARR.B_TYPE:
+            return out.reshape(B, N)
+        return out
+
+
+def _desc(degree, num_points, dim, nder, num_splines, evals, knots, ctrl, u, u0, du, out,
+          status, exact):
+    d = _SplineDesc(degree, num_points, dim, nder, num_splines, evals)
+    d.knots, d.ctrl, d.u, d.u0, d.du = (_ptr(x)[0] for x in (knots, ctrl, u, u0, du))
+    d.out, d.status, d.exact = _ptr(out)[0], _ptr(status)[0], 1 if exact else 0
+    return d
+
+
+def spline_eval_host(knots, ctrl, degree, nder, u=None, u0=None, du=None, evals=None,
+                     exact=True, out=None, device=0):
+    """tpb_spline_eval_host.  knots [S][n+p+1], ctrl [S][n][dim]; u [S][E] or grid."""
+    knots, ctrl = _f64(knots), _f64(ctrl)
+    S, n, dim = ctrl.shape
+    if u is not None:
+        u = _f64(u)
+        evals = u.shape[1]
+    else:
+        u0, du = _f64(u0), _f64(du)
+    if out is None:
+        out = np.zeros((S, evals, nder + 1, dim))
+    status = np.zeros((S, evals), np.int32)
+    d = _desc(degree, n, dim, nder, S, evals, knots, ctrl, u, u0, du, out, status, exact)
+    rc = lib().tpb_spline_eval_host(C.byref(d), device)
+    if rc != 0:
+        raise TpbError(rc, "tpb_spline_eval_host")
+    return out, status
+
+
+def spline_eval_device(knots, ctrl, degree, nder, out, u=None, u0=None, du=None, evals=None,
+                       status=None, exact=True, stream=None):
+    """tpb_spline_eval_device on torch CUDA tensors (asynchronous on `stream`)."""
+    S, n, dim = ctrl.shape
+    if u is not None:
+        evals = u.shape[1]
+    d = _desc(degree, n, dim, nder, S, evals, knots, ctrl, u, u0, du, out, status, exact)
+    rc = lib().tpb_spline_eval_device(C.byref(d), stream)
+    if rc != 0:
+        raise TpbError(rc, "tpb_spline_eval_device")

@@ -1,0 +1,620 @@
+// C ABI of the engine (include/tpb.h): handle management, stream-ordered
+// copies, stage sequencing.  No CPU implementation of any stage lives here: if
+// CUDA is unavailable, every entry point fails.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "tpb_device.cuh"
+#include "tpb_engine.h"
+
+namespace tpb {
+int launch_spline_eval(const tpb_spline_eval_desc& d, cudaStream_t st, std::string* err);
+}
+
+struct tpb_engine {
+  tpb::Dims dims;
+  tpb::DeviceArrays a;
+  tpb::Mode mode = tpb::Mode::kNone;
+  int device = 0;
+  int num_sms = 148;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  double safety = 0.8;    // PathOptions::constraint_safety_ (timeable_path.h:80)
+  double rounding = 0.2;  // PathOptions::rounding_ (timeable_path.h:82)
+  bool auto_delta = true;
+  bool have_waypoints = false, have_limits = false, sampled = false, optimized = false,
+       resampled = false;
+  std::string err;
+  int64_t launches = 0;
+  std::vector<void*> allocs;
+};
+
+namespace {
+
+using tpb::Mode;
+
+int32_t fail(tpb_engine* e, int32_t code, const std::string& msg) {
+  if (e) e->err = msg;
+  return code;
+}
+
+int32_t cuda_fail(tpb_engine* e, cudaError_t err, const char* what) {
+  return fail(e, TPB_INTERNAL, std::string(what) + ": " + cudaGetErrorString(err));
+}
+
+#define TPB_CUDA(e, call)                                        \
+  do {                                                           \
+    cudaError_t err__ = (call);                                  \
+    if (err__ != cudaSuccess) return cuda_fail(e, err__, #call); \
+  } while (0)
+
+template <typename T>
+cudaError_t dev_alloc(tpb_engine* e, T** p, size_t count) {
+  if (count == 0) count = 1;
+  void* q = nullptr;
+  cudaError_t err = cudaMalloc(&q, count * sizeof(T));
+  if (err != cudaSuccess) return err;
+  e->allocs.push_back(q);
+  *p = static_cast<T*>(q);
+  return cudaSuccess;
+}
+
+// copy `bytes` into an engine buffer from host or device memory
+cudaError_t copy_in(tpb_engine* e, void* dst, const void* src, size_t bytes, int on_device) {
+  return cudaMemcpyAsync(dst, src, bytes,
+                         on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                         e->stream);
+}
+
+cudaError_t fill_or_copy(tpb_engine* e, double* dst, const double* src, size_t count,
+                         int on_device) {
+  if (src == nullptr) return cudaMemsetAsync(dst, 0, count * sizeof(double), e->stream);
+  return copy_in(e, dst, src, count * sizeof(double), on_device);
+}
+
+struct ArrayRef {
+  void* ptr = nullptr;
+  size_t bytes = 0;
+};
+
+bool lookup(tpb_engine* e, tpb_array what, ArrayRef* r) {
+  const auto& d = e->dims;
+  const auto& a = e->a;
+  const size_t B = d.B, N = d.N, D = d.D;
+  const size_t BN = B * N * sizeof(double);
+  int64_t total = 0;
+  auto packed_rows = [&]() -> size_t {
+    if (!e->resampled) return 0;
+    cudaMemcpyAsync(&total, a.r_offset + d.B, sizeof(int64_t), cudaMemcpyDeviceToHost,
+                    e->stream);
+    cudaStreamSynchronize(e->stream);
+    return static_cast<size_t>(std::min<int64_t>(total, d.r_cap));
+  };
+  switch (what) {
+    case TPB_ARR_NUM_POINTS: *r = {a.num_points, B * sizeof(int32_t)}; return true;
+    case TPB_ARR_CTRL: *r = {a.ctrl, B * d.max_points * D * sizeof(double)}; return true;
+    case TPB_ARR_KNOTS: *r = {a.knots, B * (d.max_points + 3) * sizeof(double)}; return true;
+    case TPB_ARR_DELTA: *r = {a.delta, B * sizeof(double)}; return true;
+    case TPB_ARR_Q: *r = {a.q, BN * D}; return true;
+    case TPB_ARR_DQ: *r = {a.dq, BN * D}; return true;
+    case TPB_ARR_DDQ: *r = {a.ddq, BN * D}; return true;
+    case TPB_ARR_TIME: *r = {a.time, BN}; return true;
+    case TPB_ARR_S: *r = {a.s, BN}; return true;
+    case TPB_ARR_SD: *r = {a.sd, BN}; return true;
+    case TPB_ARR_SDD: *r = {a.sdd, BN}; return true;
+    case TPB_ARR_SD2: *r = {a.sd2, BN}; return true;
+    case TPB_ARR_B_SD2_MAX: *r = {a.b_sd2_max, BN}; return true;
+    case TPB_ARR_B_SDD_MAX: *r = {a.b_sdd_max, BN}; return true;
+    case TPB_ARR_B_SDD_MIN: *r = {a.b_sdd_min, BN}; return true;
+    case TPB_ARR_B_SD2_ZERO: *r = {a.b_sd2_zero, BN}; return true;
+    case TPB_ARR_B_TYPE: *r = {a.b_type, B * N}; return true;
+    case TPB_ARR_STATUS: *r = {a.status, B * sizeof(int32_t)}; return true;
+    case TPB_ARR_DURATION: *r = {a.duration, B * sizeof(double)}; return true;
+    case TPB_ARR_LAST_EXTREMAL: *r = {a.last_extremal, B * sizeof(int32_t)}; return true;
+    case TPB_ARR_KNOT_END: *r = {a.knot_end, B * sizeof(double)}; return true;
+    case TPB_ARR_R_OFFSET: *r = {a.r_offset, (B + 1) * sizeof(int64_t)}; return true;
+    case TPB_ARR_R_TIME: *r = {a.r_time, packed_rows() * sizeof(double)}; return true;
+    case TPB_ARR_R_POS: *r = {a.r_pos, packed_rows() * D * sizeof(double)}; return true;
+    case TPB_ARR_R_VEL: *r = {a.r_vel, packed_rows() * D * sizeof(double)}; return true;
+    case TPB_ARR_R_ACC: *r = {a.r_acc, packed_rows() * D * sizeof(double)}; return true;
+    case TPB_ARR_R_S: *r = {a.r_s, packed_rows() * sizeof(double)}; return true;
+    case TPB_ARR_R_SD: *r = {a.r_sd, packed_rows() * sizeof(double)}; return true;
+    case TPB_ARR_R_SDD: *r = {a.r_sdd, packed_rows() * sizeof(double)}; return true;
+  }
+  return false;
+}
+
+bool is_joint_array(tpb_array w) {
+  return w == TPB_ARR_NUM_POINTS || w == TPB_ARR_CTRL || w == TPB_ARR_KNOTS ||
+         w == TPB_ARR_DELTA || w == TPB_ARR_Q || w == TPB_ARR_DQ || w == TPB_ARR_DDQ ||
+         w == TPB_ARR_KNOT_END || (w >= TPB_ARR_R_OFFSET && w <= TPB_ARR_R_SDD);
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t tpb_abi_version(void) { return TPB_ABI_VERSION; }
+
+int32_t tpb_create(const tpb_config* cfg, tpb_engine** out) {
+  if (cfg == nullptr || out == nullptr) return TPB_INVALID_ARGUMENT;
+  *out = nullptr;
+  if (cfg->max_paths < 1 || cfg->num_samples < 2) return TPB_INVALID_ARGUMENT;
+  if (cfg->num_dofs < 0 || cfg->num_dofs > tpb::kMaxDofs) return TPB_OUT_OF_RANGE;
+  if (cfg->max_constraints < 0 || cfg->max_constraints > tpb::kMaxRows) return TPB_OUT_OF_RANGE;
+  if (cfg->num_dofs == 0 && cfg->max_constraints == 0) return TPB_INVALID_ARGUMENT;
+  if (cfg->num_dofs > 0 && cfg->max_waypoints < 1) return TPB_INVALID_ARGUMENT;
+  // CHECK(options_.num_path_samples() >= 3), timeable_path_joint_spline.cc:45
+  if (cfg->num_dofs > 0 && cfg->num_samples < 3) return TPB_INVALID_ARGUMENT;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return TPB_FAILED_PRECONDITION;  // no CUDA device: there is no CPU fallback
+  }
+  if (cfg->device < 0 || cfg->device >= ndev) return TPB_INVALID_ARGUMENT;
+  if (cudaSetDevice(cfg->device) != cudaSuccess) return TPB_INTERNAL;
+
+  tpb_engine* e = new tpb_engine();
+  e->device = cfg->device;
+  cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device);
+  auto& d = e->dims;
+  d.Bmax = cfg->max_paths;
+  d.B = 0;
+  d.D = cfg->num_dofs;
+  d.Wmax = cfg->max_waypoints;
+  d.max_points = (d.D > 0) ? std::max(3 * d.Wmax - 2, 4) : 0;
+  d.N = cfg->num_samples;
+  d.Cmax = cfg->max_constraints;
+  d.r_cap = (d.D > 0) ? cfg->max_time_samples_total : 0;
+  const size_t B = d.Bmax, N = d.N, D = d.D;
+  auto& a = e->a;
+  cudaError_t err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+  e->own_stream = true;
+#define TPB_ALLOC(field, count) \
+  if (err == cudaSuccess) err = dev_alloc(e, &a.field, (count))
+  if (D > 0) {
+    TPB_ALLOC(waypoints, B * d.Wmax * D);
+    TPB_ALLOC(num_wp, B);
+    TPB_ALLOC(vmax, B * D);
+    TPB_ALLOC(amax, B * D);
+    TPB_ALLOC(delta_in, B);
+    TPB_ALLOC(ctrl, B * d.max_points * D);
+    TPB_ALLOC(knots, B * (d.max_points + 3));
+    TPB_ALLOC(num_points, B);
+    TPB_ALLOC(delta, B);
+    TPB_ALLOC(knot_end, B);
+    TPB_ALLOC(q, B * N * D);
+    TPB_ALLOC(dq, B * N * D);
+    TPB_ALLOC(ddq, B * N * D);
+  }
+  if (d.Cmax > 0) {
+    TPB_ALLOC(cons, B * N * d.Cmax * 4);
+    TPB_ALLOC(s_start, B);
+    TPB_ALLOC(s_end, B);
+  }
+  TPB_ALLOC(path_start, B);
+  TPB_ALLOC(sd_start, B);
+  TPB_ALLOC(sdd_start, B);
+  TPB_ALLOC(time_start, B);
+  TPB_ALLOC(b_raw_sd2_max, B * N);
+  TPB_ALLOC(b_raw_sdd_max, B * N);
+  TPB_ALLOC(b_raw_sdd_min, B * N);
+  TPB_ALLOC(b_sd2_max, B * N);
+  TPB_ALLOC(b_sdd_max, B * N);
+  TPB_ALLOC(b_sdd_min, B * N);
+  TPB_ALLOC(b_sd2_zero, B * N);
+  TPB_ALLOC(b_at0, B * N);
+  TPB_ALLOC(b_type, B * N);
+  TPB_ALLOC(sd2, B * N);
+  TPB_ALLOC(sdd, B * N);
+  TPB_ALLOC(sd, B * N);
+  TPB_ALLOC(s, B * N);
+  TPB_ALLOC(time, B * N);
+  TPB_ALLOC(fix_val, B * N);
+  TPB_ALLOC(status, B);
+  TPB_ALLOC(last_extremal, B);
+  TPB_ALLOC(duration, B);
+  if (d.r_cap > 0) {
+    const size_t R = static_cast<size_t>(d.r_cap);
+    TPB_ALLOC(r_count, B);
+    TPB_ALLOC(r_offset, B + 1);
+    TPB_ALLOC(r_time, R);
+    TPB_ALLOC(r_pos, R * D);
+    TPB_ALLOC(r_vel, R * D);
+    TPB_ALLOC(r_acc, R * D);
+    TPB_ALLOC(r_s, R);
+    TPB_ALLOC(r_sd, R);
+    TPB_ALLOC(r_sdd, R);
+  }
+#undef TPB_ALLOC
+  if (err == cudaSuccess) err = cudaMemsetAsync(a.path_start, 0, B * sizeof(double), e->stream);
+  if (err == cudaSuccess) err = cudaMemsetAsync(a.sd_start, 0, B * sizeof(double), e->stream);
+  if (err == cudaSuccess) err = cudaMemsetAsync(a.sdd_start, 0, B * sizeof(double), e->stream);
+  if (err == cudaSuccess) err = cudaMemsetAsync(a.time_start, 0, B * sizeof(double), e->stream);
+  if (err != cudaSuccess) {
+    fprintf(stderr, "tpb_create: %s\n", cudaGetErrorString(err));
+    tpb_destroy(e);
+    return err == cudaErrorMemoryAllocation ? 8 /* kResourceExhausted */ : TPB_INTERNAL;
+  }
+  *out = e;
+  return TPB_OK;
+}
+
+int32_t tpb_destroy(tpb_engine* e) {
+  if (e == nullptr) return TPB_OK;
+  cudaSetDevice(e->device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (void* p : e->allocs) cudaFree(p);
+  if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+  return TPB_OK;
+}
+
+const char* tpb_last_error(const tpb_engine* e) { return e ? e->err.c_str() : ""; }
+
+int32_t tpb_set_stream(tpb_engine* e, void* cuda_stream) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  cudaSetDevice(e->device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
+  if (cuda_stream == nullptr) {
+    TPB_CUDA(e, cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    e->own_stream = true;
+  } else {
+    e->stream = static_cast<cudaStream_t>(cuda_stream);
+    e->own_stream = false;
+  }
+  return TPB_OK;
+}
+
+int32_t tpb_sync(tpb_engine* e) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+  return TPB_OK;
+}
+
+int64_t tpb_kernel_launches(const tpb_engine* e) { return e ? e->launches : 0; }
+
+int32_t tpb_set_path_options(tpb_engine* e, double constraint_safety, double rounding) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  e->safety = constraint_safety;
+  e->rounding = rounding;
+  return TPB_OK;
+}
+
+int32_t tpb_set_joint_waypoints(tpb_engine* e, int32_t num_paths, const int32_t* num_waypoints,
+                                const double* waypoints, int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (d.D == 0) return fail(e, TPB_FAILED_PRECONDITION, "engine was created without dofs");
+  if (num_paths < 1 || num_paths > d.Bmax)
+    return fail(e, TPB_OUT_OF_RANGE, "num_paths exceeds max_paths");
+  if (waypoints == nullptr) return fail(e, TPB_INVALID_ARGUMENT, "waypoints is null");
+  cudaSetDevice(e->device);
+  if (num_waypoints != nullptr && !on_device) {
+    for (int b = 0; b < num_paths; ++b) {
+      if (num_waypoints[b] < 1 || num_waypoints[b] > d.Wmax)
+        return fail(e, TPB_INVALID_ARGUMENT, "num_waypoints out of [1, max_waypoints]");
+    }
+  }
+  d.B = num_paths;
+  d.C = 2 * d.D;
+  e->mode = Mode::kJoint;
+  TPB_CUDA(e, copy_in(e, e->a.waypoints, waypoints,
+                      sizeof(double) * static_cast<size_t>(d.B) * d.Wmax * d.D, on_device));
+  if (num_waypoints != nullptr) {
+    TPB_CUDA(e, copy_in(e, e->a.num_wp, num_waypoints, sizeof(int32_t) * d.B, on_device));
+  } else {
+    e->launches += tpb::launch_fill_i32(e->a.num_wp, d.Wmax, d.B, e->stream);
+  }
+  e->launches += tpb::launch_joint_fit(d, e->a, e->rounding, e->auto_delta, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->have_waypoints = true;
+  e->sampled = e->optimized = e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_set_joint_limits(tpb_engine* e, const double* max_velocity,
+                             const double* max_acceleration, int32_t per_path,
+                             int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (d.D == 0) return fail(e, TPB_FAILED_PRECONDITION, "engine was created without dofs");
+  if (max_velocity == nullptr || max_acceleration == nullptr)
+    return fail(e, TPB_INVALID_ARGUMENT, "limits are null");
+  cudaSetDevice(e->device);
+  const size_t rows = per_path ? (d.B > 0 ? d.B : d.Bmax) : 1;
+  const size_t row_bytes = sizeof(double) * d.D;
+  if (per_path) {
+    TPB_CUDA(e, copy_in(e, e->a.vmax, max_velocity, rows * row_bytes, on_device));
+    TPB_CUDA(e, copy_in(e, e->a.amax, max_acceleration, rows * row_bytes, on_device));
+  } else {
+    // broadcast one row to every path
+    std::vector<double> hv(d.D), ha(d.D);
+    if (on_device) {
+      TPB_CUDA(e, cudaMemcpyAsync(hv.data(), max_velocity, row_bytes, cudaMemcpyDeviceToHost, e->stream));
+      TPB_CUDA(e, cudaMemcpyAsync(ha.data(), max_acceleration, row_bytes, cudaMemcpyDeviceToHost, e->stream));
+      TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+    } else {
+      std::memcpy(hv.data(), max_velocity, row_bytes);
+      std::memcpy(ha.data(), max_acceleration, row_bytes);
+    }
+    std::vector<double> bv(static_cast<size_t>(d.Bmax) * d.D), ba(bv.size());
+    for (int b = 0; b < d.Bmax; ++b) {
+      std::memcpy(&bv[static_cast<size_t>(b) * d.D], hv.data(), row_bytes);
+      std::memcpy(&ba[static_cast<size_t>(b) * d.D], ha.data(), row_bytes);
+    }
+    TPB_CUDA(e, cudaMemcpyAsync(e->a.vmax, bv.data(), bv.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    TPB_CUDA(e, cudaMemcpyAsync(e->a.amax, ba.data(), ba.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+  }
+  e->have_limits = true;
+  e->sampled = e->optimized = e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_set_sampling(tpb_engine* e, const double* delta, int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (d.D == 0) return fail(e, TPB_FAILED_PRECONDITION, "engine was created without dofs");
+  cudaSetDevice(e->device);
+  if (delta == nullptr) {
+    e->auto_delta = true;
+  } else {
+    if (d.B == 0) return fail(e, TPB_FAILED_PRECONDITION, "set waypoints first");
+    e->auto_delta = false;
+    TPB_CUDA(e, copy_in(e, e->a.delta_in, delta, sizeof(double) * d.B, on_device));
+    TPB_CUDA(e, copy_in(e, e->a.delta, delta, sizeof(double) * d.B, on_device));
+  }
+  if (e->have_waypoints && delta == nullptr) {
+    // recompute the automatic delta for the current splines
+    e->launches += tpb::launch_joint_fit(d, e->a, e->rounding, true, e->stream);
+    TPB_CUDA(e, cudaGetLastError());
+  }
+  e->sampled = e->optimized = e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_sample_paths(tpb_engine* e, const double* path_start, int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (e->mode != Mode::kJoint || !e->have_waypoints)
+    return fail(e, TPB_FAILED_PRECONDITION, "No path set");
+  if (!e->have_limits) return fail(e, TPB_FAILED_PRECONDITION, "joint limits not set");
+  cudaSetDevice(e->device);
+  TPB_CUDA(e, fill_or_copy(e, e->a.path_start, path_start, d.B, on_device));
+  e->launches += tpb::launch_joint_sample_limit(d, e->a, e->safety, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->sampled = true;
+  e->optimized = e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_set_constraints(tpb_engine* e, int32_t num_paths, int32_t num_constraints,
+                            const double* constraints, const double* s_start,
+                            const double* s_end, int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (d.Cmax == 0) return fail(e, TPB_FAILED_PRECONDITION, "engine has no constraint capacity");
+  if (num_paths < 1 || num_paths > d.Bmax) return fail(e, TPB_OUT_OF_RANGE, "num_paths");
+  if (num_constraints < 1 || num_constraints > d.Cmax)
+    return fail(e, TPB_OUT_OF_RANGE, "num_constraints exceeds max_constraints");
+  if (!constraints || !s_start || !s_end) return fail(e, TPB_INVALID_ARGUMENT, "null input");
+  cudaSetDevice(e->device);
+  d.B = num_paths;
+  d.C = num_constraints;
+  e->mode = Mode::kGeneric;
+  TPB_CUDA(e, copy_in(e, e->a.cons, constraints,
+                      sizeof(double) * static_cast<size_t>(d.B) * d.N * d.C * 4, on_device));
+  TPB_CUDA(e, copy_in(e, e->a.s_start, s_start, sizeof(double) * d.B, on_device));
+  TPB_CUDA(e, copy_in(e, e->a.s_end, s_end, sizeof(double) * d.B, on_device));
+  e->launches += tpb::launch_generic_limit(d, e->a, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->sampled = true;
+  e->optimized = e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_optimize(tpb_engine* e, const double* sd_start, const double* sdd_start,
+                     const double* time_start, int32_t max_loops, int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (!e->sampled) return fail(e, TPB_FAILED_PRECONDITION, "problem not defined/set up");
+  cudaSetDevice(e->device);
+  TPB_CUDA(e, fill_or_copy(e, e->a.sd_start, sd_start, d.B, on_device));
+  TPB_CUDA(e, fill_or_copy(e, e->a.sdd_start, sdd_start, d.B, on_device));
+  TPB_CUDA(e, fill_or_copy(e, e->a.time_start, time_start, d.B, on_device));
+  if (max_loops <= 0) max_loops = std::max(100, 10 * d.N);
+  e->launches += tpb::launch_integrate(d, e->a, e->mode, e->safety, max_loops, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->optimized = true;
+  e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_resample(tpb_engine* e, double start_sec, double time_step_sec,
+                     int64_t* total_samples) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (e->mode != Mode::kJoint || !e->optimized)
+    return fail(e, TPB_FAILED_PRECONDITION, "no timed joint paths");
+  if (d.r_cap <= 0) return fail(e, TPB_FAILED_PRECONDITION, "max_time_samples_total is 0");
+  if (!(time_step_sec > 0)) return fail(e, TPB_INVALID_ARGUMENT, "time step must be positive");
+  cudaSetDevice(e->device);
+  e->launches += tpb::launch_resample(d, e->a, start_sec, time_step_sec, e->num_sms, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->resampled = true;
+  if (total_samples != nullptr) {
+    int64_t total = 0;
+    TPB_CUDA(e, cudaMemcpyAsync(&total, e->a.r_offset + d.B, sizeof(int64_t),
+                                cudaMemcpyDeviceToHost, e->stream));
+    TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+    *total_samples = total;
+    if (total > d.r_cap)
+      return fail(e, TPB_OUT_OF_RANGE, "resampled rows exceed max_time_samples_total");
+  }
+  return TPB_OK;
+}
+
+int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
+  if (e == nullptr || io == nullptr) return TPB_INVALID_ARGUMENT;
+  int32_t rc;
+  if ((rc = tpb_set_joint_waypoints(e, io->num_paths, io->num_waypoints, io->waypoints, 0))) return rc;
+  if ((rc = tpb_set_joint_limits(e, io->max_velocity, io->max_acceleration, 1, 0))) return rc;
+  if ((rc = tpb_sample_paths(e, nullptr, 0))) return rc;
+  // fresh path: sd_start = sdd_start = 0, time_start = start (path_timing_trajectory.cc:322-326)
+  const auto& d = e->dims;
+  cudaSetDevice(e->device);
+  TPB_CUDA(e, cudaMemsetAsync(e->a.sd_start, 0, sizeof(double) * d.B, e->stream));
+  TPB_CUDA(e, cudaMemsetAsync(e->a.sdd_start, 0, sizeof(double) * d.B, e->stream));
+  e->launches += tpb::launch_fill_f64(e->a.time_start, io->start_sec, d.B, e->stream);
+  e->launches += tpb::launch_integrate(d, e->a, e->mode, e->safety, std::max(100, 10 * d.N),
+                                       e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->optimized = true;
+  e->resampled = false;
+  io->r_total = 0;
+  const bool want_rows = io->time_step_sec > 0 && d.r_cap > 0;
+  if (want_rows) {
+    if ((rc = tpb_resample(e, io->start_sec, io->time_step_sec, nullptr))) return rc;
+  }
+  if (io->duration)
+    TPB_CUDA(e, cudaMemcpyAsync(io->duration, e->a.duration, sizeof(double) * d.B, cudaMemcpyDeviceToHost, e->stream));
+  if (io->status)
+    TPB_CUDA(e, cudaMemcpyAsync(io->status, e->a.status, sizeof(int32_t) * d.B, cudaMemcpyDeviceToHost, e->stream));
+  if (want_rows) {
+    int64_t total = 0;
+    TPB_CUDA(e, cudaMemcpyAsync(&total, e->a.r_offset + d.B, sizeof(int64_t), cudaMemcpyDeviceToHost, e->stream));
+    if (io->r_offset)
+      TPB_CUDA(e, cudaMemcpyAsync(io->r_offset, e->a.r_offset, sizeof(int64_t) * (d.B + 1), cudaMemcpyDeviceToHost, e->stream));
+    TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+    io->r_total = total;
+    if (total > d.r_cap)
+      return fail(e, TPB_OUT_OF_RANGE, "resampled rows exceed max_time_samples_total");
+    const size_t rows = static_cast<size_t>(total);
+    const bool any_out = io->r_pos || io->r_vel || io->r_acc || io->r_s || io->r_sd || io->r_sdd;
+    if (any_out && total > io->r_capacity)
+      return fail(e, TPB_OUT_OF_RANGE, "resampled rows exceed r_capacity");
+    const size_t D = d.D;
+    if (io->r_pos) TPB_CUDA(e, cudaMemcpyAsync(io->r_pos, e->a.r_pos, rows * D * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    if (io->r_vel) TPB_CUDA(e, cudaMemcpyAsync(io->r_vel, e->a.r_vel, rows * D * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    if (io->r_acc) TPB_CUDA(e, cudaMemcpyAsync(io->r_acc, e->a.r_acc, rows * D * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    if (io->r_s) TPB_CUDA(e, cudaMemcpyAsync(io->r_s, e->a.r_s, rows * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    if (io->r_sd) TPB_CUDA(e, cudaMemcpyAsync(io->r_sd, e->a.r_sd, rows * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    if (io->r_sdd) TPB_CUDA(e, cudaMemcpyAsync(io->r_sdd, e->a.r_sdd, rows * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  }
+  TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+  return TPB_OK;
+}
+
+int32_t tpb_get(tpb_engine* e, tpb_array what, void* dst, size_t bytes, int32_t to_device) {
+  if (e == nullptr || dst == nullptr) return TPB_INVALID_ARGUMENT;
+  cudaSetDevice(e->device);
+  if (e->dims.B == 0) return fail(e, TPB_FAILED_PRECONDITION, "no batch set");
+  if (is_joint_array(what) && e->mode != Mode::kJoint)
+    return fail(e, TPB_FAILED_PRECONDITION, "array only exists for joint paths");
+  ArrayRef r;
+  if (!lookup(e, what, &r) || r.ptr == nullptr) return fail(e, TPB_NOT_FOUND, "unknown array");
+  if (bytes < r.bytes) return fail(e, TPB_OUT_OF_RANGE, "destination too small");
+  TPB_CUDA(e, cudaMemcpyAsync(dst, r.ptr, r.bytes,
+                              to_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost,
+                              e->stream));
+  if (!to_device) TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+  return TPB_OK;
+}
+
+int32_t tpb_devptr(tpb_engine* e, tpb_array what, void** ptr, size_t* bytes) {
+  if (e == nullptr || ptr == nullptr) return TPB_INVALID_ARGUMENT;
+  cudaSetDevice(e->device);
+  ArrayRef r;
+  if (!lookup(e, what, &r) || r.ptr == nullptr) return fail(e, TPB_NOT_FOUND, "unknown array");
+  *ptr = r.ptr;
+  if (bytes) *bytes = r.bytes;
+  return TPB_OK;
+}
+
+int32_t tpb_spline_eval_device(const tpb_spline_eval_desc* d, void* cuda_stream) {
+  if (d == nullptr) return TPB_INVALID_ARGUMENT;
+  std::string err;
+  const int rc = tpb::launch_spline_eval(*d, static_cast<cudaStream_t>(cuda_stream), &err);
+  if (rc != TPB_OK) fprintf(stderr, "tpb_spline_eval_device: %s\n", err.c_str());
+  return rc;
+}
+
+int32_t tpb_spline_eval_host(const tpb_spline_eval_desc* hd, int32_t device) {
+  if (hd == nullptr) return TPB_INVALID_ARGUMENT;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return TPB_FAILED_PRECONDITION;
+  }
+  if (device < 0 || device >= ndev) return TPB_INVALID_ARGUMENT;
+  if (cudaSetDevice(device) != cudaSuccess) return TPB_INTERNAL;
+  if (hd->num_splines < 1 || hd->evals_per_spline < 0 || hd->num_points < 1 || hd->dim < 1)
+    return TPB_INVALID_ARGUMENT;
+  tpb_spline_eval_desc d = *hd;
+  const size_t S = hd->num_splines, E = static_cast<size_t>(hd->evals_per_spline);
+  const size_t nk = static_cast<size_t>(hd->num_points) + hd->degree + 1;
+  const size_t nout = S * E * (hd->nder + 1) * hd->dim;
+  std::vector<void*> tmp;
+  auto up = [&](const void* src, size_t bytes, const void** dst) -> cudaError_t {
+    if (src == nullptr) {
+      *dst = nullptr;
+      return cudaSuccess;
+    }
+    void* p = nullptr;
+    cudaError_t err = cudaMalloc(&p, bytes ? bytes : 1);
+    if (err != cudaSuccess) return err;
+    tmp.push_back(p);
+    *dst = p;
+    return cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice);
+  };
+  cudaError_t err = cudaSuccess;
+  const void *dk = nullptr, *dc = nullptr, *du_ = nullptr, *du0 = nullptr, *ddu = nullptr;
+  if (err == cudaSuccess) err = up(hd->knots, S * nk * sizeof(double), &dk);
+  if (err == cudaSuccess) err = up(hd->ctrl, S * hd->num_points * hd->dim * sizeof(double), &dc);
+  if (err == cudaSuccess) err = up(hd->u, S * E * sizeof(double), &du_);
+  if (err == cudaSuccess) err = up(hd->u0, S * sizeof(double), &du0);
+  if (err == cudaSuccess) err = up(hd->du, S * sizeof(double), &ddu);
+  double* dout = nullptr;
+  int32_t* dst = nullptr;
+  if (err == cudaSuccess) err = cudaMalloc(&dout, std::max<size_t>(nout, 1) * sizeof(double));
+  if (err == cudaSuccess) tmp.push_back(dout);
+  // rows that fail the range check keep the caller's contents (like the reference)
+  if (err == cudaSuccess && hd->out)
+    err = cudaMemcpy(dout, hd->out, nout * sizeof(double), cudaMemcpyHostToDevice);
+  if (err == cudaSuccess && hd->status) {
+    err = cudaMalloc(&dst, std::max<size_t>(S * E, 1) * sizeof(int32_t));
+    if (err == cudaSuccess) tmp.push_back(dst);
+  }
+  int32_t rc = TPB_OK;
+  if (err == cudaSuccess) {
+    d.knots = static_cast<const double*>(dk);
+    d.ctrl = static_cast<const double*>(dc);
+    d.u = static_cast<const double*>(du_);
+    d.u0 = static_cast<const double*>(du0);
+    d.du = static_cast<const double*>(ddu);
+    d.out = dout;
+    d.status = dst;
+    std::string msg;
+    rc = tpb::launch_spline_eval(d, nullptr, &msg);
+    if (rc == TPB_OK) err = cudaDeviceSynchronize();
+    if (rc != TPB_OK) fprintf(stderr, "tpb_spline_eval_host: %s\n", msg.c_str());
+  }
+  if (rc == TPB_OK && err == cudaSuccess && hd->out)
+    err = cudaMemcpy(hd->out, dout, nout * sizeof(double), cudaMemcpyDeviceToHost);
+  if (rc == TPB_OK && err == cudaSuccess && hd->status)
+    err = cudaMemcpy(hd->status, dst, S * E * sizeof(int32_t), cudaMemcpyDeviceToHost);
+  for (void* p : tmp) cudaFree(p);
+  if (err != cudaSuccess) {
+    fprintf(stderr, "tpb_spline_eval_host: %s\n", cudaGetErrorString(err));
+    return TPB_INTERNAL;
+  }
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,114 @@
+// Device-resident state of one engine (one GPU, one stream) and the kernel
+// launchers the C ABI calls.  Layout in HBM (B paths, N samples, D dofs,
+// n <= max_points control points, C rows):
+//
+//   waypoints  [B][Wmax][D]      num_wp [B]          inputs
+//   vmax, amax [B][D]                                inputs (broadcast if shared)
+//   ctrl       [B][max_points][D] knots [B][max_points+3]  num_points [B]
+//   q, dq, ddq [B][N][D]         SamplePath outputs (AoS like the reference's
+//                                vector<VectorXd>; one 56-byte row per sample)
+//   cons       [B][N][C][4]      explicit constraint rows (generic problems only;
+//                                joint paths never materialise them)
+//   b_sd2_max, b_sdd_max, b_sdd_min, b_sd2_zero [B][N], b_at0/b_type u8 [B][N]
+//   sd2, sdd, sd, s, time [B][N] solver state / outputs
+//   status, last_extremal i32 [B]; duration, delta, knot_end, s_start, s_end [B]
+//   r_count i32 [B], r_offset i64 [B+1], r_* packed rows
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <string>
+
+#include <cuda_runtime.h>
+
+#include "../../include/tpb.h"
+
+namespace tpb {
+
+struct DeviceArrays {
+  // inputs
+  double* waypoints = nullptr;
+  int32_t* num_wp = nullptr;
+  double* vmax = nullptr;
+  double* amax = nullptr;
+  double* delta_in = nullptr;
+  double* path_start = nullptr;
+  double* sd_start = nullptr;
+  double* sdd_start = nullptr;
+  double* time_start = nullptr;
+  // spline
+  double* ctrl = nullptr;
+  double* knots = nullptr;
+  int32_t* num_points = nullptr;
+  double* delta = nullptr;
+  double* knot_end = nullptr;
+  // samples
+  double* q = nullptr;
+  double* dq = nullptr;
+  double* ddq = nullptr;
+  // generic constraints
+  double* cons = nullptr;
+  double* s_start = nullptr;
+  double* s_end = nullptr;
+  // limit curve: per-sample values as computed (raw) + the working copy that
+  // CalculateBoundary's passes 2-4 mutate
+  double* b_raw_sd2_max = nullptr;
+  double* b_raw_sdd_max = nullptr;
+  double* b_raw_sdd_min = nullptr;
+  double* b_sd2_max = nullptr;
+  double* b_sdd_max = nullptr;
+  double* b_sdd_min = nullptr;
+  double* b_sd2_zero = nullptr;
+  uint8_t* b_at0 = nullptr;
+  uint8_t* b_type = nullptr;
+  // solver
+  double* sd2 = nullptr;
+  double* sdd = nullptr;
+  double* sd = nullptr;
+  double* s = nullptr;
+  double* time = nullptr;
+  double* fix_val = nullptr;  // [B][N] scratch for deferred boundary fixes
+  int32_t* status = nullptr;
+  int32_t* last_extremal = nullptr;
+  double* duration = nullptr;
+  // resampled
+  int32_t* r_count = nullptr;
+  int64_t* r_offset = nullptr;
+  double* r_time = nullptr;
+  double* r_pos = nullptr;
+  double* r_vel = nullptr;
+  double* r_acc = nullptr;
+  double* r_s = nullptr;
+  double* r_sd = nullptr;
+  double* r_sdd = nullptr;
+};
+
+struct Dims {
+  int B = 0;        // current batch
+  int Bmax = 0;
+  int D = 0;
+  int Wmax = 0;
+  int max_points = 0;  // 3*Wmax-2 (>= 4)
+  int N = 0;
+  int Cmax = 0;  // capacity of explicit rows
+  int C = 0;     // rows of the current problem (2*D for joint paths)
+  int64_t r_cap = 0;
+};
+
+enum class Mode { kNone, kJoint, kGeneric };
+
+// ---- kernel launchers (tpb_kernels.cu); each returns the number of kernels
+// it launched.
+int launch_fill_f64(double* p, double v, int n, cudaStream_t st);
+int launch_fill_i32(int32_t* p, int32_t v, int n, cudaStream_t st);
+int launch_joint_fit(const Dims& d, const DeviceArrays& a, double rounding, bool auto_delta,
+                     cudaStream_t st);
+int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safety,
+                              cudaStream_t st);
+int launch_generic_limit(const Dims& d, const DeviceArrays& a, cudaStream_t st);
+int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double safety,
+                     int max_loops, cudaStream_t st);
+int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, double dt,
+                    int num_sms, cudaStream_t st);
+
+}  // namespace tpb

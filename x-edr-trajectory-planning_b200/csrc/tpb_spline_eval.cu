@@ -1,0 +1,195 @@
+// Dense B-spline evaluation with derivatives (stage A stand-alone, BASELINE
+// config 3): BSplineT::EvalCurveAndDerivatives, splines/bspline.h:539-568, over
+// many splines x many parameters.
+//
+// One CTA handles a tile of kTile consecutive parameters of one spline.  The
+// spline's knot vector and control points are staged in shared memory once per
+// CTA; each thread evaluates one parameter in FP64 registers (NURBS A2.1-A2.3
+// in the reference's operation order), the (nder+1) x dim results of the tile
+// are transposed through shared memory and leave the SM as one contiguous,
+// 16-byte-vectorised stream (the tile's output rows are contiguous in HBM).
+#include <string>
+
+#include "tpb_device.cuh"
+#include "../../include/tpb.h"
+
+namespace tpb {
+namespace {
+
+constexpr int kTile = 128;  // parameters per CTA == threads per CTA
+
+struct EvalArgs {
+  int num_points, dim, num_splines;
+  long long evals;
+  const double* knots;
+  const double* ctrl;
+  const double* u;
+  const double* u0;
+  const double* du;
+  double* out;
+  int32_t* status;
+};
+
+template <int P, int NDER>
+__global__ void __launch_bounds__(kTile) k_spline_eval(EvalArgs g) {
+  extern __shared__ double smem[];
+  const int nk = g.num_points + P + 1;
+  const int D = g.dim;
+  constexpr int K = NDER + 1;
+  double* s_knots = smem;                 // [nk]
+  double* s_ctrl = s_knots + nk;          // [num_points][D]
+  double* s_out = s_ctrl + g.num_points * D;  // [kTile][K*D]
+  const int s = blockIdx.y;
+  {
+    const double* gk = g.knots + static_cast<size_t>(s) * nk;
+    const double* gc = g.ctrl + static_cast<size_t>(s) * g.num_points * D;
+    for (int i = threadIdx.x; i < nk; i += kTile) s_knots[i] = gk[i];
+    for (int i = threadIdx.x; i < g.num_points * D; i += kTile) s_ctrl[i] = gc[i];
+  }
+  __syncthreads();
+  const long long e0 = static_cast<long long>(blockIdx.x) * kTile;
+  const long long e = e0 + threadIdx.x;
+  const int rowlen = K * D;
+  bool ok = false;
+  if (e < g.evals) {
+    const size_t flat = static_cast<size_t>(s) * g.evals + e;
+    const double u = g.u ? g.u[flat] : (g.u0[s] + static_cast<double>(e) * g.du[s]);
+    // range check of EvalCurveAndDerivatives (bspline.h:549-552); NaN fails too
+    ok = (u >= s_knots[0]) && (u <= s_knots[nk - 1]);
+    if (g.status) g.status[flat] = ok ? TPB_OK : TPB_OUT_OF_RANGE;
+    if (ok) {
+      const int span = knot_span(s_knots, nk, P, u);
+      double ders[K][P + 1];
+      basis_ders<P, NDER>(s_knots, span, u, ders);
+      const double* P0 = s_ctrl + (span - P) * D;
+      double* o = s_out + threadIdx.x * rowlen;
+      for (int d = 0; d < D; ++d) {
+        double acc[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) acc[k] = 0.0;
+#pragma unroll
+        for (int j = 0; j <= P; ++j) {
+          const double Pj = P0[j * D + d];
+#pragma unroll
+          for (int k = 0; k < K; ++k) acc[k] += ders[k][j] * Pj;
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) o[k * D + d] = acc[k];
+      }
+    }
+  }
+  // Rows that failed the range check must keep the caller's memory: if the
+  // whole tile is in range (the common case) stream it out contiguously,
+  // otherwise fall back to per-row stores.
+  const int all_ok = __syncthreads_and(ok || e >= g.evals);
+  const long long n_in_tile = min(static_cast<long long>(kTile), g.evals - e0);
+  double* gout = g.out + (static_cast<size_t>(s) * g.evals + e0) * rowlen;
+  if (all_ok) {
+    const int total = static_cast<int>(n_in_tile) * rowlen;
+    if ((reinterpret_cast<uintptr_t>(gout) & 15) == 0 && (total & 1) == 0) {
+      const double2* s2 = reinterpret_cast<const double2*>(s_out);
+      double2* g2 = reinterpret_cast<double2*>(gout);
+      for (int i = threadIdx.x; i < total / 2; i += kTile) g2[i] = s2[i];
+    } else {
+      for (int i = threadIdx.x; i < total; i += kTile) gout[i] = s_out[i];
+    }
+  } else if (ok) {
+    const double* o = s_out + threadIdx.x * rowlen;
+    for (int i = 0; i < rowlen; ++i) gout[threadIdx.x * rowlen + i] = o[i];
+  }
+}
+
+template <int P, int NDER>
+void launch_one(const EvalArgs& g, cudaStream_t st) {
+  const int nk = g.num_points + P + 1;
+  const size_t smem = sizeof(double) * (nk + static_cast<size_t>(g.num_points) * g.dim +
+                                        static_cast<size_t>(kTile) * (NDER + 1) * g.dim);
+  cudaFuncSetAttribute(k_spline_eval<P, NDER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       static_cast<int>(smem));
+  dim3 grid(static_cast<unsigned>((g.evals + kTile - 1) / kTile), g.num_splines);
+  k_spline_eval<P, NDER><<<grid, kTile, smem, st>>>(g);
+}
+
+template <int P>
+bool dispatch_nder(int nder, const EvalArgs& g, cudaStream_t st) {
+  if (nder == 0) {
+    launch_one<P, 0>(g, st);
+    return true;
+  }
+  if constexpr (P >= 1) {
+    if (nder == 1) {
+      launch_one<P, 1>(g, st);
+      return true;
+    }
+  }
+  if constexpr (P >= 2) {
+    if (nder == 2) {
+      launch_one<P, 2>(g, st);
+      return true;
+    }
+  }
+  if constexpr (P >= 3) {
+    if (nder == 3) {
+      launch_one<P, 3>(g, st);
+      return true;
+    }
+  }
+  return false;
+}
+
+}  // namespace
+
+int launch_spline_eval(const tpb_spline_eval_desc& d, cudaStream_t st, std::string* err) {
+  if (d.degree < 1 || d.degree > kMaxDegree) {
+    *err = "degree must be in [1, 5]";
+    return TPB_OUT_OF_RANGE;
+  }
+  if (d.nder < 0 || d.nder > d.degree || d.nder > 3) {
+    // reference: CHECK(der <= p), bspline_base.cc:270
+    *err = "nder must be <= degree (and <= 3)";
+    return TPB_INVALID_ARGUMENT;
+  }
+  if (d.num_points < d.degree + 1 || d.dim < 1 || d.num_splines < 1 || d.evals_per_spline < 0) {
+    *err = "bad spline dimensions";
+    return TPB_INVALID_ARGUMENT;
+  }
+  if (!d.knots || !d.ctrl || !d.out || (!d.u && (!d.u0 || !d.du))) {
+    *err = "null pointer";
+    return TPB_INVALID_ARGUMENT;
+  }
+  if (d.num_splines > 65535) {
+    *err = "num_splines > 65535";
+    return TPB_OUT_OF_RANGE;
+  }
+  if (d.evals_per_spline == 0) return TPB_OK;
+  const size_t smem = sizeof(double) * (d.num_points + d.degree + 1 +
+                                        static_cast<size_t>(d.num_points) * d.dim +
+                                        static_cast<size_t>(kTile) * (d.nder + 1) * d.dim);
+  if (smem > 200 * 1024) {
+    *err = "spline tables do not fit in shared memory";
+    return TPB_OUT_OF_RANGE;
+  }
+  EvalArgs g{d.num_points, d.dim,  d.num_splines, static_cast<long long>(d.evals_per_spline),
+             d.knots,      d.ctrl, d.u,           d.u0,
+             d.du,         d.out,  d.status};
+  bool ok = false;
+  switch (d.degree) {
+    case 1: ok = dispatch_nder<1>(d.nder, g, st); break;
+    case 2: ok = dispatch_nder<2>(d.nder, g, st); break;
+    case 3: ok = dispatch_nder<3>(d.nder, g, st); break;
+    case 4: ok = dispatch_nder<4>(d.nder, g, st); break;
+    case 5: ok = dispatch_nder<5>(d.nder, g, st); break;
+  }
+  if (!ok) {
+    *err = "unsupported (degree, nder)";
+    return TPB_UNIMPLEMENTED;
+  }
+  const cudaError_t ce = cudaGetLastError();
+  if (ce != cudaSuccess) {
+    *err = cudaGetErrorString(ce);
+    return TPB_INTERNAL;
+  }
+  return TPB_OK;
+}
+
+}  // namespace tpb
