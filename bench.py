@@ -1,0 +1,452 @@
+#!/usr/bin/env python
+"""Benchmark of the batched path-timing hot path (BASELINE.json metric:
+"7-DoF paths timed/sec at 1/2/4/8 B200; B-spline evals/sec vs HBM roofline").
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (CUDA, C ABI)
+    python bench.py --impl reference --gpus N --steps K ...  # reference CPU arm
+
+One step = one pass of the whole hot path (fit -> SamplePath+ConstraintSetup ->
+limit curve -> Pfeiffer-Johanni phase-plane integration -> trajectory assembly
+and uniform-in-time resampling) over one batch of BASELINE config 2:
+4,096 synthetic 7-DoF joint-spline paths x 2,048 samples per GPU.  With N > 1
+(torchrun, one rank per GPU) every rank times its own shard of independent
+paths (weak scaling, no data-path collective; a final all_gather of the
+durations happens outside the timed region).
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every key.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+from __graft_entry__ import load_oracle, load_package  # noqa: E402
+
+METRIC = "7-DoF paths timed/sec"
+UNIT = "paths/s"
+PATHS_PER_GPU = 4096
+NUM_SAMPLES = 2048
+NUM_WAYPOINTS = 10
+NUM_DOFS = 7
+TIME_STEP = 0.004  # planner time step of the reference tests (4 ms)
+WORKLOAD = ("cfg2: 4096 synthetic 7-DoF joint-spline paths x 2048 samples per GPU, "
+            "time-optimal timing + 4 ms uniform resampling")
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# --------------------------------------------------------------------------
+# clocks
+# --------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100", "-i", str(index)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        self.p.wait()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        self.f.close()
+        os.unlink(self.f.name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------
+# reference arm (CPU): oracle/_ref when compiled, else the oracle port
+# --------------------------------------------------------------------------
+def _cpu_paths_per_sec(po, wp, vmax, amax, threads, impl):
+    """Time the reference's CPU algorithm on `threads` host threads (ctypes
+    releases the GIL, so plain Python threads run the C code concurrently)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    B = wp.shape[0]
+
+    def work(lo_hi):
+        lo, hi = lo_hi
+        ok = 0
+        for b in range(lo, hi):
+            r = po.plan_joint(wp[b], vmax[b], amax[b], NUM_SAMPLES, dt=TIME_STEP,
+                              M_cap=16384, impl=impl)
+            ok += bool(r["ok"])
+        return ok
+
+    chunks = [(i * B // threads, (i + 1) * B // threads) for i in range(threads)]
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        ok = sum(ex.map(work, chunks))
+    dt = time.perf_counter() - t0
+    return B / dt, dt, ok
+
+
+def _cpu_setup():
+    po = load_oracle()
+    po.build()
+    impl = "ref" if po.have_ref() else "port"
+    kind = "reference" if impl == "ref" else "port"
+    cores = os.cpu_count() or 1
+    return po, impl, kind, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    pkg = load_package()
+    po, impl, kind, cores = _cpu_setup()
+    sample = max(64, 32 * cores)
+    wp, vmax, amax = pkg.workloads.joint_paths(PATHS_PER_GPU, NUM_WAYPOINTS, NUM_DOFS, 1000)
+    wp, vmax, amax = wp[:sample], vmax[:sample], amax[:sample]
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    saved = os.dup(2)
+    os.dup2(devnull, 2)  # the reference logs "Negative sd2" hints to stderr
+    try:
+        for _ in range(args.warmup):
+            _cpu_paths_per_sec(po, wp, vmax, amax, cores, impl)
+        times = []
+        for _ in range(args.steps):
+            _, dt, _ = _cpu_paths_per_sec(po, wp, vmax, amax, cores, impl)
+            times.append(dt)
+    finally:
+        os.dup2(saved, 2)
+    ms = 1e3 * float(np.mean(times))
+    value = sample / (ms / 1e3)
+    desc = (f"first {sample} paths of the cfg2 batch per step; stage C = reference "
+            f"time_optimal_path_timing.cc compiled verbatim (oracle/_ref), stages A/B/D = C "
+            f"restatement" if kind == "reference" else
+            f"first {sample} paths of the cfg2 batch per step; C restatement of all stages")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD, "paths_per_step": sample, "num_samples": NUM_SAMPLES,
+                   "num_dofs": NUM_DOFS, "host_threads": cores},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": desc},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# --------------------------------------------------------------------------
+# our arm (CUDA through the C ABI)
+# --------------------------------------------------------------------------
+def _bytes_per_sample_model(D):
+    """Algorithmic HBM bytes per path sample of each stage kernel."""
+    return {
+        # writes q,q',q'' + (sd2_max, sd2_zero, sdd_max, sdd_min) + flag
+        "sample_limit": (3 * D + 4) * 8 + 1,
+        # reads raw limit curve (3x8) + sd2_zero (8) + flag (1) + q',q'' (2D x 8);
+        # writes working limit curve (3x8) + type (1) + s, sd2, sdd, sd, time (5x8)
+        "integrate": 3 * 8 + 8 + 1 + 2 * D * 8 + 3 * 8 + 1 + 5 * 8,
+    }
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback "
+                         "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    pkg = load_package()
+    B, N, D, W = PATHS_PER_GPU, NUM_SAMPLES, NUM_DOFS, NUM_WAYPOINTS
+    wp, vmax, amax = pkg.workloads.joint_paths(B * world, W, D, seed=1000)
+    sl = slice(rank * B, (rank + 1) * B)
+    wp, vmax, amax = wp[sl].copy(), vmax[sl].copy(), amax[sl].copy()
+    d_wp = torch.from_numpy(wp).to(dev)
+    d_vmax = torch.from_numpy(vmax).to(dev)
+    d_amax = torch.from_numpy(amax).to(dev)
+
+    r_cap = B * 6144
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=r_cap, device=local_rank)
+    # a dedicated (non-default) stream shared by torch's events and the engine:
+    # tpb_set_stream(NULL) would mean "engine-owned stream", and torch.cuda.Event
+    # only sees work on the stream it is recorded on
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
+    eng.set_stream(stream.cuda_stream)
+
+    def stage_fit():
+        eng.set_joint_waypoints(d_wp)
+        eng.set_joint_limits(d_vmax, d_amax)
+
+    def step_device():
+        stage_fit()
+        eng.sample_paths()
+        eng.optimize()
+        eng.resample(0.0, TIME_STEP, want_total=False)
+
+    # ---- value: inputs resident in HBM, CUDA events on the launching stream ----
+    for _ in range(args.warmup):
+        step_device()
+    torch.cuda.synchronize()
+    barrier()
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    l0 = eng.kernel_launches
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    barrier()
+    elapsed_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    launches = eng.kernel_launches - l0
+    clock_info = clocks.stop() if clocks else None
+    ms_per_step = elapsed_ms / args.steps
+    value = B * world / (ms_per_step / 1e3)
+
+    status = eng.get(pkg.ARR.STATUS)
+    durations = eng.get(pkg.ARR.DURATION)
+    n_ok = int((status == 0).sum())
+    total_rows = int(eng.get(pkg.ARR.R_OFFSET)[-1])
+    if total_rows > r_cap:
+        raise SystemExit(f"resampled rows {total_rows} exceed capacity {r_cap}")
+
+    # ---- per-stage device times (same work, events around each C-ABI stage) ----
+    stage_ms = {"fit": 0.0, "sample_limit": 0.0, "integrate": 0.0, "resample": 0.0}
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+    reps = max(3, args.steps)
+    for _ in range(reps):
+        evs[0].record(stream)
+        stage_fit()
+        evs[1].record(stream)
+        eng.sample_paths()
+        evs[2].record(stream)
+        eng.optimize()
+        evs[3].record(stream)
+        eng.resample(0.0, TIME_STEP, want_total=False)
+        evs[4].record(stream)
+        torch.cuda.synchronize()
+        for i, k in enumerate(stage_ms):
+            stage_ms[k] += evs[i].elapsed_time(evs[i + 1]) / reps
+    peak, peak_src = _peaks()
+    model = _bytes_per_sample_model(D)
+    dom = max(("sample_limit", "integrate", "resample"), key=lambda k: stage_ms[k])
+    if dom == "resample":
+        alg_bytes = total_rows * (3 * D + 4) * 8 + B * N * (3 * D + 4) * 8
+    else:
+        alg_bytes = B * N * model[dom]
+    achieved = alg_bytes / (stage_ms[dom] / 1e3) / 1e9
+    kernel_names = {"sample_limit": "k_joint_sample_limit", "integrate": "k_integrate",
+                    "resample": "k_resample_fill"}
+    roofline = {"bound": "hbm", "kernel": kernel_names[dom], "achieved": achieved,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                "avg_launch_ms": stage_ms[dom],
+                "note": ("k_integrate is a sequential FP64 phase-plane sweep, one warp per "
+                         "path: latency/FP64-issue bound, not HBM bound (DESIGN.md)")
+                if dom == "integrate" else ""}
+
+    # ---- e2e: host buffers in and out through tpb_plan_joint_host ----
+    h_wp = torch.from_numpy(wp).pin_memory()
+    h_vmax = torch.from_numpy(vmax).pin_memory()
+    h_amax = torch.from_numpy(amax).pin_memory()
+    rows = total_rows
+    out = {"duration": torch.empty(B, dtype=torch.float64).pin_memory(),
+           "status": torch.empty(B, dtype=torch.int32).pin_memory(),
+           "r_offset": torch.empty(B + 1, dtype=torch.int64).pin_memory()}
+    for k in ("r_pos", "r_vel", "r_acc"):
+        out[k] = torch.empty((rows, D), dtype=torch.float64).pin_memory()
+    for k in ("r_s", "r_sd", "r_sdd"):
+        out[k] = torch.empty(rows, dtype=torch.float64).pin_memory()
+
+    def step_host():
+        return eng.plan_joint_host(h_wp, h_vmax, h_amax, 0.0, TIME_STEP, out=out)
+
+    for _ in range(min(args.warmup, 3)):
+        step_host()
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        got = step_host()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0) / args.steps
+    barrier()
+    assert got == rows
+    h2d = wp.nbytes + vmax.nbytes + amax.nbytes
+    d2h = B * 8 + B * 4 + (B + 1) * 8 + rows * (3 * D + 3) * 8
+    e2e = {"value": B * world / e2e_s, "unit": UNIT, "ms_per_step": 1e3 * e2e_s,
+           "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+           "api": "tpb_plan_joint_host (pinned host buffers in/out)"}
+    same = bool(np.array_equal(out["duration"].numpy(), durations, equal_nan=True))
+
+    # ---- dense spline evaluation sweep (BASELINE config 3) ----
+    spline = run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, world,
+                              args)
+
+    # ---- final gather of the per-path durations (outside any timed region) ----
+    if world > 1:
+        g = [torch.empty(B, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(g, torch.from_numpy(durations).to(dev))
+        all_dur = torch.cat(g).cpu().numpy()
+    else:
+        all_dur = durations
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        po, impl, kind, cores = _cpu_setup()
+        sample = max(64, 32 * cores)
+        devnull = os.open(os.devnull, os.O_WRONLY)
+        saved = os.dup(2)
+        os.dup2(devnull, 2)
+        try:
+            _cpu_paths_per_sec(po, wp[:cores], vmax[:cores], amax[:cores], cores, impl)
+            v, dt, ok = _cpu_paths_per_sec(po, wp[:sample], vmax[:sample], amax[:sample],
+                                           cores, impl)
+        finally:
+            os.dup2(saved, 2)
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
+                        "sample": f"first {sample} paths of this batch, {dt:.1f} s wall, "
+                                  f"{cores} host threads (stage C = reference .cc verbatim)"
+                        if kind == "reference" else
+                        f"first {sample} paths of this batch, {dt:.1f} s wall, oracle port"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "paths_per_gpu": B, "num_samples": N,
+                       "num_dofs": D, "num_waypoints": W, "time_step_s": TIME_STEP,
+                       "l2": "per-step working set ~2 GB per GPU (> 126 MB L2), no flush needed",
+                       "parallelism": f"independent-path sharding x{world}"},
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
+            "gpu_launches": int(launches), "clocks": clock_info,
+            "stage_ms": stage_ms, "paths_ok": n_ok, "resampled_rows_per_gpu": total_rows,
+            "mean_duration_s": float(np.nanmean(all_dur)),
+            "e2e_matches_device_run": same, "spline_eval": spline,
+        }
+        print(json.dumps(line))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, world, args):
+    """BASELINE config 3: 4,096 splines x 24,576 parameters = 1.007e8 evaluations
+    with 1st/2nd derivatives per (degree, dim); output [S][E][3][dim] in HBM."""
+    if args.no_spline:
+        return None
+    S, E, npts = 4096, 24576, 32
+    res = {}
+    out = torch.empty(S * E * 3 * 7, dtype=torch.float64, device=dev)
+    for P in (3, 4, 5):
+        for D in (7, 6):
+            knots, ctrl = pkg.workloads.dense_splines(S, P, D, npts, 8.0)
+            d_k = torch.from_numpy(knots).to(dev)
+            d_c = torch.from_numpy(ctrl).to(dev)
+            u0 = torch.zeros(S, dtype=torch.float64, device=dev)
+            du = torch.full((S,), 8.0 / (E - 1), dtype=torch.float64, device=dev)
+            o = out[:S * E * 3 * D].view(S, E, 3, D)
+
+            def run():
+                pkg.spline_eval_device(d_k, d_c, P, 2, o, u0=u0, du=du, evals=E,
+                                       exact=False, stream=stream.cuda_stream)
+            for _ in range(3):
+                run()
+            torch.cuda.synchronize()
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = 5
+            e0.record(stream)
+            for _ in range(reps):
+                run()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            ms = max_over_ranks(e0.elapsed_time(e1)) / reps
+            gbs = S * E * 3 * D * 8 / (ms / 1e3) / 1e9
+            res[f"p{P}_d{D}"] = {"evals_per_s": world * S * E / (ms / 1e3), "ms": ms,
+                                 "hbm_gbs_per_gpu": gbs, "frac_of_peak": gbs / peak}
+    res["bytes_per_eval"] = "3*dim*8 written (implicit parameter grid, tables in smem)"
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-spline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -32,13 +32,14 @@ struct EvalArgs {
 
 template <int P, int NDER>
 __global__ void __launch_bounds__(kTile) k_spline_eval(EvalArgs g) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
   const int nk = g.num_points + P + 1;
   const int D = g.dim;
   constexpr int K = NDER + 1;
   double* s_knots = smem;                 // [nk]
   double* s_ctrl = s_knots + nk;          // [num_points][D]
-  double* s_out = s_ctrl + g.num_points * D;  // [kTile][K*D]
+  // 16-byte aligned so the tile can be streamed out as double2
+  double* s_out = smem + ((nk + g.num_points * D + 1) & ~1);  // [kTile][K*D]
   const int s = blockIdx.y;
   {
     const double* gk = g.knots + static_cast<size_t>(s) * nk;
@@ -102,7 +103,7 @@ __global__ void __launch_bounds__(kTile) k_spline_eval(EvalArgs g) {
 template <int P, int NDER>
 void launch_one(const EvalArgs& g, cudaStream_t st) {
   const int nk = g.num_points + P + 1;
-  const size_t smem = sizeof(double) * (nk + static_cast<size_t>(g.num_points) * g.dim +
+  const size_t smem = sizeof(double) * (nk + static_cast<size_t>(g.num_points) * g.dim + 1 +
                                         static_cast<size_t>(kTile) * (NDER + 1) * g.dim);
   cudaFuncSetAttribute(k_spline_eval<P, NDER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                        static_cast<int>(smem));
@@ -162,7 +163,7 @@ int launch_spline_eval(const tpb_spline_eval_desc& d, cudaStream_t st, std::stri
     return TPB_OUT_OF_RANGE;
   }
   if (d.evals_per_spline == 0) return TPB_OK;
-  const size_t smem = sizeof(double) * (d.num_points + d.degree + 1 +
+  const size_t smem = sizeof(double) * (d.num_points + d.degree + 2 +
                                         static_cast<size_t>(d.num_points) * d.dim +
                                         static_cast<size_t>(kTile) * (d.nder + 1) * d.dim);
   if (smem > 200 * 1024) {
