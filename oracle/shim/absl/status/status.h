@@ -6,7 +6,7 @@
 #ifndef ORACLE_SHIM_ABSL_STATUS_STATUS_H_
 #define ORACLE_SHIM_ABSL_STATUS_STATUS_H_
 
-#include <sstream>
+#include <cstdio>
 #include <string>
 #include <utility>
 
@@ -64,11 +64,24 @@ inline Status OutOfRangeError(std::string m) {
 }
 
 // The reference .cc calls absl::StrCat without including str_cat.h directly.
+// (No iostreams here: this library is dlopen()ed with a static libstdc++.)
+namespace shim_detail {
+inline void Append(std::string* out, const char* v) { out->append(v); }
+inline void Append(std::string* out, const std::string& v) { out->append(v); }
+inline void Append(std::string* out, int v) { out->append(std::to_string(v)); }
+inline void Append(std::string* out, long v) { out->append(std::to_string(v)); }
+inline void Append(std::string* out, unsigned long v) { out->append(std::to_string(v)); }
+inline void Append(std::string* out, double v) {
+  char buf[40];
+  std::snprintf(buf, sizeof(buf), "%g", v);
+  out->append(buf);
+}
+}  // namespace shim_detail
 template <typename... Args>
 std::string StrCat(const Args&... args) {
-  std::ostringstream os;
-  (os << ... << args);
-  return os.str();
+  std::string out;
+  (shim_detail::Append(&out, args), ...);
+  return out;
 }
 
 }  // namespace absl
