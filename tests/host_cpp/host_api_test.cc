@@ -1,0 +1,232 @@
+// Exercises the host C++ mirror of the reference API (host/include/...) the way
+// the reference's own tests do (path_timing_trajectory_test.cc:88-173,
+// time_optimal_path_timing_test.cc:496-559, splines/bspline_test.cc:730-840) and
+// prints the results as one JSON object; tests/test_gpu_host_cpp.py compares
+// them with the CPU oracle.  Needs a GPU.
+#include <cmath>
+#include <cstdio>
+#include <memory>
+#include <vector>
+
+#include "trajectory_planning/path_timing_batch.h"
+#include "trajectory_planning/path_timing_trajectory.h"
+#include "trajectory_planning/splines/bspline.h"
+#include "trajectory_planning/time_optimal_path_timing.h"
+#include "trajectory_planning/timeable_path_joint_spline.h"
+
+using namespace trajectory_planning;  // NOLINT
+using tp::VectorXd;
+
+static int g_fail = 0;
+#define EXPECT(cond)                                                     \
+  do {                                                                   \
+    if (!(cond)) {                                                       \
+      fprintf(stderr, "EXPECT failed %s:%d: %s\n", __FILE__, __LINE__, #cond); \
+      ++g_fail;                                                          \
+    }                                                                    \
+  } while (0)
+
+static void PrintArray(const char* name, const std::vector<double>& v, bool comma = true) {
+  printf("\"%s\": [", name);
+  for (size_t i = 0; i < v.size(); ++i) printf("%s%.17g", i ? "," : "", v[i]);
+  printf("]%s\n", comma ? "," : "");
+}
+static std::vector<double> Flatten(const std::vector<VectorXd>& v) {
+  std::vector<double> out;
+  for (const auto& x : v) out.insert(out.end(), x.begin(), x.end());
+  return out;
+}
+
+int main() {
+  constexpr size_t kNDof = 3, kNumSamples = 1000;
+  printf("{\n");
+  // ---- PathErrors (path_timing_trajectory_test.cc:88-109)
+  {
+    auto more_dofs = std::make_shared<TimeableJointSplinePath>(
+        JointPathOptions().set_num_dofs(kNDof + 1).set_num_path_samples(kNumSamples));
+    auto more_samples = std::make_shared<TimeableJointSplinePath>(
+        JointPathOptions().set_num_dofs(kNDof).set_num_path_samples(kNumSamples + 1));
+    PathTimingTrajectory planner(PathTimingTrajectoryOptions()
+                                     .SetTimeStep(tp::Milliseconds(4))
+                                     .SetNumDofs(kNDof)
+                                     .SetNumPathSamples(kNumSamples));
+    EXPECT(planner.SetPath(nullptr).code() == tp::StatusCode::kInvalidArgument);
+    EXPECT(planner.SetPath(more_dofs).code() == tp::StatusCode::kInvalidArgument);
+    EXPECT(planner.SetPath(more_samples).code() == tp::StatusCode::kInvalidArgument);
+    EXPECT(planner.Plan(TimeFromSec(0), tp::Seconds(1)).code() == tp::StatusCode::kFailedPrecondition);
+  }
+  // ---- RestToRestPlanningWorks (:112-173), with delta chosen so that the whole
+  // path fits one planning window
+  {
+    auto path = std::make_shared<TimeableJointSplinePath>(JointPathOptions()
+                                                              .set_num_dofs(kNDof)
+                                                              .set_num_path_samples(kNumSamples)
+                                                              .set_delta_parameter(0.016));
+    PathTimingTrajectory planner(PathTimingTrajectoryOptions()
+                                     .SetTimeStep(tp::Milliseconds(4))
+                                     .SetNumDofs(kNDof)
+                                     .SetNumPathSamples(kNumSamples));
+    EXPECT(planner.SetPath(path).ok());
+    EXPECT(path->GetState() == TimeablePath::State::kNoPath);
+    std::vector<VectorXd> wps = {VectorXd{1, 2, 3}, VectorXd{-1, -2, -3}, VectorXd{1, 2, 3}};
+    EXPECT(path->SetWaypoints(wps).ok());
+    EXPECT(path->GetState() == TimeablePath::State::kNewPath);
+    EXPECT(path->SetWaypoints(std::vector<VectorXd>{VectorXd{1, 2}}).code() ==
+           tp::StatusCode::kInvalidArgument);
+    EXPECT(path->SetWaypoints(wps).ok());
+    VectorXd vmax = VectorXd::Constant(kNDof, 1.0), amax = VectorXd::Constant(kNDof, 2.0);
+    EXPECT(path->SetMaxJointVelocity(ToSpan(vmax)).ok());
+    EXPECT(path->SetMaxJointAcceleration(ToSpan(amax)).ok());
+    EXPECT(path->SetMaxJointVelocity(std::vector<double>{1.0}).code() == tp::StatusCode::kInvalidArgument);
+    const tp::Status st = planner.Plan(TimeFromSec(0.0), tp::Seconds(100));
+    EXPECT(st.ok());
+    if (!st.ok()) fprintf(stderr, "Plan: %s\n", st.message().c_str());
+    EXPECT(path->GetState() == TimeablePath::State::kPathWasSampled);
+    EXPECT(planner.IsTrajectoryAtEnd());
+    const auto& pos = planner.GetPositions();
+    EXPECT(!pos.empty());
+    if (!pos.empty()) {
+      EXPECT(pos.back() == wps.back());  // ends exactly at the last waypoint (:167-172)
+      for (size_t d = 0; d < kNDof; ++d) EXPECT(planner.GetVelocities().back()[d] == 0.0);
+    }
+    // a second Plan() inside the planned span only trims the front (:590-601)
+    const size_t m0 = planner.GetNumTimeSamples();
+    EXPECT(planner.Plan(TimeFromSec(0.2), tp::Seconds(0.1)).ok());
+    EXPECT(planner.GetNumTimeSamples() == m0 - 50);
+    EXPECT(std::abs(planner.GetTime().front() - 0.2) < 1e-12);
+    printf("\"rest_to_rest\": {\n");
+    PrintArray("knots", path->GetKnots());
+    PrintArray("control_points", Flatten(path->GetControlPoints()));
+    PrintArray("time", planner.GetTime());
+    PrintArray("positions", Flatten(planner.GetPositions()));
+    PrintArray("velocities", Flatten(planner.GetVelocities()));
+    PrintArray("accelerations", Flatten(planner.GetAccelerations()));
+    PrintArray("path_parameter", planner.GetPathParameters());
+    PrintArray("q0", std::vector<double>(path->GetPathPositionAt(0).begin(), path->GetPathPositionAt(0).end()));
+    printf("\"end_time_ns\": %lld, \"final_decel_start_ns\": %lld, \"trimmed\": 50},\n",
+           static_cast<long long>(planner.GetEndTime().ns),
+           static_cast<long long>(planner.GetFinalDecelStart().ns));
+    // constraint rows of sample 10 (ConstraintSetup, timeable_path_joint_spline.cc:320-343)
+    const auto& c = path->GetConstraints()[10];
+    std::vector<double> rows;
+    for (int r = 0; r < c.size(); ++r) {
+      rows.push_back(c.a_coefficient(r));
+      rows.push_back(c.b_coefficient(r));
+      rows.push_back(c.lower(r));
+      rows.push_back(c.upper(r));
+    }
+    PrintArray("constraints_sample10", rows);
+    // moving-horizon use is outside the hot path
+    auto path2 = std::make_shared<TimeableJointSplinePath>(
+        JointPathOptions().set_num_dofs(kNDof).set_num_path_samples(kNumSamples));
+    PathTimingTrajectory planner2(PathTimingTrajectoryOptions()
+                                      .SetTimeStep(tp::Milliseconds(4))
+                                      .SetNumDofs(kNDof)
+                                      .SetNumPathSamples(kNumSamples));
+    EXPECT(planner2.SetPath(path2).ok());
+    EXPECT(path2->SetWaypoints(wps).ok());
+    path2->SetMaxJointVelocity(ToSpan(vmax));
+    path2->SetMaxJointAcceleration(ToSpan(amax));
+    EXPECT(planner2.Plan(TimeFromSec(0.0), tp::Seconds(100)).code() == tp::StatusCode::kUnimplemented);
+  }
+  // ---- Circle (time_optimal_path_timing_test.cc:496-559)
+  {
+    const double R = 2.0, vmax = 1.2, amax = 1.0;
+    printf("\"circle\": [\n");
+    const struct { int n; double sd; } cases[] = {{50, 0.0}, {51, 0.0}, {50, 0.1}, {51, 0.1}};
+    for (int ci = 0; ci < 4; ++ci) {
+      const int N = cases[ci].n;
+      std::vector<TimeOptimalPathProfile::Constraint> cons(N);
+      const double ds = M_PI / (N - 1);
+      for (int i = 0; i < N; ++i) {
+        const double s = i * ds;
+        auto& c = cons[i];
+        c.resize(4);
+        c.a_coefficient(0) = -R * sin(s);
+        c.a_coefficient(1) = R * cos(s);
+        c.b_coefficient(0) = -R * cos(s);
+        c.b_coefficient(1) = -R * sin(s);
+        c.b_coefficient(2) = pow(R * sin(s), 2);
+        c.b_coefficient(3) = pow(R * cos(s), 2);
+        c.upper(0) = c.upper(1) = amax;
+        c.lower(0) = c.lower(1) = -amax;
+        c.upper(2) = c.upper(3) = pow(vmax, 2);
+      }
+      TimeOptimalPathTiming opt;  // BASELINE.json's name for TimeOptimalPathProfile
+      EXPECT(!opt.OptimizePathParameter());  // not set up yet
+      EXPECT(opt.InitSolver(N, 4));
+      EXPECT(opt.SetupProblem(cons, 0.0, M_PI, cases[ci].sd, 0.0, 0.0));
+      EXPECT(opt.OptimizePathParameter());
+      double s0, sd0, sdd0;
+      EXPECT(opt.GetPathParameterAndDerivatives(0.0, &s0, &sd0, &sdd0));
+      EXPECT(std::abs(sd0 - cases[ci].sd) < 1e-15);
+      EXPECT(opt.SolutionSatisfiesConstraints().ok());
+      double smx, sddmx, szero;
+      opt.FindMaxSd2Simplex(cons[N / 3], &smx, &sddmx, &szero);
+      printf("{\"N\": %d, \"sd_start\": %.17g, \"duration\": %.17g, \"last_extremal\": %d, "
+             "\"lp_sd2max\": %.17g, \"lp_sd2zero\": %.17g, \"dt_max\": %.17g}%s\n",
+             N, cases[ci].sd, opt.GetTotalDuration(), opt.GetLastExtremalIndex(), smx, szero,
+             opt.GetMaxTimeIncrement(), ci < 3 ? "," : "");
+      // setup errors return false like the reference
+      cons[3].lower(1) = cons[3].upper(1);
+      EXPECT(!opt.SetupProblem(cons, 0.0, M_PI, 0.0, 0.0, 0.0));
+    }
+    printf("],\n");
+  }
+  // ---- BSpline golden configuration (splines/bspline_test.cc:730-840)
+  {
+    BSplineXd spline;
+    std::vector<double> knots = {0, 0, 0, 0, 0.5, 1, 1, 1, 1};
+    EXPECT(spline.Init(3, knots.size(), 2).ok());
+    EXPECT(spline.SetKnotVector(knots).ok());
+    std::vector<VectorXd> poly = {VectorXd{1, 1}, VectorXd{2, 3}, VectorXd{3, -1}, VectorXd{4, 1}, VectorXd{5, 0}};
+    EXPECT(spline.SetControlPoints(poly).ok());
+    EXPECT(spline.SetControlPoints(std::vector<VectorXd>(4, VectorXd{0, 0})).code() ==
+           tp::StatusCode::kInvalidArgument);
+    std::vector<double> us(101);
+    for (int i = 0; i < 101; ++i) us[i] = 0.0 + i * (1.0 / 100);
+    std::vector<double> out(101 * 4 * 2);
+    std::vector<int32_t> st(101);
+    EXPECT(spline.EvalCurveAndDerivativesBatch(us, 3, out.data(), st.data()).ok());
+    VectorXd p(2);
+    EXPECT(spline.EvalCurve(0.5, p).ok());
+    EXPECT(spline.EvalCurve(1.5, p).code() == tp::StatusCode::kOutOfRange);
+    EXPECT(spline.EvalCurve(-0.1, p).code() == tp::StatusCode::kOutOfRange);
+    std::vector<VectorXd> pk(4, VectorXd(2));
+    EXPECT(spline.EvalCurveAndDerivatives(0.01, tp::Span<VectorXd>(pk.data(), pk.size())).ok());
+    printf("\"bspline\": {\n");
+    PrintArray("values", out);
+    PrintArray("at_0p01", Flatten(pk), false);
+    printf("},\n");
+    BSplineXd auto_knots;
+    EXPECT(auto_knots.Init(1, 7, 1).ok());
+    EXPECT(auto_knots.SetUniformKnotVector(7).ok());
+    auto kv = auto_knots.GetKnotVector();
+    EXPECT(kv.size() == 7 && kv[2] == 0.25 && kv[3] == 0.5 && kv[4] == 0.75);
+  }
+  // ---- batched front-end
+  {
+    const int B = 5, W = 4, D = 3, N = 256;
+    std::vector<double> wp(B * W * D), vm(B * D, 1.0), am(B * D, 2.0);
+    for (size_t i = 0; i < wp.size(); ++i) wp[i] = std::sin(0.37 * static_cast<double>(i) + 0.1) * 2.0;
+    std::vector<int32_t> nw = {4, 3, 2, 4, 1};
+    PathTimingTrajectoryBatch batch(JointPathOptions().set_num_dofs(D),
+                                    PathTimingTrajectoryOptions()
+                                        .SetTimeStep(tp::Milliseconds(4))
+                                        .SetNumDofs(D)
+                                        .SetNumPathSamples(N),
+                                    B, W, 1 << 20);
+    PathTimingTrajectoryBatch::Result res;
+    EXPECT(batch.Plan(B, nw.data(), wp.data(), vm.data(), am.data(), TimeFromSec(0.0), &res).ok());
+    printf("\"batch\": {\n");
+    PrintArray("waypoints", wp);
+    PrintArray("duration", res.duration);
+    std::vector<double> off(res.offset.begin(), res.offset.end()), st(res.status.begin(), res.status.end());
+    PrintArray("offset", off);
+    PrintArray("status", st);
+    PrintArray("positions", res.positions, false);
+    printf("},\n");
+  }
+  printf("\"failures\": %d\n}\n", g_fail);
+  return g_fail ? 1 : 0;
+}

@@ -1,0 +1,89 @@
+"""GPU test: the host C++ mirror of the reference API (host/include/...) driven by
+tests/host_cpp/host_api_test.cc, compared with the CPU oracle."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "x-edr-trajectory-planning_b200", "host", "bin", "host_api_test")
+
+
+@pytest.fixture(scope="module")
+def result():
+    if not os.path.exists(BIN):
+        subprocess.run(["make", "-C", os.path.dirname(os.path.dirname(BIN)), "all"], check=True)
+    p = subprocess.run([BIN], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr[-2000:]
+    r = json.loads(p.stdout)
+    assert r["failures"] == 0, p.stderr[-2000:]
+    return r
+
+
+def test_rest_to_rest_plan_matches_oracle(result, po):
+    r = result["rest_to_rest"]
+    rows10 = result["constraints_sample10"]
+    wp = np.array([[1, 2, 3], [-1, -2, -3], [1, 2, 3]], float)
+    vmax, amax = np.full(3, 1.0), np.full(3, 2.0)
+    o = po.plan_joint(wp, vmax, amax, 1000, delta=0.016, dt=0.004, M_cap=20000)
+    assert o["ok"]
+    ctrl, knots = po.joint_fit(wp, 0.2)
+    np.testing.assert_array_equal(np.array(r["knots"]), knots)
+    np.testing.assert_array_equal(np.array(r["control_points"]).reshape(-1, 3), ctrl)
+    k = r["trimmed"]  # the second Plan() erased the first 50 samples
+    np.testing.assert_array_equal(np.array(r["time"]), o["r_t"][k:])
+    assert np.max(np.abs(np.array(r["positions"]).reshape(-1, 3) - o["r_pos"][k:])) <= 1e-9
+    assert np.max(np.abs(np.array(r["velocities"]).reshape(-1, 3) - o["r_vel"][k:])) <= 1e-9
+    assert np.max(np.abs(np.array(r["accelerations"]).reshape(-1, 3) - o["r_acc"][k:])) <= 1e-9
+    np.testing.assert_allclose(np.array(r["path_parameter"]), o["r_s"][k:], atol=1e-12)
+    # end_time_ = TimeFromSec(time_.back()) clamped to a time-step multiple
+    # (path_timing_trajectory.cc:662-666, 229-233)
+    end_ns = po.time_from_sec(round(po.time_to_sec(po.time_from_sec(o["r_t"][-1])) / 0.004) * 0.004)
+    assert r["end_time_ns"] == end_ns
+    cons = po.joint_constraints(o["dq"], o["ddq"], vmax, amax, 0.8)
+    np.testing.assert_array_equal(np.array(rows10).reshape(6, 4), cons[10])
+
+
+def test_circle_profile_matches_oracle(result, po, pkg):
+    for c in result["circle"]:
+        cons = pkg.workloads.circle_constraints(c["N"])
+        o = po.solve(cons, 0.0, np.pi, c["sd_start"])
+        assert o["ok"]
+        assert c["duration"] == o["time"][-1] - o["time"][0]
+        assert c["last_extremal"] == o["last_extremal_index"]
+        lp = po.find_max_sd2(cons[c["N"] // 3])
+        assert c["lp_sd2max"] == lp[0] and c["lp_sd2zero"] == lp[2]
+        assert c["dt_max"] == pytest.approx(np.max(np.diff(o["time"])), abs=1e-15)
+
+
+def test_bspline_matches_golden_and_oracle(result, po):
+    g = json.load(open(os.path.join(ROOT, "tests", "golden", "bspline_mathematica.json")))
+    v = np.array(result["bspline"]["values"]).reshape(101, 4, 2)
+    for k, (nx, ny) in enumerate((("X", "Y"), ("Xp", "Yp"), ("Xpp", "Ypp"), ("Xppp", "Yppp"))):
+        assert np.sum((v[:, k, 0] - g[nx]) ** 2) <= 5e-14
+        assert np.sum((v[:, k, 1] - g[ny]) ** 2) <= 5e-14
+    us = 0.0 + np.arange(101) * (1.0 / 100)
+    _, ref = po.eval_curve_ders(np.array(g["knots"], float), np.array(g["control_points"], float),
+                                3, 3, us)
+    np.testing.assert_array_equal(v, ref)
+    np.testing.assert_array_equal(np.array(result["bspline"]["at_0p01"]).reshape(4, 2), ref[1])
+
+
+def test_batch_front_end_matches_oracle(result, po):
+    b = result["batch"]
+    wp = np.array(b["waypoints"]).reshape(5, 4, 3)
+    nw = [4, 3, 2, 4, 1]
+    off = np.array(b["offset"], np.int64)
+    pos = np.array(b["positions"]).reshape(-1, 3)
+    for i in range(5):
+        o = po.plan_joint(wp[i, :nw[i]], np.full(3, 1.0), np.full(3, 2.0), 256, dt=0.004,
+                          M_cap=20000)
+        assert (b["status"][i] == 0) == o["ok"]
+        if not o["ok"]:
+            continue
+        assert abs(b["duration"][i] - o["duration"]) <= 1e-6 * max(o["duration"], 1e-300)
+        assert off[i + 1] - off[i] == o["M"]
+        assert np.max(np.abs(pos[off[i]:off[i + 1]] - o["r_pos"])) <= 1e-9

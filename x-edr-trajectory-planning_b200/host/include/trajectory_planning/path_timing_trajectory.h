@@ -1,0 +1,289 @@
+// Host-side mirror of PathTimingTrajectory
+// (trajectory_planning/path_timing_trajectory.h:33-186, .cc:206-902).
+//
+// Plan() drives the GPU stages through the path's engine: SamplePath + limit
+// curve -> OptimizePathParameter -> per-sample assembly + uniform-in-time
+// resampling (ComputeTimingProfile .cc:307-475, ResampleEquidistantlyInTime
+// .cc:755-783), then downloads the resampled trajectory into the
+// TrajectoryPlanner vectors.
+//
+// Scope: a fresh path (State::kNewPath) whose
+// planning loop needs one path window, plus the "already planned enough"
+// re-entry (.cc:590-601).  Moving-horizon re-planning across windows,
+// kSkipSamplesCloserThanTimeStep and GetPathStopParameter are "next" rows and
+// return kUnimplemented.  Paths must be TimeableJointSplinePath.
+#ifndef TRAJECTORY_PLANNING_PATH_TIMING_TRAJECTORY_H_
+#define TRAJECTORY_PLANNING_PATH_TIMING_TRAJECTORY_H_
+
+#include <algorithm>
+#include <cmath>
+#include <limits>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "trajectory_planning/timeable_path_joint_spline.h"
+#include "trajectory_planning/trajectory_planner.h"
+
+namespace trajectory_planning {
+
+class PathTimingTrajectoryOptions : public TrajectoryPlannerOptions<PathTimingTrajectoryOptions> {
+ public:
+  enum class TimeSamplingMethod { kUniformlyInTime, kSkipSamplesCloserThanTimeStep };
+  size_t GetNumPathSamples() const { return num_path_samples_; }
+  PathTimingTrajectoryOptions& SetNumPathSamples(size_t n) {
+    num_path_samples_ = n;
+    return *this;
+  }
+  double GetMaxInitialVelocityError() const { return max_initial_velocity_error_; }
+  PathTimingTrajectoryOptions& SetMaxInitialVelocityError(double e) {
+    max_initial_velocity_error_ = e;
+    return *this;
+  }
+  PathTimingTrajectoryOptions& SetMaxPlanningLoops(int n) {
+    max_planning_iterations_ = n;
+    return *this;
+  }
+  int GetMaxPlanningIterations() const { return max_planning_iterations_; }
+  PathTimingTrajectoryOptions& SetTimeSamplingMethod(TimeSamplingMethod m) {
+    time_sampling_method_ = m;
+    return *this;
+  }
+  TimeSamplingMethod GetTimeSamplingMethod() const { return time_sampling_method_; }
+
+ private:
+  size_t num_path_samples_ = 1000;            // path_timing_trajectory.h:71
+  double max_initial_velocity_error_ = 1e-2;  // :72
+  int max_planning_iterations_ = 200;         // :73
+  TimeSamplingMethod time_sampling_method_ = TimeSamplingMethod::kUniformlyInTime;
+};
+
+class PathTimingTrajectory : public TrajectoryPlanner {
+ public:
+  explicit PathTimingTrajectory(const PathTimingTrajectoryOptions& options)
+      : options_(options),
+        time_step_sec_(TimeToSec(tp::FromUnixNanos(options.GetTimeStep().ns))) {
+    Reset();
+  }
+
+  // SetPath (.cc:844-864)
+  tp::Status SetPath(std::shared_ptr<TimeablePath> path) override {
+    if (path == nullptr) return tp::InvalidArgumentError("Path is nullptr.");
+    if (path->NumDofs() != options_.GetNumDofs()) {
+      return tp::InvalidArgumentError("Path has " + std::to_string(path->NumDofs()) +
+                                      " dofs but planner has " + std::to_string(options_.GetNumDofs()));
+    }
+    if (path->NumPathSamples() != options_.GetNumPathSamples()) {
+      return tp::InvalidArgumentError("Path has " + std::to_string(path->NumPathSamples()) +
+                                      " samples but planner has " +
+                                      std::to_string(options_.GetNumPathSamples()));
+    }
+    path_ = path;
+    return tp::OkStatus();
+  }
+
+  // Plan (.cc:579-684)
+  tp::Status Plan(tp::Time start, tp::Duration time_horizon) override {
+    const double start_sec = TimeToSec(start);
+    if (path_ == nullptr) return {tp::StatusCode::kFailedPrecondition, "No path set."};
+    // HandleTimeArguments (.cc:502-538)
+    if (initial_plan_ && start > end_time_ + tp::Seconds(time_step_sec_)) {
+      return {tp::StatusCode::kOutOfRange, "start > end of previous plan"};
+    }
+    if (!initial_plan_) {
+      start_time_ = start;
+      end_time_ = start;
+      path_start_ = 0.0;
+    } else {
+      if (start > end_time_) return tp::InvalidArgumentError("Start time must be < end time");
+      if (start < start_time_) return tp::InvalidArgumentError("Start time must be >= previous start time");
+      start_time_ = start;
+    }
+    // UpdatePathTrackingStatus (.cc:477-500)
+    target_reached_ = false;
+    planned_to_end_ = false;
+    const auto state = path_->GetState();
+    const bool fresh = state == TimeablePath::State::kNewPath || state == TimeablePath::State::kModifiedPath;
+    if (!initial_plan_) {
+      path_horizon_ = 0;
+      path_start_ = 0;
+    } else {
+      planned_to_end_ = path_->CloseToEnd(path_horizon_);
+      if (planned_to_end_) {
+        if (!fresh) {
+          target_reached_ = true;
+        } else {
+          path_horizon_ = path_start_ = 0.0;
+          planned_to_end_ = false;
+        }
+      }
+    }
+    const bool planned_enough = !fresh && (final_decel_start_ >= start + time_horizon);
+    if (!time_.empty() && planned_enough) {
+      EraseTrajectoryBefore(start);
+      return tp::OkStatus();
+    }
+    if (planned_to_end_) {  // nothing left to plan (loop at .cc:628 does not run)
+      target_reached_ = true;
+      return tp::OkStatus();
+    }
+    if (state != TimeablePath::State::kNewPath) {
+      return tp::UnimplementedError(
+          "moving-horizon re-planning of a partially planned path is outside the hot path");
+    }
+    if (options_.GetTimeSamplingMethod() != PathTimingTrajectoryOptions::TimeSamplingMethod::kUniformlyInTime) {
+      return tp::UnimplementedError("kSkipSamplesCloserThanTimeStep is outside the hot path");
+    }
+    auto* joint = dynamic_cast<TimeableJointSplinePath*>(path_.get());
+    if (joint == nullptr || joint->engine() == nullptr) {
+      return tp::UnimplementedError("only TimeableJointSplinePath is accelerated");
+    }
+    tpb_engine* e = joint->engine();
+    if (time_horizon.ns <= 0) return tp::InvalidArgumentError("Duration must be positive");
+
+    // ---- ComputeTimingProfile (.cc:307-475), kNewPath branch
+    path_start_ = 0.0;
+    path_start_velocity_ = 0.0;
+    path_start_acceleration_ = 0.0;
+    path_time_start_ = start_sec;
+    const int N = path_->GetNumPathSamples();
+    path_horizon_ = path_start_ + path_->GetPathSamplingDistance() * (N - 1);
+    if (auto st = path_->SamplePath(path_start_); !st.ok()) return st;
+    if (auto st = path_->ConstraintSetup(); !st.ok()) return st;
+    {  // initial-velocity projection onto the path tangent (.cc:352-385)
+      const tp::VectorXd& d0 = path_->GetFirstPathDerivativeAt(0);
+      const tp::VectorXd& v0 = path_->GetInitialVelocity();
+      double sq = 0.0, dot = 0.0;
+      for (size_t i = 0; i < d0.size(); ++i) {
+        sq += d0[i] * d0[i];
+        dot += v0[i] * d0[i];
+      }
+      if (sq > 100 * std::numeric_limits<double>::epsilon()) {
+        path_start_velocity_ = std::max(dot / sq, 0.0);
+      }
+      double err = 0.0;
+      for (size_t i = 0; i < d0.size(); ++i) {
+        err = std::max(err, std::abs(d0[i] * path_start_velocity_ - v0[i]));
+      }
+      if (err > options_.GetMaxInitialVelocityError()) {
+        return tp::InvalidArgumentError(
+            "Could not satisfy initial velocity (probably not parallel to initial tangent): error = " +
+            std::to_string(err));
+      }
+    }
+    const int max_solver_loops = static_cast<int>(std::max<size_t>(100, 10 * options_.GetNumPathSamples()));
+    int32_t rc = tpb_optimize(e, &path_start_velocity_, &path_start_acceleration_, &path_time_start_,
+                              max_solver_loops, 0);
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
+    int32_t status = TPB_PATH_NOT_RUN, last_extremal = 0;
+    tpb_get(e, TPB_ARR_STATUS, &status, sizeof(status), 0);
+    if (status == TPB_PATH_FAIL_SETUP) {
+      return {tp::StatusCode::kInternal, "Error setting up optimization problem"};
+    }
+    if (status != TPB_PATH_OK) return {tp::StatusCode::kInternal, "Error optimizing path parameter"};
+    tpb_get(e, TPB_ARR_LAST_EXTREMAL, &last_extremal, sizeof(last_extremal), 0);
+    time_at_path_samples_.resize(N);
+    tpb_get(e, TPB_ARR_TIME, time_at_path_samples_.data(), sizeof(double) * N, 0);
+
+    // ---- loop bookkeeping of Plan (.cc:635-658), first iteration
+    const int decel_start = std::max(last_extremal, static_cast<int>(options_.GetNumPathSamples() / 2));
+    final_decel_start_ = TimeFromSec(time_at_path_samples_[decel_start]);
+    planned_to_end_ = path_->CloseToEnd(path_horizon_);
+    const bool time_horizon_reached =
+        (time_at_path_samples_[N - 1] - start_sec) > static_cast<double>(time_horizon.ns) / 1e9;
+    if (!planned_to_end_ && !time_horizon_reached) {
+      return tp::UnimplementedError(
+          "path needs more than one planning window (increase num_path_samples * delta_parameter)");
+    }
+
+    // ---- ResampleTrajectory (.cc:697-707, 755-783) on the device
+    int64_t total = 0;
+    rc = tpb_resample(e, start_sec, time_step_sec_, &total);
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
+    const size_t M = static_cast<size_t>(total), D = options_.GetNumDofs();
+    time_.resize(M);
+    path_parameter_.resize(M);
+    path_parameter_derivative_.resize(M);
+    second_path_parameter_derivative_.resize(M);
+    std::vector<double> buf(M * D);
+    tpb_get(e, TPB_ARR_R_TIME, time_.data(), M * sizeof(double), 0);
+    tpb_get(e, TPB_ARR_R_S, path_parameter_.data(), M * sizeof(double), 0);
+    tpb_get(e, TPB_ARR_R_SD, path_parameter_derivative_.data(), M * sizeof(double), 0);
+    tpb_get(e, TPB_ARR_R_SDD, second_path_parameter_derivative_.data(), M * sizeof(double), 0);
+    std::vector<tp::VectorXd>* dst[3] = {&positions_, &velocities_, &accelerations_};
+    const tpb_array what[3] = {TPB_ARR_R_POS, TPB_ARR_R_VEL, TPB_ARR_R_ACC};
+    for (int k = 0; k < 3; ++k) {
+      tpb_get(e, what[k], buf.data(), buf.size() * sizeof(double), 0);
+      dst[k]->resize(M);
+      for (size_t i = 0; i < M; ++i) (*dst[k])[i] = tp::VectorXd(&buf[i * D], D);
+    }
+
+    initial_plan_ = true;
+    if (!time_.empty()) {
+      end_time_ = TimeFromSec(time_.back());
+      ClampToTimeStepMultiple(&end_time_);
+      final_decel_start_ = TimeFromSec(time_at_path_samples_[last_extremal]);
+      ClampToTimeStepMultiple(&final_decel_start_);
+    } else {
+      end_time_ = start_time_;
+      final_decel_start_ = end_time_;
+    }
+    target_reached_ = planned_to_end_;
+    return tp::OkStatus();
+  }
+
+  size_t NumTimeSamples() const { return time_.size(); }
+  tp::Time GetFinalDecelStart() const { return final_decel_start_; }
+  tp::Time GetNextPlanStartTime(tp::Time target_time) {
+    return std::min(end_time_, std::max(target_time, start_time_),
+                    [](tp::Time a, tp::Time b) { return a < b; });
+  }
+  void SetProfileDebugVerbosity(int) {}
+  tp::StatusOr<double> GetPathStopParameter(tp::Time) const {
+    return tp::UnimplementedError("GetPathStopParameter is outside the hot path (next-2)");
+  }
+  const PathTimingTrajectoryOptions& GetOptions() const { return options_; }
+
+ protected:
+  void ResetDerived() override {
+    initial_plan_ = false;
+    path_time_start_ = path_start_ = path_start_velocity_ = path_start_acceleration_ = 0.0;
+    path_horizon_ = 0.0;
+    planned_to_end_ = true;
+    final_decel_start_ = TimeFromSec(0.0);
+    time_at_path_samples_.clear();
+  }
+
+ private:
+  // ClampToTimeStepMultiple (.cc:229-233)
+  void ClampToTimeStepMultiple(tp::Time* time) const {
+    const int64_t loop_multiple = static_cast<int64_t>(std::round(TimeToSec(*time) / time_step_sec_));
+    *time = TimeFromSec(loop_multiple * time_step_sec_);
+  }
+  // EraseTrajectoryBefore (.cc:540-577), kUniformlyInTime
+  void EraseTrajectoryBefore(tp::Time time) {
+    const double time_sec = TimeToSec(time);
+    if (time_.empty() || time_sec < time_.front()) return;
+    const int offset = std::min<int>(static_cast<int>(std::round((time_sec - time_.front()) / time_step_sec_)),
+                                     static_cast<int>(time_.size()) - 1);
+    auto erase = [offset](auto& v) { v.erase(v.begin(), v.begin() + offset); };
+    erase(time_);
+    erase(path_parameter_);
+    erase(path_parameter_derivative_);
+    erase(second_path_parameter_derivative_);
+    erase(positions_);
+    erase(velocities_);
+    erase(accelerations_);
+  }
+
+  const PathTimingTrajectoryOptions options_;
+  const double time_step_sec_;
+  tp::Time final_decel_start_;
+  double path_horizon_ = 0, path_time_start_ = 0, path_start_ = 0, path_start_velocity_ = 0,
+         path_start_acceleration_ = 0;
+  bool initial_plan_ = false, planned_to_end_ = false;
+  std::vector<double> time_at_path_samples_;
+};
+
+}  // namespace trajectory_planning
+#endif  // TRAJECTORY_PLANNING_PATH_TIMING_TRAJECTORY_H_
