@@ -1,0 +1,817 @@
+// Stage C, sequential part: one warp per path (k_integrate<Policy>).
+//
+// CalculateBoundary passes 2-4 (time_optimal_path_timing.cc:1379-1484), the
+// extremal sweeps AddForwardExtremal / AddBackwardExtremal (:769-952), the
+// switching-point loop of OptimizePathParameter (:287-490), NextCriticalPoint
+// (:697-720), ComputeSddAtIntersection (:722-751) and the time integration
+// (:450-467).
+//
+// The scalar state machine is replicated in every lane (warp-uniform control
+// flow); lanes split the O(C^2) work of FindSddMax/FindSddMin/
+// AreDerivativesValid (:624-695) -- how, is the Policy:
+//
+//   Joint8Policy   joint-space paths with D <= 8.  Lane = 8*g + d: group g of 8
+//                  lanes tests candidate j = 4*round + g against acceleration row
+//                  d.  Rows (q', q'' of one sample) live in registers and are
+//                  prefetched one step ahead of the sweep; the 2D velocity rows
+//                  have A == 0, so they never yield a candidate and their validity
+//                  does not depend on the candidate (tested once per call).
+//   GenericPolicy  explicit constraint tables (C <= 32) and joint paths with
+//                  D > 8: rows of the current sample staged per warp in shared
+//                  memory, lane j owns candidate (row j/2, bound j&1).
+//
+// Both give results bit-identical to the reference's sequential loops: the
+// extremum over the candidates that pass every row's test does not depend on
+// evaluation order.
+#pragma once
+
+#include "tpb_engine.h"
+#include "tpb_device.cuh"
+
+namespace tpb {
+
+constexpr int kWarpsPerBlock = 4;
+
+// ---------------------------------------------------------------------------
+// Policies
+// ---------------------------------------------------------------------------
+
+struct GenericPolicy {
+  struct Rows {
+    int idx;
+  };
+  int lane, C, D;
+  bool joint;
+  const double *dq, *ddq, *cons;
+  double *sA, *sB, *sLo, *sHi;  // shared, this warp
+  int staged;
+
+  __device__ __forceinline__ Rows load(int idx) const { return Rows{idx}; }
+
+  // Bring the rows of sample idx on chip.  Joint paths synthesise them from
+  // q', q'' (ConstraintSetup); their lower/upper bounds were filled once.
+  __device__ void stage(int idx) {
+    if (staged == idx) return;
+    __syncwarp();
+    if (joint) {
+      if (lane < D) {
+        const double d1 = dq[static_cast<size_t>(idx) * D + lane];
+        const double d2 = ddq[static_cast<size_t>(idx) * D + lane];
+        sA[lane] = d1;
+        sB[lane] = d2;
+        sA[D + lane] = 0.0;
+        sB[D + lane] = d1 * d1;
+      }
+    } else {
+      const double* c = cons + static_cast<size_t>(idx) * C * 4;
+      for (int r = lane; r < C; r += 32) {
+        sA[r] = c[r * 4 + 0];
+        sB[r] = c[r * 4 + 1];
+        sLo[r] = c[r * 4 + 2];
+        sHi[r] = c[r * 4 + 3];
+      }
+    }
+    __syncwarp();
+    staged = idx;
+  }
+
+  // AreDerivativesValid (:624-636): lane r tests row r.
+  __device__ bool valid(Rows r, double sddv, double sd2v) {
+    stage(r.idx);
+    bool bad = false;
+    if (lane < C) {
+      const double v = sA[lane] * sddv + sB[lane] * sd2v;
+      bad = (v + kTiny < sLo[lane]) || (v - kTiny > sHi[lane]);
+    }
+    return __ballot_sync(kFullMask, bad) == 0u;
+  }
+
+  // FindSddMax / FindSddMin (:638-695)
+  template <bool kMax>
+  __device__ double find_sdd(Rows rw, double sd2v) {
+    stage(rw.idx);
+    double best = kMax ? -DBL_MAX : DBL_MAX;
+    for (int j = lane; j < 2 * C; j += 32) {
+      const int r = j >> 1;
+      const double Ar = sA[r];
+      if (is_tiny(Ar)) continue;
+      const double cand = (((j & 1) ? sHi[r] : sLo[r]) - sB[r] * sd2v) / Ar;
+      bool ok = (cand == cand);
+      for (int i = 0; i < C && ok; ++i) {
+        const double v = sA[i] * cand + sB[i] * sd2v;
+        ok = !((v + kTiny < sLo[i]) || (v - kTiny > sHi[i]));
+      }
+      if (ok) {
+        if (kMax) {
+          best = (cand > best) ? cand : best;
+        } else {
+          best = (cand < best) ? cand : best;
+        }
+      }
+    }
+    best = kMax ? warp_max(best) : warp_min(best);
+    if (best == (kMax ? -DBL_MAX : DBL_MAX)) best = 0.0;
+    return best;
+  }
+};
+
+struct Joint8Policy {
+  struct Rows {
+    double A, B;  // q'_d, q''_d of one sample (0 for d >= D)
+  };
+  int lane, D;
+  int g, d;  // lane = 8*g + d
+  const double *dq, *ddq;
+  double aS, vS2;  // amax_d*safety, (vmax_d*safety)^2 (row bounds: -aS..aS, 0..vS2)
+
+  __device__ __forceinline__ Rows load(int idx) const {
+    Rows r{0.0, 0.0};
+    if (d < D) {
+      r.A = dq[static_cast<size_t>(idx) * D + d];
+      r.B = ddq[static_cast<size_t>(idx) * D + d];
+    }
+    return r;
+  }
+
+  // velocity rows (A = 0, B = q'^2, 0 <= . <= vS2): candidate independent
+  __device__ __forceinline__ bool velocity_rows_bad(const Rows& r, double sd2v) const {
+    bool bad = false;
+    if (d < D) {
+      const double v = (r.A * r.A) * sd2v;
+      bad = (v + kTiny < 0.0) || (v - kTiny > vS2);
+    }
+    return __ballot_sync(kFullMask, bad) != 0u;
+  }
+
+  // AreDerivativesValid (:624-636)
+  __device__ bool valid(const Rows& r, double sddv, double sd2v) const {
+    bool bad = false;
+    if (d < D) {
+      const double v = r.A * sddv + r.B * sd2v;
+      bad = (v + kTiny < -aS) || (v - kTiny > aS);
+      // velocity row: 0*sdd contributes +-0 (or NaN for a non-finite sdd, which
+      // then passes every comparison exactly like in the reference)
+      const double w = 0.0 * sddv + (r.A * r.A) * sd2v;
+      bad = bad || (w + kTiny < 0.0) || (w - kTiny > vS2);
+    }
+    return __ballot_sync(kFullMask, bad) == 0u;
+  }
+
+  // FindSddMax / FindSddMin (:638-695)
+  template <bool kMax>
+  __device__ double find_sdd(const Rows& r, double sd2v) const {
+    const double Bs = r.B * sd2v;
+    // candidate of (row d, bound g&1); lanes of groups 2,3 duplicate groups 0,1
+    double cand = quiet_nan();
+    if (d < D && !is_tiny(r.A)) cand = (((g & 1) ? aS : -aS) - Bs) / r.A;
+    const bool vbad = velocity_rows_bad(r, sd2v);
+    double best = kMax ? -DBL_MAX : DBL_MAX;
+    const int ncand = 2 * D;
+    for (int j0 = 0; j0 < ncand; j0 += 4) {
+      const int j = j0 + g;  // this group's candidate: row j>>1, bound j&1
+      const int src = ((j & 1) << 3) | ((j >> 1) & 7);
+      const double c = __shfl_sync(kFullMask, cand, src);
+      bool bad = false;
+      if (d < D) {
+        const double v = r.A * c + Bs;
+        bad = (v + kTiny < -aS) || (v - kTiny > aS);
+      }
+      const unsigned m = __ballot_sync(kFullMask, bad);
+      // finite candidates only: NaN marks "no candidate"; +-inf fails its own row
+      const bool ok = (j < ncand) && (c == c) && (((m >> (8 * g)) & 0xffu) == 0u);
+      if (ok) {
+        if (kMax) {
+          best = (c > best) ? c : best;
+        } else {
+          best = (c < best) ? c : best;
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 8; o <= 16; o <<= 1) {
+      const double w = __shfl_xor_sync(kFullMask, best, o);
+      if (kMax) {
+        best = (w > best) ? w : best;
+      } else {
+        best = (w < best) ? w : best;
+      }
+    }
+    if (vbad || best == (kMax ? -DBL_MAX : DBL_MAX)) best = 0.0;
+    return best;
+  }
+};
+
+// ---------------------------------------------------------------------------
+// The per-path solver
+// ---------------------------------------------------------------------------
+
+template <class P>
+struct Solver {
+  using Rows = typename P::Rows;
+  P p;
+  int lane, N;
+  double ds;
+  double *sd2, *sdd, *bmax, *bsmax, *bsmin, *bzero;
+  uint8_t *at0, *type;
+
+  __device__ __forceinline__ void st(double* ptr, double v) const {
+    if (lane == 0) *ptr = v;
+    __syncwarp();
+  }
+
+  // ComputeSddAtIntersection (:722-751)
+  __device__ void sdd_at_intersection(int index, const Rows& rows) {
+    double cand[3];
+    int n = 0;
+    if (index > 0 && index < N - 1) cand[n++] = 0.25 / ds * (sd2[index + 1] - sd2[index - 1]);
+    if (index < N - 1) cand[n++] = 0.5 / ds * (sd2[index + 1] - sd2[index]);
+    if (index > 0) cand[n++] = 0.5 / ds * (sd2[index] - sd2[index - 1]);
+    const double here = sd2[index];
+    double r = 0.0;
+    for (int k = 0; k < n; ++k) {
+      if (p.valid(rows, cand[k], here)) {
+        r = cand[k];
+        break;
+      }
+    }
+    st(&sdd[index], r);
+  }
+
+  // One (rare) pass-2 fix of CalculateBoundary at sample i (:1384-1396).
+  __device__ void fix_isolated(int i) {
+    const double zm = bzero[i - 1];
+    const Rows rm = p.load(i - 1);
+    const double a1 = p.template find_sdd<true>(rm, zm);
+    const double a2 = p.template find_sdd<false>(rm, zm);
+    const double zp = bzero[i + 1];
+    const Rows rp = p.load(i + 1);
+    const double a3 = p.template find_sdd<true>(rp, zp);
+    if (lane == 0) {
+      bmax[i - 1] = zm;
+      bsmax[i - 1] = a1;
+      bsmin[i - 1] = a2;
+      bmax[i + 1] = zp;
+      bsmax[i + 1] = a3;
+      bsmin[i + 1] = a3;  // sic: FindSddMax, time_optimal_path_timing.cc:1394-1395
+    }
+    __syncwarp();
+  }
+
+  // "skipped maximum" value at sample i (:1422-1429)
+  __device__ double skipped_value(int i, double bm, double bp) {
+    const double fw = bm + 2.0 * ds * p.template find_sdd<true>(p.load(i - 1), bm);
+    const double bw = bp - 2.0 * ds * p.template find_sdd<false>(p.load(i + 1), bp);
+    double m = bzero[i];
+    if (fw < m) m = fw;
+    if (bw < m) m = bw;
+    return (0.0 < m) ? m : 0.0;
+  }
+
+  // CalculateBoundary passes 2-4 (:1379-1484).  Pass 2 mutates neighbours in
+  // place while it scans, but only where an isolated critical point exists
+  // (flags at0 = 0,1,0); paths without one (the common case) are scanned 32
+  // samples at a time, the others take the warp-uniform serial scan.
+  __device__ void boundary_passes(double* fix_val, int* fix_idx) {
+    if (lane == 0) {
+      type[0] = kNone;
+      type[N - 1] = kNone;
+    }
+    bool iso = false;
+    for (int i = 1 + lane; i < N - 1; i += 32) iso |= (!at0[i - 1] && at0[i] && !at0[i + 1]);
+    const bool any_iso = __ballot_sync(kFullMask, iso) != 0u;
+    int nwork = 0;
+    if (!any_iso) {
+      for (int base = 1; base < N - 1; base += 32) {
+        const int i = base + lane;
+        bool hit = false;
+        if (i < N - 1) {
+          const double bi = bmax[i], bp = bmax[i + 1], bm = bmax[i - 1];
+          const double sd2p = (bp - bi) / ds;
+          const double smax_i = bsmax[i];
+          const bool sink_or_source = (sd2p < 2 * bsmin[i]) || (sd2p > 2 * smax_i);
+          const bool skipped_sdd = (smax_i > 0) && (bsmin[i + 1] < 0);
+          const bool skipped_sd2 = (bi > bm - kTiny) && (bi > bp - kTiny);
+          hit = (skipped_sd2 || skipped_sdd) && sink_or_source;
+        }
+        unsigned m = __ballot_sync(kFullMask, hit);
+        while (m) {
+          const int k = __ffs(m) - 1;
+          m &= m - 1;
+          const int ii = base + k;
+          const double v = skipped_value(ii, bmax[ii - 1], bmax[ii + 1]);
+          if (lane == 0) {
+            fix_idx[nwork] = ii;
+            fix_val[nwork] = v;
+          }
+          ++nwork;
+        }
+      }
+    } else {
+      for (int i = 1; i < N - 1; ++i) {
+        if (!at0[i - 1] && at0[i] && !at0[i + 1]) fix_isolated(i);
+        const double bi = bmax[i], bp = bmax[i + 1], bm = bmax[i - 1];
+        const double sd2p = (bp - bi) / ds;
+        const double smax_i = bsmax[i];
+        const bool sink_or_source = (sd2p < 2 * bsmin[i]) || (sd2p > 2 * smax_i);
+        const bool skipped_sdd = (smax_i > 0) && (bsmin[i + 1] < 0);
+        const bool skipped_sd2 = (bi > bm - kTiny) && (bi > bp - kTiny);
+        if ((skipped_sd2 || skipped_sdd) && sink_or_source) {
+          const double v = skipped_value(i, bm, bp);
+          if (lane == 0) {
+            fix_idx[nwork] = i;
+            fix_val[nwork] = v;
+          }
+          ++nwork;
+        }
+      }
+    }
+    __syncwarp();
+    // deferred fixes (:1432-1451), in list order
+    for (int w = 0; w < nwork; ++w) {
+      const int index = fix_idx[w];
+      const double value = fix_val[w];
+      const Rows r0 = p.load(index);
+      const double a1 = p.template find_sdd<true>(r0, value);
+      const double a2 = p.template find_sdd<false>(r0, value);
+      if (lane == 0) {
+        bmax[index] = value;
+        bsmax[index] = a1;
+        bsmin[index] = a2;
+      }
+      if (index > 0) {
+        const double z = bzero[index - 1];
+        const Rows r1 = p.load(index - 1);
+        const double c1 = p.template find_sdd<true>(r1, z);
+        const double c2 = p.template find_sdd<false>(r1, z);
+        if (lane == 0) {
+          bmax[index - 1] = z;
+          bsmax[index - 1] = c1;
+          bsmin[index - 1] = c2;
+        }
+      }
+      if (index < N - 1) {
+        const double z = bzero[index + 1];
+        const Rows r1 = p.load(index + 1);
+        const double c1 = p.template find_sdd<true>(r1, z);
+        const double c2 = p.template find_sdd<false>(r1, z);
+        if (lane == 0) {
+          bmax[index + 1] = z;
+          bsmax[index + 1] = c1;
+          bsmin[index + 1] = c2;
+        }
+      }
+      __syncwarp();
+    }
+    // classification (:1453-1484), lane-parallel
+    for (int i = 1 + lane; i < N - 1; i += 32) {
+      const double sd2p = (bmax[i + 1] - bmax[i]) / ds;
+      const double sd2p_min = 2 * bsmin[i];
+      const double sd2p_max = 2 * bsmax[i];
+      uint8_t t = kNone;
+      if (sd2p < sd2p_min) {
+        t = kSink;
+      } else if (sd2p > sd2p_max) {
+        t = kSource;
+      }
+      if ((sd2p <= sd2p_max) && (sd2p >= sd2p_min)) t = kTrajectory;
+      type[i] = t;
+    }
+    __syncwarp();
+  }
+
+  // AddForwardExtremal (:769-857).  The data of step idx+1 (rows, sd2_max,
+  // type, previously written sd2) is requested while step idx computes.
+  __device__ int add_forward(int idx_lo) {
+    if (idx_lo >= N - 2) return N - 1;
+    double cur = sd2[idx_lo];
+    double bcur = bmax[idx_lo];
+    uint8_t tcur = type[idx_lo];
+    Rows rows = p.load(idx_lo);
+    double bnext = bmax[idx_lo + 1];
+    uint8_t tnext = type[idx_lo + 1];
+    double nxt = sd2[idx_lo + 1];
+    for (int idx = idx_lo; idx < N - 2; ++idx) {
+      // prefetch for step idx + 1 (indices stay in range: idx + 2 <= N - 1)
+      const Rows rows_n = p.load(idx + 1);
+      const double bnext_n = bmax[idx + 2];
+      const uint8_t tnext_n = type[idx + 2];
+      const double nxt_n = sd2[idx + 2];
+
+      double sd2tmp, sddtmp;
+      const bool on_boundary = is_tiny(cur - bcur);
+      if (on_boundary && (tcur & kTrajectory) && (tnext & kTrajectory)) {
+        sd2tmp = bnext;
+        sddtmp = 0.5 * (sd2tmp - cur) / ds;
+      } else {
+        sddtmp = p.template find_sdd<true>(rows, cur);
+        sd2tmp = cur + 2.0 * ds * sddtmp;
+      }
+      if (!(nxt != nxt) && (nxt < sd2tmp)) {
+        sdd_at_intersection(idx, rows);
+        return N - 1;
+      }
+      if (sd2tmp > bnext) {
+        const double sdd_bound = 0.5 * (bnext - cur) / ds;
+        const bool deriv_invalid = !p.valid(rows, sdd_bound, bcur);
+        const bool type_invalid = tnext & kSink;
+        if (type_invalid || deriv_invalid) return idx;
+        sd2tmp = bnext;
+        sddtmp = sdd_bound;
+      }
+      if (sd2tmp < 0) {
+        sd2tmp = 0.0;
+        if (idx <= 1) {
+          sddtmp = 0.0;
+        } else {
+          sddtmp = -sd2[idx - 1] / ds;
+        }
+      }
+      if (lane == 0) {
+        sd2[idx + 1] = sd2tmp;
+        sdd[idx] = sddtmp;
+      }
+      __syncwarp();
+      cur = sd2tmp;
+      bcur = bnext;
+      tcur = tnext;
+      rows = rows_n;
+      bnext = bnext_n;
+      tnext = tnext_n;
+      nxt = nxt_n;
+    }
+    return N - 1;
+  }
+
+  // AddBackwardExtremal (:859-952)
+  __device__ int add_backward(int idx_hi) {
+    if (idx_hi <= 1) return 0;
+    double cur = sd2[idx_hi];
+    double bcur = bmax[idx_hi];
+    uint8_t tcur = type[idx_hi];
+    Rows rows = p.load(idx_hi);
+    double bprev = bmax[idx_hi - 1];
+    uint8_t tprev = type[idx_hi - 1];
+    double prv = sd2[idx_hi - 1];
+    const bool is_connecting = (idx_hi != (N - 1));
+    for (int idx = idx_hi; idx > 1; --idx) {
+      // prefetch for step idx - 1 (idx - 2 >= 0)
+      const Rows rows_n = p.load(idx - 1);
+      const double bprev_n = bmax[idx - 2];
+      const uint8_t tprev_n = type[idx - 2];
+      const double prv_n = sd2[idx - 2];
+
+      double sd2tmp, sddtmp;
+      const bool on_boundary = is_tiny(cur - bcur);
+      if (on_boundary && (tcur & kTrajectory) && (tprev & kTrajectory)) {
+        sd2tmp = bprev;
+        sddtmp = 0.5 * (cur - sd2tmp) / ds;
+      } else {
+        sddtmp = p.template find_sdd<false>(rows, cur);
+        sd2tmp = cur - 2.0 * ds * sddtmp;
+      }
+      if (!(prv != prv) && (prv < sd2tmp)) {
+        sdd_at_intersection(idx, rows);
+        return 0;
+      }
+      if (sd2tmp > bprev) {
+        const double sdd_bound = 0.5 * (cur - bprev) / ds;
+        const bool deriv_invalid = !p.valid(rows, sdd_bound, cur);
+        const bool type_invalid = tprev & kSource;
+        if ((type_invalid || deriv_invalid) && !is_connecting) return idx;
+        sd2tmp = bprev;
+        sddtmp = sdd_bound;
+      }
+      if (sd2tmp < 0) {
+        sd2tmp = 0.0;
+        if (idx < N - 1) {
+          sddtmp = sd2[idx + 1] / ds;
+        } else {
+          sddtmp = 0.0;
+        }
+      }
+      if (lane == 0) {
+        sd2[idx - 1] = sd2tmp;
+        sdd[idx] = sddtmp;
+      }
+      __syncwarp();
+      cur = sd2tmp;
+      bcur = bprev;
+      tcur = tprev;
+      rows = rows_n;
+      bprev = bprev_n;
+      tprev = tprev_n;
+      prv = prv_n;
+    }
+    return 0;
+  }
+
+  // NextCriticalPoint (:697-720), 32 samples per step via ballots.  Sequential
+  // meaning: crit = first idx with a Source/Trajectory type; afterwards crit
+  // moves to any idx with sd2_max[idx] == sd2_max_for_sdd0[0] (sic, index 0);
+  // return crit at the first idx (at or after the first crit) whose sd2 is set.
+  __device__ int next_critical(int idx_lo, int idx_hi) const {
+    int crit = -1;
+    const double bz0 = bzero[0];
+    for (int base = idx_lo + 1; base <= idx_hi; base += 32) {
+      const int idx = base + lane;
+      const bool in = idx <= idx_hi;
+      bool f1 = false, f2 = false, f3 = false;
+      if (in) {
+        f1 = (type[idx] & (kSource | kTrajectory)) != 0;
+        f2 = bmax[idx] == bz0;
+        const double v = sd2[idx];
+        f3 = !(v != v);
+      }
+      const unsigned m1 = __ballot_sync(kFullMask, f1);
+      unsigned m2 = __ballot_sync(kFullMask, f2);
+      unsigned m3 = __ballot_sync(kFullMask, f3);
+      if (crit < 0) {
+        if (m1 == 0u) continue;
+        const int q = __ffs(m1) - 1;
+        crit = base + q;
+        // f2 is only consulted strictly after q; f3 from q on.
+        m2 = (q == 31) ? 0u : (m2 & (~0u << (q + 1)));
+        m3 &= (~0u << q);
+      }
+      if (m3) {
+        const int t = __ffs(m3) - 1;
+        const unsigned upto = (t == 31) ? ~0u : ((1u << (t + 1)) - 1u);
+        const unsigned m2r = m2 & upto;
+        if (m2r) crit = base + (31 - __clz(m2r));
+        return crit;
+      }
+      if (m2) crit = base + (31 - __clz(m2));
+    }
+    return -1;
+  }
+};
+
+// ---------------------------------------------------------------------------
+// Kernel: SetupProblem checks, OptimizePathParameter, outputs
+// ---------------------------------------------------------------------------
+
+template <class P>
+__device__ __forceinline__ void init_policy(P& p, const Dims& dm, const DeviceArrays& a, int b,
+                                            int lane, double safety, double* smem_rows,
+                                            bool joint, int* status);
+
+template <>
+__device__ __forceinline__ void init_policy<GenericPolicy>(GenericPolicy& p, const Dims& dm,
+                                                           const DeviceArrays& a, int b, int lane,
+                                                           double safety, double* smem_rows,
+                                                           bool joint, int* status) {
+  const size_t o = static_cast<size_t>(b) * dm.N;
+  p.lane = lane;
+  p.C = dm.C;
+  p.D = dm.D;
+  p.joint = joint;
+  p.dq = joint ? a.dq + o * dm.D : nullptr;
+  p.ddq = joint ? a.ddq + o * dm.D : nullptr;
+  p.cons = joint ? nullptr : a.cons + o * dm.C * 4;
+  p.sA = smem_rows;
+  p.sB = smem_rows + kMaxRows;
+  p.sLo = smem_rows + 2 * kMaxRows;
+  p.sHi = smem_rows + 3 * kMaxRows;
+  p.staged = -1;
+  bool bad = false;
+  if (joint) {
+    const int D = dm.D;
+    if (lane < D) {
+      const double aS = a.amax[static_cast<size_t>(b) * D + lane] * safety;
+      const double vs = a.vmax[static_cast<size_t>(b) * D + lane] * safety;
+      const double vS2 = vs * vs;
+      p.sLo[lane] = -aS;
+      p.sHi[lane] = aS;
+      p.sLo[D + lane] = 0.0;
+      p.sHi[D + lane] = vS2;
+      bad = (-aS >= aS) || (0.0 >= vS2);
+    }
+  } else {
+    // IsSetupValid (:554-561): every row needs lower < upper
+    const double* c = p.cons;
+    const size_t rows = static_cast<size_t>(dm.N) * dm.C;
+    for (size_t r = lane; r < rows; r += 32) bad |= (c[r * 4 + 2] >= c[r * 4 + 3]);
+  }
+  if (__ballot_sync(kFullMask, bad)) *status = TPB_PATH_FAIL_SETUP;
+  __syncwarp();
+}
+
+template <>
+__device__ __forceinline__ void init_policy<Joint8Policy>(Joint8Policy& p, const Dims& dm,
+                                                          const DeviceArrays& a, int b, int lane,
+                                                          double safety, double*, bool,
+                                                          int* status) {
+  const size_t o = static_cast<size_t>(b) * dm.N;
+  const int D = dm.D;
+  p.lane = lane;
+  p.D = D;
+  p.g = lane >> 3;
+  p.d = lane & 7;
+  p.dq = a.dq + o * D;
+  p.ddq = a.ddq + o * D;
+  p.aS = 0.0;
+  p.vS2 = 0.0;
+  bool bad = false;
+  if (p.d < D) {
+    p.aS = a.amax[static_cast<size_t>(b) * D + p.d] * safety;
+    const double vs = a.vmax[static_cast<size_t>(b) * D + p.d] * safety;
+    p.vS2 = vs * vs;
+    bad = (-p.aS >= p.aS) || (0.0 >= p.vS2);
+  }
+  if (__ballot_sync(kFullMask, bad)) *status = TPB_PATH_FAIL_SETUP;
+}
+
+template <class P, int kMinBlocks>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, kMinBlocks)
+k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
+  __shared__ double s_rows[std::is_same<P, GenericPolicy>::value ? kWarpsPerBlock * 4 * kMaxRows : 1];
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * kWarpsPerBlock + warp;
+  if (b >= dm.B) return;
+  const int N = dm.N;
+  const size_t o = static_cast<size_t>(b) * N;
+
+  int status = TPB_PATH_OK;
+  Solver<P> S;
+  init_policy<P>(S.p, dm, a, b, lane, safety,
+                 s_rows + (std::is_same<P, GenericPolicy>::value ? warp * 4 * kMaxRows : 0), joint,
+                 &status);
+  S.lane = lane;
+  S.N = N;
+  S.sd2 = a.sd2 + o;
+  S.sdd = a.sdd + o;
+  S.bmax = a.b_sd2_max + o;
+  S.bsmax = a.b_sdd_max + o;
+  S.bsmin = a.b_sdd_min + o;
+  S.bzero = a.b_sd2_zero + o;
+  S.at0 = a.b_at0 + o;
+  S.type = a.b_type + o;
+  double* time = a.time + o;
+  double* sv = a.s + o;
+  double* sd = a.sd + o;
+  double* fix_val = a.fix_val + o;
+  int* fix_idx = reinterpret_cast<int*>(a.time + o);  // time[] is free until the end
+
+  const double sd_start = a.sd_start[b];
+  const double sdd_start = a.sdd_start[b];
+  const double time_start = a.time_start[b];
+  double s_start, s_end;
+  // SetupProblem (:161-203); joint paths: ComputeTimingProfile sets
+  // path_horizon_ = path_start_ + delta * (N - 1) (path_timing_trajectory.cc:341-342)
+  if (joint) {
+    s_start = a.path_start[b];
+    s_end = s_start + a.delta[b] * (N - 1);
+  } else {
+    s_start = a.s_start[b];
+    s_end = a.s_end[b];
+  }
+  if (s_start >= s_end || sd_start < 0 || N < 2) status = TPB_PATH_FAIL_SETUP;
+
+  int last_extremal = 0;
+  const double nan = quiet_nan();
+  if (status == TPB_PATH_OK) {
+    // SetSetupDone (:535-552)
+    const double ds = (s_end - s_start) / (N - 1);
+    S.ds = ds;
+    // The per-sample limit curve is kept as computed (b_raw_*); passes 2-4 mutate
+    // a working copy, so tpb_optimize can be repeated like the reference's
+    // OptimizePathParameter (which recomputes the boundary).
+    const double* raw_max = a.b_raw_sd2_max + o;
+    const double* raw_smax = a.b_raw_sdd_max + o;
+    const double* raw_smin = a.b_raw_sdd_min + o;
+    for (int i = lane; i < N; i += 32) {
+      sv[i] = (i == N - 1) ? s_end : ds * i + s_start;
+      S.sd2[i] = (i == 0) ? sd_start * sd_start : ((i == N - 1) ? 0.0 : nan);
+      S.sdd[i] = nan;
+      S.bmax[i] = raw_max[i];
+      S.bsmax[i] = raw_smax[i];
+      S.bsmin[i] = raw_smin[i];
+    }
+    __syncwarp();
+
+    // ---- OptimizePathParameter (:287-490)
+    S.boundary_passes(fix_val, fix_idx);
+
+    int iforw_lo = 0, iback_hi = N - 1, iback_lo, iforw_hi, icrit, icrit_lo, icrit_hi;
+    iback_lo = S.add_backward(iback_hi);
+    iforw_hi = S.add_forward(iforw_lo);
+    icrit_hi = iback_lo;
+    if ((iforw_hi < icrit_hi) && ((icrit_hi < N - 2) && (icrit_hi >= 2))) {
+      S.st(&S.sd2[icrit_hi], nan);
+      icrit_hi++;
+      iback_lo++;
+    }
+    icrit_lo = iforw_hi;
+    for (int loop = 0; loop < max_loops; ++loop) {
+      if (iforw_hi >= icrit_hi) break;
+      icrit = S.next_critical(icrit_lo, icrit_hi);
+      if (icrit < 0 || icrit >= N) icrit = static_cast<int>(0.5 * (icrit_lo + icrit_hi));
+      if (icrit > 0 && icrit < N - 1) S.st(&S.sd2[icrit], S.bmax[icrit]);
+      if (icrit < 1) {
+        status = TPB_PATH_FAIL_INDEX;
+        break;
+      }
+      if (S.bmax[icrit - 1] <= S.bmax[icrit]) {
+        iback_hi = icrit - 1;
+        S.st(&S.sd2[icrit - 1], S.bmax[icrit - 1]);
+      } else {
+        iback_hi = icrit;
+      }
+      iback_lo = S.add_backward(iback_hi);
+      iforw_lo = icrit;
+      iforw_hi = S.add_forward(iforw_lo);
+      if (iback_lo > icrit_lo) {
+        status = TPB_PATH_FAIL_CONNECT;
+        break;
+      }
+      icrit_lo = iforw_hi;
+    }
+  }
+  if (status == TPB_PATH_OK) {
+    // NaN audit (:398-403)
+    bool any_nan = false;
+    for (int i = lane; i < N; i += 32) {
+      const double v = S.sd2[i];
+      any_nan |= (v != v);
+    }
+    if (__ballot_sync(kFullMask, any_nan)) status = TPB_PATH_FAIL_NAN;
+  }
+  if (status == TPB_PATH_OK) {
+    // intersection fill (:404-411)
+    for (int base = 0; base < N; base += 32) {
+      const int i = base + lane;
+      bool need = false;
+      if (i < N) {
+        const double v = S.sdd[i];
+        need = (v != v);
+      }
+      unsigned m = __ballot_sync(kFullMask, need);
+      while (m) {
+        const int k = __ffs(m) - 1;
+        m &= m - 1;
+        S.sdd_at_intersection(base + k, S.p.load(base + k));
+      }
+    }
+    if (S.p.valid(S.p.load(0), sdd_start, S.sd2[0])) S.st(&S.sdd[0], sdd_start);  // (:414-416)
+    __syncwarp();
+    if (S.sd2[N - 1] != 0) status = TPB_PATH_FAIL_TERMINAL;
+  }
+  if (status == TPB_PATH_OK) {
+    for (int i = lane; i < N; i += 32) sd[i] = sqrt(S.sd2[i]);
+    // last_extremal_index_ (:435-445): highest i in [1, N-2] with sdd > 0 or on
+    // the limit curve, else 0; 32 samples per step from the top.
+    last_extremal = 0;
+    for (int top = (N - 2 > 1) ? N - 2 : 1; top >= 1; top -= 32) {
+      const int i = top - lane;
+      bool stop = false;
+      if (i >= 1) stop = (S.sdd[i] > 0.0) || (fabs(S.sd2[i] - S.bmax[i]) < kTiny);
+      const unsigned m = __ballot_sync(kFullMask, stop);
+      if (m) {
+        last_extremal = top - (__ffs(m) - 1);
+        break;
+      }
+    }
+    __syncwarp();
+    // time integration (:450-467): dt per lane, serial prefix in sample order.
+    double t = time_start;
+    if (lane == 0) time[0] = t;
+    for (int base = 1; base < N; base += 32) {
+      const int i = base + lane;
+      double dt = 0.0;
+      if (i < N) {
+        const double s2a = S.sd2[i - 1], s2b = S.sd2[i];
+        if ((s2a > 0) || (s2b > 0)) {
+          dt = 2.0 * S.ds / (sd[i - 1] + sd[i]);
+        } else {
+          dt = -1.0;  // marker: both zero
+        }
+      }
+      double mine = 0.0;
+      const int cnt = min(32, N - base);
+      for (int k = 0; k < cnt; ++k) {
+        const double dk = __shfl_sync(kFullMask, dt, k);
+        if (dk >= 0.0) t = t + dk;
+        if (k == lane) mine = t;
+      }
+      if (i < N) {
+        time[i] = mine;
+        if (dt < 0.0) {  // (:456-466) zero velocity on both sides
+          S.sdd[i - 1] = 0;
+          S.sdd[i] = 0;
+        }
+      }
+    }
+    __syncwarp();
+  }
+  if (lane == 0) {
+    a.status[b] = status;
+    a.last_extremal[b] = last_extremal;
+  }
+  __syncwarp();
+  if (lane == 0) {
+    a.duration[b] = (status == TPB_PATH_OK) ? (time[N - 1] - time[0]) : nan;
+  }
+}
+
+}  // namespace tpb
