@@ -10,7 +10,7 @@
 // flow); lanes split the O(C^2) work of FindSddMax/FindSddMin/
 // AreDerivativesValid (:624-695) -- how, is the Policy:
 //
-//   Joint8Policy   joint-space paths with D <= 8.  Lane = 8*g + d: group g of 8
+//   Joint8Policy<D> joint-space paths with D <= 8.  Lane = 8*g + d: group g of 8
 //                  lanes tests candidate j = 4*round + g against acceleration row
 //                  d.  Rows (q', q'' of one sample) live in registers and are
 //                  prefetched one step ahead of the sweep; the 2D velocity rows
@@ -115,86 +115,71 @@ struct GenericPolicy {
   }
 };
 
+// kD = number of dofs (1..8), compile-time so that the candidate rounds unroll.
+// Padding lanes (d >= kD) carry A = B = aS = vS2 = 0: their row tests evaluate
+// 0*c + 0 against [-0, 0] with kTiny slack and can never fail (NaN compares
+// false), so no lane predicate is needed anywhere.
+template <int kD>
 struct Joint8Policy {
   struct Rows {
-    double A, B;  // q'_d, q''_d of one sample (0 for d >= D)
+    double A, B;  // q'_d, q''_d of one sample (0 for d >= kD)
   };
-  int lane, D;
+  int lane;
   int g, d;  // lane = 8*g + d
-  const double *dq, *ddq;
+  const double *dq, *ddq;  // this path's rows, already offset by min(d, kD-1)
   double aS, vS2;  // amax_d*safety, (vmax_d*safety)^2 (row bounds: -aS..aS, 0..vS2)
+  bool active;     // d < kD
 
   __device__ __forceinline__ Rows load(int idx) const {
-    Rows r{0.0, 0.0};
-    if (d < D) {
-      r.A = dq[static_cast<size_t>(idx) * D + d];
-      r.B = ddq[static_cast<size_t>(idx) * D + d];
-    }
+    Rows r;
+    const double a0 = dq[idx * kD];
+    const double b0 = ddq[idx * kD];
+    r.A = active ? a0 : 0.0;
+    r.B = active ? b0 : 0.0;
     return r;
   }
 
-  // velocity rows (A = 0, B = q'^2, 0 <= . <= vS2): candidate independent
-  __device__ __forceinline__ bool velocity_rows_bad(const Rows& r, double sd2v) const {
-    bool bad = false;
-    if (d < D) {
-      const double v = (r.A * r.A) * sd2v;
-      bad = (v + kTiny < 0.0) || (v - kTiny > vS2);
-    }
-    return __ballot_sync(kFullMask, bad) != 0u;
-  }
-
   // AreDerivativesValid (:624-636)
-  __device__ bool valid(const Rows& r, double sddv, double sd2v) const {
-    bool bad = false;
-    if (d < D) {
-      const double v = r.A * sddv + r.B * sd2v;
-      bad = (v + kTiny < -aS) || (v - kTiny > aS);
-      // velocity row: 0*sdd contributes +-0 (or NaN for a non-finite sdd, which
-      // then passes every comparison exactly like in the reference)
-      const double w = 0.0 * sddv + (r.A * r.A) * sd2v;
-      bad = bad || (w + kTiny < 0.0) || (w - kTiny > vS2);
-    }
+  __device__ __forceinline__ bool valid(const Rows& r, double sddv, double sd2v) const {
+    const double v = r.A * sddv + r.B * sd2v;
+    bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
+    // velocity row (A = 0, B = q'^2, 0 <= . <= vS2): 0*sdd contributes +-0 (or NaN
+    // for a non-finite sdd, which then passes every comparison like in the reference)
+    const double w = 0.0 * sddv + (r.A * r.A) * sd2v;
+    bad = bad || (w + kTiny < 0.0) || (w - kTiny > vS2);
     return __ballot_sync(kFullMask, bad) == 0u;
   }
 
-  // FindSddMax / FindSddMin (:638-695)
+  // FindSddMax / FindSddMin (:638-695).  Velocity rows never yield a candidate
+  // (A == 0 exactly) and their validity does not depend on a finite candidate, so
+  // they are tested once; a non-finite candidate already fails its own row.
   template <bool kMax>
-  __device__ double find_sdd(const Rows& r, double sd2v) const {
+  __device__ __forceinline__ double find_sdd(const Rows& r, double sd2v) const {
     const double Bs = r.B * sd2v;
     // candidate of (row d, bound g&1); lanes of groups 2,3 duplicate groups 0,1
-    double cand = quiet_nan();
-    if (d < D && !is_tiny(r.A)) cand = (((g & 1) ? aS : -aS) - Bs) / r.A;
-    const bool vbad = velocity_rows_bad(r, sd2v);
+    const double num = ((g & 1) ? aS : -aS) - Bs;
+    const double cand = is_tiny(r.A) ? quiet_nan() : num / r.A;
+    const double vv = (r.A * r.A) * sd2v;
+    const bool vbad = __ballot_sync(kFullMask, (vv + kTiny < 0.0) || (vv - kTiny > vS2)) != 0u;
     double best = kMax ? -DBL_MAX : DBL_MAX;
-    const int ncand = 2 * D;
+    constexpr int ncand = 2 * kD;
+#pragma unroll
     for (int j0 = 0; j0 < ncand; j0 += 4) {
       const int j = j0 + g;  // this group's candidate: row j>>1, bound j&1
       const int src = ((j & 1) << 3) | ((j >> 1) & 7);
       const double c = __shfl_sync(kFullMask, cand, src);
-      bool bad = false;
-      if (d < D) {
-        const double v = r.A * c + Bs;
-        bad = (v + kTiny < -aS) || (v - kTiny > aS);
-      }
+      const double v = r.A * c + Bs;
+      const bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
       const unsigned m = __ballot_sync(kFullMask, bad);
-      // finite candidates only: NaN marks "no candidate"; +-inf fails its own row
+      // NaN marks "no candidate" (and fails c == c)
       const bool ok = (j < ncand) && (c == c) && (((m >> (8 * g)) & 0xffu) == 0u);
-      if (ok) {
-        if (kMax) {
-          best = (c > best) ? c : best;
-        } else {
-          best = (c < best) ? c : best;
-        }
-      }
+      const double pick = kMax ? ((c > best) ? c : best) : ((c < best) ? c : best);
+      best = ok ? pick : best;
     }
 #pragma unroll
     for (int o = 8; o <= 16; o <<= 1) {
       const double w = __shfl_xor_sync(kFullMask, best, o);
-      if (kMax) {
-        best = (w > best) ? w : best;
-      } else {
-        best = (w < best) ? w : best;
-      }
+      best = kMax ? ((w > best) ? w : best) : ((w < best) ? w : best);
     }
     if (vbad || best == (kMax ? -DBL_MAX : DBL_MAX)) best = 0.0;
     return best;
@@ -550,16 +535,9 @@ struct Solver {
 // Kernel: SetupProblem checks, OptimizePathParameter, outputs
 // ---------------------------------------------------------------------------
 
-template <class P>
-__device__ __forceinline__ void init_policy(P& p, const Dims& dm, const DeviceArrays& a, int b,
-                                            int lane, double safety, double* smem_rows,
-                                            bool joint, int* status);
-
-template <>
-__device__ __forceinline__ void init_policy<GenericPolicy>(GenericPolicy& p, const Dims& dm,
-                                                           const DeviceArrays& a, int b, int lane,
-                                                           double safety, double* smem_rows,
-                                                           bool joint, int* status) {
+__device__ __forceinline__ void init_policy(GenericPolicy& p, const Dims& dm,
+                                            const DeviceArrays& a, int b, int lane, double safety,
+                                            double* smem_rows, bool joint, int* status) {
   const size_t o = static_cast<size_t>(b) * dm.N;
   p.lane = lane;
   p.C = dm.C;
@@ -596,25 +574,24 @@ __device__ __forceinline__ void init_policy<GenericPolicy>(GenericPolicy& p, con
   __syncwarp();
 }
 
-template <>
-__device__ __forceinline__ void init_policy<Joint8Policy>(Joint8Policy& p, const Dims& dm,
-                                                          const DeviceArrays& a, int b, int lane,
-                                                          double safety, double*, bool,
-                                                          int* status) {
+template <int kD>
+__device__ __forceinline__ void init_policy(Joint8Policy<kD>& p, const Dims& dm,
+                                            const DeviceArrays& a, int b, int lane, double safety,
+                                            double*, bool, int* status) {
   const size_t o = static_cast<size_t>(b) * dm.N;
-  const int D = dm.D;
   p.lane = lane;
-  p.D = D;
   p.g = lane >> 3;
   p.d = lane & 7;
-  p.dq = a.dq + o * D;
-  p.ddq = a.ddq + o * D;
+  p.active = p.d < kD;
+  const int dd = p.active ? p.d : kD - 1;  // padding lanes read a valid address
+  p.dq = a.dq + o * kD + dd;
+  p.ddq = a.ddq + o * kD + dd;
   p.aS = 0.0;
   p.vS2 = 0.0;
   bool bad = false;
-  if (p.d < D) {
-    p.aS = a.amax[static_cast<size_t>(b) * D + p.d] * safety;
-    const double vs = a.vmax[static_cast<size_t>(b) * D + p.d] * safety;
+  if (p.active) {
+    p.aS = a.amax[static_cast<size_t>(b) * kD + p.d] * safety;
+    const double vs = a.vmax[static_cast<size_t>(b) * kD + p.d] * safety;
     p.vS2 = vs * vs;
     bad = (-p.aS >= p.aS) || (0.0 >= p.vS2);
   }
@@ -634,7 +611,7 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
 
   int status = TPB_PATH_OK;
   Solver<P> S;
-  init_policy<P>(S.p, dm, a, b, lane, safety,
+  init_policy(S.p, dm, a, b, lane, safety,
                  s_rows + (std::is_same<P, GenericPolicy>::value ? warp * 4 * kMaxRows : 0), joint,
                  &status);
   S.lane = lane;

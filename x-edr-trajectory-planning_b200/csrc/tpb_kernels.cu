@@ -412,7 +412,13 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
   const int blocks = (d.B + kWarpsPerBlock - 1) / kWarpsPerBlock;
   const bool joint = mode == Mode::kJoint;
   if (joint && d.D <= 8) {
-    k_integrate<Joint8Policy, 7><<<blocks, kWarpsPerBlock * 32, 0, st>>>(d, a, true, safety, max_loops);
+    const int threads = kWarpsPerBlock * 32;
+#define TPB_J8(K) \
+  case K: k_integrate<Joint8Policy<K>, 7><<<blocks, threads, 0, st>>>(d, a, true, safety, max_loops); break
+    switch (d.D) {
+      TPB_J8(1); TPB_J8(2); TPB_J8(3); TPB_J8(4); TPB_J8(5); TPB_J8(6); TPB_J8(7); TPB_J8(8);
+    }
+#undef TPB_J8
   } else {
     k_integrate<GenericPolicy, 4><<<blocks, kWarpsPerBlock * 32, 0, st>>>(d, a, joint, safety, max_loops);
   }
