@@ -101,7 +101,10 @@ typedef enum {
   TPB_ARR_R_ACC = 54,    /* double [total][D] */
   TPB_ARR_R_S = 55,      /* double [total] */
   TPB_ARR_R_SD = 56,     /* double [total] */
-  TPB_ARR_R_SDD = 57     /* double [total] */
+  TPB_ARR_R_SDD = 57,    /* double [total] */
+  /* diagnostics: solver scratch [B][N]; holds per-path phase cycle stamps when the
+   * library is built with -DTPB_PROFILE_PHASES, otherwise unspecified */
+  TPB_ARR_DEBUG = 99
 } tpb_array;
 
 typedef struct tpb_engine tpb_engine;

@@ -1,0 +1,49 @@
+#!/usr/bin/env python
+"""Per-path phase timing of k_integrate (diagnostics, not a benchmark).
+
+Needs a library built with -DTPB_PROFILE_PHASES:
+    make -C x-edr-trajectory-planning_b200/csrc clean all EXTRA=-DTPB_PROFILE_PHASES
+Prints the distribution over paths of the SM-cycle count of every phase.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from __graft_entry__ import load_package  # noqa: E402
+
+pkg = load_package()
+B, N, D, W = 4096, 2048, 7, 10
+wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=1000)
+eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                 max_time_samples_total=B * 6144)
+eng.set_joint_waypoints(wp)
+eng.set_joint_limits(vmax, amax)
+eng.sample_paths()
+for _ in range(3):
+    eng.optimize()
+dbg = eng.get(pkg.ARR.DEBUG).reshape(B, N)[:, :16]
+names = ["init", "boundary", "first_back", "first_fwd", "loop", "finalize"]
+ph = np.diff(dbg[:, :7], axis=1)
+tot = dbg[:, 6]
+print("cycles per path: phase  mean  p50  p90  p99  max")
+for k, n in enumerate(names):
+    c = ph[:, k]
+    print(f"{n:12s} {c.mean():10.0f} {np.percentile(c, 50):10.0f} {np.percentile(c, 90):10.0f} "
+          f"{np.percentile(c, 99):10.0f} {c.max():10.0f}")
+print(f"{'total':12s} {tot.mean():10.0f} {np.percentile(tot, 50):10.0f} {np.percentile(tot, 90):10.0f} "
+      f"{np.percentile(tot, 99):10.0f} {tot.max():10.0f}")
+print("switching loops: mean %.1f max %d" % (dbg[:, 7].mean(), dbg[:, 7].max()))
+for k, n in ((10, "next_critical"), (11, "add_backward"), (12, "add_forward")):
+    c = dbg[:, k]
+    print(f"  loop/{n:14s} mean {c.mean():10.0f} p99 {np.percentile(c, 99):10.0f}")
+print("  loop steps backward mean %.0f forward mean %.0f; cycles/step bw %.0f fw %.0f" % (
+    dbg[:, 13].mean(), dbg[:, 14].mean(), dbg[:, 11].sum() / max(dbg[:, 13].sum(), 1),
+    dbg[:, 12].sum() / max(dbg[:, 14].sum(), 1)))
+start = dbg[:, 9] - dbg[:, 9].min()
+print("kernel span (cycles): %.0f; last start %.0f" % ((start + tot).max(), start.max()))
+worst = np.argsort(-tot)[:5]
+for b in worst:
+    print("path", b, "phases", ph[b].astype(int).tolist(), "loops", int(dbg[b, 7]))

@@ -162,3 +162,55 @@ def test_plan_joint_host_matches_staged_calls(pkg, po):
     np.testing.assert_array_equal(out["r_pos"], res["R_POS"])
     np.testing.assert_array_equal(out["r_acc"], res["R_ACC"])
     np.testing.assert_array_equal(out["r_sdd"], res["R_SDD"])
+
+
+def _limit_curve_oracle(po, wp_b, vmax_b, amax_b, N, rounding=0.2, safety=0.8):
+    ctrl, knots = po.joint_fit(wp_b, rounding)
+    delta = knots[-1] / (N - 1)
+    q, dq, ddq = po.joint_sample(knots, ctrl, N, 0.0, delta)
+    cons = po.joint_constraints(dq, ddq, vmax_b, amax_b, safety)
+    return po.solve(cons, 0.0, delta * (N - 1), max_loops=max(100, 10 * N)), cons
+
+
+@pytest.mark.parametrize("D", [2, 4, 7, 8])
+def test_tied_rows_duplicate_and_mirrored_dofs(pkg, po, D):
+    """Dofs that are copies / mirror images of dof 0 with the same limits make
+    two or more constraint rows active within kTiny in FindMaxSd2Simplex
+    (time_optimal_path_timing.cc:1187-1260): the tie handling (active-set order,
+    strict '<' slope choice, pairwise IsOptimal) must match the reference's
+    list semantics.  The limit curve itself is compared bit for bit."""
+    B, W, N = 6, 5, 300
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=123 + D)
+    for b in range(B):
+        for d in range(1, D):
+            kind = (b + d) % 3
+            if kind == 0:
+                wp[b, :, d] = wp[b, :, 0]
+            elif kind == 1:
+                wp[b, :, d] = -wp[b, :, 0]
+            if kind != 2:
+                vmax[b, d] = vmax[b, 0]
+                amax[b, d] = amax[b, 0]
+    res = _run_engine(pkg, wp, vmax, amax, N)
+    assert _check_against_oracle(po, res, wp, vmax, amax, N) == B
+    for b in range(B):
+        o, _ = _limit_curve_oracle(po, wp[b], vmax[b], amax[b], N)
+        for k, ok in (("B_SD2_MAX", "b_sd2_max"), ("B_SDD_MAX", "b_sdd_max"),
+                      ("B_SDD_MIN", "b_sdd_min"), ("B_SD2_ZERO", "b_sd2_zero"),
+                      ("B_TYPE", "b_type")):
+            assert np.array_equal(res[k][b], o[ok]), (b, k)
+
+
+def test_limit_curve_bitwise_cfg2_shape(pkg, po):
+    """The register-only joint LP (tpb_joint_limit.cuh) against the oracle's
+    FindMaxSd2Simplex / FindSddMax / FindSddMin on cfg2-shaped paths: limit
+    curve after CalculateBoundary's passes, boundary types and sd^2, bit for bit."""
+    B, W, D, N = 8, 10, 7, 1024
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=2024)
+    res = _run_engine(pkg, wp, vmax, amax, N)
+    for b in range(B):
+        o, _ = _limit_curve_oracle(po, wp[b], vmax[b], amax[b], N)
+        for k, ok in (("B_SD2_MAX", "b_sd2_max"), ("B_SDD_MAX", "b_sdd_max"),
+                      ("B_SDD_MIN", "b_sdd_min"), ("B_SD2_ZERO", "b_sd2_zero"),
+                      ("B_TYPE", "b_type"), ("SD2", "sd2")):
+            assert np.array_equal(res[k][b], o[ok], equal_nan=True), (b, k)

@@ -23,6 +23,7 @@ class ARR:
     B_SD2_MAX, B_SDD_MAX, B_SDD_MIN, B_SD2_ZERO, B_TYPE = 30, 31, 32, 33, 34
     STATUS, DURATION, LAST_EXTREMAL, KNOT_END = 40, 41, 42, 43
     R_OFFSET, R_TIME, R_POS, R_VEL, R_ACC, R_S, R_SD, R_SDD = 50, 51, 52, 53, 54, 55, 56, 57
+    DEBUG = 99
 
 
 class TpbError(RuntimeError):

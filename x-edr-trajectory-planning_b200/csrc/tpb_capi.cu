@@ -116,6 +116,7 @@ bool lookup(tpb_engine* e, tpb_array what, ArrayRef* r) {
     case TPB_ARR_DURATION: *r = {a.duration, B * sizeof(double)}; return true;
     case TPB_ARR_LAST_EXTREMAL: *r = {a.last_extremal, B * sizeof(int32_t)}; return true;
     case TPB_ARR_KNOT_END: *r = {a.knot_end, B * sizeof(double)}; return true;
+    case TPB_ARR_DEBUG: *r = {a.fix_val, BN}; return true;
     case TPB_ARR_R_OFFSET: *r = {a.r_offset, (B + 1) * sizeof(int64_t)}; return true;
     case TPB_ARR_R_TIME: *r = {a.r_time, packed_rows() * sizeof(double)}; return true;
     case TPB_ARR_R_POS: *r = {a.r_pos, packed_rows() * D * sizeof(double)}; return true;

@@ -11,8 +11,8 @@
 // AreDerivativesValid (:624-695) -- how, is the Policy:
 //
 //   Joint8Policy<D> joint-space paths with D <= 8.  Lane = 8*g + d: group g of 8
-//                  lanes tests candidate j = 4*round + g against acceleration row
-//                  d.  Rows (q', q'' of one sample) live in registers and are
+//                  lanes tests one candidate per round against acceleration row
+//                  d (four candidates per round).  Rows (q', q'' of one sample) live in registers and are
 //                  prefetched one step ahead of the sweep; the 2D velocity rows
 //                  have A == 0, so they never yield a candidate and their validity
 //                  does not depend on the candidate (tested once per call).
@@ -153,33 +153,56 @@ struct Joint8Policy {
   // FindSddMax / FindSddMin (:638-695).  Velocity rows never yield a candidate
   // (A == 0 exactly) and their validity does not depend on a finite candidate, so
   // they are tested once; a non-finite candidate already fails its own row.
+  //
+  // Row d has two candidates, (-aS - Bs)/A and (aS - Bs)/A; division by A is
+  // monotone, so which of the two is the larger one follows from the sign of A.
+  // Even groups compute the row's "outer" candidate (the larger one for kMax,
+  // the smaller one for kMin), odd groups the other.  The outer candidates of all
+  // rows are tested first (two rounds of four); the inner ones can only matter
+  // if one of them lies beyond the best valid outer candidate, which a single
+  // ballot decides -- then (rarely: infeasible or degenerate samples) they are
+  // tested as well.  The extremum over all valid candidates is what the
+  // reference's sequential loop returns, whatever the order of evaluation.
   template <bool kMax>
   __device__ __forceinline__ double find_sdd(const Rows& r, double sd2v) const {
     const double Bs = r.B * sd2v;
-    // candidate of (row d, bound g&1); lanes of groups 2,3 duplicate groups 0,1
-    const double num = ((g & 1) ? aS : -aS) - Bs;
-    const double cand = is_tiny(r.A) ? quiet_nan() : num / r.A;
+    const bool pos = r.A > 0.0;
+    const bool plus = ((g & 1) == 0) ? (kMax == pos) : (kMax != pos);
+    const double num = (plus ? aS : -aS) - Bs;
+    // rows without a candidate (|A| < kTiny, padding lanes) divide by 1 instead:
+    // x/0 would send the whole warp through the division's slow path
+    const bool none = is_tiny(r.A);
+    const double cand = none ? quiet_nan() : num / (none ? 1.0 : r.A);
     const double vv = (r.A * r.A) * sd2v;
     const bool vbad = __ballot_sync(kFullMask, (vv + kTiny < 0.0) || (vv - kTiny > vS2)) != 0u;
     double best = kMax ? -DBL_MAX : DBL_MAX;
-    constexpr int ncand = 2 * kD;
-#pragma unroll
-    for (int j0 = 0; j0 < ncand; j0 += 4) {
-      const int j = j0 + g;  // this group's candidate: row j>>1, bound j&1
-      const int src = ((j & 1) << 3) | ((j >> 1) & 7);
-      const double c = __shfl_sync(kFullMask, cand, src);
+    // one round: group g tests the candidate held by lane (src_group, row) against
+    // acceleration row d
+    auto round = [&](int row, int src_group) {
+      const double c = __shfl_sync(kFullMask, cand, (src_group << 3) | (row & 7));
       const double v = r.A * c + Bs;
       const bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
       const unsigned m = __ballot_sync(kFullMask, bad);
       // NaN marks "no candidate" (and fails c == c)
-      const bool ok = (j < ncand) && (c == c) && (((m >> (8 * g)) & 0xffu) == 0u);
+      const bool ok = (row < kD) && (c == c) && (((m >> (8 * g)) & 0xffu) == 0u);
       const double pick = kMax ? ((c > best) ? c : best) : ((c < best) ? c : best);
       best = ok ? pick : best;
-    }
+    };
+    auto reduce = [&]() {
 #pragma unroll
-    for (int o = 8; o <= 16; o <<= 1) {
-      const double w = __shfl_xor_sync(kFullMask, best, o);
-      best = kMax ? ((w > best) ? w : best) : ((w < best) ? w : best);
+      for (int o = 8; o <= 16; o <<= 1) {
+        const double w = __shfl_xor_sync(kFullMask, best, o);
+        best = kMax ? ((w > best) ? w : best) : ((w < best) ? w : best);
+      }
+    };
+#pragma unroll
+    for (int j0 = 0; j0 < kD; j0 += 4) round(j0 + g, 0);
+    reduce();
+    const bool beyond = (g & 1) && (cand == cand) && (kMax ? (cand > best) : (cand < best));
+    if (__ballot_sync(kFullMask, beyond) != 0u) {
+#pragma unroll
+      for (int j0 = 0; j0 < kD; j0 += 4) round(j0 + g, 1);
+      reduce();
     }
     if (vbad || best == (kMax ? -DBL_MAX : DBL_MAX)) best = 0.0;
     return best;
@@ -252,32 +275,34 @@ struct Solver {
     return (0.0 < m) ? m : 0.0;
   }
 
-  // CalculateBoundary passes 2-4 (:1379-1484).  Pass 2 mutates neighbours in
-  // place while it scans, but only where an isolated critical point exists
-  // (flags at0 = 0,1,0); paths without one (the common case) are scanned 32
-  // samples at a time, the others take the warp-uniform serial scan.
+  // CalculateBoundary passes 2-4 (:1379-1484).  Pass 2 mutates the neighbours of
+  // an isolated critical point (flags at0 = 0,1,0 around i) in place while it
+  // scans, and later iterations read the mutated values.  The scan therefore runs
+  // 32 samples at a time where that is equivalent to the serial order -- a chunk
+  // without an isolated point: everything before it has been applied, nothing
+  // inside it mutates -- and sample by sample (warp-uniform) through the rare
+  // chunks that contain one.
   __device__ void boundary_passes(double* fix_val, int* fix_idx) {
     if (lane == 0) {
       type[0] = kNone;
       type[N - 1] = kNone;
     }
-    bool iso = false;
-    for (int i = 1 + lane; i < N - 1; i += 32) iso |= (!at0[i - 1] && at0[i] && !at0[i + 1]);
-    const bool any_iso = __ballot_sync(kFullMask, iso) != 0u;
     int nwork = 0;
-    if (!any_iso) {
-      for (int base = 1; base < N - 1; base += 32) {
-        const int i = base + lane;
+    auto test = [&](int i, double bm, double bi, double bp) {
+      const double sd2p = (bp - bi) / ds;
+      const double smax_i = bsmax[i];
+      const bool sink_or_source = (sd2p < 2 * bsmin[i]) || (sd2p > 2 * smax_i);
+      const bool skipped_sdd = (smax_i > 0) && (bsmin[i + 1] < 0);
+      const bool skipped_sd2 = (bi > bm - kTiny) && (bi > bp - kTiny);
+      return (skipped_sd2 || skipped_sdd) && sink_or_source;
+    };
+    for (int base = 1; base < N - 1; base += 32) {
+      const int i = base + lane;
+      const bool in = i < N - 1;
+      const bool iso = in && !at0[i - 1] && at0[i] && !at0[i + 1];
+      if (__ballot_sync(kFullMask, iso) == 0u) {
         bool hit = false;
-        if (i < N - 1) {
-          const double bi = bmax[i], bp = bmax[i + 1], bm = bmax[i - 1];
-          const double sd2p = (bp - bi) / ds;
-          const double smax_i = bsmax[i];
-          const bool sink_or_source = (sd2p < 2 * bsmin[i]) || (sd2p > 2 * smax_i);
-          const bool skipped_sdd = (smax_i > 0) && (bsmin[i + 1] < 0);
-          const bool skipped_sd2 = (bi > bm - kTiny) && (bi > bp - kTiny);
-          hit = (skipped_sd2 || skipped_sdd) && sink_or_source;
-        }
+        if (in) hit = test(i, bmax[i - 1], bmax[i], bmax[i + 1]);
         unsigned m = __ballot_sync(kFullMask, hit);
         while (m) {
           const int k = __ffs(m) - 1;
@@ -290,24 +315,21 @@ struct Solver {
           }
           ++nwork;
         }
-      }
-    } else {
-      for (int i = 1; i < N - 1; ++i) {
-        if (!at0[i - 1] && at0[i] && !at0[i + 1]) fix_isolated(i);
-        const double bi = bmax[i], bp = bmax[i + 1], bm = bmax[i - 1];
-        const double sd2p = (bp - bi) / ds;
-        const double smax_i = bsmax[i];
-        const bool sink_or_source = (sd2p < 2 * bsmin[i]) || (sd2p > 2 * smax_i);
-        const bool skipped_sdd = (smax_i > 0) && (bsmin[i + 1] < 0);
-        const bool skipped_sd2 = (bi > bm - kTiny) && (bi > bp - kTiny);
-        if ((skipped_sd2 || skipped_sdd) && sink_or_source) {
-          const double v = skipped_value(i, bm, bp);
-          if (lane == 0) {
-            fix_idx[nwork] = i;
-            fix_val[nwork] = v;
+      } else {
+        const int top = min(base + 32, N - 1);
+        for (int ii = base; ii < top; ++ii) {
+          if (!at0[ii - 1] && at0[ii] && !at0[ii + 1]) fix_isolated(ii);
+          const double bm = bmax[ii - 1], bp = bmax[ii + 1];
+          if (test(ii, bm, bmax[ii], bp)) {
+            const double v = skipped_value(ii, bm, bp);
+            if (lane == 0) {
+              fix_idx[nwork] = ii;
+              fix_val[nwork] = v;
+            }
+            ++nwork;
           }
-          ++nwork;
         }
+        __syncwarp();
       }
     }
     __syncwarp();
@@ -647,6 +669,17 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
 
   int last_extremal = 0;
   const double nan = quiet_nan();
+#ifdef TPB_PROFILE_PHASES
+  long long ph[8];
+  long long acc_nc = 0, acc_bw = 0, acc_fw = 0;
+  int steps_bw = 0, steps_fw = 0;
+  int nloops = 0;
+  for (int k = 0; k < 8; ++k) ph[k] = 0;
+  ph[0] = clock64();
+#define TPB_STAMP(k) ph[k] = clock64()
+#else
+#define TPB_STAMP(k)
+#endif
   if (status == TPB_PATH_OK) {
     // SetSetupDone (:535-552)
     const double ds = (s_end - s_start) / (N - 1);
@@ -668,11 +701,15 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
     __syncwarp();
 
     // ---- OptimizePathParameter (:287-490)
+    TPB_STAMP(1);
     S.boundary_passes(fix_val, fix_idx);
+    TPB_STAMP(2);
 
     int iforw_lo = 0, iback_hi = N - 1, iback_lo, iforw_hi, icrit, icrit_lo, icrit_hi;
     iback_lo = S.add_backward(iback_hi);
+    TPB_STAMP(3);
     iforw_hi = S.add_forward(iforw_lo);
+    TPB_STAMP(4);
     icrit_hi = iback_lo;
     if ((iforw_hi < icrit_hi) && ((icrit_hi < N - 2) && (icrit_hi >= 2))) {
       S.st(&S.sd2[icrit_hi], nan);
@@ -682,7 +719,16 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
     icrit_lo = iforw_hi;
     for (int loop = 0; loop < max_loops; ++loop) {
       if (iforw_hi >= icrit_hi) break;
+#ifdef TPB_PROFILE_PHASES
+      ++nloops;
+#endif
+#ifdef TPB_PROFILE_PHASES
+      const long long c0 = clock64();
+#endif
       icrit = S.next_critical(icrit_lo, icrit_hi);
+#ifdef TPB_PROFILE_PHASES
+      acc_nc += clock64() - c0;
+#endif
       if (icrit < 0 || icrit >= N) icrit = static_cast<int>(0.5 * (icrit_lo + icrit_hi));
       if (icrit > 0 && icrit < N - 1) S.st(&S.sd2[icrit], S.bmax[icrit]);
       if (icrit < 1) {
@@ -695,9 +741,21 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
       } else {
         iback_hi = icrit;
       }
+#ifdef TPB_PROFILE_PHASES
+      const long long c1 = clock64();
+#endif
       iback_lo = S.add_backward(iback_hi);
+#ifdef TPB_PROFILE_PHASES
+      const long long c2 = clock64();
+      acc_bw += c2 - c1;
+      steps_bw += iback_hi - iback_lo;
+#endif
       iforw_lo = icrit;
       iforw_hi = S.add_forward(iforw_lo);
+#ifdef TPB_PROFILE_PHASES
+      acc_fw += clock64() - c2;
+      steps_fw += iforw_hi - iforw_lo;
+#endif
       if (iback_lo > icrit_lo) {
         status = TPB_PATH_FAIL_CONNECT;
         break;
@@ -705,6 +763,7 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
       icrit_lo = iforw_hi;
     }
   }
+  TPB_STAMP(5);
   if (status == TPB_PATH_OK) {
     // NaN audit (:398-403)
     bool any_nan = false;
@@ -789,6 +848,24 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
   if (lane == 0) {
     a.duration[b] = (status == TPB_PATH_OK) ? (time[N - 1] - time[0]) : nan;
   }
+#ifdef TPB_PROFILE_PHASES
+  // diagnostics build only: per-path phase time stamps (SM cycles) in fix_val
+  TPB_STAMP(6);
+  if (lane == 0 && N >= 16) {
+    for (int k = 0; k < 7; ++k) fix_val[k] = static_cast<double>(ph[k] - ph[0]);
+    fix_val[7] = nloops;
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    fix_val[8] = smid;
+    fix_val[9] = static_cast<double>(ph[0]);
+    fix_val[10] = static_cast<double>(acc_nc);
+    fix_val[11] = static_cast<double>(acc_bw);
+    fix_val[12] = static_cast<double>(acc_fw);
+    fix_val[13] = steps_bw;
+    fix_val[14] = steps_fw;
+  }
+#endif
+#undef TPB_STAMP
 }
 
 }  // namespace tpb

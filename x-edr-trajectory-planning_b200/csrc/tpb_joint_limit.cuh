@@ -1,0 +1,329 @@
+// Per-sample limit curve of a joint-space path with kD <= 8 dofs, one sample per
+// thread, everything in registers (no local-memory arrays).
+//
+// Same results, bit for bit, as the generic lp_max_sd2 / find_sdd_min_max of
+// tpb_solver.cuh (FindMaxSd2Simplex time_optimal_path_timing.cc:1149-1363,
+// IsOptimal :1105-1147, FindSddMax/FindSddMin/AreDerivativesValid :624-695)
+// applied to the rows TimeableJointSplinePath::ConstraintSetup builds
+// (timeable_path_joint_spline.cc:320-343):
+//
+//   row d      (acceleration)  A = q'_d   B = q''_d    -aS_d <= . <= aS_d
+//   row kD + d (velocity)      A = 0      B = q'_d^2    0    <= . <= vS2_d
+//
+// What the specialisation uses:
+//  * loops over rows are compile-time unrolled, so A[], B[] are registers; the
+//    reference's constraint_set_ / active-set vectors are 32-bit slot masks
+//    (slot = 2*row + (type == lower)) walked in ascending order = list order;
+//  * velocity rows have A == 0: along an edge sdd = a + b*sd2 their B
+//    coefficient stays q'^2 whenever b is finite, so 1/q'^2 is computed once and
+//    reused by every simplex iteration (the identity is checked at run time, the
+//    division is redone when it does not hold); their lower slots (bound 0) can
+//    never become active because the walk only accepts sd2 > current sd2 > 0;
+//  * the common case of exactly one new active row per iteration keeps that row
+//    as scalars; ties (two or more rows within kTiny) take a slow path that
+//    fetches rows with select chains.
+#pragma once
+
+#include "tpb_device.cuh"
+
+namespace tpb {
+
+struct LpEntry {
+  double A, B, bound;
+  int type;  // kUpper / kLower
+  int slot;
+};
+
+// IsOptimal (:1105-1147) on two explicit rows.
+__device__ __forceinline__ bool lp_is_optimal_e(const LpEntry& e1, const LpEntry& e2) {
+  const double denom = e2.A * e1.B - e1.A * e2.B;
+  if (fabs(denom) < kTiny) return false;
+  const double x = denom * e1.A;
+  const double y = denom * (-e2.A);
+  if (e1.type == kUpper) {
+    if (e2.type == kUpper) return x <= 0 && y <= 0;
+    return x >= 0 && y <= 0;
+  }
+  if (e2.type == kUpper) return x <= 0 && y >= 0;
+  return x >= 0 && y >= 0;
+}
+
+template <int kD>
+struct JointLimit {
+  double A[kD], B[kD];  // q', q'' of this sample
+  double Bv[kD];        // q'^2 (B of the velocity rows)
+  double invBv[kD];     // 1 / q'^2
+  const double* aS;     // [kD] shared memory: amax * safety
+  const double* vS2;    // [kD] shared memory: (vmax * safety)^2
+
+  __device__ __forceinline__ static double sel(const double (&x)[kD], int i) {
+    double r = x[0];
+#pragma unroll
+    for (int k = 1; k < kD; ++k) r = (i == k) ? x[k] : r;
+    return r;
+  }
+
+  // row data by slot (slow paths only)
+  __device__ LpEntry entry(int slot) const {
+    const int row = slot >> 1;
+    const bool lower = slot & 1;
+    LpEntry e;
+    e.slot = slot;
+    e.type = lower ? kLower : kUpper;
+    if (row < kD) {
+      e.A = sel(A, row);
+      e.B = sel(B, row);
+      const double s = aS[row];
+      e.bound = lower ? -s : s;
+    } else {
+      e.A = 0.0;
+      e.B = sel(Bv, row - kD);
+      e.bound = lower ? 0.0 : vS2[row - kD];
+    }
+    return e;
+  }
+
+  __device__ __forceinline__ void prepare() {
+#pragma unroll
+    for (int d = 0; d < kD; ++d) {
+      Bv[d] = A[d] * A[d];
+      // only used where Bv >= kTiny (rows with |Bc| < kTiny are skipped)
+      invBv[d] = 1.0 / ((Bv[d] < kTiny) ? 1.0 : Bv[d]);
+    }
+  }
+
+  // FindMaxSd2Simplex (:1149-1363)
+  __device__ void lp(double& sd2max, double& sddmax, double& sd2zero) const {
+    constexpr int C = 2 * kD;
+    unsigned act = 0u;
+    double sd2 = DBL_MAX;
+    double sdd = 0.0;
+    LpEntry last;
+    last.A = last.B = last.bound = 0.0;
+    last.type = kUpper;
+    last.slot = 0;
+
+    // Step 2: walk along sdd = 0.
+#pragma unroll
+    for (int d = 0; d < kD; ++d) {
+      const double Bi = B[d];
+      const bool up = Bi > kTiny, dn = Bi < -kTiny;
+      const double invB = 1.0 / ((up || dn) ? Bi : 1.0);  // unused rows: keep the fast path
+      const double bound = up ? aS[d] : -aS[d];
+      const double tmp = bound * invB;
+      if ((up || dn) && tmp < (sd2 + kTiny) && tmp > 0) {
+        if (tmp < sd2 - kTiny) act = 0u;
+        const int slot = 2 * d + (up ? 0 : 1);
+        act |= 1u << slot;
+        sd2 = tmp;
+        last.A = A[d];
+        last.B = Bi;
+        last.bound = bound;
+        last.type = up ? kUpper : kLower;
+        last.slot = slot;
+      }
+    }
+#pragma unroll
+    for (int d = 0; d < kD; ++d) {
+      const double Bi = Bv[d];
+      const double tmp = vS2[d] * invBv[d];
+      if (Bi > kTiny && tmp < (sd2 + kTiny) && tmp > 0) {
+        if (tmp < sd2 - kTiny) act = 0u;
+        const int slot = 2 * (kD + d);
+        act |= 1u << slot;
+        sd2 = tmp;
+        last.A = 0.0;
+        last.B = Bi;
+        last.bound = vS2[d];
+        last.type = kUpper;
+        last.slot = slot;
+      }
+    }
+    if (sd2 > kMaxSd2 || act == 0u) {
+      sd2zero = kMaxSd2;
+      sd2max = kMaxSd2;
+      sddmax = 0.0;
+      return;
+    }
+    sd2zero = sd2;
+
+    // Step 3 on the initial active set.
+    LpEntry s = last;
+    if (__popc(act) > 1) {
+      unsigned m = act;
+      double s_slope = DBL_MAX;
+      bool first = true;
+      while (m) {
+        const int f = __ffs(m) - 1;
+        m &= m - 1;
+        const LpEntry ef = entry(f);
+        const double slope = fabs(ef.A * (1.0 / ef.B));
+        if (first || slope < s_slope) {
+          s = ef;
+          s_slope = slope;
+          first = false;
+        }
+        unsigned m2 = m;
+        while (m2) {
+          const int g = __ffs(m2) - 1;
+          m2 &= m2 - 1;
+          if (lp_is_optimal_e(ef, entry(g))) {
+            sd2max = sd2;
+            sddmax = 0.0;
+            return;
+          }
+        }
+      }
+    }
+    unsigned in_set = ((C >= 16) ? ~0u : ((1u << (2 * C)) - 1u)) & ~act;
+
+    for (int loop = 0; loop < C; ++loop) {
+      const double As = s.A;
+      if (fabs(As) < kTiny) {
+        sd2max = sd2;
+        sddmax = sdd;
+        return;
+      }
+      const double invA = 1.0 / As;
+      const double b = -s.B * invA;
+      const double a = s.bound * invA;
+
+      // Step 4: next vertex along sdd = a + b * sd2.
+      act = 0u;
+      double next_sd2 = DBL_MAX, next_sdd = 0.0;
+#pragma unroll
+      for (int d = 0; d < kD; ++d) {
+        const double Ac = A[d];
+        const double Bc = Ac * b + B[d];
+        const bool usable = !(fabs(Bc) < kTiny);
+        const double invB = 1.0 / (usable ? Bc : 1.0);
+        const double Aca = Ac * a;
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {  // upper slot first, then lower (slot order)
+          const int slot = 2 * d + w;
+          const double bound = w ? -aS[d] : aS[d];
+          const double tmp = (bound - Aca) * invB;
+          if (usable && ((in_set >> slot) & 1u) && tmp < (next_sd2 + kTiny) && tmp > sd2) {
+            if (tmp < next_sd2 - kTiny) act = 0u;
+            act |= 1u << slot;
+            next_sd2 = tmp;
+            next_sdd = a + b * next_sd2;
+            last.A = Ac;
+            last.B = B[d];
+            last.bound = bound;
+            last.type = w ? kLower : kUpper;
+            last.slot = slot;
+          }
+        }
+      }
+      const double zb = 0.0 * b, za = 0.0 * a;
+#pragma unroll
+      for (int d = 0; d < kD; ++d) {
+        const double Bc = zb + Bv[d];
+        const bool usable = !(fabs(Bc) < kTiny);
+        const int slot = 2 * (kD + d);
+        double invB = invBv[d];
+        if (!(Bc == Bv[d])) invB = 1.0 / Bc;  // non-finite b only
+        const double tmp = (vS2[d] - za) * invB;
+        if (usable && ((in_set >> slot) & 1u) && tmp < (next_sd2 + kTiny) && tmp > sd2) {
+          if (tmp < next_sd2 - kTiny) act = 0u;
+          act |= 1u << slot;
+          next_sd2 = tmp;
+          next_sdd = a + b * next_sd2;
+          last.A = 0.0;
+          last.B = Bv[d];
+          last.bound = vS2[d];
+          last.type = kUpper;
+          last.slot = slot;
+        }
+        // lower slot: tmp = (0 - za) * invB is +-0 or NaN, never > sd2 > 0
+      }
+      if (act == 0u) {  // unbounded along this edge
+        sd2max = sd2zero;
+        sddmax = 0.0;
+        return;
+      }
+      // active list = new rows (slot order) followed by s: pairwise optimality,
+      // next edge = lowest slope among the new rows (first one on ties)
+      bool optimal = false;
+      LpEntry sn = last;
+      if (__popc(act) == 1) {
+        optimal = lp_is_optimal_e(last, s);
+      } else {
+        unsigned m = act;
+        double s_slope = DBL_MAX;
+        while (m) {
+          const int f = __ffs(m) - 1;
+          m &= m - 1;
+          const LpEntry ef = entry(f);
+          const double Bc = ef.A * b + ef.B;
+          const double slope = fabs(ef.A * (1.0 / Bc));
+          if (slope < s_slope) {
+            sn = ef;
+            s_slope = slope;
+          }
+          unsigned m2 = m;
+          while (m2) {
+            const int g = __ffs(m2) - 1;
+            m2 &= m2 - 1;
+            optimal = optimal || lp_is_optimal_e(ef, entry(g));
+          }
+          optimal = optimal || lp_is_optimal_e(ef, s);
+        }
+      }
+      if (optimal) {
+        sd2max = next_sd2;
+        sddmax = next_sdd;
+        if (next_sd2 > kMaxSd2) {
+          sd2max = kMaxSd2;
+          sddmax = 0.0;
+        }
+        return;
+      }
+      in_set &= ~act;
+      s = sn;
+      sd2 = next_sd2;
+      sdd = next_sdd;
+    }
+    sd2max = sd2zero;
+    sddmax = 0.0;
+  }
+
+  // FindSddMax and FindSddMin at the same sd2 (:638-695) with the validity test
+  // (:624-636).  Only acceleration rows yield candidates (velocity rows have
+  // A == 0); a velocity row evaluates 0*cand + q'^2*sd2, which does not depend
+  // on a finite candidate and is NaN (passes every comparison) otherwise.
+  __device__ void sdd_min_max(double sd2, double& sdd_max, double& sdd_min) const {
+    double Bs[kD];
+    bool vbad = false;
+#pragma unroll
+    for (int d = 0; d < kD; ++d) {
+      Bs[d] = B[d] * sd2;
+      const double w = Bv[d] * sd2;
+      vbad = vbad || (w + kTiny < 0.0) || (w - kTiny > vS2[d]);
+    }
+    double mx = -DBL_MAX, mn = DBL_MAX;
+#pragma unroll
+    for (int i = 0; i < kD; ++i) {
+      const double Ai = A[i];
+      const bool has = !is_tiny(Ai);
+#pragma unroll
+      for (int w = 0; w < 2; ++w) {
+        const double cand = ((w == 0 ? -aS[i] : aS[i]) - Bs[i]) / (has ? Ai : 1.0);
+        const double zc = 0.0 * cand;
+        bool ok = has && !((zc == zc) && vbad);
+#pragma unroll
+        for (int r = 0; r < kD; ++r) {
+          const double v = A[r] * cand + Bs[r];
+          ok = ok && !((v + kTiny < -aS[r]) || (v - kTiny > aS[r]));
+        }
+        mx = (ok && cand > mx) ? cand : mx;
+        mn = (ok && cand < mn) ? cand : mn;
+      }
+    }
+    sdd_max = (mx == -DBL_MAX) ? 0.0 : mx;
+    sdd_min = (mn == DBL_MAX) ? 0.0 : mn;
+  }
+};
+
+}  // namespace tpb

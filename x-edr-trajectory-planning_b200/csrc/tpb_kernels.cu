@@ -11,10 +11,12 @@
 //                         extremals + switching-point loop + time integration (:287-490)
 //  k_resample_*           trajectory assembly + ResampleEquidistantlyInTime
 //                         (path_timing_trajectory.cc:458-472, :686-783)
+#include <algorithm>
 #include <type_traits>
 
 #include "tpb_engine.h"
 #include "tpb_integrate.cuh"
+#include "tpb_joint_limit.cuh"
 #include "tpb_solver.cuh"
 
 namespace tpb {
@@ -118,8 +120,9 @@ __global__ void k_joint_fit(Dims dm, DeviceArrays a, double rounding, bool auto_
 
 constexpr int kSampleThreads = 128;
 
+// Any D <= kMaxDofs: rows in thread-local arrays, generic LP (used for D > 8).
 __global__ void __launch_bounds__(kSampleThreads)
-k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
+k_joint_sample_limit_any(Dims dm, DeviceArrays a, double safety) {
   extern __shared__ double smem[];
   const int b = blockIdx.y;
   const int D = dm.D;
@@ -205,6 +208,108 @@ k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
   a.b_at0[o] = fabs(sd2max - sd2zero) < kTiny;
 }
 
+// D = kD <= 8: one sample per thread, rows and the whole active-set LP in
+// registers (tpb_joint_limit.cuh); q, q', q'' leave through shared memory so that
+// each CTA writes its 128 consecutive [sample][D] rows as contiguous runs.
+template <int kD>
+__global__ void __launch_bounds__(kSampleThreads)
+k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
+  extern __shared__ double smem[];
+  const int b = blockIdx.y;
+  const int n = a.num_points[b];
+  const int nk = n + 3;
+  double* s_knots = smem;                         // [max_points + 3]
+  double* s_ctrl = s_knots + dm.max_points + 3;   // [max_points][kD]
+  double* s_aS = s_ctrl + dm.max_points * kD;     // [kD]  amax * safety
+  double* s_vS2 = s_aS + kD;                      // [kD]  (vmax * safety)^2
+  double* s_out = s_vS2 + kD;                     // [3][kSampleThreads * kD]
+  {
+    const double* gk = a.knots + static_cast<size_t>(b) * (dm.max_points + 3);
+    const double* gc = a.ctrl + static_cast<size_t>(b) * dm.max_points * kD;
+    for (int i = threadIdx.x; i < nk; i += blockDim.x) s_knots[i] = gk[i];
+    for (int i = threadIdx.x; i < n * kD; i += blockDim.x) s_ctrl[i] = gc[i];
+    if (threadIdx.x < kD) {
+      const double am = a.amax[static_cast<size_t>(b) * kD + threadIdx.x];
+      const double vm = a.vmax[static_cast<size_t>(b) * kD + threadIdx.x];
+      s_aS[threadIdx.x] = am * safety;
+      const double vs = vm * safety;
+      s_vS2[threadIdx.x] = vs * vs;
+    }
+  }
+  __syncthreads();
+  const int idx0 = blockIdx.x * kSampleThreads;
+  const int idx = idx0 + threadIdx.x;
+  const bool live = idx < dm.N;
+
+  JointLimit<kD> J;
+  J.aS = s_aS;
+  J.vS2 = s_vS2;
+  if (live) {
+    // SamplePath, timeable_path_joint_spline.cc:294-318.
+    const double delta = a.delta[b];
+    const double path_start = a.path_start[b];
+    const double parameter = path_start + idx * delta;
+    const double k0 = s_knots[0], k1 = s_knots[nk - 1];
+    double* o0 = s_out + threadIdx.x * kD;
+    double* o1 = o0 + kSampleThreads * kD;
+    double* o2 = o1 + kSampleThreads * kD;
+    if (parameter < k1 + delta) {
+      const double u = (parameter < k0) ? k0 : ((k1 < parameter) ? k1 : parameter);
+      const int span = knot_span(s_knots, nk, 2, u);
+      double ders[3][3];
+      basis_ders<2, 2>(s_knots, span, u, ders);
+      // EvalCurveAndDerivatives, splines/bspline.h:561-566.
+      const double* P0 = s_ctrl + (span - 2) * kD;
+#pragma unroll
+      for (int d = 0; d < kD; ++d) {
+        double v0 = 0.0, v1 = 0.0, v2 = 0.0;
+#pragma unroll
+        for (int j = 0; j <= 2; ++j) {
+          const double Pj = P0[j * kD + d];
+          v0 += ders[0][j] * Pj;
+          v1 += ders[1][j] * Pj;
+          v2 += ders[2][j] * Pj;
+        }
+        o0[d] = v0;
+        o1[d] = v1;
+        o2[d] = v2;
+        J.A[d] = v1;
+        J.B[d] = v2;
+      }
+    } else {
+#pragma unroll
+      for (int d = 0; d < kD; ++d) {
+        o0[d] = s_ctrl[(n - 1) * kD + d];
+        o1[d] = 0.0;
+        o2[d] = 0.0;
+        J.A[d] = 0.0;
+        J.B[d] = 0.0;
+      }
+    }
+    // ConstraintSetup (:320-343) + CalculateBoundary's per-sample part
+    // (time_optimal_path_timing.cc:1366-1377); rows never leave the registers.
+    J.prepare();
+    double sd2max, sddmax, sd2zero, smax, smin;
+    J.lp(sd2max, sddmax, sd2zero);
+    J.sdd_min_max(sd2max, smax, smin);
+    const size_t o = static_cast<size_t>(b) * dm.N + idx;
+    a.b_raw_sd2_max[o] = sd2max;
+    a.b_sd2_zero[o] = sd2zero;
+    a.b_raw_sdd_max[o] = smax;
+    a.b_raw_sdd_min[o] = smin;
+    a.b_at0[o] = fabs(sd2max - sd2zero) < kTiny;
+  }
+  __syncthreads();
+  // coalesced copy-out of this CTA's rows [idx0, idx0 + cnt)
+  const int cnt = min(kSampleThreads, dm.N - idx0);
+  const size_t g0 = (static_cast<size_t>(b) * dm.N + idx0) * kD;
+  for (int k = threadIdx.x; k < cnt * kD; k += kSampleThreads) {
+    a.q[g0 + k] = s_out[k];
+    a.dq[g0 + k] = s_out[kSampleThreads * kD + k];
+    a.ddq[g0 + k] = s_out[2 * kSampleThreads * kD + k];
+  }
+}
+
 __global__ void __launch_bounds__(kSampleThreads)
 k_generic_limit(Dims dm, DeviceArrays a) {
   const int b = blockIdx.y;
@@ -284,79 +389,103 @@ __device__ __forceinline__ double clampa(double v, double lim) {
   return (lim < v) ? lim : v;  // cwiseMin(amax)
 }
 
-constexpr int kResampleThreads = 128;
+constexpr int kResampleThreads = 256;
 
-// One thread per packed output row (grid-stride; the row count is read from
-// r_offset[B] on the device, so no host round trip).  Rows past r_capacity are
-// dropped (the host reports kOutOfRange).
+// One CTA per path (grid-stride over paths): time[] of the path is staged in
+// shared memory (the per-row lower-index search runs there), each thread owns
+// one output row per pass, and every warp transposes its 32 rows x D values
+// through shared memory so that the packed [row][D] arrays are written as
+// contiguous 256-byte runs.  Rows past r_capacity are dropped (the host reports
+// kOutOfRange).  kSmemTime = false: N too large for shared memory, search in
+// global memory.
+template <bool kSmemTime>
 __global__ void __launch_bounds__(kResampleThreads)
 k_resample_fill(Dims dm, DeviceArrays a, double start_sec, double dt) {
-  const int64_t total = min(a.r_offset[dm.B], dm.r_cap);
-  for (int64_t row = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; row < total;
-       row += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    // path owning this row: last b with r_offset[b] <= row
-    int blo = 0, bhi = dm.B - 1;
-    while (blo < bhi) {
-      const int mid = (blo + bhi + 1) >> 1;
-      if (a.r_offset[mid] <= row) {
-        blo = mid;
-      } else {
-        bhi = mid - 1;
-      }
-    }
-    const int b = blo;
+  extern __shared__ double smem[];
+  const int N = dm.N, D = dm.D;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double* s_time = smem;                                    // [N] (kSmemTime)
+  double* s_tile = smem + (kSmemTime ? N : 0) + warp * 3 * 32 * D;  // [3][32][D] per warp
+  for (int b = blockIdx.x; b < dm.B; b += gridDim.x) {
     const int M = a.r_count[b];
-    const int i = static_cast<int>(row - a.r_offset[b]);
-    const int N = dm.N, D = dm.D;
+    if (M == 0) continue;  // uniform per CTA
+    const int64_t row0 = a.r_offset[b];
     const size_t o = static_cast<size_t>(b) * N;
-    const double* tp = a.time + o;
-    const double t = start_sec + dt * i;
-    // TimeAtPathSamplesLowerIndex (:686-695): first index with time[index+1] > t,
-    // else N-1.  time[] is non-decreasing, so the reference's monotone linear scan
-    // equals this binary search.
-    int lo = 0, hi = N - 1;  // answer in [0, N-1]
-    while (lo < hi) {
-      const int mid = (lo + hi) >> 1;
-      if (tp[mid + 1] > t) {
-        hi = mid;
-      } else {
-        lo = mid + 1;
-      }
+    const double* tg = a.time + o;
+    if (kSmemTime) {
+      __syncthreads();  // previous path's searches are done
+      for (int i = threadIdx.x; i < N; i += blockDim.x) s_time[i] = tg[i];
+      __syncthreads();
     }
-    const int li = lo;
-    const int ui = min(N - 1, li + 1);
-    const double tl = tp[li], tu = tp[ui];
-    const double at = (fabs(tu - tl) < DBL_EPSILON) ? 0.5 : (t - tl) / (tu - tl);
-    const double sdl = a.sd[o + li], sdu = a.sd[o + ui];
-    const double sddl = a.sdd[o + li], sddu = a.sdd[o + ui];
-    a.r_time[row] = t;
-    a.r_s[row] = lerp(at, a.s[o + li], a.s[o + ui]);
-    a.r_sd[row] = lerp(at, sdl, sdu);
-    a.r_sdd[row] = lerp(at, sddl, sddu);
-    const bool last = (i == M - 1);
-    const double sdl2 = sdl * sdl, sdu2 = sdu * sdu;  // eigenmath::Square
-    for (int d = 0; d < D; ++d) {
-      const double am = a.amax[static_cast<size_t>(b) * D + d];
-      const size_t rl = (o + li) * D + d, ru = (o + ui) * D + d;
-      double pos, vel, acc;
-      if (last) {  // (:780-782)
-        pos = a.q[(o + N - 1) * D + d];
-        vel = 0.0;
-        acc = 0.0;
-      } else {
-        const double d1l = a.dq[rl], d1u = a.dq[ru];
-        const double d2l = a.ddq[rl], d2u = a.ddq[ru];
-        // per-sample velocity / clamped acceleration (:458-472)
-        const double vl = d1l * sdl, vu = d1u * sdu;
-        const double al = clampa(d1l * sddl + d2l * sdl2, am);
-        const double au = clampa(d1u * sddu + d2u * sdu2, am);
-        pos = lerp(at, a.q[rl], a.q[ru]);
-        vel = lerp(at, vl, vu);
-        acc = clampa(lerp(at, al, au), am);
+    const double* tp = kSmemTime ? s_time : tg;
+    for (int base = warp * 32; base < M; base += kResampleThreads) {
+      const int i = base + lane;
+      const bool live = i < M;
+      if (live) {
+        const int64_t row = row0 + i;
+        const double t = start_sec + dt * i;
+        // TimeAtPathSamplesLowerIndex (:686-695): first index with time[index+1] > t,
+        // else N-1.  time[] is non-decreasing, so the reference's monotone linear scan
+        // equals this binary search.
+        int lo = 0, hi = N - 1;  // answer in [0, N-1]
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (tp[mid + 1] > t) {
+            hi = mid;
+          } else {
+            lo = mid + 1;
+          }
+        }
+        const int li = lo;
+        const int ui = min(N - 1, li + 1);
+        const double tl = tp[li], tu = tp[ui];
+        const double at = (fabs(tu - tl) < DBL_EPSILON) ? 0.5 : (t - tl) / (tu - tl);
+        const double sdl = a.sd[o + li], sdu = a.sd[o + ui];
+        const double sddl = a.sdd[o + li], sddu = a.sdd[o + ui];
+        if (row < dm.r_cap) {
+          a.r_time[row] = t;
+          a.r_s[row] = lerp(at, a.s[o + li], a.s[o + ui]);
+          a.r_sd[row] = lerp(at, sdl, sdu);
+          a.r_sdd[row] = lerp(at, sddl, sddu);
+        }
+        const bool last = (i == M - 1);
+        const double sdl2 = sdl * sdl, sdu2 = sdu * sdu;  // eigenmath::Square
+        for (int d = 0; d < D; ++d) {
+          const double am = a.amax[static_cast<size_t>(b) * D + d];
+          const size_t rl = (o + li) * D + d, ru = (o + ui) * D + d;
+          double pos, vel, acc;
+          if (last) {  // (:780-782)
+            pos = a.q[(o + N - 1) * D + d];
+            vel = 0.0;
+            acc = 0.0;
+          } else {
+            const double d1l = a.dq[rl], d1u = a.dq[ru];
+            const double d2l = a.ddq[rl], d2u = a.ddq[ru];
+            // per-sample velocity / clamped acceleration (:458-472)
+            const double vl = d1l * sdl, vu = d1u * sdu;
+            const double al = clampa(d1l * sddl + d2l * sdl2, am);
+            const double au = clampa(d1u * sddu + d2u * sdu2, am);
+            pos = lerp(at, a.q[rl], a.q[ru]);
+            vel = lerp(at, vl, vu);
+            acc = clampa(lerp(at, al, au), am);
+          }
+          s_tile[lane * D + d] = pos;
+          s_tile[32 * D + lane * D + d] = vel;
+          s_tile[64 * D + lane * D + d] = acc;
+        }
       }
-      a.r_pos[row * D + d] = pos;
-      a.r_vel[row * D + d] = vel;
-      a.r_acc[row * D + d] = acc;
+      __syncwarp();
+      // rows [base, base + cnt) of this path are contiguous in the packed arrays
+      const int64_t wrow = row0 + base;
+      int cnt = min(32, M - base);
+      if (wrow + cnt > dm.r_cap) cnt = (wrow < dm.r_cap) ? static_cast<int>(dm.r_cap - wrow) : 0;
+      const size_t g0 = static_cast<size_t>(wrow) * D;
+      for (int k = lane; k < cnt * D; k += 32) {
+        a.r_pos[g0 + k] = s_tile[k];
+        a.r_vel[g0 + k] = s_tile[32 * D + k];
+        a.r_acc[g0 + k] = s_tile[64 * D + k];
+      }
+      __syncwarp();
     }
   }
 }
@@ -394,10 +523,20 @@ int launch_joint_fit(const Dims& d, const DeviceArrays& a, double rounding, bool
 
 int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safety,
                               cudaStream_t st) {
-  const size_t smem =
+  const size_t tables =
       sizeof(double) * (static_cast<size_t>(d.max_points) + 3 + static_cast<size_t>(d.max_points) * d.D + 2 * d.D);
   dim3 grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
-  k_joint_sample_limit<<<grid, kSampleThreads, smem, st>>>(d, a, safety);
+  const size_t smem = tables + sizeof(double) * 3 * kSampleThreads * d.D;
+  if (d.D <= 8 && smem <= 48 * 1024) {
+#define TPB_SL(K) \
+  case K: k_joint_sample_limit<K><<<grid, kSampleThreads, smem, st>>>(d, a, safety); break
+    switch (d.D) {
+      TPB_SL(1); TPB_SL(2); TPB_SL(3); TPB_SL(4); TPB_SL(5); TPB_SL(6); TPB_SL(7); TPB_SL(8);
+    }
+#undef TPB_SL
+  } else {
+    k_joint_sample_limit_any<<<grid, kSampleThreads, tables, st>>>(d, a, safety);
+  }
   return 1;
 }
 
@@ -430,7 +569,17 @@ int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, doub
   const int threads = 128;
   k_resample_count<<<(d.B + threads - 1) / threads, threads, 0, st>>>(d, a, start_sec, dt);
   k_scan_offsets<<<1, 1024, 0, st>>>(d.B, a.r_count, a.r_offset);
-  k_resample_fill<<<num_sms * 8, kResampleThreads, 0, st>>>(d, a, start_sec, dt);
+  const size_t tile = sizeof(double) * (kResampleThreads / 32) * 3 * 32 * d.D;
+  const size_t with_time = tile + sizeof(double) * d.N;
+  const int grid = std::min(d.B, num_sms * 16);
+  if (with_time <= 160 * 1024) {
+    // > 48 KB of dynamic shared memory is opt-in (per device, so set it every time)
+    cudaFuncSetAttribute(k_resample_fill<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         160 * 1024);
+    k_resample_fill<true><<<grid, kResampleThreads, with_time, st>>>(d, a, start_sec, dt);
+  } else {
+    k_resample_fill<false><<<grid, kResampleThreads, tile, st>>>(d, a, start_sec, dt);
+  }
   return 3;
 }
 
