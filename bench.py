@@ -42,6 +42,17 @@ WORKLOAD = ("cfg2: 4096 synthetic 7-DoF joint-spline paths x 2048 samples per GP
             "time-optimal timing + 4 ms uniform resampling")
 
 
+def _traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the committed `ncu --set full` capture
+    (profiles/traffic.json: dram__bytes_read.sum + dram__bytes_write.sum), or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            return json.load(f).get(kernel, {}).get("dram_bytes_per_launch")
+    except (OSError, ValueError):
+        return None
+
+
 def _peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -137,7 +148,9 @@ def run_reference(args):
         return
     pkg = load_package()
     po, impl, kind, cores = _cpu_setup()
-    sample = max(64, 32 * cores)
+    # bounded sample: the first min(4096, 256 * cores) paths of the cfg2 batch per step
+    # (about 1 s of wall time on all host cores, i.e. ~cores seconds of CPU work)
+    sample = min(PATHS_PER_GPU, 256 * cores)
     wp, vmax, amax = pkg.workloads.joint_paths(PATHS_PER_GPU, NUM_WAYPOINTS, NUM_DOFS, 1000)
     wp, vmax, amax = wp[:sample], vmax[:sample], amax[:sample]
     devnull = os.open(os.devnull, os.O_WRONLY)
@@ -299,7 +312,8 @@ def run_ours(args):
     kernel_names = {"sample_limit": "k_joint_sample_limit", "integrate": "k_integrate",
                     "resample": "k_resample_fill"}
     roofline = {"bound": "hbm", "kernel": kernel_names[dom], "achieved": achieved,
-                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": _traffic(kernel_names[dom]),
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                 "avg_launch_ms": stage_ms[dom],
                 "note": ("k_integrate is a sequential FP64 phase-plane sweep, one warp per "
@@ -355,7 +369,8 @@ def run_ours(args):
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         po, impl, kind, cores = _cpu_setup()
-        sample = max(64, 32 * cores)
+        # bounded sample sized for 10-30 s of CPU work: ~4 ms per path per core
+        sample = min(B, 256 * cores)
         devnull = os.open(os.devnull, os.O_WRONLY)
         saved = os.dup(2)
         os.dup2(devnull, 2)
@@ -366,10 +381,12 @@ def run_ours(args):
         finally:
             os.dup2(saved, 2)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
-                        "sample": f"first {sample} paths of this batch, {dt:.1f} s wall, "
-                                  f"{cores} host threads (stage C = reference .cc verbatim)"
+                        "sample": f"first {sample} paths of this batch, {dt:.1f} s wall = "
+                                  f"{dt * cores:.0f} core-seconds on {cores} host threads "
+                                  f"(stage C = reference .cc verbatim)"
                         if kind == "reference" else
-                        f"first {sample} paths of this batch, {dt:.1f} s wall, oracle port"}
+                        f"first {sample} paths of this batch, {dt:.1f} s wall = "
+                        f"{dt * cores:.0f} core-seconds, oracle port"}
 
     if rank == 0:
         line = {

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define TPB_ABI_VERSION 1
+#define TPB_ABI_VERSION 2
 
 /* absl::StatusCode values used by this library. */
 enum {
@@ -71,10 +71,16 @@ typedef enum {
   TPB_ARR_CTRL = 2,       /* double [B][max_points][D] */
   TPB_ARR_KNOTS = 3,      /* double [B][max_points + 3] */
   TPB_ARR_DELTA = 4,      /* double [B] path sampling distance actually used */
+  /* Cartesian paths: pose control points, rows (tx,ty,tz,qx,qy,qz,qw) */
+  TPB_ARR_POSE_CTRL = 5,  /* double [B][max_points][7] */
   /* SamplePath outputs: GetPathPositionAt / GetFirst.. / GetSecond.. */
   TPB_ARR_Q = 10,   /* double [B][N][D] */
   TPB_ARR_DQ = 11,  /* double [B][N][D] */
   TPB_ARR_DDQ = 12, /* double [B][N][D] */
+  /* Cartesian paths: what SamplePath hands to the path IK (IK indices -1..N-1,
+   * timeable_path_cartesian_spline.cc:464-500) */
+  TPB_ARR_POSE_TARGETS = 13,  /* double [B][N+1][7] */
+  TPB_ARR_JOINT_TARGETS = 14, /* double [B][N+1][D] */
   /* TimeOptimalPathProfile outputs (time_optimal_path_timing.h:152-159) */
   TPB_ARR_TIME = 20, /* double [B][N] */
   TPB_ARR_S = 21,    /* double [B][N] */
@@ -87,6 +93,8 @@ typedef enum {
   TPB_ARR_B_SDD_MIN = 32,  /* double [B][N] */
   TPB_ARR_B_SD2_ZERO = 33, /* double [B][N] */
   TPB_ARR_B_TYPE = 34,     /* uint8  [B][N]  (1 source, 2 sink, 4 trajectory) */
+  /* constraint rows (A, B, lower, upper) of explicit / Cartesian problems */
+  TPB_ARR_CONS = 35,       /* double [B][N][C][4] */
   /* per-path scalars */
   TPB_ARR_STATUS = 40,        /* int32  [B] TPB_PATH_* */
   TPB_ARR_DURATION = 41,      /* double [B] GetTotalDuration (NaN if failed) */
@@ -117,6 +125,8 @@ typedef struct {
   int32_t num_samples;     /* N (num_path_samples) */
   int32_t max_constraints; /* C capacity for tpb_set_constraints; 0 -> 2*D only */
   int64_t max_time_samples_total; /* capacity of the packed resampled output; 0 -> none */
+  int32_t cartesian;       /* != 0: allocate the Cartesian-path buffers (needs num_dofs > 0;
+                              the constraint capacity is raised to 2*D + 2) */
 } tpb_config;
 
 /* ---- life cycle ---------------------------------------------------------- */
@@ -154,6 +164,40 @@ int32_t tpb_set_sampling(tpb_engine* e, const double* delta, int32_t on_device);
  * CalculateBoundary (time_optimal_path_timing.cc:1366-1377).  path_start: [B]
  * or NULL (0). */
 int32_t tpb_sample_paths(tpb_engine* e, const double* path_start, int32_t on_device);
+
+/* ---- Cartesian paths: TimeableCartesianSplinePath -------------------------- */
+/* Built-in device kinematics.  TPB_KIN_FAKE7 is the reference test's fake robot
+ * (path_timing_trajectory_test.cc:548-587): translation = q[0:3], rotation =
+ * ExpSO3(q[3:6]), q[6] copied from the joint target. */
+enum { TPB_KIN_HOST = 0, TPB_KIN_FAKE7 = 1 };
+/* CartesianPathOptions::translation_rounding (default 0.05) and
+ * SetMaxCartesianVelocity (timeable_path_cartesian_spline.h:31-58, .cc:352-366).
+ * The rotation rounding is PathOptions::rounding (tpb_set_path_options). */
+int32_t tpb_set_cart_options(tpb_engine* e, double translation_rounding,
+                             double max_translational_velocity,
+                             double max_rotational_velocity);
+/* SetWaypoints (.cc:166-188) + FitSplineToWaypoints (.cc:396-462).
+ * pose_waypoints: [num_paths][max_waypoints][7] rows (tx,ty,tz,qx,qy,qz,qw);
+ * joint_waypoints: [num_paths][max_waypoints][D]. */
+int32_t tpb_set_cart_waypoints(tpb_engine* e, int32_t num_paths, const int32_t* num_waypoints,
+                               const double* pose_waypoints, const double* joint_waypoints,
+                               int32_t on_device);
+/* The spline half of SamplePath(0) (.cc:464-500): fills TPB_ARR_POSE_TARGETS /
+ * TPB_ARR_JOINT_TARGETS.  Only fresh paths sampled from path_start = 0 (one
+ * planning window) are supported. */
+int32_t tpb_cart_sample_targets(tpb_engine* e);
+/* Path IK with a built-in device kinematics model: path positions
+ * TPB_ARR_Q[b][i] = IK(target i + 1) (.cc:502-513). */
+int32_t tpb_cart_solve_ik(tpb_engine* e, int32_t model);
+/* Path IK done by the caller (a user PathIKFunc on the host): upload
+ * path_ik_positions [B][N][D] (= new_ik_path[1:]). */
+int32_t tpb_cart_set_ik_positions(tpb_engine* e, const double* positions, int32_t on_device);
+/* The rest of SamplePath (ComputePathDerivatives, .cc:39-68) + ConstraintSetup
+ * (.cc:551-595) + the per-sample limit curve.  jacobians: [B][N][6][D] row-major
+ * (rows 0-2 linear, 3-5 angular) from the caller's JacobianFunc, or NULL to use
+ * the built-in `model`. */
+int32_t tpb_cart_setup_constraints(tpb_engine* e, int32_t model, const double* jacobians,
+                                   int32_t on_device);
 
 /* ---- explicit constraints: TimeOptimalPathProfile ------------------------ */
 /* InitSolver + SetupProblem (time_optimal_path_timing.cc:135-203) for

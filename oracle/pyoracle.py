@@ -66,6 +66,14 @@ class _PlanOut(C.Structure):
         ("r_t", "r_pos", "r_vel", "r_acc", "r_s", "r_sd", "r_sdd")]
 
 
+class _CartCfg(C.Structure):
+    _fields_ = [("N", C.c_int), ("W", C.c_int), ("translation_rounding", C.c_double),
+                ("rotation_rounding", C.c_double), ("safety", C.c_double),
+                ("delta", C.c_double), ("start_sec", C.c_double), ("dt", C.c_double),
+                ("max_translational_velocity", C.c_double),
+                ("max_rotational_velocity", C.c_double)]
+
+
 _lib = None
 _ref = None
 
@@ -126,6 +134,35 @@ def lib():
         L.orc_plan_joint.restype = C.c_int
         L.orc_plan_joint.argtypes = [C.POINTER(_PlanCfg), c_double_p, c_double_p,
                                      c_double_p, C.POINTER(_PlanOut)]
+        # Cartesian path (tp_oracle_cart.c)
+        for fn, n in (("orc_quat_mul", 3), ("orc_quat_log", 2), ("orc_quat_exp", 2),
+                      ("orc_exp_so3", 2), ("orc_log_so3", 2), ("orc_log_so3_derivative", 2),
+                      ("orc_fake_jacobian", 2)):
+            getattr(L, fn).argtypes = [c_double_p] * n
+            getattr(L, fn).restype = None
+        L.orc_quat_power.argtypes = [c_double_p, C.c_double, c_double_p]
+        L.orc_quat_eval_curve.restype = C.c_int
+        L.orc_quat_eval_curve.argtypes = [c_double_p, C.c_int, c_double_p, C.c_int,
+                                          C.c_double, c_double_p]
+        L.orc_pose_polyline_to_bspline3.restype = C.c_int
+        L.orc_pose_polyline_to_bspline3.argtypes = [c_double_p, C.c_int, C.c_double,
+                                                    C.c_double, c_double_p]
+        L.orc_cart_fit.restype = C.c_int
+        L.orc_cart_fit.argtypes = [c_double_p, c_double_p, C.c_int, C.c_int, C.c_double,
+                                   C.c_double, c_double_p, c_double_p, c_double_p]
+        L.orc_cart_sample_targets.argtypes = [c_double_p, C.c_int, c_double_p, c_double_p,
+                                              C.c_int, C.c_int, C.c_double, c_double_p,
+                                              c_double_p]
+        L.orc_cart_derivatives.argtypes = [c_double_p, C.c_int, C.c_int, C.c_double,
+                                           c_double_p, c_double_p]
+        L.orc_cart_constraints.argtypes = [c_double_p, c_double_p, c_double_p, C.c_int,
+                                           C.c_int, c_double_p, c_double_p, C.c_double,
+                                           C.c_double, C.c_double, c_double_p]
+        L.orc_fake_ik.argtypes = [c_double_p, c_double_p, C.c_int, c_double_p]
+        L.orc_plan_cart_fake.restype = C.c_int
+        L.orc_plan_cart_fake.argtypes = [C.POINTER(_CartCfg), c_double_p, c_double_p,
+                                         c_double_p, c_double_p, C.POINTER(_PlanOut),
+                                         c_double_p, c_double_p, c_double_p, c_double_p]
         _lib = L
     return _lib
 
@@ -328,6 +365,154 @@ def plan_joint(waypoints, vmax, amax, N, rounding=0.2, safety=0.8, delta=-1.0,
     res.update(status=st, ok=(st == ORC_OK), duration=out.duration,
                delta=out.delta_used, knot_end=out.knot_end, M=M,
                last_extremal_index=out.last_extremal_index)
+    return res
+
+
+# ----------------------------------------------------------------- Cartesian path
+def _q(a):
+    return np.ascontiguousarray(a, np.float64)
+
+
+def quat_mul(a, b):
+    out = np.zeros(4)
+    lib().orc_quat_mul(_dp(_q(a)), _dp(_q(b)), _dp(out))
+    return out
+
+
+def quat_exp(q):
+    out = np.zeros(4)
+    lib().orc_quat_exp(_dp(_q(q)), _dp(out))
+    return out
+
+
+def quat_log(q):
+    out = np.zeros(4)
+    lib().orc_quat_log(_dp(_q(q)), _dp(out))
+    return out
+
+
+def quat_power(q, power):
+    out = np.zeros(4)
+    lib().orc_quat_power(_dp(_q(q)), float(power), _dp(out))
+    return out
+
+
+def quat_eval_curve(knots, quats, degree, u):
+    """BSplineQ::EvalCurve; quats [n][4] in (x, y, z, w) order."""
+    knots, quats = _q(knots), _q(quats)
+    out = np.zeros(4)
+    st = lib().orc_quat_eval_curve(_dp(knots), len(knots), _dp(quats), degree, float(u),
+                                   _dp(out))
+    return st, out
+
+
+def pose_polyline_to_bspline3(corners, translation_radius, rotational_radius):
+    corners = _q(corners)
+    W = corners.shape[0]
+    out = np.zeros((max(3 * W - 2, 4), 7))
+    n = lib().orc_pose_polyline_to_bspline3(_dp(corners), W, float(translation_radius),
+                                            float(rotational_radius), _dp(out))
+    return out[:n]
+
+
+def exp_so3(v):
+    out = np.zeros(4)
+    lib().orc_exp_so3(_dp(_q(v)), _dp(out))
+    return out
+
+
+def log_so3(q):
+    out = np.zeros(3)
+    lib().orc_log_so3(_dp(_q(q)), _dp(out))
+    return out
+
+
+def log_so3_derivative(q):
+    out = np.zeros((3, 4))
+    lib().orc_log_so3_derivative(_dp(_q(q)), _dp(out))
+    return out
+
+
+def fake_jacobian(joints):
+    out = np.zeros((6, 7))
+    lib().orc_fake_jacobian(_dp(_q(joints)), _dp(out))
+    return out
+
+
+def fake_ik(pose_targets, joint_targets):
+    pt, jt = _q(pose_targets), _q(joint_targets)
+    out = np.zeros((pt.shape[0], 7))
+    lib().orc_fake_ik(_dp(pt), _dp(jt), pt.shape[0], _dp(out))
+    return out
+
+
+def cart_fit(pose_wp, joint_wp, translation_rounding=0.05, rotation_rounding=0.2):
+    pose_wp, joint_wp = _q(pose_wp), _q(joint_wp)
+    W, D = joint_wp.shape
+    nmax = max(3 * W - 2, 4)
+    pc, jc, kn = np.zeros((nmax, 7)), np.zeros((nmax, D)), np.zeros(nmax + 3)
+    n = lib().orc_cart_fit(_dp(pose_wp), _dp(joint_wp), W, D, float(translation_rounding),
+                           float(rotation_rounding), _dp(pc), _dp(jc), _dp(kn))
+    return pc[:n], jc[:n], kn[:n + 3]
+
+
+def cart_sample_targets(knots, pose_ctrl, joint_ctrl, N, delta):
+    knots, pose_ctrl, joint_ctrl = _q(knots), _q(pose_ctrl), _q(joint_ctrl)
+    D = joint_ctrl.shape[1]
+    pt, jt = np.zeros((N + 1, 7)), np.zeros((N + 1, D))
+    lib().orc_cart_sample_targets(_dp(knots), len(knots), _dp(pose_ctrl), _dp(joint_ctrl), D,
+                                  N, float(delta), _dp(pt), _dp(jt))
+    return pt, jt
+
+
+def cart_derivatives(pos, delta):
+    pos = _q(pos)
+    N, D = pos.shape
+    d1, d2 = np.zeros((N, D)), np.zeros((N, D))
+    lib().orc_cart_derivatives(_dp(pos), N, D, float(delta), _dp(d1), _dp(d2))
+    return d1, d2
+
+
+def cart_constraints(d1, d2, jac, vmax, amax, safety, max_trans_vel, max_rot_vel):
+    d1, d2, jac, vmax, amax = _q(d1), _q(d2), _q(jac), _q(vmax), _q(amax)
+    N, D = d1.shape
+    cons = np.zeros((N, 2 * D + 2, 4))
+    lib().orc_cart_constraints(_dp(d1), _dp(d2), _dp(jac), N, D, _dp(vmax), _dp(amax),
+                               float(safety), float(max_trans_vel), float(max_rot_vel),
+                               _dp(cons))
+    return cons
+
+
+def plan_cart_fake(pose_wp, joint_wp, vmax, amax, N, translation_rounding=0.05,
+                   rotation_rounding=0.2, safety=0.8, delta=-1.0, start_sec=0.0, dt=0.0,
+                   M_cap=0, max_trans_vel=0.5, max_rot_vel=0.25):
+    """One fresh 7-dof Cartesian path with the reference test's fake kinematics."""
+    pose_wp, joint_wp, vmax, amax = _q(pose_wp), _q(joint_wp), _q(vmax), _q(amax)
+    W, D = joint_wp.shape
+    assert D == 7
+    cfg = _CartCfg(N, W, translation_rounding, rotation_rounding, safety, delta, start_sec,
+                   dt, max_trans_vel, max_rot_vel)
+    o = {k: np.full(N, np.nan) for k in ("time", "s", "sd", "sdd")}
+    o.update({k: np.zeros((N, D)) for k in ("q", "dq", "ddq", "vel", "acc")})
+    r = {"r_t": np.zeros(M_cap), "r_s": np.zeros(M_cap), "r_sd": np.zeros(M_cap),
+         "r_sdd": np.zeros(M_cap), "r_pos": np.zeros((M_cap, D)),
+         "r_vel": np.zeros((M_cap, D)), "r_acc": np.zeros((M_cap, D))}
+    out = _PlanOut(**{k: _dp(v) for k, v in o.items()}, M_cap=M_cap,
+                   **{k: (_dp(v) if M_cap > 0 else None) for k, v in r.items()})
+    nmax = max(3 * W - 2, 4)
+    pose_ctrl, knots = np.zeros((nmax, 7)), np.zeros(nmax + 3)
+    pose_targets, cons = np.zeros((N + 1, 7)), np.zeros((N, 2 * D + 2, 4))
+    st = lib().orc_plan_cart_fake(C.byref(cfg), _dp(pose_wp), _dp(joint_wp), _dp(vmax),
+                                  _dp(amax), C.byref(out), _dp(pose_ctrl), _dp(knots),
+                                  _dp(pose_targets), _dp(cons))
+    res = dict(o)
+    M = out.M
+    res.update({k: v[:M] for k, v in r.items()})
+    n = 4 if W == 1 else 3 * W - 2
+    res.update(status=st, ok=(st == ORC_OK), duration=out.duration, delta=out.delta_used,
+               knot_end=out.knot_end, M=M, last_extremal_index=out.last_extremal_index,
+               pose_ctrl=pose_ctrl[:n], knots=knots[:n + 3], pose_targets=pose_targets,
+               cons=cons)
     return res
 
 

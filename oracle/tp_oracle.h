@@ -135,6 +135,49 @@ typedef struct {
 int orc_plan_joint(const orc_plan_cfg* cfg, const double* waypoints,
                    const double* vmax, const double* amax, orc_plan_out* out);
 
+/* ---- Cartesian timeable path (BASELINE config 5), tp_oracle_cart.c ------- */
+/* quaternions: 4 doubles (x, y, z, w); poses: 7 doubles (tx,ty,tz,qx,qy,qz,qw) */
+void orc_quat_mul(const double* a, const double* b, double* out);
+void orc_quat_log(const double* q, double* out);
+void orc_quat_exp(const double* q, double* out);
+void orc_quat_power(const double* q, double power, double* out);
+int orc_quat_eval_curve(const double* knots, int num_knots, const double* quats,
+                        int degree, double u, double* out);
+int orc_pose_polyline_to_bspline3(const double* corners, int W, double translation_radius,
+                                  double rotational_radius, double* out);
+int orc_cart_fit(const double* pose_wp, const double* joint_wp, int W, int dim,
+                 double translation_rounding, double rotation_rounding, double* pose_ctrl,
+                 double* joint_ctrl, double* knots);
+void orc_cart_sample_targets(const double* knots, int num_knots, const double* pose_ctrl,
+                             const double* joint_ctrl, int dim, int N, double delta,
+                             double* pose_targets /* [N+1][7] */,
+                             double* joint_targets /* [N+1][dim] */);
+void orc_cart_derivatives(const double* pos, int N, int dim, double delta, double* d1,
+                          double* d2);
+void orc_cart_constraints(const double* d1, const double* d2, const double* jac, int N,
+                          int dim, const double* vmax, const double* amax, double safety,
+                          double max_trans_vel, double max_rot_vel,
+                          double* cons /* [N][2dim+2][4] */);
+/* the reference test's fake kinematics (path_timing_trajectory_test.cc:548-587) */
+void orc_exp_so3(const double* v, double* q);
+void orc_log_so3(const double* q, double* v);
+void orc_log_so3_derivative(const double* q, double* out /* [3][4] */);
+void orc_fake_ik(const double* pose_targets, const double* joint_targets, int M, double* ik);
+void orc_fake_jacobian(const double* joints, double* J /* [6][7] */);
+typedef struct {
+  int N, W;
+  double translation_rounding, rotation_rounding, safety;
+  double delta; /* <= 0: knots.back()/(N-1) */
+  double start_sec, dt;
+  double max_translational_velocity, max_rotational_velocity;
+} orc_cart_cfg;
+/* optional outputs (may be NULL): pose_ctrl [3W-2][7], knots [3W+1],
+ * pose_targets [N+1][7], cons [N][16][4] */
+int orc_plan_cart_fake(const orc_cart_cfg* cfg, const double* pose_wp, const double* joint_wp,
+                       const double* vmax, const double* amax, orc_plan_out* out,
+                       double* pose_ctrl_out, double* knots_out, double* pose_targets_out,
+                       double* cons_out);
+
 #ifdef __cplusplus
 }
 #endif

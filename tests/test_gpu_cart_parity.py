@@ -1,0 +1,173 @@
+"""GPU parity: Cartesian timeable paths (BASELINE config 5) through the C ABI vs
+the CPU oracle (oracle/tp_oracle_cart.c).
+
+Two modes, like the reference's API allows:
+ * host callbacks (user PathIKFunc / JacobianFunc): the path-IK positions and the
+   Jacobians are produced on the host (here: by the oracle's restatement of the
+   reference test's fake kinematics) and uploaded; forward differences,
+   constraint rows, limit curve, timing and resampling run on the GPU and must be
+   BIT-IDENTICAL to the oracle given the same positions;
+ * built-in device kinematics (TPB_KIN_FAKE7): everything on the GPU.  The
+   quaternion spline and the kinematics use sin/cos/atan2/log/exp, where CUDA's
+   libm and glibc differ by an ulp, so this mode is compared with the tolerances
+   BASELINE.json states (1e-12 spline values, 1e-6 relative durations, 1e-9 rad
+   resampled positions) -- the forward differences amplify an ulp by 1/delta^2.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+N = 1000
+DT = 0.004
+
+
+def _engine(pkg, B, W, cap=40000):
+    return pkg.Engine(max_paths=B, num_samples=N, num_dofs=7, max_waypoints=W,
+                      max_time_samples_total=B * cap, cartesian=True)
+
+
+def _oracle(po, pw, jw, vm, am, delta=-1.0, **kw):
+    return po.plan_cart_fake(pw, jw, vm, am, N, delta=delta, dt=DT, M_cap=40000, **kw)
+
+
+def test_fit_and_targets_match_oracle(pkg, po):
+    B, W = 12, 5
+    pw, jw, vm, am = pkg.workloads.cart_paths(B, W, seed=5000)
+    eng = _engine(pkg, B, W)
+    eng.set_cart_options(0.05, 0.5, 0.25)
+    eng.set_cart_waypoints(pw, jw)
+    eng.cart_sample_targets()
+    A = pkg.ARR
+    pose_ctrl, knots, npts = eng.get(A.POSE_CTRL), eng.get(A.KNOTS), eng.get(A.NUM_POINTS)
+    ctrl, pt, jt = eng.get(A.CTRL), eng.get(A.POSE_TARGETS), eng.get(A.JOINT_TARGETS)
+    delta = eng.get(A.DELTA)
+    eng.close()
+    for b in range(B):
+        pc, jc, kn = po.cart_fit(pw[b], jw[b], 0.05, 0.2)
+        n = npts[b]
+        assert n == len(pc) == 3 * W - 2
+        assert np.max(np.abs(pose_ctrl[b, :n] - pc)) <= 1e-12
+        assert np.max(np.abs(ctrl[b, :n] - jc)) <= 1e-12
+        assert np.max(np.abs(knots[b, :n + 3] - kn)) <= 1e-12 * kn[-1]
+        d = kn[-1] / (N - 1)
+        assert abs(delta[b] - d) <= 1e-15
+        opt, ojt = po.cart_sample_targets(kn, pc, jc, N, d)
+        assert np.max(np.abs(pt[b] - opt)) <= 1e-12
+        assert np.max(np.abs(jt[b] - ojt)) <= 1e-12
+        # unit quaternions with non-negative real part (bsplineq.cc:99-109)
+        assert np.max(np.abs(np.linalg.norm(pt[b][:, 3:], axis=1) - 1.0)) <= 1e-12
+        assert (pt[b][:, 6] >= 0).all()
+        # IK index -1 and 0 are both parameter 0 (.cc:478-482)
+        assert np.array_equal(pt[b][0], pt[b][1])
+
+
+@pytest.mark.parametrize("explicit_delta", [False, True])
+def test_host_callback_mode_is_bit_identical(pkg, po, explicit_delta):
+    """Positions and Jacobians uploaded (what a user PathIKFunc / JacobianFunc
+    would return): derivatives, rows, limit curve, timing, resampling on the GPU."""
+    B, W = 8, 5
+    pw, jw, vm, am = pkg.workloads.cart_paths(B, W, seed=5100)
+    eng = _engine(pkg, B, W)
+    eng.set_cart_options(0.05, 0.5, 0.25)
+    eng.set_cart_waypoints(pw, jw)
+    if explicit_delta:
+        # CartesianPathOptions' default delta_parameter 0.005: the first planning
+        # window s in [0, 4.995] of a longer path
+        eng.set_sampling(np.full(B, 0.005))
+    eng.set_joint_limits(vm, am)
+    ora = [_oracle(po, pw[b], jw[b], vm[b], am[b], delta=0.005 if explicit_delta else -1.0)
+           for b in range(B)]
+    q = np.stack([o["q"] for o in ora])
+    jac = np.stack([np.stack([po.fake_jacobian(q[b, i]) for i in range(N)]) for b in range(B)])
+    if not explicit_delta:
+        # the engine's automatic delta must be the oracle's, bit for bit, for the
+        # rest to be comparable at that level; it depends on the device-side pose
+        # control polygon (sin/cos), so upload the oracle's value when it differs
+        d_gpu = eng.get(pkg.ARR.DELTA)
+        d_orc = np.array([o["delta"] for o in ora])
+        assert np.max(np.abs(d_gpu - d_orc)) <= 1e-15
+        if not np.array_equal(d_gpu, d_orc):
+            eng.set_sampling(d_orc)
+    eng.cart_set_ik_positions(q)
+    eng.cart_setup_constraints(model=0, jacobians=jac)
+    eng.optimize()
+    total = eng.resample(0.0, DT)
+    A = pkg.ARR
+    res = {k: eng.get(getattr(A, k)) for k in
+           ("DQ", "DDQ", "CONS", "TIME", "S", "SD", "SDD", "STATUS", "DURATION",
+            "LAST_EXTREMAL", "R_OFFSET", "R_POS", "R_VEL", "R_ACC", "R_TIME")}
+    eng.close()
+    assert total == res["R_OFFSET"][-1]
+    for b, o in enumerate(ora):
+        assert np.array_equal(res["DQ"][b], o["dq"])
+        assert np.array_equal(res["DDQ"][b], o["ddq"])
+        assert np.array_equal(res["CONS"][b], o["cons"])
+        assert (res["STATUS"][b] == 0) == o["ok"], (b, res["STATUS"][b], o["status"])
+        if not o["ok"]:
+            continue
+        for k, ok in (("TIME", "time"), ("S", "s"), ("SD", "sd"), ("SDD", "sdd")):
+            assert np.array_equal(res[k][b], o[ok]), (b, k)
+        assert res["DURATION"][b] == o["duration"]
+        assert res["LAST_EXTREMAL"][b] == o["last_extremal_index"]
+        lo, hi = res["R_OFFSET"][b], res["R_OFFSET"][b + 1]
+        assert hi - lo == o["M"]
+        assert np.array_equal(res["R_POS"][lo:hi], o["r_pos"])
+        assert np.array_equal(res["R_VEL"][lo:hi], o["r_vel"])
+        assert np.array_equal(res["R_ACC"][lo:hi], o["r_acc"])
+
+
+def test_builtin_kinematics_pipeline(pkg, po):
+    """Everything on the device with TPB_KIN_FAKE7, BASELINE tolerances."""
+    B, W = 16, 5
+    pw, jw, vm, am = pkg.workloads.cart_paths(B, W, seed=5200)
+    eng = _engine(pkg, B, W)
+    eng.set_cart_options(0.05, 0.5, 0.25)
+    eng.set_cart_waypoints(pw, jw)
+    eng.set_joint_limits(vm, am)
+    eng.cart_sample_targets()
+    eng.cart_solve_ik(1)
+    eng.cart_setup_constraints(1)
+    eng.optimize()
+    eng.resample(0.0, DT)
+    A = pkg.ARR
+    res = {k: eng.get(getattr(A, k)) for k in
+           ("Q", "DQ", "STATUS", "DURATION", "R_OFFSET", "R_POS", "TIME")}
+    eng.close()
+    n_ok = 0
+    for b in range(B):
+        o = _oracle(po, pw[b], jw[b], vm[b], am[b])
+        assert np.max(np.abs(res["Q"][b] - o["q"])) <= 1e-12
+        # forward differences amplify by 1/delta (delta ~ 0.03-0.05 here)
+        assert np.max(np.abs(res["DQ"][b] - o["dq"])) <= 1e-10
+        assert (res["STATUS"][b] == 0) == o["ok"]
+        if not o["ok"]:
+            continue
+        n_ok += 1
+        assert abs(res["DURATION"][b] - o["duration"]) <= 1e-6 * o["duration"]
+        lo, hi = res["R_OFFSET"][b], res["R_OFFSET"][b + 1]
+        assert abs((hi - lo) - o["M"]) <= 1
+        m = min(hi - lo, o["M"]) - 1  # the last row is the end position in both
+        assert np.max(np.abs(res["R_POS"][lo:lo + m] - o["r_pos"][:m])) <= 1e-9
+        # path ends at the last waypoint (fake IK of the last pose)
+        assert np.max(np.abs(res["R_POS"][hi - 1] - jw[b, -1])) <= 1e-9
+    assert n_ok >= B // 2
+
+
+def test_cart_argument_errors(pkg):
+    eng = _engine(pkg, 2, 3, cap=100)
+    with pytest.raises(pkg.TpbError) as ei:
+        eng.set_cart_options(0.0, 0.5, 0.25)   # SetTranslationRounding(0) -> kInvalidArgument
+    assert ei.value.code == 3
+    with pytest.raises(pkg.TpbError) as ei:
+        eng.set_cart_options(0.05, -1.0, 0.25)  # SetMaxCartesianVelocity -> kInvalidArgument
+    assert ei.value.code == 3
+    with pytest.raises(pkg.TpbError) as ei:
+        eng.cart_sample_targets()               # no path set
+    assert ei.value.code == 9
+    eng.close()
+    joint_only = pkg.Engine(max_paths=2, num_samples=N, num_dofs=7, max_waypoints=3)
+    with pytest.raises(pkg.TpbError) as ei:
+        joint_only.set_cart_options(0.05, 0.5, 0.25)
+    assert ei.value.code == 9
+    joint_only.close()

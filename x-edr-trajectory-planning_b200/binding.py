@@ -17,8 +17,9 @@ PATH_OK = 0
 
 
 class ARR:
-    NUM_POINTS, CTRL, KNOTS, DELTA = 1, 2, 3, 4
-    Q, DQ, DDQ = 10, 11, 12
+    NUM_POINTS, CTRL, KNOTS, DELTA, POSE_CTRL = 1, 2, 3, 4, 5
+    Q, DQ, DDQ, POSE_TARGETS, JOINT_TARGETS = 10, 11, 12, 13, 14
+    CONS = 35
     TIME, S, SD, SDD, SD2 = 20, 21, 22, 23, 24
     B_SD2_MAX, B_SDD_MAX, B_SDD_MIN, B_SD2_ZERO, B_TYPE = 30, 31, 32, 33, 34
     STATUS, DURATION, LAST_EXTREMAL, KNOT_END = 40, 41, 42, 43
@@ -35,7 +36,8 @@ class TpbError(RuntimeError):
 class _Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("max_paths", C.c_int32), ("num_dofs", C.c_int32),
                 ("max_waypoints", C.c_int32), ("num_samples", C.c_int32),
-                ("max_constraints", C.c_int32), ("max_time_samples_total", C.c_int64)]
+                ("max_constraints", C.c_int32), ("max_time_samples_total", C.c_int64),
+                ("cartesian", C.c_int32)]
 
 
 class _PlanIO(C.Structure):
@@ -97,6 +99,18 @@ def lib():
         L.tpb_set_sampling.argtypes = [vp, vp, i32]
         L.tpb_sample_paths.restype = i32
         L.tpb_sample_paths.argtypes = [vp, vp, i32]
+        L.tpb_set_cart_options.restype = i32
+        L.tpb_set_cart_options.argtypes = [vp, f64, f64, f64]
+        L.tpb_set_cart_waypoints.restype = i32
+        L.tpb_set_cart_waypoints.argtypes = [vp, i32, vp, vp, vp, i32]
+        L.tpb_cart_sample_targets.restype = i32
+        L.tpb_cart_sample_targets.argtypes = [vp]
+        L.tpb_cart_solve_ik.restype = i32
+        L.tpb_cart_solve_ik.argtypes = [vp, i32]
+        L.tpb_cart_set_ik_positions.restype = i32
+        L.tpb_cart_set_ik_positions.argtypes = [vp, vp, i32]
+        L.tpb_cart_setup_constraints.restype = i32
+        L.tpb_cart_setup_constraints.argtypes = [vp, i32, vp, i32]
         L.tpb_set_constraints.restype = i32
         L.tpb_set_constraints.argtypes = [vp, i32, i32, vp, vp, vp, i32]
         L.tpb_optimize.restype = i32
@@ -144,7 +158,7 @@ class Engine:
     """One engine = one GPU + one stream (tpb_engine)."""
 
     def __init__(self, max_paths, num_samples, num_dofs=0, max_waypoints=0,
-                 max_constraints=0, max_time_samples_total=0, device=0):
+                 max_constraints=0, max_time_samples_total=0, device=0, cartesian=False):
         self._h = C.c_void_p()
         self.max_paths, self.N, self.D = max_paths, num_samples, num_dofs
         self.Wmax = max_waypoints
@@ -152,7 +166,7 @@ class Engine:
         self.B = 0
         self.C = 0
         cfg = _Config(device, max_paths, num_dofs, max_waypoints, num_samples,
-                      max_constraints, max_time_samples_total)
+                      max_constraints, max_time_samples_total, 1 if cartesian else 0)
         rc = lib().tpb_create(C.byref(cfg), C.byref(self._h))
         if rc != 0:
             self._h = C.c_void_p()
@@ -217,6 +231,43 @@ class Engine:
         path_start = _f64(path_start)
         p, dev = _ptr(path_start)
         self._ck(lib().tpb_sample_paths(self._h, p, dev))
+
+    # -- Cartesian paths -----------------------------------------------------
+    def set_cart_options(self, translation_rounding=0.05, max_translational_velocity=0.5,
+                         max_rotational_velocity=0.25):
+        self._ck(lib().tpb_set_cart_options(self._h, translation_rounding,
+                                            max_translational_velocity,
+                                            max_rotational_velocity))
+
+    def set_cart_waypoints(self, pose_waypoints, joint_waypoints, num_waypoints=None):
+        pose_waypoints, joint_waypoints = _f64(pose_waypoints), _f64(joint_waypoints)
+        B = joint_waypoints.shape[0]
+        assert tuple(joint_waypoints.shape[1:]) == (self.Wmax, self.D)
+        assert tuple(pose_waypoints.shape) == (B, self.Wmax, 7)
+        pp, dev = _ptr(pose_waypoints)
+        pj, dev2 = _ptr(joint_waypoints)
+        assert dev == dev2
+        if num_waypoints is not None and not hasattr(num_waypoints, "data_ptr"):
+            num_waypoints = np.ascontiguousarray(num_waypoints, np.int32)
+        nw, _ = _ptr(num_waypoints)
+        self._ck(lib().tpb_set_cart_waypoints(self._h, B, nw, pp, pj, dev))
+        self.B, self.C = B, 2 * self.D + 2
+
+    def cart_sample_targets(self):
+        self._ck(lib().tpb_cart_sample_targets(self._h))
+
+    def cart_solve_ik(self, model=1):
+        self._ck(lib().tpb_cart_solve_ik(self._h, model))
+
+    def cart_set_ik_positions(self, positions):
+        positions = _f64(positions)
+        p, dev = _ptr(positions)
+        self._ck(lib().tpb_cart_set_ik_positions(self._h, p, dev))
+
+    def cart_setup_constraints(self, model=1, jacobians=None):
+        jacobians = _f64(jacobians)
+        p, dev = _ptr(jacobians)
+        self._ck(lib().tpb_cart_setup_constraints(self._h, model, p, dev))
 
     # -- explicit constraints --------------------------------------------------
     def set_constraints(self, cons, s_start, s_end):
@@ -290,6 +341,14 @@ class Engine:
             return out.reshape(B, self.max_points, D)
         if what == ARR.KNOTS:
             return out.reshape(B, self.max_points + 3)
+        if what == ARR.POSE_CTRL:
+            return out.reshape(B, self.max_points, 7)
+        if what == ARR.POSE_TARGETS:
+            return out.reshape(B, N + 1, 7)
+        if what == ARR.JOINT_TARGETS:
+            return out.reshape(B, N + 1, D)
+        if what == ARR.CONS:
+            return out.reshape(B, N, self.C, 4)
         if what in (ARR.R_POS, ARR.R_VEL, ARR.R_ACC):
             return out.reshape(-1, D)
         if ARR.TIME <= what <= ARR.B_TYPE:

@@ -23,6 +23,10 @@ struct tpb_engine {
   int num_sms = 148;
   cudaStream_t stream = nullptr;
   bool own_stream = false;
+  bool cartesian = false;
+  double translation_rounding = 0.05;  // CartesianPathOptions (timeable_path_cartesian_spline.h:50)
+  double max_trans_vel = 0.0, max_rot_vel = 0.0;
+  bool have_targets = false, have_ik = false;
   double safety = 0.8;    // PathOptions::constraint_safety_ (timeable_path.h:80)
   double rounding = 0.2;  // PathOptions::rounding_ (timeable_path.h:82)
   bool auto_delta = true;
@@ -99,6 +103,10 @@ bool lookup(tpb_engine* e, tpb_array what, ArrayRef* r) {
     case TPB_ARR_CTRL: *r = {a.ctrl, B * d.max_points * D * sizeof(double)}; return true;
     case TPB_ARR_KNOTS: *r = {a.knots, B * (d.max_points + 3) * sizeof(double)}; return true;
     case TPB_ARR_DELTA: *r = {a.delta, B * sizeof(double)}; return true;
+    case TPB_ARR_POSE_CTRL: *r = {a.pose_ctrl, B * d.max_points * 7 * sizeof(double)}; return true;
+    case TPB_ARR_POSE_TARGETS: *r = {a.pose_targets, B * (N + 1) * 7 * sizeof(double)}; return true;
+    case TPB_ARR_JOINT_TARGETS: *r = {a.joint_targets, B * (N + 1) * D * sizeof(double)}; return true;
+    case TPB_ARR_CONS: *r = {a.cons, BN * d.C * 4}; return true;
     case TPB_ARR_Q: *r = {a.q, BN * D}; return true;
     case TPB_ARR_DQ: *r = {a.dq, BN * D}; return true;
     case TPB_ARR_DDQ: *r = {a.ddq, BN * D}; return true;
@@ -127,6 +135,10 @@ bool lookup(tpb_engine* e, tpb_array what, ArrayRef* r) {
     case TPB_ARR_R_SDD: *r = {a.r_sdd, packed_rows() * sizeof(double)}; return true;
   }
   return false;
+}
+
+bool is_cart_array(tpb_array w) {
+  return w == TPB_ARR_POSE_CTRL || w == TPB_ARR_POSE_TARGETS || w == TPB_ARR_JOINT_TARGETS;
 }
 
 bool is_joint_array(tpb_array w) {
@@ -161,6 +173,7 @@ int32_t tpb_create(const tpb_config* cfg, tpb_engine** out) {
 
   tpb_engine* e = new tpb_engine();
   e->device = cfg->device;
+  e->cartesian = cfg->cartesian != 0;
   cudaDeviceGetAttribute(&e->num_sms, cudaDevAttrMultiProcessorCount, cfg->device);
   auto& d = e->dims;
   d.Bmax = cfg->max_paths;
@@ -170,6 +183,11 @@ int32_t tpb_create(const tpb_config* cfg, tpb_engine** out) {
   d.max_points = (d.D > 0) ? std::max(3 * d.Wmax - 2, 4) : 0;
   d.N = cfg->num_samples;
   d.Cmax = cfg->max_constraints;
+  if (cfg->cartesian) {
+    if (cfg->num_dofs < 1) return TPB_INVALID_ARGUMENT;
+    if (2 * cfg->num_dofs + 2 > tpb::kMaxRows) return TPB_OUT_OF_RANGE;
+    d.Cmax = std::max(d.Cmax, 2 * cfg->num_dofs + 2);
+  }
   d.r_cap = (d.D > 0) ? cfg->max_time_samples_total : 0;
   const size_t B = d.Bmax, N = d.N, D = d.D;
   auto& a = e->a;
@@ -191,6 +209,12 @@ int32_t tpb_create(const tpb_config* cfg, tpb_engine** out) {
     TPB_ALLOC(q, B * N * D);
     TPB_ALLOC(dq, B * N * D);
     TPB_ALLOC(ddq, B * N * D);
+  }
+  if (e->cartesian) {
+    TPB_ALLOC(pose_wp, B * d.Wmax * 7);
+    TPB_ALLOC(pose_ctrl, B * d.max_points * 7);
+    TPB_ALLOC(pose_targets, B * (N + 1) * 7);
+    TPB_ALLOC(joint_targets, B * (N + 1) * D);
   }
   if (d.Cmax > 0) {
     TPB_ALLOC(cons, B * N * d.Cmax * 4);
@@ -373,9 +397,14 @@ int32_t tpb_set_sampling(tpb_engine* e, const double* delta, int32_t on_device) 
   }
   if (e->have_waypoints && delta == nullptr) {
     // recompute the automatic delta for the current splines
-    e->launches += tpb::launch_joint_fit(d, e->a, e->rounding, true, e->stream);
+    if (e->mode == Mode::kCartesian) {
+      e->launches += tpb::launch_cart_fit(d, e->a, e->rounding, e->translation_rounding, true, e->stream);
+    } else {
+      e->launches += tpb::launch_joint_fit(d, e->a, e->rounding, true, e->stream);
+    }
     TPB_CUDA(e, cudaGetLastError());
   }
+  e->have_targets = e->have_ik = false;
   e->sampled = e->optimized = e->resampled = false;
   return TPB_OK;
 }
@@ -389,6 +418,130 @@ int32_t tpb_sample_paths(tpb_engine* e, const double* path_start, int32_t on_dev
   cudaSetDevice(e->device);
   TPB_CUDA(e, fill_or_copy(e, e->a.path_start, path_start, d.B, on_device));
   e->launches += tpb::launch_joint_sample_limit(d, e->a, e->safety, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->sampled = true;
+  e->optimized = e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_set_cart_options(tpb_engine* e, double translation_rounding,
+                             double max_translational_velocity,
+                             double max_rotational_velocity) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  if (!e->cartesian) return fail(e, TPB_FAILED_PRECONDITION, "engine was created without cartesian");
+  // SetTranslationRounding / SetMaxCartesianVelocity argument checks
+  // (timeable_path_cartesian_spline.cc:352-390)
+  if (translation_rounding <= 0.0)
+    return fail(e, TPB_INVALID_ARGUMENT, "translation_rounding needs to be greater than zero");
+  if (max_translational_velocity <= 0 || max_rotational_velocity <= 0)
+    return fail(e, TPB_INVALID_ARGUMENT, "Velocity limits must be positive");
+  e->translation_rounding = translation_rounding;
+  e->max_trans_vel = max_translational_velocity;
+  e->max_rot_vel = max_rotational_velocity;
+  e->sampled = e->optimized = e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_set_cart_waypoints(tpb_engine* e, int32_t num_paths, const int32_t* num_waypoints,
+                               const double* pose_waypoints, const double* joint_waypoints,
+                               int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (!e->cartesian) return fail(e, TPB_FAILED_PRECONDITION, "engine was created without cartesian");
+  if (num_paths < 1 || num_paths > d.Bmax)
+    return fail(e, TPB_OUT_OF_RANGE, "num_paths exceeds max_paths");
+  if (pose_waypoints == nullptr || joint_waypoints == nullptr)
+    return fail(e, TPB_INVALID_ARGUMENT, "waypoints are null");
+  cudaSetDevice(e->device);
+  if (num_waypoints != nullptr && !on_device) {
+    for (int b = 0; b < num_paths; ++b) {
+      if (num_waypoints[b] < 1 || num_waypoints[b] > d.Wmax)
+        return fail(e, TPB_INVALID_ARGUMENT, "num_waypoints out of [1, max_waypoints]");
+    }
+  }
+  d.B = num_paths;
+  d.C = 2 * d.D + 2;
+  e->mode = Mode::kCartesian;
+  const size_t BW = static_cast<size_t>(d.B) * d.Wmax;
+  TPB_CUDA(e, copy_in(e, e->a.waypoints, joint_waypoints, sizeof(double) * BW * d.D, on_device));
+  TPB_CUDA(e, copy_in(e, e->a.pose_wp, pose_waypoints, sizeof(double) * BW * 7, on_device));
+  if (num_waypoints != nullptr) {
+    TPB_CUDA(e, copy_in(e, e->a.num_wp, num_waypoints, sizeof(int32_t) * d.B, on_device));
+  } else {
+    e->launches += tpb::launch_fill_i32(e->a.num_wp, d.Wmax, d.B, e->stream);
+  }
+  e->launches += tpb::launch_cart_fit(d, e->a, e->rounding, e->translation_rounding,
+                                      e->auto_delta, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->have_waypoints = true;
+  e->have_targets = e->have_ik = false;
+  e->sampled = e->optimized = e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_cart_sample_targets(tpb_engine* e) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  if (e->mode != Mode::kCartesian || !e->have_waypoints)
+    return fail(e, TPB_FAILED_PRECONDITION, "No path set");
+  cudaSetDevice(e->device);
+  TPB_CUDA(e, cudaMemsetAsync(e->a.path_start, 0, sizeof(double) * e->dims.B, e->stream));
+  e->launches += tpb::launch_cart_sample_targets(e->dims, e->a, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->have_targets = true;
+  e->have_ik = false;
+  e->sampled = e->optimized = e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_cart_solve_ik(tpb_engine* e, int32_t model) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  if (e->mode != Mode::kCartesian || !e->have_targets)
+    return fail(e, TPB_FAILED_PRECONDITION, "targets not sampled");
+  cudaSetDevice(e->device);
+  const int n = tpb::launch_cart_ik_builtin(e->dims, e->a, model, e->stream);
+  if (n < 0) return fail(e, TPB_INVALID_ARGUMENT, "unknown kinematics model for this dof count");
+  e->launches += n;
+  TPB_CUDA(e, cudaGetLastError());
+  e->have_ik = true;
+  e->sampled = e->optimized = e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_cart_set_ik_positions(tpb_engine* e, const double* positions, int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  const auto& d = e->dims;
+  if (e->mode != Mode::kCartesian || !e->have_waypoints)
+    return fail(e, TPB_FAILED_PRECONDITION, "No path set");
+  if (positions == nullptr) return fail(e, TPB_INVALID_ARGUMENT, "positions is null");
+  cudaSetDevice(e->device);
+  TPB_CUDA(e, copy_in(e, e->a.q, positions, sizeof(double) * static_cast<size_t>(d.B) * d.N * d.D,
+                      on_device));
+  e->have_ik = true;
+  e->sampled = e->optimized = e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_cart_setup_constraints(tpb_engine* e, int32_t model, const double* jacobians,
+                                   int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  const auto& d = e->dims;
+  if (e->mode != Mode::kCartesian || !e->have_ik)
+    return fail(e, TPB_FAILED_PRECONDITION, "path IK positions not set");
+  if (!e->have_limits) return fail(e, TPB_FAILED_PRECONDITION, "joint limits not set");
+  if (!(e->max_trans_vel > 0) || !(e->max_rot_vel > 0))
+    return fail(e, TPB_FAILED_PRECONDITION, "Cartesian velocity limits not set");
+  cudaSetDevice(e->device);
+  if (jacobians != nullptr) {
+    if (e->a.jac == nullptr)
+      TPB_CUDA(e, dev_alloc(e, &e->a.jac, static_cast<size_t>(d.Bmax) * d.N * 6 * d.D));
+    TPB_CUDA(e, copy_in(e, e->a.jac, jacobians,
+                        sizeof(double) * static_cast<size_t>(d.B) * d.N * 6 * d.D, on_device));
+  }
+  const int n = tpb::launch_cart_constraints(d, e->a, e->safety, e->max_trans_vel, e->max_rot_vel,
+                                             model, jacobians != nullptr, e->stream);
+  if (n < 0) return fail(e, TPB_INVALID_ARGUMENT, "unknown kinematics model for this dof count");
+  e->launches += n;
+  e->launches += tpb::launch_generic_limit(d, e->a, e->stream);
   TPB_CUDA(e, cudaGetLastError());
   e->sampled = true;
   e->optimized = e->resampled = false;
@@ -441,7 +594,7 @@ int32_t tpb_resample(tpb_engine* e, double start_sec, double time_step_sec,
                      int64_t* total_samples) {
   if (e == nullptr) return TPB_INVALID_ARGUMENT;
   auto& d = e->dims;
-  if (e->mode != Mode::kJoint || !e->optimized)
+  if ((e->mode != Mode::kJoint && e->mode != Mode::kCartesian) || !e->optimized)
     return fail(e, TPB_FAILED_PRECONDITION, "no timed joint paths");
   if (d.r_cap <= 0) return fail(e, TPB_FAILED_PRECONDITION, "max_time_samples_total is 0");
   if (!(time_step_sec > 0)) return fail(e, TPB_INVALID_ARGUMENT, "time step must be positive");
@@ -516,8 +669,10 @@ int32_t tpb_get(tpb_engine* e, tpb_array what, void* dst, size_t bytes, int32_t 
   if (e == nullptr || dst == nullptr) return TPB_INVALID_ARGUMENT;
   cudaSetDevice(e->device);
   if (e->dims.B == 0) return fail(e, TPB_FAILED_PRECONDITION, "no batch set");
-  if (is_joint_array(what) && e->mode != Mode::kJoint)
+  if (is_joint_array(what) && e->mode != Mode::kJoint && e->mode != Mode::kCartesian)
     return fail(e, TPB_FAILED_PRECONDITION, "array only exists for joint paths");
+  if (is_cart_array(what) && e->mode != Mode::kCartesian)
+    return fail(e, TPB_FAILED_PRECONDITION, "array only exists for Cartesian paths");
   ArrayRef r;
   if (!lookup(e, what, &r) || r.ptr == nullptr) return fail(e, TPB_NOT_FOUND, "unknown array");
   if (bytes < r.bytes) return fail(e, TPB_OUT_OF_RANGE, "destination too small");

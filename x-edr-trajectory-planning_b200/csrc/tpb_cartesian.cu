@@ -1,0 +1,568 @@
+// Cartesian timeable path (BASELINE config 5) for sm_100a, compiled with
+// -fmad=false like the rest of the path-timing kernels.
+//
+//  k_cart_fit             one thread per path: pose + joint waypoints -> control
+//                         polygons and knots (spline_utils.cc:47-203,
+//                         timeable_path_cartesian_spline.cc:396-462)
+//  k_cart_sample_targets  one thread per (path, IK index): joint / translation /
+//                         quaternion spline EvalCurve (bspline.h:514-536,
+//                         bsplineq.cc:113-146, 223-244, 309-317) -> the pose and
+//                         joint targets SamplePath hands to the path IK
+//                         (timeable_path_cartesian_spline.cc:464-500)
+//  k_cart_ik_builtin      built-in device kinematics: the IK of the reference
+//                         test's fake robot (path_timing_trajectory_test.cc:548-570)
+//  k_cart_constraints     one thread per (path, sample): forward-difference path
+//                         derivatives (:39-68) and the 2D+2 constraint rows of
+//                         ConstraintSetup (:551-595), Jacobian either uploaded by
+//                         the host (user JacobianFunc) or of the built-in model
+//
+// A user-supplied PathIKFunc / JacobianFunc is host code with sequential
+// warm-start semantics: the host layer downloads the targets, runs the user's
+// callbacks and uploads joint positions / Jacobians (tpb_cart_set_ik_positions,
+// tpb_cart_setup_constraints); everything else stays on the device.
+#include "tpb_engine.h"
+#include "tpb_fit.cuh"
+
+namespace tpb {
+namespace {
+
+constexpr double kDummyPrecision = 1e-12;  // Eigen::NumTraits<double>::dummy_precision()
+
+struct Quat {
+  double x, y, z, w;
+};
+
+__device__ __forceinline__ double sq_norm(const Quat& q) {
+  return q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w;
+}
+// Eigen stableNorm() of the vector part: scale * sqrt(sum((v/scale)^2))
+__device__ __forceinline__ double stable_norm3(const Quat& q) {
+  double scale = fabs(q.x);
+  if (fabs(q.y) > scale) scale = fabs(q.y);
+  if (fabs(q.z) > scale) scale = fabs(q.z);
+  if (!(scale > 0)) return 0.0;
+  const double inv = 1.0 / scale;
+  const double a = q.x * inv, b = q.y * inv, c = q.z * inv;
+  return scale * sqrt(a * a + b * b + c * c);
+}
+// Eigen stableNormalized() of the vector part
+__device__ __forceinline__ void stable_normalized3(const Quat& q, double* out) {
+  double w = fabs(q.x);
+  if (fabs(q.y) > w) w = fabs(q.y);
+  if (fabs(q.z) > w) w = fabs(q.z);
+  double z = 0.0;
+  if (w > 0) {
+    const double a = q.x / w, b = q.y / w, c = q.z / w;
+    z = a * a + b * b + c * c;
+  }
+  if (z > 0) {
+    const double d = sqrt(z) * w;
+    out[0] = q.x / d;
+    out[1] = q.y / d;
+    out[2] = q.z / d;
+  } else {
+    out[0] = q.x;
+    out[1] = q.y;
+    out[2] = q.z;
+  }
+}
+// Eigen quat_product, scalar formula
+__device__ __forceinline__ Quat qmul(const Quat& a, const Quat& b) {
+  Quat r;
+  r.x = a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y;
+  r.y = a.w * b.y + a.y * b.w + a.z * b.x - a.x * b.z;
+  r.z = a.w * b.z + a.z * b.w + a.x * b.y - a.y * b.x;
+  r.w = a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z;
+  return r;
+}
+// QuaternionBase::inverse(): conjugate / squaredNorm
+__device__ __forceinline__ Quat qinv(const Quat& q) {
+  const double n2 = sq_norm(q);
+  Quat r;
+  if (n2 > 0) {
+    r.x = -q.x / n2;
+    r.y = -q.y / n2;
+    r.z = -q.z / n2;
+    r.w = q.w / n2;
+  } else {
+    r.x = r.y = r.z = r.w = 0.0;
+  }
+  return r;
+}
+// QuaternionBase::_transformVector
+__device__ __forceinline__ void qrot(const Quat& q, const double* v, double* out) {
+  double ux = q.y * v[2] - q.z * v[1];
+  double uy = q.z * v[0] - q.x * v[2];
+  double uz = q.x * v[1] - q.y * v[0];
+  ux += ux;
+  uy += uy;
+  uz += uz;
+  const double cx = q.y * uz - q.z * uy;
+  const double cy = q.z * ux - q.x * uz;
+  const double cz = q.x * uy - q.y * ux;
+  out[0] = v[0] + q.w * ux + cx;
+  out[1] = v[1] + q.w * uy + cy;
+  out[2] = v[2] + q.w * uz + cz;
+}
+// NormalizeIfNecessaryAndEnsurePositiveReal, splines/bsplineq.cc:99-109
+__device__ __forceinline__ void normalize_positive_real(Quat& q) {
+  if (q.w < 0) {
+    q.x *= -1.0;
+    q.y *= -1.0;
+    q.z *= -1.0;
+    q.w *= -1.0;
+  }
+  if (fabs(sq_norm(q) - 1.0) > kDummyPrecision) {
+    const double n = sqrt(sq_norm(q));
+    q.x /= n;
+    q.y /= n;
+    q.z /= n;
+    q.w /= n;
+  }
+}
+// QuatLog, splines/bsplineq.cc:113-126
+__device__ __forceinline__ Quat qlog(const Quat& q) {
+  const double squared_norm_q = sq_norm(q);
+  const double norm_v = stable_norm3(q);
+  Quat r;
+  r.w = 0.5 * log(squared_norm_q);
+  if (norm_v > kDummyPrecision) {
+    double n[3];
+    stable_normalized3(q, n);
+    const double ang = atan2(norm_v, q.w);
+    r.x = n[0] * ang;
+    r.y = n[1] * ang;
+    r.z = n[2] * ang;
+  } else {
+    r.x = q.x;
+    r.y = q.y;
+    r.z = q.z;
+  }
+  return r;
+}
+// QuatExp, splines/bsplineq.cc:128-135
+__device__ __forceinline__ Quat qexp(const Quat& q) {
+  const double norm_v = stable_norm3(q);
+  double n[3];
+  stable_normalized3(q, n);
+  const double s = sin(norm_v);
+  const double e = exp(q.w);
+  Quat r;
+  r.w = cos(norm_v);
+  r.x = n[0] * s;
+  r.y = n[1] * s;
+  r.z = n[2] * s;
+  r.x *= e;
+  r.y *= e;
+  r.z *= e;
+  r.w *= e;
+  return r;
+}
+// QuatPower, splines/bsplineq.cc:137-146
+__device__ __forceinline__ Quat qpow(Quat q, double power) {
+  normalize_positive_real(q);
+  Quat l = qlog(q);
+  l.x *= power;
+  l.y *= power;
+  l.z *= power;
+  l.w *= power;
+  return qexp(l);
+}
+
+__device__ __forceinline__ Quat load_quat(const double* p) { return Quat{p[0], p[1], p[2], p[3]}; }
+__device__ __forceinline__ void store_quat(double* p, const Quat& q) {
+  p[0] = q.x;
+  p[1] = q.y;
+  p[2] = q.z;
+  p[3] = q.w;
+}
+
+// poses: 7 doubles (tx, ty, tz, qx, qy, qz, qw); a * b = (qa*qb, ta + qa*tb)
+__device__ inline void pose_mul(const double* a, const double* b, double* out) {
+  const Quat qa = load_quat(a + 3);
+  double r[3];
+  qrot(qa, b, r);
+  const Quat q = qmul(qa, load_quat(b + 3));
+  out[0] = a[0] + r[0];
+  out[1] = a[1] + r[1];
+  out[2] = a[2] + r[2];
+  store_quat(out + 3, q);
+}
+__device__ inline void pose_inverse(const double* a, double* out) {
+  const Quat qc{-a[3], -a[4], -a[5], a[6]};
+  double r[3];
+  qrot(qc, a, r);
+  out[0] = -r[0];
+  out[1] = -r[1];
+  out[2] = -r[2];
+  store_quat(out + 3, qc);
+}
+
+// CornerOffset (Pose3d), splines/spline_utils.cc:105-146, with Eigen's
+// AngleAxis <-> Quaternion conversions.
+__device__ inline void pose_corner_offset(const double* delta, double translation_radius,
+                                          double rotation_radius, double* offset) {
+  constexpr double kMinRadius = 1e-6;
+  constexpr double kMinWaypointSpacingFactor = 4.0;
+  offset[0] = offset[1] = offset[2] = 0.0;
+  offset[3] = offset[4] = offset[5] = 0.0;
+  offset[6] = 1.0;
+  if (translation_radius < kMinRadius || rotation_radius < kMinRadius) return;
+  const double translation_norm =
+      sqrt(delta[0] * delta[0] + delta[1] * delta[1] + delta[2] * delta[2]);
+  const Quat q = load_quat(delta + 3);
+  double n = sqrt(q.x * q.x + q.y * q.y + q.z * q.z);
+  if (n < DBL_EPSILON) n = stable_norm3(q);
+  double angle, ax, ay, az;
+  if (n != 0.0) {
+    angle = 2.0 * atan2(n, fabs(q.w));
+    if (q.w < 0.0) n = -n;
+    ax = q.x / n;
+    ay = q.y / n;
+    az = q.z / n;
+  } else {
+    angle = 0.0;
+    ax = 1.0;
+    ay = 0.0;
+    az = 0.0;
+  }
+  const double inf = __longlong_as_double(0x7ff0000000000000LL);
+  const double pct_trans = (translation_norm == 0.0) ? inf : translation_radius / translation_norm;
+  const double pct_rot = (angle == 0.0) ? inf : rotation_radius / angle;
+  double pct = (pct_rot < pct_trans) ? pct_rot : pct_trans;
+  if (pct > (1.0 / kMinWaypointSpacingFactor)) pct = 1.0 / kMinWaypointSpacingFactor;
+  offset[0] = delta[0] * pct;
+  offset[1] = delta[1] * pct;
+  offset[2] = delta[2] * pct;
+  angle *= pct;
+  const double ha = 0.5 * angle;
+  const double s = sin(ha);
+  offset[6] = cos(ha);
+  offset[3] = s * ax;
+  offset[4] = s * ay;
+  offset[5] = s * az;
+}
+
+// PolyLineToBspline3Waypoints (Pose3d), splines/spline_utils.cc:148-203
+__device__ inline int pose_polyline_to_bspline3(const double* corners, int W, double tr,
+                                                double rr, double* out) {
+  if (W == 1) {
+    for (int i = 0; i < 4; ++i)
+      for (int k = 0; k < 7; ++k) out[7 * i + k] = corners[k];
+    return 4;
+  }
+  const int n = 3 * W - 2;
+  double inv[7], rel[7], off[7];
+  for (int i = 0; i < W; ++i)
+    for (int k = 0; k < 7; ++k) out[7 * 3 * i + k] = corners[7 * i + k];
+  for (int idx = 1; idx < W - 1; ++idx) {
+    const int k = 3 * idx, knext = 3 * (idx + 1), klast = 3 * (idx - 1);
+    pose_inverse(out + 7 * k, inv);
+    pose_mul(inv, out + 7 * knext, rel);
+    pose_corner_offset(rel, tr, rr, off);
+    pose_mul(out + 7 * k, off, out + 7 * (k + 1));
+    pose_mul(inv, out + 7 * klast, rel);
+    pose_corner_offset(rel, tr, rr, off);
+    pose_mul(out + 7 * k, off, out + 7 * (k - 1));
+  }
+  pose_inverse(out, inv);
+  pose_mul(inv, out + 7 * 3, rel);
+  pose_corner_offset(rel, tr, rr, off);
+  pose_mul(out, off, out + 7);
+  pose_inverse(out + 7 * (n - 1), inv);
+  pose_mul(inv, out + 7 * (n - 4), rel);
+  pose_corner_offset(rel, tr, rr, off);
+  pose_mul(out + 7 * (n - 1), off, out + 7 * (n - 2));
+  return n;
+}
+
+__global__ void k_cart_fit(Dims dm, DeviceArrays a, double rotation_rounding,
+                           double translation_rounding, bool auto_delta) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= dm.B) return;
+  const int D = dm.D;
+  const int W = a.num_wp[b];
+  const double* jwp = a.waypoints + static_cast<size_t>(b) * dm.Wmax * D;
+  const double* pwp = a.pose_wp + static_cast<size_t>(b) * dm.Wmax * 7;
+  double* jc = a.ctrl + static_cast<size_t>(b) * dm.max_points * D;
+  double* pc = a.pose_ctrl + static_cast<size_t>(b) * dm.max_points * 7;
+  double* kn = a.knots + static_cast<size_t>(b) * (dm.max_points + 3);
+  // FitSplineToWaypoints, timeable_path_cartesian_spline.cc:396-462
+  const int n = polyline_to_bspline3(jwp, W, D, rotation_rounding, jc);
+  pose_polyline_to_bspline3(pwp, W, translation_rounding, rotation_rounding, pc);
+  const int nk = uniform_knots_degree2(n, kn);
+  double len_t = 0.0;
+  for (int i = 0; i < n - 1; ++i) {
+    const double* p0 = pc + 7 * i;
+    const double* p1 = pc + 7 * (i + 1);
+    const double dx = p0[0] - p1[0], dy = p0[1] - p1[1], dz = p0[2] - p1[2];
+    len_t += sqrt(dx * dx + dy * dy + dz * dz);
+  }
+  // sic: translation + translation (:432-434); rotation is not counted
+  constexpr double kMinimumFinalKnotValue = 0.1;
+  constexpr double kPathParameterPerPolygonLength = 10.0;
+  double weighted = len_t + len_t;
+  if (weighted < kMinimumFinalKnotValue) weighted = kMinimumFinalKnotValue;
+  const double scale = weighted * kPathParameterPerPolygonLength;
+  for (int i = 0; i < nk; ++i) kn[i] *= scale;
+  a.num_points[b] = n;
+  const double kend = kn[nk - 1];
+  a.knot_end[b] = kend;
+  a.delta[b] = auto_delta ? kend / (dm.N - 1) : a.delta_in[b];
+}
+
+constexpr int kCartThreads = 128;
+
+// IK index i = m - 1 for m in [0, N]: parameter 0 is evaluated twice (:478-482)
+__global__ void __launch_bounds__(kCartThreads)
+k_cart_sample_targets(Dims dm, DeviceArrays a) {
+  extern __shared__ double smem[];
+  const int b = blockIdx.y;
+  const int D = dm.D;
+  const int n = a.num_points[b];
+  const int nk = n + 3;
+  double* s_knots = smem;                        // [max_points + 3]
+  double* s_jc = s_knots + dm.max_points + 3;    // [max_points][D]
+  double* s_pc = s_jc + dm.max_points * D;       // [max_points][7]
+  {
+    const double* gk = a.knots + static_cast<size_t>(b) * (dm.max_points + 3);
+    const double* gj = a.ctrl + static_cast<size_t>(b) * dm.max_points * D;
+    const double* gp = a.pose_ctrl + static_cast<size_t>(b) * dm.max_points * 7;
+    for (int i = threadIdx.x; i < nk; i += blockDim.x) s_knots[i] = gk[i];
+    for (int i = threadIdx.x; i < n * D; i += blockDim.x) s_jc[i] = gj[i];
+    for (int i = threadIdx.x; i < n * 7; i += blockDim.x) s_pc[i] = gp[i];
+  }
+  __syncthreads();
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m > dm.N) return;
+  const int i = m - 1;
+  const double delta = a.delta[b];
+  const double parameter = (i < 0) ? 0.0 : i * delta;
+  const double kend = s_knots[nk - 1];
+  double* pt = a.pose_targets + (static_cast<size_t>(b) * (dm.N + 1) + m) * 7;
+  double* jt = a.joint_targets + (static_cast<size_t>(b) * (dm.N + 1) + m) * D;
+  if (parameter < kend - delta) {
+    // EvalCurve range check (bspline.h:519-522) cannot fail: 0 <= parameter < kend
+    const int span = knot_span(s_knots, nk, 2, parameter);
+    double basis[3];
+    basis_funs<2>(s_knots, span, parameter, basis);
+    for (int d = 0; d < D; ++d) {
+      double v = 0.0;
+#pragma unroll
+      for (int k = 0; k <= 2; ++k) v += basis[k] * s_jc[(span - 2 + k) * D + d];
+      jt[d] = v;
+    }
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      double v = 0.0;
+#pragma unroll
+      for (int k = 0; k <= 2; ++k) v += basis[k] * s_pc[(span - 2 + k) * 7 + d];
+      pt[d] = v;
+    }
+    // BSplineQ::EvalCurve (bsplineq.cc:223-244), cumulative basis (:309-317)
+    double cum[2];
+    cum[1] = basis[2];
+    cum[0] = cum[1] + basis[1];
+    Quat q = load_quat(s_pc + (span - 2) * 7 + 3);
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const Quat p0 = load_quat(s_pc + (span - 2 + k) * 7 + 3);
+      const Quat p1 = load_quat(s_pc + (span - 2 + k + 1) * 7 + 3);
+      q = qmul(q, qpow(qmul(qinv(p0), p1), cum[k]));
+    }
+    normalize_positive_real(q);
+    store_quat(pt + 3, q);
+  } else {
+    for (int k = 0; k < 7; ++k) pt[k] = s_pc[(n - 1) * 7 + k];
+    for (int d = 0; d < D; ++d) jt[d] = s_jc[(n - 1) * D + d];
+  }
+}
+
+// ---- built-in kinematics model TPB_KIN_FAKE7 (path_timing_trajectory_test.cc:548-587)
+__device__ __forceinline__ Quat exp_so3(const double* v) {
+  const double th2 = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
+  const double th = sqrt(th2);
+  double k;
+  if (th < 1e-8) {
+    k = 0.5 - th2 / 48.0;
+  } else {
+    k = sin(0.5 * th) / th;
+  }
+  return Quat{k * v[0], k * v[1], k * v[2], cos(0.5 * th)};
+}
+__device__ __forceinline__ void log_so3(const Quat& q, double* v) {
+  const double n = sqrt(q.x * q.x + q.y * q.y + q.z * q.z);
+  double k;
+  if (n < 1e-10) {
+    k = 2.0 / q.w;
+  } else {
+    k = 2.0 * atan2(n, q.w) / n;
+  }
+  v[0] = k * q.x;
+  v[1] = k * q.y;
+  v[2] = k * q.z;
+}
+// d LogSO3(q) / d (qx, qy, qz, qw), 3x4 row-major
+__device__ __forceinline__ void log_so3_derivative(const Quat& q, double* out) {
+  const double qv[3] = {q.x, q.y, q.z};
+  const double n2 = q.x * q.x + q.y * q.y + q.z * q.z;
+  const double n = sqrt(n2);
+  const double w = q.w;
+  const double den = n2 + w * w;
+  double k, c;
+  if (n < 1e-6) {
+    k = 2.0 / w;
+    c = (-4.0 / 3.0) / (w * w * w);
+  } else {
+    k = 2.0 * atan2(n, w) / n;
+    c = (2.0 * w / den - k) / n2;
+  }
+  for (int r = 0; r < 3; ++r) {
+    for (int col = 0; col < 3; ++col)
+      out[r * 4 + col] = ((r == col) ? k : 0.0) + c * qv[r] * qv[col];
+    out[r * 4 + 3] = -2.0 * qv[r] / den;
+  }
+}
+
+// FakePathIK: path position i = IK of target i + 1 (new_ik_path[1:], :512-513)
+__global__ void k_cart_ik_fake7(Dims dm, DeviceArrays a) {
+  const int b = blockIdx.y;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= dm.N) return;
+  const double* pt = a.pose_targets + (static_cast<size_t>(b) * (dm.N + 1) + i + 1) * 7;
+  const double* jt = a.joint_targets + (static_cast<size_t>(b) * (dm.N + 1) + i + 1) * 7;
+  double* o = a.q + (static_cast<size_t>(b) * dm.N + i) * 7;
+  o[0] = pt[0];
+  o[1] = pt[1];
+  o[2] = pt[2];
+  log_so3(load_quat(pt + 3), o + 3);
+  o[6] = jt[6];
+}
+
+// ComputePathDerivatives (:39-68) + ConstraintSetup (:551-595)
+template <bool kFake7>
+__global__ void __launch_bounds__(kCartThreads)
+k_cart_constraints(Dims dm, DeviceArrays a, double safety, double max_trans_vel,
+                   double max_rot_vel) {
+  const int b = blockIdx.y;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int N = dm.N, D = dm.D, C = dm.C;
+  if (idx >= N) return;
+  const size_t row = (static_cast<size_t>(b) * N + idx) * D;
+  const double delta = a.delta[b];
+  const double inv = 1.0 / delta;
+  double d1[kMaxDofs], d2[kMaxDofs], p0[kMaxDofs];
+  for (int d = 0; d < D; ++d) {
+    p0[d] = a.q[row + d];
+    double f1 = 0.0, f2 = 0.0;
+    if (idx < N - 1) {
+      const double p1 = a.q[row + D + d];
+      f1 = inv * (p1 - p0[d]);
+      if (idx >= 1) {
+        // first derivative of the next sample (0 at the last one)
+        double g1 = 0.0;
+        if (idx + 1 < N - 1) g1 = inv * (a.q[row + 2 * D + d] - p1);
+        f2 = inv * (g1 - f1);
+      }
+    }
+    d1[d] = f1;
+    d2[d] = f2;
+    a.dq[row + d] = f1;
+    a.ddq[row + d] = f2;
+  }
+  double* c = a.cons + (static_cast<size_t>(b) * N + idx) * C * 4;
+  for (int d = 0; d < D; ++d) {
+    const double am = a.amax[static_cast<size_t>(b) * D + d];
+    const double vm = a.vmax[static_cast<size_t>(b) * D + d];
+    c[d * 4 + 0] = d1[d];
+    c[d * 4 + 1] = d2[d];
+    c[d * 4 + 2] = -am * safety;
+    c[d * 4 + 3] = am * safety;
+    const double vs = vm * safety;
+    c[(D + d) * 4 + 0] = 0.0;
+    c[(D + d) * 4 + 1] = d1[d] * d1[d];
+    c[(D + d) * 4 + 2] = 0.0;
+    c[(D + d) * 4 + 3] = vs * vs;
+  }
+  double v[6];
+  if (kFake7) {
+    // FakeJacobian: rows 0-2 = identity on q[0:3]; rows 3-5, columns 3-6 =
+    // d LogSO3 / d quaternion coefficients at ExpSO3(q[3:6])
+    double dl[12];
+    log_so3_derivative(exp_so3(p0 + 3), dl);
+    for (int r = 0; r < 3; ++r) {
+      // full row sums like the dense product jacobian * q' (zeros included)
+      double s = 0.0;
+      for (int d = 0; d < 7; ++d) s += ((d == r) ? 1.0 : 0.0) * d1[d];
+      v[r] = s;
+      double t = 0.0;
+      for (int d = 0; d < 7; ++d) t += ((d >= 3) ? dl[r * 4 + d - 3] : 0.0) * d1[d];
+      v[3 + r] = t;
+    }
+  } else {
+    const double* J = a.jac + (static_cast<size_t>(b) * N + idx) * 6 * D;
+    for (int r = 0; r < 6; ++r) {
+      double s = 0.0;
+      for (int d = 0; d < D; ++d) s += J[r * D + d] * d1[d];
+      v[r] = s;
+    }
+  }
+  const double vt2 = max_trans_vel * max_trans_vel;
+  const double vr2 = max_rot_vel * max_rot_vel;
+  c[(2 * D) * 4 + 0] = 0.0;
+  c[(2 * D) * 4 + 1] = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
+  c[(2 * D) * 4 + 2] = -vt2;
+  c[(2 * D) * 4 + 3] = vt2;
+  c[(2 * D + 1) * 4 + 0] = 0.0;
+  c[(2 * D + 1) * 4 + 1] = v[3] * v[3] + v[4] * v[4] + v[5] * v[5];
+  c[(2 * D + 1) * 4 + 2] = -vr2;
+  c[(2 * D + 1) * 4 + 3] = vr2;
+  if (idx == 0) {
+    // SetupProblem: s in [path_start, path_start + delta (N-1)], path_start = 0
+    a.s_start[b] = 0.0;
+    a.s_end[b] = 0.0 + delta * (N - 1);
+  }
+}
+
+}  // namespace
+
+int launch_cart_fit(const Dims& d, const DeviceArrays& a, double rotation_rounding,
+                    double translation_rounding, bool auto_delta, cudaStream_t st) {
+  const int threads = 64;
+  k_cart_fit<<<(d.B + threads - 1) / threads, threads, 0, st>>>(d, a, rotation_rounding,
+                                                                translation_rounding, auto_delta);
+  return 1;
+}
+
+int launch_cart_sample_targets(const Dims& d, const DeviceArrays& a, cudaStream_t st) {
+  const size_t smem = sizeof(double) * (static_cast<size_t>(d.max_points) + 3 +
+                                        static_cast<size_t>(d.max_points) * (d.D + 7));
+  dim3 grid((d.N + 1 + kCartThreads - 1) / kCartThreads, d.B);
+  if (smem > 48 * 1024)
+    cudaFuncSetAttribute(k_cart_sample_targets, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         static_cast<int>(smem));
+  k_cart_sample_targets<<<grid, kCartThreads, smem, st>>>(d, a);
+  return 1;
+}
+
+int launch_cart_ik_builtin(const Dims& d, const DeviceArrays& a, int model, cudaStream_t st) {
+  if (model != TPB_KIN_FAKE7 || d.D != 7) return -1;
+  dim3 grid((d.N + kCartThreads - 1) / kCartThreads, d.B);
+  k_cart_ik_fake7<<<grid, kCartThreads, 0, st>>>(d, a);
+  return 1;
+}
+
+int launch_cart_constraints(const Dims& d, const DeviceArrays& a, double safety,
+                            double max_trans_vel, double max_rot_vel, int model, bool have_jac,
+                            cudaStream_t st) {
+  dim3 grid((d.N + kCartThreads - 1) / kCartThreads, d.B);
+  if (have_jac) {
+    k_cart_constraints<false><<<grid, kCartThreads, 0, st>>>(d, a, safety, max_trans_vel, max_rot_vel);
+  } else {
+    if (model != TPB_KIN_FAKE7 || d.D != 7) return -1;
+    k_cart_constraints<true><<<grid, kCartThreads, 0, st>>>(d, a, safety, max_trans_vel, max_rot_vel);
+  }
+  return 1;
+}
+
+}  // namespace tpb

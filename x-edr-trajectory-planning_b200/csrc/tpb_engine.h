@@ -46,6 +46,13 @@ struct DeviceArrays {
   double* q = nullptr;
   double* dq = nullptr;
   double* ddq = nullptr;
+  // Cartesian paths: pose waypoints / control points (tx,ty,tz,qx,qy,qz,qw), the
+  // targets SamplePath hands to the path IK, uploaded Jacobians
+  double* pose_wp = nullptr;        // [B][Wmax][7]
+  double* pose_ctrl = nullptr;      // [B][max_points][7]
+  double* pose_targets = nullptr;   // [B][N+1][7]
+  double* joint_targets = nullptr;  // [B][N+1][D]
+  double* jac = nullptr;            // [B][N][6][D], allocated on first upload
   // generic constraints
   double* cons = nullptr;
   double* s_start = nullptr;
@@ -95,7 +102,7 @@ struct Dims {
   int64_t r_cap = 0;
 };
 
-enum class Mode { kNone, kJoint, kGeneric };
+enum class Mode { kNone, kJoint, kGeneric, kCartesian };
 
 // ---- kernel launchers (tpb_kernels.cu); each returns the number of kernels
 // it launched.
@@ -110,5 +117,14 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
                      int max_loops, cudaStream_t st);
 int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, double dt,
                     int num_sms, cudaStream_t st);
+
+// Cartesian path (tpb_cartesian.cu); -1 = unsupported built-in model
+int launch_cart_fit(const Dims& d, const DeviceArrays& a, double rotation_rounding,
+                    double translation_rounding, bool auto_delta, cudaStream_t st);
+int launch_cart_sample_targets(const Dims& d, const DeviceArrays& a, cudaStream_t st);
+int launch_cart_ik_builtin(const Dims& d, const DeviceArrays& a, int model, cudaStream_t st);
+int launch_cart_constraints(const Dims& d, const DeviceArrays& a, double safety,
+                            double max_trans_vel, double max_rot_vel, int model, bool have_jac,
+                            cudaStream_t st);
 
 }  // namespace tpb

@@ -15,6 +15,7 @@
 #include <type_traits>
 
 #include "tpb_engine.h"
+#include "tpb_fit.cuh"
 #include "tpb_integrate.cuh"
 #include "tpb_joint_limit.cuh"
 #include "tpb_solver.cuh"
@@ -26,26 +27,6 @@ namespace {
 // K2: joint_fit
 // ===========================================================================
 
-// PolyLineToBspline3WaypointsCornerOffset, splines/spline_utils.cc:25-45.
-__device__ void corner_offset(const double* delta, int D, double radius, double* off) {
-  constexpr double kMinNorm = 1e-6;
-  constexpr double kMinWaypointSpacingFactor = 4.0;  // spline_utils.h:46
-  double s = 0.0;
-  for (int d = 0; d < D; ++d) s += delta[d] * delta[d];
-  const double norm = sqrt(s);
-  if (norm > kMinNorm) {
-    for (int d = 0; d < D; ++d) off[d] = delta[d] / norm;
-  } else {
-    for (int d = 0; d < D; ++d) off[d] = 0.0;
-  }
-  if (norm > kMinWaypointSpacingFactor * radius) {
-    for (int d = 0; d < D; ++d) off[d] = off[d] * radius;
-  } else {
-    const double f = 1.0 / kMinWaypointSpacingFactor;
-    for (int d = 0; d < D; ++d) off[d] = (off[d] * f) * norm;
-  }
-}
-
 __global__ void k_joint_fit(Dims dm, DeviceArrays a, double rounding, bool auto_delta) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= dm.B) return;
@@ -54,45 +35,10 @@ __global__ void k_joint_fit(Dims dm, DeviceArrays a, double rounding, bool auto_
   const double* wp = a.waypoints + static_cast<size_t>(b) * dm.Wmax * D;
   double* c = a.ctrl + static_cast<size_t>(b) * dm.max_points * D;
   double* kn = a.knots + static_cast<size_t>(b) * (dm.max_points + 3);
-  double delta[kMaxDofs], off[kMaxDofs];
 
-  // PolyLineToBspline3Waypoints (VectorXd), splines/spline_utils.cc:47-102.
-  int n;
-  if (W == 1) {
-    n = 4;
-    for (int i = 0; i < 4; ++i)
-      for (int d = 0; d < D; ++d) c[i * D + d] = wp[d];
-  } else {
-    n = 3 * W - 2;
-    for (int i = 0; i < W; ++i)
-      for (int d = 0; d < D; ++d) c[3 * i * D + d] = wp[i * D + d];
-    for (int i = 1; i < W - 1; ++i) {
-      const int k = 3 * i, knext = 3 * (i + 1), klast = 3 * (i - 1);
-      for (int d = 0; d < D; ++d) delta[d] = c[knext * D + d] - c[k * D + d];
-      corner_offset(delta, D, rounding, off);
-      for (int d = 0; d < D; ++d) c[(k + 1) * D + d] = c[k * D + d] + off[d];
-      for (int d = 0; d < D; ++d) delta[d] = c[klast * D + d] - c[k * D + d];
-      corner_offset(delta, D, rounding, off);
-      for (int d = 0; d < D; ++d) c[(k - 1) * D + d] = c[k * D + d] + off[d];
-    }
-    for (int d = 0; d < D; ++d) delta[d] = c[3 * D + d] - c[d];
-    corner_offset(delta, D, rounding, off);
-    for (int d = 0; d < D; ++d) c[D + d] = c[d] + off[d];
-    for (int d = 0; d < D; ++d) delta[d] = c[(n - 4) * D + d] - c[(n - 1) * D + d];
-    corner_offset(delta, D, rounding, off);
-    for (int d = 0; d < D; ++d) c[(n - 2) * D + d] = c[(n - 1) * D + d] + off[d];
-  }
-
-  // MakeUniformKnotVector on [0,1] (bspline_base.cc:350-381), degree 2
-  // (kSplineOrder, timeable_path_joint_spline.h:89), then scaled by the control
-  // polygon length (timeable_path_joint_spline.cc:271-285).
-  constexpr int p = 2;
-  const int nk = n + p + 1;
-  for (int i = 0; i <= p; ++i) kn[i] = 0.0;
-  const double denom = nk - 2.0 * (p + 1.0) + 1.0;
-  const double spacing = (1.0 / denom) * (1.0 - 0.0);
-  for (int i = p + 1; i < nk - p - 1; ++i) kn[i] = kn[i - 1] + spacing;
-  for (int i = nk - p - 1; i < nk; ++i) kn[i] = 1.0;
+  const int n = polyline_to_bspline3(wp, W, D, rounding, c);
+  const int nk = uniform_knots_degree2(n, kn);
+  // knots scaled by the control polygon length (timeable_path_joint_spline.cc:271-285)
   double length = 0.0;
   for (int i = 0; i < n - 1; ++i) {
     double s = 0.0;

@@ -133,3 +133,32 @@ def random_constraints(rng, N, C):
         else:
             c[:, r, 0], c[:, r, 1], c[:, r, 2], c[:, r, 3] = 0.0, A * A, 0.0, rng.uniform(0.5, 4.0)
     return c
+
+
+def _exp_so3(v):
+    """Rotation vector -> quaternion (x, y, z, w)."""
+    th = np.linalg.norm(v, axis=-1, keepdims=True)
+    k = np.where(th < 1e-8, 0.5 - th * th / 48.0, np.sin(0.5 * th) / np.where(th == 0, 1.0, th))
+    return np.concatenate([k * v, np.cos(0.5 * th)], axis=-1)
+
+
+def cart_paths(num_paths, num_waypoints=5, seed=5000):
+    """cfg5: Cartesian paths for the reference test's fake 7-dof kinematics
+    (path_timing_trajectory_test.cc:548-587).  Waypoint translations
+    ~ U(-0.5, 0.5)^3 m, rotations ExpSO3(U(-1, 1)^3); joint waypoints are the
+    fake IK of the poses (q[0:3] = translation, q[3:6] = rotation vector) plus
+    q[6] ~ U(-1, 1); v_max = 1 rad/s, a_max = 2 rad/s^2 (the reference test's
+    limits).  Returns (pose_wp [B][W][7] rows (tx,ty,tz,qx,qy,qz,qw),
+    joint_wp [B][W][7], vmax [B][7], amax [B][7])."""
+    rng = np.random.default_rng(seed)
+    B, W = num_paths, num_waypoints
+    per = rng.random((B, W * 7))
+    per = per.reshape(B, W, 7)
+    trans = per[..., 0:3] - 0.5
+    rotvec = per[..., 3:6] * 2.0 - 1.0
+    q6 = per[..., 6:7] * 2.0 - 1.0
+    pose = np.concatenate([trans, _exp_so3(rotvec)], axis=-1)
+    joint = np.concatenate([trans, rotvec, q6], axis=-1)
+    vmax = np.full((B, 7), 1.0)
+    amax = np.full((B, 7), 2.0)
+    return (np.ascontiguousarray(pose), np.ascontiguousarray(joint), vmax, amax)
