@@ -12,6 +12,7 @@
 #include "trajectory_planning/path_timing_trajectory.h"
 #include "trajectory_planning/splines/bspline.h"
 #include "trajectory_planning/time_optimal_path_timing.h"
+#include "trajectory_planning/timeable_path_cartesian_spline.h"
 #include "trajectory_planning/timeable_path_joint_spline.h"
 
 using namespace trajectory_planning;  // NOLINT
@@ -35,6 +36,58 @@ static std::vector<double> Flatten(const std::vector<VectorXd>& v) {
   std::vector<double> out;
   for (const auto& x : v) out.insert(out.end(), x.begin(), x.end());
   return out;
+}
+
+// ---- the reference test's fake kinematics (path_timing_trajectory_test.cc:548-587)
+// as host callbacks: translation = q[0:3], rotation = ExpSO3(q[3:6]).
+constexpr int kFakeDofs = 7;
+static tp::Quaterniond ExpSO3(double x, double y, double z) {
+  const double th2 = x * x + y * y + z * z, th = std::sqrt(th2);
+  const double k = (th < 1e-8) ? 0.5 - th2 / 48.0 : std::sin(0.5 * th) / th;
+  return tp::Quaterniond(std::cos(0.5 * th), k * x, k * y, k * z);
+}
+static void LogSO3(const tp::Quaterniond& q, double* v) {
+  const double n = std::sqrt(q.x() * q.x() + q.y() * q.y() + q.z() * q.z());
+  const double k = (n < 1e-10) ? 2.0 / q.w() : 2.0 * std::atan2(n, q.w()) / n;
+  v[0] = k * q.x();
+  v[1] = k * q.y();
+  v[2] = k * q.z();
+}
+static tp::Pose3d FakeFK(const VectorXd& j) {
+  return tp::Pose3d(ExpSO3(j[3], j[4], j[5]), tp::Vector3d(j[0], j[1], j[2]));
+}
+static tp::Status FakePathIK(const VectorXd&, const std::vector<tp::Pose3d>& pose,
+                             const std::vector<VectorXd>& joint, std::vector<VectorXd>* solution) {
+  solution->resize(pose.size());
+  for (size_t i = 0; i < pose.size(); ++i) {
+    VectorXd s(kFakeDofs);
+    for (int k = 0; k < 3; ++k) s[k] = pose[i].translation()[k];
+    LogSO3(pose[i].quaternion(), &s[3]);
+    s[6] = joint[i][6];
+    (*solution)[i] = s;
+  }
+  return tp::OkStatus();
+}
+static tp::Status FakeJacobian(const VectorXd& j, tp::Matrix6Xd* jac) {
+  const tp::Quaterniond q = ExpSO3(j[3], j[4], j[5]);
+  const double qv[3] = {q.x(), q.y(), q.z()};
+  const double n2 = qv[0] * qv[0] + qv[1] * qv[1] + qv[2] * qv[2], n = std::sqrt(n2), w = q.w();
+  const double den = n2 + w * w;
+  double k, c;
+  if (n < 1e-6) {
+    k = 2.0 / w;
+    c = (-4.0 / 3.0) / (w * w * w);
+  } else {
+    k = 2.0 * std::atan2(n, w) / n;
+    c = (2.0 * w / den - k) / n2;
+  }
+  jac->setZero();
+  for (int r = 0; r < 3; ++r) {
+    (*jac)(r, r) = 1.0;
+    for (int col = 0; col < 3; ++col) (*jac)(3 + r, 3 + col) = ((r == col) ? k : 0.0) + c * qv[r] * qv[col];
+    (*jac)(3 + r, 6) = -2.0 * qv[r] / den;
+  }
+  return tp::OkStatus();
 }
 
 int main() {
@@ -203,6 +256,86 @@ int main() {
     EXPECT(auto_knots.SetUniformKnotVector(7).ok());
     auto kv = auto_knots.GetKnotVector();
     EXPECT(kv.size() == 7 && kv[2] == 0.25 && kv[3] == 0.5 && kv[4] == 0.75);
+  }
+  // ---- Cartesian path (path_timing_trajectory_test.cc:589-700): corner rounding
+  // setters, then a whole path planned with host IK / Jacobian callbacks and with
+  // the built-in device kinematics
+  {
+    constexpr size_t kN = 1000;
+    auto make_path = [&](int model) {
+      CartesianPathOptions opt;
+      opt.set_path_ik_func(FakePathIK).set_jacobian_func(FakeJacobian);
+      opt.set_num_dofs(kFakeDofs).set_num_path_samples(kN).set_delta_parameter(0.02);
+      opt.set_device_kinematics(model);
+      return std::make_shared<TimeableCartesianSplinePath>(opt);
+    };
+    auto path = make_path(TPB_KIN_HOST);
+    EXPECT(path->SetRotationRounding(0.1).ok());
+    EXPECT(path->SetTranslationRounding(0.05).ok());
+    EXPECT(path->GetRotationRounding() == 0.1 && path->GetTranslationRounding() == 0.05);
+    EXPECT(path->SetRotationRounding(0.0).code() == tp::StatusCode::kInvalidArgument);
+    EXPECT(path->SetTranslationRounding(-1.0).code() == tp::StatusCode::kInvalidArgument);
+    EXPECT(path->SetMaxCartesianVelocity(0.0, 0.25).code() == tp::StatusCode::kInvalidArgument);
+    std::vector<VectorXd> jw = {VectorXd{0.1, 0.0, 0.2, 0.0, 0.1, 0.0, 0.3},
+                                VectorXd{0.3, 0.1, 0.1, 0.2, -0.1, 0.3, -0.2},
+                                VectorXd{0.2, 0.3, 0.0, -0.1, 0.2, 0.1, 0.1}};
+    std::vector<tp::Pose3d> pw;
+    for (const auto& j : jw) pw.push_back(FakeFK(j));
+    printf("\"cartesian\": {\n");
+    for (int mode = 0; mode < 2; ++mode) {
+      if (mode == 1) {
+        path = make_path(TPB_KIN_FAKE7);
+        path->SetRotationRounding(0.1);
+        path->SetTranslationRounding(0.05);
+      }
+      PathTimingTrajectory planner(PathTimingTrajectoryOptions()
+                                       .SetTimeStep(tp::Milliseconds(4))
+                                       .SetNumDofs(kFakeDofs)
+                                       .SetNumPathSamples(kN));
+      EXPECT(planner.SetPath(path).ok());
+      EXPECT(path->SetWaypoints(pw, std::vector<VectorXd>{jw[0]}).code() == tp::StatusCode::kInvalidArgument);
+      EXPECT(path->SetWaypoints(pw, jw).ok());
+      EXPECT(path->GetState() == TimeablePath::State::kNewPath);
+      VectorXd vmax = VectorXd::Constant(kFakeDofs, 1.0), amax = VectorXd::Constant(kFakeDofs, 2.0);
+      EXPECT(path->SetMaxJointVelocity(ToSpan(vmax)).ok());
+      EXPECT(path->SetMaxJointAcceleration(ToSpan(amax)).ok());
+      EXPECT(path->SetMaxCartesianVelocity(0.5, 0.25).ok());
+      const tp::Status st = planner.Plan(TimeFromSec(0.0), tp::Seconds(1000));
+      EXPECT(st.ok());
+      if (!st.ok()) fprintf(stderr, "Cartesian Plan (mode %d): %s\n", mode, st.message().c_str());
+      EXPECT(path->GetState() == TimeablePath::State::kPathWasSampled);
+      EXPECT(path->NumConstraints() == 16 && path->GetConstraints().size() == kN);
+      EXPECT(path->GetSplineIKPosition().size() == kN);
+      EXPECT(path->PathIkIndex(0.1) == 5 && path->PathIkParameter(5) == 0.1);
+      const auto& pos = planner.GetPositions();
+      EXPECT(!pos.empty());
+      printf("\"%s\": {\n", mode == 0 ? "host_callbacks" : "device_kinematics");
+      PrintArray("knots", path->GetKnots());
+      PrintArray("time", planner.GetTime());
+      PrintArray("positions", Flatten(planner.GetPositions()));
+      PrintArray("velocities", Flatten(planner.GetVelocities()));
+      PrintArray("q_last", std::vector<double>(path->GetPathEnd().begin(), path->GetPathEnd().end()));
+      const auto& c = path->GetConstraints()[10];
+      std::vector<double> rows;
+      for (int r = 0; r < c.size(); ++r) {
+        rows.push_back(c.a_coefficient(r));
+        rows.push_back(c.b_coefficient(r));
+        rows.push_back(c.lower(r));
+        rows.push_back(c.upper(r));
+      }
+      PrintArray("constraints_sample10", rows, false);
+      printf("}%s\n", mode == 0 ? "," : "");
+    }
+    std::vector<double> jflat, pflat;
+    for (size_t w = 0; w < jw.size(); ++w) {
+      jflat.insert(jflat.end(), jw[w].begin(), jw[w].end());
+      for (int k = 0; k < 3; ++k) pflat.push_back(pw[w].translation()[k]);
+      for (int k = 0; k < 4; ++k) pflat.push_back(pw[w].quaternion().coeffs()[k]);
+    }
+    printf(",");
+    PrintArray("joint_waypoints", jflat);
+    PrintArray("pose_waypoints", pflat, false);
+    printf("},\n");
   }
   // ---- batched front-end
   {

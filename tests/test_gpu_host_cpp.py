@@ -87,3 +87,34 @@ def test_batch_front_end_matches_oracle(result, po):
         assert abs(b["duration"][i] - o["duration"]) <= 1e-6 * max(o["duration"], 1e-300)
         assert off[i + 1] - off[i] == o["M"]
         assert np.max(np.abs(pos[off[i]:off[i + 1]] - o["r_pos"])) <= 1e-9
+
+
+def test_cartesian_path_matches_oracle(result, po):
+    """TimeableCartesianSplinePath + PathTimingTrajectory::Plan with the reference
+    test's fake kinematics: as host PathIKFunc / JacobianFunc callbacks and as the
+    built-in device model, against the oracle's whole-path restatement."""
+    c = result["cartesian"]
+    jw = np.array(c["joint_waypoints"]).reshape(3, 7)
+    pw = np.array(c["pose_waypoints"]).reshape(3, 7)
+    vmax, amax = np.full(7, 1.0), np.full(7, 2.0)
+    o = po.plan_cart_fake(pw, jw, vmax, amax, 1000, translation_rounding=0.05,
+                          rotation_rounding=0.1, delta=0.02, dt=0.004, M_cap=40000)
+    assert o["ok"]
+    for mode in ("host_callbacks", "device_kinematics"):
+        r = c[mode]
+        assert np.max(np.abs(np.array(r["knots"]) - o["knots"])) <= 1e-12 * o["knots"][-1]
+        t = np.array(r["time"])
+        pos = np.array(r["positions"]).reshape(-1, 7)
+        vel = np.array(r["velocities"]).reshape(-1, 7)
+        assert abs(len(t) - o["M"]) <= 1
+        assert abs(t[-1] - o["r_t"][-1]) <= 1e-6 * o["r_t"][-1] + 0.004
+        m = min(len(t), o["M"]) - 1
+        assert np.max(np.abs(pos[:m] - o["r_pos"][:m])) <= 1e-9
+        assert np.max(np.abs(vel[:m] - o["r_vel"][:m])) <= 1e-6
+        # ends at the last waypoint (fake IK of the last pose), at rest
+        assert np.max(np.abs(pos[-1] - jw[-1])) <= 1e-9
+        assert (vel[-1] == 0).all()
+        assert np.max(np.abs(np.array(r["q_last"]) - jw[-1])) <= 1e-12
+        rows = np.array(r["constraints_sample10"]).reshape(16, 4)
+        assert np.max(np.abs(rows - o["cons"][10])) <= 1e-8
+        assert (rows[:7, 3] == 1.6).all() and (rows[14, 3] == 0.25) and (rows[15, 3] == 0.0625)

@@ -127,6 +127,67 @@ class VectorXd {
   std::vector<double> d_;
 };
 
+// Minimal stand-ins for eigenmath::Vector3d / Quaterniond / Pose3d / Matrix6Xd:
+// plain storage in Eigen's coefficient order (x, y, z, w), no arithmetic (the
+// Cartesian path's arithmetic runs on the device).
+struct Vector3d {
+  double v[3] = {0.0, 0.0, 0.0};
+  Vector3d() = default;
+  Vector3d(double x, double y, double z) : v{x, y, z} {}
+  double& operator[](size_t i) { return v[i]; }
+  const double& operator[](size_t i) const { return v[i]; }
+  double& operator()(size_t i) { return v[i]; }
+  const double& operator()(size_t i) const { return v[i]; }
+};
+struct Quaterniond {
+  double c[4] = {0.0, 0.0, 0.0, 1.0};  // x, y, z, w
+  Quaterniond() = default;
+  Quaterniond(double w, double x, double y, double z) : c{x, y, z, w} {}  // Eigen's ctor order
+  static Quaterniond Identity() { return Quaterniond(); }
+  double x() const { return c[0]; }
+  double y() const { return c[1]; }
+  double z() const { return c[2]; }
+  double w() const { return c[3]; }
+  const double* coeffs() const { return c; }
+  double* coeffs() { return c; }
+};
+class Pose3d {
+ public:
+  Pose3d() = default;
+  explicit Pose3d(const Vector3d& t) : t_(t) {}
+  explicit Pose3d(const Quaterniond& q) : q_(q) {}
+  Pose3d(const Quaterniond& q, const Vector3d& t) : t_(t), q_(q) {}
+  const Vector3d& translation() const { return t_; }
+  Vector3d& translation() { return t_; }
+  const Quaterniond& quaternion() const { return q_; }
+  void setQuaternion(const Quaterniond& q) { q_ = q; }
+
+ private:
+  Vector3d t_;
+  Quaterniond q_;
+};
+// 6 x n, row-major storage, (row, col) access like Eigen's operator().
+class Matrix6Xd {
+ public:
+  Matrix6Xd() = default;
+  Matrix6Xd(size_t rows, size_t cols) : cols_(cols), d_(6 * cols, 0.0) { (void)rows; }
+  void resize(size_t rows, size_t cols) {
+    (void)rows;
+    cols_ = cols;
+    d_.assign(6 * cols, 0.0);
+  }
+  void setZero() { for (auto& x : d_) x = 0.0; }
+  size_t rows() const { return 6; }
+  size_t cols() const { return cols_; }
+  double& operator()(size_t r, size_t c) { return d_[r * cols_ + c]; }
+  const double& operator()(size_t r, size_t c) const { return d_[r * cols_ + c]; }
+  const double* data() const { return d_.data(); }
+
+ private:
+  size_t cols_ = 0;
+  std::vector<double> d_;
+};
+
 // absl::Time / absl::Duration only matter through int64-nanosecond conversions
 // (trajectory_planning/time.h:23-30).
 struct Duration {

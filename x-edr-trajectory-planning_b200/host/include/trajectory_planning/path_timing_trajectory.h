@@ -134,11 +134,10 @@ class PathTimingTrajectory : public TrajectoryPlanner {
     if (options_.GetTimeSamplingMethod() != PathTimingTrajectoryOptions::TimeSamplingMethod::kUniformlyInTime) {
       return tp::UnimplementedError("kSkipSamplesCloserThanTimeStep is outside the hot path");
     }
-    auto* joint = dynamic_cast<TimeableJointSplinePath*>(path_.get());
-    if (joint == nullptr || joint->engine() == nullptr) {
-      return tp::UnimplementedError("only TimeableJointSplinePath is accelerated");
+    if (path_->DeviceEngine() == nullptr) {
+      return tp::UnimplementedError(
+          "only device-backed paths (TimeableJointSplinePath, TimeableCartesianSplinePath) are timed");
     }
-    tpb_engine* e = joint->engine();
     if (time_horizon.ns <= 0) return tp::InvalidArgumentError("Duration must be positive");
 
     // ---- ComputeTimingProfile (.cc:307-475), kNewPath branch
@@ -171,6 +170,9 @@ class PathTimingTrajectory : public TrajectoryPlanner {
             std::to_string(err));
       }
     }
+    // the Cartesian path creates its engine state in SamplePath / ConstraintSetup
+    tpb_engine* e = path_->DeviceEngine();
+    if (e == nullptr) return tp::InternalError("path has no device engine after SamplePath");
     const int max_solver_loops = static_cast<int>(std::max<size_t>(100, 10 * options_.GetNumPathSamples()));
     int32_t rc = tpb_optimize(e, &path_start_velocity_, &path_start_acceleration_, &path_time_start_,
                               max_solver_loops, 0);

@@ -86,6 +86,10 @@ class TimeablePath {
   virtual const tp::VectorXd& GetPathPositionAt(size_t n) const = 0;
   virtual const tp::VectorXd& GetFirstPathDerivativeAt(size_t n) const = 0;
   virtual const tp::VectorXd& GetSecondPathDerivativeAt(size_t n) const = 0;
+  // Extension (not in the reference): the engine that holds this path's device
+  // state once SamplePath + ConstraintSetup have run; PathTimingTrajectory times
+  // the path there.  nullptr = not a device-backed path.
+  virtual tpb_engine* DeviceEngine() { return nullptr; }
 };
 
 inline constexpr const char* ToString(const TimeablePath::State state) {

@@ -203,6 +203,7 @@ class TimeableJointSplinePath : public TimeablePath {
   const std::vector<tp::VectorXd>& GetControlPoints() const { return control_points_; }
   const std::vector<double>& GetKnots() const { return knots_; }
   tpb_engine* engine() { return e_; }
+  tpb_engine* DeviceEngine() override { return e_; }
 
  private:
   static constexpr int kSplineOrder = 2;  // .h:89
