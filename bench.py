@@ -358,6 +358,10 @@ def run_ours(args):
     spline = run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, world,
                               args)
 
+    # ---- Cartesian paths (BASELINE config 5) ----
+    cartesian = run_cartesian_leg(pkg, torch, dev, stream, local_rank, max_over_ranks, barrier,
+                                  world, rank, args)
+
     # ---- final gather of the per-path durations (outside any timed region) ----
     if world > 1:
         g = [torch.empty(B, dtype=torch.float64, device=dev) for _ in range(world)]
@@ -403,11 +407,62 @@ def run_ours(args):
             "stage_ms": stage_ms, "paths_ok": n_ok, "resampled_rows_per_gpu": total_rows,
             "mean_duration_s": float(np.nanmean(all_dur)),
             "e2e_matches_device_run": same, "spline_eval": spline,
+            "cartesian": cartesian,
         }
         print(json.dumps(line))
     eng.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_cartesian_leg(pkg, torch, dev, stream, local_rank, max_over_ranks, barrier, world, rank,
+                      args):
+    """BASELINE config 5: 4,096 Cartesian paths (position + quaternion spline, W = 5 pose
+    waypoints, N = 1000 samples) per GPU: fit, SamplePath (quaternion / translation / joint
+    spline targets, built-in fake-robot IK, forward-difference derivatives), ConstraintSetup
+    (2D+2 = 16 rows), limit curve and time-optimal timing.  The whole path is one planning
+    window (delta = knots.back() / (N - 1)).  Inputs resident in HBM, CUDA events."""
+    if args.no_cartesian:
+        return None
+    B, W, N = 4096, 5, 1000
+    pw, jw, vm, am = pkg.workloads.cart_paths(B * world, W, seed=5000)
+    sl = slice(rank * B, (rank + 1) * B)
+    d_pw = torch.from_numpy(pw[sl].copy()).to(dev)
+    d_jw = torch.from_numpy(jw[sl].copy()).to(dev)
+    d_vm = torch.from_numpy(vm[sl].copy()).to(dev)
+    d_am = torch.from_numpy(am[sl].copy()).to(dev)
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=7, max_waypoints=W, cartesian=True,
+                     device=local_rank)
+    eng.set_stream(stream.cuda_stream)
+    eng.set_cart_options(0.05, 0.5, 0.25)
+
+    def step():
+        eng.set_cart_waypoints(d_pw, d_jw)
+        eng.set_joint_limits(d_vm, d_am)
+        eng.cart_sample_targets()
+        eng.cart_solve_ik(1)
+        eng.cart_setup_constraints(1)
+        eng.optimize()
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = max(3, args.steps)
+    e0.record(stream)
+    for _ in range(reps):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = max_over_ranks(e0.elapsed_time(e1)) / reps
+    status = eng.get(pkg.ARR.STATUS)
+    dur = eng.get(pkg.ARR.DURATION)
+    eng.close()
+    return {"paths_per_s": world * B / (ms / 1e3), "ms": ms, "paths_per_gpu": B,
+            "num_samples": N, "num_waypoints": W, "rows_per_sample": 16,
+            "kinematics": "TPB_KIN_FAKE7 (reference test's fake robot) on the device",
+            "paths_ok": int((status == 0).sum()), "mean_duration_s": float(np.nanmean(dur))}
 
 
 def run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, world, args):
@@ -427,25 +482,31 @@ def run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, wor
             du = torch.full((S,), 8.0 / (E - 1), dtype=torch.float64, device=dev)
             o = out[:S * E * 3 * D].view(S, E, 3, D)
 
-            def run():
-                pkg.spline_eval_device(d_k, d_c, P, 2, o, u0=u0, du=du, evals=E,
-                                       exact=False, stream=stream.cuda_stream)
-            for _ in range(3):
-                run()
-            torch.cuda.synchronize()
-            barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            reps = 5
-            e0.record(stream)
-            for _ in range(reps):
-                run()
-            e1.record(stream)
-            torch.cuda.synchronize()
-            ms = max_over_ranks(e0.elapsed_time(e1)) / reps
-            gbs = S * E * 3 * D * 8 / (ms / 1e3) / 1e9
-            res[f"p{P}_d{D}"] = {"evals_per_s": world * S * E / (ms / 1e3), "ms": ms,
-                                 "hbm_gbs_per_gpu": gbs, "frac_of_peak": gbs / peak}
+            for exact in (False, True):
+                def run():
+                    pkg.spline_eval_device(d_k, d_c, P, 2, o, u0=u0, du=du, evals=E,
+                                           exact=exact, stream=stream.cuda_stream)
+                for _ in range(3):
+                    run()
+                torch.cuda.synchronize()
+                barrier()
+                e0, e1 = (torch.cuda.Event(enable_timing=True),
+                          torch.cuda.Event(enable_timing=True))
+                reps = 5
+                e0.record(stream)
+                for _ in range(reps):
+                    run()
+                e1.record(stream)
+                torch.cuda.synchronize()
+                ms = max_over_ranks(e0.elapsed_time(e1)) / reps
+                gbs = S * E * 3 * D * 8 / (ms / 1e3) / 1e9
+                key = f"p{P}_d{D}" + ("_exact" if exact else "")
+                res[key] = {"evals_per_s": world * S * E / (ms / 1e3), "ms": ms,
+                            "hbm_gbs_per_gpu": gbs, "frac_of_peak": gbs / peak}
     res["bytes_per_eval"] = "3*dim*8 written (implicit parameter grid, tables in smem)"
+    res["modes"] = ("pP_dD: per-span polynomial form (<= 1e-12 of the reference); pP_dD_exact: "
+                    "NURBS A2.3 in the reference's operation order (bit-identical, "
+                    "FP64-division bound)")
     return res
 
 
@@ -457,6 +518,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-spline", action="store_true")
+    ap.add_argument("--no-cartesian", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -28,6 +28,7 @@ struct EvalArgs {
   const double* du;
   double* out;
   int32_t* status;
+  bool exact;
 };
 
 template <int P, int NDER>
@@ -100,6 +101,131 @@ __global__ void __launch_bounds__(kTile) k_spline_eval(EvalArgs g) {
   }
 }
 
+// ---------------------------------------------------------------------------
+// exact == 0: per-span polynomial form.
+//
+// On one knot span the curve is a polynomial of degree P.  The CTA first builds,
+// for every span of its spline, the Taylor coefficients about the span's
+// midpoint, c_k = C^(k)(mid) / k!, with the same A2.3 routine (NDER = P), and
+// keeps them in shared memory: [span][k][dim].  Every parameter then costs a
+// span search plus 3 fused multiply-adds per coefficient and dimension
+// (Horner with derivatives) and no division, which makes the kernel a pure
+// HBM write stream.  |u - mid| <= h/2 keeps the power basis well conditioned;
+// results agree with the exact form to <= 1e-12 (tests/test_gpu_spline_eval.py).
+// A CTA evaluates kPolyTiles tiles of kTile parameters so that the table build
+// is amortised.
+// ---------------------------------------------------------------------------
+constexpr int kPolyTiles = 16;
+
+template <int P, int NDER>
+__global__ void __launch_bounds__(kTile) k_spline_eval_poly(EvalArgs g) {
+  extern __shared__ __align__(16) double smem[];
+  const int n = g.num_points;
+  const int nk = n + P + 1;
+  const int D = g.dim;
+  const int nspan = n - P;
+  constexpr int K = NDER + 1;
+  double* s_knots = smem;                          // [nk]
+  double* s_mid = s_knots + nk;                    // [nspan]
+  double* s_coef = s_mid + nspan;                  // [nspan][P+1][D]
+  double* s_ctrl = s_coef + nspan * (P + 1) * D;   // [n][D] (table build only)
+  double* s_out = smem + ((nk + nspan + nspan * (P + 1) * D + n * D + 1) & ~1);  // [kTile][K*D]
+  const int s = blockIdx.y;
+  {
+    const double* gk = g.knots + static_cast<size_t>(s) * nk;
+    const double* gc = g.ctrl + static_cast<size_t>(s) * n * D;
+    for (int i = threadIdx.x; i < nk; i += kTile) s_knots[i] = gk[i];
+    for (int i = threadIdx.x; i < n * D; i += kTile) s_ctrl[i] = gc[i];
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < nspan; t += kTile) {
+    const int sp = P + t;
+    const double lo = s_knots[sp], hi = s_knots[sp + 1];
+    const double mid = 0.5 * (lo + hi);
+    s_mid[t] = mid;
+    if (hi > lo) {  // empty spans are never selected by KnotSpan
+      double ders[P + 1][P + 1];
+      basis_ders<P, P>(s_knots, sp, mid, ders);
+      double fact = 1.0;
+#pragma unroll
+      for (int k = 0; k <= P; ++k) {
+        if (k > 1) fact *= static_cast<double>(k);
+        for (int d = 0; d < D; ++d) {
+          double acc = 0.0;
+#pragma unroll
+          for (int j = 0; j <= P; ++j) acc = fma(ders[k][j], s_ctrl[(sp - P + j) * D + d], acc);
+          s_coef[(t * (P + 1) + k) * D + d] = acc / fact;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  const int rowlen = K * D;
+  const long long chunk0 = static_cast<long long>(blockIdx.x) * kTile * kPolyTiles;
+  for (int tile = 0; tile < kPolyTiles; ++tile) {
+    const long long e0 = chunk0 + static_cast<long long>(tile) * kTile;
+    if (e0 >= g.evals) break;
+    const long long e = e0 + threadIdx.x;
+    bool ok = false;
+    if (e < g.evals) {
+      const size_t flat = static_cast<size_t>(s) * g.evals + e;
+      const double u = g.u ? g.u[flat] : (g.u0[s] + static_cast<double>(e) * g.du[s]);
+      ok = (u >= s_knots[0]) && (u <= s_knots[nk - 1]);
+      if (g.status) g.status[flat] = ok ? TPB_OK : TPB_OUT_OF_RANGE;
+      if (ok) {
+        const int t = knot_span(s_knots, nk, P, u) - P;
+        const double x = u - s_mid[t];
+        const double* c = s_coef + t * (P + 1) * D;
+        double* o = s_out + threadIdx.x * rowlen;
+        for (int d = 0; d < D; ++d) {
+          double p0 = c[P * D + d], p1 = 0.0, p2 = 0.0, p3 = 0.0;
+#pragma unroll
+          for (int k = P - 1; k >= 0; --k) {
+            if (NDER >= 3) p3 = fma(p3, x, p2);
+            if (NDER >= 2) p2 = fma(p2, x, p1);
+            if (NDER >= 1) p1 = fma(p1, x, p0);
+            p0 = fma(p0, x, c[k * D + d]);
+          }
+          o[d] = p0;
+          if (NDER >= 1) o[D + d] = p1;
+          if (NDER >= 2) o[2 * D + d] = 2.0 * p2;
+          if (NDER >= 3) o[3 * D + d] = 6.0 * p3;
+        }
+      }
+    }
+    const int all_ok = __syncthreads_and(ok || e >= g.evals);
+    const long long n_in_tile = min(static_cast<long long>(kTile), g.evals - e0);
+    double* gout = g.out + (static_cast<size_t>(s) * g.evals + e0) * rowlen;
+    if (all_ok) {
+      const int total = static_cast<int>(n_in_tile) * rowlen;
+      if ((reinterpret_cast<uintptr_t>(gout) & 15) == 0 && (total & 1) == 0) {
+        const double2* s2 = reinterpret_cast<const double2*>(s_out);
+        double2* g2 = reinterpret_cast<double2*>(gout);
+        for (int i = threadIdx.x; i < total / 2; i += kTile) g2[i] = s2[i];
+      } else {
+        for (int i = threadIdx.x; i < total; i += kTile) gout[i] = s_out[i];
+      }
+    } else if (ok) {
+      const double* o = s_out + threadIdx.x * rowlen;
+      for (int i = 0; i < rowlen; ++i) gout[threadIdx.x * rowlen + i] = o[i];
+    }
+    __syncthreads();  // s_out is reused by the next tile
+  }
+}
+
+template <int P, int NDER>
+void launch_one_poly(const EvalArgs& g, cudaStream_t st) {
+  const int n = g.num_points, nk = n + P + 1, nspan = n - P;
+  const size_t smem = sizeof(double) * (nk + nspan + static_cast<size_t>(nspan) * (P + 1) * g.dim +
+                                        static_cast<size_t>(n) * g.dim + 1 +
+                                        static_cast<size_t>(kTile) * (NDER + 1) * g.dim);
+  cudaFuncSetAttribute(k_spline_eval_poly<P, NDER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       static_cast<int>(smem));
+  const long long per_cta = static_cast<long long>(kTile) * kPolyTiles;
+  dim3 grid(static_cast<unsigned>((g.evals + per_cta - 1) / per_cta), g.num_splines);
+  k_spline_eval_poly<P, NDER><<<grid, kTile, smem, st>>>(g);
+}
+
 template <int P, int NDER>
 void launch_one(const EvalArgs& g, cudaStream_t st) {
   const int nk = g.num_points + P + 1;
@@ -111,27 +237,36 @@ void launch_one(const EvalArgs& g, cudaStream_t st) {
   k_spline_eval<P, NDER><<<grid, kTile, smem, st>>>(g);
 }
 
+template <int P, int NDER>
+void launch_either(const EvalArgs& g, cudaStream_t st) {
+  if (g.exact) {
+    launch_one<P, NDER>(g, st);
+  } else {
+    launch_one_poly<P, NDER>(g, st);
+  }
+}
+
 template <int P>
 bool dispatch_nder(int nder, const EvalArgs& g, cudaStream_t st) {
   if (nder == 0) {
-    launch_one<P, 0>(g, st);
+    launch_either<P, 0>(g, st);
     return true;
   }
   if constexpr (P >= 1) {
     if (nder == 1) {
-      launch_one<P, 1>(g, st);
+      launch_either<P, 1>(g, st);
       return true;
     }
   }
   if constexpr (P >= 2) {
     if (nder == 2) {
-      launch_one<P, 2>(g, st);
+      launch_either<P, 2>(g, st);
       return true;
     }
   }
   if constexpr (P >= 3) {
     if (nder == 3) {
-      launch_one<P, 3>(g, st);
+      launch_either<P, 3>(g, st);
       return true;
     }
   }
@@ -163,16 +298,20 @@ int launch_spline_eval(const tpb_spline_eval_desc& d, cudaStream_t st, std::stri
     return TPB_OUT_OF_RANGE;
   }
   if (d.evals_per_spline == 0) return TPB_OK;
-  const size_t smem = sizeof(double) * (d.num_points + d.degree + 2 +
-                                        static_cast<size_t>(d.num_points) * d.dim +
-                                        static_cast<size_t>(kTile) * (d.nder + 1) * d.dim);
+  size_t smem = sizeof(double) * (d.num_points + d.degree + 2 +
+                                  static_cast<size_t>(d.num_points) * d.dim +
+                                  static_cast<size_t>(kTile) * (d.nder + 1) * d.dim);
+  if (!d.exact) {  // + span midpoints and the per-span coefficient table
+    const size_t nspan = static_cast<size_t>(d.num_points - d.degree);
+    smem += sizeof(double) * (nspan + nspan * (d.degree + 1) * d.dim);
+  }
   if (smem > 200 * 1024) {
     *err = "spline tables do not fit in shared memory";
     return TPB_OUT_OF_RANGE;
   }
   EvalArgs g{d.num_points, d.dim,  d.num_splines, static_cast<long long>(d.evals_per_spline),
              d.knots,      d.ctrl, d.u,           d.u0,
-             d.du,         d.out,  d.status};
+             d.du,         d.out,  d.status,      d.exact != 0};
   bool ok = false;
   switch (d.degree) {
     case 1: ok = dispatch_nder<1>(d.nder, g, st); break;
