@@ -157,8 +157,11 @@ k_joint_sample_limit_any(Dims dm, DeviceArrays a, double safety) {
 // D = kD <= 8: one sample per thread, rows and the whole active-set LP in
 // registers (tpb_joint_limit.cuh); q, q', q'' leave through shared memory so that
 // each CTA writes its 128 consecutive [sample][D] rows as contiguous runs.
+#ifndef TPB_SL_MINBLOCKS
+#define TPB_SL_MINBLOCKS 1
+#endif
 template <int kD>
-__global__ void __launch_bounds__(kSampleThreads)
+__global__ void __launch_bounds__(kSampleThreads, TPB_SL_MINBLOCKS)
 k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
   extern __shared__ double smem[];
   const int b = blockIdx.y;
