@@ -214,3 +214,44 @@ def test_limit_curve_bitwise_cfg2_shape(pkg, po):
                       ("B_SDD_MIN", "b_sdd_min"), ("B_SD2_ZERO", "b_sd2_zero"),
                       ("B_TYPE", "b_type"), ("SD2", "sd2")):
             assert np.array_equal(res[k][b], o[ok], equal_nan=True), (b, k)
+
+
+def test_plan_joint_host_chunked_pipeline_matches_staged_calls(pkg):
+    """Batches of >= 1024 paths go through tpb_plan_joint_host in chunks whose
+    device-to-host copies overlap the next chunk's kernels; every output must be
+    identical to the staged whole-batch calls."""
+    B, W, D, N = 1500, 4, 7, 128
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=11)
+    nw = np.full(B, W, np.int32)
+    nw[::7] = 2
+    nw[5::11] = 1
+    res = _run_engine(pkg, wp, vmax, amax, N, num_waypoints=nw)
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * 16384)
+    cap = int(res["total"])
+    out = {"duration": np.zeros(B), "status": np.zeros(B, np.int32),
+           "r_offset": np.zeros(B + 1, np.int64), "r_pos": np.zeros((cap, D)),
+           "r_vel": np.zeros((cap, D)), "r_acc": np.zeros((cap, D)), "r_s": np.zeros(cap),
+           "r_sd": np.zeros(cap), "r_sdd": np.zeros(cap)}
+    for _ in range(2):  # a second call reuses the pipeline's stream / events
+        total = eng.plan_joint_host(wp, vmax, amax, 0.0, 0.004, num_waypoints=nw, out=out)
+    assert total == res["total"]
+    np.testing.assert_array_equal(out["duration"], res["DURATION"])
+    np.testing.assert_array_equal(out["status"], res["STATUS"])
+    np.testing.assert_array_equal(out["r_offset"], res["R_OFFSET"])
+    for k, a in (("r_pos", "R_POS"), ("r_vel", "R_VEL"), ("r_acc", "R_ACC"), ("r_s", "R_S"),
+                 ("r_sd", "R_SD"), ("r_sdd", "R_SDD")):
+        np.testing.assert_array_equal(out[k], res[a], err_msg=k)
+    # staged getters still work on the engine after the pipelined call
+    np.testing.assert_array_equal(eng.get(pkg.ARR.R_POS), res["R_POS"])
+    np.testing.assert_array_equal(eng.get(pkg.ARR.TIME), res["TIME"])
+    # too small a host capacity is reported, not overrun
+    small = dict(out)
+    for k in ("r_pos", "r_vel", "r_acc"):
+        small[k] = np.zeros((cap // 2, D))
+    for k in ("r_s", "r_sd", "r_sdd"):
+        small[k] = np.zeros(cap // 2)
+    with pytest.raises(pkg.TpbError) as ei:
+        eng.plan_joint_host(wp, vmax, amax, 0.0, 0.004, num_waypoints=nw, out=small)
+    assert ei.value.code == 11
+    eng.close()

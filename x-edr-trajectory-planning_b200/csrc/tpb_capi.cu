@@ -35,6 +35,12 @@ struct tpb_engine {
   std::string err;
   int64_t launches = 0;
   std::vector<void*> allocs;
+  // tpb_plan_joint_host pipeline: device-to-host copies of finished chunks run on
+  // their own stream while later chunks are computed
+  cudaStream_t copy_stream = nullptr;
+  static constexpr int kMaxChunks = 16;
+  cudaEvent_t chunk_done[kMaxChunks] = {};
+  int64_t* chunk_rows = nullptr;  // pinned host: rows up to the end of chunk c
 };
 
 namespace {
@@ -274,6 +280,13 @@ int32_t tpb_destroy(tpb_engine* e) {
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (void* p : e->allocs) cudaFree(p);
+  if (e->copy_stream) {
+    cudaStreamSynchronize(e->copy_stream);
+    cudaStreamDestroy(e->copy_stream);
+  }
+  for (auto& ev : e->chunk_done)
+    if (ev) cudaEventDestroy(ev);
+  if (e->chunk_rows) cudaFreeHost(e->chunk_rows);
   if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
   delete e;
   return TPB_OK;
@@ -619,41 +632,116 @@ int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
   int32_t rc;
   if ((rc = tpb_set_joint_waypoints(e, io->num_paths, io->num_waypoints, io->waypoints, 0))) return rc;
   if ((rc = tpb_set_joint_limits(e, io->max_velocity, io->max_acceleration, 1, 0))) return rc;
-  if ((rc = tpb_sample_paths(e, nullptr, 0))) return rc;
-  // fresh path: sd_start = sdd_start = 0, time_start = start (path_timing_trajectory.cc:322-326)
   const auto& d = e->dims;
   cudaSetDevice(e->device);
+  // fresh path: sd_start = sdd_start = 0, time_start = start (path_timing_trajectory.cc:322-326)
+  TPB_CUDA(e, cudaMemsetAsync(e->a.path_start, 0, sizeof(double) * d.B, e->stream));
   TPB_CUDA(e, cudaMemsetAsync(e->a.sd_start, 0, sizeof(double) * d.B, e->stream));
   TPB_CUDA(e, cudaMemsetAsync(e->a.sdd_start, 0, sizeof(double) * d.B, e->stream));
   e->launches += tpb::launch_fill_f64(e->a.time_start, io->start_sec, d.B, e->stream);
-  e->launches += tpb::launch_integrate(d, e->a, e->mode, e->safety, std::max(100, 10 * d.N),
-                                       e->stream);
-  TPB_CUDA(e, cudaGetLastError());
-  e->optimized = true;
-  e->resampled = false;
   io->r_total = 0;
   const bool want_rows = io->time_step_sec > 0 && d.r_cap > 0;
-  if (want_rows) {
-    if ((rc = tpb_resample(e, io->start_sec, io->time_step_sec, nullptr))) return rc;
+  const bool any_out = io->r_pos || io->r_vel || io->r_acc || io->r_s || io->r_sd || io->r_sdd;
+  const int max_loops = std::max(100, 10 * d.N);
+
+  // Chunks of the batch go through sample -> integrate -> resample one after the
+  // other on the engine's stream; the packed rows of a finished chunk are copied
+  // to the host on a second stream while the next chunks are computed.  The first
+  // chunks are small (their compute time is exposed), later ones double in size.
+  int bounds[tpb_engine::kMaxChunks + 1];
+  int nchunks = 0;
+  bounds[0] = 0;
+  if (want_rows && any_out && d.B >= 1024) {
+    int size = std::max(128, d.B / 16);
+    while (bounds[nchunks] < d.B && nchunks < tpb_engine::kMaxChunks - 1) {
+      const int next = std::min(d.B, bounds[nchunks] + size);
+      bounds[++nchunks] = next;
+      if (nchunks >= 2) size *= 2;
+    }
+    if (bounds[nchunks] < d.B) bounds[++nchunks] = d.B;
+  } else {
+    bounds[++nchunks] = d.B;
   }
+  if (nchunks > 1) {
+    if (e->copy_stream == nullptr)
+      TPB_CUDA(e, cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+    if (e->chunk_rows == nullptr)
+      TPB_CUDA(e, cudaMallocHost(&e->chunk_rows, sizeof(int64_t) * tpb_engine::kMaxChunks));
+    for (int c = 0; c < nchunks; ++c)
+      if (e->chunk_done[c] == nullptr)
+        TPB_CUDA(e, cudaEventCreateWithFlags(&e->chunk_done[c], cudaEventDisableTiming));
+  }
+
+  auto launch_chunk = [&](int c) {
+    tpb::Dims dc = d;
+    dc.B = bounds[c + 1] - bounds[c];
+    const tpb::DeviceArrays ac = (nchunks > 1) ? tpb::shifted_joint(e->a, d, bounds[c]) : e->a;
+    e->launches += tpb::launch_joint_sample_limit(dc, ac, e->safety, e->stream);
+    e->launches += tpb::launch_integrate(dc, ac, e->mode, e->safety, max_loops, e->stream);
+    if (want_rows)
+      e->launches += tpb::launch_resample(dc, ac, io->start_sec, io->time_step_sec, e->num_sms,
+                                          e->stream, /*continued=*/c > 0);
+  };
+  const size_t D = d.D;
+  int64_t rows_before = 0;
+  rc = TPB_OK;
+  if (nchunks > 1) {
+    for (int c = 0; c <= nchunks; ++c) {
+      if (c < nchunks) {
+        launch_chunk(c);
+        TPB_CUDA(e, cudaGetLastError());
+        TPB_CUDA(e, cudaMemcpyAsync(&e->chunk_rows[c], e->a.r_offset + bounds[c + 1], sizeof(int64_t),
+                                    cudaMemcpyDeviceToHost, e->stream));
+        TPB_CUDA(e, cudaEventRecord(e->chunk_done[c], e->stream));
+      }
+      if (c == 0) continue;
+      // chunk c-1 is done (or will be while chunk c runs): copy its rows out
+      const int k = c - 1;
+      TPB_CUDA(e, cudaEventSynchronize(e->chunk_done[k]));
+      const int64_t rows_end = e->chunk_rows[k];
+      if (rows_end > d.r_cap || rows_end > io->r_capacity) {
+        rc = fail(e, TPB_OUT_OF_RANGE, rows_end > d.r_cap
+                                           ? "resampled rows exceed max_time_samples_total"
+                                           : "resampled rows exceed r_capacity");
+        break;
+      }
+      const size_t r0 = static_cast<size_t>(rows_before), n = static_cast<size_t>(rows_end - rows_before);
+      auto out = [&](double* dst, const double* src, size_t width) -> cudaError_t {
+        if (dst == nullptr || n == 0) return cudaSuccess;
+        return cudaMemcpyAsync(dst + r0 * width, src + r0 * width, n * width * sizeof(double),
+                               cudaMemcpyDeviceToHost, e->copy_stream);
+      };
+      TPB_CUDA(e, out(io->r_pos, e->a.r_pos, D));
+      TPB_CUDA(e, out(io->r_vel, e->a.r_vel, D));
+      TPB_CUDA(e, out(io->r_acc, e->a.r_acc, D));
+      TPB_CUDA(e, out(io->r_s, e->a.r_s, 1));
+      TPB_CUDA(e, out(io->r_sd, e->a.r_sd, 1));
+      TPB_CUDA(e, out(io->r_sdd, e->a.r_sdd, 1));
+      rows_before = rows_end;
+    }
+    io->r_total = rows_before;
+  } else {
+    launch_chunk(0);
+    TPB_CUDA(e, cudaGetLastError());
+  }
+  e->sampled = e->optimized = true;
+  e->resampled = want_rows;
   if (io->duration)
     TPB_CUDA(e, cudaMemcpyAsync(io->duration, e->a.duration, sizeof(double) * d.B, cudaMemcpyDeviceToHost, e->stream));
   if (io->status)
     TPB_CUDA(e, cudaMemcpyAsync(io->status, e->a.status, sizeof(int32_t) * d.B, cudaMemcpyDeviceToHost, e->stream));
-  if (want_rows) {
+  if (want_rows && io->r_offset)
+    TPB_CUDA(e, cudaMemcpyAsync(io->r_offset, e->a.r_offset, sizeof(int64_t) * (d.B + 1), cudaMemcpyDeviceToHost, e->stream));
+  if (want_rows && nchunks == 1) {
     int64_t total = 0;
     TPB_CUDA(e, cudaMemcpyAsync(&total, e->a.r_offset + d.B, sizeof(int64_t), cudaMemcpyDeviceToHost, e->stream));
-    if (io->r_offset)
-      TPB_CUDA(e, cudaMemcpyAsync(io->r_offset, e->a.r_offset, sizeof(int64_t) * (d.B + 1), cudaMemcpyDeviceToHost, e->stream));
     TPB_CUDA(e, cudaStreamSynchronize(e->stream));
     io->r_total = total;
     if (total > d.r_cap)
       return fail(e, TPB_OUT_OF_RANGE, "resampled rows exceed max_time_samples_total");
     const size_t rows = static_cast<size_t>(total);
-    const bool any_out = io->r_pos || io->r_vel || io->r_acc || io->r_s || io->r_sd || io->r_sdd;
     if (any_out && total > io->r_capacity)
       return fail(e, TPB_OUT_OF_RANGE, "resampled rows exceed r_capacity");
-    const size_t D = d.D;
     if (io->r_pos) TPB_CUDA(e, cudaMemcpyAsync(io->r_pos, e->a.r_pos, rows * D * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
     if (io->r_vel) TPB_CUDA(e, cudaMemcpyAsync(io->r_vel, e->a.r_vel, rows * D * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
     if (io->r_acc) TPB_CUDA(e, cudaMemcpyAsync(io->r_acc, e->a.r_acc, rows * D * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
@@ -662,7 +750,8 @@ int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
     if (io->r_sdd) TPB_CUDA(e, cudaMemcpyAsync(io->r_sdd, e->a.r_sdd, rows * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   }
   TPB_CUDA(e, cudaStreamSynchronize(e->stream));
-  return TPB_OK;
+  if (e->copy_stream) TPB_CUDA(e, cudaStreamSynchronize(e->copy_stream));
+  return rc;
 }
 
 int32_t tpb_get(tpb_engine* e, tpb_array what, void* dst, size_t bytes, int32_t to_device) {

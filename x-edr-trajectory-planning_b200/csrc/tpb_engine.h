@@ -115,8 +115,59 @@ int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safet
 int launch_generic_limit(const Dims& d, const DeviceArrays& a, cudaStream_t st);
 int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double safety,
                      int max_loops, cudaStream_t st);
+// continued: the batch is a chunk following another one; r_offset[0] already
+// holds the number of rows before it
 int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, double dt,
-                    int num_sms, cudaStream_t st);
+                    int num_sms, cudaStream_t st, bool continued = false);
+
+// The arrays of paths [b0, ...) of a joint-space batch: every per-path pointer
+// advanced by b0 paths (the packed r_* rows are addressed through r_offset and
+// stay where they are).  Used to run the stage kernels on a chunk of the batch.
+inline DeviceArrays shifted_joint(const DeviceArrays& a, const Dims& d, int b0) {
+  DeviceArrays s = a;
+  const size_t b = static_cast<size_t>(b0), N = d.N, D = d.D;
+  auto adv = [&](auto*& p, size_t stride) {
+    if (p) p += b * stride;
+  };
+  adv(s.waypoints, static_cast<size_t>(d.Wmax) * D);
+  adv(s.num_wp, 1);
+  adv(s.vmax, D);
+  adv(s.amax, D);
+  adv(s.delta_in, 1);
+  adv(s.path_start, 1);
+  adv(s.sd_start, 1);
+  adv(s.sdd_start, 1);
+  adv(s.time_start, 1);
+  adv(s.ctrl, static_cast<size_t>(d.max_points) * D);
+  adv(s.knots, static_cast<size_t>(d.max_points) + 3);
+  adv(s.num_points, 1);
+  adv(s.delta, 1);
+  adv(s.knot_end, 1);
+  adv(s.q, N * D);
+  adv(s.dq, N * D);
+  adv(s.ddq, N * D);
+  adv(s.b_raw_sd2_max, N);
+  adv(s.b_raw_sdd_max, N);
+  adv(s.b_raw_sdd_min, N);
+  adv(s.b_sd2_max, N);
+  adv(s.b_sdd_max, N);
+  adv(s.b_sdd_min, N);
+  adv(s.b_sd2_zero, N);
+  adv(s.b_at0, N);
+  adv(s.b_type, N);
+  adv(s.sd2, N);
+  adv(s.sdd, N);
+  adv(s.sd, N);
+  adv(s.s, N);
+  adv(s.time, N);
+  adv(s.fix_val, N);
+  adv(s.status, 1);
+  adv(s.last_extremal, 1);
+  adv(s.duration, 1);
+  adv(s.r_count, 1);
+  adv(s.r_offset, 1);
+  return s;
+}
 
 // Cartesian path (tpb_cartesian.cu); -1 = unsupported built-in model
 int launch_cart_fit(const Dims& d, const DeviceArrays& a, double rotation_rounding,

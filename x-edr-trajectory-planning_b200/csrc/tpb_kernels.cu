@@ -301,9 +301,11 @@ __global__ void k_resample_count(Dims dm, DeviceArrays a, double start_sec, doub
   a.r_count[b] = m;
 }
 
-// exclusive scan of r_count into r_offset (single block; B is at most ~1e6)
+// exclusive scan of r_count into r_offset (single block; B is at most ~1e6).
+// continued != 0: this batch is a chunk that follows another one, offset[0]
+// already holds the rows before it (the previous chunk's offset[B]).
 __global__ void k_scan_offsets(int B, const int32_t* __restrict__ count,
-                               int64_t* __restrict__ offset) {
+                               int64_t* __restrict__ offset, int continued) {
   __shared__ long long s_part[1024];
   const int tid = threadIdx.x;
   const int per = (B + blockDim.x - 1) / blockDim.x;
@@ -313,7 +315,7 @@ __global__ void k_scan_offsets(int B, const int32_t* __restrict__ count,
   s_part[tid] = sum;
   __syncthreads();
   if (tid == 0) {
-    long long run = 0;
+    long long run = continued ? offset[0] : 0;
     for (int i = 0; i < blockDim.x; ++i) {
       const long long v = s_part[i];
       s_part[i] = run;
@@ -514,10 +516,10 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
 }
 
 int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, double dt,
-                    int num_sms, cudaStream_t st) {
+                    int num_sms, cudaStream_t st, bool continued) {
   const int threads = 128;
   k_resample_count<<<(d.B + threads - 1) / threads, threads, 0, st>>>(d, a, start_sec, dt);
-  k_scan_offsets<<<1, 1024, 0, st>>>(d.B, a.r_count, a.r_offset);
+  k_scan_offsets<<<1, 1024, 0, st>>>(d.B, a.r_count, a.r_offset, continued ? 1 : 0);
   const size_t tile = sizeof(double) * (kResampleThreads / 32) * 3 * 32 * d.D;
   const size_t with_time = tile + sizeof(double) * d.N;
   const int grid = std::min(d.B, num_sms * 16);
