@@ -24,7 +24,7 @@ eng.set_joint_limits(vmax, amax)
 eng.sample_paths()
 for _ in range(3):
     eng.optimize()
-dbg = eng.get(pkg.ARR.DEBUG).reshape(B, N)[:, :16]
+dbg = eng.get(pkg.ARR.DEBUG).reshape(B, N)[:, :20]
 names = ["init", "boundary", "first_back", "first_fwd", "loop", "finalize"]
 ph = np.diff(dbg[:, :7], axis=1)
 tot = dbg[:, 6]
@@ -42,6 +42,8 @@ for k, n in ((10, "next_critical"), (11, "add_backward"), (12, "add_forward")):
 print("  loop steps backward mean %.0f forward mean %.0f; cycles/step bw %.0f fw %.0f" % (
     dbg[:, 13].mean(), dbg[:, 14].mean(), dbg[:, 11].sum() / max(dbg[:, 13].sum(), 1),
     dbg[:, 12].sum() / max(dbg[:, 14].sum(), 1)))
+print("  loop: sum of max(backward, forward) cycles mean %.0f (vs sum %.0f); all extremal steps mean %.0f max %d" % (
+    dbg[:, 15].mean(), (dbg[:, 11] + dbg[:, 12]).mean(), dbg[:, 16].mean(), dbg[:, 16].max()))
 start = dbg[:, 9] - dbg[:, 9].min()
 print("kernel span (cycles): %.0f; last start %.0f" % ((start + tot).max(), start.max()))
 worst = np.argsort(-tot)[:5]

@@ -116,26 +116,24 @@ struct GenericPolicy {
 };
 
 // kD = number of dofs (1..8), compile-time so that the candidate rounds unroll.
-// Padding lanes (d >= kD) carry A = B = aS = vS2 = 0: their row tests evaluate
-// 0*c + 0 against [-0, 0] with kTiny slack and can never fail (NaN compares
-// false), so no lane predicate is needed anywhere.
+// Padding lanes (d >= kD) hold a copy of row kD-1 and of its limits: a row tested
+// twice changes no outcome, so no lane predicate is needed anywhere, and the
+// copies keep real operands in the divisions (0/1 would take the slow path of
+// the double-precision division).
 template <int kD>
 struct Joint8Policy {
   struct Rows {
-    double A, B;  // q'_d, q''_d of one sample (0 for d >= kD)
+    double A, B;  // q'_d, q''_d of one sample (d >= kD: a copy of row kD-1)
   };
   int lane;
   int g, d;  // lane = 8*g + d
   const double *dq, *ddq;  // this path's rows, already offset by min(d, kD-1)
   double aS, vS2;  // amax_d*safety, (vmax_d*safety)^2 (row bounds: -aS..aS, 0..vS2)
-  bool active;     // d < kD
 
   __device__ __forceinline__ Rows load(int idx) const {
     Rows r;
-    const double a0 = dq[idx * kD];
-    const double b0 = ddq[idx * kD];
-    r.A = active ? a0 : 0.0;
-    r.B = active ? b0 : 0.0;
+    r.A = dq[idx * kD];
+    r.B = ddq[idx * kD];
     return r;
   }
 
@@ -169,10 +167,10 @@ struct Joint8Policy {
     const bool pos = r.A > 0.0;
     const bool plus = ((g & 1) == 0) ? (kMax == pos) : (kMax != pos);
     const double num = (plus ? aS : -aS) - Bs;
-    // rows without a candidate (|A| < kTiny, padding lanes) divide by 1 instead:
-    // x/0 would send the whole warp through the division's slow path
+    // rows without a candidate (|A| < kTiny) divide 1 by 1 instead: x/0 and 0/x
+    // would send the whole warp through the division's slow path
     const bool none = is_tiny(r.A);
-    const double cand = none ? quiet_nan() : num / (none ? 1.0 : r.A);
+    const double cand = none ? quiet_nan() : (none ? 1.0 : num) / (none ? 1.0 : r.A);
     const double vv = (r.A * r.A) * sd2v;
     const bool vbad = __ballot_sync(kFullMask, (vv + kTiny < 0.0) || (vv - kTiny > vS2)) != 0u;
     double best = kMax ? -DBL_MAX : DBL_MAX;
@@ -221,6 +219,9 @@ struct Solver {
   double ds;
   double *sd2, *sdd, *bmax, *bsmax, *bsmin, *bzero;
   uint8_t *at0, *type;
+#ifdef TPB_PROFILE_PHASES
+  int nsteps = 0;  // extremal steps taken (diagnostics)
+#endif
 
   __device__ __forceinline__ void st(double* ptr, double v) const {
     if (lane == 0) *ptr = v;
@@ -403,6 +404,9 @@ struct Solver {
       const double bnext_n = bmax[idx + 2];
       const uint8_t tnext_n = type[idx + 2];
       const double nxt_n = sd2[idx + 2];
+#ifdef TPB_PROFILE_PHASES
+      ++nsteps;
+#endif
 
       double sd2tmp, sddtmp;
       const bool on_boundary = is_tiny(cur - bcur);
@@ -466,6 +470,9 @@ struct Solver {
       const double bprev_n = bmax[idx - 2];
       const uint8_t tprev_n = type[idx - 2];
       const double prv_n = sd2[idx - 2];
+#ifdef TPB_PROFILE_PHASES
+      ++nsteps;
+#endif
 
       double sd2tmp, sddtmp;
       const bool on_boundary = is_tiny(cur - bcur);
@@ -512,11 +519,58 @@ struct Solver {
     return 0;
   }
 
+  // Lookup tables for NextCriticalPoint, built once after the boundary passes
+  // (type[] and sd2_max[] do not change afterwards):
+  //   next_src[i] = smallest j >= i whose type is Source or Trajectory, else N
+  //   prev_eq0[i] = largest j <= i with sd2_max[j] == sd2_max_for_sdd0[0], else -1
+  __device__ void build_critical_tables(int* next_src, int* prev_eq0) const {
+    const double bz0 = bzero[0];
+    int carry = N;
+    for (int base = ((N - 1) / 32) * 32; base >= 0; base -= 32) {
+      const int i = base + lane;
+      const bool f = (i < N) && ((type[i] & (kSource | kTrajectory)) != 0);
+      const unsigned m = __ballot_sync(kFullMask, f);
+      const unsigned mm = m & (~0u << lane);
+      if (i < N) next_src[i] = mm ? base + (__ffs(mm) - 1) : carry;
+      if (m) carry = base + (__ffs(m) - 1);
+    }
+    carry = -1;
+    for (int base = 0; base < N; base += 32) {
+      const int i = base + lane;
+      const bool f = (i < N) && (bmax[i] == bz0);
+      const unsigned m = __ballot_sync(kFullMask, f);
+      const unsigned mm = m & (~0u >> (31 - lane));
+      if (i < N) prev_eq0[i] = mm ? base + (31 - __clz(mm)) : carry;
+      if (m) carry = base + (31 - __clz(m));
+    }
+    __syncwarp();
+  }
+
+  // NextCriticalPoint (:697-720) in O(1).  The sequential scan (kept below as
+  // next_critical_scan, and cross-checked against this one in -DTPB_CHECK_SCAN
+  // builds) returns at the first sample, at or after the first Source/Trajectory
+  // sample q of (idx_lo, idx_hi], whose sd2 is set.  In the switching loop
+  // idx_lo is where the last forward extremal stopped and idx_hi the low end of
+  // the first backward extremal: sd2 is set on [0, idx_lo] and [idx_hi, N-1] and
+  // NaN strictly between (sweeps only ever extend the lower range upwards; the
+  // backward sweep from a critical point fills down to the lower range because a
+  // connecting sweep ends only on an intersection with set samples).  So the
+  // scan always ends at idx_hi, and returns the last sample of (q, idx_hi] on
+  // the sdd0 level if there is one, else q.
+  __device__ int next_critical(int idx_lo, int idx_hi, const int* next_src,
+                               const int* prev_eq0) const {
+    if (idx_lo + 1 > idx_hi) return -1;
+    const int q = next_src[idx_lo + 1];
+    if (q > idx_hi) return -1;
+    const int p2 = prev_eq0[idx_hi];
+    return (p2 > q) ? p2 : q;
+  }
+
   // NextCriticalPoint (:697-720), 32 samples per step via ballots.  Sequential
   // meaning: crit = first idx with a Source/Trajectory type; afterwards crit
   // moves to any idx with sd2_max[idx] == sd2_max_for_sdd0[0] (sic, index 0);
   // return crit at the first idx (at or after the first crit) whose sd2 is set.
-  __device__ int next_critical(int idx_lo, int idx_hi) const {
+  __device__ int next_critical_scan(int idx_lo, int idx_hi) const {
     int crit = -1;
     const double bz0 = bzero[0];
     for (int base = idx_lo + 1; base <= idx_hi; base += 32) {
@@ -604,23 +658,25 @@ __device__ __forceinline__ void init_policy(Joint8Policy<kD>& p, const Dims& dm,
   p.lane = lane;
   p.g = lane >> 3;
   p.d = lane & 7;
-  p.active = p.d < kD;
-  const int dd = p.active ? p.d : kD - 1;  // padding lanes read a valid address
+  const int dd = min(p.d, kD - 1);  // padding lanes copy the last row
   p.dq = a.dq + o * kD + dd;
   p.ddq = a.ddq + o * kD + dd;
-  p.aS = 0.0;
-  p.vS2 = 0.0;
-  bool bad = false;
-  if (p.active) {
-    p.aS = a.amax[static_cast<size_t>(b) * kD + p.d] * safety;
-    const double vs = a.vmax[static_cast<size_t>(b) * kD + p.d] * safety;
-    p.vS2 = vs * vs;
-    bad = (-p.aS >= p.aS) || (0.0 >= p.vS2);
-  }
+  p.aS = a.amax[static_cast<size_t>(b) * kD + dd] * safety;
+  const double vs = a.vmax[static_cast<size_t>(b) * kD + dd] * safety;
+  p.vS2 = vs * vs;
+  const bool bad = (-p.aS >= p.aS) || (0.0 >= p.vS2);
   if (__ballot_sync(kFullMask, bad)) *status = TPB_PATH_FAIL_SETUP;
 }
 
-template <class P, int kMinBlocks>
+// kPhases selects what one launch does: kPhaseSetup (SetSetupDone + boundary
+// passes 2-4), kPhaseOptimize (extremal sweeps + switching loop), kPhaseFinalize
+// (audits, intersection fill, time integration, outputs).  All state between
+// them lives in the per-path arrays and a.status[], so a phase can run in a
+// launch of its own (the two-paths-per-warp optimiser of tpb_integrate_pair.cuh
+// replaces kPhaseOptimize only).
+constexpr int kPhaseSetup = 1, kPhaseOptimize = 2, kPhaseFinalize = 4, kPhaseAll = 7;
+
+template <class P, int kMinBlocks, int kPhases = kPhaseAll>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, kMinBlocks)
 k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
   __shared__ double s_rows[std::is_same<P, GenericPolicy>::value ? kWarpsPerBlock * 4 * kMaxRows : 1];
@@ -650,7 +706,11 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
   double* sv = a.s + o;
   double* sd = a.sd + o;
   double* fix_val = a.fix_val + o;
-  int* fix_idx = reinterpret_cast<int*>(a.time + o);  // time[] is free until the end
+  // time[] is free until the end: first the fix list of the boundary passes, then
+  // the two NextCriticalPoint tables (N ints each)
+  int* fix_idx = reinterpret_cast<int*>(a.time + o);
+  int* next_src = fix_idx;
+  int* prev_eq0 = fix_idx + N;
 
   const double sd_start = a.sd_start[b];
   const double sdd_start = a.sdd_start[b];
@@ -666,12 +726,14 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
     s_end = a.s_end[b];
   }
   if (s_start >= s_end || sd_start < 0 || N < 2) status = TPB_PATH_FAIL_SETUP;
+  // a later phase of a split run continues with the status the earlier ones left
+  if ((kPhases & kPhaseSetup) == 0 && status == TPB_PATH_OK) status = a.status[b];
 
   int last_extremal = 0;
   const double nan = quiet_nan();
 #ifdef TPB_PROFILE_PHASES
   long long ph[8];
-  long long acc_nc = 0, acc_bw = 0, acc_fw = 0;
+  long long acc_nc = 0, acc_bw = 0, acc_fw = 0, acc_max = 0;
   int steps_bw = 0, steps_fw = 0;
   int nloops = 0;
   for (int k = 0; k < 8; ++k) ph[k] = 0;
@@ -687,6 +749,7 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
     // The per-sample limit curve is kept as computed (b_raw_*); passes 2-4 mutate
     // a working copy, so tpb_optimize can be repeated like the reference's
     // OptimizePathParameter (which recomputes the boundary).
+    if (kPhases & kPhaseSetup) {
     const double* raw_max = a.b_raw_sd2_max + o;
     const double* raw_smax = a.b_raw_sdd_max + o;
     const double* raw_smin = a.b_raw_sdd_min + o;
@@ -703,8 +766,10 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
     // ---- OptimizePathParameter (:287-490)
     TPB_STAMP(1);
     S.boundary_passes(fix_val, fix_idx);
+    S.build_critical_tables(next_src, prev_eq0);
     TPB_STAMP(2);
-
+    }
+    if (kPhases & kPhaseOptimize) {
     int iforw_lo = 0, iback_hi = N - 1, iback_lo, iforw_hi, icrit, icrit_lo, icrit_hi;
     iback_lo = S.add_backward(iback_hi);
     TPB_STAMP(3);
@@ -725,7 +790,13 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
 #ifdef TPB_PROFILE_PHASES
       const long long c0 = clock64();
 #endif
-      icrit = S.next_critical(icrit_lo, icrit_hi);
+      icrit = S.next_critical(icrit_lo, icrit_hi, next_src, prev_eq0);
+#ifdef TPB_CHECK_SCAN
+      if (icrit != S.next_critical_scan(icrit_lo, icrit_hi)) {
+        status = TPB_PATH_FAIL_INDEX;
+        break;
+      }
+#endif
 #ifdef TPB_PROFILE_PHASES
       acc_nc += clock64() - c0;
 #endif
@@ -743,18 +814,22 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
       }
 #ifdef TPB_PROFILE_PHASES
       const long long c1 = clock64();
+      const int n1 = S.nsteps;
 #endif
       iback_lo = S.add_backward(iback_hi);
 #ifdef TPB_PROFILE_PHASES
       const long long c2 = clock64();
+      const int n2 = S.nsteps;
       acc_bw += c2 - c1;
-      steps_bw += iback_hi - iback_lo;
+      steps_bw += n2 - n1;
 #endif
       iforw_lo = icrit;
       iforw_hi = S.add_forward(iforw_lo);
 #ifdef TPB_PROFILE_PHASES
-      acc_fw += clock64() - c2;
-      steps_fw += iforw_hi - iforw_lo;
+      const long long c3 = clock64();
+      acc_fw += c3 - c2;
+      steps_fw += S.nsteps - n2;
+      acc_max += (c3 - c2 > c2 - c1) ? (c3 - c2) : (c2 - c1);
 #endif
       if (iback_lo > icrit_lo) {
         status = TPB_PATH_FAIL_CONNECT;
@@ -762,8 +837,13 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
       }
       icrit_lo = iforw_hi;
     }
+    }
   }
   TPB_STAMP(5);
+  if ((kPhases & kPhaseFinalize) == 0) {
+    if (lane == 0) a.status[b] = status;
+    return;
+  }
   if (status == TPB_PATH_OK) {
     // NaN audit (:398-403)
     bool any_nan = false;
@@ -863,6 +943,8 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
     fix_val[12] = static_cast<double>(acc_fw);
     fix_val[13] = steps_bw;
     fix_val[14] = steps_fw;
+    fix_val[15] = static_cast<double>(acc_max);
+    fix_val[16] = S.nsteps;
   }
 #endif
 #undef TPB_STAMP

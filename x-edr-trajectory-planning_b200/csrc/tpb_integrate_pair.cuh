@@ -1,0 +1,423 @@
+// Stage C, the extremal sweeps and the switching-point loop, for joint-space
+// paths with D <= 8: TWO paths per warp (k_optimize_pair<D>), 16 lanes each.
+//
+// Same algorithm and the same results, bit for bit, as kPhaseOptimize of
+// k_integrate<Joint8Policy> (tpb_integrate.cuh; AddForwardExtremal /
+// AddBackwardExtremal time_optimal_path_timing.cc:769-952, the switching-point
+// loop :287-490, NextCriticalPoint :697-720 through the lookup tables the setup
+// phase leaves behind).  What changes is the mapping onto the warp:
+//
+//  * a half-warp (lanes 16h .. 16h+15) owns one path;
+//  * the sweeps are a per-half state machine that advances ONE extremal step
+//    per trip of a common loop.  The forward and the backward step are the same
+//    code with a direction sign, and FindSddMax / FindSddMin are one routine
+//    that maximises +-candidate (negation is exact).  Whatever the two paths are
+//    doing -- sweeping in opposite directions, at different samples -- the
+//    halves execute the same instructions, so one instruction stream times two
+//    paths;
+//  * every warp primitive in the step is issued by all 32 lanes with the full,
+//    compile-time mask (a per-half mask is not warp-uniform, and the compiler
+//    then serialises the two halves around every shuffle and vote): ballots are
+//    taken over the warp and each half reads its own 16 bits, shuffles use
+//    width 16, and the rare sub-steps (validity test at the limit curve,
+//    ComputeSddAtIntersection) are entered by the whole warp when either half
+//    needs them, with the side effects predicated.  Only the driver transitions
+//    between sweeps (a few dozen per path) diverge, and they use no primitives.
+//
+// Lane = 8*g + d within the half: d = acceleration row, g = 0 holds the row's
+// outer candidate (the larger one for FindSddMax, the smaller one for
+// FindSddMin), g = 1 the inner one.  See Joint8Policy for why testing the outer
+// candidates first is exact.
+#pragma once
+
+#include "tpb_device.cuh"
+#include "tpb_engine.h"
+
+namespace tpb {
+
+constexpr int kPairWarpsPerBlock = 4;  // 8 paths per CTA
+
+template <int kD>
+struct PairSolver {
+  struct Rows {
+    double A, B;  // q'_d, q''_d of one sample (d >= kD: a copy of row kD-1)
+  };
+  // lane geometry
+  int lane;     // 0..15 within the half
+  int g, d;     // lane = 8*g + d
+  int shift;    // 0 or 16: position of the half in a warp ballot
+  // this half's path
+  // Padding lanes (d >= kD) hold a copy of row kD-1 and of its limits: a row
+  // tested twice changes no outcome, and the copies keep real operands in the
+  // divisions (0/1 would take the slow path of the double-precision division).
+  const double *dq, *ddq;  // rows, already offset by min(d, kD-1)
+  double aS, vS2;          // amax_d*safety, (vmax_d*safety)^2
+  int N;
+  double ds;
+  double *sd2, *sdd;
+  const double* bmax;
+  const uint8_t* type;
+  const int *next_src, *prev_eq0;  // Solver::build_critical_tables
+
+  // This half's 16 bits of a warp-wide ballot.  Convergent: all 32 lanes.
+  __device__ __forceinline__ unsigned ballot(bool pred) const {
+    return (__ballot_sync(kFullMask, pred) >> shift) & 0xffffu;
+  }
+  __device__ __forceinline__ static bool any(bool pred) {
+    return __any_sync(kFullMask, pred);
+  }
+  __device__ __forceinline__ int clampi(int i) const { return min(max(i, 0), N - 1); }
+
+  __device__ __forceinline__ Rows load(int idx) const {
+    Rows r;
+    r.A = dq[idx * kD];
+    r.B = ddq[idx * kD];
+    return r;
+  }
+
+  // AreDerivativesValid (:624-636); see Joint8Policy::valid.  Convergent.
+  __device__ __forceinline__ bool valid(const Rows& r, double sddv, double sd2v) const {
+    const double v = r.A * sddv + r.B * sd2v;
+    bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
+    const double w = 0.0 * sddv + (r.A * r.A) * sd2v;
+    bad = bad || (w + kTiny < 0.0) || (w - kTiny > vS2);
+    return ballot(bad) == 0u;
+  }
+
+  // FindSddMax (want_max) / FindSddMin (:638-695): maximise key = +-candidate.
+  // Convergent; want_max and the data are per half.
+  __device__ __forceinline__ double find_sdd(const Rows& r, double sd2v, bool want_max) const {
+    const double Bs = r.B * sd2v;
+    const bool pos = r.A > 0.0;
+    const bool plus = (g == 0) ? (want_max == pos) : (want_max != pos);
+    const double num = (plus ? aS : -aS) - Bs;
+    // rows without a candidate divide 1 by 1: x/0 and 0/x leave the fast path
+    const bool none = is_tiny(r.A);
+    const double cand = none ? quiet_nan() : (none ? 1.0 : num) / (none ? 1.0 : r.A);
+    const double vv = (r.A * r.A) * sd2v;
+    const bool vbad = ballot((vv + kTiny < 0.0) || (vv - kTiny > vS2)) != 0u;
+    double best = -DBL_MAX;  // of the keys
+    auto round = [&](int row, int src_group) {
+      const double c = __shfl_sync(kFullMask, cand, (src_group << 3) | (row & 7), 16);
+      const double v = r.A * c + Bs;
+      const bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
+      const unsigned m = ballot(bad);
+      const bool ok = (row < kD) && (c == c) && (((m >> (8 * g)) & 0xffu) == 0u);
+      const double key = want_max ? c : -c;
+      best = (ok && key > best) ? key : best;
+    };
+    auto reduce = [&]() {
+      const double w = __shfl_xor_sync(kFullMask, best, 8, 16);
+      best = (w > best) ? w : best;
+    };
+#pragma unroll
+    for (int j0 = 0; j0 < kD; j0 += 2) round(j0 + g, 0);
+    reduce();
+    // Inner candidates only matter to a half where one lies beyond its best outer
+    // one; testing them in the other half as well changes nothing there (none of
+    // its inner keys exceeds its best).
+    const double mykey = want_max ? cand : -cand;
+    const bool beyond = (g == 1) && (cand == cand) && (mykey > best);
+    if (any(beyond)) {
+#pragma unroll
+      for (int j0 = 0; j0 < kD; j0 += 2) round(j0 + g, 1);
+      reduce();
+    }
+    if (vbad || best == -DBL_MAX) return 0.0;
+    return want_max ? best : -best;
+  }
+
+  // ComputeSddAtIntersection (:722-751).  Convergent; stores only where `on`.
+  // The reference tries up to three candidates in order and keeps the first
+  // valid one; all three are tested here and the first valid one selected.
+  __device__ __forceinline__ void sdd_at_intersection(int index, const Rows& rows, bool on) {
+    const bool has_hi = index < N - 1, has_lo = index > 0;
+    const double sp = sd2[clampi(index + 1)];
+    const double sm = sd2[clampi(index - 1)];
+    const double here = sd2[index];
+    const double c1 = 0.25 / ds * (sp - sm);
+    const double c2 = 0.5 / ds * (sp - here);
+    const double c3 = 0.5 / ds * (here - sm);
+    const bool v1 = valid(rows, c1, here);
+    const bool v2 = valid(rows, c2, here);
+    const bool v3 = valid(rows, c3, here);
+    double r = 0.0;
+    if (has_lo && v3) r = c3;
+    if (has_hi && v2) r = c2;
+    if (has_lo && has_hi && v1) r = c1;
+    if (on && lane == 0) sdd[index] = r;
+    __syncwarp();
+  }
+
+  // -------------------------------------------------------------------------
+  // Per-half state machine: OptimizePathParameter (:287-490) unrolled into
+  // sweeps that advance one extremal step per trip.
+  // -------------------------------------------------------------------------
+  enum : int { kFirstBack = 0, kFirstFwd = 1, kLoopBack = 2, kLoopFwd = 3 };
+  bool sweeping;  // a sweep is in progress (false: this half is done or idle)
+  int stage, status;
+  // sweep state (AddForwardExtremal :769-857 / AddBackwardExtremal :859-952)
+  int dir, idx;
+  bool connecting;
+  double cur, bcur, bnb, nb;  // sd2[idx], sd2_max[idx], sd2_max[idx+dir], sd2[idx+dir]
+  uint8_t tcur, tnb;
+  Rows rows;
+  // driver state
+  int iforw_hi, iback_lo, iback_hi, icrit, icrit_lo, icrit_hi, loop, max_loops;
+
+  // A store the same half reads back later in the same (divergent) transition:
+  // every lane writes the same value and each then reads its own write.
+  __device__ __forceinline__ void st_all(double* ptr, double v) const { *ptr = v; }
+
+  // Starts a sweep at sample `start`.  Returns true (and the sweep's return value
+  // in *ret) when the reference's early-out applies, so no step is needed.
+  __device__ __forceinline__ bool begin_sweep(int direction, int start, int* ret) {
+    dir = direction;
+    if (direction > 0) {
+      if (start >= N - 2) {
+        *ret = N - 1;
+        return true;
+      }
+    } else {
+      if (start <= 1) {
+        *ret = 0;
+        return true;
+      }
+    }
+    idx = start;
+    cur = sd2[start];
+    bcur = bmax[start];
+    tcur = type[start];
+    rows = load(start);
+    bnb = bmax[start + direction];
+    tnb = type[start + direction];
+    nb = sd2[start + direction];
+    connecting = (direction < 0) && (start != (N - 1));
+    return false;
+  }
+
+  // One iteration of the extremal loop in direction dir, for the halves with
+  // `live` set.  Convergent.  Returns true (to a live half) when its sweep has
+  // ended, with the sweep's return value in *ret.
+  __device__ __forceinline__ bool sweep_step(bool live, int* ret) {
+    const bool fwd = dir > 0;
+    const bool at_end = fwd ? !(idx < N - 2) : !(idx > 1);
+    bool run = live && !at_end;
+    bool ended = live && at_end;
+    int r = fwd ? N - 1 : 0;
+    // data of the step after this one (clamped: a half that is not running may
+    // sit at either end)
+    const int i1 = clampi(idx + dir), i2 = clampi(idx + 2 * dir);
+    const Rows rows_n = load(i1);
+    const double bnb_n = bmax[i2];
+    const uint8_t tnb_n = type[i2];
+    const double nb_n = sd2[i2];
+
+    const double sgn = fwd ? 1.0 : -1.0;
+    const bool on_boundary = is_tiny(cur - bcur);
+    const bool follow = on_boundary && (tcur & kTrajectory) && (tnb & kTrajectory);
+    double f = 0.0;
+    if (any(run && !follow)) f = find_sdd(rows, cur, fwd);
+    double sd2tmp, sddtmp;
+    if (follow) {
+      sd2tmp = bnb;
+      // fwd: 0.5*(sd2tmp - cur)/ds, bwd: 0.5*(cur - sd2tmp)/ds; operands are
+      // swapped rather than the difference negated so that a zero keeps its sign
+      sddtmp = 0.5 * ((fwd ? sd2tmp : cur) - (fwd ? cur : sd2tmp)) / ds;
+    } else {
+      sddtmp = f;
+      sd2tmp = cur + sgn * (2.0 * ds * sddtmp);  // fwd: cur + 2ds*sdd, bwd: cur - 2ds*sdd
+    }
+    const bool isect = run && !(nb != nb) && (nb < sd2tmp);
+    if (any(isect)) sdd_at_intersection(idx, rows, isect);
+    if (isect) {
+      ended = true;
+      run = false;
+    }
+    const bool over = run && (sd2tmp > bnb);
+    if (any(over)) {
+      const double sdd_bound = 0.5 * ((fwd ? bnb : cur) - (fwd ? cur : bnb)) / ds;
+      const bool deriv_invalid = !valid(rows, sdd_bound, fwd ? bcur : cur);
+      if (over) {
+        const bool type_invalid = tnb & (fwd ? kSink : kSource);
+        if ((type_invalid || deriv_invalid) && !connecting) {
+          ended = true;
+          run = false;
+          r = idx;
+        } else {
+          sd2tmp = bnb;
+          sddtmp = sdd_bound;
+        }
+      }
+    }
+    if (run && sd2tmp < 0) {
+      sd2tmp = 0.0;
+      if (fwd) {
+        sddtmp = (idx <= 1) ? 0.0 : -sd2[idx - 1] / ds;
+      } else {
+        sddtmp = (idx < N - 1) ? sd2[idx + 1] / ds : 0.0;
+      }
+    }
+    if (run && lane == 0) {
+      sd2[idx + dir] = sd2tmp;
+      sdd[idx] = sddtmp;
+    }
+    __syncwarp();
+    if (run) {
+      cur = sd2tmp;
+      bcur = bnb;
+      tcur = tnb;
+      rows = rows_n;
+      bnb = bnb_n;
+      tnb = tnb_n;
+      nb = nb_n;
+      idx += dir;
+    }
+    *ret = r;
+    return ended;
+  }
+
+  // NextCriticalPoint (:697-720); see Solver::next_critical
+  __device__ __forceinline__ int next_critical(int idx_lo, int idx_hi) const {
+    if (idx_lo + 1 > idx_hi) return -1;
+    const int q = next_src[idx_lo + 1];
+    if (q > idx_hi) return -1;
+    const int p2 = prev_eq0[idx_hi];
+    return (p2 > q) ? p2 : q;
+  }
+
+  // Driver transitions (:300-396).  Called by a half whose sweep has ended with
+  // value `ret`; runs until the next sweep that needs stepping, or to the end.
+  // Divergent between the halves: plain loads and stores only.
+  __device__ void advance(int ret) {
+    for (;;) {
+      if (stage == kFirstBack) {
+        iback_lo = ret;
+        stage = kFirstFwd;
+        if (!begin_sweep(+1, 0, &ret)) return;
+        continue;
+      }
+      if (stage == kLoopBack) {
+        iback_lo = ret;
+        stage = kLoopFwd;
+        if (!begin_sweep(+1, icrit, &ret)) return;
+        continue;
+      }
+      if (stage == kFirstFwd) {
+        iforw_hi = ret;
+        icrit_hi = iback_lo;
+        if ((iforw_hi < icrit_hi) && ((icrit_hi < N - 2) && (icrit_hi >= 2))) {
+          st_all(&sd2[icrit_hi], quiet_nan());
+          icrit_hi++;
+          iback_lo++;
+        }
+        icrit_lo = iforw_hi;
+        loop = 0;
+      } else {  // kLoopFwd
+        iforw_hi = ret;
+        if (iback_lo > icrit_lo) {
+          status = TPB_PATH_FAIL_CONNECT;
+          sweeping = false;
+          return;
+        }
+        icrit_lo = iforw_hi;
+        ++loop;
+      }
+      // top of the switching loop (:345-352)
+      if (loop >= max_loops || iforw_hi >= icrit_hi) {
+        sweeping = false;
+        return;
+      }
+      icrit = next_critical(icrit_lo, icrit_hi);
+      if (icrit < 0 || icrit >= N) icrit = static_cast<int>(0.5 * (icrit_lo + icrit_hi));
+      if (icrit > 0 && icrit < N - 1) st_all(&sd2[icrit], bmax[icrit]);
+      if (icrit < 1) {
+        status = TPB_PATH_FAIL_INDEX;
+        sweeping = false;
+        return;
+      }
+      if (bmax[icrit - 1] <= bmax[icrit]) {
+        iback_hi = icrit - 1;
+        st_all(&sd2[icrit - 1], bmax[icrit - 1]);
+      } else {
+        iback_hi = icrit;
+      }
+      stage = kLoopBack;
+      if (!begin_sweep(-1, iback_hi, &ret)) return;
+    }
+  }
+
+  // Runs both sweeps and the switching-point loop of this half's path to the
+  // end, in lock step with the other half (go = false: nothing to do, idle).
+  __device__ void run(bool go) {
+    // an idle half still executes every step: keep its state addressable
+    sweeping = false;
+    dir = 1;
+    idx = 0;
+    connecting = false;
+    cur = bcur = bnb = nb = 0.0;
+    tcur = tnb = kNone;
+    rows.A = rows.B = 0.0;
+    if (go) {
+      stage = kFirstBack;
+      sweeping = true;
+      int ret = 0;
+      if (begin_sweep(-1, N - 1, &ret)) advance(ret);
+    }
+    __syncwarp();
+    while (any(sweeping)) {
+      int ret = 0;
+      const bool ended = sweep_step(sweeping, &ret);
+      if (ended) advance(ret);
+      __syncwarp();
+    }
+  }
+};
+
+// Phase kPhaseOptimize for two paths per warp.  Runs between
+// k_integrate<Joint8Policy<kD>, ., kPhaseSetup> and <., ., kPhaseFinalize>.
+template <int kD>
+__global__ void __launch_bounds__(kPairWarpsPerBlock * 32, 4)
+k_optimize_pair(Dims dm, DeviceArrays a, double safety, int max_loops) {
+  const int warp = threadIdx.x >> 5;
+  const int half = (threadIdx.x >> 4) & 1;
+  const int lane = threadIdx.x & 15;
+  const int b = (blockIdx.x * kPairWarpsPerBlock + warp) * 2 + half;
+  const bool has_path = b < dm.B;
+  const int bb = has_path ? b : 0;  // an absent half computes on path 0 and stores nothing
+  const int N = dm.N;
+  const size_t o = static_cast<size_t>(bb) * N;
+
+  PairSolver<kD> S;
+  S.lane = lane;
+  S.g = lane >> 3;
+  S.d = lane & 7;
+  S.shift = half * 16;
+  const int dd = min(S.d, kD - 1);  // padding lanes copy the last row
+  S.dq = a.dq + o * kD + dd;
+  S.ddq = a.ddq + o * kD + dd;
+  S.N = N;
+  S.sd2 = a.sd2 + o;
+  S.sdd = a.sdd + o;
+  S.bmax = a.b_sd2_max + o;
+  S.type = a.b_type + o;
+  S.next_src = reinterpret_cast<const int*>(a.time + o);
+  S.prev_eq0 = S.next_src + N;
+  S.max_loops = max_loops;
+  S.aS = a.amax[static_cast<size_t>(bb) * kD + dd] * safety;
+  const double vs = a.vmax[static_cast<size_t>(bb) * kD + dd] * safety;
+  S.vS2 = vs * vs;
+  S.status = has_path ? a.status[bb] : TPB_PATH_FAIL_SETUP;
+  const bool go = S.status == TPB_PATH_OK;
+  // SetSetupDone (:535-552), as in the setup phase
+  S.ds = 1.0;
+  if (go) {
+    const double s_start = a.path_start[bb];
+    const double s_end = s_start + a.delta[bb] * (N - 1);
+    S.ds = (s_end - s_start) / (N - 1);
+  }
+  S.run(go);
+  if (go && lane == 0) a.status[b] = S.status;
+}
+
+}  // namespace tpb

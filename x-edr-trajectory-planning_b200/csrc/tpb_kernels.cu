@@ -12,11 +12,14 @@
 //  k_resample_*           trajectory assembly + ResampleEquidistantlyInTime
 //                         (path_timing_trajectory.cc:458-472, :686-783)
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
 #include <type_traits>
 
 #include "tpb_engine.h"
 #include "tpb_fit.cuh"
 #include "tpb_integrate.cuh"
+#include "tpb_integrate_pair.cuh"
 #include "tpb_joint_limit.cuh"
 #include "tpb_solver.cuh"
 
@@ -501,7 +504,31 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
                      int max_loops, cudaStream_t st) {
   const int blocks = (d.B + kWarpsPerBlock - 1) / kWarpsPerBlock;
   const bool joint = mode == Mode::kJoint;
-  if (joint && d.D <= 8) {
+  // TPB_INTEGRATE=warp selects the one-path-per-warp kernel (read once).
+  static const bool use_pair = []() {
+    const char* e = std::getenv("TPB_INTEGRATE");
+    return !(e && std::strcmp(e, "warp") == 0);
+  }();
+  if (joint && d.D <= 8 && use_pair) {
+    // setup and finalize one warp per path, the sweeps two paths per warp
+    const int threads = kWarpsPerBlock * 32;
+    const int per_block = kPairWarpsPerBlock * 2;
+    const int pblocks = (d.B + per_block - 1) / per_block;
+    const int pthreads = kPairWarpsPerBlock * 32;
+#define TPB_P8(K)                                                                          \
+  case K:                                                                                  \
+    k_integrate<Joint8Policy<K>, 7, kPhaseSetup><<<blocks, threads, 0, st>>>(d, a, true, safety, \
+                                                                             max_loops);   \
+    k_optimize_pair<K><<<pblocks, pthreads, 0, st>>>(d, a, safety, max_loops);             \
+    k_integrate<Joint8Policy<K>, 7, kPhaseFinalize><<<blocks, threads, 0, st>>>(           \
+        d, a, true, safety, max_loops);                                                    \
+    break
+    switch (d.D) {
+      TPB_P8(1); TPB_P8(2); TPB_P8(3); TPB_P8(4); TPB_P8(5); TPB_P8(6); TPB_P8(7); TPB_P8(8);
+    }
+#undef TPB_P8
+    return 3;
+  } else if (joint && d.D <= 8) {
     const int threads = kWarpsPerBlock * 32;
 #define TPB_J8(K) \
   case K: k_integrate<Joint8Policy<K>, 7><<<blocks, threads, 0, st>>>(d, a, true, safety, max_loops); break
