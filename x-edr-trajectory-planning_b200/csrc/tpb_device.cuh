@@ -31,6 +31,26 @@ __device__ __forceinline__ double quiet_nan() {
 }
 __device__ __forceinline__ bool is_tiny(double v) { return fabs(v) < kTiny; }
 
+// num / den where the quotient is only used when !skip.  Lanes with skip set
+// divide 1 by 1 instead: x/0, 0/x and other special operands send the whole warp
+// through the slow path of the double-precision division.  The empty asm keeps
+// the compiler from folding the guard into the select that discards the result.
+__device__ __forceinline__ double guarded_div(bool skip, double num, double den) {
+  double n = skip ? 1.0 : num;
+  double d = skip ? 1.0 : den;
+  asm("" : "+d"(n), "+d"(d));
+  return n / d;
+}
+
+// x / d for a positive, normal d.  A zero numerator (a flat stretch of the limit
+// curve, zero velocity at a path end) would take the division's slow path; the
+// quotient is x itself then, sign included.
+__device__ __forceinline__ double div_pos(double x, double d) {
+  const bool zero = x == 0.0;
+  const double q = guarded_div(zero, x, d);
+  return zero ? x : q;
+}
+
 __device__ __forceinline__ double warp_max(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {

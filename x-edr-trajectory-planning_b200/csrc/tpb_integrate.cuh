@@ -170,7 +170,11 @@ struct Joint8Policy {
     // rows without a candidate (|A| < kTiny) divide 1 by 1 instead: x/0 and 0/x
     // would send the whole warp through the division's slow path
     const bool none = is_tiny(r.A);
-    const double cand = none ? quiet_nan() : (none ? 1.0 : num) / (none ? 1.0 : r.A);
+    // a row exactly on its limit (num == 0, common on the limit curve) yields a
+    // zero with the quotient's sign: num * A
+    const bool zero = num == 0.0;
+    const double quot = guarded_div(none || zero, num, r.A);
+    const double cand = none ? quiet_nan() : (zero ? num * r.A : quot);
     const double vv = (r.A * r.A) * sd2v;
     const bool vbad = __ballot_sync(kFullMask, (vv + kTiny < 0.0) || (vv - kTiny > vS2)) != 0u;
     double best = kMax ? -DBL_MAX : DBL_MAX;
@@ -290,7 +294,7 @@ struct Solver {
     }
     int nwork = 0;
     auto test = [&](int i, double bm, double bi, double bp) {
-      const double sd2p = (bp - bi) / ds;
+      const double sd2p = div_pos(bp - bi, ds);
       const double smax_i = bsmax[i];
       const bool sink_or_source = (sd2p < 2 * bsmin[i]) || (sd2p > 2 * smax_i);
       const bool skipped_sdd = (smax_i > 0) && (bsmin[i + 1] < 0);
@@ -372,7 +376,7 @@ struct Solver {
     }
     // classification (:1453-1484), lane-parallel
     for (int i = 1 + lane; i < N - 1; i += 32) {
-      const double sd2p = (bmax[i + 1] - bmax[i]) / ds;
+      const double sd2p = div_pos(bmax[i + 1] - bmax[i], ds);
       const double sd2p_min = 2 * bsmin[i];
       const double sd2p_max = 2 * bsmax[i];
       uint8_t t = kNone;
@@ -412,7 +416,7 @@ struct Solver {
       const bool on_boundary = is_tiny(cur - bcur);
       if (on_boundary && (tcur & kTrajectory) && (tnext & kTrajectory)) {
         sd2tmp = bnext;
-        sddtmp = 0.5 * (sd2tmp - cur) / ds;
+        sddtmp = div_pos(0.5 * (sd2tmp - cur), ds);
       } else {
         sddtmp = p.template find_sdd<true>(rows, cur);
         sd2tmp = cur + 2.0 * ds * sddtmp;
@@ -422,7 +426,7 @@ struct Solver {
         return N - 1;
       }
       if (sd2tmp > bnext) {
-        const double sdd_bound = 0.5 * (bnext - cur) / ds;
+        const double sdd_bound = div_pos(0.5 * (bnext - cur), ds);
         const bool deriv_invalid = !p.valid(rows, sdd_bound, bcur);
         const bool type_invalid = tnext & kSink;
         if (type_invalid || deriv_invalid) return idx;
@@ -434,7 +438,7 @@ struct Solver {
         if (idx <= 1) {
           sddtmp = 0.0;
         } else {
-          sddtmp = -sd2[idx - 1] / ds;
+          sddtmp = div_pos(-sd2[idx - 1], ds);
         }
       }
       if (lane == 0) {
@@ -478,7 +482,7 @@ struct Solver {
       const bool on_boundary = is_tiny(cur - bcur);
       if (on_boundary && (tcur & kTrajectory) && (tprev & kTrajectory)) {
         sd2tmp = bprev;
-        sddtmp = 0.5 * (cur - sd2tmp) / ds;
+        sddtmp = div_pos(0.5 * (cur - sd2tmp), ds);
       } else {
         sddtmp = p.template find_sdd<false>(rows, cur);
         sd2tmp = cur - 2.0 * ds * sddtmp;
@@ -488,7 +492,7 @@ struct Solver {
         return 0;
       }
       if (sd2tmp > bprev) {
-        const double sdd_bound = 0.5 * (cur - bprev) / ds;
+        const double sdd_bound = div_pos(0.5 * (cur - bprev), ds);
         const bool deriv_invalid = !p.valid(rows, sdd_bound, cur);
         const bool type_invalid = tprev & kSource;
         if ((type_invalid || deriv_invalid) && !is_connecting) return idx;
@@ -498,7 +502,7 @@ struct Solver {
       if (sd2tmp < 0) {
         sd2tmp = 0.0;
         if (idx < N - 1) {
-          sddtmp = sd2[idx + 1] / ds;
+          sddtmp = div_pos(sd2[idx + 1], ds);
         } else {
           sddtmp = 0.0;
         }

@@ -93,7 +93,11 @@ struct PairSolver {
     const double num = (plus ? aS : -aS) - Bs;
     // rows without a candidate divide 1 by 1: x/0 and 0/x leave the fast path
     const bool none = is_tiny(r.A);
-    const double cand = none ? quiet_nan() : (none ? 1.0 : num) / (none ? 1.0 : r.A);
+    // a row exactly on its limit (num == 0, common on the limit curve) yields a
+    // zero with the quotient's sign: num * A
+    const bool zero = num == 0.0;
+    const double quot = guarded_div(none || zero, num, r.A);
+    const double cand = none ? quiet_nan() : (zero ? num * r.A : quot);
     const double vv = (r.A * r.A) * sd2v;
     const bool vbad = ballot((vv + kTiny < 0.0) || (vv - kTiny > vS2)) != 0u;
     double best = -DBL_MAX;  // of the keys
@@ -223,7 +227,7 @@ struct PairSolver {
       sd2tmp = bnb;
       // fwd: 0.5*(sd2tmp - cur)/ds, bwd: 0.5*(cur - sd2tmp)/ds; operands are
       // swapped rather than the difference negated so that a zero keeps its sign
-      sddtmp = 0.5 * ((fwd ? sd2tmp : cur) - (fwd ? cur : sd2tmp)) / ds;
+      sddtmp = div_pos(0.5 * ((fwd ? sd2tmp : cur) - (fwd ? cur : sd2tmp)), ds);
     } else {
       sddtmp = f;
       sd2tmp = cur + sgn * (2.0 * ds * sddtmp);  // fwd: cur + 2ds*sdd, bwd: cur - 2ds*sdd
@@ -236,7 +240,7 @@ struct PairSolver {
     }
     const bool over = run && (sd2tmp > bnb);
     if (any(over)) {
-      const double sdd_bound = 0.5 * ((fwd ? bnb : cur) - (fwd ? cur : bnb)) / ds;
+      const double sdd_bound = div_pos(0.5 * ((fwd ? bnb : cur) - (fwd ? cur : bnb)), ds);
       const bool deriv_invalid = !valid(rows, sdd_bound, fwd ? bcur : cur);
       if (over) {
         const bool type_invalid = tnb & (fwd ? kSink : kSource);
@@ -253,9 +257,9 @@ struct PairSolver {
     if (run && sd2tmp < 0) {
       sd2tmp = 0.0;
       if (fwd) {
-        sddtmp = (idx <= 1) ? 0.0 : -sd2[idx - 1] / ds;
+        sddtmp = (idx <= 1) ? 0.0 : div_pos(-sd2[idx - 1], ds);
       } else {
-        sddtmp = (idx < N - 1) ? sd2[idx + 1] / ds : 0.0;
+        sddtmp = (idx < N - 1) ? div_pos(sd2[idx + 1], ds) : 0.0;
       }
     }
     if (run && lane == 0) {
