@@ -39,9 +39,6 @@ constexpr int kPairWarpsPerBlock = 4;  // 8 paths per CTA
 
 template <int kD>
 struct PairSolver {
-  struct Rows {
-    double A, B;  // q'_d, q''_d of one sample (d >= kD: a copy of row kD-1)
-  };
   // lane geometry
   int lane;     // 0..15 within the half
   int g, d;     // lane = 8*g + d
@@ -68,47 +65,49 @@ struct PairSolver {
   }
   __device__ __forceinline__ int clampi(int i) const { return min(max(i, 0), N - 1); }
 
-  __device__ __forceinline__ Rows load(int idx) const {
-    Rows r;
-    r.A = dq[idx * kD];
-    r.B = ddq[idx * kD];
-    return r;
-  }
+  // The sweeps work in "key space": with sgn = +1 for a forward and -1 for a
+  // backward sweep, rows carry Ak = sgn * q'_d and accelerations are handled as
+  // k = sgn * sdd.  Sign flips are exact, so  A*sdd == Ak*k,  (+-aS - Bs)/A ==
+  // sgn * ((+-aS - Bs)/Ak), and FindSddMin(sdd) becomes FindSddMax(k): one search
+  // routine and one step routine serve both directions without selects.
 
-  // AreDerivativesValid (:624-636); see Joint8Policy::valid.  Convergent.
-  __device__ __forceinline__ bool valid(const Rows& r, double sddv, double sd2v) const {
-    const double v = r.A * sddv + r.B * sd2v;
+  // AreDerivativesValid (:624-636) for sdd = sgn * k; see Joint8Policy::valid.
+  // Convergent.
+  __device__ __forceinline__ bool valid_k(double Ak, double B, double k, double sd2v) const {
+    const double v = Ak * k + B * sd2v;
     bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
-    const double w = 0.0 * sddv + (r.A * r.A) * sd2v;
+    const double w = 0.0 * k + (Ak * Ak) * sd2v;
     bad = bad || (w + kTiny < 0.0) || (w - kTiny > vS2);
     return ballot(bad) == 0u;
   }
 
-  // FindSddMax (want_max) / FindSddMin (:638-695): maximise key = +-candidate.
-  // Convergent; want_max and the data are per half.
-  __device__ __forceinline__ double find_sdd(const Rows& r, double sd2v, bool want_max) const {
-    const double Bs = r.B * sd2v;
-    const bool pos = r.A > 0.0;
-    const bool plus = (g == 0) ? (want_max == pos) : (want_max != pos);
+  // FindSddMax / FindSddMin (:638-695) as the maximum valid k.  *none_valid
+  // tells that no candidate passed (the reference then returns 0.0).
+  // Convergent; the data are per half.
+  __device__ __forceinline__ double find_k(double Ak, double B, double sd2v,
+                                           bool* none_valid) const {
+    const double Bs = B * sd2v;
+    const bool plus = (g == 0) == (Ak > 0.0);  // g = 0: the row's larger candidate
     const double num = (plus ? aS : -aS) - Bs;
-    // rows without a candidate divide 1 by 1: x/0 and 0/x leave the fast path
-    const bool none = is_tiny(r.A);
-    // a row exactly on its limit (num == 0, common on the limit curve) yields a
-    // zero with the quotient's sign: num * A
+    // rows without a candidate divide 1 by 1 (x/0 and 0/x leave the division's
+    // fast path); a row exactly on its limit (num == 0, common on the limit
+    // curve) yields a zero with the quotient's sign: num * Ak
+    const bool none = is_tiny(Ak);
     const bool zero = num == 0.0;
-    const double quot = guarded_div(none || zero, num, r.A);
-    const double cand = none ? quiet_nan() : (zero ? num * r.A : quot);
-    const double vv = (r.A * r.A) * sd2v;
+    const double quot = guarded_div(none || zero, num, Ak);
+    const double cand = none ? quiet_nan() : (zero ? num * Ak : quot);
+    const double vv = (Ak * Ak) * sd2v;
     const bool vbad = ballot((vv + kTiny < 0.0) || (vv - kTiny > vS2)) != 0u;
-    double best = -DBL_MAX;  // of the keys
+    double best = -DBL_MAX;
+    const unsigned gmask = 0xffu << (shift + 8 * g);  // this group's rows in a warp ballot
     auto round = [&](int row, int src_group) {
       const double c = __shfl_sync(kFullMask, cand, (src_group << 3) | (row & 7), 16);
-      const double v = r.A * c + Bs;
+      const double v = Ak * c + Bs;
       const bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
-      const unsigned m = ballot(bad);
-      const bool ok = (row < kD) && (c == c) && (((m >> (8 * g)) & 0xffu) == 0u);
-      const double key = want_max ? c : -c;
-      best = (ok && key > best) ? key : best;
+      const unsigned m = __ballot_sync(kFullMask, bad);
+      // NaN marks "no candidate" and fails c > best
+      const bool ok = (row < kD) && ((m & gmask) == 0u);
+      best = (ok && c > best) ? c : best;
     };
     auto reduce = [&]() {
       const double w = __shfl_xor_sync(kFullMask, best, 8, 16);
@@ -119,22 +118,22 @@ struct PairSolver {
     reduce();
     // Inner candidates only matter to a half where one lies beyond its best outer
     // one; testing them in the other half as well changes nothing there (none of
-    // its inner keys exceeds its best).
-    const double mykey = want_max ? cand : -cand;
-    const bool beyond = (g == 1) && (cand == cand) && (mykey > best);
+    // its inner candidates exceeds its best).
+    const bool beyond = (g == 1) && (cand > best);
     if (any(beyond)) {
 #pragma unroll
       for (int j0 = 0; j0 < kD; j0 += 2) round(j0 + g, 1);
       reduce();
     }
-    if (vbad || best == -DBL_MAX) return 0.0;
-    return want_max ? best : -best;
+    *none_valid = vbad || best == -DBL_MAX;
+    return best;
   }
 
   // ComputeSddAtIntersection (:722-751).  Convergent; stores only where `on`.
   // The reference tries up to three candidates in order and keeps the first
   // valid one; all three are tested here and the first valid one selected.
-  __device__ __forceinline__ void sdd_at_intersection(int index, const Rows& rows, bool on) {
+  __device__ __forceinline__ void sdd_at_intersection(int index, bool on) {
+    index = clampi(index);  // a half that is not `on` may have drifted out of range
     const bool has_hi = index < N - 1, has_lo = index > 0;
     const double sp = sd2[clampi(index + 1)];
     const double sm = sd2[clampi(index - 1)];
@@ -142,9 +141,9 @@ struct PairSolver {
     const double c1 = 0.25 / ds * (sp - sm);
     const double c2 = 0.5 / ds * (sp - here);
     const double c3 = 0.5 / ds * (here - sm);
-    const bool v1 = valid(rows, c1, here);
-    const bool v2 = valid(rows, c2, here);
-    const bool v3 = valid(rows, c3, here);
+    const bool v1 = valid_k(Ak, Bk, sgn * c1, here);
+    const bool v2 = valid_k(Ak, Bk, sgn * c2, here);
+    const bool v3 = valid_k(Ak, Bk, sgn * c3, here);
     double r = 0.0;
     if (has_lo && v3) r = c3;
     if (has_hi && v2) r = c2;
@@ -162,10 +161,12 @@ struct PairSolver {
   int stage, status;
   // sweep state (AddForwardExtremal :769-857 / AddBackwardExtremal :859-952)
   int dir, idx;
+  double sgn;      // dir as a double
+  int stop_types;  // kSink for a forward, kSource for a backward sweep
   bool connecting;
   double cur, bcur, bnb, nb;  // sd2[idx], sd2_max[idx], sd2_max[idx+dir], sd2[idx+dir]
-  uint8_t tcur, tnb;
-  Rows rows;
+  int tcur, tnb;
+  double Ak, Bk;  // rows of sample idx: sgn * q'_d, q''_d
   // driver state
   int iforw_hi, iback_lo, iback_hi, icrit, icrit_lo, icrit_hi, loop, max_loops;
 
@@ -177,6 +178,8 @@ struct PairSolver {
   // in *ret) when the reference's early-out applies, so no step is needed.
   __device__ __forceinline__ bool begin_sweep(int direction, int start, int* ret) {
     dir = direction;
+    sgn = static_cast<double>(direction);
+    stop_types = (direction > 0) ? kSink : kSource;
     if (direction > 0) {
       if (start >= N - 2) {
         *ret = N - 1;
@@ -192,7 +195,8 @@ struct PairSolver {
     cur = sd2[start];
     bcur = bmax[start];
     tcur = type[start];
-    rows = load(start);
+    Ak = sgn * dq[start * kD];
+    Bk = ddq[start * kD];
     bnb = bmax[start + direction];
     tnb = type[start + direction];
     nb = sd2[start + direction];
@@ -205,61 +209,59 @@ struct PairSolver {
   // ended, with the sweep's return value in *ret.
   __device__ __forceinline__ bool sweep_step(bool live, int* ret) {
     const bool fwd = dir > 0;
-    const bool at_end = fwd ? !(idx < N - 2) : !(idx > 1);
+    const bool at_end = fwd ? (idx >= N - 2) : (idx <= 1);
     bool run = live && !at_end;
     bool ended = live && at_end;
     int r = fwd ? N - 1 : 0;
     // data of the step after this one (clamped: a half that is not running may
-    // sit at either end)
+    // sit anywhere)
     const int i1 = clampi(idx + dir), i2 = clampi(idx + 2 * dir);
-    const Rows rows_n = load(i1);
+    const double A_n = dq[i1 * kD];
+    const double B_n = ddq[i1 * kD];
     const double bnb_n = bmax[i2];
-    const uint8_t tnb_n = type[i2];
+    const int tnb_n = type[i2];
     const double nb_n = sd2[i2];
 
-    const double sgn = fwd ? 1.0 : -1.0;
-    const bool on_boundary = is_tiny(cur - bcur);
-    const bool follow = on_boundary && (tcur & kTrajectory) && (tnb & kTrajectory);
-    double f = 0.0;
-    if (any(run && !follow)) f = find_sdd(rows, cur, fwd);
-    double sd2tmp, sddtmp;
-    if (follow) {
+    // The step that lands on the limit curve, and whether it is admissible
+    // (:806-813 / :898-905); independent of the search below.  fwd: 0.5*(bnb -
+    // cur)/ds, bwd: 0.5*(cur - bnb)/ds; the fma makes the difference a +0 in
+    // both directions when the two are equal.
+    const double sb = div_pos(0.5 * fma(sgn, bnb - cur, 0.0), ds);
+    const bool sb_ok = valid_k(Ak, Bk, sgn * sb, fwd ? bcur : cur);
+
+    const bool follow = is_tiny(cur - bcur) && ((tcur & tnb & kTrajectory) != 0);
+    double k = 0.0;
+    bool none_valid = true;
+    if (any(run && !follow)) k = find_k(Ak, Bk, cur, &none_valid);
+    // fwd: cur + 2ds*sdd, bwd: cur - 2ds*sdd; both are cur + 2ds*k
+    double sd2tmp = follow ? bnb : cur + 2.0 * ds * (none_valid ? 0.0 : k);
+    double sddtmp = follow ? sb : (none_valid ? 0.0 : sgn * k);
+    const bool isect = (nb == nb) && (nb < sd2tmp);
+    const bool over = sd2tmp > bnb;
+    const bool stop = over && (((tnb & stop_types) != 0) || !sb_ok) && !connecting;
+    if (over) {
       sd2tmp = bnb;
-      // fwd: 0.5*(sd2tmp - cur)/ds, bwd: 0.5*(cur - sd2tmp)/ds; operands are
-      // swapped rather than the difference negated so that a zero keeps its sign
-      sddtmp = div_pos(0.5 * ((fwd ? sd2tmp : cur) - (fwd ? cur : sd2tmp)), ds);
-    } else {
-      sddtmp = f;
-      sd2tmp = cur + sgn * (2.0 * ds * sddtmp);  // fwd: cur + 2ds*sdd, bwd: cur - 2ds*sdd
+      sddtmp = sb;
     }
-    const bool isect = run && !(nb != nb) && (nb < sd2tmp);
-    if (any(isect)) sdd_at_intersection(idx, rows, isect);
-    if (isect) {
-      ended = true;
-      run = false;
-    }
-    const bool over = run && (sd2tmp > bnb);
-    if (any(over)) {
-      const double sdd_bound = div_pos(0.5 * ((fwd ? bnb : cur) - (fwd ? cur : bnb)), ds);
-      const bool deriv_invalid = !valid(rows, sdd_bound, fwd ? bcur : cur);
-      if (over) {
-        const bool type_invalid = tnb & (fwd ? kSink : kSource);
-        if ((type_invalid || deriv_invalid) && !connecting) {
-          ended = true;
-          run = false;
-          r = idx;
+    const bool neg = sd2tmp < 0;
+    // the rare ends of a step: intersection with an earlier sweep, leaving the
+    // limit curve's admissible part, a negative sd2
+    if (any(ended || (run && (isect || stop || neg)))) {
+      if (any(run && isect)) sdd_at_intersection(idx, run && isect);
+      if (run && isect) {
+        ended = true;
+        run = false;
+      } else if (run && stop) {
+        ended = true;
+        run = false;
+        r = idx;
+      } else if (run && neg) {
+        sd2tmp = 0.0;
+        if (fwd) {
+          sddtmp = (idx <= 1) ? 0.0 : div_pos(-sd2[idx - 1], ds);
         } else {
-          sd2tmp = bnb;
-          sddtmp = sdd_bound;
+          sddtmp = (idx < N - 1) ? div_pos(sd2[idx + 1], ds) : 0.0;
         }
-      }
-    }
-    if (run && sd2tmp < 0) {
-      sd2tmp = 0.0;
-      if (fwd) {
-        sddtmp = (idx <= 1) ? 0.0 : div_pos(-sd2[idx - 1], ds);
-      } else {
-        sddtmp = (idx < N - 1) ? div_pos(sd2[idx + 1], ds) : 0.0;
       }
     }
     if (run && lane == 0) {
@@ -267,16 +269,16 @@ struct PairSolver {
       sdd[idx] = sddtmp;
     }
     __syncwarp();
-    if (run) {
-      cur = sd2tmp;
-      bcur = bnb;
-      tcur = tnb;
-      rows = rows_n;
-      bnb = bnb_n;
-      tnb = tnb_n;
-      nb = nb_n;
-      idx += dir;
-    }
+    // (a half that is not running rotates garbage; its next sweep reloads)
+    cur = sd2tmp;
+    bcur = bnb;
+    tcur = tnb;
+    Ak = sgn * A_n;
+    Bk = B_n;
+    bnb = bnb_n;
+    tnb = tnb_n;
+    nb = nb_n;
+    idx += dir;
     *ret = r;
     return ended;
   }
@@ -354,14 +356,16 @@ struct PairSolver {
   // Runs both sweeps and the switching-point loop of this half's path to the
   // end, in lock step with the other half (go = false: nothing to do, idle).
   __device__ void run(bool go) {
-    // an idle half still executes every step: keep its state addressable
+    // an idle half still executes every step: keep its state harmless
     sweeping = false;
     dir = 1;
+    sgn = 1.0;
+    stop_types = 0;
     idx = 0;
     connecting = false;
     cur = bcur = bnb = nb = 0.0;
     tcur = tnb = kNone;
-    rows.A = rows.B = 0.0;
+    Ak = Bk = 0.0;
     if (go) {
       stage = kFirstBack;
       sweeping = true;
@@ -369,11 +373,15 @@ struct PairSolver {
       if (begin_sweep(-1, N - 1, &ret)) advance(ret);
     }
     __syncwarp();
-    while (any(sweeping)) {
+    bool more = any(sweeping);
+    while (more) {
       int ret = 0;
       const bool ended = sweep_step(sweeping, &ret);
-      if (ended) advance(ret);
-      __syncwarp();
+      if (any(ended)) {
+        if (ended) advance(ret);
+        __syncwarp();
+        more = any(sweeping);
+      }
     }
   }
 };
