@@ -35,7 +35,7 @@
 
 namespace tpb {
 
-constexpr int kPairWarpsPerBlock = 4;  // 8 paths per CTA
+constexpr int kPairWarpsPerBlock = 1;  // 2 paths per CTA: 2,048 CTAs spread evenly over the SMs
 
 template <int kD>
 struct PairSolver {
@@ -161,9 +161,12 @@ struct PairSolver {
   int stage, status;
   // sweep state (AddForwardExtremal :769-857 / AddBackwardExtremal :859-952)
   int dir, idx;
+  int left;        // steps the sweep may still take before it runs into the path's end
+  int end_ret;     // what the sweep returns there: N - 1 forward, 0 backward
   double sgn;      // dir as a double
-  int stop_types;  // kSink for a forward, kSource for a backward sweep
-  bool connecting;
+  int stop_types;  // types that end a sweep at the limit curve (kSink forward, kSource
+                   // backward); 0 for a connecting sweep, which never ends there
+  int strict;      // 1: an inadmissible limit-curve step ends the sweep (not connecting)
   double cur, bcur, bnb, nb;  // sd2[idx], sd2_max[idx], sd2_max[idx+dir], sd2[idx+dir]
   int tcur, tnb;
   double Ak, Bk;  // rows of sample idx: sgn * q'_d, q''_d
@@ -179,7 +182,11 @@ struct PairSolver {
   __device__ __forceinline__ bool begin_sweep(int direction, int start, int* ret) {
     dir = direction;
     sgn = static_cast<double>(direction);
-    stop_types = (direction > 0) ? kSink : kSource;
+    const bool connecting = (direction < 0) && (start != (N - 1));
+    stop_types = connecting ? 0 : ((direction > 0) ? kSink : kSource);
+    strict = connecting ? 0 : 1;
+    left = (direction > 0) ? (N - 2 - start) : (start - 1);
+    end_ret = (direction > 0) ? N - 1 : 0;
     if (direction > 0) {
       if (start >= N - 2) {
         *ret = N - 1;
@@ -200,7 +207,6 @@ struct PairSolver {
     bnb = bmax[start + direction];
     tnb = type[start + direction];
     nb = sd2[start + direction];
-    connecting = (direction < 0) && (start != (N - 1));
     return false;
   }
 
@@ -209,10 +215,10 @@ struct PairSolver {
   // ended, with the sweep's return value in *ret.
   __device__ __forceinline__ bool sweep_step(bool live, int* ret) {
     const bool fwd = dir > 0;
-    const bool at_end = fwd ? (idx >= N - 2) : (idx <= 1);
+    const bool at_end = left <= 0;
     bool run = live && !at_end;
     bool ended = live && at_end;
-    int r = fwd ? N - 1 : 0;
+    int r = end_ret;
     // data of the step after this one (clamped: a half that is not running may
     // sit anywhere)
     const int i1 = clampi(idx + dir), i2 = clampi(idx + 2 * dir);
@@ -238,7 +244,7 @@ struct PairSolver {
     double sddtmp = follow ? sb : (none_valid ? 0.0 : sgn * k);
     const bool isect = (nb == nb) && (nb < sd2tmp);
     const bool over = sd2tmp > bnb;
-    const bool stop = over && (((tnb & stop_types) != 0) || !sb_ok) && !connecting;
+    const bool stop = over && (((tnb & stop_types) | (sb_ok ? 0 : strict)) != 0);
     if (over) {
       sd2tmp = bnb;
       sddtmp = sb;
@@ -279,6 +285,7 @@ struct PairSolver {
     tnb = tnb_n;
     nb = nb_n;
     idx += dir;
+    --left;
     *ret = r;
     return ended;
   }
@@ -362,7 +369,9 @@ struct PairSolver {
     sgn = 1.0;
     stop_types = 0;
     idx = 0;
-    connecting = false;
+    left = 0;
+    end_ret = 0;
+    strict = 0;
     cur = bcur = bnb = nb = 0.0;
     tcur = tnb = kNone;
     Ak = Bk = 0.0;
@@ -389,7 +398,7 @@ struct PairSolver {
 // Phase kPhaseOptimize for two paths per warp.  Runs between
 // k_integrate<Joint8Policy<kD>, ., kPhaseSetup> and <., ., kPhaseFinalize>.
 template <int kD>
-__global__ void __launch_bounds__(kPairWarpsPerBlock * 32, 4)
+__global__ void __launch_bounds__(kPairWarpsPerBlock * 32, 16 / kPairWarpsPerBlock)
 k_optimize_pair(Dims dm, DeviceArrays a, double safety, int max_loops) {
   const int warp = threadIdx.x >> 5;
   const int half = (threadIdx.x >> 4) & 1;
