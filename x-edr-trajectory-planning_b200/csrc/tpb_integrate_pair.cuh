@@ -198,22 +198,66 @@ struct PairSolver {
         return true;
       }
     }
-    idx = start;
-    cur = sd2[start];
-    bcur = bmax[start];
-    tcur = type[start];
-    Ak = sgn * dq[start * kD];
-    Bk = ddq[start * kD];
-    bnb = bmax[start + direction];
-    tnb = type[start + direction];
-    nb = sd2[start + direction];
+    load_state(start);
     return false;
+  }
+
+  // The sweep's registers for sample `at` (1 <= at + dir <= N - 1).
+  __device__ __forceinline__ void load_state(int at) {
+    idx = at;
+    cur = sd2[at];
+    bcur = bmax[at];
+    tcur = type[at];
+    Ak = sgn * dq[at * kD];
+    Bk = ddq[at * kD];
+    bnb = bmax[at + dir];
+    tnb = type[at + dir];
+    nb = sd2[at + dir];
+  }
+
+  // A run of steps along the limit curve (:790-794 / :882-886): while the sweep
+  // sits on the curve and this and the next sample are Trajectory points, a step
+  // copies sd2_max[next] and takes sdd from the difference -- no search, and
+  // nothing that depends on the step before except where it stands.  Lane k does
+  // step k of the run for the halves with `on` set; the run ends before the
+  // first step that the one-step routine has to look at (an intersection with an
+  // earlier sweep, a non-Trajectory sample, the path's end).  Convergent.
+  __device__ __forceinline__ void follow_run(bool on) {
+    const int j = clampi(idx + dir * lane), jn = clampi(j + dir);
+    const int tj = type[j], tn = type[jn];
+    const double bj = bmax[j], bn = bmax[jn], old = sd2[jn];
+    const double c = (lane == 0) ? cur : bj;  // sd2 where step k starts
+    const bool ok = on && (lane < left) && (lane < 15) && ((tj & tn & kTrajectory) != 0) &&
+                    !((old == old) && (old < bn)) && !(bn < 0);
+    const int len = __ffs(~ballot(ok)) - 1;  // leading steps that are all plain
+    const double sddv = div_pos(0.5 * fma(sgn, bn - c, 0.0), ds);
+    if (on && lane < len) {
+      sd2[jn] = bn;
+      sdd[j] = sddv;
+    }
+    __syncwarp();
+    if (on && len > 0) {
+      left -= len;
+      load_state(idx + dir * len);
+      // Consume the reloaded state here.  A scoreboard wait is attached to the
+      // first instruction that reads a loaded register; left to the step below,
+      // every trip would pay for it (and wait for that trip's prefetch as well).
+      // None of these comparisons can hold.
+      const bool never = (cur < -1e300) | (bcur < -1e300) | (bnb < -1e300) | (nb < -1e300) |
+                         (Ak != Ak) | (Bk != Bk) | ((tcur + tnb) == 200);
+      if (never) left = 0;
+    }
   }
 
   // One iteration of the extremal loop in direction dir, for the halves with
   // `live` set.  Convergent.  Returns true (to a live half) when its sweep has
   // ended, with the sweep's return value in *ret.
   __device__ __forceinline__ bool sweep_step(bool live, int* ret) {
+    {
+      const bool on_curve = live && (left > 0) && is_tiny(cur - bcur) &&
+                            ((tcur & tnb & kTrajectory) != 0);
+      if (any(on_curve)) follow_run(on_curve);
+    }
     const bool fwd = dir > 0;
     const bool at_end = left <= 0;
     bool run = live && !at_end;
@@ -276,14 +320,16 @@ struct PairSolver {
     }
     __syncwarp();
     // (a half that is not running rotates garbage; its next sweep reloads)
+    const double A_nx = A_n, B_nx = B_n, bnb_nx = bnb_n, nb_nx = nb_n;
+    const int tnb_nx = tnb_n;
     cur = sd2tmp;
     bcur = bnb;
     tcur = tnb;
-    Ak = sgn * A_n;
-    Bk = B_n;
-    bnb = bnb_n;
-    tnb = tnb_n;
-    nb = nb_n;
+    Ak = sgn * A_nx;
+    Bk = B_nx;
+    bnb = bnb_nx;
+    tnb = tnb_nx;
+    nb = nb_nx;
     idx += dir;
     --left;
     *ret = r;
