@@ -272,9 +272,11 @@ struct Solver {
 
   // "skipped maximum" value at sample i (:1422-1429)
   __device__ double skipped_value(int i, double bm, double bp) {
-    const double fw = bm + 2.0 * ds * p.template find_sdd<true>(p.load(i - 1), bm);
-    const double bw = bp - 2.0 * ds * p.template find_sdd<false>(p.load(i + 1), bp);
-    double m = bzero[i];
+    const Rows rm = p.load(i - 1), rp = p.load(i + 1);  // both in flight together
+    const double bz = bzero[i];
+    const double fw = bm + 2.0 * ds * p.template find_sdd<true>(rm, bm);
+    const double bw = bp - 2.0 * ds * p.template find_sdd<false>(rp, bp);
+    double m = bz;
     if (fw < m) m = fw;
     if (bw < m) m = bw;
     return (0.0 < m) ? m : 0.0;
@@ -293,48 +295,87 @@ struct Solver {
       type[N - 1] = kNone;
     }
     int nwork = 0;
-    auto test = [&](int i, double bm, double bi, double bp) {
+    auto test_v = [&](double bm, double bi, double bp, double smax_i, double smin_i,
+                      double smin_next) {
       const double sd2p = div_pos(bp - bi, ds);
-      const double smax_i = bsmax[i];
-      const bool sink_or_source = (sd2p < 2 * bsmin[i]) || (sd2p > 2 * smax_i);
-      const bool skipped_sdd = (smax_i > 0) && (bsmin[i + 1] < 0);
+      const bool sink_or_source = (sd2p < 2 * smin_i) || (sd2p > 2 * smax_i);
+      const bool skipped_sdd = (smax_i > 0) && (smin_next < 0);
       const bool skipped_sd2 = (bi > bm - kTiny) && (bi > bp - kTiny);
       return (skipped_sd2 || skipped_sdd) && sink_or_source;
     };
-    for (int base = 1; base < N - 1; base += 32) {
-      const int i = base + lane;
-      const bool in = i < N - 1;
-      const bool iso = in && !at0[i - 1] && at0[i] && !at0[i + 1];
+    auto test = [&](int i, double bm, double bi, double bp) {
+      return test_v(bm, bi, bp, bsmax[i], bsmin[i], bsmin[i + 1]);
+    };
+    auto record = [&](int ii, double bm, double bp) {
+      const double v = skipped_value(ii, bm, bp);
+      if (lane == 0) {
+        fix_idx[nwork] = ii;
+        fix_val[nwork] = v;
+      }
+      ++nwork;
+    };
+    // kGroup chunks at a time: the loads of a whole group are in flight together
+    // (one memory round trip per group instead of two per chunk).
+    constexpr int kGroup = 2;
+    for (int base0 = 1; base0 < N - 1; base0 += 32 * kGroup) {
+      bool iso = false;
+#pragma unroll
+      for (int u = 0; u < kGroup; ++u) {
+        const int i = base0 + 32 * u + lane;
+        if (i < N - 1) iso |= !at0[i - 1] && at0[i] && !at0[i + 1];
+      }
       if (__ballot_sync(kFullMask, iso) == 0u) {
-        bool hit = false;
-        if (in) hit = test(i, bmax[i - 1], bmax[i], bmax[i + 1]);
-        unsigned m = __ballot_sync(kFullMask, hit);
-        while (m) {
-          const int k = __ffs(m) - 1;
-          m &= m - 1;
-          const int ii = base + k;
-          const double v = skipped_value(ii, bmax[ii - 1], bmax[ii + 1]);
-          if (lane == 0) {
-            fix_idx[nwork] = ii;
-            fix_val[nwork] = v;
-          }
-          ++nwork;
-        }
-      } else {
-        const int top = min(base + 32, N - 1);
-        for (int ii = base; ii < top; ++ii) {
-          if (!at0[ii - 1] && at0[ii] && !at0[ii + 1]) fix_isolated(ii);
-          const double bm = bmax[ii - 1], bp = bmax[ii + 1];
-          if (test(ii, bm, bmax[ii], bp)) {
-            const double v = skipped_value(ii, bm, bp);
-            if (lane == 0) {
-              fix_idx[nwork] = ii;
-              fix_val[nwork] = v;
-            }
-            ++nwork;
+        // nothing in this group mutates the curve
+        double bm[kGroup], bi[kGroup], bp[kGroup], sx[kGroup], sn[kGroup], sq[kGroup];
+#pragma unroll
+        for (int u = 0; u < kGroup; ++u) {
+          const int i = base0 + 32 * u + lane;
+          if (i < N - 1) {
+            bm[u] = bmax[i - 1];
+            bi[u] = bmax[i];
+            bp[u] = bmax[i + 1];
+            sx[u] = bsmax[i];
+            sn[u] = bsmin[i];
+            sq[u] = bsmin[i + 1];
           }
         }
-        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < kGroup; ++u) {
+          const int base = base0 + 32 * u;
+          const bool hit = (base + lane < N - 1) && test_v(bm[u], bi[u], bp[u], sx[u], sn[u], sq[u]);
+          unsigned m = __ballot_sync(kFullMask, hit);
+          while (m) {
+            const int k = __ffs(m) - 1;
+            m &= m - 1;
+            const int ii = base + k;
+            record(ii, bmax[ii - 1], bmax[ii + 1]);
+          }
+        }
+        continue;
+      }
+      for (int base = base0; base < min(base0 + 32 * kGroup, N - 1); base += 32) {
+        const int i = base + lane;
+        const bool in = i < N - 1;
+        const bool iso1 = in && !at0[i - 1] && at0[i] && !at0[i + 1];
+        if (__ballot_sync(kFullMask, iso1) == 0u) {
+          bool hit = false;
+          if (in) hit = test(i, bmax[i - 1], bmax[i], bmax[i + 1]);
+          unsigned m = __ballot_sync(kFullMask, hit);
+          while (m) {
+            const int k = __ffs(m) - 1;
+            m &= m - 1;
+            const int ii = base + k;
+            record(ii, bmax[ii - 1], bmax[ii + 1]);
+          }
+        } else {
+          const int top = min(base + 32, N - 1);
+          for (int ii = base; ii < top; ++ii) {
+            if (!at0[ii - 1] && at0[ii] && !at0[ii + 1]) fix_isolated(ii);
+            const double bm1 = bmax[ii - 1], bp1 = bmax[ii + 1];
+            if (test(ii, bm1, bmax[ii], bp1)) record(ii, bm1, bp1);
+          }
+          __syncwarp();
+        }
       }
     }
     __syncwarp();
@@ -342,7 +383,10 @@ struct Solver {
     for (int w = 0; w < nwork; ++w) {
       const int index = fix_idx[w];
       const double value = fix_val[w];
-      const Rows r0 = p.load(index);
+      // the three samples' rows and levels in flight together
+      const int im = max(index - 1, 0), ip = min(index + 1, N - 1);
+      const Rows r0 = p.load(index), rlo = p.load(im), rhi = p.load(ip);
+      const double zlo = bzero[im], zhi = bzero[ip];
       const double a1 = p.template find_sdd<true>(r0, value);
       const double a2 = p.template find_sdd<false>(r0, value);
       if (lane == 0) {
@@ -351,8 +395,8 @@ struct Solver {
         bsmin[index] = a2;
       }
       if (index > 0) {
-        const double z = bzero[index - 1];
-        const Rows r1 = p.load(index - 1);
+        const double z = zlo;
+        const Rows r1 = rlo;
         const double c1 = p.template find_sdd<true>(r1, z);
         const double c2 = p.template find_sdd<false>(r1, z);
         if (lane == 0) {
@@ -362,8 +406,8 @@ struct Solver {
         }
       }
       if (index < N - 1) {
-        const double z = bzero[index + 1];
-        const Rows r1 = p.load(index + 1);
+        const double z = zhi;
+        const Rows r1 = rhi;
         const double c1 = p.template find_sdd<true>(r1, z);
         const double c2 = p.template find_sdd<false>(r1, z);
         if (lane == 0) {
@@ -375,18 +419,35 @@ struct Solver {
       __syncwarp();
     }
     // classification (:1453-1484), lane-parallel
-    for (int i = 1 + lane; i < N - 1; i += 32) {
-      const double sd2p = div_pos(bmax[i + 1] - bmax[i], ds);
-      const double sd2p_min = 2 * bsmin[i];
-      const double sd2p_max = 2 * bsmax[i];
-      uint8_t t = kNone;
-      if (sd2p < sd2p_min) {
-        t = kSink;
-      } else if (sd2p > sd2p_max) {
-        t = kSource;
+    for (int i0 = 1 + lane; i0 < N - 1; i0 += 32 * kGroup) {
+      double b1[kGroup], b0[kGroup], mn[kGroup], mx[kGroup];
+#pragma unroll
+      for (int u = 0; u < kGroup; ++u) {
+        const int i = i0 + 32 * u;
+        if (i < N - 1) {
+          b1[u] = bmax[i + 1];
+          b0[u] = bmax[i];
+          mn[u] = bsmin[i];
+          mx[u] = bsmax[i];
+        }
       }
-      if ((sd2p <= sd2p_max) && (sd2p >= sd2p_min)) t = kTrajectory;
-      type[i] = t;
+#pragma unroll
+      for (int u = 0; u < kGroup; ++u) {
+        const int i = i0 + 32 * u;
+        if (i < N - 1) {
+          const double sd2p = div_pos(b1[u] - b0[u], ds);
+          const double sd2p_min = 2 * mn[u];
+          const double sd2p_max = 2 * mx[u];
+          uint8_t t = kNone;
+          if (sd2p < sd2p_min) {
+            t = kSink;
+          } else if (sd2p > sd2p_max) {
+            t = kSource;
+          }
+          if ((sd2p <= sd2p_max) && (sd2p >= sd2p_min)) t = kTrajectory;
+          type[i] = t;
+        }
+      }
     }
     __syncwarp();
   }
@@ -529,23 +590,42 @@ struct Solver {
   //   prev_eq0[i] = largest j <= i with sd2_max[j] == sd2_max_for_sdd0[0], else -1
   __device__ void build_critical_tables(int* next_src, int* prev_eq0) const {
     const double bz0 = bzero[0];
+    constexpr int kGroup = 4;  // chunks whose loads are in flight together
     int carry = N;
-    for (int base = ((N - 1) / 32) * 32; base >= 0; base -= 32) {
-      const int i = base + lane;
-      const bool f = (i < N) && ((type[i] & (kSource | kTrajectory)) != 0);
-      const unsigned m = __ballot_sync(kFullMask, f);
-      const unsigned mm = m & (~0u << lane);
-      if (i < N) next_src[i] = mm ? base + (__ffs(mm) - 1) : carry;
-      if (m) carry = base + (__ffs(m) - 1);
+    for (int base0 = ((N - 1) / 32) * 32; base0 >= 0; base0 -= 32 * kGroup) {
+      bool f[kGroup];
+#pragma unroll
+      for (int u = 0; u < kGroup; ++u) {
+        const int i = base0 - 32 * u + lane;
+        f[u] = (i >= 0) && (i < N) && ((type[i] & (kSource | kTrajectory)) != 0);
+      }
+#pragma unroll
+      for (int u = 0; u < kGroup; ++u) {
+        const int base = base0 - 32 * u;
+        const int i = base + lane;
+        const unsigned m = __ballot_sync(kFullMask, f[u]);
+        const unsigned mm = m & (~0u << lane);
+        if (i >= 0 && i < N) next_src[i] = mm ? base + (__ffs(mm) - 1) : carry;
+        if (m) carry = base + (__ffs(m) - 1);
+      }
     }
     carry = -1;
-    for (int base = 0; base < N; base += 32) {
-      const int i = base + lane;
-      const bool f = (i < N) && (bmax[i] == bz0);
-      const unsigned m = __ballot_sync(kFullMask, f);
-      const unsigned mm = m & (~0u >> (31 - lane));
-      if (i < N) prev_eq0[i] = mm ? base + (31 - __clz(mm)) : carry;
-      if (m) carry = base + (31 - __clz(m));
+    for (int base0 = 0; base0 < N; base0 += 32 * kGroup) {
+      bool f[kGroup];
+#pragma unroll
+      for (int u = 0; u < kGroup; ++u) {
+        const int i = base0 + 32 * u + lane;
+        f[u] = (i < N) && (bmax[i] == bz0);
+      }
+#pragma unroll
+      for (int u = 0; u < kGroup; ++u) {
+        const int base = base0 + 32 * u;
+        const int i = base + lane;
+        const unsigned m = __ballot_sync(kFullMask, f[u]);
+        const unsigned mm = m & (~0u >> (31 - lane));
+        if (i < N) prev_eq0[i] = mm ? base + (31 - __clz(mm)) : carry;
+        if (m) carry = base + (31 - __clz(m));
+      }
     }
     __syncwarp();
   }
@@ -757,13 +837,29 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
     const double* raw_max = a.b_raw_sd2_max + o;
     const double* raw_smax = a.b_raw_sdd_max + o;
     const double* raw_smin = a.b_raw_sdd_min + o;
-    for (int i = lane; i < N; i += 32) {
-      sv[i] = (i == N - 1) ? s_end : ds * i + s_start;
-      S.sd2[i] = (i == 0) ? sd_start * sd_start : ((i == N - 1) ? 0.0 : nan);
-      S.sdd[i] = nan;
-      S.bmax[i] = raw_max[i];
-      S.bsmax[i] = raw_smax[i];
-      S.bsmin[i] = raw_smin[i];
+    for (int i0 = lane; i0 < N; i0 += 32 * 4) {
+      double rm[4], rx[4], rn[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + 32 * u;
+        if (i < N) {
+          rm[u] = raw_max[i];
+          rx[u] = raw_smax[i];
+          rn[u] = raw_smin[i];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + 32 * u;
+        if (i < N) {
+          sv[i] = (i == N - 1) ? s_end : ds * i + s_start;
+          S.sd2[i] = (i == 0) ? sd_start * sd_start : ((i == N - 1) ? 0.0 : nan);
+          S.sdd[i] = nan;
+          S.bmax[i] = rm[u];
+          S.bsmax[i] = rx[u];
+          S.bsmin[i] = rn[u];
+        }
+      }
     }
     __syncwarp();
 
