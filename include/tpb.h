@@ -214,6 +214,17 @@ int32_t tpb_set_constraints(tpb_engine* e, int32_t num_paths, int32_t num_constr
  * max(100, 10 N) as PathTimingTrajectory sets it (path_timing_trajectory.cc:398-400). */
 int32_t tpb_optimize(tpb_engine* e, const double* sd_start, const double* sdd_start,
                      const double* time_start, int32_t max_loops, int32_t on_device);
+/* Device-side timing of tpb_optimize's three phases (diagnostics / benchmarks).
+ * With timing on, every tpb_optimize records CUDA events on the engine's stream
+ * around (0) the setup phase -- SetSetupDone + CalculateBoundary passes 2-4
+ * (time_optimal_path_timing.cc:535-552, 1379-1484), (1) the extremal sweeps and
+ * the switching loop (:300-396, 769-952) and (2) the final audits and time
+ * integration (:398-467).  tpb_last_phase_ms waits for the last timed call and
+ * writes the three durations in milliseconds.  Paths that run all three phases
+ * in one kernel (explicit constraint tables, more than 8 dofs) report the whole
+ * kernel as phase 1 and zero for the others. */
+int32_t tpb_time_phases(tpb_engine* e, int32_t on);
+int32_t tpb_last_phase_ms(tpb_engine* e, double* ms3);
 
 /* ---- stage D: trajectory assembly + ResampleEquidistantlyInTime ---------- */
 /* (path_timing_trajectory.cc:458-472, :755-783).  start_sec = TimeToSec(start),

@@ -113,6 +113,10 @@ def lib():
         L.tpb_cart_setup_constraints.argtypes = [vp, i32, vp, i32]
         L.tpb_set_constraints.restype = i32
         L.tpb_set_constraints.argtypes = [vp, i32, i32, vp, vp, vp, i32]
+        L.tpb_time_phases.restype = i32
+        L.tpb_time_phases.argtypes = [vp, i32]
+        L.tpb_last_phase_ms.restype = i32
+        L.tpb_last_phase_ms.argtypes = [vp, vp]
         L.tpb_optimize.restype = i32
         L.tpb_optimize.argtypes = [vp, vp, vp, vp, i32, i32]
         L.tpb_resample.restype = i32
@@ -288,6 +292,16 @@ class Engine:
             ptrs.append(p)
             dev = dev or d
         self._ck(lib().tpb_optimize(self._h, *ptrs, max_loops, dev))
+
+    def time_phases(self, on=True):
+        """Record CUDA events around the three phases of every optimize()."""
+        self._ck(lib().tpb_time_phases(self._h, 1 if on else 0))
+
+    def last_phase_ms(self):
+        """(setup, sweeps, finalize) milliseconds of the last timed optimize()."""
+        ms = (C.c_double * 3)()
+        self._ck(lib().tpb_last_phase_ms(self._h, C.cast(ms, C.c_void_p)))
+        return [ms[0], ms[1], ms[2]]
 
     def resample(self, start_sec, time_step_sec, want_total=True):
         total = C.c_int64(0)

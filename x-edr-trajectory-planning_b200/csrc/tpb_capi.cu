@@ -40,6 +40,8 @@ struct tpb_engine {
   cudaStream_t copy_stream = nullptr;
   static constexpr int kMaxChunks = 16;
   cudaEvent_t chunk_done[kMaxChunks] = {};
+  cudaEvent_t phase_ev[4] = {};  // tpb_time_phases
+  bool time_phases = false;
   int64_t* chunk_rows = nullptr;  // pinned host: rows up to the end of chunk c
 };
 
@@ -285,6 +287,8 @@ int32_t tpb_destroy(tpb_engine* e) {
     cudaStreamDestroy(e->copy_stream);
   }
   for (auto& ev : e->chunk_done)
+    if (ev) cudaEventDestroy(ev);
+  for (auto& ev : e->phase_ev)
     if (ev) cudaEventDestroy(ev);
   if (e->chunk_rows) cudaFreeHost(e->chunk_rows);
   if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
@@ -596,10 +600,36 @@ int32_t tpb_optimize(tpb_engine* e, const double* sd_start, const double* sdd_st
   TPB_CUDA(e, fill_or_copy(e, e->a.sdd_start, sdd_start, d.B, on_device));
   TPB_CUDA(e, fill_or_copy(e, e->a.time_start, time_start, d.B, on_device));
   if (max_loops <= 0) max_loops = std::max(100, 10 * d.N);
-  e->launches += tpb::launch_integrate(d, e->a, e->mode, e->safety, max_loops, e->stream);
+  e->launches += tpb::launch_integrate(d, e->a, e->mode, e->safety, max_loops, e->stream,
+                                       e->time_phases ? e->phase_ev : nullptr);
   TPB_CUDA(e, cudaGetLastError());
   e->optimized = true;
   e->resampled = false;
+  return TPB_OK;
+}
+
+int32_t tpb_time_phases(tpb_engine* e, int32_t on) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  cudaSetDevice(e->device);
+  if (on) {
+    for (auto& ev : e->phase_ev)
+      if (ev == nullptr) TPB_CUDA(e, cudaEventCreate(&ev));
+  }
+  e->time_phases = on != 0;
+  return TPB_OK;
+}
+
+int32_t tpb_last_phase_ms(tpb_engine* e, double* ms3) {
+  if (e == nullptr || ms3 == nullptr) return TPB_INVALID_ARGUMENT;
+  if (!e->time_phases || !e->optimized)
+    return fail(e, TPB_FAILED_PRECONDITION, "no timed tpb_optimize on this engine");
+  cudaSetDevice(e->device);
+  TPB_CUDA(e, cudaEventSynchronize(e->phase_ev[3]));
+  for (int k = 0; k < 3; ++k) {
+    float ms = 0.f;
+    TPB_CUDA(e, cudaEventElapsedTime(&ms, e->phase_ev[k], e->phase_ev[k + 1]));
+    ms3[k] = ms;
+  }
   return TPB_OK;
 }
 

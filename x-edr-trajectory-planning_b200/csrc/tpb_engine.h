@@ -114,7 +114,8 @@ int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safet
                               cudaStream_t st);
 int launch_generic_limit(const Dims& d, const DeviceArrays& a, cudaStream_t st);
 int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double safety,
-                     int max_loops, cudaStream_t st);
+                     int max_loops, cudaStream_t st,
+                     cudaEvent_t* phase_events = nullptr);
 // continued: the batch is a chunk following another one; r_offset[0] already
 // holds the number of rows before it
 int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, double dt,

@@ -501,7 +501,13 @@ int launch_generic_limit(const Dims& d, const DeviceArrays& a, cudaStream_t st) 
 }
 
 int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double safety,
-                     int max_loops, cudaStream_t st) {
+                     int max_loops, cudaStream_t st, cudaEvent_t* phase_events) {
+  // phase_events (4, optional): recorded before setup, before the sweeps, after
+  // the sweeps and after finalize; a single-kernel path records the inner two
+  // around the whole kernel as well
+  auto mark = [&](int k) {
+    if (phase_events != nullptr) cudaEventRecord(phase_events[k], st);
+  };
   const int blocks = (d.B + kWarpsPerBlock - 1) / kWarpsPerBlock;
   const bool joint = mode == Mode::kJoint;
   // TPB_INTEGRATE=warp selects the one-path-per-warp kernel (read once).
@@ -517,18 +523,25 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
     const int pthreads = kPairWarpsPerBlock * 32;
 #define TPB_P8(K)                                                                          \
   case K:                                                                                  \
+    mark(0);                                                                               \
     k_integrate<Joint8Policy<K>, 7, kPhaseSetup><<<blocks, threads, 0, st>>>(d, a, true, safety, \
                                                                              max_loops);   \
+    mark(1);                                                                               \
     k_optimize_pair<K><<<pblocks, pthreads, 0, st>>>(d, a, safety, max_loops);             \
+    mark(2);                                                                               \
     k_integrate<Joint8Policy<K>, 7, kPhaseFinalize><<<blocks, threads, 0, st>>>(           \
         d, a, true, safety, max_loops);                                                    \
+    mark(3);                                                                               \
     break
     switch (d.D) {
       TPB_P8(1); TPB_P8(2); TPB_P8(3); TPB_P8(4); TPB_P8(5); TPB_P8(6); TPB_P8(7); TPB_P8(8);
     }
 #undef TPB_P8
     return 3;
-  } else if (joint && d.D <= 8) {
+  }
+  mark(0);
+  mark(1);
+  if (joint && d.D <= 8) {
     const int threads = kWarpsPerBlock * 32;
 #define TPB_J8(K) \
   case K: k_integrate<Joint8Policy<K>, 7><<<blocks, threads, 0, st>>>(d, a, true, safety, max_loops); break
@@ -539,6 +552,8 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
   } else {
     k_integrate<GenericPolicy, 4><<<blocks, kWarpsPerBlock * 32, 0, st>>>(d, a, joint, safety, max_loops);
   }
+  mark(2);
+  mark(3);
   return 1;
 }
 
