@@ -163,6 +163,12 @@ def lib():
         L.orc_plan_cart_fake.argtypes = [C.POINTER(_CartCfg), c_double_p, c_double_p,
                                          c_double_p, c_double_p, C.POINTER(_PlanOut),
                                          c_double_p, c_double_p, c_double_p, c_double_p]
+        # stopping trajectories (tp_oracle_stop.c)
+        L.orc_sampled_trajectory_inputs_valid.restype = C.c_int
+        L.orc_sampled_trajectory_inputs_valid.argtypes = [C.c_int, c_double_p]
+        L.orc_rescale_to_stop.restype = C.c_int
+        L.orc_rescale_to_stop.argtypes = [C.c_int, C.c_int] + [c_double_p] * 4 + [
+            C.POINTER(C.c_int), C.POINTER(C.c_int)] + [c_double_p] * 3
         _lib = L
     return _lib
 
@@ -188,6 +194,9 @@ def ref():
         R.tpref_plan_joint.restype = C.c_int
         R.tpref_plan_joint.argtypes = [C.POINTER(_PlanCfg), c_double_p, c_double_p,
                                        c_double_p, C.POINTER(_PlanOut)]
+        R.tpref_rescale_to_stop.restype = C.c_int
+        R.tpref_rescale_to_stop.argtypes = [C.c_int, C.c_int] + [c_double_p] * 5 + [
+            C.POINTER(C.c_int), C.POINTER(C.c_int)] + [c_double_p] * 4
         _ref = R
     return _ref
 
@@ -366,6 +375,34 @@ def plan_joint(waypoints, vmax, amax, N, rounding=0.2, safety=0.8, delta=-1.0,
                delta=out.delta_used, knot_end=out.knot_end, M=M,
                last_extremal_index=out.last_extremal_index)
     return res
+
+
+# ----------------------------------------------------------------- stopping trajectory
+def rescale_to_stop(max_acc, times, positions, velocities, accelerations, impl="port"):
+    """RescaleTrajectoryBackwardToStop.  impl: 'port' | 'ref'.
+    Returns dict(status, count, switch_index, times, positions, velocities, accelerations)."""
+    t = np.ascontiguousarray(times, np.float64)
+    p = np.ascontiguousarray(positions, np.float64)
+    v = np.ascontiguousarray(velocities, np.float64)
+    a = np.ascontiguousarray(accelerations, np.float64)
+    amax = np.ascontiguousarray(max_acc, np.float64)
+    n, D = v.shape
+    ot, ov, oa = np.zeros(n), np.zeros((n, D)), np.zeros((n, D))
+    cnt, sw = C.c_int(0), C.c_int(0)
+    if impl == "port":
+        st = lib().orc_rescale_to_stop(n, D, _dp(amax), _dp(t), _dp(v), _dp(a), C.byref(cnt),
+                                       C.byref(sw), _dp(ot), _dp(ov), _dp(oa))
+        m = cnt.value
+        op = p[sw.value:sw.value + m].copy()
+    else:
+        op = np.zeros((n, D))
+        st = ref().tpref_rescale_to_stop(n, D, _dp(amax), _dp(t), _dp(p), _dp(v), _dp(a),
+                                         C.byref(cnt), C.byref(sw), _dp(ot), _dp(op),
+                                         _dp(ov), _dp(oa))
+        m = cnt.value
+        op = op[:m].copy()
+    return dict(status=st, count=m, switch_index=sw.value, times=ot[:m].copy(), positions=op,
+                velocities=ov[:m].copy(), accelerations=oa[:m].copy())
 
 
 # ----------------------------------------------------------------- Cartesian path

@@ -1,0 +1,29 @@
+// TEST INFRASTRUCTURE ONLY -- minimal stand-in for absl/status/statusor.h.
+#ifndef ORACLE_SHIM_ABSL_STATUS_STATUSOR_H_
+#define ORACLE_SHIM_ABSL_STATUS_STATUSOR_H_
+
+#include <utility>
+
+#include "absl/status/status.h"
+
+namespace absl {
+
+template <typename T>
+class StatusOr {
+ public:
+  StatusOr(const Status& s) : status_(s) {}              // NOLINT
+  StatusOr(T v) : value_(std::move(v)) {}                // NOLINT
+  bool ok() const { return status_.ok(); }
+  const Status& status() const { return status_; }
+  T& operator*() { return value_; }
+  const T& operator*() const { return value_; }
+  T* operator->() { return &value_; }
+
+ private:
+  Status status_;
+  T value_{};
+};
+
+}  // namespace absl
+
+#endif  // ORACLE_SHIM_ABSL_STATUS_STATUSOR_H_

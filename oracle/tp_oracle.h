@@ -178,6 +178,17 @@ int orc_plan_cart_fake(const orc_cart_cfg* cfg, const double* pose_wp, const dou
                        double* pose_ctrl_out, double* knots_out, double* pose_targets_out,
                        double* cons_out);
 
+/* ---- RescaleTrajectoryBackwardToStop (rescale_to_stop.cc:35-161) ---------- */
+/* sampled_trajectory.cc:24-44; 1 = valid */
+int orc_sampled_trajectory_inputs_valid(int n, const double* times);
+/* Trajectory [n][D] row-major (positions are not needed: the result's positions
+ * are input rows switch_index .. switch_index+count-1).  out_* hold n rows of
+ * capacity; rows 0..count-1 are the stopping trajectory.  count == 0: the input
+ * already ends in a stop.  Returns ORC_OK or ORC_FAIL_SETUP (invalid input). */
+int orc_rescale_to_stop(int n, int D, const double* max_acc, const double* times,
+                        const double* vel, const double* acc, int* count, int* switch_index,
+                        double* out_times, double* out_vel, double* out_acc);
+
 #ifdef __cplusplus
 }
 #endif
