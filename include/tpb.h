@@ -295,6 +295,45 @@ int32_t tpb_spline_eval_device(const tpb_spline_eval_desc* d, void* cuda_stream)
 /* Same with host pointers (allocates, copies in, evaluates, copies out). */
 int32_t tpb_spline_eval_host(const tpb_spline_eval_desc* d, int32_t device);
 
+/* ---- stopping trajectories ------------------------------ */
+/* Batched RescaleTrajectoryBackwardToStop (rescale_to_stop.cc:35-161, declared
+ * in rescale_to_stop.h:31-35): for each sampled trajectory the fastest stop that
+ * traces its tail without exceeding max_acceleration, by backward integration of
+ * the squared time-scaling rate.  Trajectories are packed: trajectory b is rows
+ * begin[b] .. begin[b]+length[b]-1 of times [rows], velocities and accelerations
+ * [rows][num_dofs] (the layout of TPB_ARR_R_*; positions are not needed).
+ *
+ * Results: count[b] samples (0: the trajectory already ends in a stop,
+ * rescale_to_stop.cc:60-63), which correspond to input samples switch_index[b] ..
+ * length[b]-1 -- the stopping trajectory's positions ARE those input rows -- and
+ * are written to the same rows of out_times / out_velocities / out_accelerations
+ * (rows begin[b]+switch_index[b] ..; other rows are left untouched).  status[b] is
+ * TPB_PATH_OK or TPB_PATH_FAIL_SETUP (AreInputsValidForSampledTrajectory,
+ * sampled_trajectory.cc:24-44: fewer than two samples, times not strictly
+ * increasing).  num_dofs <= 16. */
+typedef struct {
+  int32_t num_trajectories;
+  int32_t num_dofs;
+  int64_t total_rows;             /* rows of the packed arrays */
+  const int64_t* begin;           /* [num_trajectories] */
+  const int32_t* length;          /* [num_trajectories] */
+  const double* times;            /* [total_rows] */
+  const double* velocities;       /* [total_rows][num_dofs] */
+  const double* accelerations;    /* [total_rows][num_dofs] */
+  const double* max_acceleration; /* [num_trajectories][num_dofs] */
+  int32_t* count;                 /* [num_trajectories] */
+  int32_t* switch_index;          /* [num_trajectories] */
+  int32_t* status;                /* [num_trajectories] */
+  double* out_times;              /* [total_rows] */
+  double* out_velocities;         /* [total_rows][num_dofs] */
+  double* out_accelerations;      /* [total_rows][num_dofs] */
+} tpb_stop_desc;
+/* All pointers are device pointers; asynchronous on cuda_stream. */
+int32_t tpb_rescale_to_stop_device(const tpb_stop_desc* d, void* cuda_stream);
+/* All pointers are host pointers; copies in, runs on `device`, copies out, returns
+ * when done. */
+int32_t tpb_rescale_to_stop_host(const tpb_stop_desc* d, int32_t device);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,6 +11,7 @@ The directory name contains hyphens, so import it through
 ``__graft_entry__.load_package()`` (module name ``x_edr_trajectory_planning_b200``).
 """
 from .binding import (  # noqa: F401
-    ARR, PATH_OK, Engine, TpbError, lib, lib_path, spline_eval_device, spline_eval_host,
+    ARR, PATH_OK, Engine, TpbError, lib, lib_path, rescale_to_stop_device, rescale_to_stop_host,
+    spline_eval_device, spline_eval_host,
 )
 from . import workloads  # noqa: F401

@@ -14,6 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_HERE, "lib", "libtpb.so")
 
 PATH_OK = 0
+PATH_FAIL_SETUP = 1
 
 
 class ARR:
@@ -49,6 +50,14 @@ class _PlanIO(C.Structure):
                 ("r_vel", C.c_void_p), ("r_acc", C.c_void_p), ("r_s", C.c_void_p),
                 ("r_sd", C.c_void_p), ("r_sdd", C.c_void_p), ("r_capacity", C.c_int64),
                 ("r_total", C.c_int64)]
+
+
+class _StopDesc(C.Structure):
+    _fields_ = [("num_trajectories", C.c_int32), ("num_dofs", C.c_int32),
+                ("total_rows", C.c_int64)] + [(n, C.c_void_p) for n in (
+                    "begin", "length", "times", "velocities", "accelerations",
+                    "max_acceleration", "count", "switch_index", "status", "out_times",
+                    "out_velocities", "out_accelerations")]
 
 
 class _SplineDesc(C.Structure):
@@ -131,6 +140,10 @@ def lib():
         L.tpb_spline_eval_device.argtypes = [C.POINTER(_SplineDesc), vp]
         L.tpb_spline_eval_host.restype = i32
         L.tpb_spline_eval_host.argtypes = [C.POINTER(_SplineDesc), i32]
+        L.tpb_rescale_to_stop_device.restype = i32
+        L.tpb_rescale_to_stop_device.argtypes = [C.POINTER(_StopDesc), vp]
+        L.tpb_rescale_to_stop_host.restype = i32
+        L.tpb_rescale_to_stop_host.argtypes = [C.POINTER(_StopDesc), i32]
         _lib = L
     return _lib
 
@@ -408,3 +421,55 @@ def spline_eval_device(knots, ctrl, degree, nder, out, u=None, u0=None, du=None,
     rc = lib().tpb_spline_eval_device(C.byref(d), stream)
     if rc != 0:
         raise TpbError(rc, "tpb_spline_eval_device")
+
+
+def _addr(x):
+    """Address of a numpy array or of a torch CUDA tensor."""
+    if x is None:
+        return None
+    if isinstance(x, np.ndarray):
+        return x.ctypes.data
+    return x.data_ptr()
+
+
+def rescale_to_stop_host(max_acceleration, begin, length, times, velocities, accelerations,
+                         device=0):
+    """tpb_rescale_to_stop_host on packed numpy trajectories.
+
+    times [R], velocities/accelerations [R][D]; trajectory b = rows begin[b] ..
+    begin[b]+length[b]-1; max_acceleration [T][D].  Returns dict(count, switch_index,
+    status, times, velocities, accelerations): the out_* arrays have the layout of the
+    inputs, the stopping trajectory of b is rows begin[b]+switch_index[b] ..
+    begin[b]+length[b]-1 of them (NaN elsewhere).
+    """
+    amax = _f64(max_acceleration)
+    t, v, a = _f64(times), _f64(velocities), _f64(accelerations)
+    begin = np.ascontiguousarray(begin, np.int64)
+    length = np.ascontiguousarray(length, np.int32)
+    T, D = amax.shape
+    R = t.shape[0]
+    out = dict(count=np.zeros(T, np.int32), switch_index=np.zeros(T, np.int32),
+               status=np.zeros(T, np.int32), times=np.full(R, np.nan),
+               velocities=np.full((R, D), np.nan), accelerations=np.full((R, D), np.nan))
+    d = _StopDesc(T, D, R, _addr(begin), _addr(length), _addr(t), _addr(v), _addr(a), _addr(amax),
+                  _addr(out["count"]), _addr(out["switch_index"]), _addr(out["status"]),
+                  _addr(out["times"]), _addr(out["velocities"]), _addr(out["accelerations"]))
+    rc = lib().tpb_rescale_to_stop_host(C.byref(d), device)
+    if rc != 0:
+        raise TpbError(rc, "tpb_rescale_to_stop_host")
+    return out
+
+
+def rescale_to_stop_device(max_acceleration, begin, length, times, velocities, accelerations,
+                           count, switch_index, status, out_times, out_velocities,
+                           out_accelerations, stream=None):
+    """tpb_rescale_to_stop_device on torch CUDA tensors (asynchronous on `stream`)."""
+    T, D = max_acceleration.shape
+    R = times.shape[0]
+    d = _StopDesc(T, D, R, _addr(begin), _addr(length), _addr(times), _addr(velocities),
+                  _addr(accelerations), _addr(max_acceleration), _addr(count),
+                  _addr(switch_index), _addr(status), _addr(out_times), _addr(out_velocities),
+                  _addr(out_accelerations))
+    rc = lib().tpb_rescale_to_stop_device(C.byref(d), stream)
+    if rc != 0:
+        raise TpbError(rc, "tpb_rescale_to_stop_device")

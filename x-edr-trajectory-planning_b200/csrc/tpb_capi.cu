@@ -812,6 +812,124 @@ int32_t tpb_devptr(tpb_engine* e, tpb_array what, void** ptr, size_t* bytes) {
   return TPB_OK;
 }
 
+int32_t tpb_rescale_to_stop_device(const tpb_stop_desc* d, void* cuda_stream) {
+  if (d == nullptr || d->num_trajectories < 0 || d->num_dofs < 1) return TPB_INVALID_ARGUMENT;
+  if (d->num_dofs > 16) return TPB_UNIMPLEMENTED;  // one lane per (joint, sign) candidate
+  if (d->num_trajectories == 0) return TPB_OK;
+  if (!d->begin || !d->length || !d->times || !d->velocities || !d->accelerations ||
+      !d->max_acceleration || !d->count || !d->switch_index || !d->status || !d->out_times ||
+      !d->out_velocities || !d->out_accelerations)
+    return TPB_INVALID_ARGUMENT;
+  tpb::StopArgs p;
+  p.num_traj = d->num_trajectories;
+  p.D = d->num_dofs;
+  p.begin = d->begin;
+  p.length = d->length;
+  p.times = d->times;
+  p.vel = d->velocities;
+  p.acc = d->accelerations;
+  p.max_acc = d->max_acceleration;
+  p.count = d->count;
+  p.switch_index = d->switch_index;
+  p.status = d->status;
+  p.out_times = d->out_times;
+  p.out_vel = d->out_velocities;
+  p.out_acc = d->out_accelerations;
+  tpb::launch_rescale_to_stop(p, static_cast<cudaStream_t>(cuda_stream));
+  return cudaGetLastError() == cudaSuccess ? TPB_OK : TPB_INTERNAL;
+}
+
+int32_t tpb_rescale_to_stop_host(const tpb_stop_desc* hd, int32_t device) {
+  if (hd == nullptr || hd->num_trajectories < 0 || hd->num_dofs < 1 || hd->total_rows < 0)
+    return TPB_INVALID_ARGUMENT;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return TPB_FAILED_PRECONDITION;
+  }
+  if (device < 0 || device >= ndev) return TPB_INVALID_ARGUMENT;
+  if (cudaSetDevice(device) != cudaSuccess) return TPB_INTERNAL;
+  if (hd->num_trajectories == 0) return TPB_OK;
+  const size_t T = hd->num_trajectories, D = hd->num_dofs, R = static_cast<size_t>(hd->total_rows);
+  // every trajectory must lie inside the packed arrays
+  for (size_t b = 0; b < T; ++b) {
+    if (hd->begin[b] < 0 || hd->length[b] < 0 ||
+        hd->begin[b] + hd->length[b] > hd->total_rows)
+      return TPB_INVALID_ARGUMENT;
+  }
+  std::vector<void*> tmp;
+  auto alloc = [&](size_t bytes, void** out) -> cudaError_t {
+    cudaError_t err = cudaMalloc(out, bytes ? bytes : 1);
+    if (err == cudaSuccess) tmp.push_back(*out);
+    return err;
+  };
+  auto up = [&](const void* src, size_t bytes, const void** dst) -> cudaError_t {
+    void* p = nullptr;
+    cudaError_t err = alloc(bytes, &p);
+    if (err != cudaSuccess) return err;
+    *dst = p;
+    return cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice);
+  };
+  tpb_stop_desc d = *hd;
+  cudaError_t err = cudaSuccess;
+  const void* q = nullptr;
+#define TPB_UP(field, bytes)                                        \
+  if (err == cudaSuccess) {                                         \
+    err = up(hd->field, bytes, &q);                                 \
+    d.field = static_cast<decltype(d.field)>(q);                    \
+  }
+  TPB_UP(begin, T * sizeof(int64_t));
+  TPB_UP(length, T * sizeof(int32_t));
+  TPB_UP(times, R * sizeof(double));
+  TPB_UP(velocities, R * D * sizeof(double));
+  TPB_UP(accelerations, R * D * sizeof(double));
+  TPB_UP(max_acceleration, T * D * sizeof(double));
+#undef TPB_UP
+  void* w = nullptr;
+#define TPB_OUT(field, bytes)                                       \
+  if (err == cudaSuccess) {                                         \
+    err = alloc(bytes, &w);                                         \
+    d.field = static_cast<decltype(d.field)>(w);                    \
+  }
+  TPB_OUT(count, T * sizeof(int32_t));
+  TPB_OUT(switch_index, T * sizeof(int32_t));
+  TPB_OUT(status, T * sizeof(int32_t));
+  TPB_OUT(out_times, R * sizeof(double));
+  TPB_OUT(out_velocities, R * D * sizeof(double));
+  TPB_OUT(out_accelerations, R * D * sizeof(double));
+#undef TPB_OUT
+  int32_t rc = TPB_OK;
+  if (err == cudaSuccess) {
+    // rows outside the stopping segments keep what the caller's buffers hold
+    err = cudaMemcpy(d.out_times, hd->out_times, R * sizeof(double), cudaMemcpyHostToDevice);
+    if (err == cudaSuccess)
+      err = cudaMemcpy(d.out_velocities, hd->out_velocities, R * D * sizeof(double),
+                       cudaMemcpyHostToDevice);
+    if (err == cudaSuccess)
+      err = cudaMemcpy(d.out_accelerations, hd->out_accelerations, R * D * sizeof(double),
+                       cudaMemcpyHostToDevice);
+  }
+  if (err == cudaSuccess) {
+    rc = tpb_rescale_to_stop_device(&d, nullptr);
+    if (rc == TPB_OK) err = cudaDeviceSynchronize();
+  }
+#define TPB_DOWN(field, bytes) \
+  if (rc == TPB_OK && err == cudaSuccess) err = cudaMemcpy(hd->field, d.field, bytes, cudaMemcpyDeviceToHost)
+  TPB_DOWN(count, T * sizeof(int32_t));
+  TPB_DOWN(switch_index, T * sizeof(int32_t));
+  TPB_DOWN(status, T * sizeof(int32_t));
+  TPB_DOWN(out_times, R * sizeof(double));
+  TPB_DOWN(out_velocities, R * D * sizeof(double));
+  TPB_DOWN(out_accelerations, R * D * sizeof(double));
+#undef TPB_DOWN
+  for (void* p : tmp) cudaFree(p);
+  if (err != cudaSuccess) {
+    fprintf(stderr, "tpb_rescale_to_stop_host: %s\n", cudaGetErrorString(err));
+    return TPB_INTERNAL;
+  }
+  return rc;
+}
+
 int32_t tpb_spline_eval_device(const tpb_spline_eval_desc* d, void* cuda_stream) {
   if (d == nullptr) return TPB_INVALID_ARGUMENT;
   std::string err;

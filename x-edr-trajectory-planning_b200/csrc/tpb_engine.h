@@ -121,6 +121,18 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
 int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, double dt,
                     int num_sms, cudaStream_t st, bool continued = false);
 
+// Batched RescaleTrajectoryBackwardToStop (tpb_stop.cu); all pointers device.
+struct StopArgs {
+  int num_traj, D;
+  const int64_t* begin;   // [num_traj] first row of trajectory b in the packed arrays
+  const int32_t* length;  // [num_traj] its number of samples
+  const double *times, *vel, *acc;  // [rows], [rows][D], [rows][D]
+  const double* max_acc;            // [num_traj][D]
+  int32_t *count, *switch_index, *status;  // [num_traj]
+  double *out_times, *out_vel, *out_acc;   // layout of the inputs
+};
+int launch_rescale_to_stop(const StopArgs& p, cudaStream_t st);
+
 // The arrays of paths [b0, ...) of a joint-space batch: every per-path pointer
 // advanced by b0 paths (the packed r_* rows are addressed through r_offset and
 // stay where they are).  Used to run the stage kernels on a chunk of the batch.
