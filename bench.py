@@ -340,6 +340,10 @@ def run_ours(args):
         stage_ms["integrate_phases"] = {"setup": phase_ms[0], "sweeps": phase_ms[1],
                                         "finalize": phase_ms[2]}
 
+    # ---- stopping trajectories on the resident resampled batch ----
+    stop = run_stop_leg(pkg, torch, dev, stream, eng, d_amax, B, D, max_over_ranks, barrier,
+                        world, args)
+
     # ---- e2e: host buffers in and out through tpb_plan_joint_host ----
     h_wp = torch.from_numpy(wp).pin_memory()
     h_vmax = torch.from_numpy(vmax).pin_memory()
@@ -427,12 +431,78 @@ def run_ours(args):
             "stage_ms": stage_ms, "paths_ok": n_ok, "resampled_rows_per_gpu": total_rows,
             "mean_duration_s": float(np.nanmean(all_dur)),
             "e2e_matches_device_run": same, "spline_eval": spline,
-            "cartesian": cartesian,
+            "cartesian": cartesian, "stop": stop,
         }
         print(json.dumps(line))
     eng.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+class _DevPtr:
+    """A raw device address with the data_ptr() the binding expects."""
+
+    def __init__(self, ptr):
+        self._p = ptr
+
+    def data_ptr(self):
+        return self._p
+
+
+def run_stop_leg(pkg, torch, dev, stream, eng, d_amax, B, D, max_over_ranks, barrier, world,
+                 args):
+    """Batched RescaleTrajectoryBackwardToStop: every resampled trajectory of the batch is cut
+    at 60 % of its samples (where it still moves) and the fastest stop tracing the tail of what
+    is left is generated, all trajectories in one launch.  Inputs are the engine's packed
+    TPB_ARR_R_* arrays in HBM; CUDA events on the launching stream."""
+    if args.no_stop:
+        return None
+    off = eng.get(pkg.ARR.R_OFFSET).astype(np.int64)
+    rows = int(off[-1])
+    length = np.maximum(2, ((off[1:] - off[:-1]) * 0.6).astype(np.int64)).astype(np.int32)
+    d_begin = torch.from_numpy(off[:-1].copy()).to(dev)
+    d_len = torch.from_numpy(length).to(dev)
+    t_in = _DevPtr(eng.devptr(pkg.ARR.R_TIME)[0])
+    v_in = _DevPtr(eng.devptr(pkg.ARR.R_VEL)[0])
+    a_in = _DevPtr(eng.devptr(pkg.ARR.R_ACC)[0])
+    cnt = torch.zeros(B, dtype=torch.int32, device=dev)
+    sw = torch.zeros(B, dtype=torch.int32, device=dev)
+    st = torch.zeros(B, dtype=torch.int32, device=dev)
+    o_t = torch.empty(rows, dtype=torch.float64, device=dev)
+    o_v = torch.empty(rows * D, dtype=torch.float64, device=dev)
+    o_a = torch.empty(rows * D, dtype=torch.float64, device=dev)
+
+    class _Shape:  # the binding reads .shape of these two
+        def __init__(self, t, shape):
+            self._t, self.shape = t, shape
+
+        def data_ptr(self):
+            return self._t.data_ptr()
+
+    amax = _Shape(d_amax, (B, D))
+    times = _Shape(t_in, (rows,))
+
+    def run():
+        pkg.rescale_to_stop_device(amax, d_begin, d_len, times, v_in, a_in, cnt, sw, st, o_t, o_v,
+                                   o_a, stream=stream.cuda_stream)
+
+    for _ in range(3):
+        run()
+    torch.cuda.synchronize()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = max(3, args.steps)
+    e0.record(stream)
+    for _ in range(reps):
+        run()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = max_over_ranks(e0.elapsed_time(e1)) / reps
+    c = cnt.cpu().numpy()
+    return {"trajectories_per_s": world * B / (ms / 1e3), "ms": ms, "trajectories_per_gpu": B,
+            "ok": int((st.cpu().numpy() == 0).sum()), "mean_input_samples": float(length.mean()),
+            "mean_stop_samples": float(c.mean()), "kernel": "k_rescale_to_stop",
+            "note": "tail of each 4 ms resampled trajectory cut at 60 % of its samples"}
 
 
 def run_cartesian_leg(pkg, torch, dev, stream, local_rank, max_over_ranks, barrier, world, rank,
@@ -539,6 +609,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-spline", action="store_true")
     ap.add_argument("--no-cartesian", action="store_true")
+    ap.add_argument("--no-stop", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

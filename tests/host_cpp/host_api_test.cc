@@ -10,6 +10,7 @@
 
 #include "trajectory_planning/path_timing_batch.h"
 #include "trajectory_planning/path_timing_trajectory.h"
+#include "trajectory_planning/rescale_to_stop.h"
 #include "trajectory_planning/splines/bspline.h"
 #include "trajectory_planning/time_optimal_path_timing.h"
 #include "trajectory_planning/timeable_path_cartesian_spline.h"
@@ -359,6 +360,54 @@ int main() {
     PrintArray("status", st);
     PrintArray("positions", res.positions, false);
     printf("},\n");
+  }
+  // ---- RescaleTrajectoryBackwardToStop (rescale_to_stop_test.cc:29-84)
+  {
+    constexpr int kSampleCount = 200, kJointCount = 4;
+    constexpr double kTimeStepSec = 8e-3, kMaxAcceleration = 2.0;
+    printf("\"stop\": {\n");
+    int idx = 0;
+    for (double velocity : {-1.0, 1.0}) {
+      std::vector<double> times(kSampleCount);
+      std::vector<VectorXd> pos(kSampleCount), vel(kSampleCount), acc(kSampleCount);
+      for (int i = 0; i < kSampleCount; ++i) {
+        times[i] = i * kTimeStepSec;
+        acc[i] = VectorXd::Zero(kJointCount);
+        vel[i] = VectorXd::Constant(kJointCount, velocity);
+        pos[i] = VectorXd::Constant(kJointCount, velocity * times[i]);
+      }
+      auto result = RescaleTrajectoryBackwardToStop(VectorXd::Constant(kJointCount, kMaxAcceleration),
+                                                    times, pos, vel, acc);
+      EXPECT(result.ok());
+      const SampledTrajectory& r = *result;
+      const double ramp_up_time_sec = std::fabs(velocity) / kMaxAcceleration;
+      const double stopping_distance = velocity * velocity / (2.0 * kMaxAcceleration);
+      EXPECT(!r.positions.empty() && r.times.size() == r.positions.size() &&
+             r.times.size() == r.velocities.size() && r.times.size() == r.accelerations.size());
+      if (!r.times.empty()) {
+        EXPECT(std::fabs((r.times.back() - r.times.front()) - ramp_up_time_sec) <= kTimeStepSec);
+        for (int j = 0; j < kJointCount; ++j) {
+          EXPECT(r.velocities.back()[j] == 0.0 && r.accelerations.back()[j] == 0.0);
+          const double moved = r.positions.back()[j] - r.positions.front()[j];
+          EXPECT(std::fabs(moved - stopping_distance * (velocity < 0 ? -1 : 1)) <=
+                 std::fabs(velocity * kTimeStepSec));
+        }
+      }
+      printf("\"case%d\": {\n", idx++);
+      PrintArray("times", r.times);
+      PrintArray("velocities", Flatten(r.velocities));
+      PrintArray("accelerations", Flatten(r.accelerations), false);
+      printf("},\n");
+      // error behaviour: AreInputsValidForSampledTrajectory's statuses come back
+      std::vector<double> bad = times;
+      bad[5] = bad[4];
+      EXPECT(RescaleTrajectoryBackwardToStop(VectorXd::Constant(kJointCount, 2.0), bad, pos, vel, acc)
+                 .status().code() == tp::StatusCode::kInvalidArgument);
+      vel.back() = VectorXd::Zero(kJointCount);  // already stopped: empty result
+      auto empty = RescaleTrajectoryBackwardToStop(VectorXd::Constant(kJointCount, 2.0), times, pos, vel, acc);
+      EXPECT(empty.ok() && (*empty).times.empty());
+    }
+    printf("\"cases\": %d},\n", idx);
   }
   printf("\"failures\": %d\n}\n", g_fail);
   return g_fail ? 1 : 0;

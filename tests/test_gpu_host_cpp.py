@@ -118,3 +118,16 @@ def test_cartesian_path_matches_oracle(result, po):
         rows = np.array(r["constraints_sample10"]).reshape(16, 4)
         assert np.max(np.abs(rows - o["cons"][10])) <= 1e-8
         assert (rows[:7, 3] == 1.6).all() and (rows[14, 3] == 0.25) and (rows[15, 3] == 0.0625)
+
+
+def test_rescale_to_stop_matches_oracle(result, po):
+    """host RescaleTrajectoryBackwardToStop on rescale_to_stop_test.cc's scenario."""
+    import test_oracle_stop as T
+    assert result["stop"]["cases"] == 2
+    for k, velocity in enumerate((-1.0, 1.0)):
+        t, pos, vel, acc = T.constant_velocity_case(velocity)
+        o = po.rescale_to_stop(np.full(4, 2.0), t, pos, vel, acc)
+        c = result["stop"][f"case{k}"]
+        assert np.array_equal(np.array(c["times"]), o["times"])
+        assert np.array_equal(np.array(c["velocities"]).reshape(-1, 4), o["velocities"])
+        assert np.array_equal(np.array(c["accelerations"]).reshape(-1, 4), o["accelerations"])
