@@ -295,6 +295,23 @@ int32_t tpb_spline_eval_device(const tpb_spline_eval_desc* d, void* cuda_stream)
 /* Same with host pointers (allocates, copies in, evaluates, copies out). */
 int32_t tpb_spline_eval_host(const tpb_spline_eval_desc* d, int32_t device);
 
+/* ---- stop queries ----------------------------------------- */
+/* Batched PathTimingTrajectory::GetPathStopParameter (path_timing_trajectory.cc:
+ * 235-287) with ComputeFastestStop (:75-172) on the engine's resampled
+ * trajectories (after tpb_resample / tpb_plan_joint_host): for path b, starting
+ * at the first resampled row at or after time_sec[b], time is scaled forward
+ * from rate 1 with the largest deceleration the acceleration limits admit until
+ * the rate reaches 0.  stop_parameter[b] is the path parameter of the row where
+ * that happens (the reference's return value), stop_row[b] that row's index in
+ * the path's trajectory, stop_duration[b] the duration of the stop.  status[b] is
+ * TPB_PATH_FAIL_SETUP when time_sec[b] lies after the trajectory (the reference
+ * returns kInvalidArgument), TPB_PATH_OK otherwise.  Output pointers may be NULL.
+ * Uses the acceleration limits as set (no safety factor), like the reference.
+ * With host pointers the call returns when the results are in place. */
+int32_t tpb_path_stop_parameter(tpb_engine* e, const double* time_sec, double* stop_parameter,
+                                int32_t* stop_row, double* stop_duration, int32_t* status,
+                                int32_t on_device);
+
 /* ---- stopping trajectories ------------------------------ */
 /* Batched RescaleTrajectoryBackwardToStop (rescale_to_stop.cc:35-161, declared
  * in rescale_to_stop.h:31-35): for each sampled trajectory the fastest stop that

@@ -169,6 +169,11 @@ def lib():
         L.orc_rescale_to_stop.restype = C.c_int
         L.orc_rescale_to_stop.argtypes = [C.c_int, C.c_int] + [c_double_p] * 4 + [
             C.POINTER(C.c_int), C.POINTER(C.c_int)] + [c_double_p] * 3
+        L.orc_fastest_stop.restype = C.c_int
+        L.orc_fastest_stop.argtypes = [C.c_int, C.c_int] + [c_double_p] * 8 + [C.POINTER(C.c_int)]
+        L.orc_path_stop_parameter.restype = C.c_int
+        L.orc_path_stop_parameter.argtypes = [C.c_int, C.c_int] + [c_double_p] * 5 + [
+            C.c_double, c_double_p, C.POINTER(C.c_int), c_double_p]
         _lib = L
     return _lib
 
@@ -403,6 +408,38 @@ def rescale_to_stop(max_acc, times, positions, velocities, accelerations, impl="
         op = op[:m].copy()
     return dict(status=st, count=m, switch_index=sw.value, times=ot[:m].copy(), positions=op,
                 velocities=ov[:m].copy(), accelerations=oa[:m].copy())
+
+
+def fastest_stop(stop_acc, times, velocities, accelerations):
+    """ComputeFastestStop: dict(stop_index, duration, time, rate2, diff)."""
+    t = np.ascontiguousarray(times, np.float64)
+    v = np.ascontiguousarray(velocities, np.float64)
+    a = np.ascontiguousarray(accelerations, np.float64)
+    sa = np.ascontiguousarray(stop_acc, np.float64)
+    n, D = v.shape
+    dur = np.zeros(1)
+    st, sr, sd = np.zeros(n + 1), np.zeros(n + 1), np.zeros(n + 1)
+    ns = C.c_int(0)
+    idx = lib().orc_fastest_stop(n, D, _dp(sa), _dp(t), _dp(v), _dp(a), _dp(dur), _dp(st),
+                                 _dp(sr), _dp(sd), C.byref(ns))
+    k = ns.value
+    return dict(stop_index=idx, duration=float(dur[0]), time=st[:k].copy(), rate2=sr[:k].copy(),
+                diff=sd[:k].copy())
+
+
+def path_stop_parameter(time, path_parameter, velocities, accelerations, max_acc, query_time):
+    """GetPathStopParameter on a resampled trajectory: dict(status, parameter, row, duration)."""
+    t = np.ascontiguousarray(time, np.float64)
+    s = np.ascontiguousarray(path_parameter, np.float64)
+    v = np.ascontiguousarray(velocities, np.float64)
+    a = np.ascontiguousarray(accelerations, np.float64)
+    am = np.ascontiguousarray(max_acc, np.float64)
+    M, D = v.shape
+    par, dur = np.zeros(1), np.zeros(1)
+    row = C.c_int(0)
+    st = lib().orc_path_stop_parameter(M, D, _dp(t), _dp(s), _dp(v), _dp(a), _dp(am),
+                                       float(query_time), _dp(par), C.byref(row), _dp(dur))
+    return dict(status=st, parameter=float(par[0]), row=row.value, duration=float(dur[0]))
 
 
 # ----------------------------------------------------------------- Cartesian path

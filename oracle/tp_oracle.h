@@ -189,6 +189,17 @@ int orc_rescale_to_stop(int n, int D, const double* max_acc, const double* times
                         const double* vel, const double* acc, int* count, int* switch_index,
                         double* out_times, double* out_vel, double* out_acc);
 
+/* ---- ComputeFastestStop / GetPathStopParameter (path_timing_trajectory.cc:75-172,
+ * 235-287).  Restated; pinned through the reference test's properties only. */
+int orc_fastest_stop(int n, int D, const double* stop_acc, const double* times,
+                     const double* vel, const double* acc, double* total_duration,
+                     double* series_time, double* series_rate2, double* series_diff,
+                     int* num_series);
+int orc_path_stop_parameter(int M, int D, const double* time, const double* path_parameter,
+                            const double* vel, const double* acc, const double* max_acc,
+                            double query_time, double* stop_parameter, int* stop_row,
+                            double* stop_duration);
+
 #ifdef __cplusplus
 }
 #endif

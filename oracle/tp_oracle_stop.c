@@ -108,3 +108,101 @@ int orc_rescale_to_stop(int n, int D, const double* max_acc, const double* times
   *switch_index = sw;
   return ORC_OK;
 }
+
+/* ---------------------------------------------------------------------------
+ * ComputeFastestStop (path_timing_trajectory.cc:75-172) and
+ * PathTimingTrajectory::GetPathStopParameter (:235-287).
+ *
+ * PARITY: restated line by line; the reference file cannot be compiled on its
+ * own here (it needs eigenmath / genit), and the reference's test
+ * (path_timing_trajectory_test.cc:942-992) states properties, no values: pinned
+ * through those properties only.
+ * ------------------------------------------------------------------------- */
+
+/* Forward time scaling from rate 1 until the rate reaches 0: returns the index
+ * (relative to the first sample) of the last sample used, writes the stopping
+ * duration.  Optional series outputs (n+1 capacity each, may be NULL) receive
+ * what the reference passes to append_time / append_rate_squared /
+ * append_diff_rate_squared; *num_series their count. */
+int orc_fastest_stop(int n, int D, const double* stop_acc, const double* times,
+                     const double* vel, const double* acc, double* total_duration,
+                     double* series_time, double* series_rate2, double* series_diff,
+                     int* num_series) {
+  double total = 0.0;
+  double rate_squared = 1.0;
+  double diff_rate_squared = 0.0;
+  const double first_time_point = times[0];
+  int path_index;
+  int ns = 0;
+  for (path_index = 0; (path_index < n - 1) && (rate_squared > 0.0); path_index++) {
+    const double* v = vel + (size_t)path_index * D;
+    const double* a = acc + (size_t)path_index * D;
+    double diff_min = 0.0;
+    for (int dof = 0; dof < D; dof++) {
+      const double kEpsilon = 1e-6;
+      if (fabs(v[dof]) < kEpsilon) continue;
+      for (int s = 0; s < 2; ++s) {
+        const double bias_dof = a[dof] * rate_squared;
+        const double d = (s == 0) ? 2.0 * (-bias_dof - stop_acc[dof]) / v[dof]
+                                  : 2.0 * (-bias_dof + stop_acc[dof]) / v[dof];
+        double mn = INFINITY, mx = -INFINITY;
+        for (int k = 0; k < D; ++k) {
+          const double ak = a[k] * rate_squared + 0.5 * v[k] * d;
+          const double hi = stop_acc[k] - ak;
+          const double lo = -stop_acc[k] - ak;
+          if (hi < mn) mn = hi;
+          if (lo > mx) mx = lo;
+        }
+        const int valid = (mn >= -1e-10) && (mx <= 1e-10);
+        if (valid && d < diff_min) diff_min = d;
+      }
+    }
+    diff_rate_squared = (0.0 < diff_min) ? 0.0 : diff_min; /* std::min(diff_min, 0.0) */
+    if (series_time) series_time[ns] = first_time_point + total;
+    if (series_rate2) series_rate2[ns] = rate_squared;
+    if (series_diff) series_diff[ns] = diff_rate_squared;
+    ++ns;
+    const double unscaled_dt = times[path_index + 1] - times[path_index];
+    const double cand = rate_squared + unscaled_dt * diff_rate_squared;
+    const double next_rate_squared = (0.0 < cand) ? cand : 0.0; /* std::max(0.0, cand) */
+    const double dt = 2.0 * unscaled_dt / (sqrt(rate_squared) + sqrt(next_rate_squared));
+    total += dt;
+    rate_squared = next_rate_squared;
+  }
+  if (series_time) series_time[ns] = first_time_point + total;
+  if (series_rate2) series_rate2[ns] = rate_squared;
+  if (series_diff) series_diff[ns] = diff_rate_squared;
+  ++ns;
+  if (num_series) *num_series = ns;
+  if (path_index >= n) path_index = n - 1;
+  *total_duration = total;
+  return path_index;
+}
+
+/* GetPathStopParameter on a resampled trajectory of M rows (time, path parameter,
+ * velocities, accelerations).  Returns ORC_OK and writes *stop_parameter, the
+ * absolute row *stop_row and *stop_duration; ORC_FAIL_SETUP when time is past
+ * the trajectory (kInvalidArgument in the reference). */
+int orc_path_stop_parameter(int M, int D, const double* time, const double* path_parameter,
+                            const double* vel, const double* acc, const double* max_acc,
+                            double query_time, double* stop_parameter, int* stop_row,
+                            double* stop_duration) {
+  /* absl::c_lower_bound(time_, double_time) */
+  int lo = 0, hi = M;
+  while (lo < hi) {
+    const int mid = lo + (hi - lo) / 2;
+    if (time[mid] < query_time) lo = mid + 1; else hi = mid;
+  }
+  *stop_duration = 0.0;
+  if (lo == M) return ORC_FAIL_SETUP;
+  if (lo == M - 1) {
+    *stop_parameter = path_parameter[M - 1];
+    *stop_row = M - 1;
+    return ORC_OK;
+  }
+  const int rel = orc_fastest_stop(M - lo, D, max_acc, time + lo, vel + (size_t)lo * D,
+                                   acc + (size_t)lo * D, stop_duration, NULL, NULL, NULL, NULL);
+  *stop_row = rel + lo;
+  *stop_parameter = path_parameter[*stop_row];
+  return ORC_OK;
+}

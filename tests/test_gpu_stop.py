@@ -130,3 +130,60 @@ def test_too_many_dofs_is_unimplemented():
     with pytest.raises(pkg.TpbError) as ei:
         pkg.rescale_to_stop_host(np.ones((1, D)), [0], [n], t, np.ones((n, D)), np.zeros((n, D)))
     assert ei.value.code == 12
+
+
+# ---- GetPathStopParameter / ComputeFastestStop on the engine's resampled batch ----
+def test_path_stop_parameter_matches_oracle_bitwise():
+    B, W, D, N, dt = 24, 6, 7, 400, 0.004
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=777)
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * 8000)
+    eng.set_joint_waypoints(wp)
+    eng.set_joint_limits(vmax, amax)
+    eng.sample_paths()
+    eng.optimize()
+    eng.resample(0.0, dt)
+    off = eng.get(pkg.ARR.R_OFFSET)
+    rt, rs = eng.get(pkg.ARR.R_TIME), eng.get(pkg.ARR.R_S)
+    rv, ra = eng.get(pkg.ARR.R_VEL).reshape(-1, D), eng.get(pkg.ARR.R_ACC).reshape(-1, D)
+    rng = np.random.default_rng(3)
+    for trial in range(4):
+        if trial == 0:
+            query = np.zeros(B)                        # from the start
+        elif trial == 1:
+            query = np.array([rt[off[b + 1] - 1] for b in range(B)])   # from the last sample
+        elif trial == 2:
+            query = np.array([rt[off[b + 1] - 1] + 1.0 for b in range(B)])  # past the end
+        else:
+            query = np.array([rng.uniform(0, rt[off[b + 1] - 1]) for b in range(B)])
+        got = eng.path_stop_parameter(query)
+        for b in range(B):
+            sl = slice(off[b], off[b + 1])
+            o = orc.path_stop_parameter(rt[sl], rs[sl], rv[sl], ra[sl], amax[b], query[b])
+            assert (got["status"][b] == 0) == (o["status"] == 0)
+            if o["status"] != 0:
+                continue
+            assert got["row"][b] == o["row"]
+            assert got["parameter"][b] == o["parameter"]
+            assert got["duration"][b] == o["duration"]
+    eng.close()
+
+
+def test_path_stop_parameter_reference_test_scenario():
+    """path_timing_trajectory_test.cc:942-992 through the engine."""
+    wp = np.array([[[0.0, 0, 0], [1, 1, 1], [2, 2, 2]]])
+    eng = pkg.Engine(max_paths=1, num_samples=500, num_dofs=3, max_waypoints=3,
+                     max_time_samples_total=20000)
+    eng.set_path_options(constraint_safety=1.0)
+    eng.set_joint_waypoints(wp)
+    eng.set_joint_limits(np.ones((1, 3)), np.full((1, 3), 2.0))
+    eng.sample_paths()
+    eng.optimize()
+    eng.resample(0.0, 0.001)
+    rs, rt = eng.get(pkg.ARR.R_S), eng.get(pkg.ARR.R_TIME)
+    q = eng.path_stop_parameter([0.0])
+    assert q["status"][0] == 0
+    assert np.searchsorted(rs, q["parameter"][0], side="right") <= 3
+    q = eng.path_stop_parameter([rt[-1]])
+    assert q["parameter"][0] == rs[-1]
+    eng.close()

@@ -102,3 +102,41 @@ def test_port_matches_committed_golden_vectors():
         assert r["count"] == int(g[f"count_{c}"]) and r["switch_index"] == int(g[f"switch_{c}"])
         for k in ("times", "velocities", "accelerations"):
             assert r[k].tobytes() == g[f"out_{k}_{c}"].tobytes(), (c, k)
+
+
+# ---- ComputeFastestStop / GetPathStopParameter --------------------------------
+def test_path_stop_parameter_reference_test_properties():
+    """path_timing_trajectory_test.cc:942-992 (GetPathStopParameterWorksInSimpleCase):
+    collinear 3-dof waypoints, safety 1, 500 samples, 1 ms time step."""
+    wp = np.array([[0.0, 0, 0], [1, 1, 1], [2, 2, 2]])
+    amax = np.full(3, 2.0)
+    r = orc.plan_joint(wp, np.ones(3), amax, 500, safety=1.0, dt=0.001, M_cap=20000)
+    assert r["ok"]
+    args = (r["r_t"], r["r_s"], r["r_vel"], r["r_acc"], amax)
+    # from the first sample the path can stop (almost) immediately
+    q = orc.path_stop_parameter(*args, 0.0)
+    assert q["status"] == 0
+    assert np.searchsorted(r["r_s"], q["parameter"], side="right") <= 3
+    # from the last sample the parameter is the final one
+    q = orc.path_stop_parameter(*args, r["r_t"][-1])
+    assert q["status"] == 0 and q["parameter"] == r["r_s"][-1]
+    assert np.searchsorted(r["r_s"], q["parameter"], side="right") == len(r["r_s"])
+    # past the trajectory: the reference returns kInvalidArgument
+    assert orc.path_stop_parameter(*args, r["r_t"][-1] + 1.0)["status"] != 0
+    # in between: the stop lasts about |v| / a_max and ends where the scaled trajectory rests
+    k = r["M"] // 3
+    q = orc.path_stop_parameter(*args, r["r_t"][k])
+    v = np.abs(r["r_vel"][k]).max()
+    assert q["row"] > k and abs(q["duration"] - v / 2.0) < 0.05 * v / 2.0 + 2e-3
+
+
+def test_fastest_stop_series_is_consistent():
+    t, pos, vel, acc = constant_velocity_case(1.0)
+    f = orc.fastest_stop(np.full(4, 2.0), t, vel, acc)
+    assert f["rate2"][0] == 1.0 and f["rate2"][-1] == 0.0
+    assert np.all(np.diff(f["rate2"]) <= 0) and np.all(f["diff"] <= 0)
+    # v / a_max = 0.5 in the continuum; the trapezoidal time of the last step, where the
+    # rate reaches 0, overshoots by O(sqrt(time step))
+    assert 0.5 <= f["duration"] <= 0.5 + 2.0 * np.sqrt(8e-3)
+    assert abs(f["time"][-1] - (t[0] + f["duration"])) < 1e-15
+    assert f["stop_index"] == len(f["time"]) - 1

@@ -140,6 +140,8 @@ def lib():
         L.tpb_spline_eval_device.argtypes = [C.POINTER(_SplineDesc), vp]
         L.tpb_spline_eval_host.restype = i32
         L.tpb_spline_eval_host.argtypes = [C.POINTER(_SplineDesc), i32]
+        L.tpb_path_stop_parameter.restype = i32
+        L.tpb_path_stop_parameter.argtypes = [vp, vp, vp, vp, vp, vp, i32]
         L.tpb_rescale_to_stop_device.restype = i32
         L.tpb_rescale_to_stop_device.argtypes = [C.POINTER(_StopDesc), vp]
         L.tpb_rescale_to_stop_host.restype = i32
@@ -305,6 +307,17 @@ class Engine:
             ptrs.append(p)
             dev = dev or d
         self._ck(lib().tpb_optimize(self._h, *ptrs, max_loops, dev))
+
+    def path_stop_parameter(self, time_sec):
+        """Batched GetPathStopParameter on the resampled trajectories (host arrays).
+        Returns dict(parameter [B], row [B], duration [B], status [B])."""
+        t = _f64(np.broadcast_to(np.asarray(time_sec, np.float64), (self.B,)).copy())
+        out = dict(parameter=np.zeros(self.B), row=np.zeros(self.B, np.int32),
+                   duration=np.zeros(self.B), status=np.zeros(self.B, np.int32))
+        self._ck(lib().tpb_path_stop_parameter(self._h, t.ctypes.data, out["parameter"].ctypes.data,
+                                               out["row"].ctypes.data, out["duration"].ctypes.data,
+                                               out["status"].ctypes.data, 0))
+        return out
 
     def time_phases(self, on=True):
         """Record CUDA events around the three phases of every optimize()."""

@@ -43,6 +43,9 @@ struct tpb_engine {
   cudaEvent_t phase_ev[4] = {};  // tpb_time_phases
   bool time_phases = false;
   int64_t* chunk_rows = nullptr;  // pinned host: rows up to the end of chunk c
+  // tpb_path_stop_parameter scratch: [Bmax] each
+  double *sq_query = nullptr, *sq_parameter = nullptr, *sq_duration = nullptr;
+  int32_t *sq_row = nullptr, *sq_status = nullptr;
 };
 
 namespace {
@@ -809,6 +812,60 @@ int32_t tpb_devptr(tpb_engine* e, tpb_array what, void** ptr, size_t* bytes) {
   if (!lookup(e, what, &r) || r.ptr == nullptr) return fail(e, TPB_NOT_FOUND, "unknown array");
   *ptr = r.ptr;
   if (bytes) *bytes = r.bytes;
+  return TPB_OK;
+}
+
+int32_t tpb_path_stop_parameter(tpb_engine* e, const double* time_sec, double* stop_parameter,
+                                int32_t* stop_row, double* stop_duration, int32_t* status,
+                                int32_t on_device) {
+  if (e == nullptr || time_sec == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (!e->resampled) return fail(e, TPB_FAILED_PRECONDITION, "no resampled trajectories");
+  if (d.D > 16) return fail(e, TPB_UNIMPLEMENTED, "stop queries need num_dofs <= 16");
+  cudaSetDevice(e->device);
+  if (e->sq_query == nullptr) {
+    TPB_CUDA(e, dev_alloc(e, &e->sq_query, d.Bmax));
+    TPB_CUDA(e, dev_alloc(e, &e->sq_parameter, d.Bmax));
+    TPB_CUDA(e, dev_alloc(e, &e->sq_duration, d.Bmax));
+    TPB_CUDA(e, dev_alloc(e, &e->sq_row, d.Bmax));
+    TPB_CUDA(e, dev_alloc(e, &e->sq_status, d.Bmax));
+  }
+  tpb::StopQueryArgs p;
+  p.B = d.B;
+  p.D = d.D;
+  p.offset = e->a.r_offset;
+  p.times = e->a.r_time;
+  p.s = e->a.r_s;
+  p.vel = e->a.r_vel;
+  p.acc = e->a.r_acc;
+  p.max_acc = e->a.amax;  // path_->GetMaxJointAcceleration(): the limit itself, no safety factor
+  if (on_device) {
+    p.query = time_sec;
+    p.parameter = stop_parameter ? stop_parameter : e->sq_parameter;
+    p.row = stop_row ? stop_row : e->sq_row;
+    p.duration = stop_duration ? stop_duration : e->sq_duration;
+    p.status = status ? status : e->sq_status;
+  } else {
+    TPB_CUDA(e, copy_in(e, e->sq_query, time_sec, sizeof(double) * d.B, 0));
+    p.query = e->sq_query;
+    p.parameter = e->sq_parameter;
+    p.row = e->sq_row;
+    p.duration = e->sq_duration;
+    p.status = e->sq_status;
+  }
+  e->launches += tpb::launch_path_stop_parameter(p, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  if (!on_device) {
+    auto down = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
+      if (dst == nullptr) return cudaSuccess;
+      return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, e->stream);
+    };
+    TPB_CUDA(e, down(stop_parameter, e->sq_parameter, sizeof(double) * d.B));
+    TPB_CUDA(e, down(stop_row, e->sq_row, sizeof(int32_t) * d.B));
+    TPB_CUDA(e, down(stop_duration, e->sq_duration, sizeof(double) * d.B));
+    TPB_CUDA(e, down(status, e->sq_status, sizeof(int32_t) * d.B));
+    TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+  }
   return TPB_OK;
 }
 

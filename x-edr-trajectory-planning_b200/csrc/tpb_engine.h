@@ -133,6 +133,20 @@ struct StopArgs {
 };
 int launch_rescale_to_stop(const StopArgs& p, cudaStream_t st);
 
+// Batched GetPathStopParameter over packed resampled trajectories (tpb_stop.cu).
+struct StopQueryArgs {
+  int B, D;
+  const int64_t* offset;                // [B+1] rows of trajectory b: offset[b] .. offset[b+1]-1
+  const double *times, *s, *vel, *acc;  // [rows], [rows], [rows][D], [rows][D]
+  const double* max_acc;                // [B][D]
+  const double* query;                  // [B] query times
+  double* parameter;                    // [B] path parameter at which the path can stop
+  int32_t* row;                         // [B] its row within the trajectory
+  double* duration;                     // [B] duration of the stop
+  int32_t* status;                      // [B]
+};
+int launch_path_stop_parameter(const StopQueryArgs& p, cudaStream_t st);
+
 // The arrays of paths [b0, ...) of a joint-space batch: every per-path pointer
 // advanced by b0 paths (the packed r_* rows are addressed through r_offset and
 // stay where they are).  Used to run the stage kernels on a chunk of the batch.
