@@ -361,6 +361,47 @@ int main() {
     PrintArray("positions", res.positions, false);
     printf("},\n");
   }
+  // ---- GetPathStopParameterWorksInSimpleCase (path_timing_trajectory_test.cc:942-992),
+  // with delta chosen so that the path fits one planning window
+  {
+    constexpr int kStopSamples = 500;
+    auto path = std::make_shared<TimeableJointSplinePath>(JointPathOptions()
+                                                              .set_num_dofs(kNDof)
+                                                              .set_constraint_safety(1.0)
+                                                              .set_num_path_samples(kStopSamples)
+                                                              .set_delta_parameter(0.008));
+    PathTimingTrajectory planner(PathTimingTrajectoryOptions()
+                                     .SetTimeStep(tp::Milliseconds(1))
+                                     .SetNumDofs(kNDof)
+                                     .SetNumPathSamples(kStopSamples));
+    // no plan yet: beginning of the path (.cc:239-242)
+    EXPECT(planner.SetPath(path).ok());
+    auto none = planner.GetPathStopParameter(TimeFromSec(0.0));
+    EXPECT(none.ok() && *none == 0.0);
+    EXPECT(path->SetWaypoints(std::vector<VectorXd>{VectorXd{0, 0, 0}, VectorXd{1, 1, 1}, VectorXd{2, 2, 2}}).ok());
+    VectorXd vmax = VectorXd::Constant(kNDof, 1.0), amax = VectorXd::Constant(kNDof, 2.0);
+    EXPECT(path->SetMaxJointVelocity(ToSpan(vmax)).ok());
+    EXPECT(path->SetMaxJointAcceleration(ToSpan(amax)).ok());
+    EXPECT(planner.Plan(TimeFromSec(0.0), tp::Seconds(100)).ok());
+    // starting from the first sample we can stop (almost) immediately
+    auto first = planner.GetPathStopParameter(TimeFromSec(0.0));
+    EXPECT(first.ok());
+    const auto& ps = planner.GetPathParameters();
+    const long stop_index = std::upper_bound(ps.begin(), ps.end(), *first) - ps.begin();
+    EXPECT(stop_index <= 3);
+    // starting from the last sample the parameter is the final value
+    auto last = planner.GetPathStopParameter(TimeFromSec(planner.GetTime().back()));
+    EXPECT(last.ok() && *last == ps.back());
+    EXPECT(std::upper_bound(ps.begin(), ps.end(), *last) == ps.end());
+    // past the end: kInvalidArgument (.cc:244-248)
+    EXPECT(planner.GetPathStopParameter(TimeFromSec(planner.GetTime().back() + 1.0)).status().code() ==
+           tp::StatusCode::kInvalidArgument);
+    const double mid_time = planner.GetTime()[planner.GetTime().size() / 3];
+    auto mid = planner.GetPathStopParameter(TimeFromSec(mid_time));
+    EXPECT(mid.ok());
+    printf("\"stop_query\": {\"first\": %.17g, \"last\": %.17g, \"mid_time\": %.17g, \"mid\": %.17g},\n",
+           *first, *last, mid_time, *mid);
+  }
   // ---- RescaleTrajectoryBackwardToStop (rescale_to_stop_test.cc:29-84)
   {
     constexpr int kSampleCount = 200, kJointCount = 4;

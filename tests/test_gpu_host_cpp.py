@@ -131,3 +131,18 @@ def test_rescale_to_stop_matches_oracle(result, po):
         assert np.array_equal(np.array(c["times"]), o["times"])
         assert np.array_equal(np.array(c["velocities"]).reshape(-1, 4), o["velocities"])
         assert np.array_equal(np.array(c["accelerations"]).reshape(-1, 4), o["accelerations"])
+
+
+def test_path_stop_parameter_matches_oracle(result, po):
+    """host GetPathStopParameter on path_timing_trajectory_test.cc:942-992's scenario."""
+    wp = np.array([[0.0, 0, 0], [1, 1, 1], [2, 2, 2]])
+    amax = np.full(3, 2.0)
+    o = po.plan_joint(wp, np.ones(3), amax, 500, safety=1.0, delta=0.008, dt=0.001, M_cap=20000)
+    assert o["ok"]
+    args = (o["r_t"], o["r_s"], o["r_vel"], o["r_acc"], amax)
+    q = result["stop_query"]
+    assert q["first"] == po.path_stop_parameter(*args, 0.0)["parameter"]
+    assert q["last"] == o["r_s"][-1]
+    # TimeFromSec quantises the query time to nanoseconds
+    t = po.time_to_sec(po.time_from_sec(q["mid_time"]))
+    assert q["mid"] == po.path_stop_parameter(*args, t)["parameter"]

@@ -10,8 +10,8 @@
 // Scope: a fresh path (State::kNewPath) whose
 // planning loop needs one path window, plus the "already planned enough"
 // re-entry (.cc:590-601).  Moving-horizon re-planning across windows,
-// kSkipSamplesCloserThanTimeStep and GetPathStopParameter are "next" rows and
-// return kUnimplemented.  Paths must be TimeableJointSplinePath.
+// kSkipSamplesCloserThanTimeStep is a "next" row and returns kUnimplemented;
+// GetPathStopParameter runs on the device.  Paths must be TimeableJointSplinePath.
 #ifndef TRAJECTORY_PLANNING_PATH_TIMING_TRAJECTORY_H_
 #define TRAJECTORY_PLANNING_PATH_TIMING_TRAJECTORY_H_
 
@@ -241,8 +241,29 @@ class PathTimingTrajectory : public TrajectoryPlanner {
                     [](tp::Time a, tp::Time b) { return a < b; });
   }
   void SetProfileDebugVerbosity(int) {}
-  tp::StatusOr<double> GetPathStopParameter(tp::Time) const {
-    return tp::UnimplementedError("GetPathStopParameter is outside the hot path (next-2)");
+  // GetPathStopParameter (.cc:235-287): the path parameter at which the path can be
+  // stopped when braking from `time` on; ComputeFastestStop (.cc:75-172) runs on
+  // the device over the resampled trajectory (tpb_path_stop_parameter).
+  tp::StatusOr<double> GetPathStopParameter(tp::Time time) const {
+    const double double_time = TimeToSec(time);
+    if (!initial_plan_) return 0.0;  // no plan yet: beginning of the path
+    const auto time_it = std::lower_bound(time_.begin(), time_.end(), double_time);
+    if (time_it == time_.end()) {
+      return tp::InvalidArgumentError("Time " + std::to_string(double_time) +
+                                      " not in timed path range");
+    }
+    if (time_it == std::prev(time_.end())) return path_parameter_.back();
+    tpb_engine* e = path_ ? path_->DeviceEngine() : nullptr;
+    if (e == nullptr) return tp::FailedPreconditionError("path has no device engine");
+    double parameter = 0.0;
+    int32_t status = TPB_PATH_NOT_RUN;
+    const int32_t rc = tpb_path_stop_parameter(e, &double_time, &parameter, nullptr, nullptr, &status, 0);
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
+    if (status != TPB_PATH_OK) {
+      return tp::InvalidArgumentError("Time " + std::to_string(double_time) +
+                                      " not in timed path range");
+    }
+    return parameter;
   }
   const PathTimingTrajectoryOptions& GetOptions() const { return options_; }
 
