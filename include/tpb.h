@@ -232,6 +232,14 @@ int32_t tpb_last_phase_ms(tpb_engine* e, double* ms3);
  * *total_samples (may be NULL) receives R_OFFSET[B] (this synchronises). */
 int32_t tpb_resample(tpb_engine* e, double start_sec, double time_step_sec,
                      int64_t* total_samples);
+/* The same with TimeSamplingMethod::kSkipSamplesCloserThanTimeStep
+ * (ResampleSkippingSamplesCloserThanTimeStep, path_timing_trajectory.cc:785-836):
+ * row 0 is interpolated at start_sec, then every path sample whose time lies at
+ * least GetMinTimeDeltaToKeep() = 0.95 * time_step_sec (:893-900) after the last
+ * kept row is copied; the last kept row gets the final position and zero
+ * derivatives.  A path yields at most N + 1 rows. */
+int32_t tpb_resample_skipping(tpb_engine* e, double start_sec, double time_step_sec,
+                              int64_t* total_samples);
 
 /* Whole pipeline for a batch of fresh joint paths with HOST buffers in and out:
  * set waypoints+limits, sample, optimize, resample, copy back durations,

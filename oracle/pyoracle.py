@@ -54,7 +54,7 @@ class _PlanCfg(C.Structure):
     _fields_ = [("N", C.c_int), ("dim", C.c_int), ("W", C.c_int),
                 ("rounding", C.c_double), ("safety", C.c_double),
                 ("delta", C.c_double), ("start_sec", C.c_double),
-                ("dt", C.c_double)]
+                ("dt", C.c_double), ("skip_method", C.c_int)]
 
 
 class _PlanOut(C.Structure):
@@ -163,6 +163,9 @@ def lib():
         L.orc_plan_cart_fake.argtypes = [C.POINTER(_CartCfg), c_double_p, c_double_p,
                                          c_double_p, c_double_p, C.POINTER(_PlanOut),
                                          c_double_p, c_double_p, c_double_p, c_double_p]
+        L.orc_resample_skip.restype = C.c_int
+        L.orc_resample_skip.argtypes = [C.c_int, C.c_int] + [c_double_p] * 8 + [
+            C.c_double, C.c_double] + [c_double_p] * 7
         # stopping trajectories (tp_oracle_stop.c)
         L.orc_sampled_trajectory_inputs_valid.restype = C.c_int
         L.orc_sampled_trajectory_inputs_valid.argtypes = [C.c_int, c_double_p]
@@ -357,13 +360,15 @@ def query(sol, s_start, s_end, t):
 
 # ----------------------------------------------------------------- stage D
 def plan_joint(waypoints, vmax, amax, N, rounding=0.2, safety=0.8, delta=-1.0,
-               start_sec=0.0, dt=0.0, M_cap=0, impl="port"):
-    """One fresh joint path, single window.  impl: 'port' | 'ref'."""
+               start_sec=0.0, dt=0.0, M_cap=0, impl="port", skip=False):
+    """One fresh joint path, single window.  impl: 'port' | 'ref'.  skip: resample with
+    kSkipSamplesCloserThanTimeStep (port only; M_cap >= N + 1)."""
     wp = np.ascontiguousarray(waypoints, np.float64)
     vmax = np.ascontiguousarray(vmax, np.float64)
     amax = np.ascontiguousarray(amax, np.float64)
     W, D = wp.shape
-    cfg = _PlanCfg(N, D, W, rounding, safety, delta, start_sec, dt)
+    cfg = _PlanCfg(N, D, W, rounding, safety, delta, start_sec, dt, 1 if skip else 0)
+    assert not (skip and impl != "port")
     o = {k: np.full(N, np.nan) for k in ("time", "s", "sd", "sdd")}
     o.update({k: np.zeros((N, D)) for k in ("q", "dq", "ddq", "vel", "acc")})
     r = {"r_t": np.zeros(M_cap), "r_s": np.zeros(M_cap), "r_sd": np.zeros(M_cap),
@@ -380,6 +385,23 @@ def plan_joint(waypoints, vmax, amax, N, rounding=0.2, safety=0.8, delta=-1.0,
                delta=out.delta_used, knot_end=out.knot_end, M=M,
                last_extremal_index=out.last_extremal_index)
     return res
+
+
+def resample_skip(plan, amax, start_sec, dt):
+    """ResampleSkippingSamplesCloserThanTimeStep on the path samples of plan_joint's result."""
+    N, D = plan["q"].shape
+    amax = np.ascontiguousarray(amax, np.float64)
+    r = {"r_t": np.zeros(N + 1), "r_s": np.zeros(N + 1), "r_sd": np.zeros(N + 1),
+         "r_sdd": np.zeros(N + 1), "r_pos": np.zeros((N + 1, D)), "r_vel": np.zeros((N + 1, D)),
+         "r_acc": np.zeros((N + 1, D))}
+    M = lib().orc_resample_skip(N, D, _dp(plan["time"]), _dp(plan["s"]), _dp(plan["sd"]),
+                                _dp(plan["sdd"]), _dp(plan["q"]), _dp(plan["vel"]),
+                                _dp(plan["acc"]), _dp(amax), float(start_sec), float(dt),
+                                _dp(r["r_t"]), _dp(r["r_pos"]), _dp(r["r_vel"]), _dp(r["r_acc"]),
+                                _dp(r["r_s"]), _dp(r["r_sd"]), _dp(r["r_sdd"]))
+    out = {k: v[:M].copy() for k, v in r.items()}
+    out["M"] = M
+    return out
 
 
 # ----------------------------------------------------------------- stopping trajectory

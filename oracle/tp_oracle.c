@@ -1048,6 +1048,65 @@ void orc_resample_uniform(int N, int dim, const double* time_ps,
   }
 }
 
+/* ResampleSkippingSamplesCloserThanTimeStep (:785-836) with InterpolateAtTime
+ * (:709-753) for the first row and GetMinTimeDeltaToKeep (:893-900).  Output
+ * capacity N + 1 rows; returns the number of rows. */
+int orc_resample_skip(int N, int dim, const double* time_ps, const double* s_ps,
+                      const double* sd_ps, const double* sdd_ps, const double* pos_ps,
+                      const double* vel_ps, const double* acc_ps, const double* amax,
+                      double start_sec, double dt, double* t, double* pos, double* vel,
+                      double* acc, double* s, double* sd, double* sdd) {
+  /* TimeAtPathSamplesLowerIndex(0, start_sec) (:686-695) */
+  int li = N - 1;
+  for (int index = 0; index < N - 1; ++index) {
+    if (time_ps[index + 1] > start_sec) {
+      li = index;
+      break;
+    }
+  }
+  const double min_delta = 0.95 * dt;
+  /* first row: values interpolated at start_sec (:808-816) */
+  {
+    const int ui = (N - 1 < li + 1) ? N - 1 : li + 1;
+    const double at = (fabs(time_ps[ui] - time_ps[li]) < DBL_EPSILON)
+                          ? 0.5
+                          : (start_sec - time_ps[li]) / (time_ps[ui] - time_ps[li]);
+    t[0] = start_sec;
+    for (int d = 0; d < dim; ++d) {
+      pos[d] = lerp(at, pos_ps[(size_t)li * dim + d], pos_ps[(size_t)ui * dim + d]);
+      vel[d] = lerp(at, vel_ps[(size_t)li * dim + d], vel_ps[(size_t)ui * dim + d]);
+      double a = lerp(at, acc_ps[(size_t)li * dim + d], acc_ps[(size_t)ui * dim + d]);
+      a = (a < -amax[d]) ? -amax[d] : a;
+      a = (amax[d] < a) ? amax[d] : a;
+      acc[d] = a;
+    }
+    s[0] = lerp(at, s_ps[li], s_ps[ui]);
+    sd[0] = lerp(at, sd_ps[li], sd_ps[ui]);
+    sdd[0] = lerp(at, sdd_ps[li], sdd_ps[ui]);
+  }
+  int M = 1;
+  for (int i = li + 1; i < N; ++i) {
+    if (fabs(time_ps[i] - t[M - 1]) < min_delta) continue;
+    t[M] = time_ps[i];
+    for (int d = 0; d < dim; ++d) {
+      pos[(size_t)M * dim + d] = pos_ps[(size_t)i * dim + d];
+      vel[(size_t)M * dim + d] = vel_ps[(size_t)i * dim + d];
+      acc[(size_t)M * dim + d] = acc_ps[(size_t)i * dim + d];
+    }
+    s[M] = s_ps[i];
+    sd[M] = sd_ps[i];
+    sdd[M] = sdd_ps[i];
+    ++M;
+  }
+  /* the last KEPT row gets the final position and zero derivatives (:832-835) */
+  for (int d = 0; d < dim; ++d) {
+    pos[(size_t)(M - 1) * dim + d] = pos_ps[(size_t)(N - 1) * dim + d];
+    vel[(size_t)(M - 1) * dim + d] = 0.0;
+    acc[(size_t)(M - 1) * dim + d] = 0.0;
+  }
+  return M;
+}
+
 /* SetWaypoints (timeable_path_joint_spline.cc:200-207) + Plan for a fresh
  * path in one window (path_timing_trajectory.cc:579-684 with :307-475):
  * path_start = 0, sd_start = sdd_start = 0, zero initial velocity,
@@ -1084,6 +1143,16 @@ int orc_plan_joint(const orc_plan_cfg* cfg, const double* waypoints,
     out->duration = out->time[N - 1] - out->time[0];
     orc_assemble(out->dq, out->ddq, out->sd, out->sdd, amax, N, D, out->vel, out->acc);
     if (cfg->dt > 0 && out->r_t) {
+      if (cfg->skip_method && out->M_cap >= N + 1) {
+        out->M = orc_resample_skip(N, D, out->time, out->s, out->sd, out->sdd, out->q,
+                                   out->vel, out->acc, amax, cfg->start_sec, cfg->dt,
+                                   out->r_t, out->r_pos, out->r_vel, out->r_acc, out->r_s,
+                                   out->r_sd, out->r_sdd);
+        free(ctrl);
+        free(knots);
+        free(cons);
+        return st;
+      }
       int M = orc_resample_count(out->time[N - 1], cfg->start_sec, cfg->dt);
       if (M > out->M_cap) M = out->M_cap;
       out->M = M;

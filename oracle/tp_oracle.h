@@ -101,6 +101,11 @@ void orc_assemble(const double* dq, const double* ddq, const double* sd,
 /* number of uniform samples ResampleEquidistantlyInTime would produce. */
 int orc_resample_count(double t_end, double start_sec, double dt);
 /* outputs: t[M], pos/vel/acc [M][dim], s/sd/sdd [M] */
+int orc_resample_skip(int N, int dim, const double* time_ps, const double* s_ps,
+                      const double* sd_ps, const double* sdd_ps, const double* pos_ps,
+                      const double* vel_ps, const double* acc_ps, const double* amax,
+                      double start_sec, double dt, double* t, double* pos, double* vel,
+                      double* acc, double* s, double* sd, double* sdd);
 void orc_resample_uniform(int N, int dim, const double* time_ps,
                           const double* s_ps, const double* sd_ps,
                           const double* sdd_ps, const double* pos_ps,
@@ -118,6 +123,7 @@ typedef struct {
   double rounding, safety, delta; /* delta <= 0: use knots.back()/(N-1) */
   double start_sec;
   double dt; /* <= 0: skip resampling */
+  int skip_method; /* != 0: kSkipSamplesCloserThanTimeStep instead of kUniformlyInTime */
 } orc_plan_cfg;
 typedef struct {
   /* [N] */

@@ -361,6 +361,47 @@ int main() {
     PrintArray("positions", res.positions, false);
     printf("},\n");
   }
+  // ---- RestToRestPlanningWorks with TimeSamplingMethod::kSkipSamplesCloserThanTimeStep
+  // (the reference runs its PathTimingTrajectoryTest suite for both methods, :994-1002)
+  {
+    auto path = std::make_shared<TimeableJointSplinePath>(JointPathOptions()
+                                                              .set_num_dofs(kNDof)
+                                                              .set_num_path_samples(kNumSamples)
+                                                              .set_delta_parameter(0.016));
+    PathTimingTrajectory planner(
+        PathTimingTrajectoryOptions()
+            .SetTimeStep(tp::Milliseconds(4))
+            .SetNumDofs(kNDof)
+            .SetNumPathSamples(kNumSamples)
+            .SetTimeSamplingMethod(
+                PathTimingTrajectoryOptions::TimeSamplingMethod::kSkipSamplesCloserThanTimeStep));
+    EXPECT(planner.SetPath(path).ok());
+    std::vector<VectorXd> wps = {VectorXd{1, 2, 3}, VectorXd{-1, -2, -3}, VectorXd{1, 2, 3}};
+    EXPECT(path->SetWaypoints(wps).ok());
+    VectorXd vmax = VectorXd::Constant(kNDof, 1.0), amax = VectorXd::Constant(kNDof, 2.0);
+    EXPECT(path->SetMaxJointVelocity(ToSpan(vmax)).ok());
+    EXPECT(path->SetMaxJointAcceleration(ToSpan(amax)).ok());
+    EXPECT(planner.Plan(TimeFromSec(0.0), tp::Seconds(100)).ok());
+    EXPECT(planner.IsTrajectoryAtEnd());
+    const auto& t = planner.GetTime();
+    EXPECT(!t.empty() && t.size() <= kNumSamples + 1);
+    if (!t.empty()) {
+      EXPECT(planner.GetPositions().back() == wps.back());
+      for (size_t d = 0; d < kNDof; ++d) EXPECT(planner.GetVelocities().back()[d] == 0.0);
+      for (size_t i = 1; i < t.size(); ++i) EXPECT(t[i] - t[i - 1] >= 0.95 * 0.004 - 1e-15);
+    }
+    printf("\"rest_to_rest_skip\": {\n");
+    PrintArray("time", t);
+    PrintArray("positions", Flatten(planner.GetPositions()));
+    PrintArray("velocities", Flatten(planner.GetVelocities()), false);
+    printf("},\n");
+    // a second Plan() inside the planned span trims the front and re-interpolates the
+    // first sample (EraseTrajectoryBefore, .cc:545-569)
+    const size_t m0 = planner.GetNumTimeSamples();
+    EXPECT(planner.Plan(TimeFromSec(0.2), tp::Seconds(0.1)).ok());
+    EXPECT(planner.GetNumTimeSamples() < m0 && planner.GetTime().front() == 0.2);
+    EXPECT(planner.GetTime()[1] - planner.GetTime()[0] > 0.0);
+  }
   // ---- GetPathStopParameterWorksInSimpleCase (path_timing_trajectory_test.cc:942-992),
   // with delta chosen so that the path fits one planning window
   {

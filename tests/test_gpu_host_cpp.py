@@ -146,3 +146,15 @@ def test_path_stop_parameter_matches_oracle(result, po):
     # TimeFromSec quantises the query time to nanoseconds
     t = po.time_to_sec(po.time_from_sec(q["mid_time"]))
     assert q["mid"] == po.path_stop_parameter(*args, t)["parameter"]
+
+
+def test_skip_method_plan_matches_oracle(result, po):
+    """host Plan() with kSkipSamplesCloserThanTimeStep vs the oracle's restatement."""
+    wp = np.array([[1.0, 2, 3], [-1, -2, -3], [1, 2, 3]])
+    o = po.plan_joint(wp, np.ones(3), np.full(3, 2.0), 1000, delta=0.016, dt=0.004, M_cap=1001,
+                      skip=True)
+    assert o["ok"]
+    r = result["rest_to_rest_skip"]
+    assert np.array_equal(np.array(r["time"]), o["r_t"])
+    assert np.array_equal(np.array(r["positions"]).reshape(-1, 3), o["r_pos"])
+    assert np.array_equal(np.array(r["velocities"]).reshape(-1, 3), o["r_vel"])

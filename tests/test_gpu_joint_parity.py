@@ -255,3 +255,43 @@ def test_plan_joint_host_chunked_pipeline_matches_staged_calls(pkg):
         eng.plan_joint_host(wp, vmax, amax, 0.0, 0.004, num_waypoints=nw, out=small)
     assert ei.value.code == 11
     eng.close()
+
+
+def test_resample_skipping_samples_closer_than_time_step_bitwise(pkg, po):
+    """kSkipSamplesCloserThanTimeStep (path_timing_trajectory.cc:785-836): every packed
+    array bit-identical to the oracle, for time steps below, around and above the
+    spacing of the path samples, and a start time inside the trajectory."""
+    B, W, D, N = 12, 6, 7, 300
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=99)
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * (N + 1))
+    eng.set_joint_waypoints(wp)
+    eng.set_joint_limits(vmax, amax)
+    eng.sample_paths()
+    eng.optimize()
+    for dt, start in ((0.004, 0.0), (0.02, 0.0), (0.1, 0.0), (0.02, 0.37)):
+        total = eng.resample(start, dt, skip=True)
+        off = eng.get(pkg.ARR.R_OFFSET)
+        assert total == off[-1]
+        got = {k: eng.get(getattr(pkg.ARR, k)) for k in
+               ("R_TIME", "R_S", "R_SD", "R_SDD", "R_POS", "R_VEL", "R_ACC")}
+        for b in range(B):
+            o = po.plan_joint(wp[b], vmax[b], amax[b], N, start_sec=0.0, dt=dt, M_cap=N + 1,
+                              skip=True) if start == 0.0 else None
+            if o is None:
+                # a later start: resample the oracle's path samples directly
+                full = po.plan_joint(wp[b], vmax[b], amax[b], N, dt=0.0)
+                o = po.resample_skip(full, amax[b], start, dt)
+            lo, hi = off[b], off[b + 1]
+            assert hi - lo == o["M"]
+            assert np.array_equal(got["R_TIME"][lo:hi], o["r_t"])
+            assert np.array_equal(got["R_S"][lo:hi], o["r_s"])
+            assert np.array_equal(got["R_SD"][lo:hi], o["r_sd"])
+            assert np.array_equal(got["R_SDD"][lo:hi], o["r_sdd"])
+            assert np.array_equal(got["R_POS"].reshape(-1, D)[lo:hi], o["r_pos"])
+            assert np.array_equal(got["R_VEL"].reshape(-1, D)[lo:hi], o["r_vel"])
+            assert np.array_equal(got["R_ACC"].reshape(-1, D)[lo:hi], o["r_acc"])
+            # the reference's own rule, restated on the result: consecutive kept
+            # samples are at least 0.95 dt apart
+            assert np.all(np.diff(o["r_t"]) >= 0.95 * dt - 1e-15)
+    eng.close()

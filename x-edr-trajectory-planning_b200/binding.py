@@ -140,6 +140,8 @@ def lib():
         L.tpb_spline_eval_device.argtypes = [C.POINTER(_SplineDesc), vp]
         L.tpb_spline_eval_host.restype = i32
         L.tpb_spline_eval_host.argtypes = [C.POINTER(_SplineDesc), i32]
+        L.tpb_resample_skipping.restype = i32
+        L.tpb_resample_skipping.argtypes = [vp, C.c_double, C.c_double, C.POINTER(C.c_int64)]
         L.tpb_path_stop_parameter.restype = i32
         L.tpb_path_stop_parameter.argtypes = [vp, vp, vp, vp, vp, vp, i32]
         L.tpb_rescale_to_stop_device.restype = i32
@@ -329,10 +331,11 @@ class Engine:
         self._ck(lib().tpb_last_phase_ms(self._h, C.cast(ms, C.c_void_p)))
         return [ms[0], ms[1], ms[2]]
 
-    def resample(self, start_sec, time_step_sec, want_total=True):
+    def resample(self, start_sec, time_step_sec, want_total=True, skip=False):
+        """tpb_resample (uniform in time) or, with skip, tpb_resample_skipping."""
         total = C.c_int64(0)
-        self._ck(lib().tpb_resample(self._h, start_sec, time_step_sec,
-                                    C.byref(total) if want_total else None))
+        fn = lib().tpb_resample_skipping if skip else lib().tpb_resample
+        self._ck(fn(self._h, start_sec, time_step_sec, C.byref(total) if want_total else None))
         return total.value
 
     def plan_joint_host(self, waypoints, vmax, amax, start_sec=0.0, time_step_sec=0.0,

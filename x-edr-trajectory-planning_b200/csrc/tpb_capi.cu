@@ -636,8 +636,21 @@ int32_t tpb_last_phase_ms(tpb_engine* e, double* ms3) {
   return TPB_OK;
 }
 
+static int32_t resample_impl(tpb_engine* e, double start_sec, double time_step_sec,
+                             int64_t* total_samples, bool skip);
+
 int32_t tpb_resample(tpb_engine* e, double start_sec, double time_step_sec,
                      int64_t* total_samples) {
+  return resample_impl(e, start_sec, time_step_sec, total_samples, false);
+}
+
+int32_t tpb_resample_skipping(tpb_engine* e, double start_sec, double time_step_sec,
+                              int64_t* total_samples) {
+  return resample_impl(e, start_sec, time_step_sec, total_samples, true);
+}
+
+static int32_t resample_impl(tpb_engine* e, double start_sec, double time_step_sec,
+                             int64_t* total_samples, bool skip) {
   if (e == nullptr) return TPB_INVALID_ARGUMENT;
   auto& d = e->dims;
   if ((e->mode != Mode::kJoint && e->mode != Mode::kCartesian) || !e->optimized)
@@ -645,7 +658,8 @@ int32_t tpb_resample(tpb_engine* e, double start_sec, double time_step_sec,
   if (d.r_cap <= 0) return fail(e, TPB_FAILED_PRECONDITION, "max_time_samples_total is 0");
   if (!(time_step_sec > 0)) return fail(e, TPB_INVALID_ARGUMENT, "time step must be positive");
   cudaSetDevice(e->device);
-  e->launches += tpb::launch_resample(d, e->a, start_sec, time_step_sec, e->num_sms, e->stream);
+  e->launches += tpb::launch_resample(d, e->a, start_sec, time_step_sec, e->num_sms, e->stream,
+                                      false, skip);
   TPB_CUDA(e, cudaGetLastError());
   e->resampled = true;
   if (total_samples != nullptr) {

@@ -118,8 +118,10 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
                      cudaEvent_t* phase_events = nullptr);
 // continued: the batch is a chunk following another one; r_offset[0] already
 // holds the number of rows before it
+// skip: ResampleSkippingSamplesCloserThanTimeStep instead of
+// ResampleEquidistantlyInTime
 int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, double dt,
-                    int num_sms, cudaStream_t st, bool continued = false);
+                    int num_sms, cudaStream_t st, bool continued = false, bool skip = false);
 
 // Batched RescaleTrajectoryBackwardToStop (tpb_stop.cu); all pointers device.
 struct StopArgs {

@@ -304,6 +304,53 @@ __global__ void k_resample_count(Dims dm, DeviceArrays a, double start_sec, doub
   a.r_count[b] = m;
 }
 
+// ResampleSkippingSamplesCloserThanTimeStep (:785-836), the decisions: one warp per
+// path.  Row 0 is interpolated at start_sec; after it a path sample is kept iff its
+// time is at least GetMinTimeDeltaToKeep() = 0.95 * time step (:893-900) after the
+// last kept one.  Lanes test 32 samples against the last kept time; the first lane
+// that passes is the next kept sample, whatever the others say (they are re-tested
+// against the new time) -- the reference's sequential rule.  keep[b][k] receives
+// the sample index of row k + 1, r_count[b] the number of rows.
+__global__ void k_resample_skip_count(Dims dm, DeviceArrays a, int32_t* keep, double start_sec,
+                                      double dt) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int b = warp;
+  if (b >= dm.B) return;
+  const int N = dm.N;
+  if (a.status[b] != TPB_PATH_OK) {
+    if (lane == 0) a.r_count[b] = 0;
+    return;
+  }
+  const double* tp = a.time + static_cast<size_t>(b) * N;
+  int32_t* kp = keep + static_cast<size_t>(b) * N;
+  // TimeAtPathSamplesLowerIndex(0, start_sec) (:686-695)
+  int li = N - 1;
+  for (int base = 0; base < N - 1; base += 32) {
+    const int i = base + lane;
+    const unsigned m = __ballot_sync(kFullMask, (i < N - 1) && (tp[i + 1] > start_sec));
+    if (m) {
+      li = base + (__ffs(m) - 1);
+      break;
+    }
+  }
+  const double min_delta = 0.95 * dt;
+  double last = start_sec;
+  int rows = 1;
+  for (int base = li + 1; base < N; base += 32) {
+    const int i = base + lane;
+    const double t = (i < N) ? tp[i] : 0.0;
+    unsigned cand = __ballot_sync(kFullMask, (i < N) && !(fabs(t - last) < min_delta));
+    while (cand) {
+      const int k = __ffs(cand) - 1;
+      if (lane == 0) kp[rows - 1] = base + k;
+      ++rows;
+      last = __shfl_sync(kFullMask, t, k);
+      cand = __ballot_sync(kFullMask, (i < N) && (lane > k) && !(fabs(t - last) < min_delta));
+    }
+  }
+  if (lane == 0) a.r_count[b] = rows;
+}
+
 // exclusive scan of r_count into r_offset (single block; B is at most ~1e6).
 // continued != 0: this batch is a chunk that follows another one, offset[0]
 // already holds the rows before it (the previous chunk's offset[B]).
@@ -352,9 +399,14 @@ constexpr int kResampleThreads = 256;
 // contiguous 256-byte runs.  Rows past r_capacity are dropped (the host reports
 // kOutOfRange).  kSmemTime = false: N too large for shared memory, search in
 // global memory.
-template <bool kSmemTime>
+//
+// kSkip: rows follow ResampleSkippingSamplesCloserThanTimeStep instead of the uniform
+// grid: row 0 is interpolated at start_sec, row i > 0 IS path sample keep[b][i-1]
+// (li = ui = that sample, values taken as they are), so that both methods share the
+// assembly and the transposed writes.
+template <bool kSmemTime, bool kSkip>
 __global__ void __launch_bounds__(kResampleThreads)
-k_resample_fill(Dims dm, DeviceArrays a, double start_sec, double dt) {
+k_resample_fill(Dims dm, DeviceArrays a, const int32_t* keep, double start_sec, double dt) {
   extern __shared__ double smem[];
   const int N = dm.N, D = dm.D;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -377,12 +429,14 @@ k_resample_fill(Dims dm, DeviceArrays a, double start_sec, double dt) {
       const bool live = i < M;
       if (live) {
         const int64_t row = row0 + i;
-        const double t = start_sec + dt * i;
+        const bool sample_row = kSkip && i > 0;
+        const int src = sample_row ? keep[o + i - 1] : 0;
+        const double t = sample_row ? tp[src] : start_sec + dt * i;
         // TimeAtPathSamplesLowerIndex (:686-695): first index with time[index+1] > t,
         // else N-1.  time[] is non-decreasing, so the reference's monotone linear scan
         // equals this binary search.
         int lo = 0, hi = N - 1;  // answer in [0, N-1]
-        while (lo < hi) {
+        while (!sample_row && lo < hi) {
           const int mid = (lo + hi) >> 1;
           if (tp[mid + 1] > t) {
             hi = mid;
@@ -390,17 +444,17 @@ k_resample_fill(Dims dm, DeviceArrays a, double start_sec, double dt) {
             lo = mid + 1;
           }
         }
-        const int li = lo;
-        const int ui = min(N - 1, li + 1);
+        const int li = sample_row ? src : lo;
+        const int ui = sample_row ? src : min(N - 1, li + 1);
         const double tl = tp[li], tu = tp[ui];
         const double at = (fabs(tu - tl) < DBL_EPSILON) ? 0.5 : (t - tl) / (tu - tl);
         const double sdl = a.sd[o + li], sdu = a.sd[o + ui];
         const double sddl = a.sdd[o + li], sddu = a.sdd[o + ui];
         if (row < dm.r_cap) {
           a.r_time[row] = t;
-          a.r_s[row] = lerp(at, a.s[o + li], a.s[o + ui]);
-          a.r_sd[row] = lerp(at, sdl, sdu);
-          a.r_sdd[row] = lerp(at, sddl, sddu);
+          a.r_s[row] = sample_row ? a.s[o + li] : lerp(at, a.s[o + li], a.s[o + ui]);
+          a.r_sd[row] = sample_row ? sdl : lerp(at, sdl, sdu);
+          a.r_sdd[row] = sample_row ? sddl : lerp(at, sddl, sddu);
         }
         const bool last = (i == M - 1);
         const double sdl2 = sdl * sdl, sdu2 = sdu * sdu;  // eigenmath::Square
@@ -419,9 +473,9 @@ k_resample_fill(Dims dm, DeviceArrays a, double start_sec, double dt) {
             const double vl = d1l * sdl, vu = d1u * sdu;
             const double al = clampa(d1l * sddl + d2l * sdl2, am);
             const double au = clampa(d1u * sddu + d2u * sdu2, am);
-            pos = lerp(at, a.q[rl], a.q[ru]);
-            vel = lerp(at, vl, vu);
-            acc = clampa(lerp(at, al, au), am);
+            pos = sample_row ? a.q[rl] : lerp(at, a.q[rl], a.q[ru]);
+            vel = sample_row ? vl : lerp(at, vl, vu);
+            acc = sample_row ? al : clampa(lerp(at, al, au), am);
           }
           s_tile[lane * D + d] = pos;
           s_tile[32 * D + lane * D + d] = vel;
@@ -558,20 +612,36 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
 }
 
 int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, double dt,
-                    int num_sms, cudaStream_t st, bool continued) {
+                    int num_sms, cudaStream_t st, bool continued, bool skip) {
   const int threads = 128;
-  k_resample_count<<<(d.B + threads - 1) / threads, threads, 0, st>>>(d, a, start_sec, dt);
+  // the kept-sample lists of the skipping method live in the boundary passes' scratch
+  int32_t* keep = reinterpret_cast<int32_t*>(a.fix_val);
+  if (skip) {
+    const int warps_per_block = threads / 32;
+    k_resample_skip_count<<<(d.B + warps_per_block - 1) / warps_per_block, threads, 0, st>>>(
+        d, a, keep, start_sec, dt);
+  } else {
+    k_resample_count<<<(d.B + threads - 1) / threads, threads, 0, st>>>(d, a, start_sec, dt);
+  }
   k_scan_offsets<<<1, 1024, 0, st>>>(d.B, a.r_count, a.r_offset, continued ? 1 : 0);
   const size_t tile = sizeof(double) * (kResampleThreads / 32) * 3 * 32 * d.D;
   const size_t with_time = tile + sizeof(double) * d.N;
   const int grid = std::min(d.B, num_sms * 16);
   if (with_time <= 160 * 1024) {
     // > 48 KB of dynamic shared memory is opt-in (per device, so set it every time)
-    cudaFuncSetAttribute(k_resample_fill<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         160 * 1024);
-    k_resample_fill<true><<<grid, kResampleThreads, with_time, st>>>(d, a, start_sec, dt);
+    if (skip) {
+      cudaFuncSetAttribute(k_resample_fill<true, true>,
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+      k_resample_fill<true, true><<<grid, kResampleThreads, with_time, st>>>(d, a, keep, start_sec, dt);
+    } else {
+      cudaFuncSetAttribute(k_resample_fill<true, false>,
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+      k_resample_fill<true, false><<<grid, kResampleThreads, with_time, st>>>(d, a, keep, start_sec, dt);
+    }
+  } else if (skip) {
+    k_resample_fill<false, true><<<grid, kResampleThreads, tile, st>>>(d, a, keep, start_sec, dt);
   } else {
-    k_resample_fill<false><<<grid, kResampleThreads, tile, st>>>(d, a, start_sec, dt);
+    k_resample_fill<false, false><<<grid, kResampleThreads, tile, st>>>(d, a, keep, start_sec, dt);
   }
   return 3;
 }

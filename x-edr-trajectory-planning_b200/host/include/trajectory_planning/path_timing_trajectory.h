@@ -10,8 +10,8 @@
 // Scope: a fresh path (State::kNewPath) whose
 // planning loop needs one path window, plus the "already planned enough"
 // re-entry (.cc:590-601).  Moving-horizon re-planning across windows,
-// kSkipSamplesCloserThanTimeStep is a "next" row and returns kUnimplemented;
-// GetPathStopParameter runs on the device.  Paths must be TimeableJointSplinePath.
+// is a "next" row; both time sampling methods and GetPathStopParameter run on
+// the device.  Paths must be TimeableJointSplinePath.
 #ifndef TRAJECTORY_PLANNING_PATH_TIMING_TRAJECTORY_H_
 #define TRAJECTORY_PLANNING_PATH_TIMING_TRAJECTORY_H_
 
@@ -131,9 +131,6 @@ class PathTimingTrajectory : public TrajectoryPlanner {
       return tp::UnimplementedError(
           "moving-horizon re-planning of a partially planned path is outside the hot path");
     }
-    if (options_.GetTimeSamplingMethod() != PathTimingTrajectoryOptions::TimeSamplingMethod::kUniformlyInTime) {
-      return tp::UnimplementedError("kSkipSamplesCloserThanTimeStep is outside the hot path");
-    }
     if (path_->DeviceEngine() == nullptr) {
       return tp::UnimplementedError(
           "only device-backed paths (TimeableJointSplinePath, TimeableCartesianSplinePath) are timed");
@@ -200,7 +197,10 @@ class PathTimingTrajectory : public TrajectoryPlanner {
 
     // ---- ResampleTrajectory (.cc:697-707, 755-783) on the device
     int64_t total = 0;
-    rc = tpb_resample(e, start_sec, time_step_sec_, &total);
+    const bool skipping = options_.GetTimeSamplingMethod() ==
+                          PathTimingTrajectoryOptions::TimeSamplingMethod::kSkipSamplesCloserThanTimeStep;
+    rc = skipping ? tpb_resample_skipping(e, start_sec, time_step_sec_, &total)
+                  : tpb_resample(e, start_sec, time_step_sec_, &total);
     if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
     const size_t M = static_cast<size_t>(total), D = options_.GetNumDofs();
     time_.resize(M);
@@ -283,10 +283,92 @@ class PathTimingTrajectory : public TrajectoryPlanner {
     const int64_t loop_multiple = static_cast<int64_t>(std::round(TimeToSec(*time) / time_step_sec_));
     *time = TimeFromSec(loop_multiple * time_step_sec_);
   }
-  // EraseTrajectoryBefore (.cc:540-577), kUniformlyInTime
+  // GetMinTimeDeltaToKeep (.cc:893-900)
+  double GetMinTimeDeltaToKeep() const { return 0.95 * time_step_sec_; }
+
+  struct InterpolationResult {
+    tp::VectorXd position, velocity, acceleration;
+    double path_parameter = 0, path_parameter_derivative = 0, second_path_parameter_derivative = 0;
+  };
+  // InterpolateAtTime (.cc:709-753) on the path samples held by the device engine
+  // (bookkeeping for EraseTrajectoryBefore; the bulk interpolation of Plan() runs
+  // on the device).
+  InterpolationResult InterpolateAtTime(double time_sec) const {
+    InterpolationResult r;
+    tpb_engine* e = path_->DeviceEngine();
+    const size_t N = time_at_path_samples_.size(), D = options_.GetNumDofs();
+    size_t li = N - 1;  // TimeAtPathSamplesLowerIndex (.cc:686-695)
+    for (size_t i = 0; i + 1 < N; ++i) {
+      if (time_at_path_samples_[i + 1] > time_sec) {
+        li = i;
+        break;
+      }
+    }
+    const size_t ui = std::min(N - 1, li + 1);
+    const double tl = time_at_path_samples_[li], tu = time_at_path_samples_[ui];
+    const double at = std::abs(tu - tl) < std::numeric_limits<double>::epsilon()
+                          ? 0.5
+                          : (time_sec - tl) / (tu - tl);
+    std::vector<double> s(N), sd(N), sdd(N), q(N * D), dq(N * D), ddq(N * D);
+    tpb_get(e, TPB_ARR_S, s.data(), N * sizeof(double), 0);
+    tpb_get(e, TPB_ARR_SD, sd.data(), N * sizeof(double), 0);
+    tpb_get(e, TPB_ARR_SDD, sdd.data(), N * sizeof(double), 0);
+    tpb_get(e, TPB_ARR_Q, q.data(), N * D * sizeof(double), 0);
+    tpb_get(e, TPB_ARR_DQ, dq.data(), N * D * sizeof(double), 0);
+    tpb_get(e, TPB_ARR_DDQ, ddq.data(), N * D * sizeof(double), 0);
+    auto lerp = [at](double x, double y) { return x + at * (y - x); };
+    const auto& amax = path_->GetMaxJointAcceleration();
+    auto clamp = [](double v, double lim) {
+      v = (v < -lim) ? -lim : v;
+      return (lim < v) ? lim : v;
+    };
+    r.position = tp::VectorXd(D);
+    r.velocity = tp::VectorXd(D);
+    r.acceleration = tp::VectorXd(D);
+    for (size_t d = 0; d < D; ++d) {
+      const double vl = dq[li * D + d] * sd[li], vu = dq[ui * D + d] * sd[ui];
+      const double al = clamp(dq[li * D + d] * sdd[li] + ddq[li * D + d] * (sd[li] * sd[li]), amax[d]);
+      const double au = clamp(dq[ui * D + d] * sdd[ui] + ddq[ui * D + d] * (sd[ui] * sd[ui]), amax[d]);
+      r.position[d] = lerp(q[li * D + d], q[ui * D + d]);
+      r.velocity[d] = lerp(vl, vu);
+      r.acceleration[d] = clamp(lerp(al, au), amax[d]);
+    }
+    r.path_parameter = lerp(s[li], s[ui]);
+    r.path_parameter_derivative = lerp(sd[li], sd[ui]);
+    r.second_path_parameter_derivative = lerp(sdd[li], sdd[ui]);
+    return r;
+  }
+
+  // EraseTrajectoryBefore (.cc:540-577)
   void EraseTrajectoryBefore(tp::Time time) {
     const double time_sec = TimeToSec(time);
     if (time_.empty() || time_sec < time_.front()) return;
+    if (options_.GetTimeSamplingMethod() ==
+        PathTimingTrajectoryOptions::TimeSamplingMethod::kSkipSamplesCloserThanTimeStep) {
+      // number of samples with a timestamp < time_sec
+      const int below = static_cast<int>(std::lower_bound(time_.begin(), time_.end(), time_sec) - time_.begin());
+      const InterpolationResult v = InterpolateAtTime(time_sec);
+      const int until = (below < static_cast<int>(time_.size()) &&
+                         time_[below] < time_sec + GetMinTimeDeltaToKeep())
+                            ? below
+                            : below - 1;
+      auto erase_n = [until](auto& vec) { vec.erase(vec.begin(), vec.begin() + std::max(until, 0)); };
+      erase_n(time_);
+      erase_n(path_parameter_);
+      erase_n(path_parameter_derivative_);
+      erase_n(second_path_parameter_derivative_);
+      erase_n(positions_);
+      erase_n(velocities_);
+      erase_n(accelerations_);
+      time_.front() = time_sec;  // fix the first sample
+      positions_.front() = v.position;
+      velocities_.front() = v.velocity;
+      accelerations_.front() = v.acceleration;
+      path_parameter_.front() = v.path_parameter;
+      path_parameter_derivative_.front() = v.path_parameter_derivative;
+      second_path_parameter_derivative_.front() = v.second_path_parameter_derivative;
+      return;
+    }
     const int offset = std::min<int>(static_cast<int>(std::round((time_sec - time_.front()) / time_step_sec_)),
                                      static_cast<int>(time_.size()) - 1);
     auto erase = [offset](auto& v) { v.erase(v.begin(), v.begin() + offset); };
