@@ -23,6 +23,13 @@ c_double_p = C.POINTER(C.c_double)
 c_ubyte_p = C.POINTER(C.c_ubyte)
 
 ORC_OK = 0
+ORC_FAIL_CAPACITY = 6
+ORC_FAIL_DEADLINE = 7
+ORC_FAIL_START_RANGE = 8
+ORC_FAIL_START_ARG = 9
+ORC_FAIL_START_END = 10
+ORC_FAIL_NO_SAMPLES = 11
+ORC_FAIL_INITIAL_VELOCITY = 12
 
 
 def build(force: bool = False) -> None:
@@ -64,6 +71,25 @@ class _PlanOut(C.Structure):
         ("knot_end", C.c_double), ("last_extremal_index", C.c_int),
         ("M_cap", C.c_int), ("M", C.c_int)] + [(n, c_double_p) for n in
         ("r_t", "r_pos", "r_vel", "r_acc", "r_s", "r_sd", "r_sdd")]
+
+
+class _Planner(C.Structure):
+    """orc_planner (tp_oracle.h)"""
+    _fields_ = [("N", C.c_int), ("dim", C.c_int), ("W", C.c_int), ("rounding", C.c_double),
+                ("safety", C.c_double), ("delta", C.c_double), ("dt", C.c_double),
+                ("skip_method", C.c_int), ("max_planning_iterations", C.c_int),
+                ("max_initial_velocity_error", C.c_double)] + [
+        (n, c_double_p) for n in ("waypoints", "vmax", "amax", "initial_velocity", "ctrl",
+                                  "knots")] + [("P_cap", C.c_int)] + [
+        (n, c_double_p) for n in ("w_time", "w_s", "w_sd", "w_sdd", "w_q", "w_vel", "w_acc")] + [
+        ("M_cap", C.c_int)] + [
+        (n, c_double_p) for n in ("r_t", "r_pos", "r_vel", "r_acc", "r_s", "r_sd", "r_sdd")] + [
+        ("num_points", C.c_int), ("knot_end", C.c_double), ("delta_used", C.c_double),
+        ("len", C.c_int), ("M", C.c_int), ("initial_plan", C.c_int), ("sampled", C.c_int),
+        ("planned_to_end", C.c_int), ("target_reached", C.c_int), ("start_time", C.c_int64),
+        ("end_time", C.c_int64), ("final_decel_start", C.c_int64), ("path_horizon", C.c_double),
+        ("path_start", C.c_double), ("decel_time", C.c_double), ("last_extremal_index", C.c_int),
+        ("loops", C.c_int), ("erased", C.c_int)]
 
 
 class _CartCfg(C.Structure):
@@ -166,6 +192,10 @@ def lib():
         L.orc_resample_skip.restype = C.c_int
         L.orc_resample_skip.argtypes = [C.c_int, C.c_int] + [c_double_p] * 8 + [
             C.c_double, C.c_double] + [c_double_p] * 7
+        L.orc_planner_init.restype = C.c_int
+        L.orc_planner_init.argtypes = [C.POINTER(_Planner)]
+        L.orc_planner_plan.restype = C.c_int
+        L.orc_planner_plan.argtypes = [C.POINTER(_Planner), C.c_int64, C.c_int64]
         # stopping trajectories (tp_oracle_stop.c)
         L.orc_sampled_trajectory_inputs_valid.restype = C.c_int
         L.orc_sampled_trajectory_inputs_valid.argtypes = [C.c_int, c_double_p]
@@ -385,6 +415,53 @@ def plan_joint(waypoints, vmax, amax, N, rounding=0.2, safety=0.8, delta=-1.0,
                delta=out.delta_used, knot_end=out.knot_end, M=M,
                last_extremal_index=out.last_extremal_index)
     return res
+
+
+class Planner:
+    """PathTimingTrajectory with its state between Plan() calls, for one joint path
+    (orc_planner, tp_oracle_windows.c).  Times are absl::Time / Duration as integer
+    nanoseconds."""
+
+    def __init__(self, waypoints, vmax, amax, N, delta, dt, rounding=0.2, safety=0.8, skip=False,
+                 max_planning_iterations=200, initial_velocity=None,
+                 max_initial_velocity_error=1e-4, P_cap=None, M_cap=200000):
+        wp = np.ascontiguousarray(waypoints, np.float64)
+        W, D = wp.shape
+        P = P_cap or 64 * N
+        n = max(4, 3 * W - 2)
+        self._keep = dict(
+            waypoints=wp, vmax=np.ascontiguousarray(vmax, np.float64),
+            amax=np.ascontiguousarray(amax, np.float64),
+            initial_velocity=np.ascontiguousarray(
+                np.zeros(D) if initial_velocity is None else initial_velocity, np.float64),
+            ctrl=np.zeros((n, D)), knots=np.zeros(n + 3))
+        self.w = {k: np.full(P, np.nan) for k in ("w_time", "w_s", "w_sd", "w_sdd")}
+        self.w.update({k: np.zeros((P, D)) for k in ("w_q", "w_vel", "w_acc")})
+        self.r = {k: np.zeros(M_cap) for k in ("r_t", "r_s", "r_sd", "r_sdd")}
+        self.r.update({k: np.zeros((M_cap, D)) for k in ("r_pos", "r_vel", "r_acc")})
+        self.c = _Planner(N=N, dim=D, W=W, rounding=rounding, safety=safety, delta=delta, dt=dt,
+                          skip_method=1 if skip else 0,
+                          max_planning_iterations=max_planning_iterations,
+                          max_initial_velocity_error=max_initial_velocity_error, P_cap=P,
+                          M_cap=M_cap, **{k: _dp(v) for k, v in self._keep.items()},
+                          **{k: _dp(v) for k, v in self.w.items()},
+                          **{k: _dp(v) for k, v in self.r.items()})
+        lib().orc_planner_init(C.byref(self.c))
+
+    def plan(self, start_ns, horizon_ns):
+        """Plan(start, horizon); returns the ORC_* status."""
+        return lib().orc_planner_plan(C.byref(self.c), int(start_ns), int(horizon_ns))
+
+    def trajectory(self):
+        M = self.c.M
+        return {k: v[:M].copy() for k, v in self.r.items()}
+
+    def path_samples(self):
+        n = self.c.len
+        return {k: v[:n].copy() for k, v in self.w.items()}
+
+    def __getattr__(self, name):  # state fields: len, M, end_time, planned_to_end, ...
+        return getattr(self.__dict__["c"], name)
 
 
 def resample_skip(plan, amax, start_sec, dt):

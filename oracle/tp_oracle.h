@@ -30,7 +30,14 @@ enum {
   ORC_FAIL_CONNECT = 2,  /* iback_lo > icrit_lo */
   ORC_FAIL_NAN = 3,      /* sd2 still NaN after the extremal loop */
   ORC_FAIL_TERMINAL = 4, /* non-zero terminal velocity */
-  ORC_FAIL_INDEX = 5     /* reference would index sd2_max[-1] (UB there) */
+  ORC_FAIL_INDEX = 5,    /* reference would index sd2_max[-1] (UB there) */
+  ORC_FAIL_CAPACITY = 6, /* path samples / rows exceed the caller's capacity */
+  ORC_FAIL_DEADLINE = 7, /* kDeadlineExceeded (path_timing_trajectory.cc:652-655) */
+  ORC_FAIL_START_RANGE = 8,  /* kOutOfRange (:504-511, :294-296) */
+  ORC_FAIL_START_ARG = 9,    /* kInvalidArgument (:517-535, :314-318) */
+  ORC_FAIL_START_END = 10,   /* kInternal: start >= last trajectory time (:298-303) */
+  ORC_FAIL_NO_SAMPLES = 11,  /* kFailedPrecondition (:291-293) */
+  ORC_FAIL_INITIAL_VELOCITY = 12 /* kInvalidArgument (:377-385) */
 };
 
 /* ---- stage A: B-splines ------------------------------------------------ */
@@ -205,6 +212,41 @@ int orc_path_stop_parameter(int M, int D, const double* time, const double* path
                             const double* vel, const double* acc, const double* max_acc,
                             double query_time, double* stop_parameter, int* stop_row,
                             double* stop_duration);
+
+/* ---- PathTimingTrajectory::Plan with its state between calls
+ * (path_timing_trajectory.cc:307-475, 477-684) for a joint path that is not
+ * modified after the first plan; see tp_oracle_windows.c.  All storage is the
+ * caller's. */
+typedef struct {
+  /* configuration */
+  int N, dim, W;
+  double rounding, safety, delta; /* delta <= 0: knots.back()/(N-1) */
+  double dt;                      /* time step */
+  int skip_method;                /* != 0: kSkipSamplesCloserThanTimeStep */
+  int max_planning_iterations;
+  double max_initial_velocity_error;
+  const double *waypoints, *vmax, *amax, *initial_velocity; /* [W][dim], 3 x [dim] */
+  /* storage */
+  double *ctrl, *knots; /* [max(4,3W-2)][dim], [max(4,3W-2)+3] */
+  int P_cap;            /* capacity of the *_at_path_samples_ arrays */
+  double *w_time, *w_s, *w_sd, *w_sdd; /* [P_cap] */
+  double *w_q, *w_vel, *w_acc;         /* [P_cap][dim] */
+  int M_cap;                           /* capacity of the trajectory */
+  double *r_t, *r_pos, *r_vel, *r_acc, *r_s, *r_sd, *r_sdd;
+  /* state */
+  int num_points;
+  double knot_end, delta_used;
+  int len; /* path samples held */
+  int M;   /* trajectory rows held */
+  int initial_plan, sampled, planned_to_end, target_reached;
+  int64_t start_time, end_time, final_decel_start; /* absl::Time as Unix ns */
+  double path_horizon, path_start, decel_time;
+  int last_extremal_index;
+  int loops;  /* planning windows computed by the last call */
+  int erased; /* the last call found enough planned and only erased (:594-599) */
+} orc_planner;
+int orc_planner_init(orc_planner* p);
+int orc_planner_plan(orc_planner* p, int64_t start_ns, int64_t horizon_ns);
 
 #ifdef __cplusplus
 }
