@@ -60,6 +60,17 @@ enum {
   TPB_PATH_FAIL_NAN = 3,      /* sd2 still NaN after the loop (:400-403) */
   TPB_PATH_FAIL_TERMINAL = 4, /* non-zero terminal velocity (:422-428) */
   TPB_PATH_FAIL_INDEX = 5,    /* reference would read sd2_max[-1] (:372, UB there) */
+  /* tpb_planner_plan (PathTimingTrajectory::Plan, path_timing_trajectory.cc) */
+  TPB_PATH_FAIL_CAPACITY = 6,     /* spliced path samples exceed path_sample_capacity */
+  TPB_PATH_FAIL_DEADLINE = 7,     /* kDeadlineExceeded: max planning loops (:652-655) */
+  TPB_PATH_FAIL_START_RANGE = 8,  /* kOutOfRange: start past the previous plan (:504-511) or
+                                     before its first sample (:294-296) */
+  TPB_PATH_FAIL_START_ARG = 9,    /* kInvalidArgument: start vs. previous start / end
+                                     (:517-535), non-positive target duration (:314-318) */
+  TPB_PATH_FAIL_START_END = 10,   /* kInternal: start >= the last trajectory time (:298-303) */
+  TPB_PATH_FAIL_NO_SAMPLES = 11,  /* kFailedPrecondition: no samples yet (:291-293) */
+  TPB_PATH_FAIL_INITIAL_VELOCITY = 12, /* kInvalidArgument: initial velocity not along the
+                                          first path tangent (:377-385) */
   TPB_PATH_NOT_RUN = 100
 };
 
@@ -110,6 +121,30 @@ typedef enum {
   TPB_ARR_R_S = 55,      /* double [total] */
   TPB_ARR_R_SD = 56,     /* double [total] */
   TPB_ARR_R_SDD = 57,    /* double [total] */
+  /* moving-horizon planner (tpb_planner_reset / tpb_planner_plan): the
+   * *_at_path_samples_ arrays of PathTimingTrajectory (path_timing_trajectory.h),
+   * P = path_sample_capacity slots per path of which W_LEN[b] are held; W_DQ / W_DDQ
+   * are the path derivatives (velocity = W_DQ * W_SD etc., :458-472) */
+  TPB_ARR_W_LEN = 60,  /* int32  [B] */
+  TPB_ARR_W_TIME = 61, /* double [B][P] */
+  TPB_ARR_W_S = 62,    /* double [B][P] */
+  TPB_ARR_W_SD = 63,   /* double [B][P] */
+  TPB_ARR_W_SDD = 64,  /* double [B][P] */
+  TPB_ARR_W_Q = 65,    /* double [B][P][D] */
+  TPB_ARR_W_DQ = 66,   /* double [B][P][D] */
+  TPB_ARR_W_DDQ = 67,  /* double [B][P][D] */
+  /* ... and the planner's state after the last tpb_planner_plan */
+  TPB_ARR_PLAN_STATUS = 70,            /* int32 [B] TPB_PATH_* of the last call */
+  TPB_ARR_PLAN_LOOPS = 71,             /* int32 [B] planning windows computed by it */
+  TPB_ARR_PLAN_PLANNED_TO_END = 72,    /* int32 [B] planned_to_end_ */
+  TPB_ARR_PLAN_TARGET_REACHED = 73,    /* int32 [B] IsTrajectoryAtEnd() */
+  TPB_ARR_PLAN_START_TIME = 74,        /* int64 [B] GetStartTime(), Unix ns */
+  TPB_ARR_PLAN_END_TIME = 75,          /* int64 [B] GetEndTime(), Unix ns */
+  TPB_ARR_PLAN_FINAL_DECEL_START = 76, /* int64 [B] GetFinalDecelStart(), Unix ns */
+  TPB_ARR_PLAN_ERASED = 77,            /* int32 [B] 0: the trajectory was resampled from the
+                                          start time, 1: rows kept (enough was planned, only
+                                          EraseTrajectoryBefore ran; or the call failed its
+                                          argument checks), 2: no rows (failed while planning) */
   /* diagnostics: solver scratch [B][N]; holds per-path phase cycle stamps when the
    * library is built with -DTPB_PROFILE_PHASES, otherwise unspecified */
   TPB_ARR_DEBUG = 99
@@ -240,6 +275,33 @@ int32_t tpb_resample(tpb_engine* e, double start_sec, double time_step_sec,
  * derivatives.  A path yields at most N + 1 rows. */
 int32_t tpb_resample_skipping(tpb_engine* e, double start_sec, double time_step_sec,
                               int64_t* total_samples);
+
+/* ---- PathTimingTrajectory::Plan with its state between calls ----------------- */
+/* (path_timing_trajectory.cc:477-684) for every joint path of the batch: the
+ * moving-horizon loop over planning windows of num_path_samples samples
+ * (ComputeTimingProfile :307-475), splicing of the per-path-sample arrays,
+ * the "already planned enough" shortcut with EraseTrajectoryBefore (:540-577,
+ * :594-599), the time argument checks (:503-538, :289-305) and the resampling
+ * of the spliced samples, all on the device.  The paths are not modified between
+ * calls (TimeablePath::State kNewPath for the first window, kPathWasSampled
+ * afterwards); tpb_set_joint_waypoints / tpb_resample* end the planner's state.
+ *
+ * tpb_planner_reset = PathTimingTrajectory::Reset + the options of
+ * PathTimingTrajectoryOptions (time step, sampling method, max planning loops,
+ * max initial velocity error) + TimeablePath::SetInitialVelocity
+ * (initial_velocity [B][num_dofs], NULL = zero).  path_sample_capacity >= N bounds
+ * the spliced samples per path (device memory: (5 + 3 * num_dofs) * 8 bytes per slot).
+ *
+ * tpb_planner_plan = Plan(start, time_horizon), absl::Time / Duration as integer
+ * nanoseconds.  Per-path outcome in TPB_ARR_PLAN_STATUS (the reference's Status
+ * codes as TPB_PATH_*); the trajectory in TPB_ARR_R_* as after tpb_resample.
+ * *total_samples (may be NULL) receives R_OFFSET[B] (this synchronises). */
+int32_t tpb_planner_reset(tpb_engine* e, int32_t path_sample_capacity, double time_step_sec,
+                          int32_t skip_method, int32_t max_planning_iterations,
+                          double max_initial_velocity_error, const double* initial_velocity,
+                          int32_t on_device);
+int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
+                         int64_t* total_samples);
 
 /* Whole pipeline for a batch of fresh joint paths with HOST buffers in and out:
  * set waypoints+limits, sample, optimize, resample, copy back durations,

@@ -1,0 +1,206 @@
+"""Moving-horizon PathTimingTrajectory::Plan on the GPU (tpb_planner_reset /
+tpb_planner_plan): every call of a re-planning loop compared bit for bit with the CPU
+oracle's planner (oracle/tp_oracle_windows.c), per path of a batch, plus the
+properties of the reference's integration tests
+(path_timing_trajectory_test.cc:112-297)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import pyoracle as orc  # noqa: E402
+from __graft_entry__ import load_package  # noqa: E402
+
+pkg = load_package()
+ARR = pkg.ARR
+pytestmark = pytest.mark.gpu
+
+MS = 1_000_000
+REF_WAYPOINTS = np.array([[1, 2, 3], [-1, -2, -3], [1, 2, 3.0]])  # _test.cc:127-128
+
+
+def device_state(eng):
+    keys = dict(status=ARR.PLAN_STATUS, loops=ARR.PLAN_LOOPS, planned_to_end=ARR.PLAN_PLANNED_TO_END,
+                target_reached=ARR.PLAN_TARGET_REACHED, start_time=ARR.PLAN_START_TIME,
+                end_time=ARR.PLAN_END_TIME, final_decel_start=ARR.PLAN_FINAL_DECEL_START,
+                erased=ARR.PLAN_ERASED, len=ARR.W_LEN)
+    return {k: eng.get(v) for k, v in keys.items()}
+
+
+def device_rows(eng):
+    off = eng.get(ARR.R_OFFSET)
+    rows = dict(r_t=eng.get(ARR.R_TIME), r_pos=eng.get(ARR.R_POS), r_vel=eng.get(ARR.R_VEL),
+                r_acc=eng.get(ARR.R_ACC), r_s=eng.get(ARR.R_S), r_sd=eng.get(ARR.R_SD),
+                r_sdd=eng.get(ARR.R_SDD))
+    return off, rows
+
+
+def compare_call(eng, planners, statuses, what):
+    st = device_state(eng)
+    off, rows = device_rows(eng)
+    for b, (pl, ost) in enumerate(zip(planners, statuses)):
+        tag = f"{what} path {b}"
+        assert st["status"][b] == ost, tag
+        assert st["len"][b] == pl.len, tag
+        assert st["start_time"][b] == pl.start_time, tag
+        assert st["end_time"][b] == pl.end_time, tag
+        assert st["final_decel_start"][b] == pl.final_decel_start, tag
+        assert st["planned_to_end"][b] == pl.planned_to_end, tag
+        assert st["target_reached"][b] == pl.target_reached, tag
+        if ost == orc.ORC_OK:
+            assert st["loops"][b] == pl.loops, tag
+            assert (st["erased"][b] == 1) == bool(pl.erased), tag
+        tr = pl.trajectory()
+        assert off[b + 1] - off[b] == pl.M, tag
+        for k, v in tr.items():
+            assert rows[k][off[b]:off[b + 1]].tobytes() == v.tobytes(), f"{tag} {k}"
+    return st
+
+
+def compare_path_samples(eng, planners):
+    wt, ws, wsd, wsdd = (eng.get(a) for a in (ARR.W_TIME, ARR.W_S, ARR.W_SD, ARR.W_SDD))
+    wq, wdq = eng.get(ARR.W_Q), eng.get(ARR.W_DQ)
+    for b, pl in enumerate(planners):
+        ps, n = pl.path_samples(), pl.len
+        assert wt[b, :n].tobytes() == ps["w_time"].tobytes()
+        assert ws[b, :n].tobytes() == ps["w_s"].tobytes()
+        assert wsd[b, :n].tobytes() == ps["w_sd"].tobytes()
+        assert wsdd[b, :n].tobytes() == ps["w_sdd"].tobytes()
+        assert wq[b, :n].tobytes() == ps["w_q"].tobytes()
+        assert (wdq[b, :n] * wsd[b, :n, None]).tobytes() == ps["w_vel"].tobytes()
+
+
+def run_replanning(wp, vmax, amax, N, delta, dt, skip, horizon, replan, P_cap, max_calls=400,
+                   initial_velocity=None):
+    """Plan() at start, start + replan, ... on the device batch and per path in the
+    oracle until every path is at its end; every call compared."""
+    B, W, D = wp.shape
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * 40000)
+    eng.set_joint_limits(vmax, amax)
+    eng.set_joint_waypoints(wp)
+    eng.set_sampling(np.full(B, delta))
+    eng.planner_reset(P_cap, dt, skip=skip, initial_velocity=initial_velocity)
+    planners = [orc.Planner(wp[b], vmax[b], amax[b], N, delta, dt, skip=skip, P_cap=P_cap,
+                            initial_velocity=None if initial_velocity is None
+                            else initial_velocity[b]) for b in range(B)]
+    start, calls, erased, windows = 0, 0, 0, 0
+    done = np.zeros(B, bool)
+    while not done.all():
+        statuses = [pl.plan(start, horizon) for pl in planners]
+        total = eng.planner_plan(start, horizon)
+        st = compare_call(eng, planners, statuses, f"call {calls} start {start}")
+        assert total == sum(pl.M for pl in planners)
+        erased += int((st["erased"] == 1).sum())
+        windows += int(st["loops"].sum())
+        done |= (st["target_reached"] == 1) | (st["status"] != 0)
+        start += replan
+        calls += 1
+        assert calls < max_calls
+    compare_path_samples(eng, planners)
+    return eng, planners, dict(calls=calls, erased=erased, windows=windows)
+
+
+@pytest.mark.parametrize("skip", [False, True])
+def test_reference_rest_to_rest_replanning(skip):
+    """RestToRestPlanningWorks (_test.cc:112-173), N = 1000, 4 ms, horizon 750 ms,
+    re-planned every 200 ms."""
+    wp = REF_WAYPOINTS[None]
+    eng, planners, n = run_replanning(wp, np.ones((1, 3)), np.full((1, 3), 2.0), 1000, 0.005,
+                                      0.004, skip, 750 * MS, 200 * MS, 8192)
+    assert n["erased"] > 10 and n["windows"] >= 3
+    off, rows = device_rows(eng)
+    np.testing.assert_allclose(rows["r_pos"][-1], REF_WAYPOINTS[-1], atol=1e-12)
+    np.testing.assert_array_equal(rows["r_vel"][-1], 0.0)
+    assert np.all(np.abs(rows["r_vel"]) <= 1.0 + 1e-9) and np.all(np.abs(rows["r_acc"]) <= 2.0 + 1e-9)
+
+
+@pytest.mark.parametrize("skip", [False, True])
+def test_batch_of_seven_dof_paths(skip):
+    """A batch of different 7-dof paths re-planned in lockstep; the paths need different
+    numbers of windows and finish at different times (late calls fail the time argument
+    checks for the finished ones exactly as the reference's would)."""
+    B = 12
+    wp, vmax, amax = pkg.workloads.joint_paths(B, 6, 7, seed=77)
+    knot_end = max(orc.joint_fit(wp[b], 0.2)[1][-1] for b in range(B))
+    N = 256
+    delta = knot_end / (N - 1) / 3.2
+    eng, planners, n = run_replanning(wp, vmax, amax, N, delta, 0.008, skip, 600 * MS, 250 * MS,
+                                      16 * N)
+    assert n["windows"] >= 3 * B and n["erased"] > 0
+    assert all(pl.target_reached for pl in planners)
+
+
+def test_one_call_long_horizon_and_statuses():
+    """One Plan() with a horizon longer than the motion loops over the windows on its
+    own (:628-658); capacity / deadline / argument failures are reported per path."""
+    B = 6
+    wp, vmax, amax = pkg.workloads.joint_paths(B, 5, 7, seed=5)
+    knot_end = [orc.joint_fit(wp[b], 0.2)[1][-1] for b in range(B)]
+    N, dt = 192, 0.004
+    delta = max(knot_end) / (N - 1) / 4.0
+    long_horizon = 3600 * 1000 * MS
+
+    def engine(P_cap, iters):
+        eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=7, max_waypoints=5,
+                         max_time_samples_total=B * 60000)
+        eng.set_joint_limits(vmax, amax)
+        eng.set_joint_waypoints(wp)
+        eng.set_sampling(np.full(B, delta))
+        eng.planner_reset(P_cap, dt, max_planning_iterations=iters)
+        return eng
+
+    eng = engine(16 * N, 200)
+    planners = [orc.Planner(wp[b], vmax[b], amax[b], N, delta, dt, P_cap=16 * N) for b in range(B)]
+    statuses = [pl.plan(5 * MS, long_horizon) for pl in planners]
+    eng.planner_plan(5 * MS, long_horizon)
+    st = compare_call(eng, planners, statuses, "long horizon")
+    assert np.all(st["status"] == 0) and np.all(st["loops"] >= 3) and np.all(st["target_reached"] == 1)
+    compare_path_samples(eng, planners)
+    # calls that fail HandleTimeArguments leave everything as it was
+    for start in (int(max(pl.end_time for pl in planners)) + 50 * MS, 1 * MS):
+        statuses = [pl.plan(start, long_horizon) for pl in planners]
+        eng.planner_plan(start, long_horizon)
+        st = compare_call(eng, planners, statuses, f"bad start {start}")
+        assert np.all(st["status"] != 0)
+    # too few planning loops / too little room for the spliced samples
+    for P_cap, iters, expect in ((16 * N, 1, orc.ORC_FAIL_DEADLINE), (N + N // 2, 200, orc.ORC_FAIL_CAPACITY)):
+        eng = engine(P_cap, iters)
+        planners = [orc.Planner(wp[b], vmax[b], amax[b], N, delta, dt, P_cap=P_cap,
+                                max_planning_iterations=iters) for b in range(B)]
+        statuses = [pl.plan(0, long_horizon) for pl in planners]
+        eng.planner_plan(0, long_horizon)
+        got = eng.get(ARR.PLAN_STATUS)
+        assert list(got) == statuses and expect in statuses
+
+
+def test_initial_velocity():
+    """(:352-385) per path: projection onto the first tangent, rejection otherwise."""
+    B = 4
+    wp, vmax, amax = pkg.workloads.joint_paths(B, 4, 7, seed=9)
+    v0 = np.zeros((B, 7))
+    for b in range(B):
+        t = wp[b, 1] - wp[b, 0]
+        v0[b] = 0.03 * t / np.linalg.norm(t)
+    v0[2] = 0.0
+    v0[3, :] = [0.05, 0, 0, 0, 0, 0, 0]  # not along the tangent
+    N, dt = 256, 0.004
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=7, max_waypoints=4,
+                     max_time_samples_total=B * 40000)
+    eng.set_joint_limits(vmax, amax)
+    eng.set_joint_waypoints(wp)
+    delta = eng.get(ARR.DELTA)
+    eng.planner_reset(4 * N, dt, initial_velocity=v0)
+    planners = [orc.Planner(wp[b], vmax[b], amax[b], N, 0.0, dt, P_cap=4 * N,
+                            initial_velocity=v0[b]) for b in range(B)]
+    statuses = [pl.plan(0, 500 * MS) for pl in planners]
+    assert statuses[3] == orc.ORC_FAIL_INITIAL_VELOCITY and statuses[:3] == [0, 0, 0]
+    eng.planner_plan(0, 500 * MS)
+    compare_call(eng, planners, statuses, "initial velocity")
+    off, rows = device_rows(eng)
+    for b in range(2):
+        np.testing.assert_allclose(rows["r_vel"][off[b]], v0[b], atol=1e-9)
+    assert np.all(delta > 0)

@@ -25,6 +25,9 @@ class ARR:
     B_SD2_MAX, B_SDD_MAX, B_SDD_MIN, B_SD2_ZERO, B_TYPE = 30, 31, 32, 33, 34
     STATUS, DURATION, LAST_EXTREMAL, KNOT_END = 40, 41, 42, 43
     R_OFFSET, R_TIME, R_POS, R_VEL, R_ACC, R_S, R_SD, R_SDD = 50, 51, 52, 53, 54, 55, 56, 57
+    W_LEN, W_TIME, W_S, W_SD, W_SDD, W_Q, W_DQ, W_DDQ = 60, 61, 62, 63, 64, 65, 66, 67
+    (PLAN_STATUS, PLAN_LOOPS, PLAN_PLANNED_TO_END, PLAN_TARGET_REACHED, PLAN_START_TIME,
+     PLAN_END_TIME, PLAN_FINAL_DECEL_START, PLAN_ERASED) = 70, 71, 72, 73, 74, 75, 76, 77
     DEBUG = 99
 
 
@@ -142,6 +145,10 @@ def lib():
         L.tpb_spline_eval_host.argtypes = [C.POINTER(_SplineDesc), i32]
         L.tpb_resample_skipping.restype = i32
         L.tpb_resample_skipping.argtypes = [vp, C.c_double, C.c_double, C.POINTER(C.c_int64)]
+        L.tpb_planner_reset.restype = i32
+        L.tpb_planner_reset.argtypes = [vp, i32, C.c_double, i32, i32, C.c_double, vp, i32]
+        L.tpb_planner_plan.restype = i32
+        L.tpb_planner_plan.argtypes = [vp, C.c_int64, C.c_int64, C.POINTER(C.c_int64)]
         L.tpb_path_stop_parameter.restype = i32
         L.tpb_path_stop_parameter.argtypes = [vp, vp, vp, vp, vp, vp, i32]
         L.tpb_rescale_to_stop_device.restype = i32
@@ -172,7 +179,11 @@ def _f64(x):
 
 
 _DTYPES = {ARR.NUM_POINTS: np.int32, ARR.STATUS: np.int32, ARR.LAST_EXTREMAL: np.int32,
-           ARR.B_TYPE: np.uint8, ARR.R_OFFSET: np.int64}
+           ARR.B_TYPE: np.uint8, ARR.R_OFFSET: np.int64, ARR.W_LEN: np.int32,
+           ARR.PLAN_STATUS: np.int32, ARR.PLAN_LOOPS: np.int32,
+           ARR.PLAN_PLANNED_TO_END: np.int32, ARR.PLAN_TARGET_REACHED: np.int32,
+           ARR.PLAN_START_TIME: np.int64, ARR.PLAN_END_TIME: np.int64,
+           ARR.PLAN_FINAL_DECEL_START: np.int64, ARR.PLAN_ERASED: np.int32}
 
 
 class Engine:
@@ -338,6 +349,25 @@ class Engine:
         self._ck(fn(self._h, start_sec, time_step_sec, C.byref(total) if want_total else None))
         return total.value
 
+    def planner_reset(self, path_sample_capacity, time_step_sec, skip=False,
+                      max_planning_iterations=200, max_initial_velocity_error=1e-4,
+                      initial_velocity=None):
+        """tpb_planner_reset: PathTimingTrajectory::Reset + its options for every path."""
+        v0 = _f64(initial_velocity)  # stays alive across the call
+        p, dev = _ptr(v0)
+        self._ck(lib().tpb_planner_reset(self._h, int(path_sample_capacity), time_step_sec,
+                                         1 if skip else 0, max_planning_iterations,
+                                         max_initial_velocity_error, p, dev))
+        self.P = int(path_sample_capacity)
+
+    def planner_plan(self, start_ns, horizon_ns, want_total=True):
+        """tpb_planner_plan: PathTimingTrajectory::Plan(start, horizon) for every path
+        (times in integer nanoseconds).  Returns the number of trajectory rows."""
+        total = C.c_int64(0)
+        self._ck(lib().tpb_planner_plan(self._h, int(start_ns), int(horizon_ns),
+                                        C.byref(total) if want_total else None))
+        return total.value
+
     def plan_joint_host(self, waypoints, vmax, amax, start_sec=0.0, time_step_sec=0.0,
                         num_waypoints=None, out=None):
         """tpb_plan_joint_host.  `out`: dict of preallocated (ideally pinned) host
@@ -394,6 +424,10 @@ class Engine:
             return out.reshape(B, N, self.C, 4)
         if what in (ARR.R_POS, ARR.R_VEL, ARR.R_ACC):
             return out.reshape(-1, D)
+        if what in (ARR.W_Q, ARR.W_DQ, ARR.W_DDQ):
+            return out.reshape(B, self.P, D)
+        if ARR.W_TIME <= what <= ARR.W_SDD:
+            return out.reshape(B, self.P)
         if ARR.TIME <= what <= ARR.B_TYPE:
             return out.reshape(B, N)
         return out

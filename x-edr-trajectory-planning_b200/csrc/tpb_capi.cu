@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "tpb_device.cuh"
@@ -46,6 +47,12 @@ struct tpb_engine {
   // tpb_path_stop_parameter scratch: [Bmax] each
   double *sq_query = nullptr, *sq_parameter = nullptr, *sq_duration = nullptr;
   int32_t *sq_row = nullptr, *sq_status = nullptr;
+  // moving-horizon planner (tpb_planner_reset / tpb_planner_plan)
+  tpb::PlannerArrays w;
+  tpb::PlannerOptions wopt;
+  std::vector<void*> w_big;  // the P_cap-sized arrays (reallocated when the capacity grows)
+  bool planner_ready = false;
+  int32_t* any_active_host = nullptr;  // pinned
 };
 
 namespace {
@@ -144,6 +151,32 @@ bool lookup(tpb_engine* e, tpb_array what, ArrayRef* r) {
     case TPB_ARR_R_S: *r = {a.r_s, packed_rows() * sizeof(double)}; return true;
     case TPB_ARR_R_SD: *r = {a.r_sd, packed_rows() * sizeof(double)}; return true;
     case TPB_ARR_R_SDD: *r = {a.r_sdd, packed_rows() * sizeof(double)}; return true;
+    default: break;
+  }
+  if (what >= TPB_ARR_W_LEN && what <= TPB_ARR_PLAN_ERASED) {
+    if (!e->planner_ready) return false;
+    const auto& w = e->w;
+    const size_t BP = B * static_cast<size_t>(w.P_cap) * sizeof(double);
+    const size_t Bi = B * sizeof(int32_t), Bl = B * sizeof(int64_t);
+    switch (what) {
+      case TPB_ARR_W_LEN: *r = {w.len, Bi}; return true;
+      case TPB_ARR_W_TIME: *r = {w.w_time, BP}; return true;
+      case TPB_ARR_W_S: *r = {w.w_s, BP}; return true;
+      case TPB_ARR_W_SD: *r = {w.w_sd, BP}; return true;
+      case TPB_ARR_W_SDD: *r = {w.w_sdd, BP}; return true;
+      case TPB_ARR_W_Q: *r = {w.w_q, BP * D}; return true;
+      case TPB_ARR_W_DQ: *r = {w.w_dq, BP * D}; return true;
+      case TPB_ARR_W_DDQ: *r = {w.w_ddq, BP * D}; return true;
+      case TPB_ARR_PLAN_STATUS: *r = {w.status, Bi}; return true;
+      case TPB_ARR_PLAN_LOOPS: *r = {w.loops, Bi}; return true;
+      case TPB_ARR_PLAN_PLANNED_TO_END: *r = {w.planned_to_end, Bi}; return true;
+      case TPB_ARR_PLAN_TARGET_REACHED: *r = {w.target_reached, Bi}; return true;
+      case TPB_ARR_PLAN_START_TIME: *r = {w.start_time, Bl}; return true;
+      case TPB_ARR_PLAN_END_TIME: *r = {w.end_time, Bl}; return true;
+      case TPB_ARR_PLAN_FINAL_DECEL_START: *r = {w.final_decel_start, Bl}; return true;
+      case TPB_ARR_PLAN_ERASED: *r = {w.mode, Bi}; return true;
+      default: break;
+    }
   }
   return false;
 }
@@ -285,6 +318,8 @@ int32_t tpb_destroy(tpb_engine* e) {
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (void* p : e->allocs) cudaFree(p);
+  for (void* p : e->w_big) cudaFree(p);
+  if (e->any_active_host) cudaFreeHost(e->any_active_host);
   if (e->copy_stream) {
     cudaStreamSynchronize(e->copy_stream);
     cudaStreamDestroy(e->copy_stream);
@@ -360,6 +395,7 @@ int32_t tpb_set_joint_waypoints(tpb_engine* e, int32_t num_paths, const int32_t*
   TPB_CUDA(e, cudaGetLastError());
   e->have_waypoints = true;
   e->sampled = e->optimized = e->resampled = false;
+  e->planner_ready = false;
   return TPB_OK;
 }
 
@@ -425,6 +461,7 @@ int32_t tpb_set_sampling(tpb_engine* e, const double* delta, int32_t on_device) 
     TPB_CUDA(e, cudaGetLastError());
   }
   e->have_targets = e->have_ik = false;
+  e->planner_ready = false;
   e->sampled = e->optimized = e->resampled = false;
   return TPB_OK;
 }
@@ -662,6 +699,7 @@ static int32_t resample_impl(tpb_engine* e, double start_sec, double time_step_s
                                       false, skip);
   TPB_CUDA(e, cudaGetLastError());
   e->resampled = true;
+  e->planner_ready = false;  // the trajectory rows are no longer the planner's
   if (total_samples != nullptr) {
     int64_t total = 0;
     TPB_CUDA(e, cudaMemcpyAsync(&total, e->a.r_offset + d.B, sizeof(int64_t),
@@ -799,6 +837,149 @@ int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
   TPB_CUDA(e, cudaStreamSynchronize(e->stream));
   if (e->copy_stream) TPB_CUDA(e, cudaStreamSynchronize(e->copy_stream));
   return rc;
+}
+
+// ---------------------------------------------------------------- moving-horizon planner
+int32_t tpb_planner_reset(tpb_engine* e, int32_t path_sample_capacity, double time_step_sec,
+                          int32_t skip_method, int32_t max_planning_iterations,
+                          double max_initial_velocity_error, const double* initial_velocity,
+                          int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (e->mode != Mode::kJoint || !e->have_waypoints)
+    return fail(e, TPB_FAILED_PRECONDITION, "No path set");
+  if (d.r_cap <= 0) return fail(e, TPB_FAILED_PRECONDITION, "max_time_samples_total is 0");
+  if (!(time_step_sec > 0)) return fail(e, TPB_INVALID_ARGUMENT, "time step must be positive");
+  if (path_sample_capacity < d.N)
+    return fail(e, TPB_INVALID_ARGUMENT, "path_sample_capacity is below num_path_samples");
+  cudaSetDevice(e->device);
+  auto& w = e->w;
+  const size_t Bm = d.Bmax;
+  if (w.len == nullptr) {  // the per-path state, once
+    int32_t** i32[] = {&w.len, &w.active, &w.status, &w.mode, &w.initial_plan, &w.sampled,
+                       &w.planned_to_end, &w.target_reached, &w.loops, &w.offset,
+                       &w.erase_rows, &w.first_from, &w.keep_base};
+    for (auto p : i32) TPB_CUDA(e, dev_alloc(e, p, Bm));
+    int64_t** i64[] = {&w.start_time, &w.end_time, &w.final_decel_start, &w.loop_start};
+    for (auto p : i64) TPB_CUDA(e, dev_alloc(e, p, Bm));
+    double** f64[] = {&w.path_horizon, &w.decel_time, &w.origin, &w.front_time, &w.back_time};
+    for (auto p : f64) TPB_CUDA(e, dev_alloc(e, p, Bm));
+    TPB_CUDA(e, dev_alloc(e, &w.init_vel, Bm * d.D));
+    TPB_CUDA(e, dev_alloc(e, &w.any_active, 1));
+    TPB_CUDA(e, cudaMallocHost(reinterpret_cast<void**>(&e->any_active_host), sizeof(int32_t)));
+  }
+  if (path_sample_capacity > w.P_cap) {
+    TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+    for (void* p : e->w_big) cudaFree(p);
+    e->w_big.clear();
+    w.P_cap = 0;
+    const size_t BP = Bm * static_cast<size_t>(path_sample_capacity);
+    auto big = [&](auto** p, size_t count) -> cudaError_t {
+      void* q = nullptr;
+      cudaError_t err = cudaMalloc(&q, count * sizeof(**p));
+      if (err != cudaSuccess) return err;
+      e->w_big.push_back(q);
+      *p = static_cast<std::remove_reference_t<decltype(*p)>>(q);
+      return cudaSuccess;
+    };
+    TPB_CUDA(e, big(&w.w_time, BP));
+    TPB_CUDA(e, big(&w.w_s, BP));
+    TPB_CUDA(e, big(&w.w_sd, BP));
+    TPB_CUDA(e, big(&w.w_sdd, BP));
+    TPB_CUDA(e, big(&w.w_q, BP * d.D));
+    TPB_CUDA(e, big(&w.w_dq, BP * d.D));
+    TPB_CUDA(e, big(&w.w_ddq, BP * d.D));
+    TPB_CUDA(e, big(&w.keep, BP));
+    w.P_cap = path_sample_capacity;
+  }
+  e->wopt.dt = time_step_sec;
+  e->wopt.skip = skip_method != 0;
+  e->wopt.max_planning_iterations = max_planning_iterations;
+  e->wopt.max_initial_velocity_error = max_initial_velocity_error;
+  TPB_CUDA(e, fill_or_copy(e, w.init_vel, initial_velocity, static_cast<size_t>(d.B) * d.D,
+                           on_device));
+  TPB_CUDA(e, cudaMemsetAsync(e->a.r_count, 0, sizeof(int32_t) * d.B, e->stream));
+  TPB_CUDA(e, cudaMemsetAsync(e->a.r_offset, 0, sizeof(int64_t) * (d.B + 1), e->stream));
+  e->launches += tpb::launch_planner_reset(d, w, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->planner_ready = true;
+  e->resampled = true;  // zero rows so far
+  return TPB_OK;
+}
+
+int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
+                         int64_t* total_samples) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (e->mode != Mode::kJoint || !e->have_waypoints)
+    return fail(e, TPB_FAILED_PRECONDITION, "No path set.");
+  if (!e->have_limits) return fail(e, TPB_FAILED_PRECONDITION, "joint limits not set");
+  if (!e->planner_ready)
+    return fail(e, TPB_FAILED_PRECONDITION, "tpb_planner_reset was not called for these paths");
+  cudaSetDevice(e->device);
+  const auto& w = e->w;
+  const auto& o = e->wopt;
+  auto read_flag = [&](int32_t* flag) -> cudaError_t {
+    cudaError_t err = cudaMemcpyAsync(e->any_active_host, w.any_active, sizeof(int32_t),
+                                      cudaMemcpyDeviceToHost, e->stream);
+    if (err != cudaSuccess) return err;
+    err = cudaStreamSynchronize(e->stream);
+    *flag = *e->any_active_host;
+    return err;
+  };
+  TPB_CUDA(e, cudaMemsetAsync(w.any_active, 0, sizeof(int32_t), e->stream));
+  e->launches += tpb::launch_plan_begin(d, e->a, w, o, start_ns, horizon_ns, e->stream);
+  int32_t more = 0;
+  TPB_CUDA(e, read_flag(&more));
+  tpb::DeviceArrays am = e->a;  // the stage kernels, masked to the paths that plan a window
+  am.active = w.active;
+  const int max_solver_loops = std::max(100, 10 * d.N);  // (:399-401)
+  for (int window = 0; more != 0; ++window) {
+    if (window > o.max_planning_iterations + 1)
+      return fail(e, TPB_INTERNAL, "planning loop did not terminate");
+    e->launches += tpb::launch_window_begin(d, e->a, w, start_ns, horizon_ns, e->stream);
+    e->launches += tpb::launch_joint_sample_limit(d, am, e->safety, e->stream);
+    e->launches += tpb::launch_window_velocity(d, e->a, w, o, e->stream);
+    e->launches += tpb::launch_integrate(d, am, Mode::kJoint, e->safety, max_solver_loops,
+                                         e->stream);
+    TPB_CUDA(e, cudaMemsetAsync(w.any_active, 0, sizeof(int32_t), e->stream));
+    e->launches += tpb::launch_window_append(d, e->a, w, o, start_ns, horizon_ns, e->stream);
+    TPB_CUDA(e, read_flag(&more));
+  }
+  e->launches += tpb::launch_plan_rows(d, e->a, w, o, start_ns, e->stream);
+  // row assembly over the spliced samples: the resampling kernel on a view
+  tpb::Dims dv = d;
+  dv.N = w.P_cap;
+  tpb::DeviceArrays av = e->a;
+  av.time = w.w_time;
+  av.s = w.w_s;
+  av.sd = w.w_sd;
+  av.sdd = w.w_sdd;
+  av.q = w.w_q;
+  av.dq = w.w_dq;
+  av.ddq = w.w_ddq;
+  tpb::ResampleView v;
+  v.len = w.len;
+  v.origin = w.origin;
+  v.grid_skip = w.erase_rows;
+  v.first_from = w.first_from;
+  v.keep_base = w.keep_base;
+  e->launches += tpb::launch_resample_rows(dv, av, v, w.keep, 0.0, o.dt, e->num_sms, e->stream,
+                                           o.skip);
+  e->launches += tpb::launch_plan_end(d, e->a, w, o, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->sampled = e->optimized = false;  // the window scratch is not a fresh-path solution
+  e->resampled = true;
+  if (total_samples != nullptr) {
+    int64_t total = 0;
+    TPB_CUDA(e, cudaMemcpyAsync(&total, e->a.r_offset + d.B, sizeof(int64_t),
+                                cudaMemcpyDeviceToHost, e->stream));
+    TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+    *total_samples = total;
+    if (total > d.r_cap)
+      return fail(e, TPB_OUT_OF_RANGE, "trajectory rows exceed max_time_samples_total");
+  }
+  return TPB_OK;
 }
 
 int32_t tpb_get(tpb_engine* e, tpb_array what, void* dst, size_t bytes, int32_t to_device) {

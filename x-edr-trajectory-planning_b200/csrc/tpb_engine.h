@@ -88,6 +88,47 @@ struct DeviceArrays {
   double* r_s = nullptr;
   double* r_sd = nullptr;
   double* r_sdd = nullptr;
+  // moving-horizon planner: only paths with active[b] != 0 are sampled / timed
+  // (nullptr: all of them)
+  const int32_t* active = nullptr;
+};
+
+// Per-path overrides of the resampling kernels, used by the moving-horizon planner
+// (all nullptr: the plain fresh-path resampling of N samples from start_sec).
+struct ResampleView {
+  const int32_t* len = nullptr;         // number of path samples held
+  const double* origin = nullptr;       // time of row 0 of the uniform grid / of row 0
+  const int32_t* grid_skip = nullptr;   // uniform: rows of that grid erased in front
+  const int32_t* first_from = nullptr;  // skip method: the lower-index scan of row 0 starts here
+  const int32_t* keep_base = nullptr;   // skip method: kept-sample entries erased in front
+};
+
+// State of PathTimingTrajectory between Plan() calls for every path of the batch
+// (tpb_planner.cu).  P_cap path samples per path.
+struct PlannerArrays {
+  int P_cap = 0;
+  // *_at_path_samples_ (path_timing_trajectory.h): [B][P_cap], [B][P_cap][D]
+  double *w_time = nullptr, *w_s = nullptr, *w_sd = nullptr, *w_sdd = nullptr;
+  double *w_q = nullptr, *w_dq = nullptr, *w_ddq = nullptr;
+  int32_t* keep = nullptr;  // [B][P_cap] sample index of trajectory row k + 1 (skip method)
+  // [B]
+  int32_t *len = nullptr, *active = nullptr, *status = nullptr, *mode = nullptr,
+          *initial_plan = nullptr, *sampled = nullptr, *planned_to_end = nullptr,
+          *target_reached = nullptr, *loops = nullptr, *offset = nullptr,
+          *erase_rows = nullptr, *first_from = nullptr, *keep_base = nullptr;
+  int64_t *start_time = nullptr, *end_time = nullptr, *final_decel_start = nullptr,
+          *loop_start = nullptr;
+  double *path_horizon = nullptr, *decel_time = nullptr, *origin = nullptr,
+         *front_time = nullptr, *back_time = nullptr;
+  double* init_vel = nullptr;     // [B][D]
+  int32_t* any_active = nullptr;  // [1]
+};
+
+struct PlannerOptions {
+  double dt = 0.0;  // time step
+  bool skip = false;
+  int max_planning_iterations = 0;
+  double max_initial_velocity_error = 0.0;
 };
 
 struct Dims {
@@ -122,6 +163,30 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
 // ResampleEquidistantlyInTime
 int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, double dt,
                     int num_sms, cudaStream_t st, bool continued = false, bool skip = false);
+
+// scan of r_count + row assembly only (the counts are already in r_count)
+int launch_resample_rows(const Dims& d, const DeviceArrays& a, const ResampleView& v,
+                         const int32_t* keep, double start_sec, double dt, int num_sms,
+                         cudaStream_t st, bool skip, bool continued = false);
+
+// Moving-horizon planner (tpb_planner.cu).  plan_begin .. plan_end bracket one
+// Plan() call; window_begin / window_velocity / window_append bracket the
+// sampling + timing of one planning window of the active paths.
+int launch_planner_reset(const Dims& d, const PlannerArrays& w, cudaStream_t st);
+int launch_plan_begin(const Dims& d, const DeviceArrays& a, const PlannerArrays& w,
+                      const PlannerOptions& o, int64_t start_ns, int64_t horizon_ns,
+                      cudaStream_t st);
+int launch_window_begin(const Dims& d, const DeviceArrays& a, const PlannerArrays& w,
+                        int64_t start_ns, int64_t horizon_ns, cudaStream_t st);
+int launch_window_velocity(const Dims& d, const DeviceArrays& a, const PlannerArrays& w,
+                           const PlannerOptions& o, cudaStream_t st);
+int launch_window_append(const Dims& d, const DeviceArrays& a, const PlannerArrays& w,
+                         const PlannerOptions& o, int64_t start_ns, int64_t horizon_ns,
+                         cudaStream_t st);
+int launch_plan_rows(const Dims& d, const DeviceArrays& a, const PlannerArrays& w,
+                     const PlannerOptions& o, int64_t start_ns, cudaStream_t st);
+int launch_plan_end(const Dims& d, const DeviceArrays& a, const PlannerArrays& w,
+                    const PlannerOptions& o, cudaStream_t st);
 
 // Batched RescaleTrajectoryBackwardToStop (tpb_stop.cu); all pointers device.
 struct StopArgs {
@@ -195,6 +260,7 @@ inline DeviceArrays shifted_joint(const DeviceArrays& a, const Dims& d, int b0) 
   adv(s.duration, 1);
   adv(s.r_count, 1);
   adv(s.r_offset, 1);
+  adv(s.active, 1);
   return s;
 }
 

@@ -768,6 +768,7 @@ k_integrate(Dims dm, DeviceArrays a, bool joint, double safety, int max_loops) {
   const int lane = threadIdx.x & 31;
   const int b = blockIdx.x * kWarpsPerBlock + warp;
   if (b >= dm.B) return;
+  if (a.active != nullptr && a.active[b] == 0) return;  // moving-horizon planner: not in this window
   const int N = dm.N;
   const size_t o = static_cast<size_t>(b) * N;
 

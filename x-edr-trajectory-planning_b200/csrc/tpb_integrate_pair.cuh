@@ -450,7 +450,7 @@ k_optimize_pair(Dims dm, DeviceArrays a, double safety, int max_loops) {
   const int half = (threadIdx.x >> 4) & 1;
   const int lane = threadIdx.x & 15;
   const int b = (blockIdx.x * kPairWarpsPerBlock + warp) * 2 + half;
-  const bool has_path = b < dm.B;
+  const bool has_path = b < dm.B && (a.active == nullptr || a.active[b] != 0);
   const int bb = has_path ? b : 0;  // an absent half computes on path 0 and stores nothing
   const int N = dm.N;
   const size_t o = static_cast<size_t>(bb) * N;

@@ -74,6 +74,7 @@ __global__ void __launch_bounds__(kSampleThreads)
 k_joint_sample_limit_any(Dims dm, DeviceArrays a, double safety) {
   extern __shared__ double smem[];
   const int b = blockIdx.y;
+  if (a.active != nullptr && a.active[b] == 0) return;  // uniform per CTA
   const int D = dm.D;
   const int n = a.num_points[b];
   const int nk = n + 3;
@@ -168,6 +169,7 @@ __global__ void __launch_bounds__(kSampleThreads, TPB_SL_MINBLOCKS)
 k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
   extern __shared__ double smem[];
   const int b = blockIdx.y;
+  if (a.active != nullptr && a.active[b] == 0) return;  // uniform per CTA
   const int n = a.num_points[b];
   const int nk = n + 3;
   double* s_knots = smem;                         // [max_points + 3]
@@ -404,19 +406,31 @@ constexpr int kResampleThreads = 256;
 // grid: row 0 is interpolated at start_sec, row i > 0 IS path sample keep[b][i-1]
 // (li = ui = that sample, values taken as they are), so that both methods share the
 // assembly and the transposed writes.
+//
+// ResampleView v (moving-horizon planner): path b holds v.len[b] of the dm.N sample
+// slots, its rows start at time v.origin[b], v.grid_skip[b] rows of the uniform grid
+// are erased in front (row i is grid row i + grid_skip, so that the times keep the
+// bits of the grid they were first computed on), and with kSkip row 0's lower-index
+// scan starts at v.first_from[b] and row i > 0 is sample keep[b][keep_base + i - 1].
 template <bool kSmemTime, bool kSkip>
 __global__ void __launch_bounds__(kResampleThreads)
-k_resample_fill(Dims dm, DeviceArrays a, const int32_t* keep, double start_sec, double dt) {
+k_resample_fill(Dims dm, DeviceArrays a, ResampleView v, const int32_t* keep, double start_sec,
+                double dt) {
   extern __shared__ double smem[];
-  const int N = dm.N, D = dm.D;
+  const int stride = dm.N, D = dm.D;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double* s_time = smem;                                    // [N] (kSmemTime)
-  double* s_tile = smem + (kSmemTime ? N : 0) + warp * 3 * 32 * D;  // [3][32][D] per warp
+  double* s_tile = smem + (kSmemTime ? stride : 0) + warp * 3 * 32 * D;  // [3][32][D] per warp
   for (int b = blockIdx.x; b < dm.B; b += gridDim.x) {
     const int M = a.r_count[b];
     if (M == 0) continue;  // uniform per CTA
+    const int N = v.len ? v.len[b] : stride;
+    const double t0 = v.origin ? v.origin[b] : start_sec;
+    const int grid_skip = v.grid_skip ? v.grid_skip[b] : 0;
+    const int from = (kSkip && v.first_from) ? v.first_from[b] : 0;
+    const int kbase = (kSkip && v.keep_base) ? v.keep_base[b] : 0;
     const int64_t row0 = a.r_offset[b];
-    const size_t o = static_cast<size_t>(b) * N;
+    const size_t o = static_cast<size_t>(b) * stride;
     const double* tg = a.time + o;
     if (kSmemTime) {
       __syncthreads();  // previous path's searches are done
@@ -430,12 +444,12 @@ k_resample_fill(Dims dm, DeviceArrays a, const int32_t* keep, double start_sec, 
       if (live) {
         const int64_t row = row0 + i;
         const bool sample_row = kSkip && i > 0;
-        const int src = sample_row ? keep[o + i - 1] : 0;
-        const double t = sample_row ? tp[src] : start_sec + dt * i;
+        const int src = sample_row ? keep[o + kbase + i - 1] : 0;
+        const double t = sample_row ? tp[src] : (kSkip ? t0 : t0 + dt * (i + grid_skip));
         // TimeAtPathSamplesLowerIndex (:686-695): first index with time[index+1] > t,
         // else N-1.  time[] is non-decreasing, so the reference's monotone linear scan
         // equals this binary search.
-        int lo = 0, hi = N - 1;  // answer in [0, N-1]
+        int lo = min(from, N - 1), hi = N - 1;  // answer in [from, N-1]
         while (!sample_row && lo < hi) {
           const int mid = (lo + hi) >> 1;
           if (tp[mid + 1] > t) {
@@ -611,6 +625,32 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
   return 1;
 }
 
+int launch_resample_rows(const Dims& d, const DeviceArrays& a, const ResampleView& v,
+                         const int32_t* keep, double start_sec, double dt, int num_sms,
+                         cudaStream_t st, bool skip, bool continued) {
+  k_scan_offsets<<<1, 1024, 0, st>>>(d.B, a.r_count, a.r_offset, continued ? 1 : 0);
+  const size_t tile = sizeof(double) * (kResampleThreads / 32) * 3 * 32 * d.D;
+  const size_t with_time = tile + sizeof(double) * d.N;
+  const int grid = std::min(d.B, num_sms * 16);
+  if (with_time <= 160 * 1024) {
+    // > 48 KB of dynamic shared memory is opt-in (per device, so set it every time)
+    if (skip) {
+      cudaFuncSetAttribute(k_resample_fill<true, true>,
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+      k_resample_fill<true, true><<<grid, kResampleThreads, with_time, st>>>(d, a, v, keep, start_sec, dt);
+    } else {
+      cudaFuncSetAttribute(k_resample_fill<true, false>,
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+      k_resample_fill<true, false><<<grid, kResampleThreads, with_time, st>>>(d, a, v, keep, start_sec, dt);
+    }
+  } else if (skip) {
+    k_resample_fill<false, true><<<grid, kResampleThreads, tile, st>>>(d, a, v, keep, start_sec, dt);
+  } else {
+    k_resample_fill<false, false><<<grid, kResampleThreads, tile, st>>>(d, a, v, keep, start_sec, dt);
+  }
+  return 2;
+}
+
 int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, double dt,
                     int num_sms, cudaStream_t st, bool continued, bool skip) {
   const int threads = 128;
@@ -623,27 +663,8 @@ int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, doub
   } else {
     k_resample_count<<<(d.B + threads - 1) / threads, threads, 0, st>>>(d, a, start_sec, dt);
   }
-  k_scan_offsets<<<1, 1024, 0, st>>>(d.B, a.r_count, a.r_offset, continued ? 1 : 0);
-  const size_t tile = sizeof(double) * (kResampleThreads / 32) * 3 * 32 * d.D;
-  const size_t with_time = tile + sizeof(double) * d.N;
-  const int grid = std::min(d.B, num_sms * 16);
-  if (with_time <= 160 * 1024) {
-    // > 48 KB of dynamic shared memory is opt-in (per device, so set it every time)
-    if (skip) {
-      cudaFuncSetAttribute(k_resample_fill<true, true>,
-                           cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-      k_resample_fill<true, true><<<grid, kResampleThreads, with_time, st>>>(d, a, keep, start_sec, dt);
-    } else {
-      cudaFuncSetAttribute(k_resample_fill<true, false>,
-                           cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-      k_resample_fill<true, false><<<grid, kResampleThreads, with_time, st>>>(d, a, keep, start_sec, dt);
-    }
-  } else if (skip) {
-    k_resample_fill<false, true><<<grid, kResampleThreads, tile, st>>>(d, a, keep, start_sec, dt);
-  } else {
-    k_resample_fill<false, false><<<grid, kResampleThreads, tile, st>>>(d, a, keep, start_sec, dt);
-  }
-  return 3;
+  return 1 + launch_resample_rows(d, a, ResampleView{}, keep, start_sec, dt, num_sms, st, skip,
+                                  continued);
 }
 
 }  // namespace tpb
