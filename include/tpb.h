@@ -302,6 +302,12 @@ int32_t tpb_planner_reset(tpb_engine* e, int32_t path_sample_capacity, double ti
                           int32_t on_device);
 int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
                          int64_t* total_samples);
+/* New waypoints were set (tpb_set_joint_waypoints) on a planner that keeps its plan:
+ * every path is TimeablePath::State::kNewPath again (timed from its first sample at
+ * the next plan, :322-327, all previous path samples replaced), the trajectory,
+ * start / end times stay (no PathTimingTrajectory::Reset).  The batch size must not
+ * have changed. */
+int32_t tpb_planner_new_path(tpb_engine* e, const double* initial_velocity, int32_t on_device);
 
 /* Whole pipeline for a batch of fresh joint paths with HOST buffers in and out:
  * set waypoints+limits, sample, optimize, resample, copy back durations,

@@ -170,18 +170,70 @@ int main() {
       rows.push_back(c.upper(r));
     }
     PrintArray("constraints_sample10", rows);
-    // moving-horizon use is outside the hot path
+  }
+  // ---- RestToRestPlanningWorks (:112-173) as the reference runs it: default path
+  // sampling distance (several planning windows), Plan() called again every 200 ms
+  // with a 750 ms horizon until the trajectory is at its end; both sampling methods
+  for (int method = 0; method < 2; ++method) {
+    std::vector<VectorXd> wps = {VectorXd{1, 2, 3}, VectorXd{-1, -2, -3}, VectorXd{1, 2, 3}};
+    VectorXd vmax = VectorXd::Constant(kNDof, 1.0), amax = VectorXd::Constant(kNDof, 2.0);
     auto path2 = std::make_shared<TimeableJointSplinePath>(
         JointPathOptions().set_num_dofs(kNDof).set_num_path_samples(kNumSamples));
-    PathTimingTrajectory planner2(PathTimingTrajectoryOptions()
-                                      .SetTimeStep(tp::Milliseconds(4))
-                                      .SetNumDofs(kNDof)
-                                      .SetNumPathSamples(kNumSamples));
+    PathTimingTrajectory planner2(
+        PathTimingTrajectoryOptions()
+            .SetTimeStep(tp::Milliseconds(4))
+            .SetNumDofs(kNDof)
+            .SetNumPathSamples(kNumSamples)
+            .SetTimeSamplingMethod(method == 0
+                                       ? PathTimingTrajectoryOptions::TimeSamplingMethod::kUniformlyInTime
+                                       : PathTimingTrajectoryOptions::TimeSamplingMethod::
+                                             kSkipSamplesCloserThanTimeStep));
     EXPECT(planner2.SetPath(path2).ok());
     EXPECT(path2->SetWaypoints(wps).ok());
     path2->SetMaxJointVelocity(ToSpan(vmax));
     path2->SetMaxJointAcceleration(ToSpan(amax));
-    EXPECT(planner2.Plan(TimeFromSec(0.0), tp::Seconds(100)).code() == tp::StatusCode::kUnimplemented);
+    tp::Time start_time = TimeFromSec(0.0);
+    int loops = 0, windows = 0;
+    std::vector<double> starts, counts, first_times, end_times;
+    for (; !planner2.IsTrajectoryAtEnd() && loops < 500; ++loops) {
+      const tp::Status st = planner2.Plan(start_time, tp::Milliseconds(750));
+      EXPECT(st.ok());
+      if (!st.ok()) {
+        fprintf(stderr, "Plan %d: %s\n", loops, st.message().c_str());
+        break;
+      }
+      windows += planner2.LastPlanWindows();
+      EXPECT(planner2.GetPositions().size() == planner2.GetVelocities().size());
+      EXPECT(planner2.GetPositions().size() == planner2.GetAccelerations().size());
+      starts.push_back(static_cast<double>(start_time.ns));
+      counts.push_back(static_cast<double>(planner2.GetNumTimeSamples()));
+      first_times.push_back(planner2.GetTime().front());
+      end_times.push_back(static_cast<double>(planner2.GetEndTime().ns));
+      const tp::Time next = start_time + tp::Milliseconds(200);
+      start_time = planner2.GetEndTime() < next ? planner2.GetEndTime() : next;
+    }
+    EXPECT(planner2.IsTrajectoryAtEnd());
+    EXPECT(windows >= 3);
+    EXPECT(!planner2.GetPositions().empty());
+    if (!planner2.GetPositions().empty()) {
+      EXPECT(planner2.GetPositions().back() == wps.back());
+      for (size_t d = 0; d < kNDof; ++d) EXPECT(planner2.GetVelocities().back()[d] == 0.0);
+    }
+    // a start past the end of the plan is rejected (HandleTimeArguments, :503-511)
+    EXPECT(planner2.Plan(planner2.GetEndTime() + tp::Seconds(1.0), tp::Milliseconds(750)).code() ==
+           tp::StatusCode::kOutOfRange);
+    printf("\"%s\": {\n", method == 0 ? "replanning" : "replanning_skip");
+    PrintArray("starts_ns", starts);
+    PrintArray("counts", counts);
+    PrintArray("first_times", first_times);
+    PrintArray("end_times_ns", end_times);
+    PrintArray("time", planner2.GetTime());
+    PrintArray("positions", Flatten(planner2.GetPositions()));
+    PrintArray("velocities", Flatten(planner2.GetVelocities()));
+    PrintArray("accelerations", Flatten(planner2.GetAccelerations()));
+    PrintArray("path_parameter", planner2.GetPathParameters());
+    printf("\"loops\": %d, \"windows\": %d, \"final_decel_start_ns\": %lld},\n", loops, windows,
+           static_cast<long long>(planner2.GetFinalDecelStart().ns));
   }
   // ---- Circle (time_optimal_path_timing_test.cc:496-559)
   {

@@ -158,3 +158,34 @@ def test_skip_method_plan_matches_oracle(result, po):
     assert np.array_equal(np.array(r["time"]), o["r_t"])
     assert np.array_equal(np.array(r["positions"]).reshape(-1, 3), o["r_pos"])
     assert np.array_equal(np.array(r["velocities"]).reshape(-1, 3), o["r_vel"])
+
+
+@pytest.mark.parametrize("key,skip", [("replanning", False), ("replanning_skip", True)])
+def test_moving_horizon_replanning_matches_oracle(result, po, key, skip):
+    """host Plan() called again every 200 ms with a 750 ms horizon over several planning
+    windows (RestToRestPlanningWorks, path_timing_trajectory_test.cc:112-173) against the
+    oracle's planner, every call's sample count / first time / end time and the final
+    trajectory bit for bit."""
+    wp = np.array([[1.0, 2, 3], [-1, -2, -3], [1, 2, 3]])
+    r = result[key]
+    pl = po.Planner(wp, np.ones(3), np.full(3, 2.0), 1000, 0.005, 0.004, skip=skip,
+                    max_initial_velocity_error=1e-2)
+    start, counts, firsts, ends, windows = 0, [], [], [], 0
+    while not pl.target_reached:
+        assert pl.plan(start, 750_000_000) == po.ORC_OK
+        counts.append(pl.M)
+        firsts.append(pl.trajectory()["r_t"][0])
+        ends.append(pl.end_time)
+        windows += pl.loops
+        start = min(pl.end_time, start + 200_000_000)
+    assert r["loops"] == len(counts) and r["windows"] == windows
+    assert [int(c) for c in r["counts"]] == counts
+    assert np.array_equal(np.array(r["first_times"]), np.array(firsts))
+    assert [int(x) for x in r["end_times_ns"]] == ends
+    tr = pl.trajectory()
+    assert np.array_equal(np.array(r["time"]), tr["r_t"])
+    assert np.array_equal(np.array(r["positions"]).reshape(-1, 3), tr["r_pos"])
+    assert np.array_equal(np.array(r["velocities"]).reshape(-1, 3), tr["r_vel"])
+    assert np.array_equal(np.array(r["accelerations"]).reshape(-1, 3), tr["r_acc"])
+    assert np.array_equal(np.array(r["path_parameter"]), tr["r_s"])
+    assert r["final_decel_start_ns"] == pl.final_decel_start

@@ -147,6 +147,8 @@ def lib():
         L.tpb_resample_skipping.argtypes = [vp, C.c_double, C.c_double, C.POINTER(C.c_int64)]
         L.tpb_planner_reset.restype = i32
         L.tpb_planner_reset.argtypes = [vp, i32, C.c_double, i32, i32, C.c_double, vp, i32]
+        L.tpb_planner_new_path.restype = i32
+        L.tpb_planner_new_path.argtypes = [vp, vp, i32]
         L.tpb_planner_plan.restype = i32
         L.tpb_planner_plan.argtypes = [vp, C.c_int64, C.c_int64, C.POINTER(C.c_int64)]
         L.tpb_path_stop_parameter.restype = i32
@@ -359,6 +361,12 @@ class Engine:
                                          1 if skip else 0, max_planning_iterations,
                                          max_initial_velocity_error, p, dev))
         self.P = int(path_sample_capacity)
+
+    def planner_new_path(self, initial_velocity=None):
+        """tpb_planner_new_path: new waypoints on a planner that keeps its plan."""
+        v0 = _f64(initial_velocity)
+        p, dev = _ptr(v0)
+        self._ck(lib().tpb_planner_new_path(self._h, p, dev))
 
     def planner_plan(self, start_ns, horizon_ns, want_total=True):
         """tpb_planner_plan: PathTimingTrajectory::Plan(start, horizon) for every path

@@ -907,6 +907,23 @@ int32_t tpb_planner_reset(tpb_engine* e, int32_t path_sample_capacity, double ti
   return TPB_OK;
 }
 
+int32_t tpb_planner_new_path(tpb_engine* e, const double* initial_velocity, int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (e->mode != Mode::kJoint || !e->have_waypoints)
+    return fail(e, TPB_FAILED_PRECONDITION, "No path set");
+  if (e->w.len == nullptr || e->w.P_cap < d.N)
+    return fail(e, TPB_FAILED_PRECONDITION, "tpb_planner_reset was never called");
+  cudaSetDevice(e->device);
+  TPB_CUDA(e, fill_or_copy(e, e->w.init_vel, initial_velocity, static_cast<size_t>(d.B) * d.D,
+                           on_device));
+  e->launches += tpb::launch_planner_new_path(d, e->w, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  e->planner_ready = true;
+  e->resampled = true;
+  return TPB_OK;
+}
+
 int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
                          int64_t* total_samples) {
   if (e == nullptr) return TPB_INVALID_ARGUMENT;

@@ -173,6 +173,7 @@ int launch_resample_rows(const Dims& d, const DeviceArrays& a, const ResampleVie
 // Plan() call; window_begin / window_velocity / window_append bracket the
 // sampling + timing of one planning window of the active paths.
 int launch_planner_reset(const Dims& d, const PlannerArrays& w, cudaStream_t st);
+int launch_planner_new_path(const Dims& d, const PlannerArrays& w, cudaStream_t st);
 int launch_plan_begin(const Dims& d, const DeviceArrays& a, const PlannerArrays& w,
                       const PlannerOptions& o, int64_t start_ns, int64_t horizon_ns,
                       cudaStream_t st);

@@ -67,6 +67,13 @@ __global__ void k_planner_reset(Dims dm, PlannerArrays w) {
   w.path_horizon[b] = w.decel_time[b] = w.origin[b] = w.front_time[b] = w.back_time[b] = 0.0;
 }
 
+// SetWaypoints on a planner that already holds a plan: every path is kNewPath again,
+// the planner keeps its trajectory and times.
+__global__ void k_planner_new_path(Dims dm, PlannerArrays w) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < dm.B) w.sampled[b] = 0;
+}
+
 // time of trajectory row i of path b (the rows themselves may lie past r_capacity)
 __device__ __forceinline__ double row_time(const PlannerArrays& w, const PlannerOptions& o, int b,
                                            int i) {
@@ -407,6 +414,10 @@ inline int blocks_for(int n, int threads) { return (n + threads - 1) / threads; 
 
 int launch_planner_reset(const Dims& d, const PlannerArrays& w, cudaStream_t st) {
   k_planner_reset<<<blocks_for(d.B, 128), 128, 0, st>>>(d, w);
+  return 1;
+}
+int launch_planner_new_path(const Dims& d, const PlannerArrays& w, cudaStream_t st) {
+  k_planner_new_path<<<blocks_for(d.B, 128), 128, 0, st>>>(d, w);
   return 1;
 }
 int launch_plan_begin(const Dims& d, const DeviceArrays& a, const PlannerArrays& w,

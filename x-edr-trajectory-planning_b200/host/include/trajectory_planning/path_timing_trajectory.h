@@ -1,17 +1,20 @@
 // Host-side mirror of PathTimingTrajectory
 // (trajectory_planning/path_timing_trajectory.h:33-186, .cc:206-902).
 //
-// Plan() drives the GPU stages through the path's engine: SamplePath + limit
-// curve -> OptimizePathParameter -> per-sample assembly + uniform-in-time
-// resampling (ComputeTimingProfile .cc:307-475, ResampleEquidistantlyInTime
-// .cc:755-783), then downloads the resampled trajectory into the
-// TrajectoryPlanner vectors.
+// Plan() runs on the device.  For a TimeableJointSplinePath the whole
+// PathTimingTrajectory::Plan state machine lives there (tpb_planner_plan:
+// HandleTimeArguments, the moving-horizon loop over ComputeTimingProfile .cc:307-475
+// with splicing of the path samples, the "already planned enough" erase, both time
+// sampling methods); this class keeps the options, maps the per-path status back to
+// the reference's Status codes and downloads the trajectory into the
+// TrajectoryPlanner vectors.  Re-planning with a shifted start time (Plan() called
+// again while the previous trajectory is being executed) works as in the reference.
 //
-// Scope: a fresh path (State::kNewPath) whose
-// planning loop needs one path window, plus the "already planned enough"
-// re-entry (.cc:590-601).  Moving-horizon re-planning across windows,
-// is a "next" row; both time sampling methods and GetPathStopParameter run on
-// the device.  Paths must be TimeableJointSplinePath.
+// Paths whose samples come from host callbacks (TimeableCartesianSplinePath with
+// user PathIKFunc / JacobianFunc) are planned one window at a time from here
+// (PlanOneWindow): a fresh path (State::kNewPath) whose planning loop needs a single
+// window, plus the "already planned enough" re-entry (.cc:590-601).
+// GetPathStopParameter runs on the device for both.
 #ifndef TRAJECTORY_PLANNING_PATH_TIMING_TRAJECTORY_H_
 #define TRAJECTORY_PLANNING_PATH_TIMING_TRAJECTORY_H_
 
@@ -84,8 +87,122 @@ class PathTimingTrajectory : public TrajectoryPlanner {
 
   // Plan (.cc:579-684)
   tp::Status Plan(tp::Time start, tp::Duration time_horizon) override {
-    const double start_sec = TimeToSec(start);
     if (path_ == nullptr) return {tp::StatusCode::kFailedPrecondition, "No path set."};
+    if (path_->SupportsDevicePlanner()) return PlanOnDevice(start, time_horizon);
+    return PlanOneWindow(start, time_horizon);
+  }
+
+  // Extension: capacity (in path samples) of the spliced *_at_path_samples_ arrays on
+  // the device; 0 = 64 planning windows.
+  void SetPathSampleCapacity(size_t samples) { path_sample_capacity_ = samples; }
+
+ private:
+  // Plan (.cc:579-684) through tpb_planner_plan.
+  tp::Status PlanOnDevice(tp::Time start, tp::Duration time_horizon) {
+    const auto state = path_->GetState();
+    if (state == TimeablePath::State::kNoPath) return tp::FailedPreconditionError("No path set");
+    if (state == TimeablePath::State::kModifiedPath) {
+      return tp::UnimplementedError("re-timing of a modified path (SwitchToWaypointPath)");
+    }
+    if (auto st = path_->BeforeDevicePlan(); !st.ok()) return st;
+    tpb_engine* e = path_->DeviceEngine();
+    if (e == nullptr) return tp::InternalError("path has no device engine");
+    const bool skipping = options_.GetTimeSamplingMethod() ==
+                          PathTimingTrajectoryOptions::TimeSamplingMethod::kSkipSamplesCloserThanTimeStep;
+    int32_t rc = TPB_OK;
+    if (state == TimeablePath::State::kNewPath) {
+      const tp::VectorXd& v0 = path_->GetInitialVelocity();
+      if (initial_plan_ && device_planner_ == e) {
+        rc = tpb_planner_new_path(e, v0.data(), 0);  // the plan so far stays (no Reset())
+      } else {
+        const size_t cap = path_sample_capacity_ ? path_sample_capacity_ : 64 * options_.GetNumPathSamples();
+        rc = tpb_planner_reset(e, static_cast<int32_t>(cap), time_step_sec_, skipping ? 1 : 0,
+                               options_.GetMaxPlanningIterations(),
+                               options_.GetMaxInitialVelocityError(), v0.data(), 0);
+      }
+      if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
+      device_planner_ = e;
+    } else if (device_planner_ != e) {
+      return tp::FailedPreconditionError("the path was sampled, but not by this planner");
+    }
+    int64_t total = 0;
+    rc = tpb_planner_plan(e, start.ns, time_horizon.ns, &total);
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
+    // the planner's state after the call
+    int32_t status = TPB_PATH_NOT_RUN, loops = 0, to_end = 0, reached = 0, rows_mode = 0;
+    int64_t start_ns = 0, end_ns = 0, decel_ns = 0;
+    tpb_get(e, TPB_ARR_PLAN_STATUS, &status, sizeof(status), 0);
+    tpb_get(e, TPB_ARR_PLAN_LOOPS, &loops, sizeof(loops), 0);
+    tpb_get(e, TPB_ARR_PLAN_PLANNED_TO_END, &to_end, sizeof(to_end), 0);
+    tpb_get(e, TPB_ARR_PLAN_TARGET_REACHED, &reached, sizeof(reached), 0);
+    tpb_get(e, TPB_ARR_PLAN_ERASED, &rows_mode, sizeof(rows_mode), 0);
+    tpb_get(e, TPB_ARR_PLAN_START_TIME, &start_ns, sizeof(start_ns), 0);
+    tpb_get(e, TPB_ARR_PLAN_END_TIME, &end_ns, sizeof(end_ns), 0);
+    tpb_get(e, TPB_ARR_PLAN_FINAL_DECEL_START, &decel_ns, sizeof(decel_ns), 0);
+    start_time_ = tp::FromUnixNanos(start_ns);
+    end_time_ = tp::FromUnixNanos(end_ns);
+    final_decel_start_ = tp::FromUnixNanos(decel_ns);
+    planned_to_end_ = to_end != 0;
+    target_reached_ = reached != 0;
+    last_plan_windows_ = loops;
+    if (auto st = path_->AfterDevicePlan(loops > 0); !st.ok()) return st;
+    if (auto st = DownloadTrajectory(e, total); !st.ok()) return st;
+    if (status != TPB_PATH_OK) return PlanStatus(status);
+    if (rows_mode == 0) initial_plan_ = true;
+    return tp::OkStatus();
+  }
+
+  // the reference's Status for a per-path outcome of tpb_planner_plan
+  static tp::Status PlanStatus(int32_t status) {
+    switch (status) {
+      case TPB_PATH_OK: return tp::OkStatus();
+      case TPB_PATH_FAIL_SETUP: return tp::InternalError("Error setting up optimization problem");
+      case TPB_PATH_FAIL_DEADLINE:
+        return {tp::StatusCode::kDeadlineExceeded, "Reached maximum number of planning loops"};
+      case TPB_PATH_FAIL_START_RANGE:
+        return {tp::StatusCode::kOutOfRange, "start outside of the previous plan"};
+      case TPB_PATH_FAIL_START_ARG:
+        return tp::InvalidArgumentError("start time / duration not valid for the previous plan");
+      case TPB_PATH_FAIL_START_END: return tp::InternalError("time >= end_time_");
+      case TPB_PATH_FAIL_NO_SAMPLES: return tp::FailedPreconditionError("No samples yet.");
+      case TPB_PATH_FAIL_INITIAL_VELOCITY:
+        return tp::InvalidArgumentError(
+            "Could not satisfy initial velocity (probably not parallel to initial tangent)");
+      case TPB_PATH_FAIL_CAPACITY:
+        return {tp::StatusCode::kResourceExhausted, "path sample capacity exceeded (SetPathSampleCapacity)"};
+      default: return tp::InternalError("Error optimizing path parameter");
+    }
+  }
+
+  // the packed trajectory rows of the (single) path into the TrajectoryPlanner vectors
+  tp::Status DownloadTrajectory(tpb_engine* e, int64_t total) {
+    const size_t M = static_cast<size_t>(total), D = options_.GetNumDofs();
+    time_.resize(M);
+    path_parameter_.resize(M);
+    path_parameter_derivative_.resize(M);
+    second_path_parameter_derivative_.resize(M);
+    positions_.resize(M);
+    velocities_.resize(M);
+    accelerations_.resize(M);
+    if (M == 0) return tp::OkStatus();
+    std::vector<double> buf(M * D);
+    tpb_get(e, TPB_ARR_R_TIME, time_.data(), M * sizeof(double), 0);
+    tpb_get(e, TPB_ARR_R_S, path_parameter_.data(), M * sizeof(double), 0);
+    tpb_get(e, TPB_ARR_R_SD, path_parameter_derivative_.data(), M * sizeof(double), 0);
+    tpb_get(e, TPB_ARR_R_SDD, second_path_parameter_derivative_.data(), M * sizeof(double), 0);
+    std::vector<tp::VectorXd>* dst[3] = {&positions_, &velocities_, &accelerations_};
+    const tpb_array what[3] = {TPB_ARR_R_POS, TPB_ARR_R_VEL, TPB_ARR_R_ACC};
+    for (int k = 0; k < 3; ++k) {
+      const int32_t rc = tpb_get(e, what[k], buf.data(), buf.size() * sizeof(double), 0);
+      if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
+      for (size_t i = 0; i < M; ++i) (*dst[k])[i] = tp::VectorXd(&buf[i * D], D);
+    }
+    return tp::OkStatus();
+  }
+
+  // Plan (.cc:579-684) for paths sampled through host callbacks: one planning window.
+  tp::Status PlanOneWindow(tp::Time start, tp::Duration time_horizon) {
+    const double start_sec = TimeToSec(start);
     // HandleTimeArguments (.cc:502-538)
     if (initial_plan_ && start > end_time_ + tp::Seconds(time_step_sec_)) {
       return {tp::StatusCode::kOutOfRange, "start > end of previous plan"};
@@ -123,9 +240,15 @@ class PathTimingTrajectory : public TrajectoryPlanner {
       EraseTrajectoryBefore(start);
       return tp::OkStatus();
     }
-    if (planned_to_end_) {  // nothing left to plan (loop at .cc:628 does not run)
-      target_reached_ = true;
-      return tp::OkStatus();
+    if (planned_to_end_) {
+      // the loop at .cc:628 does not run: GetTimeOffsetAfter (.cc:289-305), then the
+      // trajectory is resampled from the new start (.cc:660)
+      if (time_.empty()) return tp::FailedPreconditionError("No samples yet.");
+      if (start_sec < time_.front()) return {tp::StatusCode::kOutOfRange, "time < start_time."};
+      if (!(time_.back() > start_sec)) return tp::InternalError("time >= end_time_");
+      tpb_engine* held = path_->DeviceEngine();
+      if (held == nullptr) return tp::InternalError("path has no device engine");
+      return ResampleAndFinish(held, start_sec);
     }
     if (state != TimeablePath::State::kNewPath) {
       return tp::UnimplementedError(
@@ -195,36 +318,26 @@ class PathTimingTrajectory : public TrajectoryPlanner {
           "path needs more than one planning window (increase num_path_samples * delta_parameter)");
     }
 
-    // ---- ResampleTrajectory (.cc:697-707, 755-783) on the device
+    last_extremal_ = last_extremal;
+    return ResampleAndFinish(e, start_sec);
+  }
+
+  // ResampleTrajectory (.cc:697-707, 755-783) on the device and the end of Plan
+  // (.cc:660-676), for the single window held by the engine.
+  tp::Status ResampleAndFinish(tpb_engine* e, double start_sec) {
     int64_t total = 0;
     const bool skipping = options_.GetTimeSamplingMethod() ==
                           PathTimingTrajectoryOptions::TimeSamplingMethod::kSkipSamplesCloserThanTimeStep;
-    rc = skipping ? tpb_resample_skipping(e, start_sec, time_step_sec_, &total)
-                  : tpb_resample(e, start_sec, time_step_sec_, &total);
+    const int32_t rc = skipping ? tpb_resample_skipping(e, start_sec, time_step_sec_, &total)
+                                : tpb_resample(e, start_sec, time_step_sec_, &total);
     if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
-    const size_t M = static_cast<size_t>(total), D = options_.GetNumDofs();
-    time_.resize(M);
-    path_parameter_.resize(M);
-    path_parameter_derivative_.resize(M);
-    second_path_parameter_derivative_.resize(M);
-    std::vector<double> buf(M * D);
-    tpb_get(e, TPB_ARR_R_TIME, time_.data(), M * sizeof(double), 0);
-    tpb_get(e, TPB_ARR_R_S, path_parameter_.data(), M * sizeof(double), 0);
-    tpb_get(e, TPB_ARR_R_SD, path_parameter_derivative_.data(), M * sizeof(double), 0);
-    tpb_get(e, TPB_ARR_R_SDD, second_path_parameter_derivative_.data(), M * sizeof(double), 0);
-    std::vector<tp::VectorXd>* dst[3] = {&positions_, &velocities_, &accelerations_};
-    const tpb_array what[3] = {TPB_ARR_R_POS, TPB_ARR_R_VEL, TPB_ARR_R_ACC};
-    for (int k = 0; k < 3; ++k) {
-      tpb_get(e, what[k], buf.data(), buf.size() * sizeof(double), 0);
-      dst[k]->resize(M);
-      for (size_t i = 0; i < M; ++i) (*dst[k])[i] = tp::VectorXd(&buf[i * D], D);
-    }
+    if (auto st = DownloadTrajectory(e, total); !st.ok()) return st;
 
     initial_plan_ = true;
     if (!time_.empty()) {
       end_time_ = TimeFromSec(time_.back());
       ClampToTimeStepMultiple(&end_time_);
-      final_decel_start_ = TimeFromSec(time_at_path_samples_[last_extremal]);
+      final_decel_start_ = TimeFromSec(time_at_path_samples_[last_extremal_]);
       ClampToTimeStepMultiple(&final_decel_start_);
     } else {
       end_time_ = start_time_;
@@ -234,7 +347,10 @@ class PathTimingTrajectory : public TrajectoryPlanner {
     return tp::OkStatus();
   }
 
+ public:
   size_t NumTimeSamples() const { return time_.size(); }
+  // Extension: planning windows computed by the last Plan() (device planner).
+  int LastPlanWindows() const { return last_plan_windows_; }
   tp::Time GetFinalDecelStart() const { return final_decel_start_; }
   tp::Time GetNextPlanStartTime(tp::Time target_time) {
     return std::min(end_time_, std::max(target_time, start_time_),
@@ -275,6 +391,7 @@ class PathTimingTrajectory : public TrajectoryPlanner {
     planned_to_end_ = true;
     final_decel_start_ = TimeFromSec(0.0);
     time_at_path_samples_.clear();
+    device_planner_ = nullptr;
   }
 
  private:
@@ -388,6 +505,10 @@ class PathTimingTrajectory : public TrajectoryPlanner {
          path_start_acceleration_ = 0;
   bool initial_plan_ = false, planned_to_end_ = false;
   std::vector<double> time_at_path_samples_;
+  size_t path_sample_capacity_ = 0;
+  tpb_engine* device_planner_ = nullptr;  // the engine that holds this planner's state
+  int last_plan_windows_ = 0;
+  int last_extremal_ = 0;  // of the window held by the engine (PlanOneWindow)
 };
 
 }  // namespace trajectory_planning

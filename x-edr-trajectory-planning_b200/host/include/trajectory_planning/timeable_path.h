@@ -90,6 +90,13 @@ class TimeablePath {
   // state once SamplePath + ConstraintSetup have run; PathTimingTrajectory times
   // the path there.  nullptr = not a device-backed path.
   virtual tpb_engine* DeviceEngine() { return nullptr; }
+  // Extensions for PathTimingTrajectory's device planner (tpb_planner_plan), which
+  // samples and times the planning windows of the path without host round trips:
+  // whether the path can be planned that way, upload of what the device needs before
+  // a Plan(), and the state SamplePath would have left behind after one.
+  virtual bool SupportsDevicePlanner() const { return false; }
+  virtual tp::Status BeforeDevicePlan() { return tp::OkStatus(); }
+  virtual tp::Status AfterDevicePlan(bool /*window_was_sampled*/) { return tp::OkStatus(); }
 };
 
 inline constexpr const char* ToString(const TimeablePath::State state) {

@@ -150,6 +150,35 @@ class TimeableJointSplinePath : public TimeablePath {
     return tp::OkStatus();
   }
 
+  // Device planner hooks (timeable_path.h): the limits go to the device before a
+  // Plan(); afterwards the last planning window's samples are mirrored on the host
+  // and the path counts as sampled.
+  bool SupportsDevicePlanner() const override { return true; }
+  tp::Status BeforeDevicePlan() override {
+    if (!e_ || waypoints_.empty()) return tp::FailedPreconditionError("No path set");
+    const int32_t rc =
+        tpb_set_joint_limits(e_, max_joint_velocity_.data(), max_joint_acceleration_.data(), 0, 0);
+    return rc == TPB_OK ? tp::OkStatus() : tp::FromCode(rc, tpb_last_error(e_));
+  }
+  tp::Status AfterDevicePlan(bool window_was_sampled) override {
+    if (!window_was_sampled) return tp::OkStatus();
+    const size_t N = options_.num_path_samples(), D = options_.num_dofs();
+    std::vector<double> buf(N * D);
+    tp::VectorXd* dst[3] = {path_position_.data(), first_path_derivative_.data(), second_path_derivative_.data()};
+    const tpb_array what[3] = {TPB_ARR_Q, TPB_ARR_DQ, TPB_ARR_DDQ};
+    for (int k = 0; k < 3; ++k) {
+      const int32_t rc = tpb_get(e_, what[k], buf.data(), buf.size() * sizeof(double), 0);
+      if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+      for (size_t i = 0; i < N; ++i) dst[k][i] = tp::VectorXd(&buf[i * D], D);
+    }
+    std::vector<double> s(N);
+    tpb_get(e_, TPB_ARR_S, s.data(), N * sizeof(double), 0);
+    parameter_start_ = s[0];
+    parameter_end_ = options_.num_path_samples() * options_.delta_parameter();
+    path_state_ = State::kPathWasSampled;
+    return ConstraintSetup();  // host copy of the rows, as after ComputeTimingProfile
+  }
+
   // ConstraintSetup (.cc:320-343).  The device never materialises these rows;
   // the host copy exists only for GetConstraints().
   tp::Status ConstraintSetup() override {
