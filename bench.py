@@ -386,6 +386,10 @@ def run_ours(args):
     cartesian = run_cartesian_leg(pkg, torch, dev, stream, local_rank, max_over_ranks, barrier,
                                   world, rank, args)
 
+    # ---- moving-horizon re-planning ----
+    planner = run_planner_leg(pkg, torch, dev, stream, local_rank, d_wp, d_vmax, d_amax, B, D, W,
+                              max_over_ranks, barrier, world, args)
+
     # ---- final gather of the per-path durations (outside any timed region) ----
     if world > 1:
         g = [torch.empty(B, dtype=torch.float64, device=dev) for _ in range(world)]
@@ -431,12 +435,77 @@ def run_ours(args):
             "stage_ms": stage_ms, "paths_ok": n_ok, "resampled_rows_per_gpu": total_rows,
             "mean_duration_s": float(np.nanmean(all_dur)),
             "e2e_matches_device_run": same, "spline_eval": spline,
-            "cartesian": cartesian, "stop": stop,
+            "cartesian": cartesian, "stop": stop, "planner": planner,
         }
         print(json.dumps(line))
     eng.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_planner_leg(pkg, torch, dev, stream, local_rank, d_wp, d_vmax, d_amax, B, D, W,
+                    max_over_ranks, barrier, world, args):
+    """Moving-horizon re-planning of the cfg2 batch: every path is planned
+    in windows of 512 path samples that cover a quarter of the longest path, Plan() is called
+    again every 200 ms with a 750 ms horizon (the reference test's cadence,
+    path_timing_trajectory_test.cc:64-65) until every path is at its end.  All planner state
+    stays in HBM; per call the host reads one 4-byte flag per planning window.  One untimed
+    pass collects the call / window counts, the timed pass repeats it (CUDA events on the
+    launching stream around the whole loop)."""
+    if args.no_planner:
+        return None
+    N = 512
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * 4096, device=local_rank)
+    eng.set_stream(stream.cuda_stream)
+    eng.set_joint_waypoints(d_wp)
+    eng.set_joint_limits(d_vmax, d_amax)
+    knot_end = float(eng.get(pkg.ARR.KNOT_END).max())
+    delta = knot_end / (N - 1) / 4.0
+    eng.set_sampling(np.full(B, delta))
+    horizon, replan, dt = 750_000_000, 200_000_000, TIME_STEP
+
+    def one_pass(collect):
+        eng.planner_reset(8 * N, dt)
+        start, calls, windows, erased, rows = 0, 0, 0, 0, 0
+        while calls < 400:
+            total = eng.planner_plan(start, horizon, want_total=collect)
+            calls += 1
+            if collect:
+                st = eng.get(pkg.ARR.PLAN_STATUS)
+                windows += int(eng.get(pkg.ARR.PLAN_LOOPS).sum())
+                erased += int((eng.get(pkg.ARR.PLAN_ERASED) == 1).sum())
+                rows = max(rows, total)
+                done = (eng.get(pkg.ARR.PLAN_TARGET_REACHED) == 1) | (st != 0)
+                if done.all():
+                    break
+            elif calls == one_pass.calls:
+                break
+            start += replan
+        return calls, windows, erased, rows
+
+    calls, windows, erased, rows = one_pass(True)
+    one_pass.calls = calls
+    one_pass(False)
+    torch.cuda.synchronize()
+    barrier()
+    l0 = eng.kernel_launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    one_pass(False)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    launches = eng.kernel_launches - l0
+    reached = int((eng.get(pkg.ARR.PLAN_TARGET_REACHED) == 1).sum())
+    eng.close()
+    return {"path_plans_per_s": world * B * calls / (ms / 1e3), "ms_total": ms,
+            "ms_per_plan_call": ms / calls, "plan_calls": calls, "paths_per_gpu": B,
+            "windows_planned": windows, "paths_only_erased": erased,
+            "window_paths_per_s": world * windows / (ms / 1e3), "paths_at_end": reached,
+            "max_rows_per_gpu": int(rows), "gpu_launches": int(launches),
+            "config": {"window_samples": N, "windows_per_longest_path": 4, "horizon_ms": 750,
+                       "replan_ms": 200, "time_step_s": dt}}
 
 
 class _DevPtr:
@@ -610,6 +679,7 @@ def main():
     ap.add_argument("--no-spline", action="store_true")
     ap.add_argument("--no-cartesian", action="store_true")
     ap.add_argument("--no-stop", action="store_true")
+    ap.add_argument("--no-planner", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
