@@ -73,14 +73,21 @@ class _PlanOut(C.Structure):
         ("r_t", "r_pos", "r_vel", "r_acc", "r_s", "r_sd", "r_sdd")]
 
 
+class _Spline(C.Structure):
+    """orc_spline (tp_oracle.h)"""
+    _fields_ = [("degree", C.c_int), ("dim", C.c_int), ("knot_capacity", C.c_int),
+                ("num_knots", C.c_int), ("num_points", C.c_int), ("knots", c_double_p),
+                ("points", c_double_p)]
+
+
 class _Planner(C.Structure):
     """orc_planner (tp_oracle.h)"""
     _fields_ = [("N", C.c_int), ("dim", C.c_int), ("W", C.c_int), ("rounding", C.c_double),
                 ("safety", C.c_double), ("delta", C.c_double), ("dt", C.c_double),
                 ("skip_method", C.c_int), ("max_planning_iterations", C.c_int),
                 ("max_initial_velocity_error", C.c_double)] + [
-        (n, c_double_p) for n in ("waypoints", "vmax", "amax", "initial_velocity", "ctrl",
-                                  "knots")] + [("P_cap", C.c_int)] + [
+        (n, c_double_p) for n in ("waypoints", "vmax", "amax", "initial_velocity")] + [
+        ("spline", _Spline), ("P_cap", C.c_int)] + [
         (n, c_double_p) for n in ("w_time", "w_s", "w_sd", "w_sdd", "w_q", "w_vel", "w_acc")] + [
         ("M_cap", C.c_int)] + [
         (n, c_double_p) for n in ("r_t", "r_pos", "r_vel", "r_acc", "r_s", "r_sd", "r_sdd")] + [
@@ -196,6 +203,22 @@ def lib():
         L.orc_planner_init.argtypes = [C.POINTER(_Planner)]
         L.orc_planner_plan.restype = C.c_int
         L.orc_planner_plan.argtypes = [C.POINTER(_Planner), C.c_int64, C.c_int64]
+        L.orc_planner_switch.restype = C.c_int
+        L.orc_planner_switch.argtypes = [C.POINTER(_Planner), C.c_double, c_double_p, C.c_int]
+        # online re-planning geometry (tp_oracle_switch.c)
+        L.orc_spline_insert_knot.restype = C.c_int
+        L.orc_spline_insert_knot.argtypes = [C.POINTER(_Spline), C.c_double, C.c_int]
+        L.orc_spline_truncate.restype = C.c_int
+        L.orc_spline_truncate.argtypes = [C.POINTER(_Spline), C.c_double]
+        L.orc_spline_extend.restype = C.c_int
+        L.orc_spline_extend.argtypes = [C.POINTER(_Spline), c_double_p, C.c_int]
+        L.orc_project_point_on_path.restype = C.c_int
+        L.orc_project_point_on_path.argtypes = [c_double_p, C.c_int, C.c_int, c_double_p,
+                                                C.POINTER(C.c_int), c_double_p, c_double_p,
+                                                c_double_p]
+        L.orc_joint_switch.restype = C.c_int
+        L.orc_joint_switch.argtypes = [C.POINTER(_Spline), C.c_double, c_double_p, C.c_int,
+                                       C.c_double, c_double_p, C.POINTER(C.c_int)]
         # stopping trajectories (tp_oracle_stop.c)
         L.orc_sampled_trajectory_inputs_valid.restype = C.c_int
         L.orc_sampled_trajectory_inputs_valid.argtypes = [C.c_int, c_double_p]
@@ -429,12 +452,14 @@ class Planner:
         W, D = wp.shape
         P = P_cap or 64 * N
         n = max(4, 3 * W - 2)
+        cap = max(2 * (n + 3), 100)  # timeable_path_joint_spline.cc:262-268
         self._keep = dict(
             waypoints=wp, vmax=np.ascontiguousarray(vmax, np.float64),
             amax=np.ascontiguousarray(amax, np.float64),
             initial_velocity=np.ascontiguousarray(
-                np.zeros(D) if initial_velocity is None else initial_velocity, np.float64),
-            ctrl=np.zeros((n, D)), knots=np.zeros(n + 3))
+                np.zeros(D) if initial_velocity is None else initial_velocity, np.float64).copy())
+        self._knots, self._points = np.zeros(cap), np.zeros((cap - 3, D))
+        spline = _Spline(2, D, cap, 0, 0, _dp(self._knots), _dp(self._points))
         self.w = {k: np.full(P, np.nan) for k in ("w_time", "w_s", "w_sd", "w_sdd")}
         self.w.update({k: np.zeros((P, D)) for k in ("w_q", "w_vel", "w_acc")})
         self.r = {k: np.zeros(M_cap) for k in ("r_t", "r_s", "r_sd", "r_sdd")}
@@ -443,7 +468,8 @@ class Planner:
                           skip_method=1 if skip else 0,
                           max_planning_iterations=max_planning_iterations,
                           max_initial_velocity_error=max_initial_velocity_error, P_cap=P,
-                          M_cap=M_cap, **{k: _dp(v) for k, v in self._keep.items()},
+                          M_cap=M_cap, spline=spline,
+                          **{k: _dp(v) for k, v in self._keep.items()},
                           **{k: _dp(v) for k, v in self.w.items()},
                           **{k: _dp(v) for k, v in self.r.items()})
         lib().orc_planner_init(C.byref(self.c))
@@ -451,6 +477,19 @@ class Planner:
     def plan(self, start_ns, horizon_ns):
         """Plan(start, horizon); returns the ORC_* status."""
         return lib().orc_planner_plan(C.byref(self.c), int(start_ns), int(horizon_ns))
+
+    def switch(self, keep_path_until, waypoints, initial_velocity=None):
+        """SwitchToWaypointPath (+ SetInitialVelocity); returns the absl status code."""
+        wp = np.ascontiguousarray(waypoints, np.float64)
+        if initial_velocity is not None:
+            self._keep["initial_velocity"][:] = initial_velocity
+        return lib().orc_planner_switch(C.byref(self.c), float(keep_path_until), _dp(wp),
+                                        wp.shape[0])
+
+    def spline(self):
+        """(knots, control points) of the path's spline."""
+        sp = self.c.spline
+        return self._knots[:sp.num_knots].copy(), self._points[:sp.num_points].copy()
 
     def trajectory(self):
         M = self.c.M
@@ -462,6 +501,62 @@ class Planner:
 
     def __getattr__(self, name):  # state fields: len, M, end_time, planned_to_end, ...
         return getattr(self.__dict__["c"], name)
+
+
+class Spline:
+    """A degree-2 BSplineT with the reference's capacity rules (orc_spline)."""
+
+    def __init__(self, knots, points, knot_capacity=None):
+        knots = np.asarray(knots, np.float64)
+        points = np.asarray(points, np.float64)
+        D = points.shape[1]
+        cap = knot_capacity or max(2 * len(knots), 100)
+        self._knots, self._points = np.zeros(cap), np.zeros((cap - 3, D))
+        self._knots[:len(knots)] = knots
+        self._points[:len(points)] = points
+        self.c = _Spline(2, D, cap, len(knots), len(points), _dp(self._knots), _dp(self._points))
+
+    @property
+    def knots(self):
+        return self._knots[:self.c.num_knots].copy()
+
+    @property
+    def points(self):
+        return self._points[:self.c.num_points].copy()
+
+    def insert_knot(self, knot, multiplicity=1):
+        return lib().orc_spline_insert_knot(C.byref(self.c), float(knot), int(multiplicity))
+
+    def truncate(self, u_end):
+        return lib().orc_spline_truncate(C.byref(self.c), float(u_end))
+
+    def extend(self, points):
+        pts = np.ascontiguousarray(points, np.float64)
+        return lib().orc_spline_extend(C.byref(self.c), _dp(pts), pts.shape[0])
+
+    def switch(self, keep_path_until, waypoints, rounding=0.2):
+        wp = np.ascontiguousarray(waypoints, np.float64)
+        new_ctrl = np.zeros((3 * (wp.shape[0] + 1), wp.shape[1]))
+        n = C.c_int(0)
+        st = lib().orc_joint_switch(C.byref(self.c), float(keep_path_until), _dp(wp), wp.shape[0],
+                                    float(rounding), _dp(new_ctrl), C.byref(n))
+        return st, new_ctrl[:n.value].copy()
+
+    def eval(self, u, nder=0):
+        return eval_curve_ders(self.knots, self.points, 2, nder, u)
+
+
+def project_point_on_path(waypoints, point):
+    """ProjectPointOnPath -> dict(status, waypoint_index, distance_to_path, line_parameter,
+    projected_point)."""
+    wp = np.ascontiguousarray(waypoints, np.float64)
+    pt = np.ascontiguousarray(point, np.float64)
+    W, D = wp.shape if wp.size else (0, len(pt))
+    idx, dist, t, proj = C.c_int(0), C.c_double(0), C.c_double(0), np.zeros(D)
+    st = lib().orc_project_point_on_path(_dp(wp), W, D, _dp(pt), C.byref(idx), C.byref(dist),
+                                         C.byref(t), _dp(proj))
+    return dict(status=st, waypoint_index=idx.value, distance_to_path=dist.value,
+                line_parameter=t.value, projected_point=proj)
 
 
 def resample_skip(plan, amax, start_sec, dt):

@@ -213,6 +213,28 @@ int orc_path_stop_parameter(int M, int D, const double* time, const double* path
                             double query_time, double* stop_parameter, int* stop_row,
                             double* stop_duration);
 
+/* ---- online re-planning geometry of a joint path (tp_oracle_switch.c):
+ * BSplineT knot insertion / TruncateSplineAt / ExtendWithControlPoints
+ * (splines/bspline.h:224-511), ProjectPointOnPath (path_tools.h:59-104),
+ * TimeableJointSplinePath::SwitchToWaypointPath (timeable_path_joint_spline.cc:209-250).
+ * Functions return absl::StatusCode numbers (0 = ok). */
+#define ORC_MAX_SWITCH_WAYPOINTS 64
+typedef struct {
+  int degree, dim;
+  int knot_capacity; /* knots_.size(); points_.size() = knot_capacity - degree - 1 */
+  int num_knots, num_points;
+  double* knots;  /* [knot_capacity] */
+  double* points; /* [knot_capacity - degree - 1][dim] */
+} orc_spline;
+int orc_spline_insert_knot(orc_spline* s, double knot, int multiplicity);
+int orc_spline_truncate(orc_spline* s, double u_end);
+int orc_spline_extend(orc_spline* s, const double* pts, int n);
+int orc_project_point_on_path(const double* waypoints, int W, int D, const double* point,
+                              int* waypoint_index, double* distance_to_path,
+                              double* line_parameter, double* projected_point);
+int orc_joint_switch(orc_spline* s, double keep_path_until, const double* waypoints, int W,
+                     double rounding, double* new_ctrl, int* num_new_ctrl);
+
 /* ---- PathTimingTrajectory::Plan with its state between calls
  * (path_timing_trajectory.cc:307-475, 477-684) for a joint path that is not
  * modified after the first plan; see tp_oracle_windows.c.  All storage is the
@@ -227,7 +249,8 @@ typedef struct {
   double max_initial_velocity_error;
   const double *waypoints, *vmax, *amax, *initial_velocity; /* [W][dim], 3 x [dim] */
   /* storage */
-  double *ctrl, *knots; /* [max(4,3W-2)][dim], [max(4,3W-2)+3] */
+  orc_spline spline; /* knot_capacity = max(2 * (max(4,3W-2) + 3), 100)
+                        (timeable_path_joint_spline.cc:262-268), storage the caller's */
   int P_cap;            /* capacity of the *_at_path_samples_ arrays */
   double *w_time, *w_s, *w_sd, *w_sdd; /* [P_cap] */
   double *w_q, *w_vel, *w_acc;         /* [P_cap][dim] */
@@ -238,7 +261,9 @@ typedef struct {
   double knot_end, delta_used;
   int len; /* path samples held */
   int M;   /* trajectory rows held */
-  int initial_plan, sampled, planned_to_end, target_reached;
+  int initial_plan;
+  int sampled; /* TimeablePath::State: 0 kNewPath, 1 kPathWasSampled, 2 kModifiedPath */
+  int planned_to_end, target_reached;
   int64_t start_time, end_time, final_decel_start; /* absl::Time as Unix ns */
   double path_horizon, path_start, decel_time;
   int last_extremal_index;
@@ -247,6 +272,9 @@ typedef struct {
 } orc_planner;
 int orc_planner_init(orc_planner* p);
 int orc_planner_plan(orc_planner* p, int64_t start_ns, int64_t horizon_ns);
+/* SwitchToWaypointPath on the planner's path (SetInitialVelocity = write through the
+ * initial_velocity pointer); returns an absl::StatusCode number. */
+int orc_planner_switch(orc_planner* p, double keep_path_until, const double* waypoints, int W);
 
 #ifdef __cplusplus
 }

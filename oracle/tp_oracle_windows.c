@@ -5,9 +5,9 @@
  * UpdatePathTrackingStatus, the "already planned enough" shortcut with
  * EraseTrajectoryBefore, the moving-horizon loop over ComputeTimingProfile
  * (:307-475) that splices the per-path-sample arrays window by window, and the
- * resampling of the spliced arrays, for a joint path whose waypoints do not
- * change after the first plan (TimeablePath::State kNewPath for the first
- * window, kPathWasSampled afterwards).
+ * resampling of the spliced arrays, for a joint path (TimeablePath::State
+ * kNewPath for the first window, kPathWasSampled afterwards, kModifiedPath after
+ * orc_planner_switch = SwitchToWaypointPath, tp_oracle_switch.c).
  *
  * PARITY: path_timing_trajectory.cc cannot be compiled on its own here
  * (eigenmath, genit); restated line by line from stages that are pinned
@@ -127,8 +127,13 @@ static int64_t clamp_to_time_step_multiple(const orc_planner* p, int64_t t) {
 }
 
 int orc_planner_init(orc_planner* p) {
-  p->num_points = orc_joint_fit(p->waypoints, p->W, p->dim, p->rounding, p->ctrl, p->knots);
-  p->knot_end = p->knots[p->num_points + 2];
+  p->spline.degree = 2;
+  p->spline.dim = p->dim;
+  p->num_points =
+      orc_joint_fit(p->waypoints, p->W, p->dim, p->rounding, p->spline.points, p->spline.knots);
+  p->spline.num_points = p->num_points;
+  p->spline.num_knots = p->num_points + 3;
+  p->knot_end = p->spline.knots[p->num_points + 2];
   p->delta_used = (p->delta > 0) ? p->delta : p->knot_end / (p->N - 1);
   /* ResetDerived (:214-227) */
   p->len = 0;
@@ -149,7 +154,7 @@ int orc_planner_init(orc_planner* p) {
 /* ComputeTimingProfile (:307-475).  Scratch: q [5][N][dim], tm [4][N], cons. */
 static int compute_timing_profile(orc_planner* p, int64_t start, int64_t target_duration,
                                   double* q, double* tm, double* cons) {
-  const int N = p->N, D = p->dim, nk = p->num_points + 3;
+  const int N = p->N, D = p->dim, nk = p->spline.num_knots;
   double *dq = q + (size_t)N * D, *ddq = dq + (size_t)N * D, *vel = ddq + (size_t)N * D,
          *acc = vel + (size_t)N * D;
   double *s = tm + N, *sd = s + N, *sdd = sd + N;
@@ -157,8 +162,8 @@ static int compute_timing_profile(orc_planner* p, int64_t start, int64_t target_
   if (target_duration <= 0) return ORC_FAIL_START_ARG; /* (:314-318) */
   int offset = 0;
   double path_start = 0.0, sd_start = 0.0, time_start = start_sec;
-  const int was_new = !p->sampled;
-  if (!was_new) {
+  const int old_state = p->sampled; /* 0 new, 1 sampled, 2 modified */
+  if (old_state != 0) {
     /* clamp(lower_bound(time_at, start) - begin - 1, 0, n - 1) (:334-338) */
     int lo = 0, hi = p->len;
     while (lo < hi) {
@@ -174,10 +179,11 @@ static int compute_timing_profile(orc_planner* p, int64_t start, int64_t target_
   }
   p->path_start = path_start;
   p->path_horizon = path_start + p->delta_used * (N - 1);
-  orc_joint_sample(p->knots, nk, p->ctrl, D, N, path_start, p->delta_used, q, dq, ddq);
+  orc_joint_sample(p->spline.knots, nk, p->spline.points, D, N, path_start, p->delta_used, q, dq,
+                   ddq);
   p->sampled = 1;
   orc_joint_constraints(dq, ddq, N, D, p->vmax, p->amax, p->safety, cons);
-  if (was_new) { /* (:352-385) */
+  if (old_state != 1) { /* kNewPath or kModifiedPath (:352-385) */
     double sq = 0.0, dot = 0.0;
     for (int d = 0; d < D; ++d) {
       sq += dq[d] * dq[d];
@@ -271,7 +277,7 @@ int orc_planner_plan(orc_planner* p, int64_t start, int64_t horizon) {
   } else {
     p->planned_to_end = p->path_horizon >= p->knot_end - 1e-4; /* CloseToEnd */
     if (p->planned_to_end) {
-      if (p->sampled) {
+      if (p->sampled == 1) {
         p->target_reached = 1;
       } else {
         p->path_horizon = 0.0;
@@ -280,7 +286,7 @@ int orc_planner_plan(orc_planner* p, int64_t start, int64_t horizon) {
       }
     }
   }
-  const int planned_enough = p->sampled && (p->final_decel_start >= start + horizon);
+  const int planned_enough = (p->sampled == 1) && (p->final_decel_start >= start + horizon);
   if (p->M > 0 && planned_enough) { /* (:594-599) */
     erase_trajectory_before(p, start_sec);
     p->erased = 1;
@@ -329,4 +335,14 @@ int orc_planner_plan(orc_planner* p, int64_t start, int64_t horizon) {
   }
   p->target_reached = p->planned_to_end;
   return ORC_OK;
+}
+
+int orc_planner_switch(orc_planner* p, double keep_path_until, const double* waypoints, int W) {
+  double new_ctrl[(3 * (ORC_MAX_SWITCH_WAYPOINTS + 1)) * 64];
+  int n = 0;
+  p->sampled = 2; /* kModifiedPath, also when the call fails (.cc:212) */
+  const int st = orc_joint_switch(&p->spline, keep_path_until, waypoints, W, p->rounding, new_ctrl, &n);
+  if (p->spline.num_knots > 0) p->knot_end = p->spline.knots[p->spline.num_knots - 1];
+  p->num_points = p->spline.num_points;
+  return st;
 }
