@@ -145,6 +145,8 @@ typedef enum {
                                           start time, 1: rows kept (enough was planned, only
                                           EraseTrajectoryBefore ran; or the call failed its
                                           argument checks), 2: no rows (failed while planning) */
+  TPB_ARR_SWITCH_STATUS = 80, /* int32 [B] absl::StatusCode of the last
+                                 tpb_switch_to_waypoint_path per path */
   /* diagnostics: solver scratch [B][N]; holds per-path phase cycle stamps when the
    * library is built with -DTPB_PROFILE_PHASES, otherwise unspecified */
   TPB_ARR_DEBUG = 99
@@ -308,6 +310,29 @@ int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
  * start / end times stay (no PathTimingTrajectory::Reset).  The batch size must not
  * have changed. */
 int32_t tpb_planner_new_path(tpb_engine* e, const double* initial_velocity, int32_t on_device);
+
+/* ---- online re-planning geometry ------------------------------------------ */
+/* TimeableJointSplinePath::SwitchToWaypointPath (timeable_path_joint_spline.cc:
+ * 209-250) for every path b: the spline is truncated at keep_path_until[b]
+ * (BSplineT::TruncateSplineAt, splines/bspline.h:402-427, through the knot insertion of
+ * :244-278), the switching position is projected onto the new waypoints
+ * (ProjectPointOnPath, path_tools.h:59-104), their control polygon
+ * (PolyLineToBspline3Waypoints) is appended (ExtendWithControlPoints, :429-511) and
+ * the path becomes TimeablePath::State::kModifiedPath: the planner's next
+ * tpb_planner_plan re-times it from the sample before the start time with the initial
+ * path velocity projected from initial_velocity (path_timing_trajectory.cc:329-385).
+ * waypoints is [B][max_waypoints][num_dofs] like tpb_set_joint_waypoints;
+ * num_waypoints[b] (NULL = max_waypoints each) <= 0 leaves path b as it is.
+ * initial_velocity [B][num_dofs] (NULL = unchanged) = SetInitialVelocity; it is only
+ * stored when a planner exists.  The spline keeps the reference's capacity
+ * max(2 * knots at SetWaypoints, 100) knots (:257-268); per-path status (absl codes:
+ * 0, 3, 9 capacity, 11 keep_path_until before the path) in TPB_ARR_SWITCH_STATUS.
+ * Differences to the reference are confined to rounding: its TruncateSplineAt solves
+ * the knot insertion equations with a QR decomposition, this one uses the reference's
+ * own closed form (InsertKnotAndUpdateControlPointsRef). */
+int32_t tpb_switch_to_waypoint_path(tpb_engine* e, const double* keep_path_until,
+                                    const int32_t* num_waypoints, const double* waypoints,
+                                    const double* initial_velocity, int32_t on_device);
 
 /* Whole pipeline for a batch of fresh joint paths with HOST buffers in and out:
  * set waypoints+limits, sample, optimize, resample, copy back durations,

@@ -163,7 +163,7 @@ static int compute_timing_profile(orc_planner* p, int64_t start, int64_t target_
   int offset = 0;
   double path_start = 0.0, sd_start = 0.0, time_start = start_sec;
   const int old_state = p->sampled; /* 0 new, 1 sampled, 2 modified */
-  if (old_state != 0) {
+  if (old_state != 0 && p->len > 0) { /* (the reference CHECKs !time_at_path_samples_.empty()) */
     /* clamp(lower_bound(time_at, start) - begin - 1, 0, n - 1) (:334-338) */
     int lo = 0, hi = p->len;
     while (lo < hi) {

@@ -28,6 +28,7 @@ class ARR:
     W_LEN, W_TIME, W_S, W_SD, W_SDD, W_Q, W_DQ, W_DDQ = 60, 61, 62, 63, 64, 65, 66, 67
     (PLAN_STATUS, PLAN_LOOPS, PLAN_PLANNED_TO_END, PLAN_TARGET_REACHED, PLAN_START_TIME,
      PLAN_END_TIME, PLAN_FINAL_DECEL_START, PLAN_ERASED) = 70, 71, 72, 73, 74, 75, 76, 77
+    SWITCH_STATUS = 80
     DEBUG = 99
 
 
@@ -145,6 +146,8 @@ def lib():
         L.tpb_spline_eval_host.argtypes = [C.POINTER(_SplineDesc), i32]
         L.tpb_resample_skipping.restype = i32
         L.tpb_resample_skipping.argtypes = [vp, C.c_double, C.c_double, C.POINTER(C.c_int64)]
+        L.tpb_switch_to_waypoint_path.restype = i32
+        L.tpb_switch_to_waypoint_path.argtypes = [vp, vp, vp, vp, vp, i32]
         L.tpb_planner_reset.restype = i32
         L.tpb_planner_reset.argtypes = [vp, i32, C.c_double, i32, i32, C.c_double, vp, i32]
         L.tpb_planner_new_path.restype = i32
@@ -182,6 +185,7 @@ def _f64(x):
 
 _DTYPES = {ARR.NUM_POINTS: np.int32, ARR.STATUS: np.int32, ARR.LAST_EXTREMAL: np.int32,
            ARR.B_TYPE: np.uint8, ARR.R_OFFSET: np.int64, ARR.W_LEN: np.int32,
+           ARR.SWITCH_STATUS: np.int32,
            ARR.PLAN_STATUS: np.int32, ARR.PLAN_LOOPS: np.int32,
            ARR.PLAN_PLANNED_TO_END: np.int32, ARR.PLAN_TARGET_REACHED: np.int32,
            ARR.PLAN_START_TIME: np.int64, ARR.PLAN_END_TIME: np.int64,
@@ -351,6 +355,21 @@ class Engine:
         self._ck(fn(self._h, start_sec, time_step_sec, C.byref(total) if want_total else None))
         return total.value
 
+    def switch_to_waypoint_path(self, keep_path_until, waypoints, num_waypoints=None,
+                                initial_velocity=None):
+        """tpb_switch_to_waypoint_path: SwitchToWaypointPath for every path of the batch
+        (num_waypoints[b] <= 0 leaves path b alone).  Returns the per-path status codes."""
+        keep = _f64(keep_path_until)
+        wp = _f64(waypoints)
+        assert tuple(wp.shape[1:]) == (self.Wmax, self.D), wp.shape
+        if num_waypoints is not None and not hasattr(num_waypoints, "data_ptr"):
+            num_waypoints = np.ascontiguousarray(num_waypoints, np.int32)
+        v0 = _f64(initial_velocity)
+        pk, dev = _ptr(keep)
+        self._ck(lib().tpb_switch_to_waypoint_path(self._h, pk, _ptr(num_waypoints)[0],
+                                                   _ptr(wp)[0], _ptr(v0)[0], dev))
+        return self.get(ARR.SWITCH_STATUS)
+
     def planner_reset(self, path_sample_capacity, time_step_sec, skip=False,
                       max_planning_iterations=200, max_initial_velocity_error=1e-4,
                       initial_velocity=None):
@@ -418,10 +437,10 @@ class Engine:
         B, N, D = self.B, self.N, self.D
         if what in (ARR.Q, ARR.DQ, ARR.DDQ):
             return out.reshape(B, N, D)
-        if what == ARR.CTRL:
-            return out.reshape(B, self.max_points, D)
+        if what == ARR.CTRL:  # the per-path capacity grows with the first switch
+            return out.reshape(B, -1, D)
         if what == ARR.KNOTS:
-            return out.reshape(B, self.max_points + 3)
+            return out.reshape(B, -1)
         if what == ARR.POSE_CTRL:
             return out.reshape(B, self.max_points, 7)
         if what == ARR.POSE_TARGETS:

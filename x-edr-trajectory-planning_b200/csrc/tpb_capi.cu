@@ -53,6 +53,10 @@ struct tpb_engine {
   std::vector<void*> w_big;  // the P_cap-sized arrays (reallocated when the capacity grows)
   bool planner_ready = false;
   int32_t* any_active_host = nullptr;  // pinned
+  // tpb_switch_to_waypoint_path staging: [Bmax] / [Bmax][Wmax][D]
+  double *sw_keep = nullptr, *sw_wp = nullptr;
+  int32_t *sw_num = nullptr, *sw_status = nullptr, *sw_modified = nullptr;
+  std::vector<void*> spline_big;  // ctrl / knots of the reference's knot capacity
 };
 
 namespace {
@@ -153,6 +157,11 @@ bool lookup(tpb_engine* e, tpb_array what, ArrayRef* r) {
     case TPB_ARR_R_SDD: *r = {a.r_sdd, packed_rows() * sizeof(double)}; return true;
     default: break;
   }
+  if (what == TPB_ARR_SWITCH_STATUS) {
+    if (e->sw_status == nullptr) return false;
+    *r = {e->sw_status, B * sizeof(int32_t)};
+    return true;
+  }
   if (what >= TPB_ARR_W_LEN && what <= TPB_ARR_PLAN_ERASED) {
     if (!e->planner_ready) return false;
     const auto& w = e->w;
@@ -248,6 +257,7 @@ int32_t tpb_create(const tpb_config* cfg, tpb_engine** out) {
     TPB_ALLOC(ctrl, B * d.max_points * D);
     TPB_ALLOC(knots, B * (d.max_points + 3));
     TPB_ALLOC(num_points, B);
+    TPB_ALLOC(knot_cap, B);
     TPB_ALLOC(delta, B);
     TPB_ALLOC(knot_end, B);
     TPB_ALLOC(q, B * N * D);
@@ -319,6 +329,7 @@ int32_t tpb_destroy(tpb_engine* e) {
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (void* p : e->allocs) cudaFree(p);
   for (void* p : e->w_big) cudaFree(p);
+  for (void* p : e->spline_big) cudaFree(p);
   if (e->any_active_host) cudaFreeHost(e->any_active_host);
   if (e->copy_stream) {
     cudaStreamSynchronize(e->copy_stream);
@@ -839,6 +850,67 @@ int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
   return rc;
 }
 
+// ---------------------------------------------------------------- online re-planning
+int32_t tpb_switch_to_waypoint_path(tpb_engine* e, const double* keep_path_until,
+                                    const int32_t* num_waypoints, const double* waypoints,
+                                    const double* initial_velocity, int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (e->mode != Mode::kJoint || !e->have_waypoints)
+    return fail(e, TPB_FAILED_PRECONDITION, "No path set");
+  if (e->cartesian)
+    return fail(e, TPB_UNIMPLEMENTED, "engines created with cartesian = 1 do not switch joint paths");
+  if (keep_path_until == nullptr || waypoints == nullptr)
+    return fail(e, TPB_INVALID_ARGUMENT, "keep_path_until / waypoints are null");
+  cudaSetDevice(e->device);
+  const size_t Bm = d.Bmax, D = d.D;
+  // the spline arrays grow once to the reference's knot capacity
+  const int cap_points = std::max(2 * (std::max(3 * d.Wmax - 2, 4) + 3), 100) - 3;
+  if (d.max_points < cap_points) {
+    const size_t tables = sizeof(double) * (static_cast<size_t>(cap_points) + 3 +
+                                            static_cast<size_t>(cap_points) * D + 2 * D);
+    if (tables > 48 * 1024)
+      return fail(e, TPB_UNIMPLEMENTED, "spline capacity for switching exceeds the sampling kernel's shared memory");
+    double *ctrl = nullptr, *knots = nullptr;
+    TPB_CUDA(e, cudaMalloc(reinterpret_cast<void**>(&ctrl), sizeof(double) * Bm * cap_points * D));
+    e->spline_big.push_back(ctrl);
+    TPB_CUDA(e, cudaMalloc(reinterpret_cast<void**>(&knots), sizeof(double) * Bm * (cap_points + 3)));
+    e->spline_big.push_back(knots);
+    e->launches += tpb::launch_restride_spline(d.B, d.D, d.max_points, cap_points, e->a.ctrl,
+                                               e->a.knots, ctrl, knots, e->stream);
+    e->a.ctrl = ctrl;  // the smaller arrays stay allocated until tpb_destroy
+    e->a.knots = knots;
+    d.max_points = cap_points;
+  }
+  if (e->sw_keep == nullptr) {
+    TPB_CUDA(e, dev_alloc(e, &e->sw_keep, Bm));
+    TPB_CUDA(e, dev_alloc(e, &e->sw_num, Bm));
+    TPB_CUDA(e, dev_alloc(e, &e->sw_status, Bm));
+    TPB_CUDA(e, dev_alloc(e, &e->sw_modified, Bm));
+    TPB_CUDA(e, dev_alloc(e, &e->sw_wp, Bm * d.Wmax * D));
+  }
+  TPB_CUDA(e, copy_in(e, e->sw_keep, keep_path_until, sizeof(double) * d.B, on_device));
+  TPB_CUDA(e, copy_in(e, e->sw_wp, waypoints, sizeof(double) * d.B * d.Wmax * D, on_device));
+  if (num_waypoints != nullptr)
+    TPB_CUDA(e, copy_in(e, e->sw_num, num_waypoints, sizeof(int32_t) * d.B, on_device));
+  tpb::SwitchArgs s;
+  s.keep_path_until = e->sw_keep;
+  s.num_waypoints = num_waypoints ? e->sw_num : nullptr;
+  s.waypoints = e->sw_wp;
+  s.max_waypoints = d.Wmax;
+  s.status = e->sw_status;
+  s.modified = e->sw_modified;
+  e->launches += tpb::launch_joint_switch(d, e->a, s, e->rounding, e->stream);
+  if (e->planner_ready) {
+    e->launches += tpb::launch_planner_mark_modified(d, e->w, e->sw_modified, e->stream);
+    if (initial_velocity != nullptr)
+      TPB_CUDA(e, copy_in(e, e->w.init_vel, initial_velocity, sizeof(double) * d.B * D, on_device));
+  }
+  TPB_CUDA(e, cudaGetLastError());
+  e->sampled = e->optimized = false;  // the sampled window belongs to the old spline
+  return TPB_OK;
+}
+
 // ---------------------------------------------------------------- moving-horizon planner
 int32_t tpb_planner_reset(tpb_engine* e, int32_t path_sample_capacity, double time_step_sec,
                           int32_t skip_method, int32_t max_planning_iterations,
@@ -871,6 +943,7 @@ int32_t tpb_planner_reset(tpb_engine* e, int32_t path_sample_capacity, double ti
   if (path_sample_capacity > w.P_cap) {
     TPB_CUDA(e, cudaStreamSynchronize(e->stream));
     for (void* p : e->w_big) cudaFree(p);
+  for (void* p : e->spline_big) cudaFree(p);
     e->w_big.clear();
     w.P_cap = 0;
     const size_t BP = Bm * static_cast<size_t>(path_sample_capacity);

@@ -40,6 +40,7 @@ struct DeviceArrays {
   double* ctrl = nullptr;
   double* knots = nullptr;
   int32_t* num_points = nullptr;
+  int32_t* knot_cap = nullptr;  // [B] the reference's knot capacity of the path's spline
   double* delta = nullptr;
   double* knot_end = nullptr;
   // samples
@@ -112,6 +113,7 @@ struct PlannerArrays {
   double *w_q = nullptr, *w_dq = nullptr, *w_ddq = nullptr;
   int32_t* keep = nullptr;  // [B][P_cap] sample index of trajectory row k + 1 (skip method)
   // [B]
+  // sampled: TimeablePath::State of the path, 0 kNewPath, 1 kPathWasSampled, 2 kModifiedPath
   int32_t *len = nullptr, *active = nullptr, *status = nullptr, *mode = nullptr,
           *initial_plan = nullptr, *sampled = nullptr, *planned_to_end = nullptr,
           *target_reached = nullptr, *loops = nullptr, *offset = nullptr,
@@ -189,6 +191,24 @@ int launch_plan_rows(const Dims& d, const DeviceArrays& a, const PlannerArrays& 
 int launch_plan_end(const Dims& d, const DeviceArrays& a, const PlannerArrays& w,
                     const PlannerOptions& o, cudaStream_t st);
 
+// Batched TimeableJointSplinePath::SwitchToWaypointPath (tpb_switch.cu); all pointers device.
+struct SwitchArgs {
+  const double* keep_path_until = nullptr;  // [B]
+  const int32_t* num_waypoints = nullptr;   // [B] or nullptr (max_waypoints each); <= 0: path untouched
+  const double* waypoints = nullptr;        // [B][max_waypoints][D]
+  int max_waypoints = 0;                    // <= Dims::Wmax
+  int32_t* status = nullptr;                // [B] absl::StatusCode numbers
+  int32_t* modified = nullptr;              // [B] 1: the path is TimeablePath::State::kModifiedPath now
+};
+int launch_joint_switch(const Dims& d, const DeviceArrays& a, const SwitchArgs& s, double rounding,
+                        cudaStream_t st);
+int launch_restride_spline(int B, int D, int old_points, int new_points, const double* ctrl_in,
+                           const double* knots_in, double* ctrl_out, double* knots_out,
+                           cudaStream_t st);
+// planner: paths with modified[b] != 0 become kModifiedPath
+int launch_planner_mark_modified(const Dims& d, const PlannerArrays& w, const int32_t* modified,
+                                 cudaStream_t st);
+
 // Batched RescaleTrajectoryBackwardToStop (tpb_stop.cu); all pointers device.
 struct StopArgs {
   int num_traj, D;
@@ -236,6 +256,7 @@ inline DeviceArrays shifted_joint(const DeviceArrays& a, const Dims& d, int b0) 
   adv(s.ctrl, static_cast<size_t>(d.max_points) * D);
   adv(s.knots, static_cast<size_t>(d.max_points) + 3);
   adv(s.num_points, 1);
+  adv(s.knot_cap, 1);
   adv(s.delta, 1);
   adv(s.knot_end, 1);
   adv(s.q, N * D);

@@ -58,6 +58,8 @@ __global__ void k_joint_fit(Dims dm, DeviceArrays a, double rounding, bool auto_
   for (int i = 0; i < nk; ++i) kn[i] *= weighted;
 
   a.num_points[b] = n;
+  // knot capacity the reference gives the spline (timeable_path_joint_spline.cc:257-268)
+  a.knot_cap[b] = max(2 * nk, 100);
   const double kend = kn[nk - 1];
   a.knot_end[b] = kend;
   a.delta[b] = auto_delta ? kend / (dm.N - 1) : a.delta_in[b];

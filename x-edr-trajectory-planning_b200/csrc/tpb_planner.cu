@@ -74,6 +74,11 @@ __global__ void k_planner_new_path(Dims dm, PlannerArrays w) {
   if (b < dm.B) w.sampled[b] = 0;
 }
 
+__global__ void k_planner_mark_modified(Dims dm, PlannerArrays w, const int32_t* modified) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < dm.B && modified[b] != 0) w.sampled[b] = 2;
+}
+
 // time of trajectory row i of path b (the rows themselves may lie past r_capacity)
 __device__ __forceinline__ double row_time(const PlannerArrays& w, const PlannerOptions& o, int b,
                                            int i) {
@@ -111,7 +116,7 @@ __global__ void k_plan_begin(Dims dm, DeviceArrays a, PlannerArrays w, PlannerOp
   }
   // UpdatePathTrackingStatus (:477-501)
   int target_reached = 0, planned_to_end = 0;
-  const bool sampled = w.sampled[b] != 0;
+  const bool sampled = w.sampled[b] == 1;  // neither kNewPath nor kModifiedPath
   if (!initial) {
     w.path_horizon[b] = 0.0;
   } else {
@@ -197,7 +202,7 @@ __global__ void k_window_begin(Dims dm, DeviceArrays a, PlannerArrays w, int64_t
   const double start_sec = time_to_sec(loop_start);
   int offset = 0;
   double path_start = 0.0, sd_start = 0.0, time_start = start_sec;
-  if (w.sampled[b] != 0) {
+  if (w.sampled[b] != 0 && w.len[b] > 0) {  // kPathWasSampled or kModifiedPath
     // clamp(lower_bound(time_at_path_samples_, start) - begin - 1, 0, n - 1) (:334-338)
     const size_t base = static_cast<size_t>(b) * w.P_cap;
     const int len = w.len[b];
@@ -228,7 +233,7 @@ __global__ void k_window_begin(Dims dm, DeviceArrays a, PlannerArrays w, int64_t
 __global__ void k_window_velocity(Dims dm, DeviceArrays a, PlannerArrays w, PlannerOptions o) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= dm.B || w.active[b] == 0) return;
-  if (w.sampled[b] != 0) return;
+  if (w.sampled[b] == 1) return;  // only new and modified paths
   w.sampled[b] = 1;
   const int D = dm.D;
   const double* d0 = a.dq + static_cast<size_t>(b) * dm.N * D;  // GetFirstPathDerivativeAt(0)
@@ -238,7 +243,7 @@ __global__ void k_window_velocity(Dims dm, DeviceArrays a, PlannerArrays w, Plan
     sq += d0[d] * d0[d];
     dot += v0[d] * d0[d];
   }
-  double sd_start = 0.0;
+  double sd_start = a.sd_start[b];  // 0 for a new path, the previous sample's for a modified one
   if (sq > 100 * DBL_EPSILON) sd_start = fmax(dot / sq, 0.0);
   double err = 0.0;
   for (int d = 0; d < D; ++d) err = fmax(err, fabs(d0[d] * sd_start - v0[d]));
@@ -418,6 +423,11 @@ int launch_planner_reset(const Dims& d, const PlannerArrays& w, cudaStream_t st)
 }
 int launch_planner_new_path(const Dims& d, const PlannerArrays& w, cudaStream_t st) {
   k_planner_new_path<<<blocks_for(d.B, 128), 128, 0, st>>>(d, w);
+  return 1;
+}
+int launch_planner_mark_modified(const Dims& d, const PlannerArrays& w, const int32_t* modified,
+                                 cudaStream_t st) {
+  k_planner_mark_modified<<<blocks_for(d.B, 128), 128, 0, st>>>(d, w, modified);
   return 1;
 }
 int launch_plan_begin(const Dims& d, const DeviceArrays& a, const PlannerArrays& w,
