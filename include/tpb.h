@@ -310,6 +310,10 @@ int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
  * start / end times stay (no PathTimingTrajectory::Reset).  The batch size must not
  * have changed. */
 int32_t tpb_planner_new_path(tpb_engine* e, const double* initial_velocity, int32_t on_device);
+/* TimeablePath::SetInitialVelocity for every path ([B][num_dofs], NULL = zero): used by
+ * the next window of a new or modified path (:352-385). */
+int32_t tpb_planner_set_initial_velocity(tpb_engine* e, const double* initial_velocity,
+                                         int32_t on_device);
 
 /* ---- online re-planning geometry ------------------------------------------ */
 /* TimeableJointSplinePath::SwitchToWaypointPath (timeable_path_joint_spline.cc:

@@ -10,6 +10,7 @@
 
 #include "trajectory_planning/path_timing_batch.h"
 #include "trajectory_planning/path_timing_trajectory.h"
+#include "trajectory_planning/path_tools.h"
 #include "trajectory_planning/rescale_to_stop.h"
 #include "trajectory_planning/splines/bspline.h"
 #include "trajectory_planning/time_optimal_path_timing.h"
@@ -234,6 +235,112 @@ int main() {
     PrintArray("path_parameter", planner2.GetPathParameters());
     printf("\"loops\": %d, \"windows\": %d, \"final_decel_start_ns\": %lld},\n", loops, windows,
            static_cast<long long>(planner2.GetFinalDecelStart().ns));
+  }
+  // ---- SwitchToNewJointWaypointPathWorks (path_timing_trajectory_test.cc:299-436):
+  // plan until the motion is fast, switch to new waypoints at the stop parameter with the
+  // current velocity as the initial velocity, plan to the end of the new path
+  {
+    std::vector<VectorXd> wps = {VectorXd{1, 2, 3}, VectorXd{-1, -2, -3}, VectorXd{0.5, 1.0, 1.5}};
+    VectorXd vmax = VectorXd::Constant(kNDof, 1.0), amax = VectorXd::Constant(kNDof, 2.0);
+    auto path = std::make_shared<TimeableJointSplinePath>(JointPathOptions()
+                                                              .set_num_dofs(kNDof)
+                                                              .set_num_path_samples(kNumSamples)
+                                                              .set_delta_parameter(0.001));
+    PathTimingTrajectory planner(PathTimingTrajectoryOptions()
+                                     .SetTimeStep(tp::Milliseconds(4))
+                                     .SetNumDofs(kNDof)
+                                     .SetNumPathSamples(kNumSamples));
+    EXPECT(planner.SetPath(path).ok());
+    EXPECT(path->SetWaypoints(wps).ok());
+    path->SetMaxJointVelocity(ToSpan(vmax));
+    path->SetMaxJointAcceleration(ToSpan(amax));
+    tp::Time start_time = TimeFromSec(0.0);
+    int first_calls = 0;
+    for (; first_calls < 100; ++first_calls) {
+      EXPECT(planner.Plan(start_time, tp::Milliseconds(750)).ok());
+      start_time = planner.GetNextPlanStartTime(start_time + tp::Milliseconds(200));
+      double closest = 1e9;
+      for (size_t d = 0; d < kNDof; ++d) {
+        closest = std::min(closest, std::abs(std::abs(planner.GetVelocities().front()[d]) - vmax[d]));
+      }
+      if (closest < 0.3) break;
+    }
+    EXPECT(!planner.IsTrajectoryAtEnd());
+    const std::vector<VectorXd> new_wps = {VectorXd{1.0, 2.0, 3.0}, VectorXd{0.5, 1.0, 5.5}};
+    auto stop = planner.GetPathStopParameter(start_time);
+    EXPECT(stop.ok());
+    const double stop_parameter = stop.ok() ? *stop : 0.0;
+    // the velocity at start_time, interpolated in the planned trajectory
+    VectorXd v0(kNDof);
+    {
+      const auto& t = planner.GetTime();
+      const double ts = TimeToSec(start_time);
+      size_t hi = 1;
+      while (hi + 1 < t.size() && t[hi] < ts) ++hi;
+      const double w = (ts - t[hi - 1]) / (t[hi] - t[hi - 1]);
+      for (size_t d = 0; d < kNDof; ++d) {
+        v0[d] = planner.GetVelocities()[hi - 1][d] +
+                w * (planner.GetVelocities()[hi][d] - planner.GetVelocities()[hi - 1][d]);
+      }
+    }
+    const size_t knots_before = path->GetKnots().size();
+    EXPECT(path->SwitchToWaypointPath(stop_parameter, new_wps).ok());
+    EXPECT(path->GetState() == TimeablePath::State::kModifiedPath);
+    EXPECT(path->SetInitialVelocity(ToSpan(v0)).ok());
+    EXPECT(!planner.IsTrajectoryAtEnd());
+    const std::vector<double> knots_after = path->GetKnots();
+    int second_calls = 0;
+    for (; !planner.IsTrajectoryAtEnd() && second_calls < 300; ++second_calls) {
+      const tp::Status st = planner.Plan(start_time, tp::Milliseconds(750));
+      EXPECT(st.ok());
+      if (!st.ok()) {
+        fprintf(stderr, "Plan after switch %d: %s\n", second_calls, st.message().c_str());
+        break;
+      }
+      start_time = planner.GetNextPlanStartTime(start_time + tp::Milliseconds(200));
+    }
+    EXPECT(planner.IsTrajectoryAtEnd());
+    EXPECT(path->GetState() == TimeablePath::State::kPathWasSampled);
+    if (!planner.GetPositions().empty()) {
+      for (size_t d = 0; d < kNDof; ++d) {
+        EXPECT(std::abs(planner.GetPositions().back()[d] - new_wps.back()[d]) < 1e-10);
+        EXPECT(std::abs(planner.GetVelocities().back()[d]) < 1e-10);
+      }
+    }
+    // ProjectPointOnPath / ComputeStoppingPoint (path_tools_test.cc:98-165)
+    {
+      const std::vector<VectorXd> w3 = {VectorXd{1.0, 1.0}, VectorXd{2.0, 2.0}, VectorXd{-3.0, -3.0}};
+      const VectorXd pt{2.0 + 0.4 * -5.0 + 0.1, 2.0 + 0.4 * -5.0 - 0.1};
+      auto pr = ProjectPointOnPath(w3, pt);
+      EXPECT(pr.ok() && pr->waypoint_index == 1 && std::abs(pr->line_parameter - 0.4) < 1e-14);
+      EXPECT(ProjectPointOnPath(std::vector<VectorXd>{}, pt).status().code() ==
+             tp::StatusCode::kInvalidArgument);
+      const std::vector<double> pos(3, 1.0), vel0(3, 0.0), vel{0.3, -0.2, 0.1}, acc(3, 1.0);
+      auto still = ComputeStoppingPoint(pos, vel0, acc, 0.1);
+      EXPECT(still.ok() && (*still)[0] == 1.0 && (*still)[2] == 1.0);
+      auto stopped = ComputeStoppingPoint(pos, vel, acc, 0.1);
+      EXPECT(stopped.ok());
+      if (stopped.ok()) {  // on the ray from the position along the velocity
+        const double k = ((*stopped)[0] - 1.0) / vel[0];
+        EXPECT(k > 0 && std::abs((*stopped)[1] - 1.0 - k * vel[1]) < 1e-12 &&
+               std::abs((*stopped)[2] - 1.0 - k * vel[2]) < 1e-12);
+      }
+      EXPECT(ComputeStoppingPoint(pos, std::vector<double>(2), acc, 0.0).status().code() ==
+             tp::StatusCode::kInvalidArgument);
+      EXPECT(ComputeStoppingPoint(pos, vel, std::vector<double>(3, -1.0), 0.0).status().code() ==
+             tp::StatusCode::kInvalidArgument);
+    }
+    printf("\"switching\": {\n");
+    PrintArray("initial_velocity", std::vector<double>(v0.begin(), v0.end()));
+    PrintArray("knots_after_switch", knots_after);
+    PrintArray("time", planner.GetTime());
+    PrintArray("positions", Flatten(planner.GetPositions()));
+    PrintArray("velocities", Flatten(planner.GetVelocities()));
+    PrintArray("accelerations", Flatten(planner.GetAccelerations()));
+    printf("\"stop_parameter\": %.17g, \"first_calls\": %d, \"second_calls\": %d, "
+           "\"knots_before\": %zu, \"switch_start_ns\": %lld},\n",
+           stop_parameter, first_calls, second_calls, knots_before,
+           0LL);
   }
   // ---- Circle (time_optimal_path_timing_test.cc:496-559)
   {

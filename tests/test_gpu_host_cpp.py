@@ -189,3 +189,44 @@ def test_moving_horizon_replanning_matches_oracle(result, po, key, skip):
     assert np.array_equal(np.array(r["accelerations"]).reshape(-1, 3), tr["r_acc"])
     assert np.array_equal(np.array(r["path_parameter"]), tr["r_s"])
     assert r["final_decel_start_ns"] == pl.final_decel_start
+
+
+def test_switch_to_waypoint_path_matches_oracle(result, po):
+    """host SwitchToWaypointPath + re-planning of the modified path
+    (SwitchToNewJointWaypointPathWorks, path_timing_trajectory_test.cc:299-436) against the
+    oracle's planner driven the same way."""
+    r = result["switching"]
+    wp = np.array([[1.0, 2, 3], [-1, -2, -3], [0.5, 1.0, 1.5]])
+    vmax, amax = np.ones(3), np.full(3, 2.0)
+    pl = po.Planner(wp, vmax, amax, 1000, 0.001, 0.004, max_initial_velocity_error=1e-2)
+    start, first_calls = 0, 0
+    for first_calls in range(100):
+        assert pl.plan(start, 750_000_000) == po.ORC_OK
+        tr = pl.trajectory()
+        start = min(pl.end_time, max(start + 200_000_000, pl.start_time))
+        if np.min(np.abs(np.abs(tr["r_vel"][0]) - vmax)) < 0.3:
+            break
+    assert r["first_calls"] == first_calls
+    sp = po.path_stop_parameter(tr["r_t"], tr["r_s"], tr["r_vel"], tr["r_acc"], amax, start / 1e9)
+    assert r["stop_parameter"] == sp["parameter"]
+    v0 = np.array(r["initial_velocity"])
+    ts = start / 1e9
+    hi = 1
+    while hi + 1 < len(tr["r_t"]) and tr["r_t"][hi] < ts:
+        hi += 1
+    w = (ts - tr["r_t"][hi - 1]) / (tr["r_t"][hi] - tr["r_t"][hi - 1])
+    assert np.array_equal(v0, tr["r_vel"][hi - 1] + w * (tr["r_vel"][hi] - tr["r_vel"][hi - 1]))
+    assert pl.switch(sp["parameter"], np.array([[1.0, 2.0, 3.0], [0.5, 1.0, 5.5]]),
+                     initial_velocity=v0) == 0
+    assert np.array_equal(np.array(r["knots_after_switch"]), pl.spline()[0])
+    second_calls = 0
+    while not pl.target_reached:
+        assert pl.plan(start, 750_000_000) == po.ORC_OK
+        start = min(pl.end_time, max(start + 200_000_000, pl.start_time))
+        second_calls += 1
+    assert r["second_calls"] == second_calls
+    tr = pl.trajectory()
+    assert np.array_equal(np.array(r["time"]), tr["r_t"])
+    assert np.array_equal(np.array(r["positions"]).reshape(-1, 3), tr["r_pos"])
+    assert np.array_equal(np.array(r["velocities"]).reshape(-1, 3), tr["r_vel"])
+    assert np.array_equal(np.array(r["accelerations"]).reshape(-1, 3), tr["r_acc"])

@@ -152,6 +152,8 @@ def lib():
         L.tpb_planner_reset.argtypes = [vp, i32, C.c_double, i32, i32, C.c_double, vp, i32]
         L.tpb_planner_new_path.restype = i32
         L.tpb_planner_new_path.argtypes = [vp, vp, i32]
+        L.tpb_planner_set_initial_velocity.restype = i32
+        L.tpb_planner_set_initial_velocity.argtypes = [vp, vp, i32]
         L.tpb_planner_plan.restype = i32
         L.tpb_planner_plan.argtypes = [vp, C.c_int64, C.c_int64, C.POINTER(C.c_int64)]
         L.tpb_path_stop_parameter.restype = i32
@@ -386,6 +388,11 @@ class Engine:
         v0 = _f64(initial_velocity)
         p, dev = _ptr(v0)
         self._ck(lib().tpb_planner_new_path(self._h, p, dev))
+
+    def planner_set_initial_velocity(self, initial_velocity=None):
+        v0 = _f64(initial_velocity)
+        p, dev = _ptr(v0)
+        self._ck(lib().tpb_planner_set_initial_velocity(self._h, p, dev))
 
     def planner_plan(self, start_ns, horizon_ns, want_total=True):
         """tpb_planner_plan: PathTimingTrajectory::Plan(start, horizon) for every path

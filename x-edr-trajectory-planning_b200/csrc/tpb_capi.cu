@@ -997,6 +997,17 @@ int32_t tpb_planner_new_path(tpb_engine* e, const double* initial_velocity, int3
   return TPB_OK;
 }
 
+int32_t tpb_planner_set_initial_velocity(tpb_engine* e, const double* initial_velocity,
+                                         int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  if (!e->planner_ready)
+    return fail(e, TPB_FAILED_PRECONDITION, "tpb_planner_reset was not called for these paths");
+  cudaSetDevice(e->device);
+  TPB_CUDA(e, fill_or_copy(e, e->w.init_vel, initial_velocity,
+                           static_cast<size_t>(e->dims.B) * e->dims.D, on_device));
+  return TPB_OK;
+}
+
 int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
                          int64_t* total_samples) {
   if (e == nullptr) return TPB_INVALID_ARGUMENT;

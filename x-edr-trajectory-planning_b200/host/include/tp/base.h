@@ -62,6 +62,7 @@ class StatusOr {
   bool ok() const { return status_.ok(); }
   const Status& status() const { return status_; }
   const T& operator*() const { return value_; }
+  const T* operator->() const { return &value_; }
   const T& value() const { return value_; }
 
  private:

@@ -101,9 +101,6 @@ class PathTimingTrajectory : public TrajectoryPlanner {
   tp::Status PlanOnDevice(tp::Time start, tp::Duration time_horizon) {
     const auto state = path_->GetState();
     if (state == TimeablePath::State::kNoPath) return tp::FailedPreconditionError("No path set");
-    if (state == TimeablePath::State::kModifiedPath) {
-      return tp::UnimplementedError("re-timing of a modified path (SwitchToWaypointPath)");
-    }
     if (auto st = path_->BeforeDevicePlan(); !st.ok()) return st;
     tpb_engine* e = path_->DeviceEngine();
     if (e == nullptr) return tp::InternalError("path has no device engine");
@@ -122,6 +119,14 @@ class PathTimingTrajectory : public TrajectoryPlanner {
       }
       if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
       device_planner_ = e;
+    } else if (state == TimeablePath::State::kModifiedPath) {
+      // SwitchToWaypointPath marked the path on the device; the initial velocity set
+      // since (SetInitialVelocity) goes to the planner now (.cc:352-385)
+      if (device_planner_ != e) {
+        return tp::FailedPreconditionError("the path was modified, but never planned by this planner");
+      }
+      rc = tpb_planner_set_initial_velocity(e, path_->GetInitialVelocity().data(), 0);
+      if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
     } else if (device_planner_ != e) {
       return tp::FailedPreconditionError("the path was sampled, but not by this planner");
     }

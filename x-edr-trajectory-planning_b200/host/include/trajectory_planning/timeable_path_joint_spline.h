@@ -80,20 +80,72 @@ class TimeableJointSplinePath : public TimeablePath {
     const double delta = options_.delta_parameter();
     rc = tpb_set_sampling(e_, &delta, 0);
     if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
-    const int n = (W == 1) ? 4 : 3 * W - 2;
-    const int max_points = std::max(3 * wcap_ - 2, 4);
-    std::vector<double> kn(max_points + 3), ct(static_cast<size_t>(max_points) * D);
-    tpb_get(e_, TPB_ARR_KNOTS, kn.data(), kn.size() * sizeof(double), 0);
-    tpb_get(e_, TPB_ARR_CTRL, ct.data(), ct.size() * sizeof(double), 0);
+    constraints_valid_ = false;
+    return DownloadSpline();
+  }
+
+  // knots_ and the spline's control points from the device (extension: after a switch
+  // GetControlPoints() is the whole spline's, where the reference keeps the appended
+  // control polygon only)
+  tp::Status DownloadSpline() {
+    const int D = static_cast<int>(options_.num_dofs());
+    int32_t n = 0;
+    size_t knot_bytes = 0, ctrl_bytes = 0;
+    void* unused = nullptr;
+    int32_t rc = tpb_get(e_, TPB_ARR_NUM_POINTS, &n, sizeof(n), 0);
+    if (rc == TPB_OK) rc = tpb_devptr(e_, TPB_ARR_KNOTS, &unused, &knot_bytes);
+    if (rc == TPB_OK) rc = tpb_devptr(e_, TPB_ARR_CTRL, &unused, &ctrl_bytes);
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+    std::vector<double> kn(knot_bytes / sizeof(double)), ct(ctrl_bytes / sizeof(double));
+    tpb_get(e_, TPB_ARR_KNOTS, kn.data(), knot_bytes, 0);
+    tpb_get(e_, TPB_ARR_CTRL, ct.data(), ctrl_bytes, 0);
+    if (n <= 0) {
+      knots_.clear();
+      control_points_.clear();
+      return tp::OkStatus();
+    }
     knots_.assign(kn.begin(), kn.begin() + n + 3);
     control_points_.assign(n, tp::VectorXd(D));
     for (int i = 0; i < n; ++i) control_points_[i] = tp::VectorXd(&ct[static_cast<size_t>(i) * D], D);
-    constraints_valid_ = false;
     return tp::OkStatus();
   }
 
-  tp::Status SwitchToWaypointPath(double, tp::Span<const tp::VectorXd>) {
-    return tp::UnimplementedError("SwitchToWaypointPath: online replanning is outside the hot path");
+  // SwitchToWaypointPath (.cc:209-250) on the device (tpb_switch_to_waypoint_path):
+  // truncate at keep_path_until, project the switching position onto the new waypoints,
+  // append their control polygon.  The path is kModifiedPath afterwards (also when the
+  // switch fails, as in the reference).
+  tp::Status SwitchToWaypointPath(const double keep_path_until, tp::Span<const tp::VectorXd> waypoints) {
+    path_state_ = State::kModifiedPath;
+    if (!e_) return tp::FailedPreconditionError("Spline is empty or invalid.");
+    for (const auto& wp : waypoints) {
+      if (wp.size() != options_.num_dofs()) {
+        return tp::InvalidArgumentError("Invalid number of joints: waypoint.size: " + std::to_string(wp.size()));
+      }
+    }
+    if (waypoints.empty()) return tp::InvalidArgumentError("No waypoints.");
+    const int W = static_cast<int>(waypoints.size()), D = static_cast<int>(options_.num_dofs());
+    if (W > wcap_) {
+      return {tp::StatusCode::kResourceExhausted,
+              "more waypoints than the engine was created for (" + std::to_string(wcap_) + ")"};
+    }
+    std::vector<double> flat(static_cast<size_t>(wcap_) * D, 0.0);
+    size_t w = 0;
+    for (const auto& wp : waypoints) {
+      std::copy(wp.begin(), wp.end(), flat.begin() + w * D);
+      ++w;
+    }
+    const int32_t nw = W;
+    // SetInitialVelocity may follow (the reference's order); PathTimingTrajectory hands
+    // the path's initial velocity to the planner before the next Plan()
+    int32_t rc = tpb_switch_to_waypoint_path(e_, &keep_path_until, &nw, flat.data(), nullptr, 0);
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+    int32_t status = 0;
+    rc = tpb_get(e_, TPB_ARR_SWITCH_STATUS, &status, sizeof(status), 0);
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+    if (auto st = DownloadSpline(); !st.ok()) return st;
+    constraints_valid_ = false;
+    if (status != 0) return tp::FromCode(status, "SwitchToWaypointPath failed (truncate / project / extend)");
+    return tp::OkStatus();
   }
 
   tp::Status SetMaxJointVelocity(tp::Span<const double> max_velocity) override {
