@@ -330,6 +330,43 @@ int main() {
       EXPECT(ComputeStoppingPoint(pos, vel, std::vector<double>(3, -1.0), 0.0).status().code() ==
              tp::StatusCode::kInvalidArgument);
     }
+    // BSplineT knot insertion / TruncateSplineAt / ExtendWithControlPoints on the host
+    // copy (splines/bspline.h:224-511): same knots and control points as the device's
+    // SwitchToWaypointPath building blocks, curve unchanged by insertion
+    std::vector<double> bs_knots, bs_ctrl, bs_before, bs_after;
+    {
+      auto fresh = std::make_shared<TimeableJointSplinePath>(
+          JointPathOptions().set_num_dofs(kNDof).set_num_path_samples(kNumSamples));
+      EXPECT(fresh->SetWaypoints(wps).ok());
+      BSplineXd sp;
+      EXPECT(sp.Init(2, 100, kNDof).ok());
+      EXPECT(sp.SetKnotVector(fresh->GetKnots()).ok());
+      EXPECT(sp.SetControlPoints(fresh->GetControlPoints()).ok());
+      const double kend = fresh->GetKnots().back();
+      std::vector<double> us;
+      for (int i = 0; i <= 40; ++i) us.push_back(0.59 * kend * i / 40.0);
+      bs_before.resize(us.size() * kNDof);
+      bs_after.resize(us.size() * kNDof);
+      EXPECT(sp.EvalCurveBatch(us, bs_before.data(), nullptr).ok());
+      EXPECT(sp.InsertKnotAndUpdateControlPointsRef(0.0).code() == tp::StatusCode::kInvalidArgument);
+      EXPECT(sp.InsertKnotAndUpdateControlPointsRef(0.3 * kend, 2).ok());
+      EXPECT(sp.TruncateSplineAt(0.6 * kend).ok());
+      EXPECT(sp.EvalCurveBatch(us, bs_after.data(), nullptr).ok());
+      const std::vector<VectorXd> extra = {VectorXd{0.1, 0.2, 0.3}, VectorXd{0.4, 0.1, 0.0},
+                                           VectorXd{0.7, 0.0, -0.2}, VectorXd{1.0, 0.0, -0.3}};
+      EXPECT(sp.ExtendWithControlPoints(std::vector<VectorXd>{extra[0]}).code() ==
+             tp::StatusCode::kUnimplemented);
+      EXPECT(sp.ExtendWithControlPoints(extra).ok());
+      const auto kv = sp.GetKnotVector();
+      bs_knots.assign(kv.begin(), kv.end());
+      bs_ctrl = Flatten(sp.GetControlPoints());
+    }
+    printf("\"bspline_edit\": {\n");
+    PrintArray("knots", bs_knots);
+    PrintArray("control_points", bs_ctrl);
+    PrintArray("before", bs_before);
+    PrintArray("after", bs_after, false);
+    printf("},\n");
     printf("\"switching\": {\n");
     PrintArray("initial_velocity", std::vector<double>(v0.begin(), v0.end()));
     PrintArray("knots_after_switch", knots_after);

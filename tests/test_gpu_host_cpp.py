@@ -230,3 +230,21 @@ def test_switch_to_waypoint_path_matches_oracle(result, po):
     assert np.array_equal(np.array(r["positions"]).reshape(-1, 3), tr["r_pos"])
     assert np.array_equal(np.array(r["velocities"]).reshape(-1, 3), tr["r_vel"])
     assert np.array_equal(np.array(r["accelerations"]).reshape(-1, 3), tr["r_acc"])
+
+
+def test_bspline_knot_insertion_truncate_extend_match_oracle(result, po):
+    """host BSplineXd::InsertKnotAndUpdateControlPointsRef / TruncateSplineAt /
+    ExtendWithControlPoints (splines/bspline.h:224-511) against the oracle's restatement,
+    and the curve before the truncation point is what it was."""
+    r = result["bspline_edit"]
+    wp = np.array([[1.0, 2, 3], [-1, -2, -3], [0.5, 1.0, 1.5]])
+    ctrl, knots = po.joint_fit(wp, 0.2)
+    sp = po.Spline(knots, ctrl, knot_capacity=100)
+    kend = knots[-1]
+    assert sp.insert_knot(0.3 * kend, 2) == 0
+    assert sp.truncate(0.6 * kend) == 0
+    extra = np.array([[0.1, 0.2, 0.3], [0.4, 0.1, 0.0], [0.7, 0.0, -0.2], [1.0, 0.0, -0.3]])
+    assert sp.extend(extra) == 0
+    assert np.array_equal(np.array(r["knots"]), sp.knots)
+    assert np.array_equal(np.array(r["control_points"]).reshape(-1, 3), sp.points)
+    np.testing.assert_allclose(np.array(r["after"]), np.array(r["before"]), atol=1e-12)

@@ -3,11 +3,13 @@
 // the reference's checks and status codes on the host, curve evaluation on the
 // GPU (tpb_spline_eval_host).  EvalCurveBatch / EvalCurveAndDerivativesBatch are
 // the calls the GPU is for; the scalar Eval* methods are a batch of one.
-// Knot insertion / truncation / extension are replanning helpers outside the hot
-// path.
+// Knot insertion / truncation / extension (replanning helpers) run on
+// the host copy for a single spline; TimeableJointSplinePath::SwitchToWaypointPath uses
+// their batched device form (tpb_switch_to_waypoint_path).
 #ifndef TRAJECTORY_PLANNING_SPLINES_BSPLINE_H_
 #define TRAJECTORY_PLANNING_SPLINES_BSPLINE_H_
 
+#include <algorithm>
 #include <cmath>
 #include <limits>
 #include <string>
@@ -128,6 +130,131 @@ class BSplineXd {
     std::vector<Point> out(num_points_);
     for (size_t i = 0; i < num_points_; ++i) out[i] = Point(&ctrl_[i * points_dim_], points_dim_);
     return out;
+  }
+
+  // ---- replanning helpers on the host copy of the spline (a handful of control
+  // points; the batched device form is tpb_switch_to_waypoint_path).
+  // InsertKnotAndUpdateControlPointsRef (bspline.h:234-278, NURBS Alg. 5.1) with
+  // CanInsertKnot (bspline_base.cc:166-195).  InsertKnotAndUpdateControlPoints is the
+  // same curve; the reference solves its equations by QR (bspline.h:281-399).
+  tp::Status InsertKnotAndUpdateControlPointsRef(double knot, int multiplicity = 1) {
+    if (multiplicity > static_cast<int>(degree_) + 1) {
+      return tp::InvalidArgumentError("Knot multiplicity > degree + 1 not supported.");
+    }
+    if (num_knots_ + multiplicity > max_num_knots_) {
+      return tp::FailedPreconditionError("Knot capacity too small, required: " +
+                                         std::to_string(num_knots_ + multiplicity));
+    }
+    if (num_knots_ < 2) return tp::FailedPreconditionError("Set initial knot vector first.");
+    if (knot <= knots_[0] || knot >= knots_[num_knots_ - 1]) {
+      return tp::InvalidArgumentError("knot not in range of current knots, knot=" + std::to_string(knot));
+    }
+    const size_t p = degree_, D = points_dim_;
+    ctrl_.resize(static_cast<size_t>(MaxNumPoints()) * D, 0.0);
+    std::vector<double> scratch(p * D);
+    for (int m = 0; m < multiplicity; ++m) {
+      const size_t span = KnotSpan(knot);
+      std::copy_backward(ctrl_.begin() + span * D, ctrl_.begin() + num_points_ * D,
+                         ctrl_.begin() + (num_points_ + 1) * D);
+      for (size_t i = 0; i < p; ++i) {
+        const size_t k = span + i - p + 1;
+        const double alpha = (knot - knots_[k]) / (knots_[k + p] - knots_[k]);
+        for (size_t d = 0; d < D; ++d) {
+          scratch[i * D + d] = alpha * ctrl_[k * D + d] + (1.0 - alpha) * ctrl_[(k - 1) * D + d];
+        }
+      }
+      std::copy(scratch.begin(), scratch.end(), ctrl_.begin() + (span - p + 1) * D);
+      std::copy_backward(knots_.begin() + span + 1, knots_.begin() + num_knots_,
+                         knots_.begin() + num_knots_ + 1);
+      knots_[span + 1] = knot;
+      num_knots_ += 1;
+      num_points_ += 1;
+    }
+    return tp::OkStatus();
+  }
+  tp::Status InsertKnotAndUpdateControlPoints(double knot, int multiplicity = 1) {
+    return InsertKnotAndUpdateControlPointsRef(knot, multiplicity);
+  }
+  // TruncateSplineAt (bspline.h:402-427)
+  tp::Status TruncateSplineAt(double u_end) {
+    if (u_end >= umax_) return tp::OkStatus();
+    if (u_end <= umin_) {
+      umin_ = std::numeric_limits<double>::infinity();
+      umax_ = -std::numeric_limits<double>::infinity();
+      num_knots_ = num_points_ = 0;
+      return tp::OkStatus();
+    }
+    if (auto s = InsertKnotAndUpdateControlPointsRef(u_end, static_cast<int>(degree_) + 1); !s.ok()) return s;
+    num_knots_ = KnotSpan(u_end) + 1;
+    num_points_ = static_cast<size_t>(NumPoints(num_knots_, degree_));
+    umax_ = u_end;
+    return tp::OkStatus();
+  }
+  // ExtendWithControlPoints (bspline.h:429-511), degree 2 only
+  tp::Status ExtendWithControlPoints(tp::Span<const Point> points) {
+    if (degree_ != 2) return tp::UnimplementedError("Only implemented for 2nd order splines.");
+    const size_t p = degree_, D = points_dim_, n = points.size();
+    const size_t new_num_points = num_points_ + n;
+    const size_t new_num_knots = num_knots_ + NumKnots(n + 1, p) - 2 * p;
+    if (num_knots_ < MinNumKnots(p)) return tp::FailedPreconditionError("Spline is empty or invalid.");
+    if (new_num_points > static_cast<size_t>(MaxNumPoints())) {
+      return tp::FailedPreconditionError("Point capacity too small to append all points.");
+    }
+    if (new_num_knots > max_num_knots_) {
+      return tp::FailedPreconditionError("Knot capacity too small to append all points.");
+    }
+    if (n < 2) return tp::UnimplementedError("Only implemented for >= 2 points.");
+    const double u_join = knots_[num_knots_ - 1];
+    const double old_range = knots_[num_knots_ - 1] - knots_[0];
+    const double new_range = (old_range * static_cast<int>(new_num_knots - 2 * p - 1)) /
+                             static_cast<int>(num_knots_ - 2 * p - 1);
+    const size_t start = num_knots_ - p - 1, size = (new_num_knots - p) - start;
+    const double step = (size == 1) ? 0.0 : (new_range - old_range) / static_cast<double>(size - 1);
+    for (size_t i = 0; i < size; ++i) {  // setLinSpaced(old_range, new_range)
+      knots_[start + i] = (i == (size == 1 ? 1 : size - 1)) ? new_range : old_range + static_cast<double>(i) * step;
+    }
+    for (size_t i = 0; i < p + 1; ++i) knots_[new_num_knots - p - 1 + i] = knots_[0] + new_range;
+    const size_t old_points = num_points_;
+    num_knots_ = new_num_knots;
+    umax_ = knots_[new_num_knots - 1];
+    // the old end point moves so that the curve keeps its value at the join
+    const size_t span = KnotSpan(u_join), mod = old_points - 1;
+    const double left1 = u_join - knots_[span], right1 = knots_[span + 1] - u_join;
+    const double left2 = u_join - knots_[span - 1], right2 = knots_[span + 2] - u_join;
+    double b0 = 1.0, b1, tmp = b0 / (right1 + left1);  // UpdateBasis, degree 2 (A2.2)
+    b0 = right1 * tmp;
+    b1 = left1 * tmp;
+    tmp = b0 / (right1 + left2);
+    b0 = right1 * tmp;
+    double saved = left2 * tmp;
+    tmp = b1 / (right2 + left1);
+    b1 = saved + right2 * tmp;
+    if (!(b1 > 0)) return tp::InternalError("basis[1] should be > 0 (0.5)");
+    ctrl_.resize(static_cast<size_t>(MaxNumPoints()) * D, 0.0);
+    for (size_t d = 0; d < D; ++d) {
+      ctrl_[mod * D + d] = 1.0 / (b1) * (ctrl_[mod * D + d] - b0 * ctrl_[(mod - 1) * D + d]);
+    }
+    for (size_t i = 0; i < n; ++i) {
+      if (points[i].size() != D) return tp::InvalidArgumentError("Invalid point size");
+      std::copy(points[i].begin(), points[i].end(), ctrl_.begin() + (old_points + i) * D);
+    }
+    num_points_ = new_num_points;
+    return tp::OkStatus();
+  }
+  // KnotSpan (bspline_base.cc:218-246)
+  size_t KnotSpan(double u) const {
+    if (num_knots_ == 0) return 0;
+    if (u == knots_[num_knots_ - 1]) return num_points_ - 1;
+    size_t lo = degree_, hi = num_knots_ - degree_;
+    while (lo < hi) {
+      const size_t mid = lo + (hi - lo) / 2;
+      if (knots_[mid] <= u) {
+        lo = mid + 1;
+      } else {
+        hi = mid;
+      }
+    }
+    return lo - 1;
   }
 
   // EvalCurve (bspline.h:514-536)
