@@ -230,8 +230,53 @@ def lib():
         L.orc_path_stop_parameter.restype = C.c_int
         L.orc_path_stop_parameter.argtypes = [C.c_int, C.c_int] + [c_double_p] * 5 + [
             C.c_double, c_double_p, C.POINTER(C.c_int), c_double_p]
+        # trajectory buffer (tp_oracle_tbuf.c)
+        _register_tbuf(L, "orc_tbuf_", port=True)
         _lib = L
     return _lib
+
+
+def _register_tbuf(L, pre, port):
+    """ctypes signatures of the TrajectoryBuffer functions; the port (orc_tbuf_*)
+    keeps the dof count in the buffer, the reference wrapper (tpref_tbuf_*) takes
+    it per call."""
+    vp, dbl, i32, i64 = C.c_void_p, C.c_double, C.c_int, C.c_int64
+    D = [] if port else [i32]
+    f = lambda name: getattr(L, pre + name)
+    f("create").restype = i32
+    f("create").argtypes = ([dbl, i32] if port else [dbl]) + [C.POINTER(vp)]
+    f("destroy").restype = None
+    f("destroy").argtypes = [vp]
+    f("clear").restype = None
+    f("clear").argtypes = [vp]
+    f("insert_segment").restype = i32
+    f("insert_segment").argtypes = [vp, i32] + D + [c_double_p] * 4
+    f("append_sample").restype = i32
+    f("append_sample").argtypes = [vp] + D + [dbl] + [c_double_p] * 3
+    f("discard_before_sec").restype = None
+    f("discard_before_sec").argtypes = [vp, dbl]
+    f("discard_before_ns").restype = None
+    f("discard_before_ns").argtypes = [vp, i64]
+    f("positions_up_to_time_ns").restype = i32
+    f("positions_up_to_time_ns").argtypes = [vp, i64]
+    f("get_at_time").restype = i32
+    f("get_at_time").argtypes = [vp, i32, dbl, c_double_p]
+    f("stop_at_index").restype = i32
+    f("stop_at_index").argtypes = [vp, i32] + D + [c_double_p, dbl]
+    f("stop_before_time").restype = i32
+    f("stop_before_time").argtypes = [vp, dbl] + D + [c_double_p, dbl]
+    f("add_offset").restype = None
+    f("add_offset").argtypes = [vp, dbl]
+    f("num_samples").restype = i32
+    f("num_samples").argtypes = [vp]
+    f("sequence_number").restype = i32
+    f("sequence_number").argtypes = [vp]
+    f("start_ns").restype = i64
+    f("start_ns").argtypes = [vp]
+    f("end_ns").restype = i64
+    f("end_ns").argtypes = [vp]
+    f("rows").restype = None
+    f("rows").argtypes = [vp] + D + [c_double_p] * 4
 
 
 def have_ref() -> bool:
@@ -258,6 +303,11 @@ def ref():
         R.tpref_rescale_to_stop.restype = C.c_int
         R.tpref_rescale_to_stop.argtypes = [C.c_int, C.c_int] + [c_double_p] * 5 + [
             C.POINTER(C.c_int), C.POINTER(C.c_int)] + [c_double_p] * 4
+        _register_tbuf(R, "tpref_tbuf_", port=False)
+        R.tpref_time_from_sec_ns.restype = C.c_int64
+        R.tpref_time_from_sec_ns.argtypes = [C.c_double]
+        R.tpref_time_to_sec.restype = C.c_double
+        R.tpref_time_to_sec.argtypes = [C.c_int64]
         _ref = R
     return _ref
 
@@ -790,3 +840,93 @@ def time_from_sec(x):
 
 def time_to_sec(ns):
     return lib().orc_time_to_sec(int(ns))
+
+
+# ----------------------------------------------------------------- trajectory buffer
+class TrajectoryBuffer:
+    """One TrajectoryBuffer (trajectory_buffer.h:30-184).  impl: 'port' (the C
+    restatement) | 'ref' (the reference's object code).  Status returns are
+    absl::StatusCode numbers."""
+
+    def __init__(self, num_dofs, timestep_tolerance=1e-6, impl="port"):
+        self.D, self.port = int(num_dofs), impl == "port"
+        self.L = lib() if self.port else ref()
+        self.pre = "orc_tbuf_" if self.port else "tpref_tbuf_"
+        self.h = C.c_void_p()
+        args = (timestep_tolerance, self.D) if self.port else (timestep_tolerance,)
+        self.create_status = self._f("create")(*args, C.byref(self.h))
+
+    def _f(self, name):
+        return getattr(self.L, self.pre + name)
+
+    def _d(self):
+        return () if self.port else (self.D,)
+
+    def close(self):
+        if self.h:
+            self._f("destroy")(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        self.close()
+
+    def clear(self):
+        self._f("clear")(self.h)
+
+    def insert_segment(self, times, pos, vel, acc):
+        t = np.ascontiguousarray(times, np.float64)
+        p, v, a = (np.ascontiguousarray(x, np.float64).reshape(len(t), self.D)
+                   for x in (pos, vel, acc))
+        return self._f("insert_segment")(self.h, len(t), *self._d(), _dp(t), _dp(p), _dp(v), _dp(a))
+
+    def append_sample(self, time, pos, vel, acc):
+        p, v, a = (np.ascontiguousarray(x, np.float64) for x in (pos, vel, acc))
+        return self._f("append_sample")(self.h, *self._d(), float(time), _dp(p), _dp(v), _dp(a))
+
+    def discard_before_sec(self, t):
+        self._f("discard_before_sec")(self.h, float(t))
+
+    def discard_before_ns(self, ns):
+        self._f("discard_before_ns")(self.h, int(ns))
+
+    def positions_up_to_time_ns(self, ns):
+        return self._f("positions_up_to_time_ns")(self.h, int(ns))
+
+    def get_at_time(self, which, t):
+        out = np.zeros(self.D)
+        st = self._f("get_at_time")(self.h, int(which), float(t), _dp(out))
+        return st, out
+
+    def stop_at_index(self, index, max_acc, time_step):
+        am = np.ascontiguousarray(max_acc, np.float64)
+        return self._f("stop_at_index")(self.h, int(index), *self._d(), _dp(am), float(time_step))
+
+    def stop_before_time(self, t, max_acc, time_step):
+        am = np.ascontiguousarray(max_acc, np.float64)
+        return self._f("stop_before_time")(self.h, float(t), *self._d(), _dp(am), float(time_step))
+
+    def add_offset(self, offset):
+        self._f("add_offset")(self.h, float(offset))
+
+    @property
+    def num_samples(self):
+        return self._f("num_samples")(self.h)
+
+    @property
+    def sequence_number(self):
+        return self._f("sequence_number")(self.h)
+
+    @property
+    def start_ns(self):
+        return self._f("start_ns")(self.h)
+
+    @property
+    def end_ns(self):
+        return self._f("end_ns")(self.h)
+
+    def rows(self):
+        n = self.num_samples
+        t = np.zeros(n)
+        p, v, a = np.zeros((n, self.D)), np.zeros((n, self.D)), np.zeros((n, self.D))
+        self._f("rows")(self.h, *self._d(), _dp(t), _dp(p), _dp(v), _dp(a))
+        return t, p, v, a

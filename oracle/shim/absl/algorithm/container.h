@@ -9,6 +9,18 @@ template <typename C>
 void c_reverse(C& c) {
   std::reverse(c.begin(), c.end());
 }
+template <typename C, typename T>
+auto c_upper_bound(C& c, const T& value) -> decltype(c.begin()) {
+  return std::upper_bound(c.begin(), c.end(), value);
+}
+template <typename C, typename T, typename Compare>
+auto c_upper_bound(C& c, const T& value, Compare comp) -> decltype(c.begin()) {
+  return std::upper_bound(c.begin(), c.end(), value, comp);
+}
+template <typename C, typename T>
+auto c_lower_bound(C& c, const T& value) -> decltype(c.begin()) {
+  return std::lower_bound(c.begin(), c.end(), value);
+}
 }  // namespace absl
 
 #endif  // ORACLE_SHIM_ABSL_ALGORITHM_CONTAINER_H_

@@ -30,6 +30,11 @@ class Span {
   size_t n_ = 0;
 };
 
+template <typename T>
+Span<const T> MakeConstSpan(const T* p, size_t n) {
+  return Span<const T>(p, n);
+}
+
 }  // namespace absl
 
 #endif  // ORACLE_SHIM_ABSL_TYPES_SPAN_H_

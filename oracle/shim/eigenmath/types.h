@@ -40,6 +40,7 @@ class VectorXd {
   const double& operator()(int i) const { return d_[static_cast<size_t>(i)]; }
   double* data() { return d_.data(); }
   const double* data() const { return d_.data(); }
+  void setZero() { std::fill(d_.begin(), d_.end(), 0.0); }
   void setZero(int n) { d_.assign(static_cast<size_t>(n), 0.0); }
   void setConstant(int n, double v) { d_.assign(static_cast<size_t>(n), v); }
 

@@ -213,6 +213,31 @@ int orc_path_stop_parameter(int M, int D, const double* time, const double* path
                             double query_time, double* stop_parameter, int* stop_row,
                             double* stop_duration);
 
+/* ---- TrajectoryBuffer (trajectory_buffer.cc:40-393; tp_oracle_tbuf.c) -------
+ * One growable buffer of [n][D] row-major rows.  Return values are
+ * absl::StatusCode numbers.  which: 0 position, 1 velocity, 2 acceleration. */
+typedef struct orc_tbuf orc_tbuf;
+int orc_tbuf_create(double timestep_tolerance, int D, orc_tbuf** out);
+void orc_tbuf_destroy(orc_tbuf* b);
+void orc_tbuf_clear(orc_tbuf* b);
+int orc_tbuf_insert_segment(orc_tbuf* b, int n, const double* times, const double* pos,
+                            const double* vel, const double* acc);
+int orc_tbuf_append_sample(orc_tbuf* b, double time, const double* pos, const double* vel,
+                           const double* acc);
+void orc_tbuf_discard_before_sec(orc_tbuf* b, double time_sec);
+void orc_tbuf_discard_before_ns(orc_tbuf* b, int64_t ns);
+int orc_tbuf_positions_up_to_time_ns(const orc_tbuf* b, int64_t ns);
+int orc_tbuf_get_at_time(const orc_tbuf* b, int which, double time_sec, double* out);
+int orc_tbuf_stop_at_index(orc_tbuf* b, int index, const double* max_acc, double time_step);
+int orc_tbuf_stop_before_time(orc_tbuf* b, double time_sec, const double* max_acc,
+                              double time_step);
+void orc_tbuf_add_offset(orc_tbuf* b, double offset);
+int orc_tbuf_num_samples(const orc_tbuf* b);
+int orc_tbuf_sequence_number(const orc_tbuf* b);
+int64_t orc_tbuf_start_ns(const orc_tbuf* b);
+int64_t orc_tbuf_end_ns(const orc_tbuf* b);
+void orc_tbuf_rows(const orc_tbuf* b, double* times, double* pos, double* vel, double* acc);
+
 /* ---- online re-planning geometry of a joint path (tp_oracle_switch.c):
  * BSplineT knot insertion / TruncateSplineAt / ExtendWithControlPoints
  * (splines/bspline.h:224-511), ProjectPointOnPath (path_tools.h:59-104),
