@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define TPB_ABI_VERSION 2
+#define TPB_ABI_VERSION 3
 
 /* absl::StatusCode values used by this library. */
 enum {
@@ -45,6 +45,7 @@ enum {
   TPB_INVALID_ARGUMENT = 3,
   TPB_DEADLINE_EXCEEDED = 4,
   TPB_NOT_FOUND = 5,
+  TPB_RESOURCE_EXHAUSTED = 8,
   TPB_FAILED_PRECONDITION = 9,
   TPB_OUT_OF_RANGE = 11,
   TPB_UNIMPLEMENTED = 12,
@@ -455,6 +456,104 @@ int32_t tpb_rescale_to_stop_device(const tpb_stop_desc* d, void* cuda_stream);
 /* All pointers are host pointers; copies in, runs on `device`, copies out, returns
  * when done. */
 int32_t tpb_rescale_to_stop_host(const tpb_stop_desc* d, int32_t device);
+
+/* ---- trajectory buffers ----------------------------------- */
+/* A batch of TrajectoryBuffers (trajectory_buffer.h:30-184) resident on the
+ * device: the consumer format of the resampled trajectories.  Buffer b holds
+ * count[b] rows (time, position[D], velocity[D], acceleration[D]) at rows
+ * head[b] .. head[b]+count[b]-1 of its capacity_rows slots; discarding in front
+ * moves head[b], inserting moves the kept rows to the front only when the slots
+ * behind them do not suffice.  Every operation is one batched call: per-buffer
+ * arguments are arrays of num_buffers entries, per-buffer results are
+ * absl::StatusCode values in status[] (may be NULL), and the call's own return
+ * value only reports argument / CUDA errors.  A buffer that an operation's
+ * "skip" value leaves out keeps its state and gets status TPB_OK.
+ *
+ * Differences from the reference, all on paths where it has no defined result:
+ * rows beyond capacity_rows give TPB_RESOURCE_EXHAUSTED and leave the buffer
+ * unchanged; StopAtIndex on a sample that stands still but is not the last one
+ * (CHECK-abort at trajectory_buffer.cc:338) and on an empty buffer (out-of-bounds
+ * read) give TPB_INTERNAL.  eigenmath::InterpolateLinear is un-vendored; it is
+ * y0 + ((x-x0)/(x1-x0))*(y1-y0), y0 when x1 == x0 (unpinned). */
+typedef struct tpb_tbuf tpb_tbuf;
+typedef struct {
+  int32_t device;            /* CUDA device ordinal */
+  int32_t num_buffers;       /* B */
+  int32_t num_dofs;          /* D; the stop operations need D <= 16 */
+  int32_t capacity_rows;     /* slots per buffer */
+  double timestep_tolerance; /* TrajectoryBufferOptions::timestep_tolerance (1e-6) */
+} tpb_tbuf_config;
+typedef enum {
+  TPB_TBUF_TIMES = 0,         /* double [B][capacity_rows] */
+  TPB_TBUF_POSITIONS = 1,     /* double [B][capacity_rows][D] */
+  TPB_TBUF_VELOCITIES = 2,    /* double [B][capacity_rows][D] */
+  TPB_TBUF_ACCELERATIONS = 3, /* double [B][capacity_rows][D] */
+  TPB_TBUF_HEAD = 4,          /* int32 [B] */
+  TPB_TBUF_COUNT = 5,         /* int32 [B] GetNumSamples() */
+  TPB_TBUF_SEQUENCE = 6       /* int32 [B] GetSequenceNumber() */
+} tpb_tbuf_array;
+/* TrajectoryBuffer::Create (trajectory_buffer.cc:40-48): kFailedPrecondition for
+ * a non-positive tolerance. */
+int32_t tpb_tbuf_create(const tpb_tbuf_config* cfg, tpb_tbuf** out);
+int32_t tpb_tbuf_destroy(tpb_tbuf* t);
+const char* tpb_tbuf_last_error(const tpb_tbuf* t);
+int32_t tpb_tbuf_set_stream(tpb_tbuf* t, void* cuda_stream);
+int32_t tpb_tbuf_sync(tpb_tbuf* t);
+int64_t tpb_tbuf_kernel_launches(const tpb_tbuf* t);
+/* Clear (:64-70) of the buffers with select[b] != 0 (NULL: all). */
+int32_t tpb_tbuf_clear(tpb_tbuf* t, const int32_t* select, int32_t on_device);
+/* InsertSegment (:80-132).  The segments are packed like TPB_ARR_R_*: segment b
+ * is rows begin[b] .. begin[b]+length[b]-1 of times [total_rows] and positions /
+ * velocities / accelerations [total_rows][D]; with on_device the engine's
+ * resampled trajectories go in without leaving HBM (begin = TPB_ARR_R_OFFSET).
+ * length[b] < 0 skips buffer b; length[b] == 0 only counts (:97-101). */
+int32_t tpb_tbuf_insert_segments(tpb_tbuf* t, const int64_t* begin, const int32_t* length,
+                                 int64_t total_rows, const double* times,
+                                 const double* positions, const double* velocities,
+                                 const double* accelerations, int32_t* status,
+                                 int32_t on_device);
+/* AppendSample (:134-148) to the buffers with select[b] != 0 (NULL: all): time
+ * [B], positions / velocities / accelerations [B][D]. */
+int32_t tpb_tbuf_append_samples(tpb_tbuf* t, const int32_t* select, const double* time,
+                                const double* positions, const double* velocities,
+                                const double* accelerations, int32_t* status,
+                                int32_t on_device);
+/* DiscardSegmentBefore(double) (:154-207); time_sec[b] NaN skips buffer b.  The
+ * absl::Time overload is TimeToSec (time.h:27-30) on the host, then this. */
+int32_t tpb_tbuf_discard_before(tpb_tbuf* t, const double* time_sec, int32_t on_device);
+/* GetPositionsUpToTime (:209-226): num[b] leading rows lie before time_sec[b]. */
+int32_t tpb_tbuf_positions_up_to_time(tpb_tbuf* t, const double* time_sec, int32_t* num,
+                                      int32_t on_device);
+/* Get{Position,Velocity,Acceleration}AtTime (:228-293), queries_per_buffer of them
+ * per buffer: time_sec [B][Q]; outputs [B][Q][D], each may be NULL; status [B][Q]
+ * (kFailedPrecondition for an empty buffer, kOutOfRange outside it; such rows of
+ * the outputs are left untouched). */
+int32_t tpb_tbuf_sample(tpb_tbuf* t, int32_t queries_per_buffer, const double* time_sec,
+                        double* positions, double* velocities, double* accelerations,
+                        int32_t* status, int32_t on_device);
+/* StopAtIndex (:295-358): index [B] (INT32_MIN skips buffer b), max_acceleration
+ * [B][D].  Runs the batched RescaleTrajectoryBackwardToStop on rows 0..index of
+ * every selected buffer in place, then re-inserts the stopping segments. */
+int32_t tpb_tbuf_stop_at_index(tpb_tbuf* t, const int32_t* index, const double* max_acceleration,
+                               double time_step, int32_t* status, int32_t on_device);
+/* StopBeforeTime(double) (:366-381); time_sec[b] NaN skips buffer b. */
+int32_t tpb_tbuf_stop_before_time(tpb_tbuf* t, const double* time_sec,
+                                  const double* max_acceleration, double time_step,
+                                  int32_t* status, int32_t on_device);
+/* AddOffsetToTimestamps(double) (:386-389), offset [B]. */
+int32_t tpb_tbuf_add_offset(tpb_tbuf* t, const double* offset, int32_t on_device);
+/* GetNumSamples / GetSequenceNumber and the first / last time stamp of every
+ * buffer (NaN when empty; GetStartTime / GetEndTime are TimeFromSec of them, 0
+ * for an empty buffer, :50-62).  Any pointer may be NULL. */
+int32_t tpb_tbuf_get_state(tpb_tbuf* t, int32_t* num_samples, int32_t* sequence_number,
+                           double* front_time, double* back_time, int32_t on_device);
+/* Rows first_row .. first_row+num_rows-1 of one buffer (GetTimes / GetPositions /
+ * GetVelocities / GetAccelerations); any pointer may be NULL. */
+int32_t tpb_tbuf_get_rows(tpb_tbuf* t, int32_t buffer, int32_t first_row, int32_t num_rows,
+                          double* times, double* positions, double* velocities,
+                          double* accelerations, int32_t on_device);
+/* Zero-copy access for device-side consumers. */
+int32_t tpb_tbuf_devptr(tpb_tbuf* t, tpb_tbuf_array what, void** ptr, size_t* bytes);
 
 #ifdef __cplusplus
 }

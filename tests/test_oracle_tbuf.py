@@ -26,6 +26,9 @@ def ns(sec):
 
 
 def make(impl="port", tol=1e-6, dofs=D):
+    if impl == "gpu":  # one buffer of a device batch (tests/test_gpu_tbuf.py)
+        from __graft_entry__ import load_package
+        return load_package().TrajectoryBufferBatch(3, dofs, 2048, tol).view(1)
     b = orc.TrajectoryBuffer(dofs, tol, impl=impl)
     assert b.create_status == OK
     return b
@@ -38,6 +41,11 @@ def test_create_checks_options():
     """trajectory_buffer_test.cc:99-103"""
     for impl in IMPLS:
         assert orc.TrajectoryBuffer(D, -1.0, impl=impl).create_status == FAILED_PRECONDITION
+    from __graft_entry__ import load_package
+    pkg = load_package()
+    with pytest.raises(pkg.TpbError) as ei:  # checked before any device is touched
+        pkg.TrajectoryBufferBatch(2, D, 64, timestep_tolerance=-1.0)
+    assert ei.value.code == FAILED_PRECONDITION
 
 
 @pytest.mark.parametrize("impl", IMPLS)

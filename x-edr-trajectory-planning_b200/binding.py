@@ -72,6 +72,11 @@ class _SplineDesc(C.Structure):
                 ("out", C.c_void_p), ("status", C.c_void_p), ("exact", C.c_int32)]
 
 
+class _TbufConfig(C.Structure):
+    _fields_ = [("device", C.c_int32), ("num_buffers", C.c_int32), ("num_dofs", C.c_int32),
+                ("capacity_rows", C.c_int32), ("timestep_tolerance", C.c_double)]
+
+
 _lib = None
 
 
@@ -162,6 +167,43 @@ def lib():
         L.tpb_rescale_to_stop_device.argtypes = [C.POINTER(_StopDesc), vp]
         L.tpb_rescale_to_stop_host.restype = i32
         L.tpb_rescale_to_stop_host.argtypes = [C.POINTER(_StopDesc), i32]
+        # trajectory buffers
+        L.tpb_tbuf_create.restype = i32
+        L.tpb_tbuf_create.argtypes = [C.POINTER(_TbufConfig), C.POINTER(vp)]
+        L.tpb_tbuf_destroy.restype = i32
+        L.tpb_tbuf_destroy.argtypes = [vp]
+        L.tpb_tbuf_last_error.restype = C.c_char_p
+        L.tpb_tbuf_last_error.argtypes = [vp]
+        L.tpb_tbuf_set_stream.restype = i32
+        L.tpb_tbuf_set_stream.argtypes = [vp, vp]
+        L.tpb_tbuf_sync.restype = i32
+        L.tpb_tbuf_sync.argtypes = [vp]
+        L.tpb_tbuf_kernel_launches.restype = i64
+        L.tpb_tbuf_kernel_launches.argtypes = [vp]
+        L.tpb_tbuf_clear.restype = i32
+        L.tpb_tbuf_clear.argtypes = [vp, vp, i32]
+        L.tpb_tbuf_insert_segments.restype = i32
+        L.tpb_tbuf_insert_segments.argtypes = [vp, vp, vp, i64, vp, vp, vp, vp, vp, i32]
+        L.tpb_tbuf_append_samples.restype = i32
+        L.tpb_tbuf_append_samples.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32]
+        L.tpb_tbuf_discard_before.restype = i32
+        L.tpb_tbuf_discard_before.argtypes = [vp, vp, i32]
+        L.tpb_tbuf_positions_up_to_time.restype = i32
+        L.tpb_tbuf_positions_up_to_time.argtypes = [vp, vp, vp, i32]
+        L.tpb_tbuf_sample.restype = i32
+        L.tpb_tbuf_sample.argtypes = [vp, i32, vp, vp, vp, vp, vp, i32]
+        L.tpb_tbuf_stop_at_index.restype = i32
+        L.tpb_tbuf_stop_at_index.argtypes = [vp, vp, vp, f64, vp, i32]
+        L.tpb_tbuf_stop_before_time.restype = i32
+        L.tpb_tbuf_stop_before_time.argtypes = [vp, vp, vp, f64, vp, i32]
+        L.tpb_tbuf_add_offset.restype = i32
+        L.tpb_tbuf_add_offset.argtypes = [vp, vp, i32]
+        L.tpb_tbuf_get_state.restype = i32
+        L.tpb_tbuf_get_state.argtypes = [vp, vp, vp, vp, vp, i32]
+        L.tpb_tbuf_get_rows.restype = i32
+        L.tpb_tbuf_get_rows.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, i32]
+        L.tpb_tbuf_devptr.restype = i32
+        L.tpb_tbuf_devptr.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(C.c_size_t)]
         _lib = L
     return _lib
 
@@ -557,3 +599,266 @@ def rescale_to_stop_device(max_acceleration, begin, length, times, velocities, a
     rc = lib().tpb_rescale_to_stop_device(C.byref(d), stream)
     if rc != 0:
         raise TpbError(rc, "tpb_rescale_to_stop_device")
+
+
+# ------------------------------------------------------------------ trajectory buffers
+SKIP_INDEX = -2 ** 31
+
+
+def time_from_sec_ns(seconds):
+    """time.h:23-25: absl::FromUnixNanos(seconds * 1e9) (truncation toward zero)."""
+    return int(np.float64(seconds) * np.float64(1000000000))
+
+
+def time_to_sec(ns):
+    """time.h:27-30"""
+    return float(np.float64(int(ns)) / np.float64(1000000000))
+
+
+class TrajectoryBufferBatch:
+    """A batch of device-resident TrajectoryBuffers (tpb_tbuf_*, include/tpb.h).
+
+    Every method is one batched call over all buffers; per-buffer arguments are numpy
+    arrays (host) or torch CUDA tensors (device, asynchronous on the stream).  Statuses
+    are absl::StatusCode values per buffer.
+    """
+
+    def __init__(self, num_buffers, num_dofs, capacity_rows, timestep_tolerance=1e-6, device=0):
+        self.B, self.D, self.cap = int(num_buffers), int(num_dofs), int(capacity_rows)
+        self._h = C.c_void_p()
+        cfg = _TbufConfig(device, self.B, self.D, self.cap, timestep_tolerance)
+        rc = lib().tpb_tbuf_create(C.byref(cfg), C.byref(self._h))
+        if rc != 0:
+            self._h = C.c_void_p()
+            raise TpbError(rc, "tpb_tbuf_create")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().tpb_tbuf_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise TpbError(rc, lib().tpb_tbuf_last_error(self._h).decode())
+
+    @staticmethod
+    def _dev(*xs):
+        """1 when the arguments are device tensors, 0 for numpy; they must agree."""
+        kinds = {bool(hasattr(x, "data_ptr") and x.is_cuda) for x in xs if x is not None}
+        assert len(kinds) <= 1, "mix of host and device arguments"
+        return 1 if kinds == {True} else 0
+
+    def _status(self, dev, shape=None):
+        if dev:
+            return None
+        return np.zeros(self.B if shape is None else shape, np.int32)
+
+    def set_stream(self, cuda_stream_ptr):
+        self._ck(lib().tpb_tbuf_set_stream(self._h, cuda_stream_ptr))
+
+    def sync(self):
+        self._ck(lib().tpb_tbuf_sync(self._h))
+
+    @property
+    def kernel_launches(self):
+        return lib().tpb_tbuf_kernel_launches(self._h)
+
+    def clear(self, select=None):
+        if select is not None and not hasattr(select, "data_ptr"):
+            select = np.ascontiguousarray(select, np.int32)
+        self._ck(lib().tpb_tbuf_clear(self._h, _addr(select), self._dev(select)))
+
+    def insert_segments(self, begin, length, times, positions, velocities, accelerations,
+                        status=None):
+        """Packed segments (see tpb_tbuf_insert_segments).  Returns status [B] (host calls)."""
+        dev = self._dev(begin, length, times, positions, velocities, accelerations)
+        if not dev:
+            begin = np.ascontiguousarray(begin, np.int64)
+            length = np.ascontiguousarray(length, np.int32)
+            times, positions, velocities, accelerations = (
+                _f64(x) for x in (times, positions, velocities, accelerations))
+            status = self._status(dev)
+        total = int(times.shape[0])
+        self._ck(lib().tpb_tbuf_insert_segments(
+            self._h, _addr(begin), _addr(length), total, _addr(times), _addr(positions),
+            _addr(velocities), _addr(accelerations), _addr(status), dev))
+        return status
+
+    def append_samples(self, time, positions, velocities, accelerations, select=None):
+        dev = self._dev(time, positions, velocities, accelerations, select)
+        status = self._status(dev)
+        if not dev:
+            time, positions, velocities, accelerations = (
+                _f64(x) for x in (time, positions, velocities, accelerations))
+            if select is not None:
+                select = np.ascontiguousarray(select, np.int32)
+        self._ck(lib().tpb_tbuf_append_samples(
+            self._h, _addr(select), _addr(time), _addr(positions), _addr(velocities),
+            _addr(accelerations), _addr(status), dev))
+        return status
+
+    def discard_before(self, time_sec):
+        dev = self._dev(time_sec)
+        time_sec = _f64(time_sec)
+        self._ck(lib().tpb_tbuf_discard_before(self._h, _addr(time_sec), dev))
+
+    def positions_up_to_time(self, time_sec):
+        time_sec = _f64(time_sec)
+        num = np.zeros(self.B, np.int32)
+        self._ck(lib().tpb_tbuf_positions_up_to_time(self._h, _addr(time_sec), _addr(num), 0))
+        return num
+
+    def sample(self, time_sec, positions=True, velocities=True, accelerations=True, out=None):
+        """time_sec [B][Q].  Host: returns (status [B][Q], pos, vel, acc [B][Q][D] or None).
+        Device: `out` = (pos, vel, acc, status) tensors (any may be None), asynchronous."""
+        dev = self._dev(time_sec)
+        Q = int(time_sec.shape[1])
+        if dev:
+            p, v, a, st = out
+        else:
+            time_sec = _f64(time_sec)
+            mk = lambda want: np.zeros((self.B, Q, self.D)) if want else None
+            p, v, a = mk(positions), mk(velocities), mk(accelerations)
+            st = np.zeros((self.B, Q), np.int32)
+        self._ck(lib().tpb_tbuf_sample(self._h, Q, _addr(time_sec), _addr(p), _addr(v), _addr(a),
+                                       _addr(st), dev))
+        return st, p, v, a
+
+    def stop_at_index(self, index, max_acceleration, time_step):
+        dev = self._dev(index, max_acceleration)
+        status = self._status(dev)
+        if not dev:
+            index = np.ascontiguousarray(index, np.int32)
+            max_acceleration = _f64(max_acceleration)
+        self._ck(lib().tpb_tbuf_stop_at_index(self._h, _addr(index), _addr(max_acceleration),
+                                              float(time_step), _addr(status), dev))
+        return status
+
+    def stop_before_time(self, time_sec, max_acceleration, time_step):
+        dev = self._dev(time_sec, max_acceleration)
+        status = self._status(dev)
+        if not dev:
+            time_sec, max_acceleration = _f64(time_sec), _f64(max_acceleration)
+        self._ck(lib().tpb_tbuf_stop_before_time(self._h, _addr(time_sec),
+                                                 _addr(max_acceleration), float(time_step),
+                                                 _addr(status), dev))
+        return status
+
+    def add_offset(self, offset):
+        dev = self._dev(offset)
+        offset = _f64(offset)
+        self._ck(lib().tpb_tbuf_add_offset(self._h, _addr(offset), dev))
+
+    def state(self):
+        """dict(num_samples, sequence_number, front_time, back_time), numpy [B]."""
+        n, s = np.zeros(self.B, np.int32), np.zeros(self.B, np.int32)
+        f, b = np.zeros(self.B), np.zeros(self.B)
+        self._ck(lib().tpb_tbuf_get_state(self._h, _addr(n), _addr(s), _addr(f), _addr(b), 0))
+        return dict(num_samples=n, sequence_number=s, front_time=f, back_time=b)
+
+    def rows(self, buffer, num_rows=None, first_row=0):
+        if num_rows is None:
+            num_rows = int(self.state()["num_samples"][buffer]) - first_row
+        t = np.zeros(num_rows)
+        p, v, a = (np.zeros((num_rows, self.D)) for _ in range(3))
+        self._ck(lib().tpb_tbuf_get_rows(self._h, buffer, first_row, num_rows, _addr(t), _addr(p),
+                                         _addr(v), _addr(a), 0))
+        return t, p, v, a
+
+    def devptr(self, what):
+        ptr, nbytes = C.c_void_p(), C.c_size_t()
+        self._ck(lib().tpb_tbuf_devptr(self._h, what, C.byref(ptr), C.byref(nbytes)))
+        return ptr.value, nbytes.value
+
+    def view(self, buffer):
+        return TrajectoryBufferView(self, buffer)
+
+
+class TrajectoryBufferView:
+    """One buffer of a TrajectoryBufferBatch with the single-buffer interface of the
+    reference's TrajectoryBuffer (every call is a batched call that skips the others)."""
+
+    def __init__(self, batch, buffer):
+        self.batch, self.b = batch, int(buffer)
+
+    def _only(self, value, fill, dtype=np.float64, shape=()):
+        x = np.full((self.batch.B,) + shape, fill, dtype)
+        x[self.b] = value
+        return x
+
+    def _sel(self):
+        return self._only(1, 0, np.int32)
+
+    def clear(self):
+        self.batch.clear(self._sel())
+
+    def insert_segment(self, times, pos, vel, acc):
+        n = len(times)
+        D = self.batch.D
+        length = self._only(n, -1, np.int32)
+        begin = np.zeros(self.batch.B, np.int64)
+        reshape = lambda x: np.ascontiguousarray(x, np.float64).reshape(n, D)
+        return int(self.batch.insert_segments(begin, length, np.ascontiguousarray(times, np.float64),
+                                              reshape(pos), reshape(vel), reshape(acc))[self.b])
+
+    def append_sample(self, time, pos, vel, acc):
+        D = self.batch.D
+        row = lambda x: self._only(np.asarray(x, np.float64), 0.0, shape=(D,))
+        return int(self.batch.append_samples(self._only(time, 0.0), row(pos), row(vel), row(acc),
+                                             self._sel())[self.b])
+
+    def discard_before_sec(self, t):
+        self.batch.discard_before(self._only(t, np.nan))
+
+    def discard_before_ns(self, ns):
+        self.discard_before_sec(time_to_sec(ns))
+
+    def positions_up_to_time_ns(self, ns):
+        return int(self.batch.positions_up_to_time(self._only(time_to_sec(ns), np.nan))[self.b])
+
+    def get_at_time(self, which, t):
+        want = [which == 0, which == 1, which == 2]
+        st, p, v, a = self.batch.sample(self._only(t, np.nan).reshape(-1, 1), *want)
+        return int(st[self.b, 0]), (p, v, a)[which][self.b, 0].copy()
+
+    def stop_at_index(self, index, max_acc, time_step):
+        D = self.batch.D
+        amax = self._only(np.asarray(max_acc, np.float64), 1.0, shape=(D,))
+        return int(self.batch.stop_at_index(self._only(index, SKIP_INDEX, np.int32), amax,
+                                            time_step)[self.b])
+
+    def stop_before_time(self, t, max_acc, time_step):
+        D = self.batch.D
+        amax = self._only(np.asarray(max_acc, np.float64), 1.0, shape=(D,))
+        return int(self.batch.stop_before_time(self._only(t, np.nan), amax, time_step)[self.b])
+
+    def add_offset(self, offset):
+        self.batch.add_offset(self._only(offset, 0.0))
+
+    @property
+    def num_samples(self):
+        return int(self.batch.state()["num_samples"][self.b])
+
+    @property
+    def sequence_number(self):
+        return int(self.batch.state()["sequence_number"][self.b])
+
+    @property
+    def start_ns(self):
+        s = self.batch.state()
+        return time_from_sec_ns(0) if s["num_samples"][self.b] == 0 else time_from_sec_ns(
+            s["front_time"][self.b])
+
+    @property
+    def end_ns(self):
+        s = self.batch.state()
+        return 0 if s["num_samples"][self.b] == 0 else time_from_sec_ns(s["back_time"][self.b])
+
+    def rows(self):
+        return self.batch.rows(self.b)
