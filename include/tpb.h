@@ -500,6 +500,9 @@ const char* tpb_tbuf_last_error(const tpb_tbuf* t);
 int32_t tpb_tbuf_set_stream(tpb_tbuf* t, void* cuda_stream);
 int32_t tpb_tbuf_sync(tpb_tbuf* t);
 int64_t tpb_tbuf_kernel_launches(const tpb_tbuf* t);
+/* Reserve (:72-77): at least capacity_rows slots per buffer; rows, sequence numbers
+ * and contents are kept (device-to-device), the device pointers change. */
+int32_t tpb_tbuf_reserve(tpb_tbuf* t, int32_t capacity_rows);
 /* Clear (:64-70) of the buffers with select[b] != 0 (NULL: all). */
 int32_t tpb_tbuf_clear(tpb_tbuf* t, const int32_t* select, int32_t on_device);
 /* InsertSegment (:80-132).  The segments are packed like TPB_ARR_R_*: segment b

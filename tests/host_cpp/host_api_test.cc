@@ -12,6 +12,7 @@
 #include "trajectory_planning/path_timing_trajectory.h"
 #include "trajectory_planning/path_tools.h"
 #include "trajectory_planning/rescale_to_stop.h"
+#include "trajectory_planning/trajectory_buffer.h"
 #include "trajectory_planning/splines/bspline.h"
 #include "trajectory_planning/time_optimal_path_timing.h"
 #include "trajectory_planning/timeable_path_cartesian_spline.h"
@@ -686,6 +687,193 @@ int main() {
       EXPECT(empty.ok() && (*empty).times.empty());
     }
     printf("\"cases\": %d},\n", idx);
+  }
+  // ---- TrajectoryBuffer (trajectory_buffer_test.cc:99-716)
+  {
+    constexpr int kNumJoints = 9;
+    constexpr double kSampleTimeSec = 8e-3;
+    auto test_trajectory = [&](double offset, int count) {  // :80-97
+      SampledTrajectory tr;
+      for (int i = 0; i < count; ++i) {
+        tr.times.push_back(i * kSampleTimeSec + offset);
+        tr.positions.push_back(VectorXd::Constant(kNumJoints, i));
+        tr.velocities.push_back(VectorXd::Constant(kNumJoints, 10 * i));
+        tr.accelerations.push_back(VectorXd::Constant(kNumJoints, 100 * i));
+      }
+      return tr;
+    };
+    auto quadratic_trajectory = [&](int count, double dt) {  // :60-77
+      SampledTrajectory tr;
+      const double final_time = (count - 1) * dt;
+      for (int i = 0; i < count; ++i) {
+        const double t = dt * i, trel = t - final_time;
+        tr.times.push_back(t);
+        tr.positions.push_back(VectorXd::Constant(kNumJoints, 0.5 * trel * trel));
+        tr.velocities.push_back(VectorXd::Constant(kNumJoints, trel));
+        tr.accelerations.push_back(VectorXd::Constant(kNumJoints, 1.0));
+      }
+      return tr;
+    };
+    auto insert = [](TrajectoryBuffer& b, const SampledTrajectory& tr) {
+      return b.InsertSegment(tr.times, tr.positions, tr.velocities, tr.accelerations);
+    };
+    printf("\"tbuf\": {\n");
+    // CreateChecksOptions (:99-103)
+    EXPECT(TrajectoryBuffer::Create({-1}).status().code() == tp::StatusCode::kFailedPrecondition);
+    // InsertSegmentWorks (:105-195)
+    {
+      auto made = TrajectoryBuffer::Create();
+      EXPECT(made.ok());
+      TrajectoryBuffer& buffer = **made;
+      EXPECT(buffer.GetNumSamples() == 0 && buffer.GetStartTime() == TimeFromSec(0) &&
+             buffer.GetSequenceNumber() == 0);
+      EXPECT(buffer.InsertSegment({}, {}, {}, {}).ok());
+      EXPECT(buffer.GetStartTime() == TimeFromSec(0) && buffer.GetEndTime() == TimeFromSec(0));
+      EXPECT(buffer.GetSequenceNumber() == 1 && buffer.GetNumSamples() == 0);
+      buffer.Clear();
+      SampledTrajectory tr = test_trajectory(1.0, 10);
+      EXPECT(insert(buffer, tr).ok());
+      EXPECT(buffer.GetStartTime() == TimeFromSec(tr.times.front()));
+      EXPECT(buffer.GetEndTime() == TimeFromSec(tr.times.back()));
+      EXPECT(buffer.GetSequenceNumber() == 0 && buffer.GetNumSamples() == tr.positions.size());
+      for (size_t i = 0; i < tr.times.size(); ++i) {
+        EXPECT(buffer.GetTimes()[i] == tr.times[i] && buffer.GetPositions()[i] == tr.positions[i] &&
+               buffer.GetVelocities()[i] == tr.velocities[i] &&
+               buffer.GetAccelerations()[i] == tr.accelerations[i]);
+      }
+      tr = test_trajectory(1.0 + 3 * kSampleTimeSec, 5);
+      EXPECT(insert(buffer, tr).ok());
+      EXPECT(buffer.GetStartTime() == TimeFromSec(1) &&
+             buffer.GetEndTime() == TimeFromSec(tr.times.back()));
+      EXPECT(buffer.GetSequenceNumber() == 1 && buffer.GetNumSamples() == 3 + tr.positions.size());
+      const double expect_pos[8] = {0, 1, 2, 0, 1, 2, 3, 4};
+      for (int i = 0; i < 8 && buffer.GetNumSamples() == 8; ++i) {
+        EXPECT(buffer.GetTimes()[i] == 1.0 + i * kSampleTimeSec);
+        EXPECT(buffer.GetPositions()[i] == VectorXd::Constant(kNumJoints, expect_pos[i]));
+        EXPECT(buffer.GetVelocities()[i] == VectorXd::Constant(kNumJoints, 10 * expect_pos[i]));
+        EXPECT(buffer.GetAccelerations()[i] == VectorXd::Constant(kNumJoints, 100 * expect_pos[i]));
+      }
+      // InsertSegmentFailsForInvalidArguments (:290-323)
+      std::vector<double> short_times(5);
+      std::vector<VectorXd> short_rows(5);
+      tr = test_trajectory(1.0, 10);
+      EXPECT(buffer.InsertSegment(short_times, tr.positions, tr.velocities, tr.accelerations).code() ==
+             tp::StatusCode::kInvalidArgument);
+      EXPECT(buffer.InsertSegment(tr.times, short_rows, tr.velocities, tr.accelerations).code() ==
+             tp::StatusCode::kInvalidArgument);
+      EXPECT(buffer.InsertSegment(tr.times, tr.positions, short_rows, tr.accelerations).code() ==
+             tp::StatusCode::kInvalidArgument);
+      EXPECT(buffer.InsertSegment(tr.times, tr.positions, tr.velocities, short_rows).code() ==
+             tp::StatusCode::kInvalidArgument);
+      tr.times.front() = TimeToSec(buffer.GetEndTime());
+      for (size_t i = 1; i < tr.times.size(); ++i) tr.times[i] = tr.times[i - 1] + kSampleTimeSec;
+      EXPECT(insert(buffer, tr).ok());
+    }
+    // AppendSampleWorks (:197-228)
+    {
+      auto made = TrajectoryBuffer::Create();
+      TrajectoryBuffer& buffer = **made;
+      auto c = [&](double x) { return VectorXd::Constant(kNumJoints, x); };
+      EXPECT(buffer.AppendSample(1.0, c(1), c(2), c(3)).ok());
+      EXPECT(buffer.AppendSample(1.0, c(1), c(2), c(3)).code() == tp::StatusCode::kInvalidArgument);
+      EXPECT(buffer.AppendSample(-1.0, c(1), c(2), c(3)).code() == tp::StatusCode::kInvalidArgument);
+      EXPECT(buffer.AppendSample(1.1, c(1.1), c(2.1), c(3.1)).ok());
+      EXPECT(buffer.GetNumSamples() == 2);
+      EXPECT(buffer.GetPositions()[1] == c(1.1) && buffer.GetVelocities()[1] == c(2.1) &&
+             buffer.GetAccelerations()[0] == c(3));
+    }
+    // DiscardWorks (:341-471), GetPositionsUpToTime (:473-501), GetPositionAtTime (:503-528)
+    {
+      auto made = TrajectoryBuffer::Create();
+      TrajectoryBuffer& buffer = **made;
+      buffer.DiscardSegmentBefore(TimeFromSec(10));
+      EXPECT(buffer.GetSequenceNumber() == 0 && buffer.GetNumSamples() == 0);
+      const SampledTrajectory tr = test_trajectory(1.0, 10);
+      EXPECT(insert(buffer, tr).ok());
+      buffer.DiscardSegmentBefore(buffer.GetStartTime());
+      EXPECT(buffer.GetNumSamples() == 10);
+      buffer.DiscardSegmentBefore(TimeFromSec(tr.times[4]));
+      EXPECT(buffer.GetStartTime() == TimeFromSec(tr.times[4]) && buffer.GetTimes().front() == tr.times[4]);
+      EXPECT(buffer.GetEndTime() == TimeFromSec(tr.times.back()) && buffer.GetNumSamples() == 6);
+      buffer.DiscardSegmentBefore(TimeFromSec(tr.times.back() + 1.0 / 1e9));
+      EXPECT(buffer.GetStartTime() == TimeFromSec(0) && buffer.GetEndTime() == TimeFromSec(0) &&
+             buffer.GetNumSamples() == 0);
+      buffer.Clear();
+      EXPECT(insert(buffer, tr).ok());
+      const double between = 0.5 * (tr.times[5] + tr.times[6]);
+      buffer.DiscardSegmentBefore(between);
+      EXPECT(std::fabs(buffer.GetTimes().front() - between) <= 1e-10);
+      PrintArray("discard_between_times", std::vector<double>(buffer.GetTimes().begin(), buffer.GetTimes().end()));
+      PrintArray("discard_between_first_position",
+                 std::vector<double>(buffer.GetPositions().front().begin(), buffer.GetPositions().front().end()));
+      buffer.Clear();
+      const SampledTrajectory five = test_trajectory(1.0, 5);
+      EXPECT(insert(buffer, five).ok());
+      EXPECT(buffer.GetPositionsUpToTime(TimeFromSec(10)).size() == 0);
+      EXPECT(buffer.GetPositionsUpToTime(TimeFromSec(-1)).size() == 0);
+      EXPECT(buffer.GetPositionsUpToTime(TimeFromSec(five.times[2])).size() == 2);
+      EXPECT(buffer.GetPositionsUpToTime(TimeFromSec(std::nextafter(five.times[2], five.times[1]))).size() == 1);
+      EXPECT(buffer.GetPositionsUpToTime(TimeFromSec(std::nextafter(five.times[2], five.times[3]))).size() == 2);
+      for (size_t i = 0; i < five.times.size(); ++i) {
+        auto p = buffer.GetPositionAtTime(TimeFromSec(five.times[i]));
+        auto v = buffer.GetVelocityAtTime(TimeFromSec(five.times[i]));
+        EXPECT(p.ok() && v.ok());
+        for (int j = 0; j < kNumJoints && p.ok() && v.ok(); ++j) {
+          EXPECT(std::fabs((*p)[j] - five.positions[i][j]) <= 1e-10);
+          EXPECT(std::fabs((*v)[j] - five.velocities[i][j]) <= 1e-8);
+        }
+      }
+      EXPECT(buffer.GetPositionAtTime(100.0).status().code() == tp::StatusCode::kOutOfRange);
+      buffer.AddOffsetToTimestamps(0.5);
+      EXPECT(buffer.GetTimes().front() == five.times.front() + 0.5);
+    }
+    // StopAtIndex / StopBeforeTime (:530-716)
+    {
+      constexpr double kDt = 1e-3;
+      constexpr int kNumSamples = 1001, kStopIndex = kNumSamples / 2;
+      const SampledTrajectory tr = quadratic_trajectory(kNumSamples, kDt);
+      const VectorXd amax = VectorXd::Constant(kNumJoints, 5.0);
+      auto made = TrajectoryBuffer::Create();
+      TrajectoryBuffer& buffer = **made;
+      EXPECT(buffer.StopAtIndex(-1, amax, kDt).code() == tp::StatusCode::kOutOfRange);
+      EXPECT(buffer.StopAtIndex(0, amax, kDt).code() == tp::StatusCode::kOutOfRange);
+      EXPECT(buffer.StopBeforeTime(1.0, amax, kDt).ok());
+      EXPECT(insert(buffer, tr).ok());
+      EXPECT(buffer.StopAtIndex(kNumSamples, amax, kDt).code() == tp::StatusCode::kOutOfRange);
+      EXPECT(buffer.StopAtIndex(kStopIndex, amax, -0.1).code() == tp::StatusCode::kInvalidArgument);
+      EXPECT(buffer.StopAtIndex(kStopIndex, amax, kDt).ok());
+      EXPECT(static_cast<int>(buffer.GetNumSamples()) >= kStopIndex + 1);
+      for (int j = 0; j < kNumJoints; ++j) EXPECT(std::fabs(buffer.GetVelocities().back()[j]) <= 1e-12);
+      for (const auto& acc : buffer.GetAccelerations())
+        for (int j = 0; j < kNumJoints; ++j) EXPECT(std::fabs(acc[j]) <= amax[j] + 1e-8);
+      printf("\"stop_num_samples\": %d,\n", static_cast<int>(buffer.GetNumSamples()));
+      PrintArray("stop_times", std::vector<double>(buffer.GetTimes().begin(), buffer.GetTimes().end()));
+      std::vector<VectorXd> vel(buffer.GetVelocities().begin(), buffer.GetVelocities().end());
+      PrintArray("stop_velocities", Flatten(vel));
+      // infeasible (:593-632)
+      buffer.Clear();
+      EXPECT(insert(buffer, tr).ok());
+      const VectorXd weak = VectorXd::Constant(kNumJoints, 1.0);
+      EXPECT(buffer.StopAtIndex(2, weak, kDt).code() == tp::StatusCode::kNotFound);
+      EXPECT(buffer.StopBeforeTime(kDt * 2, weak, kDt).code() == tp::StatusCode::kNotFound);
+      EXPECT(buffer.StopBeforeTime(kDt * 3.1415, weak, kDt).code() == tp::StatusCode::kNotFound);
+      EXPECT(buffer.GetNumSamples() == static_cast<size_t>(kNumSamples));
+      // halfway between two samples (:673-685)
+      const double halfway = 0.5 * (buffer.GetTimes()[kStopIndex] + buffer.GetTimes()[kStopIndex + 1]);
+      EXPECT(buffer.StopBeforeTime(halfway, amax, kDt).ok());
+      EXPECT(static_cast<int>(buffer.GetNumSamples()) >= kStopIndex + 1);
+      printf("\"stop_halfway_num_samples\": %d,\n", static_cast<int>(buffer.GetNumSamples()));
+      // growth beyond the initial capacity keeps rows and sequence number
+      auto big = TrajectoryBuffer::Create();
+      TrajectoryBuffer& grow = **big;
+      EXPECT(insert(grow, quadratic_trajectory(3000, kDt)).ok());
+      SampledTrajectory more = quadratic_trajectory(9000, kDt);
+      for (auto& t : more.times) t += 2.0;
+      EXPECT(insert(grow, more).ok());
+      EXPECT(grow.GetNumSamples() == 2000 + 9000 && grow.GetSequenceNumber() == 1);
+      EXPECT(grow.GetTimes()[1999] == 1999 * kDt && grow.GetTimes()[2000] == more.times[0]);
+    }
+    printf("\"done\": 1},\n");
   }
   printf("\"failures\": %d\n}\n", g_fail);
   return g_fail ? 1 : 0;

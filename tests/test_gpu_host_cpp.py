@@ -248,3 +248,30 @@ def test_bspline_knot_insertion_truncate_extend_match_oracle(result, po):
     assert np.array_equal(np.array(r["knots"]), sp.knots)
     assert np.array_equal(np.array(r["control_points"]).reshape(-1, 3), sp.points)
     np.testing.assert_allclose(np.array(r["after"]), np.array(r["before"]), atol=1e-12)
+
+
+def test_trajectory_buffer_matches_oracle(result, po):
+    """host TrajectoryBuffer on trajectory_buffer_test.cc's scenarios (the EXPECTs run in
+    the exerciser); the rows it prints against the oracle, bit for bit."""
+    import tbuf_cases as TC
+    r = result["tbuf"]
+    assert r["done"] == 1
+    tr = TC.test_trajectory(1.0, 10)
+    b = po.TrajectoryBuffer(TC.K_NUM_JOINTS)
+    assert b.insert_segment(*tr) == 0
+    b.discard_before_sec(0.5 * (tr[0][5] + tr[0][6]))
+    t, p, _, _ = b.rows()
+    assert np.array_equal(np.array(r["discard_between_times"]), t)
+    assert np.array_equal(np.array(r["discard_between_first_position"]), p[0])
+    quad = TC.quadratic_test_trajectory(1001, 1e-3)
+    s = po.TrajectoryBuffer(TC.K_NUM_JOINTS)
+    assert s.insert_segment(*quad) == 0
+    assert s.stop_at_index(500, np.full(TC.K_NUM_JOINTS, 5.0), 1e-3) == 0
+    t, _, v, _ = s.rows()
+    assert r["stop_num_samples"] == s.num_samples
+    assert np.array_equal(np.array(r["stop_times"]), t)
+    assert np.array_equal(np.array(r["stop_velocities"]).reshape(-1, TC.K_NUM_JOINTS), v)
+    h = po.TrajectoryBuffer(TC.K_NUM_JOINTS)
+    assert h.insert_segment(*quad) == 0
+    assert h.stop_before_time(0.5 * (quad[0][500] + quad[0][501]), np.full(TC.K_NUM_JOINTS, 5.0), 1e-3) == 0
+    assert r["stop_halfway_num_samples"] == h.num_samples

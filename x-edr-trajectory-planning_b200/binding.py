@@ -180,6 +180,8 @@ def lib():
         L.tpb_tbuf_sync.argtypes = [vp]
         L.tpb_tbuf_kernel_launches.restype = i64
         L.tpb_tbuf_kernel_launches.argtypes = [vp]
+        L.tpb_tbuf_reserve.restype = i32
+        L.tpb_tbuf_reserve.argtypes = [vp, i32]
         L.tpb_tbuf_clear.restype = i32
         L.tpb_tbuf_clear.argtypes = [vp, vp, i32]
         L.tpb_tbuf_insert_segments.restype = i32
@@ -668,6 +670,10 @@ class TrajectoryBufferBatch:
     @property
     def kernel_launches(self):
         return lib().tpb_tbuf_kernel_launches(self._h)
+
+    def reserve(self, capacity_rows):
+        self._ck(lib().tpb_tbuf_reserve(self._h, int(capacity_rows)))
+        self.cap = max(self.cap, int(capacity_rows))
 
     def clear(self, select=None):
         if select is not None and not hasattr(select, "data_ptr"):

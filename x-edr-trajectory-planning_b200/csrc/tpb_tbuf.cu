@@ -534,6 +534,20 @@ k_tbuf_stop_commit(TbufDev d, const int32_t* __restrict__ pending,
   block_copy(d.a + (w + keep) * D, s_a + (o + sw) * D, static_cast<long>(m) * D);
 }
 
+// Reserve: every buffer's rows to slot 0 of arrays with `new_cap` slots per buffer.
+__global__ void __launch_bounds__(kInsertThreads)
+k_tbuf_relocate(TbufDev d, int new_cap, double* __restrict__ nt, double* __restrict__ np_,
+                double* __restrict__ nv, double* __restrict__ na) {
+  const int b = blockIdx.x, D = d.D;
+  const int n = d.count[b];
+  const size_t src = static_cast<size_t>(b) * d.cap + d.head[b];
+  const size_t dst = static_cast<size_t>(b) * new_cap;
+  block_copy(nt + dst, d.t + src, n);
+  block_copy(np_ + dst * D, d.p + src * D, static_cast<long>(n) * D);
+  block_copy(nv + dst * D, d.v + src * D, static_cast<long>(n) * D);
+  block_copy(na + dst * D, d.a + src * D, static_cast<long>(n) * D);
+}
+
 TbufDev dev_of(const tpb_tbuf* t) {
   return TbufDev{t->B, t->D, t->cap, t->tol, t->t, t->p, t->v, t->a, t->head, t->count, t->seq};
 }
@@ -610,7 +624,10 @@ int32_t stop_common(tpb_tbuf* t, const int32_t* index, const double* time_sec,
     cudaError_t e = dev_alloc(&t->s_t, R);
     if (e == cudaSuccess) e = dev_alloc(&t->s_v, R * D);
     if (e == cudaSuccess) e = dev_alloc(&t->s_a, R * D);
-    if (e == cudaSuccess) e = dev_alloc(&t->s_begin, B);
+    if (e != cudaSuccess) return fail(t, TPB_INTERNAL, std::string("stop scratch: ") + cudaGetErrorString(e));
+  }
+  if (t->s_begin == nullptr) {
+    cudaError_t e = dev_alloc(&t->s_begin, B);
     if (e == cudaSuccess) e = dev_alloc(&t->s_len, B);
     if (e == cudaSuccess) e = dev_alloc(&t->s_idx, B);
     if (e == cudaSuccess) e = dev_alloc(&t->s_pending, B);
@@ -729,6 +746,42 @@ int32_t tpb_tbuf_sync(tpb_tbuf* t) {
 }
 
 int64_t tpb_tbuf_kernel_launches(const tpb_tbuf* t) { return t ? t->launches : 0; }
+
+int32_t tpb_tbuf_reserve(tpb_tbuf* t, int32_t capacity_rows) {
+  if (t == nullptr || capacity_rows < 2) return TPB_INVALID_ARGUMENT;
+  if (capacity_rows <= t->cap) return TPB_OK;
+  cudaSetDevice(t->device);
+  const size_t B = t->B, D = t->D, R = B * static_cast<size_t>(capacity_rows);
+  double *nt = nullptr, *np_ = nullptr, *nv = nullptr, *na = nullptr;
+  cudaError_t e = dev_alloc(&nt, R);
+  if (e == cudaSuccess) e = dev_alloc(&np_, R * D);
+  if (e == cudaSuccess) e = dev_alloc(&nv, R * D);
+  if (e == cudaSuccess) e = dev_alloc(&na, R * D);
+  if (e == cudaSuccess) {
+    k_tbuf_relocate<<<t->B, kInsertThreads, 0, t->stream>>>(dev_of(t), capacity_rows, nt, np_, nv,
+                                                            na);
+    t->launches += 1;
+    e = cudaMemsetAsync(t->head, 0, B * sizeof(int32_t), t->stream);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+  if (e != cudaSuccess) {
+    for (void* q : {static_cast<void*>(nt), static_cast<void*>(np_), static_cast<void*>(nv),
+                    static_cast<void*>(na)})
+      if (q != nullptr) cudaFree(q);
+    return fail(t, TPB_INTERNAL, std::string("tpb_tbuf_reserve: ") + cudaGetErrorString(e));
+  }
+  for (void* q : {static_cast<void*>(t->t), static_cast<void*>(t->p), static_cast<void*>(t->v),
+                  static_cast<void*>(t->a), static_cast<void*>(t->s_t), static_cast<void*>(t->s_v),
+                  static_cast<void*>(t->s_a)})
+    if (q != nullptr) cudaFree(q);
+  t->t = nt;
+  t->p = np_;
+  t->v = nv;
+  t->a = na;
+  t->s_t = t->s_v = t->s_a = nullptr;  // stop scratch follows the capacity
+  t->cap = capacity_rows;
+  return TPB_OK;
+}
 
 int32_t tpb_tbuf_clear(tpb_tbuf* t, const int32_t* select, int32_t on_device) {
   if (t == nullptr) return TPB_INVALID_ARGUMENT;

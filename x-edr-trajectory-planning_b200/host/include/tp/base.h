@@ -59,9 +59,11 @@ class StatusOr {
  public:
   StatusOr(const Status& s) : status_(s) { assert(!s.ok()); }  // NOLINT
   StatusOr(const T& v) : value_(v) {}                          // NOLINT
+  StatusOr(T&& v) : value_(std::move(v)) {}                    // NOLINT
   bool ok() const { return status_.ok(); }
   const Status& status() const { return status_; }
   const T& operator*() const { return value_; }
+  T& operator*() { return value_; }
   const T* operator->() const { return &value_; }
   const T& value() const { return value_; }
 
