@@ -344,6 +344,10 @@ def run_ours(args):
     stop = run_stop_leg(pkg, torch, dev, stream, eng, d_amax, B, D, max_over_ranks, barrier,
                         world, args)
 
+    # ---- trajectory buffers fed from the resident resampled batch ----
+    tbuf = run_tbuf_leg(pkg, torch, dev, stream, local_rank, eng, d_amax, B, D, peak,
+                        max_over_ranks, barrier, world, args)
+
     # ---- e2e: host buffers in and out through tpb_plan_joint_host ----
     h_wp = torch.from_numpy(wp).pin_memory()
     h_vmax = torch.from_numpy(vmax).pin_memory()
@@ -436,6 +440,7 @@ def run_ours(args):
             "mean_duration_s": float(np.nanmean(all_dur)),
             "e2e_matches_device_run": same, "spline_eval": spline,
             "cartesian": cartesian, "stop": stop, "planner": planner,
+            "trajectory_buffer": tbuf,
         }
         print(json.dumps(line))
     eng.close()
@@ -510,12 +515,111 @@ def run_planner_leg(pkg, torch, dev, stream, local_rank, d_wp, d_vmax, d_amax, B
 
 class _DevPtr:
     """A raw device address with the data_ptr() the binding expects."""
+    is_cuda = True
 
-    def __init__(self, ptr):
+    def __init__(self, ptr, shape=None):
         self._p = ptr
+        self.shape = shape
 
     def data_ptr(self):
         return self._p
+
+
+def run_tbuf_leg(pkg, torch, dev, stream, local_rank, eng, d_amax, B, D, peak, max_over_ranks,
+                 barrier, world, args):
+    """Device-resident TrajectoryBuffers as the consumer of the timed batch: (1) every
+    resampled trajectory (the engine's packed TPB_ARR_R_* arrays) is inserted into its own
+    buffer without leaving HBM, (2) every buffer is sampled (position, velocity,
+    acceleration) at 2,048 times spread over its span, (3) every buffer is stopped before
+    60 % of its span (StopBeforeTime).  CUDA events on the launching stream."""
+    if args.no_tbuf:
+        return None
+    off = eng.get(pkg.ARR.R_OFFSET).astype(np.int64)
+    r_t = eng.get(pkg.ARR.R_TIME)
+    rows = int(off[-1])
+    counts = (off[1:] - off[:-1]).astype(np.int32)
+    cap = int(counts.max()) + 64
+    batch = pkg.TrajectoryBufferBatch(B, D, cap, device=local_rank)
+    batch.set_stream(stream.cuda_stream)
+    dp = lambda what, shape: _DevPtr(eng.devptr(what)[0], shape)
+    seg = (dp(pkg.ARR.R_OFFSET, (B + 1,)), torch.from_numpy(counts).to(dev),
+           dp(pkg.ARR.R_TIME, (rows,)), dp(pkg.ARR.R_POS, (rows, D)), dp(pkg.ARR.R_VEL, (rows, D)),
+           dp(pkg.ARR.R_ACC, (rows, D)))
+    st = torch.zeros(B, dtype=torch.int32, device=dev)
+    Q = 2048
+    t0, t1 = r_t[off[:-1]], r_t[off[1:] - 1]
+    tq = t0[:, None] + (t1 - t0)[:, None] * ((np.arange(Q) + 0.5) / Q)[None, :]
+    d_tq = torch.from_numpy(np.ascontiguousarray(tq)).to(dev)
+    outs = tuple(torch.empty((B, Q, D), dtype=torch.float64, device=dev) for _ in range(3))
+    d_qst = torch.zeros((B, Q), dtype=torch.int32, device=dev)
+    d_tstop = torch.from_numpy(t0 + 0.6 * (t1 - t0)).to(dev)
+    d_sst = torch.zeros(B, dtype=torch.int32, device=dev)
+    amax = _DevPtr(d_amax.data_ptr(), (B, D))
+    sel = torch.ones(B, dtype=torch.int32, device=dev)
+
+    def insert():
+        batch.clear(sel)
+        batch.insert_segments(*seg, status=st)
+
+    def sample():
+        batch.sample(d_tq, out=outs + (d_qst,))
+
+    def stop():
+        lib = pkg.lib()
+        rc = lib.tpb_tbuf_stop_before_time(batch._h, d_tstop.data_ptr(), amax.data_ptr(), 0.004,
+                                           d_sst.data_ptr(), 1)
+        assert rc == 0
+
+    def timed(fn, reps, before=None):
+        for _ in range(3):
+            if before:
+                before()
+            fn()
+        torch.cuda.synchronize()
+        barrier()
+        total = 0.0
+        for _ in range(reps):
+            if before:
+                before()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            fn()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            total += e0.elapsed_time(e1)
+        return max_over_ranks(total) / reps
+
+    reps = max(3, args.steps)
+    launches0 = batch.kernel_launches
+    ms_insert = timed(insert, reps)
+    assert (st.cpu().numpy() == 0).all()
+    ms_sample = timed(sample, reps)
+    assert (d_qst.cpu().numpy() == 0).all()
+    ms_stop = timed(stop, reps, before=insert)
+    stop_ok = int((d_sst.cpu().numpy() == 0).sum())
+    launches = batch.kernel_launches - launches0
+    row_bytes = (3 * D + 1) * 8
+    ins_gbs = 2.0 * rows * row_bytes / (ms_insert / 1e3) / 1e9
+    query_bytes = 8 + 2 * 3 * D * 8 + 3 * D * 8 + 4
+    smp_gbs = B * Q * query_bytes / (ms_sample / 1e3) / 1e9
+    batch.close()
+    return {"insert": {"ms": ms_insert, "rows_per_s": world * rows / (ms_insert / 1e3),
+                       "hbm_gbs_per_gpu": ins_gbs, "frac_of_peak": ins_gbs / peak,
+                       "bytes_per_row": f"{row_bytes} read + {row_bytes} written",
+                       "kernel": "k_tbuf_clear + k_tbuf_insert"},
+            "sample": {"ms": ms_sample, "queries_per_s": world * B * Q / (ms_sample / 1e3),
+                       "hbm_gbs_per_gpu": smp_gbs, "frac_of_peak": smp_gbs / peak,
+                       "queries_per_buffer": Q,
+                       "bytes_per_query": f"{query_bytes}: query time 8 + two bracketing rows of "
+                                          f"three arrays {2 * 3 * D * 8} read + {3 * D * 8} "
+                                          "written + status 4",
+                       "kernel": "k_tbuf_sample"},
+            "stop_before_time": {"ms": ms_stop, "buffers_per_s": world * B / (ms_stop / 1e3),
+                                 "ok": stop_ok,
+                                 "kernels": "k_tbuf_stop_prepare + k_rescale_to_stop + "
+                                            "k_tbuf_stop_commit"},
+            "buffers_per_gpu": B, "rows_per_gpu": rows, "capacity_rows": cap,
+            "gpu_launches": int(launches)}
 
 
 def run_stop_leg(pkg, torch, dev, stream, eng, d_amax, B, D, max_over_ranks, barrier, world,
@@ -680,6 +784,7 @@ def main():
     ap.add_argument("--no-cartesian", action="store_true")
     ap.add_argument("--no-stop", action="store_true")
     ap.add_argument("--no-planner", action="store_true")
+    ap.add_argument("--no-tbuf", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -174,7 +174,7 @@ k_tbuf_insert(TbufDev d, const int64_t* __restrict__ begin, const int32_t* __res
               int32_t* __restrict__ status) {
   const int b = blockIdx.x;
   const int n = length[b];
-  __shared__ int sh_keep, sh_head_old, sh_head_new, sh_status, sh_go;
+  __shared__ int sh_keep, sh_head_old, sh_head_new, sh_go;
   if (threadIdx.x == 0) {
     int st = TPB_OK, go = 0, keep = 0, head_old = d.head[b], head_new = head_old;
     if (n >= 0) {
@@ -208,7 +208,6 @@ k_tbuf_insert(TbufDev d, const int64_t* __restrict__ begin, const int32_t* __res
     sh_keep = keep;
     sh_head_old = head_old;
     sh_head_new = head_new;
-    sh_status = st;
     sh_go = go;
   }
   __syncthreads();
@@ -326,35 +325,78 @@ __global__ void k_tbuf_upto(TbufDev d, const double* __restrict__ time_sec,
   num[b] = r;
 }
 
-// Get{Position,Velocity,Acceleration}AtTime (:228-293)
-__global__ void k_tbuf_sample(TbufDev d, int Q, const double* __restrict__ time_sec,
-                              double* __restrict__ out_p, double* __restrict__ out_v,
-                              double* __restrict__ out_a, int32_t* __restrict__ status) {
+// Get{Position,Velocity,Acceleration}AtTime (:228-293).  A warp takes 32 consecutive
+// queries of one buffer: lane l brackets query l by binary search, then the warp walks
+// the 32*D output values of each requested array in order (coalesced writes; the
+// bracket and weight of value e come from lane e / D by shuffle).
+constexpr int kSampleWarps = 8;
+__global__ void __launch_bounds__(kSampleWarps * 32)
+k_tbuf_sample(TbufDev d, int Q, const double* __restrict__ time_sec,
+              double* __restrict__ out_p, double* __restrict__ out_v,
+              double* __restrict__ out_a, int32_t* __restrict__ status) {
   const int D = d.D;
-  const size_t per_buffer = static_cast<size_t>(Q) * D;
   const int b = blockIdx.y;
-  for (size_t e = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < per_buffer;
-       e += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int q = static_cast<int>(e / D), j = static_cast<int>(e - static_cast<size_t>(q) * D);
-    const int n = d.count[b];
-    const size_t base = static_cast<size_t>(b) * d.cap + d.head[b];
-    const double* T = d.t + base;
-    const double x = time_sec[static_cast<size_t>(b) * Q + q];
-    int i0 = 0, i1 = 0;
-    int st = (x == x) ? bracket(T, n, x, &i0, &i1) : TPB_OUT_OF_RANGE;
-    const size_t o = (static_cast<size_t>(b) * Q + q) * D + j;
+  const int lane = threadIdx.x & 31;
+  const int q0 = (blockIdx.x * kSampleWarps + (threadIdx.x >> 5)) * 32;
+  if (q0 >= Q) return;
+  const int nq = min(32, Q - q0);
+  const int n = d.count[b];
+  const size_t base = static_cast<size_t>(b) * d.cap + d.head[b];
+  const double* T = d.t + base;
+  const size_t qrow = static_cast<size_t>(b) * Q + q0;
+  int st = TPB_OUT_OF_RANGE, i0 = 0, i1 = 0;
+  double w = 0.0;
+  if (lane < nq) {
+    const double x = time_sec[qrow + lane];
+    if (x == x) st = bracket(T, n, x, &i0, &i1);
     if (st == TPB_OK) {
       const double x0 = T[i0], x1 = T[i1];
-      const size_t r0 = (base + i0) * D + j, r1 = (base + i1) * D + j;
-      if (out_p != nullptr) out_p[o] = interpolate(x, x0, x1, d.p[r0], d.p[r1]);
-      if (out_v != nullptr) out_v[o] = interpolate(x, x0, x1, d.v[r0], d.v[r1]);
-      if (out_a != nullptr) out_a[o] = interpolate(x, x0, x1, d.a[r0], d.a[r1]);
-    } else {
-      if (out_p != nullptr) out_p[o] = quiet_nan();
-      if (out_v != nullptr) out_v[o] = quiet_nan();
-      if (out_a != nullptr) out_a[o] = quiet_nan();
+      if (x1 == x0) {
+        i1 = i0;  // InterpolateLinear returns y0
+      } else {
+        w = (x - x0) / (x1 - x0);
+      }
     }
-    if (j == 0 && status != nullptr) status[static_cast<size_t>(b) * Q + q] = st;
+    if (status != nullptr) status[qrow + lane] = st;
+  }
+  const int total = nq * D;
+  for (int e0 = 0; e0 < total; e0 += 32) {
+    const int e = e0 + lane;
+    const bool active = e < total;
+    const int qq = active ? e / D : 0;
+    const int j = e - qq * D;
+    const int st_q = __shfl_sync(kFullMask, st, qq);
+    const int i0_q = __shfl_sync(kFullMask, i0, qq);
+    const int i1_q = __shfl_sync(kFullMask, i1, qq);
+    const double w_q = __shfl_sync(kFullMask, w, qq);
+    if (!active) continue;
+    const size_t o = qrow * D + e;
+    const size_t r0 = (base + i0_q) * D + j, r1 = (base + i1_q) * D + j;
+    const bool ok = st_q == TPB_OK, same = i1_q == i0_q;
+    if (out_p != nullptr) {
+      double y = quiet_nan();
+      if (ok) {
+        const double y0 = d.p[r0];
+        y = same ? y0 : y0 + w_q * (d.p[r1] - y0);
+      }
+      out_p[o] = y;
+    }
+    if (out_v != nullptr) {
+      double y = quiet_nan();
+      if (ok) {
+        const double y0 = d.v[r0];
+        y = same ? y0 : y0 + w_q * (d.v[r1] - y0);
+      }
+      out_v[o] = y;
+    }
+    if (out_a != nullptr) {
+      double y = quiet_nan();
+      if (ok) {
+        const double y0 = d.a[r0];
+        y = same ? y0 : y0 + w_q * (d.a[r1] - y0);
+      }
+      out_a[o] = y;
+    }
   }
 }
 
@@ -893,11 +935,9 @@ int32_t tpb_tbuf_sample(tpb_tbuf* t, int32_t queries_per_buffer, const double* t
   double* d_a = s.out(accelerations, B * Q * D);
   int32_t* d_status = s.out(status, B * Q);
   if (s.err == cudaSuccess) {
-    const int threads = 256;
-    const size_t per_buffer = Q * D;
-    const unsigned gx = static_cast<unsigned>(std::min<size_t>((per_buffer + threads - 1) / threads, 1024));
-    k_tbuf_sample<<<dim3(gx, t->B), threads, 0, t->stream>>>(dev_of(t), queries_per_buffer, d_time,
-                                                           d_p, d_v, d_a, d_status);
+    const unsigned gx = static_cast<unsigned>((Q + kSampleWarps * 32 - 1) / (kSampleWarps * 32));
+    k_tbuf_sample<<<dim3(gx, t->B), kSampleWarps * 32, 0, t->stream>>>(
+        dev_of(t), queries_per_buffer, d_time, d_p, d_v, d_a, d_status);
     t->launches += 1;
   }
   return done(t, s, "tpb_tbuf_sample");
