@@ -303,6 +303,14 @@ int32_t tpb_planner_reset(tpb_engine* e, int32_t path_sample_capacity, double ti
                           int32_t skip_method, int32_t max_planning_iterations,
                           double max_initial_velocity_error, const double* initial_velocity,
                           int32_t on_device);
+/* Cartesian paths (tpb_set_cart_waypoints) behind the planner: every window runs
+ * TimeableCartesianSplinePath::SamplePath (targets at the IK indices of the window,
+ * path IK, finite differences; timeable_path_cartesian_spline.cc:464-549) and
+ * ConstraintSetup (:551-595) on the device with the built-in kinematics `model`
+ * (TPB_KIN_FAKE7).  With TPB_KIN_HOST (the default; a user PathIKFunc warm-started
+ * from the previous window) tpb_planner_plan returns kUnimplemented for Cartesian
+ * paths and the caller plans window by window through tpb_cart_*. */
+int32_t tpb_planner_set_kinematics(tpb_engine* e, int32_t model);
 int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
                          int64_t* total_samples);
 /* New waypoints were set (tpb_set_joint_waypoints) on a planner that keeps its plan:

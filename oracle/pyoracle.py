@@ -96,7 +96,10 @@ class _Planner(C.Structure):
         ("planned_to_end", C.c_int), ("target_reached", C.c_int), ("start_time", C.c_int64),
         ("end_time", C.c_int64), ("final_decel_start", C.c_int64), ("path_horizon", C.c_double),
         ("path_start", C.c_double), ("decel_time", C.c_double), ("last_extremal_index", C.c_int),
-        ("loops", C.c_int), ("erased", C.c_int)]
+        ("loops", C.c_int), ("erased", C.c_int), ("cart", C.c_int),
+        ("translation_rounding", C.c_double), ("max_translational_velocity", C.c_double),
+        ("max_rotational_velocity", C.c_double), ("pose_waypoints", c_double_p),
+        ("pose_ctrl", c_double_p)]
 
 
 class _CartCfg(C.Structure):
@@ -497,7 +500,11 @@ class Planner:
 
     def __init__(self, waypoints, vmax, amax, N, delta, dt, rounding=0.2, safety=0.8, skip=False,
                  max_planning_iterations=200, initial_velocity=None,
-                 max_initial_velocity_error=1e-4, P_cap=None, M_cap=200000):
+                 max_initial_velocity_error=1e-4, P_cap=None, M_cap=200000, pose_waypoints=None,
+                 translation_rounding=0.05, max_translational_velocity=0.5,
+                 max_rotational_velocity=0.25):
+        """pose_waypoints [W][7] (tx,ty,tz,qx,qy,qz,qw): a Cartesian path with the reference
+        test's fake kinematics (`waypoints` are then the joint waypoints, 7 dofs)."""
         wp = np.ascontiguousarray(waypoints, np.float64)
         W, D = wp.shape
         P = P_cap or 64 * N
@@ -510,6 +517,14 @@ class Planner:
                 np.zeros(D) if initial_velocity is None else initial_velocity, np.float64).copy())
         self._knots, self._points = np.zeros(cap), np.zeros((cap - 3, D))
         spline = _Spline(2, D, cap, 0, 0, _dp(self._knots), _dp(self._points))
+        cart = {}
+        if pose_waypoints is not None:
+            self._pose_wp = np.ascontiguousarray(pose_waypoints, np.float64)
+            self._pose_ctrl = np.zeros((n, 7))
+            cart = dict(cart=1, translation_rounding=translation_rounding,
+                        max_translational_velocity=max_translational_velocity,
+                        max_rotational_velocity=max_rotational_velocity,
+                        pose_waypoints=_dp(self._pose_wp), pose_ctrl=_dp(self._pose_ctrl))
         self.w = {k: np.full(P, np.nan) for k in ("w_time", "w_s", "w_sd", "w_sdd")}
         self.w.update({k: np.zeros((P, D)) for k in ("w_q", "w_vel", "w_acc")})
         self.r = {k: np.zeros(M_cap) for k in ("r_t", "r_s", "r_sd", "r_sdd")}
@@ -518,7 +533,7 @@ class Planner:
                           skip_method=1 if skip else 0,
                           max_planning_iterations=max_planning_iterations,
                           max_initial_velocity_error=max_initial_velocity_error, P_cap=P,
-                          M_cap=M_cap, spline=spline,
+                          M_cap=M_cap, spline=spline, **cart,
                           **{k: _dp(v) for k, v in self._keep.items()},
                           **{k: _dp(v) for k, v in self.w.items()},
                           **{k: _dp(v) for k, v in self.r.items()})

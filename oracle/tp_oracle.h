@@ -165,6 +165,10 @@ void orc_cart_sample_targets(const double* knots, int num_knots, const double* p
                              const double* joint_ctrl, int dim, int N, double delta,
                              double* pose_targets /* [N+1][7] */,
                              double* joint_targets /* [N+1][dim] */);
+void orc_cart_sample_targets_from(const double* knots, int num_knots, const double* pose_ctrl,
+                                  const double* joint_ctrl, int dim, int N, double delta,
+                                  int start_index, double* pose_targets,
+                                  double* joint_targets);
 void orc_cart_derivatives(const double* pos, int N, int dim, double delta, double* d1,
                           double* d2);
 void orc_cart_constraints(const double* d1, const double* d2, const double* jac, int N,
@@ -294,6 +298,14 @@ typedef struct {
   int last_extremal_index;
   int loops;  /* planning windows computed by the last call */
   int erased; /* the last call found enough planned and only erased (:594-599) */
+  /* Cartesian path with the reference test's fake kinematics (cart != 0; dim 7):
+   * TimeableCartesianSplinePath behind the same planner.  `waypoints` are the joint
+   * waypoints, spline.points the joint control points; rounding is the rotation
+   * rounding. */
+  int cart;
+  double translation_rounding, max_translational_velocity, max_rotational_velocity;
+  const double* pose_waypoints; /* [W][7] (tx,ty,tz,qx,qy,qz,qw) */
+  double* pose_ctrl;            /* [max(4,3W-2)][7] storage */
 } orc_planner;
 int orc_planner_init(orc_planner* p);
 int orc_planner_plan(orc_planner* p, int64_t start_ns, int64_t horizon_ns);

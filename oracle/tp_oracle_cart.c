@@ -331,6 +331,19 @@ int orc_cart_fit(const double* pose_wp, const double* joint_wp, int W, int dim,
 void orc_cart_sample_targets(const double* knots, int num_knots, const double* pose_ctrl,
                              const double* joint_ctrl, int dim, int N, double delta,
                              double* pose_targets, double* joint_targets) {
+  orc_cart_sample_targets_from(knots, num_knots, pose_ctrl, joint_ctrl, dim, N, delta, 0,
+                               pose_targets, joint_targets);
+}
+
+/* The same for a later planning window: IK indices start_index-1 ..
+ * start_index+N-1 with start_index = PathIkIndex(path_start) (:671-678).  The
+ * reference keeps the IK solutions of earlier windows in path_ik_positions_ and
+ * only evaluates the indices it has not seen (:469-483); the targets themselves
+ * depend on the index alone, which is what this returns. */
+void orc_cart_sample_targets_from(const double* knots, int num_knots, const double* pose_ctrl,
+                                  const double* joint_ctrl, int dim, int N, double delta,
+                                  int start_index, double* pose_targets,
+                                  double* joint_targets) {
   const int n = num_knots - 3;
   double* trans = (double*)malloc(sizeof(double) * 3 * (size_t)n);
   double* quats = (double*)malloc(sizeof(double) * 4 * (size_t)n);
@@ -340,7 +353,7 @@ void orc_cart_sample_targets(const double* knots, int num_knots, const double* p
   }
   const double kend = knots[num_knots - 1];
   for (int m = 0; m <= N; ++m) {
-    const int i = m - 1;
+    const int i = start_index + m - 1;
     const double parameter = (i < 0) ? 0.0 : i * delta;
     double* pt = pose_targets + 7 * (size_t)m;
     double* jt = joint_targets + (size_t)dim * m;

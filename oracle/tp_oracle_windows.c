@@ -129,8 +129,14 @@ static int64_t clamp_to_time_step_multiple(const orc_planner* p, int64_t t) {
 int orc_planner_init(orc_planner* p) {
   p->spline.degree = 2;
   p->spline.dim = p->dim;
-  p->num_points =
-      orc_joint_fit(p->waypoints, p->W, p->dim, p->rounding, p->spline.points, p->spline.knots);
+  if (p->cart) { /* FitSplineToWaypoints (timeable_path_cartesian_spline.cc:396-462) */
+    p->num_points = orc_cart_fit(p->pose_waypoints, p->waypoints, p->W, p->dim,
+                                 p->translation_rounding, p->rounding, p->pose_ctrl,
+                                 p->spline.points, p->spline.knots);
+  } else {
+    p->num_points =
+        orc_joint_fit(p->waypoints, p->W, p->dim, p->rounding, p->spline.points, p->spline.knots);
+  }
   p->spline.num_points = p->num_points;
   p->spline.num_knots = p->num_points + 3;
   p->knot_end = p->spline.knots[p->num_points + 2];
@@ -179,10 +185,34 @@ static int compute_timing_profile(orc_planner* p, int64_t start, int64_t target_
   }
   p->path_start = path_start;
   p->path_horizon = path_start + p->delta_used * (N - 1);
-  orc_joint_sample(p->spline.knots, nk, p->spline.points, D, N, path_start, p->delta_used, q, dq,
-                   ddq);
+  const int C = p->cart ? 2 * D + 2 : 2 * D;
+  if (p->cart) {
+    /* TimeableCartesianSplinePath::SamplePath (:464-549) with FakePathIK, whose
+     * solution at an IK index does not depend on the warm start, then
+     * ConstraintSetup (:551-595) with FakeJacobian */
+    const int start_index = (int)round(path_start / p->delta_used); /* PathIkIndex */
+    double* pt = (double*)malloc(sizeof(double) * 7 * (size_t)(N + 1));
+    double* jt = (double*)malloc(sizeof(double) * (size_t)D * (N + 1));
+    double* ik = (double*)malloc(sizeof(double) * (size_t)D * (N + 1));
+    double* jac = (double*)malloc(sizeof(double) * 6 * (size_t)D * N);
+    orc_cart_sample_targets_from(p->spline.knots, nk, p->pose_ctrl, p->spline.points, D, N,
+                                 p->delta_used, start_index, pt, jt);
+    orc_fake_ik(pt, jt, N + 1, ik);
+    memcpy(q, ik + D, sizeof(double) * (size_t)D * N);
+    orc_cart_derivatives(q, N, D, p->delta_used, dq, ddq);
+    for (int i = 0; i < N; ++i) orc_fake_jacobian(q + (size_t)D * i, jac + 6 * (size_t)D * i);
+    orc_cart_constraints(dq, ddq, jac, N, D, p->vmax, p->amax, p->safety,
+                         p->max_translational_velocity, p->max_rotational_velocity, cons);
+    free(pt);
+    free(jt);
+    free(ik);
+    free(jac);
+  } else {
+    orc_joint_sample(p->spline.knots, nk, p->spline.points, D, N, path_start, p->delta_used, q,
+                     dq, ddq);
+    orc_joint_constraints(dq, ddq, N, D, p->vmax, p->amax, p->safety, cons);
+  }
   p->sampled = 1;
-  orc_joint_constraints(dq, ddq, N, D, p->vmax, p->amax, p->safety, cons);
   if (old_state != 1) { /* kNewPath or kModifiedPath (:352-385) */
     double sq = 0.0, dot = 0.0;
     for (int d = 0; d < D; ++d) {
@@ -208,7 +238,7 @@ static int compute_timing_profile(orc_planner* p, int64_t start, int64_t target_
   sol.s = s;
   sol.sd = sd;
   sol.sdd = sdd;
-  const int st = orc_solve(N, 2 * D, cons, path_start, p->path_horizon, sd_start, 0.0, time_start,
+  const int st = orc_solve(N, C, cons, path_start, p->path_horizon, sd_start, 0.0, time_start,
                            max_loops, &sol);
   if (st != ORC_OK) return st;
   p->last_extremal_index = sol.last_extremal_index;
@@ -297,7 +327,7 @@ int orc_planner_plan(orc_planner* p, int64_t start, int64_t horizon) {
     if (start_sec < p->r_t[0]) return ORC_FAIL_START_RANGE;
     if (!(p->r_t[p->M - 1] > start_sec)) return ORC_FAIL_START_END;
   }
-  double* cons = (double*)malloc(sizeof(double) * (size_t)N * 2 * D * 4);
+  double* cons = (double*)malloc(sizeof(double) * (size_t)N * (2 * D + 2) * 4);
   double* q = (double*)malloc(sizeof(double) * (size_t)N * D * 5);
   double* tm = (double*)malloc(sizeof(double) * (size_t)N * 4);
   int st = ORC_OK;

@@ -204,3 +204,90 @@ def test_initial_velocity():
     for b in range(2):
         np.testing.assert_allclose(rows["r_vel"][off[b]], v0[b], atol=1e-9)
     assert np.all(delta > 0)
+
+
+# ---- Cartesian paths behind the planner (device kinematics TPB_KIN_FAKE7) -------------
+def run_cart_replanning(pose_wp, joint_wp, N, delta, dt, skip, horizon, replan, P_cap,
+                        max_calls=600):
+    """Like run_replanning for TimeableCartesianSplinePath with the reference test's fake
+    kinematics on the device.  The device evaluates sin/cos/atan2 of the quaternion
+    spline and of the fake IK with its own libm, so values are compared within the
+    BASELINE tolerances (durations 1e-6 relative, positions 1e-9) and everything
+    discrete (statuses, window counts, spliced sample counts, flags) exactly."""
+    B, W, D = joint_wp.shape
+    vmax, amax = np.full((B, D), 1.0), np.full((B, D), 2.0)
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * 60000, cartesian=True)
+    eng.set_cart_options(0.05, 0.5, 0.25)
+    eng.set_cart_waypoints(pose_wp, joint_wp)
+    eng.set_joint_limits(vmax, amax)
+    eng.set_sampling(np.full(B, delta))
+    eng.planner_reset(P_cap, dt, skip=skip, max_initial_velocity_error=1e-2)
+    with pytest.raises(pkg.TpbError) as ei:  # host kinematics: one window at a time
+        eng.planner_plan(0, horizon)
+    assert ei.value.code == 12
+    eng.planner_set_kinematics(1)
+    planners = [orc.Planner(joint_wp[b], vmax[b], amax[b], N, delta, dt, skip=skip, P_cap=P_cap,
+                            pose_waypoints=pose_wp[b], max_initial_velocity_error=1e-2)
+                for b in range(B)]
+    start, calls, windows = 0, 0, 0
+    done = np.zeros(B, bool)
+    while not done.all():
+        statuses = [pl.plan(start, horizon) for pl in planners]
+        eng.planner_plan(start, horizon)
+        st = device_state(eng)
+        off, rows = device_rows(eng)
+        for b, (pl, ost) in enumerate(zip(planners, statuses)):
+            tag = f"call {calls} path {b}"
+            assert st["status"][b] == ost, tag
+            assert st["len"][b] == pl.len, tag
+            assert st["planned_to_end"][b] == pl.planned_to_end, tag
+            assert st["target_reached"][b] == pl.target_reached, tag
+            assert abs(st["end_time"][b] - pl.end_time) <= max(1e-6 * abs(pl.end_time), 1), tag
+            if ost == orc.ORC_OK:
+                assert st["loops"][b] == pl.loops, tag
+            tr = pl.trajectory()
+            M = off[b + 1] - off[b]
+            assert abs(M - pl.M) <= 1, tag
+            m = min(M, pl.M) - 1
+            if m > 0:
+                sl = slice(off[b], off[b] + m)
+                assert np.max(np.abs(rows["r_t"][sl] - tr["r_t"][:m])) <= 1e-9, tag
+                assert np.max(np.abs(rows["r_pos"][sl] - tr["r_pos"][:m])) <= 1e-9, tag
+                assert np.max(np.abs(rows["r_vel"][sl] - tr["r_vel"][:m])) <= 1e-7, tag
+        windows += int(st["loops"].sum())
+        done |= (st["target_reached"] == 1) | (st["status"] != 0)
+        start += replan
+        calls += 1
+        assert calls < max_calls
+    return eng, planners, dict(calls=calls, windows=windows)
+
+
+@pytest.mark.parametrize("skip", [False, True])
+def test_reference_cartesian_replanning(skip):
+    """The 5-waypoint Cartesian path of path_timing_trajectory_test.cc:695-757: N = 1000,
+    delta 0.005, 4 ms, horizon 750 ms, re-planned every 200 ms until the end."""
+    import test_oracle_windows as TW
+    joint = TW.CART_WAYPOINTS[None]
+    pose = np.stack([TW.fake_fk_pose(q) for q in TW.CART_WAYPOINTS])[None]
+    eng, planners, n = run_cart_replanning(pose, joint, 1000, 0.005, 0.004, skip, 750 * MS,
+                                           200 * MS, 16384)
+    assert n["windows"] >= 3 and planners[0].target_reached
+    off, rows = device_rows(eng)
+    np.testing.assert_allclose(rows["r_pos"][-1], TW.CART_WAYPOINTS[-1], atol=1e-9)
+    np.testing.assert_array_equal(rows["r_vel"][-1], 0.0)
+    assert np.all(np.abs(rows["r_vel"]) <= 1.0 + 1e-9) and np.all(np.abs(rows["r_acc"]) <= 2.0 + 1e-9)
+
+
+def test_batch_of_cartesian_paths():
+    """cfg5-style Cartesian paths re-planned in lockstep over several windows each."""
+    B = 8
+    pose_wp, joint_wp, _, _ = pkg.workloads.cart_paths(B, 5, seed=5300)
+    N = 256
+    knot_end = max(orc.plan_cart_fake(pose_wp[b], joint_wp[b], np.ones(7), np.full(7, 2.0),
+                                      64)["knot_end"] for b in range(B))
+    delta = knot_end / (N - 1) / 2.5
+    eng, planners, n = run_cart_replanning(pose_wp, joint_wp, N, delta, 0.008, False, 1000 * MS,
+                                           400 * MS, 16 * N)
+    assert n["windows"] >= 2 * B
+    assert all(pl.target_reached for pl in planners)

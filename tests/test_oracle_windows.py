@@ -131,3 +131,85 @@ def test_initial_velocity_projection():
     np.testing.assert_allclose(pl.trajectory()["r_vel"][0], v0, atol=1e-9)
     bad = make(False, initial_velocity=np.array([0.05, 0.0, 0.0]))
     assert bad.plan(0, HORIZON) == orc.ORC_FAIL_INITIAL_VELOCITY
+
+
+# ---- Cartesian paths behind the same planner (path_timing_trajectory_test.cc:613-757)
+def fake_fk_pose(q):
+    """FakeFK (_test.cc:548-552): translation q[0:3], rotation ExpSO3(q[3:6])."""
+    out = np.zeros(7)
+    out[:3] = q[:3]
+    quat = np.zeros(4)
+    v = np.ascontiguousarray(q[3:6], np.float64)
+    orc.lib().orc_exp_so3(v.ctypes.data_as(orc.c_double_p), quat.ctypes.data_as(orc.c_double_p))
+    out[3:] = quat
+    return out
+
+
+CART_WAYPOINTS = np.array([[1.0, 0, 0, 0, 0, 0, 0], [0, 1.0, 0, 0, 0, 0, 0], [0, 0, 0, 1.0, 0, 0, 0],
+                           [0, 0, 0, 0, 1.0, 0, 0], [0, 0, 0, 0, 0, 0, 1.0]])  # _test.cc:711-716
+
+
+def make_cart(joint_wp, skip=False, N=1000, delta=0.005, **kw):
+    joint_wp = np.asarray(joint_wp, np.float64)
+    poses = np.stack([fake_fk_pose(q) for q in joint_wp])
+    return orc.Planner(joint_wp, np.full(7, 1.0), np.full(7, 2.0), N, delta, DT, skip=skip,
+                       pose_waypoints=poses, max_initial_velocity_error=1e-2, **kw)
+
+
+@pytest.mark.parametrize("skip", [False, True])
+def test_cartesian_path_replanning(skip):
+    """The 5-waypoint Cartesian path of _test.cc:695-757, Plan() every 200 ms with a
+    750 ms horizon until the trajectory is at its end: several windows are spliced, the
+    limits hold and the motion ends at the last joint waypoint at rest."""
+    pl = make_cart(CART_WAYPOINTS, skip)
+    start, loops, windows = 0, 0, 0
+    while not pl.target_reached:
+        assert pl.plan(start, HORIZON) == orc.ORC_OK
+        tr = pl.trajectory()
+        assert len(tr["r_t"]) > 0 and np.all(np.diff(tr["r_t"]) > 0)
+        assert np.all(np.abs(tr["r_vel"]) <= 1.0 + 1e-9) and np.all(np.abs(tr["r_acc"]) <= 2.0 + 1e-9)
+        windows += pl.loops
+        start = min(pl.end_time, start + REPLAN)
+        loops += 1
+        assert loops < 2000
+    assert windows >= 3 and pl.len > N
+    np.testing.assert_allclose(tr["r_pos"][-1], CART_WAYPOINTS[-1], atol=1e-9)
+    np.testing.assert_array_equal(tr["r_vel"][-1], 0.0)
+    ps = pl.path_samples()
+    assert np.all(np.diff(ps["w_s"]) > 0)
+    # Cartesian speed limits (0.5 m/s, 0.25 rad/s through the fake Jacobian's linear part)
+    assert np.all(np.linalg.norm(ps["w_vel"][:, :3], axis=1) <= 0.5 + 1e-6)
+
+
+@pytest.mark.parametrize("skip", [False, True])
+def test_zero_length_cartesian_path(skip):
+    """SimpleCartesianPath (_test.cc:613-693): two identical waypoints give one sample at
+    the waypoint, at rest."""
+    wp = np.array([[1.0, 0, 0, 0, 0, 0, 0], [1.0, 0, 0, 0, 0, 0, 0]])
+    pl = make_cart(wp, skip)
+    start, loops = 0, 0
+    while not pl.target_reached:
+        assert pl.plan(start, HORIZON) == orc.ORC_OK
+        start = min(pl.end_time, start + REPLAN)
+        loops += 1
+        assert loops < 50
+    tr = pl.trajectory()
+    assert len(tr["r_pos"]) == 1 and len(tr["r_vel"]) == 1
+    np.testing.assert_allclose(tr["r_pos"][0], wp[0], atol=1e-12)
+    np.testing.assert_array_equal(tr["r_vel"][0], 0.0)
+
+
+def test_cartesian_single_window_equals_the_fresh_path_plan():
+    """A window that covers the whole path is the one-window plan of tp_oracle_cart.c
+    (pinned to the reference's golden vectors in tests/test_oracle_cart.py)."""
+    joint = CART_WAYPOINTS
+    poses = np.stack([fake_fk_pose(q) for q in joint])
+    N = 400
+    one = orc.plan_cart_fake(poses, joint, np.full(7, 1.0), np.full(7, 2.0), N, dt=DT, M_cap=20000)
+    assert one["ok"]
+    pl = make_cart(joint, N=N, delta=-1.0)
+    assert pl.plan(0, 60_000 * MS) == orc.ORC_OK
+    assert pl.loops == 1 and pl.len == N and pl.target_reached
+    ps, tr = pl.path_samples(), pl.trajectory()
+    assert ps["w_time"].tobytes() == one["time"].tobytes() and ps["w_q"].tobytes() == one["q"].tobytes()
+    assert tr["r_pos"].tobytes() == one["r_pos"].tobytes() and tr["r_t"].tobytes() == one["r_t"].tobytes()

@@ -159,6 +159,8 @@ def lib():
         L.tpb_planner_new_path.argtypes = [vp, vp, i32]
         L.tpb_planner_set_initial_velocity.restype = i32
         L.tpb_planner_set_initial_velocity.argtypes = [vp, vp, i32]
+        L.tpb_planner_set_kinematics.restype = i32
+        L.tpb_planner_set_kinematics.argtypes = [vp, i32]
         L.tpb_planner_plan.restype = i32
         L.tpb_planner_plan.argtypes = [vp, C.c_int64, C.c_int64, C.POINTER(C.c_int64)]
         L.tpb_path_stop_parameter.restype = i32
@@ -437,6 +439,9 @@ class Engine:
         v0 = _f64(initial_velocity)
         p, dev = _ptr(v0)
         self._ck(lib().tpb_planner_set_initial_velocity(self._h, p, dev))
+
+    def planner_set_kinematics(self, model=1):
+        self._ck(lib().tpb_planner_set_kinematics(self._h, int(model)))
 
     def planner_plan(self, start_ns, horizon_ns, want_total=True):
         """tpb_planner_plan: PathTimingTrajectory::Plan(start, horizon) for every path

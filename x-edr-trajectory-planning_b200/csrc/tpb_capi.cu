@@ -52,6 +52,7 @@ struct tpb_engine {
   tpb::PlannerOptions wopt;
   std::vector<void*> w_big;  // the P_cap-sized arrays (reallocated when the capacity grows)
   bool planner_ready = false;
+  int planner_kinematics = TPB_KIN_HOST;  // device kinematics of Cartesian planner windows
   int32_t* any_active_host = nullptr;  // pinned
   // tpb_switch_to_waypoint_path staging: [Bmax] / [Bmax][Wmax][D]
   double *sw_keep = nullptr, *sw_wp = nullptr;
@@ -918,7 +919,7 @@ int32_t tpb_planner_reset(tpb_engine* e, int32_t path_sample_capacity, double ti
                           int32_t on_device) {
   if (e == nullptr) return TPB_INVALID_ARGUMENT;
   auto& d = e->dims;
-  if (e->mode != Mode::kJoint || !e->have_waypoints)
+  if ((e->mode != Mode::kJoint && e->mode != Mode::kCartesian) || !e->have_waypoints)
     return fail(e, TPB_FAILED_PRECONDITION, "No path set");
   if (d.r_cap <= 0) return fail(e, TPB_FAILED_PRECONDITION, "max_time_samples_total is 0");
   if (!(time_step_sec > 0)) return fail(e, TPB_INVALID_ARGUMENT, "time step must be positive");
@@ -1008,13 +1009,32 @@ int32_t tpb_planner_set_initial_velocity(tpb_engine* e, const double* initial_ve
   return TPB_OK;
 }
 
+int32_t tpb_planner_set_kinematics(tpb_engine* e, int32_t model) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  if (model != TPB_KIN_HOST && model != TPB_KIN_FAKE7)
+    return fail(e, TPB_INVALID_ARGUMENT, "unknown kinematics model");
+  e->planner_kinematics = model;
+  return TPB_OK;
+}
+
 int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
                          int64_t* total_samples) {
   if (e == nullptr) return TPB_INVALID_ARGUMENT;
   auto& d = e->dims;
-  if (e->mode != Mode::kJoint || !e->have_waypoints)
+  if ((e->mode != Mode::kJoint && e->mode != Mode::kCartesian) || !e->have_waypoints)
     return fail(e, TPB_FAILED_PRECONDITION, "No path set.");
   if (!e->have_limits) return fail(e, TPB_FAILED_PRECONDITION, "joint limits not set");
+  const bool cart = e->mode == Mode::kCartesian;
+  if (cart) {
+    // windows beyond the first need IK solutions the device can produce itself; with
+    // a host PathIKFunc the caller plans window by window (tpb_cart_*)
+    if (e->planner_kinematics != TPB_KIN_FAKE7 || d.D != 7)
+      return fail(e, TPB_UNIMPLEMENTED,
+                  "moving-horizon planning of Cartesian paths needs built-in device kinematics "
+                  "(tpb_planner_set_kinematics)");
+    if (!(e->max_trans_vel > 0) || !(e->max_rot_vel > 0))
+      return fail(e, TPB_FAILED_PRECONDITION, "Cartesian velocity limits not set");
+  }
   if (!e->planner_ready)
     return fail(e, TPB_FAILED_PRECONDITION, "tpb_planner_reset was not called for these paths");
   cudaSetDevice(e->device);
@@ -1039,10 +1059,18 @@ int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
     if (window > o.max_planning_iterations + 1)
       return fail(e, TPB_INTERNAL, "planning loop did not terminate");
     e->launches += tpb::launch_window_begin(d, e->a, w, start_ns, horizon_ns, e->stream);
-    e->launches += tpb::launch_joint_sample_limit(d, am, e->safety, e->stream);
+    if (cart) {  // SamplePath (targets, path IK, finite differences) + ConstraintSetup
+      e->launches += tpb::launch_cart_sample_targets(d, am, e->stream);
+      e->launches += tpb::launch_cart_ik_builtin(d, am, e->planner_kinematics, e->stream);
+      e->launches += tpb::launch_cart_constraints(d, am, e->safety, e->max_trans_vel,
+                                                  e->max_rot_vel, e->planner_kinematics, false,
+                                                  e->stream);
+      e->launches += tpb::launch_generic_limit(d, am, e->stream);
+    } else {
+      e->launches += tpb::launch_joint_sample_limit(d, am, e->safety, e->stream);
+    }
     e->launches += tpb::launch_window_velocity(d, e->a, w, o, e->stream);
-    e->launches += tpb::launch_integrate(d, am, Mode::kJoint, e->safety, max_solver_loops,
-                                         e->stream);
+    e->launches += tpb::launch_integrate(d, am, e->mode, e->safety, max_solver_loops, e->stream);
     TPB_CUDA(e, cudaMemsetAsync(w.any_active, 0, sizeof(int32_t), e->stream));
     e->launches += tpb::launch_window_append(d, e->a, w, o, start_ns, horizon_ns, e->stream);
     TPB_CUDA(e, read_flag(&more));

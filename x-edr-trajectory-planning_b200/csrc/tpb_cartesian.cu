@@ -313,11 +313,15 @@ __global__ void k_cart_fit(Dims dm, DeviceArrays a, double rotation_rounding,
 
 constexpr int kCartThreads = 128;
 
-// IK index i = m - 1 for m in [0, N]: parameter 0 is evaluated twice (:478-482)
+// IK index i = PathIkIndex(path_start) + m - 1 for m in [0, N] (:469-483, 671-678);
+// for a fresh path parameter 0 is evaluated twice (:478-482).  The reference keeps the
+// IK solutions of earlier windows and evaluates only the indices it has not seen; the
+// targets depend on the index alone.
 __global__ void __launch_bounds__(kCartThreads)
 k_cart_sample_targets(Dims dm, DeviceArrays a) {
   extern __shared__ double smem[];
   const int b = blockIdx.y;
+  if (a.active != nullptr && a.active[b] == 0) return;  // uniform per CTA
   const int D = dm.D;
   const int n = a.num_points[b];
   const int nk = n + 3;
@@ -335,8 +339,9 @@ k_cart_sample_targets(Dims dm, DeviceArrays a) {
   __syncthreads();
   const int m = blockIdx.x * blockDim.x + threadIdx.x;
   if (m > dm.N) return;
-  const int i = m - 1;
   const double delta = a.delta[b];
+  const int start_index = static_cast<int>(round(a.path_start[b] / delta));  // PathIkIndex
+  const int i = start_index + m - 1;
   const double parameter = (i < 0) ? 0.0 : i * delta;
   const double kend = s_knots[nk - 1];
   double* pt = a.pose_targets + (static_cast<size_t>(b) * (dm.N + 1) + m) * 7;
@@ -427,6 +432,7 @@ __device__ __forceinline__ void log_so3_derivative(const Quat& q, double* out) {
 // FakePathIK: path position i = IK of target i + 1 (new_ik_path[1:], :512-513)
 __global__ void k_cart_ik_fake7(Dims dm, DeviceArrays a) {
   const int b = blockIdx.y;
+  if (a.active != nullptr && a.active[b] == 0) return;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= dm.N) return;
   const double* pt = a.pose_targets + (static_cast<size_t>(b) * (dm.N + 1) + i + 1) * 7;
@@ -445,6 +451,7 @@ __global__ void __launch_bounds__(kCartThreads)
 k_cart_constraints(Dims dm, DeviceArrays a, double safety, double max_trans_vel,
                    double max_rot_vel) {
   const int b = blockIdx.y;
+  if (a.active != nullptr && a.active[b] == 0) return;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int N = dm.N, D = dm.D, C = dm.C;
   if (idx >= N) return;
@@ -518,9 +525,10 @@ k_cart_constraints(Dims dm, DeviceArrays a, double safety, double max_trans_vel,
   c[(2 * D + 1) * 4 + 2] = -vr2;
   c[(2 * D + 1) * 4 + 3] = vr2;
   if (idx == 0) {
-    // SetupProblem: s in [path_start, path_start + delta (N-1)], path_start = 0
-    a.s_start[b] = 0.0;
-    a.s_end[b] = 0.0 + delta * (N - 1);
+    // SetupProblem: s in [parameter_start_, parameter_end_] (:546-547)
+    const double path_start = a.path_start[b];
+    a.s_start[b] = path_start;
+    a.s_end[b] = path_start + delta * (N - 1);
   }
 }
 

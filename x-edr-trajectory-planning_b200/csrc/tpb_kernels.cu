@@ -269,6 +269,7 @@ k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
 __global__ void __launch_bounds__(kSampleThreads)
 k_generic_limit(Dims dm, DeviceArrays a) {
   const int b = blockIdx.y;
+  if (a.active != nullptr && a.active[b] == 0) return;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= dm.N) return;
   const int C = dm.C;
