@@ -524,6 +524,55 @@ int main() {
       PrintArray("constraints_sample10", rows, false);
       printf("}%s\n", mode == 0 ? "," : "");
     }
+    // the reference's 5-waypoint Cartesian scenario (path_timing_trajectory_test.cc:695-757):
+    // default delta 0.005, Plan() every 200 ms with a 750 ms horizon until the end; with
+    // device kinematics every window is sampled and timed on the device
+    {
+      constexpr size_t kSamples = 1000;
+      CartesianPathOptions opt;
+      opt.set_num_dofs(kFakeDofs).set_num_path_samples(kSamples).set_device_kinematics(TPB_KIN_FAKE7);
+      auto cpath = std::make_shared<TimeableCartesianSplinePath>(opt);
+      PathTimingTrajectory planner(PathTimingTrajectoryOptions()
+                                       .SetTimeStep(tp::Milliseconds(4))
+                                       .SetNumDofs(kFakeDofs)
+                                       .SetNumPathSamples(kSamples));
+      EXPECT(planner.SetPath(cpath).ok());
+      const std::vector<VectorXd> joints = {VectorXd{1.0, 0, 0, 0, 0, 0, 0}, VectorXd{0, 1.0, 0, 0, 0, 0, 0},
+                                            VectorXd{0, 0, 0, 1.0, 0, 0, 0}, VectorXd{0, 0, 0, 0, 1.0, 0, 0},
+                                            VectorXd{0, 0, 0, 0, 0, 0, 1.0}};
+      std::vector<tp::Pose3d> poses;
+      for (const auto& j : joints) poses.push_back(FakeFK(j));
+      EXPECT(cpath->SetWaypoints(poses, joints).ok());
+      VectorXd vmax = VectorXd::Constant(kFakeDofs, 1.0), amax = VectorXd::Constant(kFakeDofs, 2.0);
+      EXPECT(cpath->SetMaxJointVelocity(ToSpan(vmax)).ok());
+      EXPECT(cpath->SetMaxJointAcceleration(ToSpan(amax)).ok());
+      EXPECT(cpath->SetMaxCartesianVelocity(0.5, 0.25).ok());
+      tp::Time start_time = TimeFromSec(0.0);
+      int loops = 0, windows = 0;
+      std::vector<double> end_times;
+      for (; !planner.IsTrajectoryAtEnd() && loops < 2000; ++loops) {
+        const tp::Status st = planner.Plan(start_time, tp::Milliseconds(750));
+        EXPECT(st.ok());
+        if (!st.ok()) {
+          fprintf(stderr, "Cartesian re-planning loop %d: %s\n", loops, st.message().c_str());
+          break;
+        }
+        EXPECT(planner.GetVelocities().size() == planner.GetPositions().size());
+        windows += planner.LastPlanWindows();
+        end_times.push_back(TimeToSec(planner.GetEndTime()));
+        const tp::Time next = start_time + tp::Milliseconds(200);
+        start_time = planner.GetEndTime() < next ? planner.GetEndTime() : next;
+      }
+      EXPECT(planner.IsTrajectoryAtEnd() && windows >= 3);
+      EXPECT(cpath->GetState() == TimeablePath::State::kPathWasSampled);
+      EXPECT(cpath->GetConstraints().size() == kSamples);
+      printf(",\"replanning\": {\n\"loops\": %d, \"windows\": %d,\n", loops, windows);
+      PrintArray("end_times", end_times);
+      PrintArray("time", planner.GetTime());
+      PrintArray("positions", Flatten(planner.GetPositions()));
+      PrintArray("velocities", Flatten(planner.GetVelocities()), false);
+      printf("}\n");
+    }
     std::vector<double> jflat, pflat;
     for (size_t w = 0; w < jw.size(); ++w) {
       jflat.insert(jflat.end(), jw[w].begin(), jw[w].end());

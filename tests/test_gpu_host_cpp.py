@@ -275,3 +275,30 @@ def test_trajectory_buffer_matches_oracle(result, po):
     assert h.insert_segment(*quad) == 0
     assert h.stop_before_time(0.5 * (quad[0][500] + quad[0][501]), np.full(TC.K_NUM_JOINTS, 5.0), 1e-3) == 0
     assert r["stop_halfway_num_samples"] == h.num_samples
+
+
+def test_cartesian_replanning_matches_oracle(result, po):
+    """The reference's 5-waypoint Cartesian re-planning scenario
+    (path_timing_trajectory_test.cc:695-757) through the host classes with device
+    kinematics (all windows on the device), against the oracle planner's loop."""
+    import test_oracle_windows as TW
+    r = result["cartesian"]["replanning"]
+    pl = TW.make_cart(TW.CART_WAYPOINTS)
+    start, loops, windows, end_times = 0, 0, 0, []
+    while not pl.target_reached:
+        assert pl.plan(start, TW.HORIZON) == po.ORC_OK
+        windows += pl.loops
+        end_times.append(pl.end_time / 1e9)
+        start = min(pl.end_time, start + TW.REPLAN)
+        loops += 1
+    assert r["loops"] == loops and r["windows"] == windows
+    assert np.max(np.abs(np.array(r["end_times"]) - np.array(end_times))) <= 0.004 + 1e-9
+    tr = pl.trajectory()
+    t = np.array(r["time"])
+    pos = np.array(r["positions"]).reshape(-1, 7)
+    vel = np.array(r["velocities"]).reshape(-1, 7)
+    assert abs(len(t) - len(tr["r_t"])) <= 1
+    m = min(len(t), len(tr["r_t"])) - 1
+    assert np.max(np.abs(pos[:m] - tr["r_pos"][:m])) <= 1e-9
+    assert np.max(np.abs(vel[:m] - tr["r_vel"][:m])) <= 1e-6
+    assert np.max(np.abs(pos[-1] - TW.CART_WAYPOINTS[-1])) <= 1e-9 and (vel[-1] == 0).all()

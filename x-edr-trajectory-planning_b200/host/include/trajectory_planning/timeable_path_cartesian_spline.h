@@ -266,8 +266,13 @@ class TimeableCartesianSplinePath : public TimeablePath {
       rc = tpb_cart_setup_constraints(e_, TPB_KIN_HOST, jac.data(), 0);
     }
     if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+    return DownloadConstraints();
+  }
+  // host copy of the rows of the window the engine holds
+  tp::Status DownloadConstraints() {
+    const size_t N = options_.num_path_samples();
     std::vector<double> cons(N * num_constraints_ * 4);
-    rc = tpb_get(e_, TPB_ARR_CONS, cons.data(), cons.size() * sizeof(double), 0);
+    const int32_t rc = tpb_get(e_, TPB_ARR_CONS, cons.data(), cons.size() * sizeof(double), 0);
     if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
     constraints_.resize(N);
     for (size_t idx = 0; idx < N; ++idx) {
@@ -284,6 +289,51 @@ class TimeableCartesianSplinePath : public TimeablePath {
     return tp::OkStatus();
   }
   const std::vector<TimeOptimalPathProfile::Constraint>& GetConstraints() const override { return constraints_; }
+
+  // Device planner hooks (timeable_path.h).  With built-in device kinematics the IK
+  // solution at an IK index does not depend on a warm start from the previous window,
+  // so PathTimingTrajectory plans all windows on the device (tpb_planner_plan); with
+  // host callbacks it plans one window at a time through SamplePath / ConstraintSetup.
+  bool SupportsDevicePlanner() const override { return options_.device_kinematics() != TPB_KIN_HOST; }
+  tp::Status BeforeDevicePlan() override {
+    if (!e_ || joint_waypoints_.empty()) return tp::FailedPreconditionError("No path set");
+    int32_t rc = tpb_set_joint_limits(e_, max_joint_velocity_.data(), max_joint_acceleration_.data(), 0, 0);
+    if (rc == TPB_OK) {
+      if (max_translational_velocity_ <= 0 || max_rotational_velocity_ <= 0) {
+        return tp::FailedPreconditionError("Cartesian velocity limits not set");
+      }
+      rc = tpb_set_cart_options(e_, options_.translation_rounding(), max_translational_velocity_,
+                                max_rotational_velocity_);
+    }
+    if (rc == TPB_OK) rc = tpb_planner_set_kinematics(e_, options_.device_kinematics());
+    return rc == TPB_OK ? tp::OkStatus() : tp::FromCode(rc, tpb_last_error(e_));
+  }
+  tp::Status AfterDevicePlan(bool window_was_sampled) override {
+    if (!window_was_sampled) return tp::OkStatus();
+    // the last window's samples, as SamplePath would have left them (.cc:527-547)
+    const size_t N = options_.num_path_samples(), D = options_.num_dofs();
+    std::vector<double> buf(N * D);
+    tp::VectorXd* dst[3] = {path_position_.data(), first_path_derivative_.data(), second_path_derivative_.data()};
+    const tpb_array what[3] = {TPB_ARR_Q, TPB_ARR_DQ, TPB_ARR_DDQ};
+    for (int k = 0; k < 3; ++k) {
+      const int32_t rc = tpb_get(e_, what[k], buf.data(), buf.size() * sizeof(double), 0);
+      if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+      for (size_t i = 0; i < N; ++i) dst[k][i] = tp::VectorXd(&buf[i * D], D);
+    }
+    std::vector<double> s(N);
+    const int32_t rc = tpb_get(e_, TPB_ARR_S, s.data(), N * sizeof(double), 0);
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+    parameter_start_ = s[0];
+    parameter_end_ = s[0] + options_.delta_parameter() * (N - 1);
+    // path_ik_positions_ up to the window's horizon index; entries of windows that were
+    // planned and spliced inside the same Plan() call stay on the device (TPB_ARR_W_Q)
+    const size_t first = static_cast<size_t>(std::max(0, PathIkIndex(parameter_start_)));
+    if (path_ik_positions_.size() < first) path_ik_positions_.resize(first, path_position_.front());
+    path_ik_positions_.resize(first + N);
+    std::copy(path_position_.begin(), path_position_.end(), path_ik_positions_.begin() + first);
+    path_state_ = State::kPathWasSampled;
+    return DownloadConstraints();
+  }
   size_t NumConstraints() const override { return num_constraints_; }
   size_t NumDofs() const override { return options_.num_dofs(); }
   size_t NumPathSamples() const override { return options_.num_path_samples(); }
