@@ -373,6 +373,16 @@ typedef struct {
   int64_t r_total;       /* out: rows written */
 } tpb_plan_io;
 int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io);
+/* The same hot path for the batch already resident on the device (after
+ * tpb_set_joint_waypoints / tpb_set_joint_limits): SamplePath + ConstraintSetup +
+ * OptimizePathParameter + (time_step_sec > 0) ResampleTrajectory from start_sec for
+ * fresh paths, i.e. tpb_sample_paths(0) + tpb_optimize + tpb_resample, with the same
+ * results.  num_chunks > 1 cuts the batch into that many chunks whose stages overlap
+ * (sampling on the engine's stream, the latency-bound timing on high-priority
+ * streams of its own, resampling on a third); the call is asynchronous on the
+ * engine's stream (which waits for the others) unless total_samples is given. */
+int32_t tpb_plan_joint_device(tpb_engine* e, double start_sec, double time_step_sec,
+                              int32_t num_chunks, int64_t* total_samples);
 
 /* ---- results ------------------------------------------------------------- */
 /* Copy array `what` (current batch) to dst (host or device); bytes must be at

@@ -216,6 +216,25 @@ def test_limit_curve_bitwise_cfg2_shape(pkg, po):
             assert np.array_equal(res[k][b], o[ok], equal_nan=True), (b, k)
 
 
+def test_plan_joint_device_matches_staged_calls(pkg):
+    """tpb_plan_joint_device (one call for the resident batch; one chunk, or several
+    chunks on overlapping streams) returns exactly what sample_paths + optimize +
+    resample return."""
+    B, W, D, N = 700, 5, 7, 256
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=12)
+    res = _run_engine(pkg, wp, vmax, amax, N)
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * 16384)
+    eng.set_joint_waypoints(wp)
+    eng.set_joint_limits(vmax, amax)
+    for chunks in (1, 3, 1, 5):
+        total = eng.plan_joint_device(0.0, 0.004, chunks)
+        assert total == res["total"]
+        for k in ("DURATION", "STATUS", "R_OFFSET", "R_POS", "R_VEL", "R_ACC", "R_S", "TIME", "SD"):
+            np.testing.assert_array_equal(eng.get(getattr(pkg.ARR, k)), res[k], err_msg=f"{chunks} {k}")
+    eng.close()
+
+
 def test_plan_joint_host_chunked_pipeline_matches_staged_calls(pkg):
     """Batches of >= 1024 paths go through tpb_plan_joint_host in chunks whose
     device-to-host copies overlap the next chunk's kernels; every output must be

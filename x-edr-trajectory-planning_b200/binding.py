@@ -139,6 +139,8 @@ def lib():
         L.tpb_optimize.argtypes = [vp, vp, vp, vp, i32, i32]
         L.tpb_resample.restype = i32
         L.tpb_resample.argtypes = [vp, f64, f64, C.POINTER(i64)]
+        L.tpb_plan_joint_device.restype = i32
+        L.tpb_plan_joint_device.argtypes = [vp, f64, f64, i32, C.POINTER(i64)]
         L.tpb_plan_joint_host.restype = i32
         L.tpb_plan_joint_host.argtypes = [vp, C.POINTER(_PlanIO)]
         L.tpb_get.restype = i32
@@ -449,6 +451,13 @@ class Engine:
         total = C.c_int64(0)
         self._ck(lib().tpb_planner_plan(self._h, int(start_ns), int(horizon_ns),
                                         C.byref(total) if want_total else None))
+        return total.value
+
+    def plan_joint_device(self, start_sec=0.0, time_step_sec=0.0, num_chunks=1, want_total=True):
+        """tpb_plan_joint_device: the whole hot path for the resident batch."""
+        total = C.c_int64(0)
+        self._ck(lib().tpb_plan_joint_device(self._h, start_sec, time_step_sec, int(num_chunks),
+                                             C.byref(total) if want_total else None))
         return total.value
 
     def plan_joint_host(self, waypoints, vmax, amax, start_sec=0.0, time_step_sec=0.0,

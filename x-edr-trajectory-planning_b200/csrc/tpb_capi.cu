@@ -38,7 +38,14 @@ struct tpb_engine {
   std::vector<void*> allocs;
   // tpb_plan_joint_host pipeline: device-to-host copies of finished chunks run on
   // their own stream while later chunks are computed
+  static constexpr int kMaxChunksDecl = 16;
   cudaStream_t copy_stream = nullptr;
+  // tpb_plan_joint_device: resampling stream, one high-priority stream per chunk for
+  // the integrate stage, events between the stages
+  cudaStream_t aux_stream = nullptr;
+  cudaStream_t integ_stream[kMaxChunksDecl] = {};
+  cudaEvent_t join_event = nullptr;
+  cudaEvent_t chunk_sampled[kMaxChunksDecl] = {}, chunk_timed[kMaxChunksDecl] = {};
   static constexpr int kMaxChunks = 16;
   cudaEvent_t chunk_done[kMaxChunks] = {};
   cudaEvent_t phase_ev[4] = {};  // tpb_time_phases
@@ -332,6 +339,20 @@ int32_t tpb_destroy(tpb_engine* e) {
   for (void* p : e->w_big) cudaFree(p);
   for (void* p : e->spline_big) cudaFree(p);
   if (e->any_active_host) cudaFreeHost(e->any_active_host);
+  if (e->aux_stream) {
+    cudaStreamSynchronize(e->aux_stream);
+    cudaStreamDestroy(e->aux_stream);
+  }
+  for (auto& st : e->integ_stream)
+    if (st) {
+      cudaStreamSynchronize(st);
+      cudaStreamDestroy(st);
+    }
+  if (e->join_event) cudaEventDestroy(e->join_event);
+  for (auto& ev : e->chunk_sampled)
+    if (ev) cudaEventDestroy(ev);
+  for (auto& ev : e->chunk_timed)
+    if (ev) cudaEventDestroy(ev);
   if (e->copy_stream) {
     cudaStreamSynchronize(e->copy_stream);
     cudaStreamDestroy(e->copy_stream);
@@ -713,6 +734,92 @@ static int32_t resample_impl(tpb_engine* e, double start_sec, double time_step_s
   e->resampled = true;
   e->planner_ready = false;  // the trajectory rows are no longer the planner's
   if (total_samples != nullptr) {
+    int64_t total = 0;
+    TPB_CUDA(e, cudaMemcpyAsync(&total, e->a.r_offset + d.B, sizeof(int64_t),
+                                cudaMemcpyDeviceToHost, e->stream));
+    TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+    *total_samples = total;
+    if (total > d.r_cap)
+      return fail(e, TPB_OUT_OF_RANGE, "resampled rows exceed max_time_samples_total");
+  }
+  return TPB_OK;
+}
+
+// The whole hot path for the resident batch, software-pipelined.  The sweeps of the
+// integrate stage are latency-bound: a path's switching loop takes about as long alone
+// as with 4,096 others, so they are worth starting early and hiding behind work that
+// is bound by something else.  The batch is cut into chunks; chunk c is sampled on the
+// engine's stream (one chunk after the other, each fills the GPU), integrated on its
+// own HIGH-PRIORITY stream (its CTAs take the slots the next chunk's sampling CTAs
+// free) and resampled on a third stream in chunk order (the continued offset scan).
+int32_t tpb_plan_joint_device(tpb_engine* e, double start_sec, double time_step_sec,
+                              int32_t num_chunks, int64_t* total_samples) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (e->mode != Mode::kJoint || !e->have_waypoints)
+    return fail(e, TPB_FAILED_PRECONDITION, "No path set");
+  if (!e->have_limits) return fail(e, TPB_FAILED_PRECONDITION, "joint limits not set");
+  const bool want_rows = time_step_sec > 0;
+  if (want_rows && d.r_cap <= 0)
+    return fail(e, TPB_FAILED_PRECONDITION, "max_time_samples_total is 0");
+  cudaSetDevice(e->device);
+  int nchunks = std::max(1, std::min<int>(num_chunks, tpb_engine::kMaxChunks));
+  nchunks = std::min(nchunks, std::max(1, d.B / 64));
+  TPB_CUDA(e, cudaMemsetAsync(e->a.path_start, 0, sizeof(double) * d.B, e->stream));
+  TPB_CUDA(e, cudaMemsetAsync(e->a.sd_start, 0, sizeof(double) * d.B, e->stream));
+  TPB_CUDA(e, cudaMemsetAsync(e->a.sdd_start, 0, sizeof(double) * d.B, e->stream));
+  e->launches += tpb::launch_fill_f64(e->a.time_start, start_sec, d.B, e->stream);
+  const int max_loops = std::max(100, 10 * d.N);
+  if (nchunks == 1) {
+    e->launches += tpb::launch_joint_sample_limit(d, e->a, e->safety, e->stream);
+    e->launches += tpb::launch_integrate(d, e->a, e->mode, e->safety, max_loops, e->stream);
+    if (want_rows)
+      e->launches += tpb::launch_resample(d, e->a, start_sec, time_step_sec, e->num_sms,
+                                          e->stream, false);
+  } else {
+    int lo_prio = 0, hi_prio = 0;
+    TPB_CUDA(e, cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
+    for (int c = 0; c < nchunks; ++c) {
+      if (e->integ_stream[c] == nullptr)
+        TPB_CUDA(e, cudaStreamCreateWithPriority(&e->integ_stream[c], cudaStreamNonBlocking,
+                                                 hi_prio));
+      if (e->chunk_sampled[c] == nullptr)
+        TPB_CUDA(e, cudaEventCreateWithFlags(&e->chunk_sampled[c], cudaEventDisableTiming));
+      if (e->chunk_timed[c] == nullptr)
+        TPB_CUDA(e, cudaEventCreateWithFlags(&e->chunk_timed[c], cudaEventDisableTiming));
+    }
+    if (e->aux_stream == nullptr)
+      TPB_CUDA(e, cudaStreamCreateWithFlags(&e->aux_stream, cudaStreamNonBlocking));
+    if (e->join_event == nullptr)
+      TPB_CUDA(e, cudaEventCreateWithFlags(&e->join_event, cudaEventDisableTiming));
+    for (int c = 0; c < nchunks; ++c) {
+      const int b0 = static_cast<int>(static_cast<int64_t>(d.B) * c / nchunks);
+      const int b1 = static_cast<int>(static_cast<int64_t>(d.B) * (c + 1) / nchunks);
+      tpb::Dims dc = d;
+      dc.B = b1 - b0;
+      const tpb::DeviceArrays ac = tpb::shifted_joint(e->a, d, b0);
+      e->launches += tpb::launch_joint_sample_limit(dc, ac, e->safety, e->stream);
+      TPB_CUDA(e, cudaEventRecord(e->chunk_sampled[c], e->stream));
+      TPB_CUDA(e, cudaStreamWaitEvent(e->integ_stream[c], e->chunk_sampled[c], 0));
+      e->launches += tpb::launch_integrate(dc, ac, e->mode, e->safety, max_loops,
+                                           e->integ_stream[c]);
+      TPB_CUDA(e, cudaEventRecord(e->chunk_timed[c], e->integ_stream[c]));
+      cudaStream_t last = want_rows ? e->aux_stream : e->stream;
+      TPB_CUDA(e, cudaStreamWaitEvent(last, e->chunk_timed[c], 0));
+      if (want_rows)
+        e->launches += tpb::launch_resample(dc, ac, start_sec, time_step_sec, e->num_sms,
+                                            e->aux_stream, /*continued=*/c > 0);
+    }
+    if (want_rows) {
+      TPB_CUDA(e, cudaEventRecord(e->join_event, e->aux_stream));
+      TPB_CUDA(e, cudaStreamWaitEvent(e->stream, e->join_event, 0));
+    }
+  }
+  TPB_CUDA(e, cudaGetLastError());
+  e->sampled = e->optimized = true;
+  e->resampled = want_rows;
+  e->planner_ready = false;
+  if (want_rows && total_samples != nullptr) {
     int64_t total = 0;
     TPB_CUDA(e, cudaMemcpyAsync(&total, e->a.r_offset + d.B, sizeof(int64_t),
                                 cudaMemcpyDeviceToHost, e->stream));
