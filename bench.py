@@ -53,6 +53,29 @@ def _traffic(kernel):
         return None
 
 
+def _fp64_report(pkg, device, kernel_ms):
+    """Achieved FP64 FLOP/s of the compute-bound kernels: thread-level
+    dadd + dmul + 2 dfma per launch from the committed ncu capture
+    (profiles/fp64_ops.json; the workload is deterministic) over the kernel's live
+    CUDA-event time, against the FP64 FMA rate measured on this device now."""
+    p = os.path.join(ROOT, "profiles", "fp64_ops.json")
+    try:
+        with open(p) as f:
+            ops = json.load(f)
+    except (OSError, ValueError):
+        return None
+    peak = pkg.measure_fp64_fma_peak(device)
+    out = {"peak_tflops": peak, "peak_source": "tpb_measure_fp64_fma_peak (8 FMA chains/thread)",
+           "ops_source": "profiles/fp64_ops.json (ncu --set full, same workload)", "kernels": {}}
+    for k, ms in kernel_ms.items():
+        if k in ops and ms > 0:
+            tf = ops[k]["flops_per_launch"] / (ms / 1e3) / 1e12
+            out["kernels"][k] = {"flops_per_launch": ops[k]["flops_per_launch"], "ms": ms,
+                                 "tflops": tf, "frac_of_fma_peak": tf / peak,
+                                 "fp64_pipe_pct_ncu": ops[k]["fp64_pipe_pct"]}
+    return out
+
+
 def _peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -339,6 +362,10 @@ def run_ours(args):
     if split:
         stage_ms["integrate_phases"] = {"setup": phase_ms[0], "sweeps": phase_ms[1],
                                         "finalize": phase_ms[2]}
+    fp64 = _fp64_report(pkg, local_rank, {"k_joint_sample_limit": stage_ms["sample_limit"],
+                                           "k_integrate_setup": phase_ms[0],
+                                           "k_optimize_pair": phase_ms[1],
+                                           "k_integrate_finalize": phase_ms[2]} if split else {})
 
     # ---- stopping trajectories on the resident resampled batch ----
     stop = run_stop_leg(pkg, torch, dev, stream, eng, d_amax, B, D, max_over_ranks, barrier,
@@ -439,7 +466,7 @@ def run_ours(args):
             "stage_ms": stage_ms, "paths_ok": n_ok, "resampled_rows_per_gpu": total_rows,
             "mean_duration_s": float(np.nanmean(all_dur)),
             "e2e_matches_device_run": same, "spline_eval": spline,
-            "cartesian": cartesian, "stop": stop, "planner": planner,
+            "fp64": fp64, "cartesian": cartesian, "stop": stop, "planner": planner,
             "trajectory_buffer": tbuf,
         }
         print(json.dumps(line))

@@ -419,6 +419,11 @@ int32_t tpb_spline_eval_device(const tpb_spline_eval_desc* d, void* cuda_stream)
 /* Same with host pointers (allocates, copies in, evaluates, copies out). */
 int32_t tpb_spline_eval_host(const tpb_spline_eval_desc* d, int32_t device);
 
+/* Diagnostics: the FP64 FMA rate of `device` in TFLOP/s (2 flops per FMA), measured
+ * with eight independent FMA chains per thread -- the denominator bench.py reports the
+ * limit-curve and phase-plane kernels' FP64 FLOP/s against. */
+int32_t tpb_measure_fp64_fma_peak(int32_t device, double* tflops);
+
 /* ---- stop queries ----------------------------------------- */
 /* Batched PathTimingTrajectory::GetPathStopParameter (path_timing_trajectory.cc:
  * 235-287) with ComputeFastestStop (:75-172) on the engine's resampled

@@ -139,6 +139,8 @@ def lib():
         L.tpb_optimize.argtypes = [vp, vp, vp, vp, i32, i32]
         L.tpb_resample.restype = i32
         L.tpb_resample.argtypes = [vp, f64, f64, C.POINTER(i64)]
+        L.tpb_measure_fp64_fma_peak.restype = i32
+        L.tpb_measure_fp64_fma_peak.argtypes = [i32, C.POINTER(f64)]
         L.tpb_plan_joint_device.restype = i32
         L.tpb_plan_joint_device.argtypes = [vp, f64, f64, i32, C.POINTER(i64)]
         L.tpb_plan_joint_host.restype = i32
@@ -615,6 +617,15 @@ def rescale_to_stop_device(max_acceleration, begin, length, times, velocities, a
     rc = lib().tpb_rescale_to_stop_device(C.byref(d), stream)
     if rc != 0:
         raise TpbError(rc, "tpb_rescale_to_stop_device")
+
+
+def measure_fp64_fma_peak(device=0):
+    """FP64 FMA rate of the device in TFLOP/s (tpb_measure_fp64_fma_peak)."""
+    out = C.c_double(0.0)
+    rc = lib().tpb_measure_fp64_fma_peak(int(device), C.byref(out))
+    if rc != 0:
+        raise TpbError(rc, "tpb_measure_fp64_fma_peak")
+    return out.value
 
 
 # ------------------------------------------------------------------ trajectory buffers
