@@ -154,6 +154,50 @@ def test_builtin_kinematics_pipeline(pkg, po):
     assert n_ok >= B // 2
 
 
+def _limit_curve_run(pkg, pw, jw, vm, am, jac_from=None):
+    B, W = pw.shape[0], pw.shape[1]
+    eng = _engine(pkg, B, W)
+    eng.set_cart_options(0.05, 0.5, 0.25)
+    eng.set_cart_waypoints(pw, jw)
+    eng.set_joint_limits(vm, am)
+    eng.cart_sample_targets()
+    eng.cart_solve_ik(1)
+    n0 = eng.kernel_launches
+    if jac_from is None:
+        eng.cart_setup_constraints(1)
+    else:
+        q = eng.get(pkg.ARR.Q)
+        jac = np.stack([np.stack([jac_from(q[b, i]) for i in range(0, N)]) for b in range(B)])
+        eng.cart_setup_constraints(model=0, jacobians=jac)
+    launches = eng.kernel_launches - n0
+    eng.optimize()
+    eng.resample(0.0, DT)
+    A = pkg.ARR
+    res = {k: eng.get(getattr(A, k)) for k in
+           ("DQ", "DDQ", "CONS", "B_SD2_MAX", "B_SDD_MAX", "B_SDD_MIN", "B_SD2_ZERO", "B_TYPE",
+            "TIME", "SD", "STATUS", "DURATION", "R_OFFSET", "R_POS", "R_VEL", "R_ACC")}
+    eng.close()
+    return res, launches
+
+
+@pytest.mark.parametrize("uploaded_jacobians", [False, True])
+def test_fused_rows_and_limit_curve_equal_the_two_kernel_path(pkg, po, monkeypatch, uploaded_jacobians):
+    """k_cart_constraints_limit (rows + LP on the registers that built them) against
+    k_cart_constraints followed by k_generic_limit reading the stored rows: every
+    array bit for bit, on paths that include failing ones."""
+    B, W = (6, 5) if uploaded_jacobians else (48, 5)
+    pw, jw, vm, am = pkg.workloads.cart_paths(B, W, seed=5300)
+    jf = po.fake_jacobian if uploaded_jacobians else None
+    monkeypatch.delenv("TPB_CART_UNFUSED", raising=False)
+    fused, n_fused = _limit_curve_run(pkg, pw, jw, vm, am, jf)
+    monkeypatch.setenv("TPB_CART_UNFUSED", "1")
+    plain, n_plain = _limit_curve_run(pkg, pw, jw, vm, am, jf)
+    assert (n_fused, n_plain) == (1, 2)
+    assert (fused["STATUS"] == 0).sum() >= B // 2
+    for k in fused:
+        assert fused[k].tobytes() == plain[k].tobytes(), k
+
+
 def test_cart_argument_errors(pkg):
     eng = _engine(pkg, 2, 3, cap=100)
     with pytest.raises(pkg.TpbError) as ei:

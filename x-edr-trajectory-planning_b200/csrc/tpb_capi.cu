@@ -630,8 +630,7 @@ int32_t tpb_cart_setup_constraints(tpb_engine* e, int32_t model, const double* j
   const int n = tpb::launch_cart_constraints(d, e->a, e->safety, e->max_trans_vel, e->max_rot_vel,
                                              model, jacobians != nullptr, e->stream);
   if (n < 0) return fail(e, TPB_INVALID_ARGUMENT, "unknown kinematics model for this dof count");
-  e->launches += n;
-  e->launches += tpb::launch_generic_limit(d, e->a, e->stream);
+  e->launches += n;  // rows and the per-sample limit curve
   TPB_CUDA(e, cudaGetLastError());
   e->sampled = true;
   e->optimized = e->resampled = false;
@@ -1171,8 +1170,7 @@ int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
       e->launches += tpb::launch_cart_ik_builtin(d, am, e->planner_kinematics, e->stream);
       e->launches += tpb::launch_cart_constraints(d, am, e->safety, e->max_trans_vel,
                                                   e->max_rot_vel, e->planner_kinematics, false,
-                                                  e->stream);
-      e->launches += tpb::launch_generic_limit(d, am, e->stream);
+                                                  e->stream);  // + limit curve
     } else {
       e->launches += tpb::launch_joint_sample_limit(d, am, e->safety, e->stream);
     }

@@ -20,8 +20,11 @@
 // warm-start semantics: the host layer downloads the targets, runs the user's
 // callbacks and uploads joint positions / Jacobians (tpb_cart_set_ik_positions,
 // tpb_cart_setup_constraints); everything else stays on the device.
+#include <cstdlib>
+
 #include "tpb_engine.h"
 #include "tpb_fit.cuh"
+#include "tpb_joint_limit.cuh"
 
 namespace tpb {
 namespace {
@@ -532,6 +535,125 @@ k_cart_constraints(Dims dm, DeviceArrays a, double safety, double max_trans_vel,
   }
 }
 
+// k_cart_constraints + the per-sample limit curve in one pass for kD <= 7 dofs
+// (2*kD + 2 <= 16 rows): the rows are still written for the sweeps, which read
+// them per sample, but the LP and FindSddMin/Max run on the registers that built
+// them (JointLimit<kD, 2>, bit-identical to lp_max_sd2 / find_sdd_min_max on the
+// stored rows), so k_generic_limit's second pass over `cons` disappears.
+template <bool kFake7, int kD>
+__global__ void __launch_bounds__(kCartThreads)
+k_cart_constraints_limit(Dims dm, DeviceArrays a, double safety, double max_trans_vel,
+                         double max_rot_vel) {
+  __shared__ double s_aS[kD], s_vS2[kD];
+  const int b = blockIdx.y;
+  if (a.active != nullptr && a.active[b] == 0) return;  // uniform per CTA
+  if (threadIdx.x < kD) {
+    const double am = a.amax[static_cast<size_t>(b) * kD + threadIdx.x];
+    const double vm = a.vmax[static_cast<size_t>(b) * kD + threadIdx.x];
+    s_aS[threadIdx.x] = am * safety;
+    const double vs = vm * safety;
+    s_vS2[threadIdx.x] = vs * vs;
+  }
+  __syncthreads();
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int N = dm.N;
+  constexpr int C = 2 * kD + 2;
+  if (idx >= N) return;
+  const size_t row = (static_cast<size_t>(b) * N + idx) * kD;
+  const double delta = a.delta[b];
+  const double inv = 1.0 / delta;
+  const double vt2 = max_trans_vel * max_trans_vel;
+  const double vr2 = max_rot_vel * max_rot_vel;
+  const double hx[2] = {vt2, vr2};
+  JointLimit<kD, 2> J;
+  J.aS = s_aS;
+  J.vS2 = s_vS2;
+  J.hX = hx;
+  double p0[kD];
+  {
+    const double* __restrict__ q = a.q + row;
+    const bool has1 = idx < N - 1, has2 = idx + 1 < N - 1;
+#pragma unroll
+    for (int d = 0; d < kD; ++d) {
+      p0[d] = q[d];
+      double f1 = 0.0, f2 = 0.0;
+      if (has1) {
+        const double p1 = q[kD + d];
+        f1 = inv * (p1 - p0[d]);
+        if (idx >= 1) {
+          // first derivative of the next sample (0 at the last one)
+          double g1 = 0.0;
+          if (has2) g1 = inv * (q[2 * kD + d] - p1);
+          f2 = inv * (g1 - f1);
+        }
+      }
+      J.A[d] = f1;
+      J.B[d] = f2;
+      a.dq[row + d] = f1;
+      a.ddq[row + d] = f2;
+    }
+  }
+  double v[6];
+  if (kFake7) {
+    static_assert(!kFake7 || kD == 7, "the fake robot has 7 joints");
+    double dl[12];
+    log_so3_derivative(exp_so3(p0 + 3), dl);
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      // full row sums like the dense product jacobian * q' (zeros included)
+      double s = 0.0;
+#pragma unroll
+      for (int d = 0; d < kD; ++d) s += ((d == r) ? 1.0 : 0.0) * J.A[d];
+      v[r] = s;
+      double t = 0.0;
+#pragma unroll
+      for (int d = 0; d < kD; ++d) t += ((d >= 3) ? dl[r * 4 + (d >= 3 ? d - 3 : 0)] : 0.0) * J.A[d];
+      v[3 + r] = t;
+    }
+  } else {
+    const double* __restrict__ Jm = a.jac + (static_cast<size_t>(b) * N + idx) * 6 * kD;
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      double s = 0.0;
+#pragma unroll
+      for (int d = 0; d < kD; ++d) s += Jm[r * kD + d] * J.A[d];
+      v[r] = s;
+    }
+  }
+  J.Bv[kD] = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
+  J.Bv[kD + 1] = v[3] * v[3] + v[4] * v[4] + v[5] * v[5];
+  J.prepare();
+  // rows for the sweeps: one 32-byte row = two 16-byte stores
+  double2* c = reinterpret_cast<double2*>(a.cons + (static_cast<size_t>(b) * N + idx) * C * 4);
+#pragma unroll
+  for (int d = 0; d < kD; ++d) {
+    c[d * 2 + 0] = make_double2(J.A[d], J.B[d]);
+    c[d * 2 + 1] = make_double2(-s_aS[d], s_aS[d]);
+    c[(kD + d) * 2 + 0] = make_double2(0.0, J.Bv[d]);
+    c[(kD + d) * 2 + 1] = make_double2(0.0, s_vS2[d]);
+  }
+  c[(2 * kD) * 2 + 0] = make_double2(0.0, J.Bv[kD]);
+  c[(2 * kD) * 2 + 1] = make_double2(-vt2, vt2);
+  c[(2 * kD + 1) * 2 + 0] = make_double2(0.0, J.Bv[kD + 1]);
+  c[(2 * kD + 1) * 2 + 1] = make_double2(-vr2, vr2);
+  // CalculateBoundary's per-sample part (time_optimal_path_timing.cc:1366-1377)
+  double sd2max, sddmax, sd2zero, smax, smin;
+  J.lp(sd2max, sddmax, sd2zero);
+  J.sdd_min_max(sd2max, smax, smin);
+  const size_t o = static_cast<size_t>(b) * N + idx;
+  a.b_raw_sd2_max[o] = sd2max;
+  a.b_sd2_zero[o] = sd2zero;
+  a.b_raw_sdd_max[o] = smax;
+  a.b_raw_sdd_min[o] = smin;
+  a.b_at0[o] = fabs(sd2max - sd2zero) < kTiny;
+  if (idx == 0) {
+    // SetupProblem: s in [parameter_start_, parameter_end_] (:546-547)
+    const double path_start = a.path_start[b];
+    a.s_start[b] = path_start;
+    a.s_end[b] = path_start + delta * (N - 1);
+  }
+}
+
 }  // namespace
 
 int launch_cart_fit(const Dims& d, const DeviceArrays& a, double rotation_rounding,
@@ -560,17 +682,33 @@ int launch_cart_ik_builtin(const Dims& d, const DeviceArrays& a, int model, cuda
   return 1;
 }
 
+// Rows + per-sample limit curve: one fused launch for 6- and 7-dof arms, else
+// k_cart_constraints followed by k_generic_limit.  TPB_CART_UNFUSED=1 forces the
+// two-kernel path (used by the parity tests to compare the two).
 int launch_cart_constraints(const Dims& d, const DeviceArrays& a, double safety,
                             double max_trans_vel, double max_rot_vel, int model, bool have_jac,
                             cudaStream_t st) {
   dim3 grid((d.N + kCartThreads - 1) / kCartThreads, d.B);
+  if (!have_jac && (model != TPB_KIN_FAKE7 || d.D != 7)) return -1;
+  const char* env = std::getenv("TPB_CART_UNFUSED");
+  const bool fused = !(env != nullptr && env[0] == '1') && d.C == 2 * d.D + 2;
+  if (fused && d.D == 7) {
+    if (have_jac)
+      k_cart_constraints_limit<false, 7><<<grid, kCartThreads, 0, st>>>(d, a, safety, max_trans_vel, max_rot_vel);
+    else
+      k_cart_constraints_limit<true, 7><<<grid, kCartThreads, 0, st>>>(d, a, safety, max_trans_vel, max_rot_vel);
+    return 1;
+  }
+  if (fused && d.D == 6 && have_jac) {
+    k_cart_constraints_limit<false, 6><<<grid, kCartThreads, 0, st>>>(d, a, safety, max_trans_vel, max_rot_vel);
+    return 1;
+  }
   if (have_jac) {
     k_cart_constraints<false><<<grid, kCartThreads, 0, st>>>(d, a, safety, max_trans_vel, max_rot_vel);
   } else {
-    if (model != TPB_KIN_FAKE7 || d.D != 7) return -1;
     k_cart_constraints<true><<<grid, kCartThreads, 0, st>>>(d, a, safety, max_trans_vel, max_rot_vel);
   }
-  return 1;
+  return 1 + launch_generic_limit(d, a, st);
 }
 
 }  // namespace tpb

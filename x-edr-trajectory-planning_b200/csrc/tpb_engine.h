@@ -291,6 +291,7 @@ int launch_cart_fit(const Dims& d, const DeviceArrays& a, double rotation_roundi
                     double translation_rounding, bool auto_delta, cudaStream_t st);
 int launch_cart_sample_targets(const Dims& d, const DeviceArrays& a, cudaStream_t st);
 int launch_cart_ik_builtin(const Dims& d, const DeviceArrays& a, int model, cudaStream_t st);
+// rows AND the per-sample limit curve (fused for 6/7 dofs, else + k_generic_limit)
 int launch_cart_constraints(const Dims& d, const DeviceArrays& a, double safety,
                             double max_trans_vel, double max_rot_vel, int model, bool have_jac,
                             cudaStream_t st);

@@ -22,6 +22,13 @@
 //  * the common case of exactly one new active row per iteration keeps that row
 //    as scalars; ties (two or more rows within kTiny) take a slow path that
 //    fetches rows with select chains.
+//
+// kX > 0 appends kX more rows of the velocity kind with symmetric bounds,
+//   row 2*kD + k               A = 0      B = Bx_k     -hX_k <= . <= hX_k
+// which is what TimeableCartesianSplinePath::ConstraintSetup adds for the
+// translational and rotational speed (timeable_path_cartesian_spline.cc:551-595):
+// the caller fills Bv[kD + k] and points hX at the kX bounds.  Their lower slots
+// (bound -hX < 0 over B >= 0) can never become active either.
 #pragma once
 
 #include "tpb_device.cuh"
@@ -48,18 +55,25 @@ __device__ __forceinline__ bool lp_is_optimal_e(const LpEntry& e1, const LpEntry
   return x >= 0 && y >= 0;
 }
 
-template <int kD>
+template <int kD, int kX = 0>
 struct JointLimit {
+  static constexpr int kV = kD + kX;  // rows with A == 0
   double A[kD], B[kD];  // q', q'' of this sample
-  double Bv[kD];        // q'^2 (B of the velocity rows)
-  double invBv[kD];     // 1 / q'^2
+  double Bv[kV];        // q'^2 (B of the velocity rows), then the kX extra rows' B
+  double invBv[kV];     // 1 / Bv
   const double* aS;     // [kD] shared memory: amax * safety
   const double* vS2;    // [kD] shared memory: (vmax * safety)^2
+  const double* hX;     // [kX] bounds of the extra rows (unused when kX == 0)
 
-  __device__ __forceinline__ static double sel(const double (&x)[kD], int i) {
+  // bounds of velocity-kind row j (compile-time j in the unrolled loops)
+  __device__ __forceinline__ double vhi(int j) const { return (j < kD) ? vS2[j] : hX[j - kD]; }
+  __device__ __forceinline__ double vlo(int j) const { return (j < kD) ? 0.0 : -hX[j - kD]; }
+
+  template <int kN>
+  __device__ __forceinline__ static double sel(const double (&x)[kN], int i) {
     double r = x[0];
 #pragma unroll
-    for (int k = 1; k < kD; ++k) r = (i == k) ? x[k] : r;
+    for (int k = 1; k < kN; ++k) r = (i == k) ? x[k] : r;
     return r;
   }
 
@@ -76,17 +90,26 @@ struct JointLimit {
       const double s = aS[row];
       e.bound = lower ? -s : s;
     } else {
+      const int j = row - kD;
       e.A = 0.0;
-      e.B = sel(Bv, row - kD);
-      e.bound = lower ? 0.0 : vS2[row - kD];
+      e.B = sel(Bv, j);
+      double hi = vS2[(j < kD) ? j : 0], lo = 0.0;
+#pragma unroll
+      for (int k = 0; k < kX; ++k) {
+        hi = (j == kD + k) ? hX[k] : hi;
+        lo = (j == kD + k) ? -hX[k] : lo;
+      }
+      e.bound = lower ? lo : hi;
     }
     return e;
   }
 
+  // (with kX > 0 the caller sets Bv[kD ..] before this)
   __device__ __forceinline__ void prepare() {
 #pragma unroll
-    for (int d = 0; d < kD; ++d) {
-      Bv[d] = A[d] * A[d];
+    for (int d = 0; d < kD; ++d) Bv[d] = A[d] * A[d];
+#pragma unroll
+    for (int d = 0; d < kV; ++d) {
       // only used where Bv >= kTiny (rows with |Bc| < kTiny are skipped)
       invBv[d] = 1.0 / ((Bv[d] < kTiny) ? 1.0 : Bv[d]);
     }
@@ -94,7 +117,8 @@ struct JointLimit {
 
   // FindMaxSd2Simplex (:1149-1363)
   __device__ void lp(double& sd2max, double& sddmax, double& sd2zero) const {
-    constexpr int C = 2 * kD;
+    constexpr int C = 2 * kD + kX;
+    static_assert(C <= 16, "slot masks are 32 bits");
     unsigned act = 0u;
     double sd2 = DBL_MAX;
     double sdd = 0.0;
@@ -124,9 +148,9 @@ struct JointLimit {
       }
     }
 #pragma unroll
-    for (int d = 0; d < kD; ++d) {
+    for (int d = 0; d < kV; ++d) {
       const double Bi = Bv[d];
-      const double tmp = vS2[d] * invBv[d];
+      const double tmp = vhi(d) * invBv[d];
       if (Bi > kTiny && tmp < (sd2 + kTiny) && tmp > 0) {
         if (tmp < sd2 - kTiny) act = 0u;
         const int slot = 2 * (kD + d);
@@ -134,7 +158,7 @@ struct JointLimit {
         sd2 = tmp;
         last.A = 0.0;
         last.B = Bi;
-        last.bound = vS2[d];
+        last.bound = vhi(d);
         last.type = kUpper;
         last.slot = slot;
       }
@@ -218,13 +242,13 @@ struct JointLimit {
       }
       const double zb = 0.0 * b, za = 0.0 * a;
 #pragma unroll
-      for (int d = 0; d < kD; ++d) {
+      for (int d = 0; d < kV; ++d) {
         const double Bc = zb + Bv[d];
         const bool usable = !(fabs(Bc) < kTiny);
         const int slot = 2 * (kD + d);
         double invB = invBv[d];
         if (!(Bc == Bv[d])) invB = 1.0 / Bc;  // non-finite b only
-        const double tmp = (vS2[d] - za) * invB;
+        const double tmp = (vhi(d) - za) * invB;
         if (usable && ((in_set >> slot) & 1u) && tmp < (next_sd2 + kTiny) && tmp > sd2) {
           if (tmp < next_sd2 - kTiny) act = 0u;
           act |= 1u << slot;
@@ -232,11 +256,11 @@ struct JointLimit {
           next_sdd = a + b * next_sd2;
           last.A = 0.0;
           last.B = Bv[d];
-          last.bound = vS2[d];
+          last.bound = vhi(d);
           last.type = kUpper;
           last.slot = slot;
         }
-        // lower slot: tmp = (0 - za) * invB is +-0 or NaN, never > sd2 > 0
+        // lower slot: tmp = (lo - za) * invB with lo <= 0 is <= 0 or NaN, never > sd2 > 0
       }
       if (act == 0u) {  // unbounded along this edge
         sd2max = sd2zero;
@@ -299,8 +323,11 @@ struct JointLimit {
 #pragma unroll
     for (int d = 0; d < kD; ++d) {
       Bs[d] = B[d] * sd2;
+    }
+#pragma unroll
+    for (int d = 0; d < kV; ++d) {
       const double w = Bv[d] * sd2;
-      vbad = vbad || (w + kTiny < 0.0) || (w - kTiny > vS2[d]);
+      vbad = vbad || (w + kTiny < vlo(d)) || (w - kTiny > vhi(d));
     }
     double mx = -DBL_MAX, mn = DBL_MAX;
 #pragma unroll
