@@ -13,8 +13,8 @@
 //                   reference's upper_bound with `<=` + timestep tolerance), the CTA
 //                   streams the segment's rows in (contiguous on both sides: a pure
 //                   HBM copy of (3D+1)*8 B per row read and written)
-//   k_tbuf_sample   1 thread / (buffer, query, dof): bracket by binary search in the
-//                   buffer's time stamps, linear interpolation, coalesced writes
+//   k_tbuf_sample   1 warp / 32 queries: bracket by a two-level search (pivots of the
+//                   time stamps in shared memory), linear interpolation, coalesced writes
 //   k_tbuf_discard, k_tbuf_append, k_tbuf_upto, k_tbuf_offset, k_tbuf_state,
 //   k_tbuf_clear    1 thread / buffer (or row): bookkeeping
 //   k_tbuf_stop_prepare -> k_rescale_to_stop (tpb_stop.cu, in place on rows
@@ -25,6 +25,7 @@
 // Results are bit-identical to the reference's for everything but
 // eigenmath::InterpolateLinear (un-vendored, see tpb.h); -fmad=false keeps the
 // interpolation un-contracted like the oracle's.
+#include <cstdlib>
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -326,76 +327,120 @@ __global__ void k_tbuf_upto(TbufDev d, const double* __restrict__ time_sec,
 }
 
 // Get{Position,Velocity,Acceleration}AtTime (:228-293).  A warp takes 32 consecutive
-// queries of one buffer: lane l brackets query l by binary search, then the warp walks
-// the 32*D output values of each requested array in order (coalesced writes; the
-// bracket and weight of value e come from lane e / D by shuffle).
-constexpr int kSampleWarps = 8;
-__global__ void __launch_bounds__(kSampleWarps * 32)
+// queries of one buffer: lane l brackets query l, then the warp walks the 32*D output
+// values of each requested array in order (coalesced writes; the bracket and weight of
+// value e come from lane e / D by shuffle).
+//
+// The bracket is c_upper_bound in the buffer's time stamps, which are non-decreasing, so
+// any search finds the same index.  The CTA (all its warps serve the same buffer) first
+// stages every S-th time stamp in shared memory, S the smallest power of two that leaves
+// at most kSamplePivots of them; a query is then located among the pivots without leaving
+// the SM and needs log2(S) dependent global loads instead of log2(n).  The gather keeps
+// the loads of kSampleBatch output values per lane in flight before the first store.
+// (60 % -> 87 % of the measured HBM peak on the bench's 8.4 M queries.)
+constexpr int kSamplePivots = 1024;
+template <int kSampleBatch, int kSampleWarps, int kMinBlocks>
+__global__ void __launch_bounds__(kSampleWarps * 32, kMinBlocks)
 k_tbuf_sample(TbufDev d, int Q, const double* __restrict__ time_sec,
               double* __restrict__ out_p, double* __restrict__ out_v,
               double* __restrict__ out_a, int32_t* __restrict__ status) {
+  __shared__ double s_pivot[kSamplePivots];
   const int D = d.D;
   const int b = blockIdx.y;
   const int lane = threadIdx.x & 31;
   const int q0 = (blockIdx.x * kSampleWarps + (threadIdx.x >> 5)) * 32;
-  if (q0 >= Q) return;
-  const int nq = min(32, Q - q0);
   const int n = d.count[b];
   const size_t base = static_cast<size_t>(b) * d.cap + d.head[b];
-  const double* T = d.t + base;
+  const double* __restrict__ T = d.t + base;
+  int shift = 0;
+  while (((n + (1 << shift) - 1) >> shift) > kSamplePivots) ++shift;
+  const int npiv = (n + (1 << shift) - 1) >> shift;
+  for (int k = threadIdx.x; k < npiv; k += kSampleWarps * 32) s_pivot[k] = T[k << shift];
+  __syncthreads();
+  if (q0 >= Q) return;
+  const int nq = min(32, Q - q0);
   const size_t qrow = static_cast<size_t>(b) * Q + q0;
   int st = TPB_OUT_OF_RANGE, i0 = 0, i1 = 0;
   double w = 0.0;
   if (lane < nq) {
     const double x = time_sec[qrow + lane];
-    if (x == x) st = bracket(T, n, x, &i0, &i1);
-    if (st == TPB_OK) {
-      const double x0 = T[i0], x1 = T[i1];
-      if (x1 == x0) {
-        i1 = i0;  // InterpolateLinear returns y0
-      } else {
-        w = (x - x0) / (x1 - x0);
+    if (x == x) {
+      // GetOffsetBracket (:232-251)
+      if (n == 0) {
+        st = TPB_FAILED_PRECONDITION;
+      } else if (!(x < s_pivot[0] || x > T[n - 1])) {
+        st = TPB_OK;
+        // first pivot above x (pivot 0 is not: x >= T[0]) ...
+        int lo = 1, hi = npiv;
+        while (lo < hi) {
+          const int mid = lo + ((hi - lo) >> 1);
+          if (x < s_pivot[mid]) hi = mid; else lo = mid + 1;
+        }
+        // ... then T[(lo-1) << shift] <= x and the first time stamp above x is in
+        // ((lo-1) << shift, lo << shift] (or n)
+        int glo = ((lo - 1) << shift) + 1, ghi = min(lo << shift, n);
+        while (glo < ghi) {
+          const int mid = glo + ((ghi - glo) >> 1);
+          if (x < T[mid]) ghi = mid; else glo = mid + 1;
+        }
+        const int upper = glo;
+        if (upper == n) {
+          i0 = i1 = n - 1;
+        } else {
+          i0 = upper - 1;
+          i1 = upper;
+        }
+        const double x0 = T[i0], x1 = T[i1];
+        if (x1 == x0) {
+          i1 = i0;  // InterpolateLinear returns y0
+        } else {
+          w = (x - x0) / (x1 - x0);
+        }
       }
     }
     if (status != nullptr) status[qrow + lane] = st;
   }
+  const double* __restrict__ src[3] = {d.p, d.v, d.a};
+  double* __restrict__ dst[3] = {out_p, out_v, out_a};
   const int total = nq * D;
-  for (int e0 = 0; e0 < total; e0 += 32) {
-    const int e = e0 + lane;
-    const bool active = e < total;
-    const int qq = active ? e / D : 0;
-    const int j = e - qq * D;
-    const int st_q = __shfl_sync(kFullMask, st, qq);
-    const int i0_q = __shfl_sync(kFullMask, i0, qq);
-    const int i1_q = __shfl_sync(kFullMask, i1, qq);
-    const double w_q = __shfl_sync(kFullMask, w, qq);
-    if (!active) continue;
-    const size_t o = qrow * D + e;
-    const size_t r0 = (base + i0_q) * D + j, r1 = (base + i1_q) * D + j;
-    const bool ok = st_q == TPB_OK, same = i1_q == i0_q;
-    if (out_p != nullptr) {
-      double y = quiet_nan();
-      if (ok) {
-        const double y0 = d.p[r0];
-        y = same ? y0 : y0 + w_q * (d.p[r1] - y0);
+  for (int e0 = 0; e0 < total; e0 += 32 * kSampleBatch) {
+    double y0[kSampleBatch][3], y1[kSampleBatch][3], wq[kSampleBatch];
+    bool act[kSampleBatch], okq[kSampleBatch], same[kSampleBatch];
+#pragma unroll
+    for (int u = 0; u < kSampleBatch; ++u) {
+      const int e = e0 + 32 * u + lane;
+      const bool active = e < total;
+      const int qq = active ? e / D : 0;
+      const int j = e - qq * D;
+      const int st_q = __shfl_sync(kFullMask, st, qq);
+      const int i0_q = __shfl_sync(kFullMask, i0, qq);
+      const int i1_q = __shfl_sync(kFullMask, i1, qq);
+      wq[u] = __shfl_sync(kFullMask, w, qq);
+      act[u] = active;
+      okq[u] = active && st_q == TPB_OK;
+      same[u] = i1_q == i0_q;
+      const size_t r0 = (base + i0_q) * D + j, r1 = (base + i1_q) * D + j;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        y0[u][k] = quiet_nan();
+        y1[u][k] = quiet_nan();
+        if (okq[u] && dst[k] != nullptr) {
+          y0[u][k] = src[k][r0];
+          y1[u][k] = src[k][r1];  // r1 == r0 when the bracket is one sample
+        }
       }
-      out_p[o] = y;
     }
-    if (out_v != nullptr) {
-      double y = quiet_nan();
-      if (ok) {
-        const double y0 = d.v[r0];
-        y = same ? y0 : y0 + w_q * (d.v[r1] - y0);
+#pragma unroll
+    for (int u = 0; u < kSampleBatch; ++u) {
+      if (!act[u]) continue;
+      const size_t o = qrow * D + e0 + 32 * u + lane;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if (dst[k] == nullptr) continue;
+        const double a0 = y0[u][k], a1 = y1[u][k];
+        // NaN rows for queries outside the buffer; y0 itself for a one-sample bracket
+        dst[k][o] = (okq[u] && !same[u]) ? a0 + wq[u] * (a1 - a0) : a0;
       }
-      out_v[o] = y;
-    }
-    if (out_a != nullptr) {
-      double y = quiet_nan();
-      if (ok) {
-        const double y0 = d.a[r0];
-        y = same ? y0 : y0 + w_q * (d.a[r1] - y0);
-      }
-      out_a[o] = y;
     }
   }
 }
@@ -935,8 +980,12 @@ int32_t tpb_tbuf_sample(tpb_tbuf* t, int32_t queries_per_buffer, const double* t
   double* d_a = s.out(accelerations, B * Q * D);
   int32_t* d_status = s.out(status, B * Q);
   if (s.err == cudaSuccess) {
-    const unsigned gx = static_cast<unsigned>((Q + kSampleWarps * 32 - 1) / (kSampleWarps * 32));
-    k_tbuf_sample<<<dim3(gx, t->B), kSampleWarps * 32, 0, t->stream>>>(
+    // measured on B200 (profiles/r1_summary.md v9): 2 values per lane in flight, 4 warps
+    // per CTA, 8 CTAs/SM (64 registers) -- 0.77 ms for 8.4 M queries; larger batches or
+    // CTAs lose more in occupancy than they gain in loads in flight
+    constexpr int kBatch = 2, kWarps = 4, kMinBlocks = 8;
+    const unsigned gx = static_cast<unsigned>((Q + kWarps * 32 - 1) / (kWarps * 32));
+    k_tbuf_sample<kBatch, kWarps, kMinBlocks><<<dim3(gx, t->B), kWarps * 32, 0, t->stream>>>(
         dev_of(t), queries_per_buffer, d_time, d_p, d_v, d_a, d_status);
     t->launches += 1;
   }
