@@ -314,3 +314,67 @@ def test_resample_skipping_samples_closer_than_time_step_bitwise(pkg, po):
             # samples are at least 0.95 dt apart
             assert np.all(np.diff(o["r_t"]) >= 0.95 * dt - 1e-15)
     eng.close()
+
+
+def test_cfg2_full_size_properties(pkg, po):
+    """BASELINE cfg2 at full size (4,096 paths x 2,048 samples, D = 7, W = 10, the bench's
+    batch): what holds whatever the size -- every path timed, limits kept, trajectories
+    start and end on their waypoints at rest, time and path parameter monotone, the
+    packed layout consistent -- plus independence of the batch: paths taken from all over
+    the batch and run as a small batch of their own give the same bits, and the oracle's."""
+    B, W, D, N, dt = 4096, 10, 7, 2048, 0.004
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=1000)
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * 6144)
+    eng.set_joint_waypoints(wp)
+    eng.set_joint_limits(vmax, amax)
+    eng.sample_paths()
+    eng.optimize()
+    total = eng.resample(0.0, dt)
+    A = pkg.ARR
+    res = {k: eng.get(getattr(A, k)) for k in
+           ("STATUS", "DURATION", "TIME", "S", "SD", "KNOT_END", "R_OFFSET", "R_TIME", "R_POS",
+            "R_VEL", "R_ACC", "R_S")}
+    eng.close()
+    off = res["R_OFFSET"]
+    assert (res["STATUS"] == 0).all()
+    dur = res["DURATION"]
+    assert np.isfinite(dur).all() and (dur > 0).all()
+    assert off[0] == 0 and off[-1] == total and (np.diff(off) >= 2).all()
+    # ResampleEquidistantlyInTime (:755-757): rows 0, dt, 2 dt, ... and the end of the path
+    rows = np.diff(off)
+    assert (np.abs(rows - (np.ceil(dur / dt) + 1)) <= 1).all()
+    assert np.array_equal(res["TIME"][:, 0], np.zeros(B))
+    assert np.array_equal(res["TIME"][:, -1], dur)
+    assert (np.diff(res["TIME"], axis=1) >= 0).all()
+    assert (np.diff(res["S"], axis=1) > 0).all()
+    assert (res["SD"] >= 0).all() and (res["SD"][:, 0] == 0).all() and (res["SD"][:, -1] == 0).all()
+    first, last = off[:-1], off[1:] - 1
+    assert np.array_equal(res["R_TIME"][first], np.zeros(B))
+    assert np.max(np.abs(res["R_POS"][first] - wp[:, 0])) <= TOL_RESAMPLED
+    assert np.max(np.abs(res["R_POS"][last] - wp[:, -1])) <= TOL_RESAMPLED
+    assert np.array_equal(res["R_VEL"][last], np.zeros((B, D)))
+    assert np.array_equal(res["R_ACC"][last], np.zeros((B, D)))
+    # per-row limits: ConstraintSetup scales them by constraint_safety = 0.8, accelerations
+    # are clamped to the unscaled limit (path_timing_trajectory.cc:458-472)
+    owner = np.repeat(np.arange(B), rows)
+    assert (np.abs(res["R_VEL"]) <= 0.8 * vmax[owner] * (1 + 1e-6) + 1e-9).all()
+    assert (np.abs(res["R_ACC"]) <= amax[owner]).all()
+    within = np.ones(total - 1, bool)   # differences between rows of the same path ...
+    within[last[:-1]] = False
+    assert (np.diff(res["R_S"])[within] >= 0).all()
+    within[last - 1] = False            # ... and not onto the final row (the path's end time)
+    assert np.max(np.abs(np.diff(res["R_TIME"])[within] - dt)) <= 1e-12 * float(np.max(dur))
+    # batch independence and the oracle on a sample of the batch
+    pick = np.array([0, 1, 777, 2048, 3000, 4095])
+    sub = _run_engine(pkg, wp[pick], vmax[pick], amax[pick], N, dt=dt)
+    for i, b in enumerate(pick):
+        lo, hi = off[b], off[b + 1]
+        slo, shi = sub["R_OFFSET"][i], sub["R_OFFSET"][i + 1]
+        assert hi - lo == shi - slo
+        assert res["DURATION"][b] == sub["DURATION"][i]
+        for k in ("R_TIME", "R_POS", "R_VEL", "R_ACC", "R_S"):
+            assert np.array_equal(res[k][lo:hi], sub[k][slo:shi]), (b, k)
+        assert np.array_equal(res["TIME"][b], sub["TIME"][i])
+    exact = _check_against_oracle(po, sub, wp[pick], vmax[pick], amax[pick], N, dt=dt)
+    assert exact == len(pick)
