@@ -175,7 +175,8 @@ def _limit_curve_run(pkg, pw, jw, vm, am, jac_from=None):
     A = pkg.ARR
     res = {k: eng.get(getattr(A, k)) for k in
            ("DQ", "DDQ", "CONS", "B_SD2_MAX", "B_SDD_MAX", "B_SDD_MIN", "B_SD2_ZERO", "B_TYPE",
-            "TIME", "SD", "STATUS", "DURATION", "R_OFFSET", "R_POS", "R_VEL", "R_ACC")}
+            "TIME", "SD", "SDD", "SD2", "STATUS", "DURATION", "LAST_EXTREMAL", "R_OFFSET", "R_POS",
+            "R_VEL", "R_ACC", "R_S", "R_SD", "R_SDD")}
     eng.close()
     return res, launches
 
@@ -196,6 +197,30 @@ def test_fused_rows_and_limit_curve_equal_the_two_kernel_path(pkg, po, monkeypat
     assert (fused["STATUS"] == 0).sum() >= B // 2
     for k in fused:
         assert fused[k].tobytes() == plain[k].tobytes(), k
+
+
+@pytest.mark.parametrize("uploaded_jacobians", [False, True])
+def test_joint_structured_sweeps_equal_the_generic_solver(pkg, po, monkeypatch, uploaded_jacobians):
+    """Cartesian rows are the joint rows plus two speed rows: the sweeps run on
+    Joint8Policy<7, true> / k_optimize_pair<7, true> (rows from q', q'' and the two stored
+    coefficients) and must give the bits of GenericPolicy reading all 16 stored rows."""
+    B, W = (6, 5) if uploaded_jacobians else (64, 5)
+    pw, jw, vm, am = pkg.workloads.cart_paths(B, W, seed=5400)
+    if not uploaded_jacobians:
+        # some unusual paths: tight / loose limits, a repeated waypoint
+        vm[3] *= 0.5
+        am[5] *= 100.0
+        am[6] *= 0.3
+        pw[7, 2] = pw[7, 1]
+        jw[7, 2] = jw[7, 1]
+    jf = po.fake_jacobian if uploaded_jacobians else None
+    monkeypatch.delenv("TPB_CART_GENERIC", raising=False)
+    fast, _ = _limit_curve_run(pkg, pw, jw, vm, am, jf)
+    monkeypatch.setenv("TPB_CART_GENERIC", "1")
+    generic, _ = _limit_curve_run(pkg, pw, jw, vm, am, jf)
+    assert (fast["STATUS"] == 0).sum() >= B // 2
+    for k in fast:
+        assert fast[k].tobytes() == generic[k].tobytes(), k
 
 
 def test_cart_argument_errors(pkg):

@@ -120,22 +120,41 @@ struct GenericPolicy {
 // twice changes no outcome, so no lane predicate is needed anywhere, and the
 // copies keep real operands in the divisions (0/1 would take the slow path of
 // the double-precision division).
-template <int kD>
+//
+// kCart: the rows of a Cartesian path (timeable_path_cartesian_spline.cc:551-595) are
+// the joint rows plus two more of the velocity kind, A = 0, B = |J q'|^2 of the
+// translational / rotational part, -v^2 <= . <= v^2.  The padding lanes d == kD of
+// groups 0 and 1 (kD <= 7) carry them: their velocity-kind coefficient V is read from
+// the stored constraint rows instead of being q'^2, and their bounds are those rows'.
+template <int kD, bool kCart = false>
 struct Joint8Policy {
   struct Rows {
     double A, B;  // q'_d, q''_d of one sample (d >= kD: a copy of row kD-1)
+    double V;     // kCart: B of this lane's velocity-kind row (else unused: it is A*A)
   };
   int lane;
   int g, d;  // lane = 8*g + d
   const double *dq, *ddq;  // this path's rows, already offset by min(d, kD-1)
   double aS, vS2;  // amax_d*safety, (vmax_d*safety)^2 (row bounds: -aS..aS, 0..vS2)
+  // kCart only: lanes with xsel read V from bx[idx * xstride]; vlo is their lower bound
+  // (0 for the joint velocity rows), vS2 their upper one
+  const double* bx;
+  int xstride;
+  bool xsel;
+  double vlo;
 
   __device__ __forceinline__ Rows load(int idx) const {
     Rows r;
     r.A = dq[idx * kD];
     r.B = ddq[idx * kD];
+    if (kCart) {
+      r.V = r.A * r.A;
+      if (xsel) r.V = bx[static_cast<size_t>(idx) * xstride];
+    }
     return r;
   }
+  __device__ __forceinline__ double vcoef(const Rows& r) const { return kCart ? r.V : r.A * r.A; }
+  __device__ __forceinline__ double vlower() const { return kCart ? vlo : 0.0; }
 
   // AreDerivativesValid (:624-636)
   __device__ __forceinline__ bool valid(const Rows& r, double sddv, double sd2v) const {
@@ -143,8 +162,8 @@ struct Joint8Policy {
     bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
     // velocity row (A = 0, B = q'^2, 0 <= . <= vS2): 0*sdd contributes +-0 (or NaN
     // for a non-finite sdd, which then passes every comparison like in the reference)
-    const double w = 0.0 * sddv + (r.A * r.A) * sd2v;
-    bad = bad || (w + kTiny < 0.0) || (w - kTiny > vS2);
+    const double w = 0.0 * sddv + vcoef(r) * sd2v;
+    bad = bad || (w + kTiny < vlower()) || (w - kTiny > vS2);
     return __ballot_sync(kFullMask, bad) == 0u;
   }
 
@@ -175,8 +194,9 @@ struct Joint8Policy {
     const bool zero = num == 0.0;
     const double quot = guarded_div(none || zero, num, r.A);
     const double cand = none ? quiet_nan() : (zero ? num * r.A : quot);
-    const double vv = (r.A * r.A) * sd2v;
-    const bool vbad = __ballot_sync(kFullMask, (vv + kTiny < 0.0) || (vv - kTiny > vS2)) != 0u;
+    const double vv = vcoef(r) * sd2v;
+    const bool vbad =
+        __ballot_sync(kFullMask, (vv + kTiny < vlower()) || (vv - kTiny > vS2)) != 0u;
     double best = kMax ? -DBL_MAX : DBL_MAX;
     // one round: group g tests the candidate held by lane (src_group, row) against
     // acceleration row d
@@ -734,8 +754,8 @@ __device__ __forceinline__ void init_policy(GenericPolicy& p, const Dims& dm,
   __syncwarp();
 }
 
-template <int kD>
-__device__ __forceinline__ void init_policy(Joint8Policy<kD>& p, const Dims& dm,
+template <int kD, bool kCart>
+__device__ __forceinline__ void init_policy(Joint8Policy<kD, kCart>& p, const Dims& dm,
                                             const DeviceArrays& a, int b, int lane, double safety,
                                             double*, bool, int* status) {
   const size_t o = static_cast<size_t>(b) * dm.N;
@@ -748,7 +768,23 @@ __device__ __forceinline__ void init_policy(Joint8Policy<kD>& p, const Dims& dm,
   p.aS = a.amax[static_cast<size_t>(b) * kD + dd] * safety;
   const double vs = a.vmax[static_cast<size_t>(b) * kD + dd] * safety;
   p.vS2 = vs * vs;
-  const bool bad = (-p.aS >= p.aS) || (0.0 >= p.vS2);
+  p.bx = nullptr;
+  p.xstride = 0;
+  p.xsel = false;
+  p.vlo = 0.0;
+  if (kCart) {
+    static_assert(!kCart || kD <= 7, "the extra rows ride on the padding lanes");
+    // rows 2*kD + g of the stored constraints, [sample][C][4] = (A, B, lower, upper)
+    p.xsel = (p.d == kD) && (p.g < 2);
+    if (p.xsel) {
+      const double* row0 = a.cons + (o * dm.C + 2 * kD + p.g) * 4;
+      p.bx = row0 + 1;
+      p.xstride = dm.C * 4;
+      p.vlo = row0[2];
+      p.vS2 = row0[3];
+    }
+  }
+  const bool bad = (-p.aS >= p.aS) || (p.vlo >= p.vS2);
   if (__ballot_sync(kFullMask, bad)) *status = TPB_PATH_FAIL_SETUP;
 }
 

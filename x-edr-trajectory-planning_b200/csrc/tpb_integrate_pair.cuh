@@ -37,7 +37,9 @@ namespace tpb {
 
 constexpr int kPairWarpsPerBlock = 1;  // 2 paths per CTA: 2,048 CTAs spread evenly over the SMs
 
-template <int kD>
+// kCart: Cartesian rows (see Joint8Policy): the padding lane d == kD of each group of
+// the half carries one of the two extra velocity-kind rows; Vk is its B coefficient.
+template <int kD, bool kCart = false>
 struct PairSolver {
   // lane geometry
   int lane;     // 0..15 within the half
@@ -49,6 +51,11 @@ struct PairSolver {
   // divisions (0/1 would take the slow path of the double-precision division).
   const double *dq, *ddq;  // rows, already offset by min(d, kD-1)
   double aS, vS2;          // amax_d*safety, (vmax_d*safety)^2
+  // kCart only: lanes with xsel read Vk from bx[idx * xstride]; vlo = their lower bound
+  const double* bx;
+  int xstride;
+  bool xsel;
+  double vlo;
   int N;
   double ds;
   double *sd2, *sdd;
@@ -76,9 +83,17 @@ struct PairSolver {
   __device__ __forceinline__ bool valid_k(double Ak, double B, double k, double sd2v) const {
     const double v = Ak * k + B * sd2v;
     bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
-    const double w = 0.0 * k + (Ak * Ak) * sd2v;
-    bad = bad || (w + kTiny < 0.0) || (w - kTiny > vS2);
+    const double w = 0.0 * k + vcoef(Ak) * sd2v;
+    bad = bad || (w + kTiny < vlower()) || (w - kTiny > vS2);
     return ballot(bad) == 0u;
+  }
+  // B coefficient of this lane's velocity-kind row at the sweep's sample
+  __device__ __forceinline__ double vcoef(double Ak) const { return kCart ? Vk : Ak * Ak; }
+  __device__ __forceinline__ double vlower() const { return kCart ? vlo : 0.0; }
+  __device__ __forceinline__ double load_v(int at, double A) const {
+    double v = A * A;
+    if (xsel) v = bx[static_cast<size_t>(at) * xstride];
+    return v;
   }
 
   // FindSddMax / FindSddMin (:638-695) as the maximum valid k.  *none_valid
@@ -96,8 +111,8 @@ struct PairSolver {
     const bool zero = num == 0.0;
     const double quot = guarded_div(none || zero, num, Ak);
     const double cand = none ? quiet_nan() : (zero ? num * Ak : quot);
-    const double vv = (Ak * Ak) * sd2v;
-    const bool vbad = ballot((vv + kTiny < 0.0) || (vv - kTiny > vS2)) != 0u;
+    const double vv = vcoef(Ak) * sd2v;
+    const bool vbad = ballot((vv + kTiny < vlower()) || (vv - kTiny > vS2)) != 0u;
     double best = -DBL_MAX;
     const unsigned gmask = 0xffu << (shift + 8 * g);  // this group's rows in a warp ballot
     auto round = [&](int row, int src_group) {
@@ -170,6 +185,7 @@ struct PairSolver {
   double cur, bcur, bnb, nb;  // sd2[idx], sd2_max[idx], sd2_max[idx+dir], sd2[idx+dir]
   int tcur, tnb;
   double Ak, Bk;  // rows of sample idx: sgn * q'_d, q''_d
+  double Vk;      // kCart: B of this lane's velocity-kind row at idx
   // driver state
   int iforw_hi, iback_lo, iback_hi, icrit, icrit_lo, icrit_hi, loop, max_loops;
 
@@ -210,6 +226,7 @@ struct PairSolver {
     tcur = type[at];
     Ak = sgn * dq[at * kD];
     Bk = ddq[at * kD];
+    if (kCart) Vk = load_v(at, Ak);
     bnb = bmax[at + dir];
     tnb = type[at + dir];
     nb = sd2[at + dir];
@@ -268,6 +285,8 @@ struct PairSolver {
     const int i1 = clampi(idx + dir), i2 = clampi(idx + 2 * dir);
     const double A_n = dq[i1 * kD];
     const double B_n = ddq[i1 * kD];
+    double V_n = 0.0;
+    if (kCart) V_n = load_v(i1, A_n);
     const double bnb_n = bmax[i2];
     const int tnb_n = type[i2];
     const double nb_n = sd2[i2];
@@ -327,6 +346,7 @@ struct PairSolver {
     tcur = tnb;
     Ak = sgn * A_nx;
     Bk = B_nx;
+    if (kCart) Vk = V_n;
     bnb = bnb_nx;
     tnb = tnb_nx;
     nb = nb_nx;
@@ -421,6 +441,7 @@ struct PairSolver {
     cur = bcur = bnb = nb = 0.0;
     tcur = tnb = kNone;
     Ak = Bk = 0.0;
+    Vk = 0.0;
     if (go) {
       stage = kFirstBack;
       sweeping = true;
@@ -443,7 +464,7 @@ struct PairSolver {
 
 // Phase kPhaseOptimize for two paths per warp.  Runs between
 // k_integrate<Joint8Policy<kD>, ., kPhaseSetup> and <., ., kPhaseFinalize>.
-template <int kD>
+template <int kD, bool kCart = false>
 __global__ void __launch_bounds__(kPairWarpsPerBlock * 32, 16 / kPairWarpsPerBlock)
 k_optimize_pair(Dims dm, DeviceArrays a, double safety, int max_loops) {
   const int warp = threadIdx.x >> 5;
@@ -455,7 +476,7 @@ k_optimize_pair(Dims dm, DeviceArrays a, double safety, int max_loops) {
   const int N = dm.N;
   const size_t o = static_cast<size_t>(bb) * N;
 
-  PairSolver<kD> S;
+  PairSolver<kD, kCart> S;
   S.lane = lane;
   S.g = lane >> 3;
   S.d = lane & 7;
@@ -474,13 +495,29 @@ k_optimize_pair(Dims dm, DeviceArrays a, double safety, int max_loops) {
   S.aS = a.amax[static_cast<size_t>(bb) * kD + dd] * safety;
   const double vs = a.vmax[static_cast<size_t>(bb) * kD + dd] * safety;
   S.vS2 = vs * vs;
+  S.bx = nullptr;
+  S.xstride = 0;
+  S.xsel = false;
+  S.vlo = 0.0;
+  if (kCart) {
+    // rows 2*kD + g of the stored constraints, [sample][C][4] = (A, B, lower, upper)
+    S.xsel = (S.d == kD);
+    if (S.xsel) {
+      const double* row0 = a.cons + (o * dm.C + 2 * kD + S.g) * 4;
+      S.bx = row0 + 1;
+      S.xstride = dm.C * 4;
+      S.vlo = row0[2];
+      S.vS2 = row0[3];
+    }
+  }
   S.status = has_path ? a.status[bb] : TPB_PATH_FAIL_SETUP;
   const bool go = S.status == TPB_PATH_OK;
   // SetSetupDone (:535-552), as in the setup phase
   S.ds = 1.0;
   if (go) {
-    const double s_start = a.path_start[bb];
-    const double s_end = s_start + a.delta[bb] * (N - 1);
+    // Cartesian paths: SetupProblem's range as k_cart_constraints* stored it
+    const double s_start = kCart ? a.s_start[bb] : a.path_start[bb];
+    const double s_end = kCart ? a.s_end[bb] : s_start + a.delta[bb] * (N - 1);
     S.ds = (s_end - s_start) / (N - 1);
   }
   S.run(go);

@@ -610,6 +610,34 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
 #undef TPB_P8
     return 3;
   }
+  // Cartesian paths with 6 or 7 dofs: joint rows + the two speed rows on the padding
+  // lanes (Joint8Policy<., true>); TPB_CART_GENERIC=1 keeps the generic rows-in-shared-
+  // memory solver (the parity tests compare the two)
+  const char* cg = std::getenv("TPB_CART_GENERIC");
+  if (mode == Mode::kCartesian && (d.D == 6 || d.D == 7) && d.C == 2 * d.D + 2 &&
+      !(cg != nullptr && cg[0] == '1')) {
+    const int threads = kWarpsPerBlock * 32;
+    const int per_block = kPairWarpsPerBlock * 2;
+    const int pblocks = (d.B + per_block - 1) / per_block;
+    const int pthreads = kPairWarpsPerBlock * 32;
+#define TPB_C8(K)                                                                              \
+  case K:                                                                                      \
+    mark(0);                                                                                   \
+    k_integrate<Joint8Policy<K, true>, 7, kPhaseSetup><<<blocks, threads, 0, st>>>(            \
+        d, a, false, safety, max_loops);                                                       \
+    mark(1);                                                                                   \
+    k_optimize_pair<K, true><<<pblocks, pthreads, 0, st>>>(d, a, safety, max_loops);           \
+    mark(2);                                                                                   \
+    k_integrate<Joint8Policy<K, true>, 7, kPhaseFinalize><<<blocks, threads, 0, st>>>(         \
+        d, a, false, safety, max_loops);                                                       \
+    mark(3);                                                                                   \
+    break
+    switch (d.D) {
+      TPB_C8(6); TPB_C8(7);
+    }
+#undef TPB_C8
+    return 3;
+  }
   mark(0);
   mark(1);
   if (joint && d.D <= 8) {
