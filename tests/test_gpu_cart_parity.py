@@ -223,6 +223,54 @@ def test_joint_structured_sweeps_equal_the_generic_solver(pkg, po, monkeypatch, 
         assert fast[k].tobytes() == generic[k].tobytes(), k
 
 
+def _six_dof_run(pkg, pw, jw6, vm, am, q, jac):
+    B, W = pw.shape[0], pw.shape[1]
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=6, max_waypoints=W,
+                     max_time_samples_total=B * 60000, cartesian=True)
+    eng.set_cart_options(0.05, 0.5, 0.25)
+    eng.set_cart_waypoints(pw, jw6)
+    eng.set_joint_limits(vm, am)
+    eng.cart_set_ik_positions(q)
+    eng.cart_setup_constraints(model=0, jacobians=jac)
+    eng.optimize()
+    eng.resample(0.0, DT)
+    A = pkg.ARR
+    res = {k: eng.get(getattr(A, k)) for k in
+           ("DQ", "DDQ", "CONS", "B_SD2_MAX", "B_SDD_MAX", "B_SDD_MIN", "B_SD2_ZERO", "B_TYPE",
+            "TIME", "SD", "SDD", "SD2", "STATUS", "DURATION", "LAST_EXTREMAL", "R_OFFSET", "R_POS",
+            "R_VEL", "R_ACC", "R_S", "R_SD", "R_SDD")}
+    eng.close()
+    return res
+
+
+def test_six_dof_arm_fast_kernels_equal_the_generic_ones(pkg, monkeypatch):
+    """A 6-dof arm with user kinematics (positions and Jacobians uploaded, here smooth
+    random ones): the fused rows/limit kernel and the joint-structured sweeps for kD = 6
+    against k_cart_constraints + k_generic_limit + GenericPolicy, bit for bit."""
+    B, W = 24, 4
+    rng = np.random.default_rng(5500)
+    pw, jw, _, _ = pkg.workloads.cart_paths(B, W, seed=5500)
+    jw6 = np.ascontiguousarray(jw[..., :6])
+    vm = rng.uniform(0.5, 2.0, (B, 6))
+    am = rng.uniform(1.0, 4.0, (B, 6))
+    # smooth joint motion along the path and a smooth, well-conditioned Jacobian field
+    u = np.linspace(0.0, 1.0, N)[None, :, None]
+    q = (rng.uniform(-1, 1, (B, 1, 6)) + u * rng.uniform(-2, 2, (B, 1, 6))
+         + 0.3 * np.sin(2 * np.pi * u * rng.uniform(0.5, 2.0, (B, 1, 6))))
+    jac = (rng.normal(0, 0.3, (B, 1, 6, 6)) + np.eye(6)[None, None]
+           + 0.2 * np.sin(3.0 * u[..., None] + rng.uniform(0, 6, (B, 1, 6, 6))))
+    q, jac = np.ascontiguousarray(q), np.ascontiguousarray(jac)
+    monkeypatch.delenv("TPB_CART_UNFUSED", raising=False)
+    monkeypatch.delenv("TPB_CART_GENERIC", raising=False)
+    fast = _six_dof_run(pkg, pw, jw6, vm, am, q, jac)
+    monkeypatch.setenv("TPB_CART_UNFUSED", "1")
+    monkeypatch.setenv("TPB_CART_GENERIC", "1")
+    generic = _six_dof_run(pkg, pw, jw6, vm, am, q, jac)
+    assert (fast["STATUS"] == 0).sum() >= B // 2
+    for k in fast:
+        assert fast[k].tobytes() == generic[k].tobytes(), k
+
+
 def test_cart_argument_errors(pkg):
     eng = _engine(pkg, 2, 3, cap=100)
     with pytest.raises(pkg.TpbError) as ei:
