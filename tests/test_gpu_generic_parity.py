@@ -82,7 +82,8 @@ def test_line_scalar_scenarios(pkg, po):
     _compare(po, res, cons, np.full(1, -3.0), np.ones(1), expect_all_ok=True)
 
 
-@pytest.mark.parametrize("N,C", [(64, 2), (200, 6), (333, 14), (128, 32), (2, 3), (3, 4)])
+@pytest.mark.parametrize("N,C", [(64, 2), (200, 6), (333, 14), (128, 32), (2, 3), (3, 4),
+                                 (300, 9), (150, 12), (100, 16), (90, 17), (257, 1)])
 def test_random_problems(pkg, po, N, C):
     rng = np.random.default_rng(100 * N + C)
     B = 24
@@ -94,6 +95,40 @@ def test_random_problems(pkg, po, N, C):
     t0 = rng.uniform(0, 10, B)
     res = _solve_batch(pkg, cons, s0, s1, sd0, sdd0, t0)
     _compare(po, res, cons, s0, s1, sd0, sdd0, t0)
+
+
+@pytest.mark.parametrize("C", [4, 7, 10, 16])
+def test_tied_rows_register_and_local_limit_kernels(pkg, po, monkeypatch, C):
+    """Duplicate, mirrored and scaled copies of rows put two or more rows on every vertex
+    of the limit-curve LP (the tie branches of FindMaxSd2Simplex): oracle bits, and the
+    register kernel (k_generic_limit_reg) against the local-memory one."""
+    rng = np.random.default_rng(900 + C)
+    B, N = 16, 120
+    half = (C + 1) // 2
+    base = np.stack([pkg.workloads.random_constraints(rng, N, half) for _ in range(B)])
+    cons = np.empty((B, N, C, 4))
+    cons[:, :, :half] = base
+    for r in range(half, C):
+        src = base[:, :, r - half]
+        kind = (r - half) % 3
+        if kind == 0:      # exact duplicate
+            cons[:, :, r] = src
+        elif kind == 1:    # mirrored: -A, -B, [-hi, -lo]
+            cons[:, :, r, 0] = -src[..., 0]
+            cons[:, :, r, 1] = -src[..., 1]
+            cons[:, :, r, 2] = -src[..., 3]
+            cons[:, :, r, 3] = -src[..., 2]
+        else:              # scaled by 2 (exact in binary)
+            cons[:, :, r] = 2.0 * src
+    s0 = np.zeros(B)
+    s1 = rng.uniform(0.5, 5, B)
+    monkeypatch.delenv("TPB_GENERIC_LIMIT_LOCAL", raising=False)
+    reg = _solve_batch(pkg, cons, s0, s1)
+    _compare(po, reg, cons, s0, s1)
+    monkeypatch.setenv("TPB_GENERIC_LIMIT_LOCAL", "1")
+    loc = _solve_batch(pkg, cons, s0, s1)
+    for k in reg:
+        assert reg[k].tobytes() == loc[k].tobytes(), k
 
 
 def test_setup_failures_are_per_path(pkg, po):

@@ -21,6 +21,7 @@
 #include "tpb_integrate.cuh"
 #include "tpb_integrate_pair.cuh"
 #include "tpb_joint_limit.cuh"
+#include "tpb_row_limit.cuh"
 #include "tpb_solver.cuh"
 
 namespace tpb {
@@ -284,6 +285,42 @@ k_generic_limit(Dims dm, DeviceArrays a) {
   double sd2max, sddmax, sd2zero, smax, smin;
   lp_max_sd2(A, Bc, LO, HI, C, sd2max, sddmax, sd2zero);
   find_sdd_min_max(A, Bc, LO, HI, C, sd2max, smax, smin);
+  const size_t o = static_cast<size_t>(b) * dm.N + idx;
+  a.b_raw_sd2_max[o] = sd2max;
+  a.b_sd2_zero[o] = sd2zero;
+  a.b_raw_sdd_max[o] = smax;
+  a.b_raw_sdd_min[o] = smin;
+  a.b_at0[o] = fabs(sd2max - sd2zero) < kTiny;
+}
+
+// The same for C <= kC <= 16 rows with everything in registers (tpb_row_limit.cuh);
+// rows are read as 16-byte halves (a row is 32 bytes, 32-byte aligned).
+template <int kC>
+__global__ void __launch_bounds__(kSampleThreads)
+k_generic_limit_reg(Dims dm, DeviceArrays a) {
+  const int b = blockIdx.y;
+  if (a.active != nullptr && a.active[b] == 0) return;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= dm.N) return;
+  const int C = dm.C;
+  RowLimit<kC> R;
+  const double2* __restrict__ c =
+      reinterpret_cast<const double2*>(a.cons + (static_cast<size_t>(b) * dm.N + idx) * C * 4);
+#pragma unroll
+  for (int r = 0; r < kC; ++r) {
+    double2 ab = make_double2(0.0, 0.0), lh = make_double2(-1.0, 1.0);  // padding row
+    if (r < C) {
+      ab = c[2 * r];
+      lh = c[2 * r + 1];
+    }
+    R.A[r] = ab.x;
+    R.B[r] = ab.y;
+    R.LO[r] = lh.x;
+    R.HI[r] = lh.y;
+  }
+  double sd2max, sddmax, sd2zero, smax, smin;
+  R.lp(C, sd2max, sddmax, sd2zero);
+  R.sdd_min_max(sd2max, smax, smin);
   const size_t o = static_cast<size_t>(b) * dm.N + idx;
   a.b_raw_sd2_max[o] = sd2max;
   a.b_sd2_zero[o] = sd2zero;
@@ -565,9 +602,23 @@ int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safet
   return 1;
 }
 
+// TPB_GENERIC_LIMIT_LOCAL=1 keeps the local-memory kernel for every C (the parity
+// tests compare the two).
 int launch_generic_limit(const Dims& d, const DeviceArrays& a, cudaStream_t st) {
   dim3 grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
-  k_generic_limit<<<grid, kSampleThreads, 0, st>>>(d, a);
+  const char* env = std::getenv("TPB_GENERIC_LIMIT_LOCAL");
+  const bool local = env != nullptr && env[0] == '1';
+  if (local || d.C > 16) {
+    k_generic_limit<<<grid, kSampleThreads, 0, st>>>(d, a);
+  } else if (d.C <= 4) {
+    k_generic_limit_reg<4><<<grid, kSampleThreads, 0, st>>>(d, a);
+  } else if (d.C <= 8) {
+    k_generic_limit_reg<8><<<grid, kSampleThreads, 0, st>>>(d, a);
+  } else if (d.C <= 12) {
+    k_generic_limit_reg<12><<<grid, kSampleThreads, 0, st>>>(d, a);
+  } else {
+    k_generic_limit_reg<16><<<grid, kSampleThreads, 0, st>>>(d, a);
+  }
   return 1;
 }
 
