@@ -293,7 +293,7 @@ k_generic_limit(Dims dm, DeviceArrays a) {
   a.b_at0[o] = fabs(sd2max - sd2zero) < kTiny;
 }
 
-// The same for C <= kC <= 16 rows with everything in registers (tpb_row_limit.cuh);
+// The same for C <= kC <= 12 rows with everything in registers (tpb_row_limit.cuh);
 // rows are read as 16-byte halves (a row is 32 bytes, 32-byte aligned).
 template <int kC>
 __global__ void __launch_bounds__(kSampleThreads)
@@ -602,22 +602,23 @@ int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safet
   return 1;
 }
 
-// TPB_GENERIC_LIMIT_LOCAL=1 keeps the local-memory kernel for every C (the parity
-// tests compare the two).
+// C <= 12: rows in registers, kC = C rounded up to even.  Above that the fully
+// predicated candidate tests (2*kC candidates x kC rows) cost more than the local-memory
+// kernel's early exits (measured, profiles/r1_summary.md v9).  TPB_GENERIC_LIMIT_LOCAL=1
+// keeps the local-memory kernel for every C (the parity tests compare the two).
 int launch_generic_limit(const Dims& d, const DeviceArrays& a, cudaStream_t st) {
   dim3 grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
   const char* env = std::getenv("TPB_GENERIC_LIMIT_LOCAL");
   const bool local = env != nullptr && env[0] == '1';
-  if (local || d.C > 16) {
-    k_generic_limit<<<grid, kSampleThreads, 0, st>>>(d, a);
-  } else if (d.C <= 4) {
-    k_generic_limit_reg<4><<<grid, kSampleThreads, 0, st>>>(d, a);
-  } else if (d.C <= 8) {
-    k_generic_limit_reg<8><<<grid, kSampleThreads, 0, st>>>(d, a);
-  } else if (d.C <= 12) {
-    k_generic_limit_reg<12><<<grid, kSampleThreads, 0, st>>>(d, a);
-  } else {
-    k_generic_limit_reg<16><<<grid, kSampleThreads, 0, st>>>(d, a);
+  const int kc = local ? 99 : (d.C + 1) / 2 * 2;
+  switch (kc) {
+    case 2: k_generic_limit_reg<2><<<grid, kSampleThreads, 0, st>>>(d, a); break;
+    case 4: k_generic_limit_reg<4><<<grid, kSampleThreads, 0, st>>>(d, a); break;
+    case 6: k_generic_limit_reg<6><<<grid, kSampleThreads, 0, st>>>(d, a); break;
+    case 8: k_generic_limit_reg<8><<<grid, kSampleThreads, 0, st>>>(d, a); break;
+    case 10: k_generic_limit_reg<10><<<grid, kSampleThreads, 0, st>>>(d, a); break;
+    case 12: k_generic_limit_reg<12><<<grid, kSampleThreads, 0, st>>>(d, a); break;
+    default: k_generic_limit<<<grid, kSampleThreads, 0, st>>>(d, a); break;
   }
   return 1;
 }
