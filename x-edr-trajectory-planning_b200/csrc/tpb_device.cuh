@@ -30,6 +30,14 @@ __device__ __forceinline__ double quiet_nan() {
   return __longlong_as_double(0x7ff8000000000000LL);
 }
 __device__ __forceinline__ bool is_tiny(double v) { return fabs(v) < kTiny; }
+// AreDerivativesValid (:624-636) for a row with symmetric bounds -lim <= v <= lim:
+//   (v + kTiny < -lim) || (v - kTiny > lim)
+// in one subtraction and one comparison.  Exact: negation commutes with rounding,
+// -(v + kTiny) == (-v) - kTiny, so the test is max(v - kTiny, -v - kTiny) > lim, and
+// rounding is monotone, so that maximum is |v| - kTiny.  (NaN: false either way.)
+__device__ __forceinline__ bool outside_sym(double v, double lim) {
+  return fabs(v) - kTiny > lim;
+}
 
 // num / den where the quotient is only used when !skip.  Lanes with skip set
 // divide 1 by 1 instead: x/0, 0/x and other special operands send the whole warp

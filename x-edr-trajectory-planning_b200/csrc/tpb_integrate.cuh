@@ -159,7 +159,7 @@ struct Joint8Policy {
   // AreDerivativesValid (:624-636)
   __device__ __forceinline__ bool valid(const Rows& r, double sddv, double sd2v) const {
     const double v = r.A * sddv + r.B * sd2v;
-    bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
+    bool bad = outside_sym(v, aS);
     // velocity row (A = 0, B = q'^2, 0 <= . <= vS2): 0*sdd contributes +-0 (or NaN
     // for a non-finite sdd, which then passes every comparison like in the reference)
     const double w = 0.0 * sddv + vcoef(r) * sd2v;
@@ -203,7 +203,7 @@ struct Joint8Policy {
     auto round = [&](int row, int src_group) {
       const double c = __shfl_sync(kFullMask, cand, (src_group << 3) | (row & 7));
       const double v = r.A * c + Bs;
-      const bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
+      const bool bad = outside_sym(v, aS);
       const unsigned m = __ballot_sync(kFullMask, bad);
       // NaN marks "no candidate" (and fails c == c)
       const bool ok = (row < kD) && (c == c) && (((m >> (8 * g)) & 0xffu) == 0u);

@@ -82,7 +82,7 @@ struct PairSolver {
   // Convergent.
   __device__ __forceinline__ bool valid_k(double Ak, double B, double k, double sd2v) const {
     const double v = Ak * k + B * sd2v;
-    bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
+    bool bad = outside_sym(v, aS);
     const double w = 0.0 * k + vcoef(Ak) * sd2v;
     bad = bad || (w + kTiny < vlower()) || (w - kTiny > vS2);
     return ballot(bad) == 0u;
@@ -118,7 +118,7 @@ struct PairSolver {
     auto round = [&](int row, int src_group) {
       const double c = __shfl_sync(kFullMask, cand, (src_group << 3) | (row & 7), 16);
       const double v = Ak * c + Bs;
-      const bool bad = (v + kTiny < -aS) || (v - kTiny > aS);
+      const bool bad = outside_sym(v, aS);
       const unsigned m = __ballot_sync(kFullMask, bad);
       // NaN marks "no candidate" and fails c > best
       const bool ok = (row < kD) && ((m & gmask) == 0u);

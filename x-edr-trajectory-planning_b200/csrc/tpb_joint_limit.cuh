@@ -342,7 +342,7 @@ struct JointLimit {
 #pragma unroll
         for (int r = 0; r < kD; ++r) {
           const double v = A[r] * cand + Bs[r];
-          ok = ok && !((v + kTiny < -aS[r]) || (v - kTiny > aS[r]));
+          ok = ok && !outside_sym(v, aS[r]);
         }
         mx = (ok && cand > mx) ? cand : mx;
         mn = (ok && cand < mn) ? cand : mn;
