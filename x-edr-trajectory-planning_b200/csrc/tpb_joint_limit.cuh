@@ -231,7 +231,6 @@ struct JointLimit {
             if (tmp < next_sd2 - kTiny) act = 0u;
             act |= 1u << slot;
             next_sd2 = tmp;
-            next_sdd = a + b * next_sd2;
             last.A = Ac;
             last.B = B[d];
             last.bound = bound;
@@ -253,7 +252,6 @@ struct JointLimit {
           if (tmp < next_sd2 - kTiny) act = 0u;
           act |= 1u << slot;
           next_sd2 = tmp;
-          next_sdd = a + b * next_sd2;
           last.A = 0.0;
           last.B = Bv[d];
           last.bound = vhi(d);
@@ -267,6 +265,8 @@ struct JointLimit {
         sddmax = 0.0;
         return;
       }
+      // (the reference assigns this at every acceptance; the last one stands)
+      next_sdd = a + b * next_sd2;
       // active list = new rows (slot order) followed by s: pairwise optimality,
       // next edge = lowest slope among the new rows (first one on ties)
       bool optimal = false;
@@ -337,8 +337,8 @@ struct JointLimit {
 #pragma unroll
       for (int w = 0; w < 2; ++w) {
         const double cand = ((w == 0 ? -aS[i] : aS[i]) - Bs[i]) / (has ? Ai : 1.0);
-        const double zc = 0.0 * cand;
-        bool ok = has && !((zc == zc) && vbad);
+        // velocity rows: 0*cand + B*sd2 is NaN (passes) for a non-finite candidate
+        bool ok = has && !((fabs(cand) <= DBL_MAX) && vbad);
 #pragma unroll
         for (int r = 0; r < kD; ++r) {
           const double v = A[r] * cand + Bs[r];

@@ -146,7 +146,6 @@ struct RowLimit {
             if (tmp < next_sd2 - kTiny) act = 0u;
             act |= 1u << slot;
             next_sd2 = tmp;
-            next_sdd = a + b * next_sd2;
             last.A = Ac;
             last.B = B[i];
             last.bound = bound;
@@ -160,6 +159,8 @@ struct RowLimit {
         sddmax = 0.0;
         return;
       }
+      // (the reference assigns this at every acceptance; the last one stands)
+      next_sdd = a + b * next_sd2;
       // active list = new rows (slot order) followed by s: pairwise optimality,
       // next edge = lowest slope among the new rows (first one on ties)
       bool optimal = false;
