@@ -1050,7 +1050,6 @@ int32_t tpb_planner_reset(tpb_engine* e, int32_t path_sample_capacity, double ti
   if (path_sample_capacity > w.P_cap) {
     TPB_CUDA(e, cudaStreamSynchronize(e->stream));
     for (void* p : e->w_big) cudaFree(p);
-  for (void* p : e->spline_big) cudaFree(p);
     e->w_big.clear();
     w.P_cap = 0;
     const size_t BP = Bm * static_cast<size_t>(path_sample_capacity);

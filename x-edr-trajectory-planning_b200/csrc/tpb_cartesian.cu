@@ -323,7 +323,8 @@ constexpr int kCartThreads = 128;
 __global__ void __launch_bounds__(kCartThreads)
 k_cart_sample_targets(Dims dm, DeviceArrays a) {
   extern __shared__ double smem[];
-  const int b = blockIdx.y;
+  const int b = path_of_block();
+  if (b >= dm.B) return;  // uniform per CTA (grid folded over y and z)
   if (a.active != nullptr && a.active[b] == 0) return;  // uniform per CTA
   const int D = dm.D;
   const int n = a.num_points[b];
@@ -434,7 +435,8 @@ __device__ __forceinline__ void log_so3_derivative(const Quat& q, double* out) {
 
 // FakePathIK: path position i = IK of target i + 1 (new_ik_path[1:], :512-513)
 __global__ void k_cart_ik_fake7(Dims dm, DeviceArrays a) {
-  const int b = blockIdx.y;
+  const int b = path_of_block();
+  if (b >= dm.B) return;  // uniform per CTA (grid folded over y and z)
   if (a.active != nullptr && a.active[b] == 0) return;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= dm.N) return;
@@ -453,7 +455,8 @@ template <bool kFake7>
 __global__ void __launch_bounds__(kCartThreads)
 k_cart_constraints(Dims dm, DeviceArrays a, double safety, double max_trans_vel,
                    double max_rot_vel) {
-  const int b = blockIdx.y;
+  const int b = path_of_block();
+  if (b >= dm.B) return;  // uniform per CTA (grid folded over y and z)
   if (a.active != nullptr && a.active[b] == 0) return;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int N = dm.N, D = dm.D, C = dm.C;
@@ -545,7 +548,8 @@ __global__ void __launch_bounds__(kCartThreads)
 k_cart_constraints_limit(Dims dm, DeviceArrays a, double safety, double max_trans_vel,
                          double max_rot_vel) {
   __shared__ double s_aS[kD], s_vS2[kD];
-  const int b = blockIdx.y;
+  const int b = path_of_block();
+  if (b >= dm.B) return;  // uniform per CTA (grid folded over y and z)
   if (a.active != nullptr && a.active[b] == 0) return;  // uniform per CTA
   if (threadIdx.x < kD) {
     const double am = a.amax[static_cast<size_t>(b) * kD + threadIdx.x];
@@ -667,7 +671,7 @@ int launch_cart_fit(const Dims& d, const DeviceArrays& a, double rotation_roundi
 int launch_cart_sample_targets(const Dims& d, const DeviceArrays& a, cudaStream_t st) {
   const size_t smem = sizeof(double) * (static_cast<size_t>(d.max_points) + 3 +
                                         static_cast<size_t>(d.max_points) * (d.D + 7));
-  dim3 grid((d.N + 1 + kCartThreads - 1) / kCartThreads, d.B);
+  const dim3 grid = path_grid((d.N + 1 + kCartThreads - 1) / kCartThreads, d.B);
   if (smem > 48 * 1024)
     cudaFuncSetAttribute(k_cart_sample_targets, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          static_cast<int>(smem));
@@ -677,7 +681,7 @@ int launch_cart_sample_targets(const Dims& d, const DeviceArrays& a, cudaStream_
 
 int launch_cart_ik_builtin(const Dims& d, const DeviceArrays& a, int model, cudaStream_t st) {
   if (model != TPB_KIN_FAKE7 || d.D != 7) return -1;
-  dim3 grid((d.N + kCartThreads - 1) / kCartThreads, d.B);
+  const dim3 grid = path_grid((d.N + kCartThreads - 1) / kCartThreads, d.B);
   k_cart_ik_fake7<<<grid, kCartThreads, 0, st>>>(d, a);
   return 1;
 }
@@ -688,7 +692,7 @@ int launch_cart_ik_builtin(const Dims& d, const DeviceArrays& a, int model, cuda
 int launch_cart_constraints(const Dims& d, const DeviceArrays& a, double safety,
                             double max_trans_vel, double max_rot_vel, int model, bool have_jac,
                             cudaStream_t st) {
-  dim3 grid((d.N + kCartThreads - 1) / kCartThreads, d.B);
+  const dim3 grid = path_grid((d.N + kCartThreads - 1) / kCartThreads, d.B);
   if (!have_jac && (model != TPB_KIN_FAKE7 || d.D != 7)) return -1;
   const char* env = std::getenv("TPB_CART_UNFUSED");
   const bool fused = !(env != nullptr && env[0] == '1') && d.C == 2 * d.D + 2;

@@ -26,6 +26,15 @@ constexpr int kMaxRows = 32;    // constraint rows per sample handled by the ker
 constexpr int kMaxDofs = 16;    // joint dofs (2*D rows <= kMaxRows)
 constexpr int kMaxDegree = 5;   // dense spline evaluator
 
+// Kernels with one CTA row per path fold the path index over gridDim.y and
+// gridDim.z (gridDim.y alone ends at 65,535 paths; BASELINE cfg4 is 65,536).
+constexpr int kMaxGridY = 32768;
+inline dim3 path_grid(unsigned tiles, int num_paths) {
+  const unsigned gy = static_cast<unsigned>(num_paths < kMaxGridY ? (num_paths > 0 ? num_paths : 1) : kMaxGridY);
+  return dim3(tiles, gy, (static_cast<unsigned>(num_paths) + gy - 1) / gy);
+}
+__device__ __forceinline__ int path_of_block() { return blockIdx.z * gridDim.y + blockIdx.y; }
+
 __device__ __forceinline__ double quiet_nan() {
   return __longlong_as_double(0x7ff8000000000000LL);
 }

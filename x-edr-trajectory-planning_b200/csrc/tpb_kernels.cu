@@ -76,7 +76,8 @@ constexpr int kSampleThreads = 128;
 __global__ void __launch_bounds__(kSampleThreads)
 k_joint_sample_limit_any(Dims dm, DeviceArrays a, double safety) {
   extern __shared__ double smem[];
-  const int b = blockIdx.y;
+  const int b = path_of_block();
+  if (b >= dm.B) return;  // uniform per CTA (grid folded over y and z)
   if (a.active != nullptr && a.active[b] == 0) return;  // uniform per CTA
   const int D = dm.D;
   const int n = a.num_points[b];
@@ -173,7 +174,8 @@ template <int kD>
 __global__ void __launch_bounds__(kSampleThreads, TPB_SL_MINBLOCKS)
 k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
   extern __shared__ double smem[];
-  const int b = blockIdx.y;
+  const int b = path_of_block();
+  if (b >= dm.B) return;  // uniform per CTA (grid folded over y and z)
   if (a.active != nullptr && a.active[b] == 0) return;  // uniform per CTA
   const int n = a.num_points[b];
   const int nk = n + 3;
@@ -271,7 +273,8 @@ k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
 
 __global__ void __launch_bounds__(kSampleThreads)
 k_generic_limit(Dims dm, DeviceArrays a) {
-  const int b = blockIdx.y;
+  const int b = path_of_block();
+  if (b >= dm.B) return;  // uniform per CTA (grid folded over y and z)
   if (a.active != nullptr && a.active[b] == 0) return;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= dm.N) return;
@@ -300,7 +303,8 @@ k_generic_limit(Dims dm, DeviceArrays a) {
 template <int kC>
 __global__ void __launch_bounds__(kSampleThreads)
 k_generic_limit_reg(Dims dm, DeviceArrays a) {
-  const int b = blockIdx.y;
+  const int b = path_of_block();
+  if (b >= dm.B) return;  // uniform per CTA (grid folded over y and z)
   if (a.active != nullptr && a.active[b] == 0) return;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= dm.N) return;
@@ -592,7 +596,7 @@ int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safet
                               cudaStream_t st) {
   const size_t tables =
       sizeof(double) * (static_cast<size_t>(d.max_points) + 3 + static_cast<size_t>(d.max_points) * d.D + 2 * d.D);
-  dim3 grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
+  const dim3 grid = path_grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
   const size_t smem = tables + sizeof(double) * 3 * kSampleThreads * d.D;
   if (d.D <= 8 && smem <= 48 * 1024) {
 #define TPB_SL(K) \
@@ -612,7 +616,7 @@ int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safet
 // kernel's early exits (measured, profiles/r1_summary.md v9).  TPB_GENERIC_LIMIT_LOCAL=1
 // keeps the local-memory kernel for every C (the parity tests compare the two).
 int launch_generic_limit(const Dims& d, const DeviceArrays& a, cudaStream_t st) {
-  dim3 grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
+  const dim3 grid = path_grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
   const char* env = std::getenv("TPB_GENERIC_LIMIT_LOCAL");
   const bool local = env != nullptr && env[0] == '1';
   const int kc = local ? 99 : (d.C + 1) / 2 * 2;
@@ -732,8 +736,13 @@ int launch_resample_rows(const Dims& d, const DeviceArrays& a, const ResampleVie
       k_resample_fill<true, false><<<grid, kResampleThreads, with_time, st>>>(d, a, v, keep, start_sec, dt);
     }
   } else if (skip) {
+    // the tile alone exceeds 48 KB from D = 10 on
+    cudaFuncSetAttribute(k_resample_fill<false, true>,
+                         cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     k_resample_fill<false, true><<<grid, kResampleThreads, tile, st>>>(d, a, v, keep, start_sec, dt);
   } else {
+    cudaFuncSetAttribute(k_resample_fill<false, false>,
+                         cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     k_resample_fill<false, false><<<grid, kResampleThreads, tile, st>>>(d, a, v, keep, start_sec, dt);
   }
   return 2;
