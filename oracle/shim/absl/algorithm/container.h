@@ -5,6 +5,10 @@
 #include <algorithm>
 
 namespace absl {
+template <typename C, typename OutIt>
+OutIt c_copy(const C& c, OutIt out) {
+  return std::copy(c.begin(), c.end(), out);
+}
 template <typename C>
 void c_reverse(C& c) {
   std::reverse(c.begin(), c.end());

@@ -21,5 +21,11 @@ inline CheckSink CheckFail(bool ok, const char* what) {
 }  // namespace oracle_shim
 
 #define CHECK(cond) ::oracle_shim::CheckFail(static_cast<bool>(cond), #cond)
+#define CHECK_EQ(a, b) CHECK((a) == (b))
+#define CHECK_NE(a, b) CHECK((a) != (b))
+#define CHECK_LE(a, b) CHECK((a) <= (b))
+#define CHECK_LT(a, b) CHECK((a) < (b))
+#define CHECK_GE(a, b) CHECK((a) >= (b))
+#define CHECK_GT(a, b) CHECK((a) > (b))
 
 #endif  // ORACLE_SHIM_ABSL_LOG_CHECK_H_

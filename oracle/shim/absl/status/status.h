@@ -10,6 +10,9 @@
 #include <string>
 #include <utility>
 
+// abseil's status.h brings Span along; bspline_base.h relies on that
+#include "absl/types/span.h"
+
 namespace absl {
 
 enum class StatusCode : int {
@@ -62,6 +65,9 @@ inline Status InternalError(std::string m) {
 inline Status OutOfRangeError(std::string m) {
   return Status(StatusCode::kOutOfRange, std::move(m));
 }
+inline Status UnimplementedError(std::string m) {
+  return Status(StatusCode::kUnimplemented, std::move(m));
+}
 
 // The reference .cc calls absl::StrCat without including str_cat.h directly.
 // (No iostreams here: this library is dlopen()ed with a static libstdc++.)
@@ -71,6 +77,8 @@ inline void Append(std::string* out, const std::string& v) { out->append(v); }
 inline void Append(std::string* out, int v) { out->append(std::to_string(v)); }
 inline void Append(std::string* out, long v) { out->append(std::to_string(v)); }
 inline void Append(std::string* out, unsigned long v) { out->append(std::to_string(v)); }
+inline void Append(std::string* out, long long v) { out->append(std::to_string(v)); }
+inline void Append(std::string* out, unsigned v) { out->append(std::to_string(v)); }
 inline void Append(std::string* out, double v) {
   char buf[40];
   std::snprintf(buf, sizeof(buf), "%g", v);
