@@ -34,12 +34,11 @@ ORC_FAIL_INITIAL_VELOCITY = 12
 
 def build(force: bool = False) -> None:
     """Compile the oracle (and oracle/_ref when /root/reference exists)."""
-    need = force or not os.path.exists(_ORACLE_SO)
-    if os.path.isdir("/root/reference/trajectory_planning") and not os.path.exists(_REF_SO):
-        need = True
-    if need:
-        subprocess.run(["make", "-C", HERE, "all"], check=True,
-                       stdout=subprocess.DEVNULL)
+    if force:
+        subprocess.run(["make", "-C", HERE, "clean"], check=True, stdout=subprocess.DEVNULL)
+    # make is a no-op when everything is up to date; without /root/reference (the GPU
+    # box) the Makefile keeps the prebuilt oracle/_ref
+    subprocess.run(["make", "-C", HERE, "all"], check=True, stdout=subprocess.DEVNULL)
 
 
 def _dp(a):
@@ -282,6 +281,39 @@ def _register_tbuf(L, pre, port):
     f("rows").argtypes = [vp] + D + [c_double_p] * 4
 
 
+def _register_ref_planner(R):
+    """The reference's own TimeableJointSplinePath + PathTimingTrajectory
+    (oracle/ref_wrap_planner.cc)."""
+    vp, i64p, ip = C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int)
+    i32p = C.POINTER(C.c_int32)
+    R.tpref_planner_create.restype = vp
+    R.tpref_planner_create.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
+                                       C.c_int64, C.c_int, C.c_int, C.c_double]
+    R.tpref_planner_destroy.restype = None
+    R.tpref_planner_destroy.argtypes = [vp]
+    for name, args in (("set_limits", [c_double_p, c_double_p]),
+                       ("set_waypoints", [C.c_int, c_double_p]),
+                       ("set_initial_velocity", [c_double_p]),
+                       ("plan", [C.c_int64, C.c_int64]),
+                       ("switch", [C.c_double, C.c_int, c_double_p]),
+                       ("stop_parameter", [C.c_int64, c_double_p])):
+        f = getattr(R, "tpref_planner_" + name)
+        f.restype = C.c_int
+        f.argtypes = [vp] + args
+    for name, args in (("state", [i64p]), ("scalars", [c_double_p]),
+                       ("rows", [c_double_p] * 7), ("path_samples", [c_double_p] * 7),
+                       ("window", [c_double_p] * 7), ("constraints", [c_double_p]),
+                       ("spline", [ip, c_double_p, C.c_int, c_double_p, C.c_int])):
+        f = getattr(R, "tpref_planner_" + name)
+        f.restype = None
+        f.argtypes = [vp] + args
+    R.tpref_plan_joint_batch.restype = None
+    R.tpref_plan_joint_batch.argtypes = [
+        C.c_int, C.c_int, C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, C.c_double,
+        C.c_double, C.c_int64, C.c_int, C.c_int, i32p, c_double_p, i32p, i64p, c_double_p,
+        c_double_p]
+
+
 def have_ref() -> bool:
     return os.path.exists(_REF_SO)
 
@@ -311,6 +343,7 @@ def ref():
         R.tpref_time_from_sec_ns.argtypes = [C.c_double]
         R.tpref_time_to_sec.restype = C.c_double
         R.tpref_time_to_sec.argtypes = [C.c_int64]
+        _register_ref_planner(R)
         _ref = R
     return _ref
 
@@ -566,6 +599,176 @@ class Planner:
 
     def __getattr__(self, name):  # state fields: len, M, end_time, planned_to_end, ...
         return getattr(self.__dict__["c"], name)
+
+
+#: absl::StatusCode an ORC_* planner status corresponds to (ref_wrap_planner.cc returns
+#: the reference's own codes)
+ABSL_OF_ORC = {0: 0, 1: 13, 2: 13, 3: 13, 4: 13, 5: 13, ORC_FAIL_DEADLINE: 4,
+               ORC_FAIL_START_RANGE: 11, ORC_FAIL_START_ARG: 3, ORC_FAIL_START_END: 13,
+               ORC_FAIL_NO_SAMPLES: 9, ORC_FAIL_INITIAL_VELOCITY: 3}
+#: TimeablePath::State of the reference -> the oracle's `sampled` field
+#: (0 kNewPath, 1 kPathWasSampled, 2 kModifiedPath)
+ORC_STATE_OF_REF = {1: 0, 3: 1, 2: 2}
+
+
+class RefPlanner:
+    """The REFERENCE's own TimeableJointSplinePath + PathTimingTrajectory object code
+    (oracle/_ref, ref_wrap_planner.cc) behind the interface of `Planner`.  plan() and
+    switch() return absl::StatusCode numbers."""
+
+    _STATE = ("start_time", "end_time", "final_decel_start", "planned_to_end", "target_reached",
+              "path_state", "initial_plan", "M", "len", "last_extremal_index", "at_end")
+
+    def __init__(self, waypoints, vmax, amax, N, delta, dt, rounding=0.2, safety=0.8, skip=False,
+                 max_planning_iterations=200, initial_velocity=None,
+                 max_initial_velocity_error=1e-4):
+        wp = np.ascontiguousarray(waypoints, np.float64)
+        self.W, self.D = wp.shape
+        self.N = N
+        dt_ns = int(round(dt * 1e9))
+        assert dt_ns * 1e-9 == dt or abs(dt_ns / 1e9 - dt) == 0.0, "dt must be whole ns"
+        self._h = ref().tpref_planner_create(N, self.D, rounding, safety, float(delta), dt_ns,
+                                             1 if skip else 0, max_planning_iterations,
+                                             max_initial_velocity_error)
+        R = ref()
+        st = R.tpref_planner_set_limits(self._h, _dp(np.ascontiguousarray(vmax, np.float64)),
+                                        _dp(np.ascontiguousarray(amax, np.float64)))
+        assert st == 0, st
+        if initial_velocity is not None:
+            iv = np.ascontiguousarray(initial_velocity, np.float64)
+            R.tpref_planner_set_initial_velocity(self._h, _dp(iv))
+        self.set_status = R.tpref_planner_set_waypoints(self._h, self.W, _dp(wp))
+
+    def close(self):
+        if self._h:
+            ref().tpref_planner_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # interpreter shutdown
+            pass
+
+    def set_waypoints(self, waypoints):
+        wp = np.ascontiguousarray(waypoints, np.float64)
+        return ref().tpref_planner_set_waypoints(self._h, wp.shape[0], _dp(wp))
+
+    def plan(self, start_ns, horizon_ns):
+        return ref().tpref_planner_plan(self._h, int(start_ns), int(horizon_ns))
+
+    def switch(self, keep_path_until, waypoints, initial_velocity=None):
+        wp = np.ascontiguousarray(waypoints, np.float64)
+        st = ref().tpref_planner_switch(self._h, float(keep_path_until), wp.shape[0], _dp(wp))
+        if initial_velocity is not None:
+            iv = np.ascontiguousarray(initial_velocity, np.float64)
+            st2 = ref().tpref_planner_set_initial_velocity(self._h, _dp(iv))
+            st = st or st2
+        return st
+
+    def stop_parameter(self, time_ns):
+        out = C.c_double(float("nan"))
+        st = ref().tpref_planner_stop_parameter(self._h, int(time_ns), C.byref(out))
+        return st, out.value
+
+    def state(self):
+        a = np.zeros(11, np.int64)
+        ref().tpref_planner_state(self._h, a.ctypes.data_as(C.POINTER(C.c_int64)))
+        return dict(zip(self._STATE, (int(x) for x in a)))
+
+    def scalars(self):
+        a = np.zeros(4)
+        ref().tpref_planner_scalars(self._h, _dp(a))
+        return dict(delta=a[0], knot_end=a[1], path_horizon=a[2], path_start=a[3])
+
+    def spline(self):
+        cnt = (C.c_int * 2)()
+        kn, pts = np.zeros(4096), np.zeros((4096, self.D))
+        ref().tpref_planner_spline(self._h, cnt, _dp(kn), 4096, _dp(pts), 4096)
+        return kn[:cnt[0]].copy(), pts[:cnt[1]].copy()
+
+    def trajectory(self):
+        M, D = self.state()["M"], self.D
+        r = {k: np.zeros(M) for k in ("r_t", "r_s", "r_sd", "r_sdd")}
+        r.update({k: np.zeros((M, D)) for k in ("r_pos", "r_vel", "r_acc")})
+        ref().tpref_planner_rows(self._h, _dp(r["r_t"]), _dp(r["r_pos"]), _dp(r["r_vel"]),
+                                 _dp(r["r_acc"]), _dp(r["r_s"]), _dp(r["r_sd"]), _dp(r["r_sdd"]))
+        return r
+
+    def path_samples(self):
+        n, D = self.state()["len"], self.D
+        w = {k: np.zeros(n) for k in ("w_time", "w_s", "w_sd", "w_sdd")}
+        w.update({k: np.zeros((n, D)) for k in ("w_q", "w_vel", "w_acc")})
+        ref().tpref_planner_path_samples(self._h, _dp(w["w_time"]), _dp(w["w_s"]), _dp(w["w_sd"]),
+                                         _dp(w["w_sdd"]), _dp(w["w_q"]), _dp(w["w_vel"]),
+                                         _dp(w["w_acc"]))
+        return w
+
+    def window(self):
+        N, D = self.N, self.D
+        o = {k: np.full(N, np.nan) for k in ("time", "s", "sd", "sdd")}
+        o.update({k: np.zeros((N, D)) for k in ("q", "dq", "ddq")})
+        ref().tpref_planner_window(self._h, _dp(o["q"]), _dp(o["dq"]), _dp(o["ddq"]),
+                                   _dp(o["time"]), _dp(o["s"]), _dp(o["sd"]), _dp(o["sdd"]))
+        return o
+
+    def constraints(self):
+        c = np.zeros((self.N, 2 * self.D, 4))
+        ref().tpref_planner_constraints(self._h, _dp(c))
+        return c
+
+
+def plan_joint_ref(waypoints, vmax, amax, N, rounding=0.2, safety=0.8, delta=-1.0, dt=0.004,
+                   skip=False, start_ns=0):
+    """plan_joint() run by NOTHING BUT the reference's object code: SetWaypoints + one
+    Plan() of a fresh path (whole path in one window when delta <= 0).  Same keys as
+    plan_joint(); `status` is the absl code."""
+    p = RefPlanner(waypoints, vmax, amax, N, delta, dt, rounding, safety, skip)
+    # a 1 ns horizon: Plan() stops after the first window also when that window ends
+    # inside the path (time_horizon_reached, path_timing_trajectory.cc:645-647)
+    st = p.set_status or p.plan(start_ns, 1)
+    res = p.window()
+    w = p.path_samples()
+    sc, state = p.scalars(), p.state()
+    res.update(p.trajectory())
+    ok = st == 0
+    res.update(status=st, ok=ok, delta=sc["delta"], knot_end=sc["knot_end"], M=state["M"],
+               last_extremal_index=state["last_extremal_index"],
+               duration=(res["time"][-1] - res["time"][0]) if ok else float("nan"),
+               vel=w["w_vel"], acc=w["w_acc"], cons=p.constraints(), spline=p.spline())
+    p.close()
+    return res
+
+
+def plan_joint_batch_ref(waypoints, vmax, amax, N, dt=0.004, rounding=0.2, safety=0.8,
+                         skip=False, threads=1, r_offset=None, want_time=False):
+    """B fresh joint paths through the reference's own classes on `threads` host threads
+    (tpref_plan_joint_batch: no Python in the loop).  Returns status [B] (absl codes),
+    duration [B], rows [B] and, on request, the positions packed at r_offset and the
+    profiles' time stamps."""
+    wp = np.ascontiguousarray(waypoints, np.float64)
+    B, W, D = wp.shape
+    vmax = np.ascontiguousarray(vmax, np.float64)
+    amax = np.ascontiguousarray(amax, np.float64)
+    status, rows = np.zeros(B, np.int32), np.zeros(B, np.int32)
+    duration = np.zeros(B)
+    off = r_pos = None
+    if r_offset is not None:
+        off = np.ascontiguousarray(r_offset, np.int64)
+        r_pos = np.full((int(off[-1]), D), np.nan)
+    ptime = np.full((B, N), np.nan) if want_time else None
+    i32 = lambda a: a.ctypes.data_as(C.POINTER(C.c_int32))
+    ref().tpref_plan_joint_batch(
+        B, N, D, W, _dp(wp), _dp(vmax), _dp(amax), rounding, safety, int(round(dt * 1e9)),
+        1 if skip else 0, int(threads), i32(status), _dp(duration), i32(rows),
+        off.ctypes.data_as(C.POINTER(C.c_int64)) if off is not None else None, _dp(r_pos),
+        _dp(ptime))
+    out = dict(status=status, duration=duration, rows=rows)
+    if r_pos is not None:
+        out["r_pos"] = r_pos
+    if ptime is not None:
+        out["time"] = ptime
+    return out
 
 
 class Spline:
