@@ -279,6 +279,43 @@ int32_t tpb_resample(tpb_engine* e, double start_sec, double time_step_sec,
 int32_t tpb_resample_skipping(tpb_engine* e, double start_sec, double time_step_sec,
                               int64_t* total_samples);
 
+/* ---- allocation-free uniform resampling ------------------------------------- */
+/* NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  The same kernels and results as tpb_resample
+ * (ResampleEquidistantlyInTime), without an engine: every input and output is a
+ * caller-provided DEVICE array, the call allocates nothing (no cudaMalloc / cudaFree,
+ * no allocating library routine) and is asynchronous on cuda_stream.
+ *
+ * Scratch: the per-path row counts live in a file-scope `static __device__` array of
+ * TPB_NOALLOC_MAX_PATHS = 65,536 int32 (256 KiB, held by every GPU that loads the
+ * library until the process exits).  num_paths beyond that is rejected with
+ * TPB_OUT_OF_RANGE and a message.  All calls share the array and it keeps the last
+ * call's contents (every entry a call uses is overwritten first, so nothing has to be
+ * cleared): calls that OVERLAP on one GPU -- different streams or host threads -- race
+ * on it; serialise them.
+ *
+ * Rows beyond row_capacity are dropped; r_offset[num_paths] holds the number of rows
+ * the batch needs.  error_message (may be NULL) receives a text for a non-zero return. */
+#define TPB_NOALLOC_MAX_PATHS 65536
+typedef struct {
+  int32_t device;      /* CUDA device ordinal of all pointers below */
+  int32_t num_paths;   /* B <= TPB_NOALLOC_MAX_PATHS */
+  int32_t num_samples; /* N path samples per path */
+  int32_t num_dofs;    /* D <= 16 */
+  const double *time, *s, *sd, *sdd; /* [B][N]: the profile (TPB_ARR_TIME, _S, _SD, _SDD) */
+  const double *q, *dq, *ddq;        /* [B][N][D]: SamplePath (TPB_ARR_Q, _DQ, _DDQ) */
+  const double* max_acceleration;    /* [B][D] */
+  const int32_t* status;             /* [B] TPB_PATH_*, paths != 0 get no rows; NULL: all ok */
+  double start_sec, time_step_sec;
+  int64_t row_capacity;              /* rows the r_* arrays hold */
+  int64_t* r_offset;                 /* out [B + 1] */
+  double *r_time, *r_s, *r_sd, *r_sdd; /* out [row_capacity] */
+  double *r_pos, *r_vel, *r_acc;       /* out [row_capacity][D] */
+} tpb_resample_desc;
+int32_t tpb_resample_uniform_noalloc(const tpb_resample_desc* d, void* cuda_stream,
+                                     char* error_message, size_t error_capacity);
+
 /* ---- PathTimingTrajectory::Plan with its state between calls ----------------- */
 /* (path_timing_trajectory.cc:477-684) for every joint path of the batch: the
  * moving-horizon loop over planning windows of num_path_samples samples

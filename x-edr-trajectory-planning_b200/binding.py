@@ -56,6 +56,16 @@ class _PlanIO(C.Structure):
                 ("r_total", C.c_int64)]
 
 
+class _ResampleDesc(C.Structure):
+    """tpb_resample_desc (include/tpb.h)"""
+    _fields_ = [("device", C.c_int32), ("num_paths", C.c_int32), ("num_samples", C.c_int32),
+                ("num_dofs", C.c_int32)] + [(n, C.c_void_p) for n in (
+                    "time", "s", "sd", "sdd", "q", "dq", "ddq", "max_acceleration", "status")] + [
+        ("start_sec", C.c_double), ("time_step_sec", C.c_double), ("row_capacity", C.c_int64)] + [
+        (n, C.c_void_p) for n in ("r_offset", "r_time", "r_s", "r_sd", "r_sdd", "r_pos", "r_vel",
+                                  "r_acc")]
+
+
 class _StopDesc(C.Structure):
     _fields_ = [("num_trajectories", C.c_int32), ("num_dofs", C.c_int32),
                 ("total_rows", C.c_int64)] + [(n, C.c_void_p) for n in (
@@ -171,6 +181,9 @@ def lib():
         L.tpb_path_stop_parameter.argtypes = [vp, vp, vp, vp, vp, vp, i32]
         L.tpb_rescale_to_stop_device.restype = i32
         L.tpb_rescale_to_stop_device.argtypes = [C.POINTER(_StopDesc), vp]
+        L.tpb_resample_uniform_noalloc.restype = i32
+        L.tpb_resample_uniform_noalloc.argtypes = [C.POINTER(_ResampleDesc), vp, C.c_char_p,
+                                                   C.c_size_t]
         L.tpb_rescale_to_stop_host.restype = i32
         L.tpb_rescale_to_stop_host.argtypes = [C.POINTER(_StopDesc), i32]
         # trajectory buffers
@@ -617,6 +630,19 @@ def rescale_to_stop_device(max_acceleration, begin, length, times, velocities, a
     rc = lib().tpb_rescale_to_stop_device(C.byref(d), stream)
     if rc != 0:
         raise TpbError(rc, "tpb_rescale_to_stop_device")
+
+
+def resample_uniform_noalloc(device, num_paths, num_samples, num_dofs, inputs, outputs, start_sec,
+                             time_step_sec, row_capacity, stream=None):
+    """tpb_resample_uniform_noalloc: `inputs` / `outputs` map the field names of
+    tpb_resample_desc to raw device addresses (ints; status may be None).  Asynchronous on
+    `stream`.  Returns (status code, error message); allocates nothing on the device."""
+    d = _ResampleDesc(device=device, num_paths=num_paths, num_samples=num_samples,
+                      num_dofs=num_dofs, start_sec=start_sec, time_step_sec=time_step_sec,
+                      row_capacity=row_capacity, **inputs, **outputs)
+    msg = C.create_string_buffer(256)
+    rc = lib().tpb_resample_uniform_noalloc(C.byref(d), stream, msg, len(msg))
+    return rc, msg.value.decode()
 
 
 def measure_fp64_fma_peak(device=0):

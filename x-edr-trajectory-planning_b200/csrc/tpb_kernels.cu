@@ -765,3 +765,138 @@ int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, doub
 }
 
 }  // namespace tpb
+
+// ===========================================================================
+// Allocation-free uniform-in-time resampling (tpb_resample_uniform_noalloc).
+// No counterpart in the reference; added for
+// callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops).
+// The per-path row counts -- the scratch the engine keeps in TPB's r_count array --
+// live in a file-scope device array instead, so the call allocates nothing.
+// ===========================================================================
+// TPB_NOALLOC_MAX_PATHS (include/tpb.h) = 65,536 paths.
+// 256 KiB per GPU that loads the library, held until the process exits.  Shared by
+// every call: calls that overlap on one GPU race on it.
+static __device__ __align__(256) int32_t g_noalloc_row_count[TPB_NOALLOC_MAX_PATHS];
+
+namespace tpb {
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+// device address of g_noalloc_row_count per device ordinal.  In host code the array's
+// name is only a stand-in for the symbol; the kernels need this address.
+int32_t* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+int g_noalloc_sms[kNoAllocMaxDevices] = {};
+
+// k_resample_count for caller-provided arrays: status may be null (every path timed)
+__global__ void k_resample_count_any(Dims dm, DeviceArrays a, double start_sec, double dt) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= dm.B) return;
+  int m = 0;
+  if (a.status == nullptr || a.status[b] == TPB_PATH_OK) {
+    const double duration = a.time[static_cast<size_t>(b) * dm.N + dm.N - 1] - start_sec;
+    const double c = ceil(duration / dt) + 1;
+    m = (c > 0 && c < 2.0e9) ? static_cast<int>(c) : 0;
+  }
+  a.r_count[b] = m;
+}
+
+void set_error(char* buf, size_t cap, const char* msg) {
+  if (buf == nullptr || cap == 0) return;
+  std::strncpy(buf, msg, cap - 1);
+  buf[cap - 1] = '\0';
+}
+}  // namespace
+}  // namespace tpb
+
+extern "C" int32_t tpb_resample_uniform_noalloc(const tpb_resample_desc* d, void* cuda_stream,
+                                                char* error_message, size_t error_capacity) {
+  using namespace tpb;
+  set_error(error_message, error_capacity, "");
+  if (d == nullptr) {
+    set_error(error_message, error_capacity, "descriptor is null");
+    return TPB_INVALID_ARGUMENT;
+  }
+  if (d->num_paths < 1 || d->num_paths > TPB_NOALLOC_MAX_PATHS) {
+    set_error(error_message, error_capacity,
+              "num_paths outside [1, 65536] (TPB_NOALLOC_MAX_PATHS: the static scratch array "
+              "holds one row count per path)");
+    return TPB_OUT_OF_RANGE;
+  }
+  if (d->num_samples < 2 || d->num_dofs < 1 || d->num_dofs > kMaxDofs) {
+    set_error(error_message, error_capacity, "num_samples < 2 or num_dofs outside [1, 16]");
+    return TPB_OUT_OF_RANGE;
+  }
+  if (!(d->time_step_sec > 0) || d->row_capacity < 0) {
+    set_error(error_message, error_capacity, "time step must be positive, row_capacity >= 0");
+    return TPB_INVALID_ARGUMENT;
+  }
+  if (d->device < 0 || d->device >= kNoAllocMaxDevices) {
+    set_error(error_message, error_capacity, "device ordinal outside [0, 64)");
+    return TPB_OUT_OF_RANGE;
+  }
+  const void* need[] = {d->time, d->s, d->sd, d->sdd, d->q, d->dq, d->ddq, d->max_acceleration,
+                        d->r_offset, d->r_time, d->r_s, d->r_sd, d->r_sdd, d->r_pos, d->r_vel,
+                        d->r_acc};
+  for (const void* p : need) {
+    if (p == nullptr) {
+      set_error(error_message, error_capacity, "a required device pointer is null");
+      return TPB_INVALID_ARGUMENT;
+    }
+  }
+  if (cudaSetDevice(d->device) != cudaSuccess) {
+    set_error(error_message, error_capacity, "cudaSetDevice failed");
+    return TPB_FAILED_PRECONDITION;
+  }
+  if (g_noalloc_ptr[d->device] == nullptr) {
+    // once per device, with that device current
+    void* ptr = nullptr;
+    const cudaError_t err = cudaGetSymbolAddress(&ptr, g_noalloc_row_count);
+    if (err != cudaSuccess || ptr == nullptr) {
+      set_error(error_message, error_capacity, cudaGetErrorString(err));
+      return TPB_INTERNAL;
+    }
+    int sms = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, d->device) != cudaSuccess ||
+        sms < 1) {
+      set_error(error_message, error_capacity, "cudaDeviceGetAttribute failed");
+      return TPB_INTERNAL;
+    }
+    g_noalloc_sms[d->device] = sms;
+    g_noalloc_ptr[d->device] = static_cast<int32_t*>(ptr);
+  }
+  Dims dm;
+  dm.B = dm.Bmax = d->num_paths;
+  dm.D = d->num_dofs;
+  dm.N = d->num_samples;
+  dm.r_cap = d->row_capacity;
+  DeviceArrays a;
+  a.time = const_cast<double*>(d->time);
+  a.s = const_cast<double*>(d->s);
+  a.sd = const_cast<double*>(d->sd);
+  a.sdd = const_cast<double*>(d->sdd);
+  a.q = const_cast<double*>(d->q);
+  a.dq = const_cast<double*>(d->dq);
+  a.ddq = const_cast<double*>(d->ddq);
+  a.amax = const_cast<double*>(d->max_acceleration);
+  a.status = const_cast<int32_t*>(d->status);
+  a.r_count = g_noalloc_ptr[d->device];  // every entry is overwritten: nothing to clear
+  a.r_offset = d->r_offset;
+  a.r_time = d->r_time;
+  a.r_s = d->r_s;
+  a.r_sd = d->r_sd;
+  a.r_sdd = d->r_sdd;
+  a.r_pos = d->r_pos;
+  a.r_vel = d->r_vel;
+  a.r_acc = d->r_acc;
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  const int threads = 128;
+  k_resample_count_any<<<(dm.B + threads - 1) / threads, threads, 0, st>>>(dm, a, d->start_sec,
+                                                                          d->time_step_sec);
+  launch_resample_rows(dm, a, ResampleView{}, nullptr, d->start_sec, d->time_step_sec,
+                       g_noalloc_sms[d->device], st, /*skip=*/false, /*continued=*/false);
+  const cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) {
+    set_error(error_message, error_capacity, cudaGetErrorString(err));
+    return TPB_INTERNAL;
+  }
+  return TPB_OK;
+}
