@@ -42,6 +42,26 @@ WORKLOAD = ("cfg2: 4096 synthetic 7-DoF joint-spline paths x 2048 samples per GP
             "time-optimal timing + 4 ms uniform resampling")
 
 
+def _csrc_hash():
+    """Hash of the CUDA sources; profiles/fp64_ops.json and traffic.json carry the hash of
+    the build they were captured from ("_csrc_hash"), so stale counters are visible."""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(ROOT, "x-edr-trajectory-planning_b200", "csrc", "*.cu*"))):
+        with open(f, "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def _stale(path):
+    try:
+        with open(path) as f:
+            return json.load(f).get("_csrc_hash") != _csrc_hash()
+    except (OSError, ValueError):
+        return True
+
+
 def _traffic(kernel):
     """DRAM bytes per launch of `kernel` from the committed `ncu --set full` capture
     (profiles/traffic.json: dram__bytes_read.sum + dram__bytes_write.sum), or None."""
@@ -66,7 +86,8 @@ def _fp64_report(pkg, device, kernel_ms):
         return None
     peak = pkg.measure_fp64_fma_peak(device)
     out = {"peak_tflops": peak, "peak_source": "tpb_measure_fp64_fma_peak (8 FMA chains/thread)",
-           "ops_source": "profiles/fp64_ops.json (ncu --set full, same workload)", "kernels": {}}
+           "ops_source": "profiles/fp64_ops.json (ncu --set full, same workload)",
+           "stale": _stale(p), "kernels": {}}
     for k, ms in kernel_ms.items():
         if k in ops and ms > 0:
             tf = ops[k]["flops_per_launch"] / (ms / 1e3) / 1e12
@@ -132,12 +153,26 @@ class ClockSampler:
 # --------------------------------------------------------------------------
 # reference arm (CPU): oracle/_ref when compiled, else the oracle port
 # --------------------------------------------------------------------------
-def _cpu_paths_per_sec(po, wp, vmax, amax, threads, impl):
-    """Time the reference's CPU algorithm on `threads` host threads (ctypes
-    releases the GIL, so plain Python threads run the C code concurrently)."""
+def _cpu_paths_per_sec(po, wp, vmax, amax, threads, impl, r_offset=None):
+    """Time the reference's CPU algorithm on `threads` host threads.  impl "ref": every
+    path goes through the reference's own object code (TimeableJointSplinePath +
+    PathTimingTrajectory, oracle/_ref) inside ONE C call that spawns the threads
+    (tpref_plan_joint_batch: no Python, no per-path allocation of result arrays in the
+    timed loop).  impl "port": the C restatement, one ctypes call per path from Python
+    threads (only when oracle/_ref could not be built).  Returns paths/s, seconds, the
+    number of paths timed successfully and the per-path results."""
+    B = wp.shape[0]
+    if impl == "ref":
+        t0 = time.perf_counter()
+        res = po.plan_joint_batch_ref(wp, vmax, amax, NUM_SAMPLES, dt=TIME_STEP, threads=threads,
+                                      r_offset=r_offset)
+        dt = time.perf_counter() - t0
+        return B / dt, dt, int((res["status"] == 0).sum()), res
+
     from concurrent.futures import ThreadPoolExecutor
 
-    B = wp.shape[0]
+    dur = np.full(B, np.nan)
+    rows = np.zeros(B, np.int32)
 
     def work(lo_hi):
         lo, hi = lo_hi
@@ -146,6 +181,7 @@ def _cpu_paths_per_sec(po, wp, vmax, amax, threads, impl):
             r = po.plan_joint(wp[b], vmax[b], amax[b], NUM_SAMPLES, dt=TIME_STEP,
                               M_cap=16384, impl=impl)
             ok += bool(r["ok"])
+            dur[b], rows[b] = r["duration"], r["M"]
         return ok
 
     chunks = [(i * B // threads, (i + 1) * B // threads) for i in range(threads)]
@@ -153,7 +189,8 @@ def _cpu_paths_per_sec(po, wp, vmax, amax, threads, impl):
     with ThreadPoolExecutor(threads) as ex:
         ok = sum(ex.map(work, chunks))
     dt = time.perf_counter() - t0
-    return B / dt, dt, ok
+    return B / dt, dt, ok, {"duration": dur, "rows": rows,
+                            "status": np.where(np.isnan(dur), 13, 0).astype(np.int32)}
 
 
 def _cpu_setup():
@@ -165,47 +202,65 @@ def _cpu_setup():
     return po, impl, kind, cores
 
 
+def _config():
+    """The workload description BOTH arms print (identical keys and values)."""
+    return {"workload": WORKLOAD, "paths_per_gpu_per_step": PATHS_PER_GPU,
+            "num_samples": NUM_SAMPLES, "num_dofs": NUM_DOFS, "num_waypoints": NUM_WAYPOINTS,
+            "time_step_s": TIME_STEP,
+            "l2": "per-step working set ~2 GB (> 126 MB L2), no flush needed"}
+
+
+def _quiet_stderr():
+    """The reference logs "Negative sd2" / "Unbounded problem" hints to stderr."""
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    saved = os.dup(2)
+    os.dup2(devnull, 2)
+    return saved
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     pkg = load_package()
     po, impl, kind, cores = _cpu_setup()
-    # bounded sample: the first min(4096, 256 * cores) paths of the cfg2 batch per step
-    # (about 1 s of wall time on all host cores, i.e. ~cores seconds of CPU work)
-    sample = min(PATHS_PER_GPU, 256 * cores)
+    # one step = the 4,096 paths of the cfg2 batch once on all host threads (~1 s of wall
+    # time on 16 threads); the host does not grow with --gpus, so neither does the sample
+    sample = PATHS_PER_GPU
     wp, vmax, amax = pkg.workloads.joint_paths(PATHS_PER_GPU, NUM_WAYPOINTS, NUM_DOFS, 1000)
-    wp, vmax, amax = wp[:sample], vmax[:sample], amax[:sample]
-    devnull = os.open(os.devnull, os.O_WRONLY)
-    saved = os.dup(2)
-    os.dup2(devnull, 2)  # the reference logs "Negative sd2" hints to stderr
+    saved = _quiet_stderr()
     try:
         for _ in range(args.warmup):
             _cpu_paths_per_sec(po, wp, vmax, amax, cores, impl)
         times = []
         for _ in range(args.steps):
-            _, dt, _ = _cpu_paths_per_sec(po, wp, vmax, amax, cores, impl)
+            _, dt, ok, _ = _cpu_paths_per_sec(po, wp, vmax, amax, cores, impl)
             times.append(dt)
+        # the single-thread figure on a bounded sample (the reference is single-threaded)
+        one = min(sample, 128)
+        v1, dt1, _, _ = _cpu_paths_per_sec(po, wp[:one], vmax[:one], amax[:one], 1, impl)
     finally:
         os.dup2(saved, 2)
     ms = 1e3 * float(np.mean(times))
     value = sample / (ms / 1e3)
-    desc = (f"first {sample} paths of the cfg2 batch per step; stage C = reference "
-            f"time_optimal_path_timing.cc compiled verbatim (oracle/_ref), stages A/B/D = C "
-            f"restatement" if kind == "reference" else
-            f"first {sample} paths of the cfg2 batch per step; C restatement of all stages")
+    desc = (f"the {sample} paths of the cfg2 batch per step; every stage is the reference's own "
+            f"object code (TimeableJointSplinePath + PathTimingTrajectory compiled verbatim, "
+            f"oracle/_ref), one path per task, threads spawned inside one C call"
+            if kind == "reference" else
+            f"the {sample} paths of the cfg2 batch per step; C restatement of all stages")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic",
-        "config": {"workload": WORKLOAD, "paths_per_step": sample, "num_samples": NUM_SAMPLES,
-                   "num_dofs": NUM_DOFS, "host_threads": cores},
+        "data": "synthetic", "config": _config(),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
-                         "sample": desc},
+                         "sample": desc, "paths_ok": ok,
+                         "single_thread": {"value": v1, "unit": UNIT, "cores": 1,
+                                           "sample": f"first {one} paths, {dt1:.1f} s"},
+                         "per_thread": value / cores},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "host_threads": cores,
     }))
 
 
@@ -350,22 +405,34 @@ def run_ours(args):
     achieved = alg_bytes / (kernel_ms[dom] / 1e3) / 1e9
     kernel_names = {"sample_limit": "k_joint_sample_limit", "integrate": "k_integrate",
                     "optimize": "k_optimize_pair", "resample": "k_resample_fill"}
-    roofline = {"bound": "hbm", "kernel": kernel_names[dom], "achieved": achieved,
-                "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": _traffic(kernel_names[dom]),
-                "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
-                "avg_launch_ms": kernel_ms[dom],
-                "note": ("the sweeps are a sequential FP64 phase-plane integration, two paths "
-                         "per warp: bound by dependent-instruction latency and FP64 issue, "
-                         "not by HBM (DESIGN.md)")
-                if dom in ("integrate", "optimize") else ""}
     if split:
         stage_ms["integrate_phases"] = {"setup": phase_ms[0], "sweeps": phase_ms[1],
                                         "finalize": phase_ms[2]}
     fp64 = _fp64_report(pkg, local_rank, {"k_joint_sample_limit": stage_ms["sample_limit"],
                                            "k_integrate_setup": phase_ms[0],
                                            "k_optimize_pair": phase_ms[1],
-                                           "k_integrate_finalize": phase_ms[2]} if split else {})
+                                           "k_integrate_finalize": phase_ms[2],
+                                           "k_resample_fill": stage_ms["resample"]} if split else {})
+    hbm = {"achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+           "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src}
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    fk = (fp64 or {}).get("kernels", {}).get(kernel_names[dom])
+    if dom == "resample" or fk is None:
+        # a streaming kernel: HBM is its roof
+        roofline = dict(hbm, bound="hbm", kernel=kernel_names[dom])
+    else:
+        # limit curve / phase-plane sweeps: FP64 arithmetic on a sequential dependence
+        # chain.  The roof SURVEY 8(d) names is the FP64 pipe; HBM is shown beside it.
+        roofline = {"bound": "fp64/latency", "kernel": kernel_names[dom],
+                    "achieved": fk["tflops"], "peak": fp64["peak_tflops"], "unit": "TFLOP/s",
+                    "frac": fk["frac_of_fma_peak"], "flops_per_launch": fk["flops_per_launch"],
+                    "fp64_pipe_pct_ncu": fk["fp64_pipe_pct_ncu"],
+                    "peak_source": fp64["peak_source"], "hbm": hbm,
+                    "note": "sequential FP64 phase-plane integration: bound by the dependent-"
+                            "instruction chain of one extremal step and FP64 issue, not by HBM "
+                            "(DESIGN.md 4)"}
+    roofline.update(traffic=_traffic(kernel_names[dom]), avg_launch_ms=kernel_ms[dom],
+                    stale=_stale(traffic_file) or bool(fp64 and fp64["stale"]))
 
     # ---- stopping trajectories on the resident resampled batch ----
     stop = run_stop_leg(pkg, torch, dev, stream, eng, d_amax, B, D, max_over_ranks, barrier,
@@ -429,46 +496,91 @@ def run_ours(args):
     else:
         all_dur = durations
 
-    cpu_baseline = None
+    cpu_baseline, parity = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         po, impl, kind, cores = _cpu_setup()
-        # bounded sample sized for 10-30 s of CPU work: ~4 ms per path per core
-        sample = min(B, 256 * cores)
-        devnull = os.open(os.devnull, os.O_WRONLY)
-        saved = os.dup(2)
-        os.dup2(devnull, 2)
+        # bounded sample: the 4,096 paths of this batch once on all host threads (10-30
+        # core-seconds) + the first 128 on one thread.  The results are not thrown away:
+        # every path's duration, row count and resampled positions are compared with the
+        # GPU's (the e2e leg's host buffers).
+        gpu_off = out["r_offset"].numpy()
+        saved = _quiet_stderr()
         try:
             _cpu_paths_per_sec(po, wp[:cores], vmax[:cores], amax[:cores], cores, impl)
-            v, dt, ok = _cpu_paths_per_sec(po, wp[:sample], vmax[:sample], amax[:sample],
-                                           cores, impl)
+            v, dt, ok, res = _cpu_paths_per_sec(po, wp, vmax, amax, cores, impl,
+                                                r_offset=gpu_off if impl == "ref" else None)
+            one = min(B, 128)
+            v1, dt1, _, _ = _cpu_paths_per_sec(po, wp[:one], vmax[:one], amax[:one], 1, impl)
         finally:
             os.dup2(saved, 2)
+        what = ("every stage = the reference's own object code, oracle/_ref"
+                if kind == "reference" else "oracle port")
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
-                        "sample": f"first {sample} paths of this batch, {dt:.1f} s wall = "
-                                  f"{dt * cores:.0f} core-seconds on {cores} host threads "
-                                  f"(stage C = reference .cc verbatim)"
-                        if kind == "reference" else
-                        f"first {sample} paths of this batch, {dt:.1f} s wall = "
-                        f"{dt * cores:.0f} core-seconds, oracle port"}
+                        "sample": f"the {B} paths of this batch, {dt:.1f} s wall = "
+                                  f"{dt * cores:.0f} core-seconds on {cores} host threads ({what})",
+                        "per_thread": v / cores,
+                        "single_thread": {"value": v1, "unit": UNIT, "cores": 1,
+                                          "sample": f"first {one} paths, {dt1:.1f} s"}}
+        gpu_dur = out["duration"].numpy()
+        gpu_ok = out["status"].numpy() == 0
+        cpu_ok = res["status"] == 0
+        both = gpu_ok & cpu_ok
+        rel = np.abs(gpu_dur[both] - res["duration"][both]) / res["duration"][both]
+        gpu_rows = np.diff(gpu_off)
+        parity = {"paths": int(B), "status_equal": bool(np.array_equal(gpu_ok, cpu_ok)),
+                  "paths_ok": int(both.sum()),
+                  "max_rel_duration_err": float(rel.max()) if rel.size else None,
+                  "durations_bit_equal": int((gpu_dur[both] == res["duration"][both]).sum()),
+                  "rows_equal": bool(np.array_equal(gpu_rows[both], res["rows"][both])),
+                  "tolerances": "duration 1e-6 relative, positions 1e-9 rad (BASELINE.json)",
+                  "against": what}
+        if "r_pos" in res:
+            d = np.abs(out["r_pos"].numpy() - res["r_pos"])
+            parity["max_abs_position_err_rad"] = float(np.nanmax(d))
+            parity["positions_compared"] = int(np.isfinite(d).sum())
+            parity["positions_bit_equal"] = int((out["r_pos"].numpy() == res["r_pos"]).sum())
 
     if rank == 0:
+        # the second half of the metric ("B-spline evals/sec vs HBM roofline"), compact:
+        # the headline configuration (degree 3, 7 dofs, two derivatives) and the worst one
+        spline_compact = None
+        if spline:
+            poly = {k: v for k, v in spline.items()
+                    if isinstance(v, dict) and "_" in k and k.count("_") == 1}
+            head = spline["p3_d7"]
+            worst = min(poly, key=lambda k: poly[k]["frac_of_peak"])
+            spline_compact = {
+                "kernel": "k_spline_eval_poly", "config": "cfg3 p3_d7: degree 3, 7 dofs, 2 derivatives, "
+                "4096 splines x 24576 parameters", "evals_per_s": head["evals_per_s"],
+                "achieved": head["hbm_gbs_per_gpu"], "peak": peak, "unit": "GB/s",
+                "frac": head["frac_of_peak"], "worst_config": worst,
+                "worst_frac": poly[worst]["frac_of_peak"],
+                "shuffled_u_frac": spline.get("p3_d7_shuffled", {}).get("frac_of_peak"),
+                "exact_mode_frac": spline.get("p3_d7_exact", {}).get("frac_of_peak")}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic",
-            "config": {"workload": WORKLOAD, "paths_per_gpu": B, "num_samples": N,
-                       "num_dofs": D, "num_waypoints": W, "time_step_s": TIME_STEP,
-                       "l2": "per-step working set ~2 GB per GPU (> 126 MB L2), no flush needed",
-                       "parallelism": f"independent-path sharding x{world}"},
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
+            "data": "synthetic", "config": _config(),
+            "spline_eval": spline_compact,
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "parity": parity, "e2e": e2e,
             "gpu_launches": int(launches), "clocks": clock_info,
             "stage_ms": stage_ms, "paths_ok": n_ok, "resampled_rows_per_gpu": total_rows,
             "mean_duration_s": float(np.nanmean(all_dur)),
-            "e2e_matches_device_run": same, "spline_eval": spline,
-            "fp64": fp64, "cartesian": cartesian, "stop": stop, "planner": planner,
-            "trajectory_buffer": tbuf,
+            "e2e_matches_device_run": same,
+            "parallelism": f"independent-path sharding x{world}, no data-path collective",
         }
+        # everything else (secondary legs) goes to a file, so that the line above survives
+        # the tail of any log: gpurun_out/bench_full.json
+        full = dict(line, spline_eval_full=spline, fp64=fp64, cartesian=cartesian, stop=stop,
+                    planner=planner, trajectory_buffer=tbuf)
+        try:
+            os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+            with open(os.path.join(ROOT, "gpurun_out", f"bench_full_n{world}.json"), "w") as f:
+                json.dump(full, f)
+            line["full"] = f"gpurun_out/bench_full_n{world}.json"
+        except OSError:
+            line["full"] = None
         print(json.dumps(line))
     eng.close()
     if world > 1:
@@ -793,6 +905,34 @@ def run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, wor
                 key = f"p{P}_d{D}" + ("_exact" if exact else "")
                 res[key] = {"evals_per_s": world * S * E / (ms / 1e3), "ms": ms,
                             "hbm_gbs_per_gpu": gbs, "frac_of_peak": gbs / peak}
+            # shuffled-u variant: the same parameters in random order per spline,
+            # read from an explicit array (8 B per evaluation more)
+            if (P, D) in ((3, 7), (5, 6)):
+                g = torch.Generator(device="cpu").manual_seed(1234 + P)
+                grid = torch.linspace(0.0, 8.0, E, dtype=torch.float64)
+                perm = torch.stack([grid[torch.randperm(E, generator=g)] for _ in range(8)])
+                d_u = perm.repeat(S // 8, 1).contiguous().to(dev)
+
+                def run_u():
+                    pkg.spline_eval_device(d_k, d_c, P, 2, o, u=d_u, exact=False,
+                                           stream=stream.cuda_stream)
+                for _ in range(3):
+                    run_u()
+                torch.cuda.synchronize()
+                barrier()
+                e0, e1 = (torch.cuda.Event(enable_timing=True),
+                          torch.cuda.Event(enable_timing=True))
+                e0.record(stream)
+                for _ in range(5):
+                    run_u()
+                e1.record(stream)
+                torch.cuda.synchronize()
+                ms = max_over_ranks(e0.elapsed_time(e1)) / 5
+                gbs = S * E * (3 * D * 8 + 8) / (ms / 1e3) / 1e9
+                res[f"p{P}_d{D}_shuffled"] = {"evals_per_s": world * S * E / (ms / 1e3), "ms": ms,
+                                              "hbm_gbs_per_gpu": gbs, "frac_of_peak": gbs / peak,
+                                              "bytes_per_eval": 3 * D * 8 + 8}
+                del d_u
     res["bytes_per_eval"] = "3*dim*8 written (implicit parameter grid, tables in smem)"
     res["modes"] = ("pP_dD: per-span polynomial form (<= 1e-12 of the reference); pP_dD_exact: "
                     "NURBS A2.3 in the reference's operation order (bit-identical, "
