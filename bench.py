@@ -442,39 +442,50 @@ def run_ours(args):
     tbuf = run_tbuf_leg(pkg, torch, dev, stream, local_rank, eng, d_amax, B, D, peak,
                         max_over_ranks, barrier, world, args)
 
-    # ---- e2e: host buffers in and out through tpb_plan_joint_host ----
+    # ---- e2e: the call a C++ user makes, PathTimingTrajectoryBatch::Plan (host class ->
+    # tpb_multi_plan_joint_host), host buffers in, page-locked result arrays out ----
     h_wp = torch.from_numpy(wp).pin_memory()
     h_vmax = torch.from_numpy(vmax).pin_memory()
     h_amax = torch.from_numpy(amax).pin_memory()
     rows = total_rows
-    out = {"duration": torch.empty(B, dtype=torch.float64).pin_memory(),
-           "status": torch.empty(B, dtype=torch.int32).pin_memory(),
-           "r_offset": torch.empty(B + 1, dtype=torch.int64).pin_memory()}
-    for k in ("r_pos", "r_vel", "r_acc"):
-        out[k] = torch.empty((rows, D), dtype=torch.float64).pin_memory()
-    for k in ("r_s", "r_sd", "r_sdd"):
-        out[k] = torch.empty(rows, dtype=torch.float64).pin_memory()
-
-    def step_host():
-        return eng.plan_joint_host(h_wp, h_vmax, h_amax, 0.0, TIME_STEP, out=out)
-
-    for _ in range(min(args.warmup, 3)):
-        step_host()
-    torch.cuda.synchronize()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        got = step_host()
-    torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0) / args.steps
-    barrier()
-    assert got == rows
+    hb = pkg.HostBatch(D, N, int(round(TIME_STEP * 1e9)), B, W, r_cap, devices=(local_rank,))
     h2d = wp.nbytes + vmax.nbytes + amax.nbytes
-    d2h = B * 8 + B * 4 + (B + 1) * 8 + rows * (3 * D + 3) * 8
-    e2e = {"value": B * world / e2e_s, "unit": UNIT, "ms_per_step": 1e3 * e2e_s,
-           "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-           "api": "tpb_plan_joint_host (pinned host buffers in/out)"}
+    PCIE_GBS = 55.0  # what one Gen5 x16 link sustains device-to-host (profiles/r1_d2h_scaling)
+
+    def e2e_leg(want, d2h_bytes):
+        for _ in range(min(args.warmup, 3)):
+            hb.plan(h_wp, h_vmax, h_amax, want=want)
+        torch.cuda.synchronize()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            got = hb.plan(h_wp, h_vmax, h_amax, want=want)
+        sec = max_over_ranks(time.perf_counter() - t0) / args.steps
+        barrier()
+        return got, {"value": B * world / sec, "unit": UNIT, "ms_per_step": 1e3 * sec,
+                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h_bytes),
+                     "pcie_frac": d2h_bytes / sec / 1e9 / PCIE_GBS}
+
+    fixed = B * 8 + B * 4 + (B + 1) * 8  # duration, status, offsets
+    got, e2e = e2e_leg("trajectory", fixed + rows * (3 * D + 3) * 8)
+    assert got == rows
+    e2e["api"] = ("PathTimingTrajectoryBatch::Plan (host C++ class, libtpb_hostapi.so): whole "
+                  "trajectory (positions, velocities, accelerations, s, sd, sdd)")
+    # keep copies of what the parity check below compares
+    out = {"duration": torch.from_numpy(hb.array("duration").copy()),
+           "status": torch.from_numpy(hb.array("status").copy()),
+           "r_offset": torch.from_numpy(hb.array("offset").copy()),
+           "r_pos": torch.from_numpy(hb.array("positions").reshape(-1, D).copy())}
     same = bool(np.array_equal(out["duration"].numpy(), durations, equal_nan=True))
+    # fewer bytes: a GetPositions() consumer, and a TimeOptimalPathProfile consumer
+    got, e2e_pos = e2e_leg("positions", fixed + rows * D * 8)
+    assert got == rows
+    same = same and np.array_equal(hb.array("positions").reshape(-1, D), out["r_pos"].numpy())
+    got, e2e_prof = e2e_leg("profile", B * 12 + 4 * B * N * 8)
+    same = same and bool(np.array_equal(hb.array("duration"), durations, equal_nan=True))
+    e2e["positions_only"] = e2e_pos
+    e2e["timing_only"] = e2e_prof
+    hb.close()
 
     # ---- dense spline evaluation sweep (BASELINE config 3) ----
     spline = run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, world,
@@ -487,6 +498,10 @@ def run_ours(args):
     # ---- moving-horizon re-planning ----
     planner = run_planner_leg(pkg, torch, dev, stream, local_rank, d_wp, d_vmax, d_amax, B, D, W,
                               max_over_ranks, barrier, world, args)
+
+    # ---- BASELINE config 4: 65,536 paths in total, strong-scaled over the ranks ----
+    cfg4 = run_cfg4_leg(pkg, torch, dev, stream, local_rank, rank, world, max_over_ranks,
+                        barrier, args)
 
     # ---- final gather of the per-path durations (outside any timed region) ----
     if world > 1:
@@ -564,6 +579,7 @@ def run_ours(args):
             "data": "synthetic", "config": _config(),
             "spline_eval": spline_compact,
             "roofline": roofline, "cpu_baseline": cpu_baseline, "parity": parity, "e2e": e2e,
+            "cfg4": cfg4,
             "gpu_launches": int(launches), "clocks": clock_info,
             "stage_ms": stage_ms, "paths_ok": n_ok, "resampled_rows_per_gpu": total_rows,
             "mean_duration_s": float(np.nanmean(all_dur)),
@@ -585,6 +601,89 @@ def run_ours(args):
     eng.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+CFG4_PATHS = 65536
+
+
+def run_cfg4_leg(pkg, torch, dev, stream, local_rank, rank, world, max_over_ranks, barrier, args):
+    """BASELINE config 4 as written: 65,536 synthetic 7-DoF paths x 2,048 samples IN TOTAL,
+    sharded over the ranks in the contiguous blocks of tpb_shard_range (strong scaling: at
+    N = 1 one GPU times all 65,536), independent-path partitioning, no data-path
+    collective; the only gather is durations + status to the host (timed in `e2e`).
+    Device-timed with CUDA events on the launching stream, max over ranks."""
+    if args.no_cfg4:
+        return None
+    N, D, W = NUM_SAMPLES, NUM_DOFS, NUM_WAYPOINTS
+    first, count = pkg.shard_range(CFG4_PATHS, world, rank)
+    wp, vmax, amax = pkg.workloads.joint_paths(CFG4_PATHS, W, D, seed=1000)
+    sl = slice(first, first + count)
+    wp, vmax, amax = wp[sl].copy(), vmax[sl].copy(), amax[sl].copy()
+    d_wp, d_vm, d_am = (torch.from_numpy(x).to(dev) for x in (wp, vmax, amax))
+    eng = pkg.Engine(max_paths=count, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=count * 4608, device=local_rank)
+    eng.set_stream(stream.cuda_stream)
+    eng.time_phases(True)
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+    stage = np.zeros(4)
+    phase = np.zeros(3)
+    reps = max(3, min(args.steps, 5))
+
+    def step():
+        evs[0].record(stream)
+        eng.set_joint_waypoints(d_wp)
+        eng.set_joint_limits(d_vm, d_am)
+        evs[1].record(stream)
+        eng.sample_paths()
+        evs[2].record(stream)
+        eng.optimize()
+        evs[3].record(stream)
+        eng.resample(0.0, TIME_STEP, want_total=False)
+        evs[4].record(stream)
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    barrier()
+    total_ms = 0.0
+    for _ in range(reps):
+        step()
+        torch.cuda.synchronize()
+        total_ms += evs[0].elapsed_time(evs[4]) / reps
+        stage += [evs[i].elapsed_time(evs[i + 1]) / reps for i in range(4)]
+        phase += np.array(eng.last_phase_ms()) / reps
+    ms = max_over_ranks(total_ms)
+    eng.time_phases(False)
+    status = eng.get(pkg.ARR.STATUS)
+    rows = int(eng.get(pkg.ARR.R_OFFSET)[-1])
+    # e2e: host waypoints in, durations + status out (SURVEY 8e's optional final gather);
+    # the trajectories stay on their GPUs for device-resident consumers
+    h = [torch.from_numpy(x).pin_memory() for x in (wp, vmax, amax)]
+    out = {"duration": torch.empty(count, dtype=torch.float64).pin_memory(),
+           "status": torch.empty(count, dtype=torch.int32).pin_memory()}
+    for _ in range(2):
+        eng.plan_joint_host(h[0], h[1], h[2], 0.0, TIME_STEP, out=out)
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        eng.plan_joint_host(h[0], h[1], h[2], 0.0, TIME_STEP, out=out)
+    e2e_s = max_over_ranks(time.perf_counter() - t0) / reps
+    ok = int((status == 0).sum())
+    eng.close()
+    del d_wp, d_vm, d_am
+    torch.cuda.empty_cache()
+    return {"paths_total": CFG4_PATHS, "paths_this_rank": count, "scaling": "strong",
+            "ms_per_step": ms, "paths_per_s": CFG4_PATHS / (ms / 1e3),
+            "stage_ms_rank0": {"fit": stage[0], "sample_limit": stage[1], "integrate": stage[2],
+                               "resample": stage[3], "setup": phase[0], "sweeps": phase[1],
+                               "finalize": phase[2]},
+            "paths_ok_rank0": ok, "rows_rank0": rows,
+            "e2e": {"value": CFG4_PATHS / e2e_s, "unit": UNIT, "ms_per_step": 1e3 * e2e_s,
+                    "h2d_bytes_per_step": int(wp.nbytes + vmax.nbytes + amax.nbytes),
+                    "d2h_bytes_per_step": int(count * 12),
+                    "api": "tpb_plan_joint_host, durations + status out (rows stay in HBM)"},
+            "partition": "tpb_shard_range: contiguous blocks of ceil(65536 / N) paths"}
 
 
 def run_planner_leg(pkg, torch, dev, stream, local_rank, d_wp, d_vmax, d_amax, B, D, W,
@@ -952,6 +1051,7 @@ def main():
     ap.add_argument("--no-stop", action="store_true")
     ap.add_argument("--no-planner", action="store_true")
     ap.add_argument("--no-tbuf", action="store_true")
+    ap.add_argument("--no-cfg4", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define TPB_ABI_VERSION 3
+#define TPB_ABI_VERSION 4
 
 /* absl::StatusCode values used by this library. */
 enum {
@@ -408,8 +408,64 @@ typedef struct {
   double* r_sdd;         /* [cap] */
   int64_t r_capacity;    /* rows available in r_* */
   int64_t r_total;       /* out: rows written */
+  /* ABI 4.  Every output pointer is optional: only the arrays a caller asks for cross
+   * PCIe (a GetPositions() consumer needs 8 * D bytes per row instead of 8 * (3 D + 3),
+   * a TimeOptimalPathProfile consumer 32 * N bytes per path and no rows at all). */
+  double* r_time;        /* [cap] GetTime() */
+  double* profile_time;  /* [B][N] GetTimeSamples() of the profile */
+  double* profile_s;     /* [B][N] GetPathParameter() */
+  double* profile_sd;    /* [B][N] GetPathVelocity() */
+  double* profile_sdd;   /* [B][N] GetPathAcceleration() */
 } tpb_plan_io;
 int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io);
+/* ---- multi-GPU front-end (csrc/tpb_multi.cu) ------------------------------- */
+/* The reference plans one path per PathTimingTrajectory::Plan call
+ * (path_timing_trajectory.cc:579-684) and paths are independent, so a batch shards
+ * over the GPUs of one box with no exchange step.  Shard g of G owns the
+ * contiguous block [g * ceil(B / G), (g + 1) * ceil(B / G)) of the batch
+ * (tpb_shard_range; processes that own one GPU each use the same rule), has its own
+ * engine and stream and is driven by its own host thread.  cfg->max_paths and
+ * cfg->max_time_samples_total are totals over all shards (every shard gets
+ * ceil(total / G)); cfg->device is ignored.  devices[g] = CUDA ordinal of shard g
+ * (NULL: g modulo the devices present; an ordinal may repeat = logical shards of one
+ * GPU).  No collective on the data path: every shard writes its own block of the
+ * caller's arrays (tpb_multi_plan_joint_host) or keeps its results on its GPU
+ * (tpb_multi_plan_joint_device + tpb_multi_shard / tpb_multi_gather). */
+typedef struct tpb_multi tpb_multi;
+/* Page-locked host memory (cudaMallocHost / cudaFreeHost) for callers that do not
+ * include the CUDA headers: outputs written there leave the GPU at the full PCIe rate. */
+int32_t tpb_host_alloc(size_t bytes, void** ptr);
+int32_t tpb_host_free(void* ptr);
+int32_t tpb_shard_range(int32_t num_paths, int32_t num_shards, int32_t shard, int32_t* first,
+                        int32_t* count);
+int32_t tpb_multi_create(const tpb_config* cfg, const int32_t* devices, int32_t num_shards,
+                         tpb_multi** out);
+int32_t tpb_multi_destroy(tpb_multi* m);
+const char* tpb_multi_last_error(const tpb_multi* m);
+int32_t tpb_multi_num_shards(const tpb_multi* m);
+int64_t tpb_multi_kernel_launches(const tpb_multi* m);
+/* Where shard `shard` of the last batch lives: device, paths [first_path, first_path +
+ * num_paths), rows [first_row, first_row + num_rows) of the packed output, its engine
+ * (for tpb_devptr / tpb_tbuf_insert_segments consumers).  Any pointer may be NULL. */
+int32_t tpb_multi_shard(const tpb_multi* m, int32_t shard, int32_t* device, int32_t* first_path,
+                        int32_t* num_paths, int64_t* first_row, int64_t* num_rows,
+                        tpb_engine** engine);
+/* tpb_set_joint_waypoints + tpb_set_joint_limits (per path) from HOST arrays of the
+ * whole batch, scattered to the shards. */
+int32_t tpb_multi_set_joint_paths(tpb_multi* m, int32_t num_paths, const int32_t* num_waypoints,
+                                  const double* waypoints, const double* max_velocity,
+                                  const double* max_acceleration);
+/* tpb_plan_joint_device on every shard at once (returns when all are done);
+ * *total_samples (may be NULL) = rows of all shards. */
+int32_t tpb_multi_plan_joint_device(tpb_multi* m, double start_sec, double time_step_sec,
+                                    int64_t* total_samples);
+/* The optional final gather of a per-path array (TPB_ARR_DURATION, _STATUS, _TIME, _Q,
+ * ...) of all shards into one host array in path order. */
+int32_t tpb_multi_gather(tpb_multi* m, tpb_array what, void* dst, size_t bytes_per_path);
+/* tpb_plan_joint_host for a batch spread over the shards: same tpb_plan_io, same
+ * outputs (r_offset and the rows are packed in path order over all shards). */
+int32_t tpb_multi_plan_joint_host(tpb_multi* m, tpb_plan_io* io);
+
 /* The same hot path for the batch already resident on the device (after
  * tpb_set_joint_waypoints / tpb_set_joint_limits): SamplePath + ConstraintSetup +
  * OptimizePathParameter + (time_step_sec > 0) ResampleTrajectory from start_sec for

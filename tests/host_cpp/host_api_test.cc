@@ -5,6 +5,7 @@
 // them with the CPU oracle.  Needs a GPU.
 #include <cmath>
 #include <cstdio>
+#include <cstring>
 #include <memory>
 #include <vector>
 
@@ -600,12 +601,46 @@ int main() {
     EXPECT(batch.Plan(B, nw.data(), wp.data(), vm.data(), am.data(), TimeFromSec(0.0), &res).ok());
     printf("\"batch\": {\n");
     PrintArray("waypoints", wp);
-    PrintArray("duration", res.duration);
+    PrintArray("duration", res.duration.to_vector());
     std::vector<double> off(res.offset.begin(), res.offset.end()), st(res.status.begin(), res.status.end());
     PrintArray("offset", off);
     PrintArray("status", st);
-    PrintArray("positions", res.positions, false);
+    PrintArray("positions", res.positions.to_vector(), false);
     printf("},\n");
+    // the same batch over two logical shards of the device, positions + profile only:
+    // bit-identical to the single-engine result, nothing else is brought back
+    PathTimingTrajectoryBatch sharded(JointPathOptions().set_num_dofs(D),
+                                      PathTimingTrajectoryOptions()
+                                          .SetTimeStep(tp::Milliseconds(4))
+                                          .SetNumDofs(D)
+                                          .SetNumPathSamples(N),
+                                      B, W, 1 << 20, std::vector<int32_t>{0, 0});
+    EXPECT(sharded.num_shards() == 2);
+    sharded.set_wanted(PathTimingTrajectoryBatch::kPositions | PathTimingTrajectoryBatch::kProfile);
+    PathTimingTrajectoryBatch::Result res2;
+    for (int rep = 0; rep < 2; ++rep)
+      EXPECT(sharded.Plan(B, nw.data(), wp.data(), vm.data(), am.data(), TimeFromSec(0.0), &res2).ok());
+    auto same = [](const auto& x, const auto& y) {  // bytes (a failed path's duration is NaN)
+      return x.size() == y.size() &&
+             std::memcmp(x.data(), y.data(), x.size() * sizeof(*x.data())) == 0;
+    };
+    EXPECT(res2.rows == res.rows);
+    EXPECT(same(res2.duration, res.duration));
+    EXPECT(same(res2.status, res.status));
+    EXPECT(same(res2.offset, res.offset));
+    EXPECT(same(res2.positions, res.positions));
+    EXPECT(res2.velocities.empty() && res2.accelerations.empty() && res2.path_parameter.empty());
+    EXPECT(res2.profile_time.size() == static_cast<size_t>(B) * N);
+    for (int b = 0; b < B; ++b) {
+      if (res.status[b] != 0) continue;
+      const double* t = res2.profile_time.data() + static_cast<size_t>(b) * N;
+      EXPECT(t[N - 1] - t[0] == res.duration[b]);
+    }
+    // the profile alone: no resampling, no rows
+    sharded.set_wanted(PathTimingTrajectoryBatch::kProfile);
+    EXPECT(sharded.Plan(B, nw.data(), wp.data(), vm.data(), am.data(), TimeFromSec(0.0), &res2).ok());
+    EXPECT(res2.rows == 0 && res2.positions.empty());
+    EXPECT(same(res2.duration, res.duration));
   }
   // ---- RestToRestPlanningWorks with TimeSamplingMethod::kSkipSamplesCloserThanTimeStep
   // (the reference runs its PathTimingTrajectoryTest suite for both methods, :994-1002)

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol(pkg):
     assert len(syms) >= 20
     for s in syms:
         assert hasattr(lib, s), f"libtpb.so does not export {s}"
-    assert pkg.lib().tpb_abi_version() == 3
+    assert pkg.lib().tpb_abi_version() == 4
 
 
 def test_header_compiles_as_c():

@@ -276,6 +276,41 @@ def test_plan_joint_host_chunked_pipeline_matches_staged_calls(pkg):
     eng.close()
 
 
+@pytest.mark.parametrize("B", [96, 1500])
+def test_plan_joint_host_selective_outputs(pkg, B):
+    """tpb_plan_io copies only the arrays a caller passes (ABI 4): positions only,
+    the profile only (no resampling at all), and time stamps + profile together, for
+    the unchunked and the chunked pipeline; values equal the staged calls'."""
+    W, D, N = 4, 7, 128
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=12)
+    res = _run_engine(pkg, wp, vmax, amax, N)
+    cap = int(res["total"])
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * 16384)
+    # positions only
+    out = {"r_offset": np.zeros(B + 1, np.int64), "r_pos": np.full((cap, D), np.nan)}
+    assert eng.plan_joint_host(wp, vmax, amax, 0.0, 0.004, out=out) == cap
+    np.testing.assert_array_equal(out["r_offset"], res["R_OFFSET"])
+    np.testing.assert_array_equal(out["r_pos"], res["R_POS"])
+    # the profile only: time step 0 = no resampling
+    prof = {k: np.full((B, N), np.nan) for k in ("profile_time", "profile_s", "profile_sd",
+                                                   "profile_sdd")}
+    prof["duration"] = np.zeros(B)
+    assert eng.plan_joint_host(wp, vmax, amax, 0.0, 0.0, out=prof) == 0
+    np.testing.assert_array_equal(prof["duration"], res["DURATION"])
+    for k, a in (("profile_time", "TIME"), ("profile_s", "S"), ("profile_sd", "SD"),
+                 ("profile_sdd", "SDD")):
+        np.testing.assert_array_equal(prof[k], res[a], err_msg=k)
+    # time stamps + one profile array with the rows
+    both = {"r_time": np.full(cap, np.nan), "r_sd": np.full(cap, np.nan),
+            "profile_time": np.full((B, N), np.nan)}
+    assert eng.plan_joint_host(wp, vmax, amax, 0.0, 0.004, out=both) == cap
+    np.testing.assert_array_equal(both["r_time"], res["R_TIME"])
+    np.testing.assert_array_equal(both["r_sd"], res["R_SD"])
+    np.testing.assert_array_equal(both["profile_time"], res["TIME"])
+    eng.close()
+
+
 def test_resample_skipping_samples_closer_than_time_step_bitwise(pkg, po):
     """kSkipSamplesCloserThanTimeStep (path_timing_trajectory.cc:785-836): every packed
     array bit-identical to the oracle, for time steps below, around and above the

@@ -47,3 +47,20 @@ def test_two_rank_sharding_matches_single_process(po, pkg):
                     for b in range(B_per * world)])
     np.testing.assert_array_equal(ret["dur"], ref)
     assert ret["tmax"] == 2.0
+
+
+def test_shard_range_is_the_contiguous_block_partition(pkg):
+    """tpb_shard_range (host code of the product library, no GPU needed): shard g of G owns
+    [g * ceil(B / G), (g + 1) * ceil(B / G)); the blocks tile the batch."""
+    for B in (0, 1, 7, 4096, 65536, 65537):
+        for G in (1, 2, 3, 4, 8, 13):
+            per = -(-B // G)
+            at = 0
+            for g in range(G):
+                first, count = pkg.shard_range(B, G, g)
+                assert first == min(B, g * per) and count == min(per, B - first)
+                assert first == at
+                at += count
+            assert at == B
+    with pytest.raises(pkg.TpbError):
+        pkg.shard_range(8, 2, 2)

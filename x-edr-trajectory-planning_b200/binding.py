@@ -53,7 +53,9 @@ class _PlanIO(C.Structure):
                 ("status", C.c_void_p), ("r_offset", C.c_void_p), ("r_pos", C.c_void_p),
                 ("r_vel", C.c_void_p), ("r_acc", C.c_void_p), ("r_s", C.c_void_p),
                 ("r_sd", C.c_void_p), ("r_sdd", C.c_void_p), ("r_capacity", C.c_int64),
-                ("r_total", C.c_int64)]
+                ("r_total", C.c_int64), ("r_time", C.c_void_p), ("profile_time", C.c_void_p),
+                ("profile_s", C.c_void_p), ("profile_sd", C.c_void_p),
+                ("profile_sdd", C.c_void_p)]
 
 
 class _ResampleDesc(C.Structure):
@@ -181,6 +183,31 @@ def lib():
         L.tpb_path_stop_parameter.argtypes = [vp, vp, vp, vp, vp, vp, i32]
         L.tpb_rescale_to_stop_device.restype = i32
         L.tpb_rescale_to_stop_device.argtypes = [C.POINTER(_StopDesc), vp]
+        # multi-GPU front-end
+        L.tpb_shard_range.restype = i32
+        L.tpb_shard_range.argtypes = [i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]
+        L.tpb_multi_create.restype = i32
+        L.tpb_multi_create.argtypes = [C.POINTER(_Config), C.POINTER(i32), i32, C.POINTER(vp)]
+        L.tpb_multi_destroy.restype = i32
+        L.tpb_multi_destroy.argtypes = [vp]
+        L.tpb_multi_last_error.restype = C.c_char_p
+        L.tpb_multi_last_error.argtypes = [vp]
+        L.tpb_multi_num_shards.restype = i32
+        L.tpb_multi_num_shards.argtypes = [vp]
+        L.tpb_multi_kernel_launches.restype = C.c_int64
+        L.tpb_multi_kernel_launches.argtypes = [vp]
+        L.tpb_multi_shard.restype = i32
+        L.tpb_multi_shard.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32),
+                                      C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(vp)]
+        L.tpb_multi_set_joint_paths.restype = i32
+        L.tpb_multi_set_joint_paths.argtypes = [vp, i32, vp, vp, vp, vp]
+        L.tpb_multi_plan_joint_device.restype = i32
+        L.tpb_multi_plan_joint_device.argtypes = [vp, C.c_double, C.c_double,
+                                                  C.POINTER(C.c_int64)]
+        L.tpb_multi_gather.restype = i32
+        L.tpb_multi_gather.argtypes = [vp, i32, vp, C.c_size_t]
+        L.tpb_multi_plan_joint_host.restype = i32
+        L.tpb_multi_plan_joint_host.argtypes = [vp, C.POINTER(_PlanIO)]
         L.tpb_resample_uniform_noalloc.restype = i32
         L.tpb_resample_uniform_noalloc.argtypes = [C.POINTER(_ResampleDesc), vp, C.c_char_p,
                                                    C.c_size_t]
@@ -478,7 +505,8 @@ class Engine:
     def plan_joint_host(self, waypoints, vmax, amax, start_sec=0.0, time_step_sec=0.0,
                         num_waypoints=None, out=None):
         """tpb_plan_joint_host.  `out`: dict of preallocated (ideally pinned) host
-        arrays keyed duration,status,r_offset,r_pos,r_vel,r_acc,r_s,r_sd,r_sdd."""
+        arrays keyed duration,status,r_offset,r_pos,r_vel,r_acc,r_s,r_sd,r_sdd,r_time and
+        profile_time,profile_s,profile_sd,profile_sdd ([B][N]); only those given are copied."""
         B = waypoints.shape[0]
         out = out or {}
         io = _PlanIO()
@@ -490,10 +518,12 @@ class Engine:
         io.start_sec, io.time_step_sec = start_sec, time_step_sec
         cap = None
         for k in ("duration", "status", "r_offset", "r_pos", "r_vel", "r_acc", "r_s",
-                  "r_sd", "r_sdd"):
+                  "r_sd", "r_sdd", "r_time", "profile_time", "profile_s", "profile_sd",
+                  "profile_sdd"):
             v = out.get(k)
             setattr(io, k, _ptr(v)[0] if v is not None else None)
-            if v is not None and k in ("r_pos", "r_vel", "r_acc", "r_s", "r_sd", "r_sdd"):
+            if v is not None and k in ("r_pos", "r_vel", "r_acc", "r_s", "r_sd", "r_sdd",
+                                       "r_time"):
                 rows = v.shape[0]
                 cap = rows if cap is None else min(cap, rows)
         io.r_capacity = cap or 0
@@ -630,6 +660,189 @@ def rescale_to_stop_device(max_acceleration, begin, length, times, velocities, a
     rc = lib().tpb_rescale_to_stop_device(C.byref(d), stream)
     if rc != 0:
         raise TpbError(rc, "tpb_rescale_to_stop_device")
+
+
+def shard_range(num_paths, num_shards, shard):
+    """tpb_shard_range: (first, count) of the contiguous block shard `shard` owns."""
+    f, c = C.c_int32(), C.c_int32()
+    rc = lib().tpb_shard_range(num_paths, num_shards, shard, C.byref(f), C.byref(c))
+    if rc != 0:
+        raise TpbError(rc, "tpb_shard_range")
+    return f.value, c.value
+
+
+class MultiEngine:
+    """tpb_multi: one batch sharded over several GPUs (or logical shards of one GPU) in
+    contiguous blocks, one engine + host thread per shard, no data-path collective."""
+
+    def __init__(self, max_paths, num_samples, num_dofs, max_waypoints, devices=None,
+                 num_shards=None, max_time_samples_total=0):
+        cfg = _Config(0, max_paths, num_dofs, max_waypoints, num_samples, 0,
+                      max_time_samples_total, 0)
+        G = num_shards or (len(devices) if devices is not None else 1)
+        dev = None
+        if devices is not None:
+            assert len(devices) == G
+            dev = (C.c_int32 * G)(*devices)
+        self._h = C.c_void_p()
+        rc = lib().tpb_multi_create(C.byref(cfg), dev, G, C.byref(self._h))
+        if rc != 0:
+            raise TpbError(rc, "tpb_multi_create")
+        self.G, self.N, self.D, self.W = G, num_samples, num_dofs, max_waypoints
+        self.B = 0
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise TpbError(rc, (lib().tpb_multi_last_error(self._h) or b"").decode())
+
+    def close(self):
+        if self._h:
+            lib().tpb_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def kernel_launches(self):
+        return lib().tpb_multi_kernel_launches(self._h)
+
+    def shard(self, g):
+        dev, f, n = C.c_int32(), C.c_int32(), C.c_int32()
+        r0, rn, e = C.c_int64(), C.c_int64(), C.c_void_p()
+        self._ck(lib().tpb_multi_shard(self._h, g, C.byref(dev), C.byref(f), C.byref(n),
+                                       C.byref(r0), C.byref(rn), C.byref(e)))
+        return dict(device=dev.value, first_path=f.value, num_paths=n.value,
+                    first_row=r0.value, num_rows=rn.value, engine=e.value)
+
+    def set_joint_paths(self, waypoints, vmax, amax, num_waypoints=None):
+        wp, vm, am = _f64(waypoints), _f64(vmax), _f64(amax)
+        nw = None if num_waypoints is None else np.ascontiguousarray(num_waypoints, np.int32)
+        self._keep = (wp, vm, am, nw)
+        self.B = wp.shape[0]
+        self._ck(lib().tpb_multi_set_joint_paths(
+            self._h, self.B, nw.ctypes.data if nw is not None else None, wp.ctypes.data,
+            vm.ctypes.data, am.ctypes.data))
+
+    def plan_device(self, start_sec=0.0, time_step_sec=0.0):
+        total = C.c_int64(0)
+        self._ck(lib().tpb_multi_plan_joint_device(self._h, start_sec, time_step_sec,
+                                                   C.byref(total)))
+        return total.value
+
+    def gather(self, what, shape_per_path=(), dtype=np.float64):
+        out = np.empty((self.B,) + tuple(shape_per_path), dtype)
+        self._ck(lib().tpb_multi_gather(self._h, what, out.ctypes.data,
+                                        out.nbytes // max(self.B, 1)))
+        return out
+
+    def plan_joint_host(self, waypoints, vmax, amax, start_sec=0.0, time_step_sec=0.0,
+                        num_waypoints=None, out=None):
+        """tpb_multi_plan_joint_host; arguments as Engine.plan_joint_host."""
+        B = waypoints.shape[0]
+        out = out or {}
+        io = _PlanIO()
+        io.num_paths = B
+        io.num_waypoints = _ptr(num_waypoints)[0]
+        io.waypoints = _ptr(waypoints)[0]
+        io.max_velocity = _ptr(vmax)[0]
+        io.max_acceleration = _ptr(amax)[0]
+        io.start_sec, io.time_step_sec = start_sec, time_step_sec
+        cap = None
+        for k in ("duration", "status", "r_offset", "r_pos", "r_vel", "r_acc", "r_s",
+                  "r_sd", "r_sdd", "r_time", "profile_time", "profile_s", "profile_sd",
+                  "profile_sdd"):
+            v = out.get(k)
+            setattr(io, k, _ptr(v)[0] if v is not None else None)
+            if v is not None and k in ("r_pos", "r_vel", "r_acc", "r_s", "r_sd", "r_sdd",
+                                       "r_time"):
+                rows = v.shape[0]
+                cap = rows if cap is None else min(cap, rows)
+        io.r_capacity = cap or 0
+        self.B = B
+        self._ck(lib().tpb_multi_plan_joint_host(self._h, C.byref(io)))
+        return io.r_total
+
+
+_hostapi = None
+
+
+def hostapi():
+    """lib/libtpb_hostapi.so: C entry points over the host C++ class
+    PathTimingTrajectoryBatch (host/src/hostapi.cc)."""
+    global _hostapi
+    if _hostapi is None:
+        path = os.path.join(os.path.dirname(lib_path()), "libtpb_hostapi.so")
+        if not os.path.exists(path):
+            raise TpbError(9, f"{path} is missing: run make -C host")
+        H = C.CDLL(path)
+        vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
+        H.tpbh_batch_create.restype = vp
+        H.tpbh_batch_create.argtypes = [i32, i32, i64, C.c_double, C.c_double, i32, i32, i64,
+                                        C.POINTER(i32), i32]
+        H.tpbh_batch_destroy.argtypes = [vp]
+        H.tpbh_batch_plan.restype = i32
+        H.tpbh_batch_plan.argtypes = [vp, C.c_uint32, i32, vp, vp, vp, vp, i64]
+        H.tpbh_batch_error.restype = C.c_char_p
+        H.tpbh_batch_error.argtypes = [vp]
+        H.tpbh_batch_rows.restype = i64
+        H.tpbh_batch_rows.argtypes = [vp]
+        H.tpbh_batch_array.restype = vp
+        H.tpbh_batch_array.argtypes = [vp, i32, C.POINTER(i64)]
+        _hostapi = H
+    return _hostapi
+
+
+class HostBatch:
+    """The host C++ class PathTimingTrajectoryBatch (path_timing_batch.h) through
+    libtpb_hostapi.so.  Results are views of the object's page-locked arrays, valid until
+    the next plan()."""
+    WANT = dict(duration=1, positions=2, velocities=4, accelerations=8, path_parameters=16,
+                time=32, profile=64, trajectory=1 | 2 | 4 | 8 | 16)
+    _ARRAYS = dict(duration=(0, np.float64), status=(1, np.int32), offset=(2, np.int64),
+                   positions=(3, np.float64), velocities=(4, np.float64),
+                   accelerations=(5, np.float64), path_parameter=(6, np.float64),
+                   path_parameter_derivative=(7, np.float64),
+                   second_path_parameter_derivative=(8, np.float64), time=(9, np.float64),
+                   profile_time=(10, np.float64), profile_s=(11, np.float64),
+                   profile_sd=(12, np.float64), profile_sdd=(13, np.float64))
+
+    def __init__(self, num_dofs, num_path_samples, time_step_ns, max_paths, max_waypoints,
+                 max_time_samples_total, devices=(0,), constraint_safety=0.8, rounding=0.2):
+        dev = (C.c_int32 * len(devices))(*devices)
+        self._h = hostapi().tpbh_batch_create(num_dofs, num_path_samples, time_step_ns,
+                                              constraint_safety, rounding, max_paths,
+                                              max_waypoints, max_time_samples_total, dev,
+                                              len(devices))
+        self.D, self.N = num_dofs, num_path_samples
+
+    def close(self):
+        if self._h:
+            hostapi().tpbh_batch_destroy(self._h)
+            self._h = None
+
+    def plan(self, waypoints, vmax, amax, want="trajectory", num_waypoints=None, start_ns=0):
+        """PathTimingTrajectoryBatch::set_wanted(want) + Plan(); returns the row count."""
+        mask = 0
+        for w in ([want] if isinstance(want, str) else want):
+            mask |= self.WANT[w]
+        rc = hostapi().tpbh_batch_plan(self._h, mask, waypoints.shape[0], _ptr(num_waypoints)[0],
+                                       _ptr(waypoints)[0], _ptr(vmax)[0], _ptr(amax)[0], start_ns)
+        if rc != 0:
+            raise TpbError(rc, (hostapi().tpbh_batch_error(self._h) or b"").decode())
+        return hostapi().tpbh_batch_rows(self._h)
+
+    def array(self, name):
+        which, dt = self._ARRAYS[name]
+        n = C.c_int64(0)
+        p = hostapi().tpbh_batch_array(self._h, which, C.byref(n))
+        if not p or n.value == 0:
+            return np.empty(0, dt)
+        buf = (C.c_char * (n.value * np.dtype(dt).itemsize)).from_address(p)
+        return np.frombuffer(buf, dtype=dt)
 
 
 def resample_uniform_noalloc(device, num_paths, num_samples, num_dofs, inputs, outputs, start_sec,

@@ -844,7 +844,10 @@ int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
   e->launches += tpb::launch_fill_f64(e->a.time_start, io->start_sec, d.B, e->stream);
   io->r_total = 0;
   const bool want_rows = io->time_step_sec > 0 && d.r_cap > 0;
-  const bool any_out = io->r_pos || io->r_vel || io->r_acc || io->r_s || io->r_sd || io->r_sdd;
+  const bool any_out =
+      io->r_pos || io->r_vel || io->r_acc || io->r_s || io->r_sd || io->r_sdd || io->r_time;
+  const bool any_profile =
+      io->profile_time || io->profile_s || io->profile_sd || io->profile_sdd;
   const int max_loops = std::max(100, 10 * d.N);
 
   // Chunks of the batch go through sample -> integrate -> resample one after the
@@ -854,7 +857,7 @@ int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
   int bounds[tpb_engine::kMaxChunks + 1];
   int nchunks = 0;
   bounds[0] = 0;
-  if (want_rows && any_out && d.B >= 1024) {
+  if (((want_rows && any_out) || any_profile) && d.B >= 1024) {
     int size = std::max(128, d.B / 16);
     while (bounds[nchunks] < d.B && nchunks < tpb_engine::kMaxChunks - 1) {
       const int next = std::min(d.B, bounds[nchunks] + size);
@@ -893,16 +896,32 @@ int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
       if (c < nchunks) {
         launch_chunk(c);
         TPB_CUDA(e, cudaGetLastError());
-        TPB_CUDA(e, cudaMemcpyAsync(&e->chunk_rows[c], e->a.r_offset + bounds[c + 1], sizeof(int64_t),
-                                    cudaMemcpyDeviceToHost, e->stream));
+        if (want_rows)
+          TPB_CUDA(e, cudaMemcpyAsync(&e->chunk_rows[c], e->a.r_offset + bounds[c + 1],
+                                      sizeof(int64_t), cudaMemcpyDeviceToHost, e->stream));
         TPB_CUDA(e, cudaEventRecord(e->chunk_done[c], e->stream));
       }
       if (c == 0) continue;
       // chunk c-1 is done (or will be while chunk c runs): copy its rows out
       const int k = c - 1;
       TPB_CUDA(e, cudaEventSynchronize(e->chunk_done[k]));
+      {
+        // the profiles of chunk k: [bounds[k], bounds[k+1]) x N
+        const size_t p0 = static_cast<size_t>(bounds[k]) * d.N;
+        const size_t pn = static_cast<size_t>(bounds[k + 1] - bounds[k]) * d.N;
+        auto prof = [&](double* dst, const double* src) -> cudaError_t {
+          if (dst == nullptr || pn == 0) return cudaSuccess;
+          return cudaMemcpyAsync(dst + p0, src + p0, pn * sizeof(double), cudaMemcpyDeviceToHost,
+                                 e->copy_stream);
+        };
+        TPB_CUDA(e, prof(io->profile_time, e->a.time));
+        TPB_CUDA(e, prof(io->profile_s, e->a.s));
+        TPB_CUDA(e, prof(io->profile_sd, e->a.sd));
+        TPB_CUDA(e, prof(io->profile_sdd, e->a.sdd));
+      }
+      if (!want_rows) continue;
       const int64_t rows_end = e->chunk_rows[k];
-      if (rows_end > d.r_cap || rows_end > io->r_capacity) {
+      if (rows_end > d.r_cap || (any_out && rows_end > io->r_capacity)) {
         rc = fail(e, TPB_OUT_OF_RANGE, rows_end > d.r_cap
                                            ? "resampled rows exceed max_time_samples_total"
                                            : "resampled rows exceed r_capacity");
@@ -920,6 +939,7 @@ int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
       TPB_CUDA(e, out(io->r_s, e->a.r_s, 1));
       TPB_CUDA(e, out(io->r_sd, e->a.r_sd, 1));
       TPB_CUDA(e, out(io->r_sdd, e->a.r_sdd, 1));
+      TPB_CUDA(e, out(io->r_time, e->a.r_time, 1));
       rows_before = rows_end;
     }
     io->r_total = rows_before;
@@ -951,6 +971,14 @@ int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
     if (io->r_s) TPB_CUDA(e, cudaMemcpyAsync(io->r_s, e->a.r_s, rows * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
     if (io->r_sd) TPB_CUDA(e, cudaMemcpyAsync(io->r_sd, e->a.r_sd, rows * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
     if (io->r_sdd) TPB_CUDA(e, cudaMemcpyAsync(io->r_sdd, e->a.r_sdd, rows * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    if (io->r_time) TPB_CUDA(e, cudaMemcpyAsync(io->r_time, e->a.r_time, rows * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  }
+  if (nchunks == 1 && any_profile) {
+    const size_t pn = static_cast<size_t>(d.B) * d.N * sizeof(double);
+    if (io->profile_time) TPB_CUDA(e, cudaMemcpyAsync(io->profile_time, e->a.time, pn, cudaMemcpyDeviceToHost, e->stream));
+    if (io->profile_s) TPB_CUDA(e, cudaMemcpyAsync(io->profile_s, e->a.s, pn, cudaMemcpyDeviceToHost, e->stream));
+    if (io->profile_sd) TPB_CUDA(e, cudaMemcpyAsync(io->profile_sd, e->a.sd, pn, cudaMemcpyDeviceToHost, e->stream));
+    if (io->profile_sdd) TPB_CUDA(e, cudaMemcpyAsync(io->profile_sdd, e->a.sdd, pn, cudaMemcpyDeviceToHost, e->stream));
   }
   TPB_CUDA(e, cudaStreamSynchronize(e->stream));
   if (e->copy_stream) TPB_CUDA(e, cudaStreamSynchronize(e->copy_stream));
