@@ -983,7 +983,7 @@ def run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, wor
             du = torch.full((S,), 8.0 / (E - 1), dtype=torch.float64, device=dev)
             o = out[:S * E * 3 * D].view(S, E, 3, D)
 
-            for exact in (False, True):
+            for exact in (0, 1, -1):
                 def run():
                     pkg.spline_eval_device(d_k, d_c, P, 2, o, u0=u0, du=du, evals=E,
                                            exact=exact, stream=stream.cuda_stream)
@@ -1001,7 +1001,7 @@ def run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, wor
                 torch.cuda.synchronize()
                 ms = max_over_ranks(e0.elapsed_time(e1)) / reps
                 gbs = S * E * 3 * D * 8 / (ms / 1e3) / 1e9
-                key = f"p{P}_d{D}" + ("_exact" if exact else "")
+                key = f"p{P}_d{D}" + {0: "", 1: "_exact", -1: "_threadstores"}[exact]
                 res[key] = {"evals_per_s": world * S * E / (ms / 1e3), "ms": ms,
                             "hbm_gbs_per_gpu": gbs, "frac_of_peak": gbs / peak}
             # shuffled-u variant: the same parameters in random order per spline,
@@ -1033,7 +1033,9 @@ def run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, wor
                                               "bytes_per_eval": 3 * D * 8 + 8}
                 del d_u
     res["bytes_per_eval"] = "3*dim*8 written (implicit parameter grid, tables in smem)"
-    res["modes"] = ("pP_dD: per-span polynomial form (<= 1e-12 of the reference); pP_dD_exact: "
+    res["modes"] = ("pP_dD: per-span polynomial form (<= 1e-12 of the reference), tiles leave shared "
+                    "memory as bulk async copies (UBLKCP); pP_dD_threadstores: the same with per-"
+                    "thread 16-byte stores (A/B); pP_dD_exact: "
                     "NURBS A2.3 in the reference's operation order (bit-identical, "
                     "FP64-division bound)")
     return res

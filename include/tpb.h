@@ -493,7 +493,9 @@ int32_t tpb_devptr(tpb_engine* e, tpb_array what, void** ptr, size_t* bytes);
  * kOutOfRange (11) when u is outside [knots.front(), knots.back()] (then the
  * output row is left untouched, like the reference).
  * exact != 0: NURBS-book A2.3 operation order (bit-identical to the oracle);
- * exact == 0: per-span polynomial form (<= 1e-12 absolute, faster). */
+ * exact == 0: per-span polynomial form (<= 1e-12 absolute, faster); finished tiles leave
+ *             shared memory as bulk asynchronous copies (the 1-D TMA path);
+ * exact < 0:  the same values with per-thread stores (kept for A/B measurements). */
 typedef struct {
   int32_t degree, num_points, dim, nder;
   int32_t num_splines;

@@ -123,3 +123,29 @@ def test_argument_errors(pkg):
     with pytest.raises(pkg.TpbError) as ei:
         pkg.spline_eval_host(knots, ctrl, 2, 3, u=u)  # CHECK(der <= p), bspline_base.cc:270
     assert ei.value.code == 3
+
+
+@pytest.mark.parametrize("P,D,E", [(3, 7, 4096), (3, 7, 4099), (5, 6, 6000), (2, 3, 2050), (4, 7, 777)])
+def test_bulk_copy_tiles_equal_thread_stores(pkg, P, D, E):
+    """The polynomial-form kernel writes its tiles with bulk asynchronous copies
+    (exact = 0) or with per-thread stores (exact = -1): the same bits, also for ragged
+    last tiles, odd tile sizes (16-byte misalignment -> fallback path), rows that fail the
+    range check (those tiles take the per-row path and leave the caller's memory alone) and
+    an explicit shuffled parameter array."""
+    nder = min(P, 2)
+    S = 5
+    knots, ctrl = pkg.workloads.dense_splines(S, P, D, num_points=32, knot_scale=8.0)
+    rng = np.random.default_rng(E)
+    u = np.tile(np.linspace(0.0, 8.0, E), (S, 1))
+    u[1] = rng.permutation(u[1])
+    u[2, 300:310] = 9.5   # out of range
+    u[3, -1] = -0.25
+    a, sa = pkg.spline_eval_host(knots, ctrl, P, nder, u=u, exact=0)
+    b, sb = pkg.spline_eval_host(knots, ctrl, P, nder, u=u, exact=-1)
+    assert np.array_equal(sa, sb) and (sa != 0).sum() == 11
+    assert a.tobytes() == b.tobytes()
+    a2, _ = pkg.spline_eval_host(knots, ctrl, P, nder, u0=np.zeros(S), du=np.full(S, 8.0 / E),
+                                 evals=E, exact=0)
+    b2, _ = pkg.spline_eval_host(knots, ctrl, P, nder, u0=np.zeros(S), du=np.full(S, 8.0 / E),
+                                 evals=E, exact=-1)
+    assert a2.tobytes() == b2.tobytes()

@@ -574,7 +574,10 @@ def _desc(degree, num_points, dim, nder, num_splines, evals, knots, ctrl, u, u0,
           status, exact):
     d = _SplineDesc(degree, num_points, dim, nder, num_splines, evals)
     d.knots, d.ctrl, d.u, d.u0, d.du = (_ptr(x)[0] for x in (knots, ctrl, u, u0, du))
-    d.out, d.status, d.exact = _ptr(out)[0], _ptr(status)[0], 1 if exact else 0
+    # exact: True / 1 = A2.3 operation order; False / 0 = polynomial form with bulk-copy
+    # tiles; -1 = polynomial form with per-thread stores (A/B)
+    mode = exact if (isinstance(exact, int) and not isinstance(exact, bool)) else (1 if exact else 0)
+    d.out, d.status, d.exact = _ptr(out)[0], _ptr(status)[0], mode
     return d
 
 

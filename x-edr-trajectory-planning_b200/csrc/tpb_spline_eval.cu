@@ -10,6 +10,7 @@
 // 16-byte-vectorised stream (the tile's output rows are contiguous in HBM).
 #include <string>
 
+#include "tpb_bulk.cuh"
 #include "tpb_device.cuh"
 #include "../../include/tpb.h"
 
@@ -29,6 +30,7 @@ struct EvalArgs {
   double* out;
   int32_t* status;
   bool exact;
+  bool bulk;  // polynomial form: tiles leave shared memory as bulk async copies
 };
 
 template <int P, int NDER>
@@ -122,7 +124,14 @@ __global__ void __launch_bounds__(kTile, TPB_SE_MINBLOCKS) k_spline_eval(EvalArg
 // ---------------------------------------------------------------------------
 constexpr int kPolyTiles = 16;
 
-template <int P, int NDER>
+//
+// kBulk: the finished tile (kTile x K x dim doubles, contiguous in HBM) leaves shared
+// memory as ONE bulk asynchronous copy (cp.async.bulk.global.shared::cta, the 1-D TMA
+// path) issued by thread 0 instead of a per-thread 16-byte copy loop; the tile is
+// double-buffered so that the copy of tile t overlaps the evaluation of tile t + 1.
+// Tiles whose HBM address or size is not a multiple of 16 bytes, and tiles with
+// out-of-range parameters, take the per-thread path.
+template <int P, int NDER, bool kBulk>
 __global__ void __launch_bounds__(kTile) k_spline_eval_poly(EvalArgs g) {
   extern __shared__ __align__(16) double smem[];
   const int n = g.num_points;
@@ -134,7 +143,9 @@ __global__ void __launch_bounds__(kTile) k_spline_eval_poly(EvalArgs g) {
   double* s_mid = s_knots + nk;                    // [nspan]
   double* s_coef = s_mid + nspan;                  // [nspan][P+1][D]
   double* s_ctrl = s_coef + nspan * (P + 1) * D;   // [n][D] (table build only)
-  double* s_out = smem + ((nk + nspan + nspan * (P + 1) * D + n * D + 1) & ~1);  // [kTile][K*D]
+  // [kTile][K*D], two of them with kBulk; 16-byte aligned
+  double* s_out0 = smem + ((nk + nspan + nspan * (P + 1) * D + n * D + 1) & ~1);
+  const int tile_doubles = (kTile * K * D + 1) & ~1;
   const int s = blockIdx.y;
   {
     const double* gk = g.knots + static_cast<size_t>(s) * nk;
@@ -171,6 +182,12 @@ __global__ void __launch_bounds__(kTile) k_spline_eval_poly(EvalArgs g) {
     const long long e0 = chunk0 + static_cast<long long>(tile) * kTile;
     if (e0 >= g.evals) break;
     const long long e = e0 + threadIdx.x;
+    double* s_out = s_out0 + (kBulk ? (tile & 1) * tile_doubles : 0);
+    if (kBulk && tile >= 2) {
+      // the bulk copy that read this buffer two tiles ago must be done reading it
+      if (threadIdx.x == 0) bulk::bulk_wait_read<1>();
+      __syncthreads();
+    }
     bool ok = false;
     if (e < g.evals) {
       const size_t flat = static_cast<size_t>(s) * g.evals + e;
@@ -198,12 +215,21 @@ __global__ void __launch_bounds__(kTile) k_spline_eval_poly(EvalArgs g) {
         }
       }
     }
+    // (with kBulk: the tile's ordinary shared-memory stores become visible to the
+    // async proxy before the barrier that precedes the bulk copy)
+    if (kBulk) bulk::fence_async_shared();
     const int all_ok = __syncthreads_and(ok || e >= g.evals);
     const long long n_in_tile = min(static_cast<long long>(kTile), g.evals - e0);
     double* gout = g.out + (static_cast<size_t>(s) * g.evals + e0) * rowlen;
     if (all_ok) {
       const int total = static_cast<int>(n_in_tile) * rowlen;
-      if ((reinterpret_cast<uintptr_t>(gout) & 15) == 0 && (total & 1) == 0) {
+      const bool vec = (reinterpret_cast<uintptr_t>(gout) & 15) == 0 && (total & 1) == 0;
+      if (kBulk && vec) {
+        if (threadIdx.x == 0) {
+          bulk::bulk_store(gout, s_out, static_cast<uint32_t>(total) * sizeof(double));
+          bulk::bulk_commit();
+        }
+      } else if (vec) {
         const double2* s2 = reinterpret_cast<const double2*>(s_out);
         double2* g2 = reinterpret_cast<double2*>(gout);
         for (int i = threadIdx.x; i < total / 2; i += kTile) g2[i] = s2[i];
@@ -214,21 +240,33 @@ __global__ void __launch_bounds__(kTile) k_spline_eval_poly(EvalArgs g) {
       const double* o = s_out + threadIdx.x * rowlen;
       for (int i = 0; i < rowlen; ++i) gout[threadIdx.x * rowlen + i] = o[i];
     }
-    __syncthreads();  // s_out is reused by the next tile
+    if (!kBulk) __syncthreads();  // s_out is reused by the next tile
   }
+  // shared memory must stay valid until every bulk copy has read it
+  if (kBulk && threadIdx.x == 0) bulk::bulk_wait_read<0>();
+}
+
+template <int P, int NDER, bool kBulk>
+void launch_one_poly_impl(const EvalArgs& g, cudaStream_t st) {
+  const int n = g.num_points, nk = n + P + 1, nspan = n - P;
+  const size_t tile = (static_cast<size_t>(kTile) * (NDER + 1) * g.dim + 1) & ~size_t{1};
+  const size_t smem = sizeof(double) * (nk + nspan + static_cast<size_t>(nspan) * (P + 1) * g.dim +
+                                        static_cast<size_t>(n) * g.dim + 1 +
+                                        (kBulk ? 2 : 1) * tile);
+  cudaFuncSetAttribute(k_spline_eval_poly<P, NDER, kBulk>,
+                       cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  const long long per_cta = static_cast<long long>(kTile) * kPolyTiles;
+  dim3 grid(static_cast<unsigned>((g.evals + per_cta - 1) / per_cta), g.num_splines);
+  k_spline_eval_poly<P, NDER, kBulk><<<grid, kTile, smem, st>>>(g);
 }
 
 template <int P, int NDER>
 void launch_one_poly(const EvalArgs& g, cudaStream_t st) {
-  const int n = g.num_points, nk = n + P + 1, nspan = n - P;
-  const size_t smem = sizeof(double) * (nk + nspan + static_cast<size_t>(nspan) * (P + 1) * g.dim +
-                                        static_cast<size_t>(n) * g.dim + 1 +
-                                        static_cast<size_t>(kTile) * (NDER + 1) * g.dim);
-  cudaFuncSetAttribute(k_spline_eval_poly<P, NDER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                       static_cast<int>(smem));
-  const long long per_cta = static_cast<long long>(kTile) * kPolyTiles;
-  dim3 grid(static_cast<unsigned>((g.evals + per_cta - 1) / per_cta), g.num_splines);
-  k_spline_eval_poly<P, NDER><<<grid, kTile, smem, st>>>(g);
+  if (g.bulk) {
+    launch_one_poly_impl<P, NDER, true>(g, st);
+  } else {
+    launch_one_poly_impl<P, NDER, false>(g, st);
+  }
 }
 
 template <int P, int NDER>
@@ -306,9 +344,19 @@ int launch_spline_eval(const tpb_spline_eval_desc& d, cudaStream_t st, std::stri
   size_t smem = sizeof(double) * (d.num_points + d.degree + 2 +
                                   static_cast<size_t>(d.num_points) * d.dim +
                                   static_cast<size_t>(kTile) * (d.nder + 1) * d.dim);
-  if (!d.exact) {  // + span midpoints and the per-span coefficient table
+  // exact > 0: A2.3; exact == 0: polynomial form, tiles leave as bulk copies;
+  // exact < 0: polynomial form with per-thread stores (kept for A/B measurements)
+  bool bulk = d.exact == 0;
+  if (d.exact <= 0) {  // + span midpoints and the per-span coefficient table
     const size_t nspan = static_cast<size_t>(d.num_points - d.degree);
     smem += sizeof(double) * (nspan + nspan * (d.degree + 1) * d.dim);
+    // the second tile buffer of the bulk variant; fall back if it does not fit
+    const size_t tile = sizeof(double) * (static_cast<size_t>(kTile) * (d.nder + 1) * d.dim + 2);
+    if (bulk && smem + tile <= 200 * 1024) {
+      smem += tile;
+    } else {
+      bulk = false;
+    }
   }
   if (smem > 200 * 1024) {
     *err = "spline tables do not fit in shared memory";
@@ -316,7 +364,8 @@ int launch_spline_eval(const tpb_spline_eval_desc& d, cudaStream_t st, std::stri
   }
   EvalArgs g{d.num_points, d.dim,  d.num_splines, static_cast<long long>(d.evals_per_spline),
              d.knots,      d.ctrl, d.u,           d.u0,
-             d.du,         d.out,  d.status,      d.exact != 0};
+             d.du,         d.out,  d.status,      d.exact > 0,
+             bulk};
   bool ok = false;
   switch (d.degree) {
     case 1: ok = dispatch_nder<1>(d.nder, g, st); break;
