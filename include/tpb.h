@@ -264,6 +264,32 @@ int32_t tpb_optimize(tpb_engine* e, const double* sd_start, const double* sdd_st
 int32_t tpb_time_phases(tpb_engine* e, int32_t on);
 int32_t tpb_last_phase_ms(tpb_engine* e, double* ms3);
 
+/* ---- queries on the solved profiles ------------------------------ */
+/* TimeOptimalPathProfile::GetPathParameterAndDerivatives, SampleIndexFromTime,
+ * GetPreviousIndex and GetPreviousDiscreteValues (time_optimal_path_timing.cc:
+ * 1497-1668) for queries_per_path times per path, on the device, after tpb_optimize
+ * (any mode).  time_sec and every output are [B][queries_per_path]; any output may be
+ * NULL.  s / sd / sdd: the path parameter and its derivatives at time_sec;
+ * previous_index: GetPreviousIndex (-1 where the reference returns -1); sk, sdk, sddk,
+ * tk: GetPreviousDiscreteValues.  status: bit 0 = GetPathParameterAndDerivatives returned
+ * false, bit 1 = GetPreviousIndex < 0 (3 for every query of a path that was not timed);
+ * outputs of a failed query are NaN / -1.  Results equal the reference's bit for bit. */
+int32_t tpb_query_profile(tpb_engine* e, int32_t queries_per_path, const double* time_sec,
+                          double* s, double* sd, double* sdd, int32_t* previous_index,
+                          double* sk, double* sdk, double* sddk, double* tk, int32_t* status,
+                          int32_t on_device);
+
+/* Cross-check kernels: for a few stages the library keeps an older, simpler kernel next
+ * to the default one; the parity tests run both and compare the bits.  `on` != 0 makes
+ * this engine use the variant.  (No environment variables are read anywhere.) */
+typedef enum {
+  TPB_VARIANT_GENERIC_LIMIT_LOCAL = 0, /* explicit rows: limit curve with rows in local memory */
+  TPB_VARIANT_INTEGRATE_WARP = 1,      /* joint paths: sweeps one path per warp (k_integrate) */
+  TPB_VARIANT_CART_GENERIC = 2,        /* Cartesian paths: sweeps on the stored 2D+2 rows */
+  TPB_VARIANT_CART_UNFUSED = 3         /* Cartesian paths: rows and limit curve in two kernels */
+} tpb_kernel_variant;
+int32_t tpb_set_kernel_variant(tpb_engine* e, tpb_kernel_variant which, int32_t on);
+
 /* ---- stage D: trajectory assembly + ResampleEquidistantlyInTime ---------- */
 /* (path_timing_trajectory.cc:458-472, :755-783).  start_sec = TimeToSec(start),
  * time_step_sec = the planner's time step.  Writes the packed TPB_ARR_R_* arrays;

@@ -2,7 +2,8 @@
 """Per-path phase timing of k_integrate (diagnostics, not a benchmark).
 
 Needs a library built with -DTPB_PROFILE_PHASES:
-    make -C x-edr-trajectory-planning_b200/csrc clean all EXTRA=-DTPB_PROFILE_PHASES
+    make -C x-edr-trajectory-planning_b200/csrc all LIB=$PWD/x-edr-trajectory-planning_b200/lib_ab/phases EXTRA=-DTPB_PROFILE_PHASES
+    TPB_LIB=$PWD/x-edr-trajectory-planning_b200/lib_ab/phases/libtpb.so python profiles/tools/phase_profile.py
 Prints the distribution over paths of the SM-cycle count of every phase.
 """
 import os
@@ -19,6 +20,7 @@ B, N, D, W = 4096, 2048, 7, 10
 wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=1000)
 eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
                  max_time_samples_total=B * 6144)
+eng.set_kernel_variant("integrate_warp")  # the counters live in the one-path-per-warp kernel
 eng.set_joint_waypoints(wp)
 eng.set_joint_limits(vmax, amax)
 eng.sample_paths()

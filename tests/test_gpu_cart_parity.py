@@ -154,9 +154,11 @@ def test_builtin_kinematics_pipeline(pkg, po):
     assert n_ok >= B // 2
 
 
-def _limit_curve_run(pkg, pw, jw, vm, am, jac_from=None):
+def _limit_curve_run(pkg, pw, jw, vm, am, jac_from=None, variants=()):
     B, W = pw.shape[0], pw.shape[1]
     eng = _engine(pkg, B, W)
+    for v in variants:  # cross-check kernels (tpb_set_kernel_variant)
+        eng.set_kernel_variant(v)
     eng.set_cart_options(0.05, 0.5, 0.25)
     eng.set_cart_waypoints(pw, jw)
     eng.set_joint_limits(vm, am)
@@ -189,10 +191,8 @@ def test_fused_rows_and_limit_curve_equal_the_two_kernel_path(pkg, po, monkeypat
     B, W = (6, 5) if uploaded_jacobians else (48, 5)
     pw, jw, vm, am = pkg.workloads.cart_paths(B, W, seed=5300)
     jf = po.fake_jacobian if uploaded_jacobians else None
-    monkeypatch.delenv("TPB_CART_UNFUSED", raising=False)
     fused, n_fused = _limit_curve_run(pkg, pw, jw, vm, am, jf)
-    monkeypatch.setenv("TPB_CART_UNFUSED", "1")
-    plain, n_plain = _limit_curve_run(pkg, pw, jw, vm, am, jf)
+    plain, n_plain = _limit_curve_run(pkg, pw, jw, vm, am, jf, variants=("cart_unfused",))
     assert (n_fused, n_plain) == (1, 2)
     assert (fused["STATUS"] == 0).sum() >= B // 2
     for k in fused:
@@ -214,19 +214,19 @@ def test_joint_structured_sweeps_equal_the_generic_solver(pkg, po, monkeypatch, 
         pw[7, 2] = pw[7, 1]
         jw[7, 2] = jw[7, 1]
     jf = po.fake_jacobian if uploaded_jacobians else None
-    monkeypatch.delenv("TPB_CART_GENERIC", raising=False)
     fast, _ = _limit_curve_run(pkg, pw, jw, vm, am, jf)
-    monkeypatch.setenv("TPB_CART_GENERIC", "1")
-    generic, _ = _limit_curve_run(pkg, pw, jw, vm, am, jf)
+    generic, _ = _limit_curve_run(pkg, pw, jw, vm, am, jf, variants=("cart_generic",))
     assert (fast["STATUS"] == 0).sum() >= B // 2
     for k in fast:
         assert fast[k].tobytes() == generic[k].tobytes(), k
 
 
-def _six_dof_run(pkg, pw, jw6, vm, am, q, jac):
+def _six_dof_run(pkg, pw, jw6, vm, am, q, jac, variants=()):
     B, W = pw.shape[0], pw.shape[1]
     eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=6, max_waypoints=W,
                      max_time_samples_total=B * 60000, cartesian=True)
+    for v in variants:
+        eng.set_kernel_variant(v)
     eng.set_cart_options(0.05, 0.5, 0.25)
     eng.set_cart_waypoints(pw, jw6)
     eng.set_joint_limits(vm, am)
@@ -260,12 +260,9 @@ def test_six_dof_arm_fast_kernels_equal_the_generic_ones(pkg, monkeypatch):
     jac = (rng.normal(0, 0.3, (B, 1, 6, 6)) + np.eye(6)[None, None]
            + 0.2 * np.sin(3.0 * u[..., None] + rng.uniform(0, 6, (B, 1, 6, 6))))
     q, jac = np.ascontiguousarray(q), np.ascontiguousarray(jac)
-    monkeypatch.delenv("TPB_CART_UNFUSED", raising=False)
-    monkeypatch.delenv("TPB_CART_GENERIC", raising=False)
     fast = _six_dof_run(pkg, pw, jw6, vm, am, q, jac)
-    monkeypatch.setenv("TPB_CART_UNFUSED", "1")
-    monkeypatch.setenv("TPB_CART_GENERIC", "1")
-    generic = _six_dof_run(pkg, pw, jw6, vm, am, q, jac)
+    generic = _six_dof_run(pkg, pw, jw6, vm, am, q, jac,
+                           variants=("cart_unfused", "cart_generic"))
     assert (fast["STATUS"] == 0).sum() >= B // 2
     for k in fast:
         assert fast[k].tobytes() == generic[k].tobytes(), k

@@ -11,9 +11,11 @@ KEYS = (("TIME", "time"), ("S", "s"), ("SD", "sd"), ("SDD", "sdd"), ("SD2", "sd2
         ("B_SD2_ZERO", "b_sd2_zero"), ("B_TYPE", "b_type"))
 
 
-def _solve_batch(pkg, cons, s0, s1, sd0=None, sdd0=None, t0=None, max_loops=100):
+def _solve_batch(pkg, cons, s0, s1, sd0=None, sdd0=None, t0=None, max_loops=100, variants=()):
     B, N, C, _ = cons.shape
     eng = pkg.Engine(max_paths=B, num_samples=N, max_constraints=C)
+    for v in variants:  # cross-check kernels (tpb_set_kernel_variant)
+        eng.set_kernel_variant(v)
     eng.set_constraints(cons, s0, s1)
     eng.optimize(sd0, sdd0, t0, max_loops=max_loops)
     A = pkg.ARR
@@ -122,11 +124,9 @@ def test_tied_rows_register_and_local_limit_kernels(pkg, po, monkeypatch, C):
             cons[:, :, r] = 2.0 * src
     s0 = np.zeros(B)
     s1 = rng.uniform(0.5, 5, B)
-    monkeypatch.delenv("TPB_GENERIC_LIMIT_LOCAL", raising=False)
     reg = _solve_batch(pkg, cons, s0, s1)
     _compare(po, reg, cons, s0, s1)
-    monkeypatch.setenv("TPB_GENERIC_LIMIT_LOCAL", "1")
-    loc = _solve_batch(pkg, cons, s0, s1)
+    loc = _solve_batch(pkg, cons, s0, s1, variants=("generic_limit_local",))
     for k in reg:
         assert reg[k].tobytes() == loc[k].tobytes(), k
 

@@ -11,7 +11,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB = os.path.join(_HERE, "lib", "libtpb.so")
+# TPB_LIB: another build of the library (A/B measurements of kernel variants only)
+_LIB = os.environ.get("TPB_LIB") or os.path.join(_HERE, "lib", "libtpb.so")
 
 PATH_OK = 0
 PATH_FAIL_SETUP = 1
@@ -208,6 +209,10 @@ def lib():
         L.tpb_multi_gather.argtypes = [vp, i32, vp, C.c_size_t]
         L.tpb_multi_plan_joint_host.restype = i32
         L.tpb_multi_plan_joint_host.argtypes = [vp, C.POINTER(_PlanIO)]
+        L.tpb_query_profile.restype = i32
+        L.tpb_query_profile.argtypes = [vp, i32] + [vp] * 10 + [i32]
+        L.tpb_set_kernel_variant.restype = i32
+        L.tpb_set_kernel_variant.argtypes = [vp, i32, i32]
         L.tpb_resample_uniform_noalloc.restype = i32
         L.tpb_resample_uniform_noalloc.argtypes = [C.POINTER(_ResampleDesc), vp, C.c_char_p,
                                                    C.c_size_t]
@@ -323,6 +328,28 @@ class Engine:
 
     def sync(self):
         self._ck(lib().tpb_sync(self._h))
+
+    def query_profile(self, times):
+        """tpb_query_profile on host times [B][Q]: dict(s, sd, sdd, previous_index, sk, sdk,
+        sddk, tk, status), each [B][Q]."""
+        t = _f64(times)
+        B, Q = t.shape
+        assert B == self.B
+        out = {k: np.empty((B, Q)) for k in ("s", "sd", "sdd", "sk", "sdk", "sddk", "tk")}
+        out["previous_index"] = np.empty((B, Q), np.int32)
+        out["status"] = np.empty((B, Q), np.int32)
+        self._ck(lib().tpb_query_profile(
+            self._h, Q, t.ctypes.data, out["s"].ctypes.data, out["sd"].ctypes.data,
+            out["sdd"].ctypes.data, out["previous_index"].ctypes.data, out["sk"].ctypes.data,
+            out["sdk"].ctypes.data, out["sddk"].ctypes.data, out["tk"].ctypes.data,
+            out["status"].ctypes.data, 0))
+        return out
+
+    VARIANTS = dict(generic_limit_local=0, integrate_warp=1, cart_generic=2, cart_unfused=3)
+
+    def set_kernel_variant(self, name, on=True):
+        """tpb_set_kernel_variant: use a cross-check kernel instead of the default one."""
+        self._ck(lib().tpb_set_kernel_variant(self._h, self.VARIANTS[name], 1 if on else 0))
 
     @property
     def kernel_launches(self):

@@ -65,6 +65,8 @@ struct tpb_engine {
   double *sw_keep = nullptr, *sw_wp = nullptr;
   int32_t *sw_num = nullptr, *sw_status = nullptr, *sw_modified = nullptr;
   std::vector<void*> spline_big;  // ctrl / knots of the reference's knot capacity
+  void* query_scratch = nullptr;  // tpb_query_profile with host arrays
+  size_t query_scratch_bytes = 0;
 };
 
 namespace {
@@ -90,7 +92,8 @@ template <typename T>
 cudaError_t dev_alloc(tpb_engine* e, T** p, size_t count) {
   if (count == 0) count = 1;
   void* q = nullptr;
-  cudaError_t err = cudaMalloc(&q, count * sizeof(T));
+  // 16 bytes of slack: bulk copies fetch runs rounded up to 16-byte units (tpb_bulk.cuh)
+  cudaError_t err = cudaMalloc(&q, count * sizeof(T) + 16);
   if (err != cudaSuccess) return err;
   e->allocs.push_back(q);
   *p = static_cast<T*>(q);
@@ -338,6 +341,7 @@ int32_t tpb_destroy(tpb_engine* e) {
   for (void* p : e->allocs) cudaFree(p);
   for (void* p : e->w_big) cudaFree(p);
   for (void* p : e->spline_big) cudaFree(p);
+  if (e->query_scratch) cudaFree(e->query_scratch);
   if (e->any_active_host) cudaFreeHost(e->any_active_host);
   if (e->aux_stream) {
     cudaStreamSynchronize(e->aux_stream);
@@ -1003,13 +1007,13 @@ int32_t tpb_switch_to_waypoint_path(tpb_engine* e, const double* keep_path_until
   const int cap_points = std::max(2 * (std::max(3 * d.Wmax - 2, 4) + 3), 100) - 3;
   if (d.max_points < cap_points) {
     const size_t tables = sizeof(double) * (static_cast<size_t>(cap_points) + 3 +
-                                            static_cast<size_t>(cap_points) * D + 2 * D);
+                                            static_cast<size_t>(cap_points) * D + 2 * D + 8);
     if (tables > 48 * 1024)
       return fail(e, TPB_UNIMPLEMENTED, "spline capacity for switching exceeds the sampling kernel's shared memory");
     double *ctrl = nullptr, *knots = nullptr;
-    TPB_CUDA(e, cudaMalloc(reinterpret_cast<void**>(&ctrl), sizeof(double) * Bm * cap_points * D));
+    TPB_CUDA(e, cudaMalloc(reinterpret_cast<void**>(&ctrl), sizeof(double) * Bm * cap_points * D + 16));
     e->spline_big.push_back(ctrl);
-    TPB_CUDA(e, cudaMalloc(reinterpret_cast<void**>(&knots), sizeof(double) * Bm * (cap_points + 3)));
+    TPB_CUDA(e, cudaMalloc(reinterpret_cast<void**>(&knots), sizeof(double) * Bm * (cap_points + 3) + 16));
     e->spline_big.push_back(knots);
     e->launches += tpb::launch_restride_spline(d.B, d.D, d.max_points, cap_points, e->a.ctrl,
                                                e->a.knots, ctrl, knots, e->stream);
@@ -1243,6 +1247,18 @@ int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
   return TPB_OK;
 }
 
+int32_t tpb_set_kernel_variant(tpb_engine* e, tpb_kernel_variant which, int32_t on) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  const int bit = static_cast<int>(which);
+  if (bit < 0 || bit > 3) return fail(e, TPB_INVALID_ARGUMENT, "unknown kernel variant");
+  if (on) {
+    e->dims.variants |= (1u << bit);
+  } else {
+    e->dims.variants &= ~(1u << bit);
+  }
+  return TPB_OK;
+}
+
 int32_t tpb_get(tpb_engine* e, tpb_array what, void* dst, size_t bytes, int32_t to_device) {
   if (e == nullptr || dst == nullptr) return TPB_INVALID_ARGUMENT;
   cudaSetDevice(e->device);
@@ -1268,6 +1284,68 @@ int32_t tpb_devptr(tpb_engine* e, tpb_array what, void** ptr, size_t* bytes) {
   if (!lookup(e, what, &r) || r.ptr == nullptr) return fail(e, TPB_NOT_FOUND, "unknown array");
   *ptr = r.ptr;
   if (bytes) *bytes = r.bytes;
+  return TPB_OK;
+}
+
+// ---------------------------------------------------------------- profile queries (A16)
+int32_t tpb_query_profile(tpb_engine* e, int32_t queries_per_path, const double* time_sec,
+                          double* s, double* sd, double* sdd, int32_t* previous_index,
+                          double* sk, double* sdk, double* sddk, double* tk, int32_t* status,
+                          int32_t on_device) {
+  if (e == nullptr || time_sec == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (!e->optimized) return fail(e, TPB_FAILED_PRECONDITION, "Error, solution not yet calculated!");
+  if (queries_per_path < 1) return fail(e, TPB_INVALID_ARGUMENT, "queries_per_path must be >= 1");
+  if (d.B > 65535) return fail(e, TPB_OUT_OF_RANGE, "profile queries need <= 65535 paths");
+  cudaSetDevice(e->device);
+  const size_t n = static_cast<size_t>(d.B) * queries_per_path;
+  tpb::ProfileQueryArgs p;
+  p.Q = queries_per_path;
+  p.use_s_range = e->mode != Mode::kJoint;
+  double* outs[7] = {s, sd, sdd, sk, sdk, sddk, tk};
+  if (on_device) {
+    p.time = time_sec;
+    p.s = s; p.sd = sd; p.sdd = sdd;
+    p.sk = sk; p.sdk = sdk; p.sddk = sddk; p.tk = tk;
+    p.prev_index = previous_index;
+    p.status = status;
+  } else {
+    // host arrays: staged through a scratch buffer of the engine that only grows
+    const size_t need = n * (8 * sizeof(double) + 2 * sizeof(int32_t));
+    if (need > e->query_scratch_bytes) {
+      TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+      if (e->query_scratch) cudaFree(e->query_scratch);
+      e->query_scratch = nullptr;
+      e->query_scratch_bytes = 0;
+      TPB_CUDA(e, cudaMalloc(&e->query_scratch, need + 16));
+      e->query_scratch_bytes = need;
+    }
+    double* base = static_cast<double*>(e->query_scratch);
+    TPB_CUDA(e, copy_in(e, base, time_sec, n * sizeof(double), 0));
+    p.time = base;
+    double** dst[7] = {&p.s, &p.sd, &p.sdd, &p.sk, &p.sdk, &p.sddk, &p.tk};
+    for (int k = 0; k < 7; ++k)
+      if (outs[k] != nullptr) *dst[k] = base + (k + 1) * n;
+    int32_t* ibase = reinterpret_cast<int32_t*>(base + 8 * n);
+    if (previous_index) p.prev_index = ibase;
+    if (status) p.status = ibase + n;
+  }
+  e->launches += tpb::launch_profile_query(d, e->a, p, e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  if (!on_device) {
+    const double* src[7] = {p.s, p.sd, p.sdd, p.sk, p.sdk, p.sddk, p.tk};
+    for (int k = 0; k < 7; ++k)
+      if (outs[k] != nullptr)
+        TPB_CUDA(e, cudaMemcpyAsync(outs[k], src[k], n * sizeof(double), cudaMemcpyDeviceToHost,
+                                    e->stream));
+    if (previous_index)
+      TPB_CUDA(e, cudaMemcpyAsync(previous_index, p.prev_index, n * sizeof(int32_t),
+                                  cudaMemcpyDeviceToHost, e->stream));
+    if (status)
+      TPB_CUDA(e, cudaMemcpyAsync(status, p.status, n * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                                  e->stream));
+    TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+  }
   return TPB_OK;
 }
 

@@ -687,15 +687,14 @@ int launch_cart_ik_builtin(const Dims& d, const DeviceArrays& a, int model, cuda
 }
 
 // Rows + per-sample limit curve: one fused launch for 6- and 7-dof arms, else
-// k_cart_constraints followed by k_generic_limit.  TPB_CART_UNFUSED=1 forces the
-// two-kernel path (used by the parity tests to compare the two).
+// k_cart_constraints followed by k_generic_limit.  TPB_VARIANT_CART_UNFUSED
+// (tpb_set_kernel_variant) forces the two-kernel path (the parity tests compare the two).
 int launch_cart_constraints(const Dims& d, const DeviceArrays& a, double safety,
                             double max_trans_vel, double max_rot_vel, int model, bool have_jac,
                             cudaStream_t st) {
   const dim3 grid = path_grid((d.N + kCartThreads - 1) / kCartThreads, d.B);
   if (!have_jac && (model != TPB_KIN_FAKE7 || d.D != 7)) return -1;
-  const char* env = std::getenv("TPB_CART_UNFUSED");
-  const bool fused = !(env != nullptr && env[0] == '1') && d.C == 2 * d.D + 2;
+  const bool fused = ((d.variants >> TPB_VARIANT_CART_UNFUSED) & 1u) == 0 && d.C == 2 * d.D + 2;
   if (fused && d.D == 7) {
     if (have_jac)
       k_cart_constraints_limit<false, 7><<<grid, kCartThreads, 0, st>>>(d, a, safety, max_trans_vel, max_rot_vel);

@@ -143,9 +143,26 @@ struct Dims {
   int Cmax = 0;  // capacity of explicit rows
   int C = 0;     // rows of the current problem (2*D for joint paths)
   int64_t r_cap = 0;
+  // tpb_set_kernel_variant: bit k set = cross-check variant TPB_VARIANT_<k> is used
+  // instead of the default kernel (host-side launch decisions only)
+  uint32_t variants = 0;
 };
 
 enum class Mode { kNone, kJoint, kGeneric, kCartesian };
+
+// tpb_query_profile (tpb_query.cu): Q query times per path, all pointers on the device,
+// outputs [B][Q], any output may be null
+struct ProfileQueryArgs {
+  int Q = 0;
+  bool use_s_range = false;  // the parameter range is s_start / s_end (explicit rows, Cartesian)
+  const double* time = nullptr;
+  double *s = nullptr, *sd = nullptr, *sdd = nullptr;
+  int32_t* prev_index = nullptr;
+  double *sk = nullptr, *sdk = nullptr, *sddk = nullptr, *tk = nullptr;
+  int32_t* status = nullptr;
+};
+int launch_profile_query(const struct Dims& d, const struct DeviceArrays& a,
+                         const ProfileQueryArgs& p, cudaStream_t st);
 
 // ---- kernel launchers (tpb_kernels.cu); each returns the number of kernels
 // it launched.

@@ -16,6 +16,7 @@
 #include <cstring>
 #include <type_traits>
 
+#include "tpb_bulk.cuh"
 #include "tpb_engine.h"
 #include "tpb_fit.cuh"
 #include "tpb_integrate.cuh"
@@ -170,34 +171,74 @@ k_joint_sample_limit_any(Dims dm, DeviceArrays a, double safety) {
 #ifndef TPB_SL_MINBLOCKS
 #define TPB_SL_MINBLOCKS 4
 #endif
+//
+// Staging: the path's knot vector and control points are contiguous runs in HBM and come
+// in as two bulk asynchronous copies (cp.async.bulk.shared::cluster.global, completion
+// counted on an mbarrier), issued by thread 0 while the other threads compute the scaled
+// limits; a run that does not start on a 16-byte boundary is fetched from the boundary
+// before it (the extra 8 bytes belong to the neighbouring path's row) and addressed with an
+// offset.  The three [128][kD] output tiles leave as bulk copies when their HBM address is
+// 16-byte aligned (always for even N).  TPB_SL_BULK_IN / TPB_SL_BULK_OUT = 0 build the
+// per-thread loops (A/B; profiles/r2_summary.md).
+#ifndef TPB_SL_BULK_IN
+#define TPB_SL_BULK_IN 1
+#endif
+#ifndef TPB_SL_BULK_OUT
+#define TPB_SL_BULK_OUT 1
+#endif
+// shared-memory doubles of k_joint_sample_limit: [knots + 2][ctrl + 2][aS][vS2][pad][3 tiles]
+__host__ __device__ inline int sample_limit_table_doubles(int max_points, int D) {
+  return ((max_points + 3 + 2 + 1) & ~1) + ((max_points * D + 2 + 1) & ~1) + ((2 * D + 1) & ~1);
+}
+
 template <int kD>
 __global__ void __launch_bounds__(kSampleThreads, TPB_SL_MINBLOCKS)
 k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
+  __shared__ __align__(8) uint64_t s_bar;
   const int b = path_of_block();
   if (b >= dm.B) return;  // uniform per CTA (grid folded over y and z)
   if (a.active != nullptr && a.active[b] == 0) return;  // uniform per CTA
   const int n = a.num_points[b];
   const int nk = n + 3;
-  double* s_knots = smem;                         // [max_points + 3]
-  double* s_ctrl = s_knots + dm.max_points + 3;   // [max_points][kD]
-  double* s_aS = s_ctrl + dm.max_points * kD;     // [kD]  amax * safety
-  double* s_vS2 = s_aS + kD;                      // [kD]  (vmax * safety)^2
-  double* s_out = s_vS2 + kD;                     // [3][kSampleThreads * kD]
-  {
-    const double* gk = a.knots + static_cast<size_t>(b) * (dm.max_points + 3);
-    const double* gc = a.ctrl + static_cast<size_t>(b) * dm.max_points * kD;
-    for (int i = threadIdx.x; i < nk; i += blockDim.x) s_knots[i] = gk[i];
-    for (int i = threadIdx.x; i < n * kD; i += blockDim.x) s_ctrl[i] = gc[i];
-    if (threadIdx.x < kD) {
-      const double am = a.amax[static_cast<size_t>(b) * kD + threadIdx.x];
-      const double vm = a.vmax[static_cast<size_t>(b) * kD + threadIdx.x];
-      s_aS[threadIdx.x] = am * safety;
-      const double vs = vm * safety;
-      s_vS2[threadIdx.x] = vs * vs;
-    }
+  double* s_kbuf = smem;                                        // [max_points + 3 + 2]
+  double* s_cbuf = s_kbuf + ((dm.max_points + 3 + 2 + 1) & ~1);  // [max_points * kD + 2]
+  double* s_aS = s_cbuf + ((dm.max_points * kD + 2 + 1) & ~1);   // [kD]  amax * safety
+  double* s_vS2 = s_aS + kD;                                    // [kD]  (vmax * safety)^2
+  double* s_out = smem + sample_limit_table_doubles(dm.max_points, kD);  // [3][128 * kD]
+  const double* gk = a.knots + static_cast<size_t>(b) * (dm.max_points + 3);
+  const double* gc = a.ctrl + static_cast<size_t>(b) * dm.max_points * kD;
+#if TPB_SL_BULK_IN
+  const int kmis = static_cast<int>((reinterpret_cast<uintptr_t>(gk) >> 3) & 1);
+  const int cmis = static_cast<int>((reinterpret_cast<uintptr_t>(gc) >> 3) & 1);
+  const double* s_knots = s_kbuf + kmis;
+  const double* s_ctrl = s_cbuf + cmis;
+  if (threadIdx.x == 0) {
+    bulk::mbar_init(&s_bar, 1);
+    bulk::fence_mbar_init();
+    const uint32_t kbytes = static_cast<uint32_t>((nk + kmis + 1) & ~1) * 8u;
+    const uint32_t cbytes = static_cast<uint32_t>((n * kD + cmis + 1) & ~1) * 8u;
+    bulk::mbar_expect_tx(&s_bar, kbytes + cbytes);
+    bulk::bulk_load(s_kbuf, gk - kmis, kbytes, &s_bar);
+    bulk::bulk_load(s_cbuf, gc - cmis, cbytes, &s_bar);
   }
-  __syncthreads();
+#else
+  double* s_knots = s_kbuf;
+  double* s_ctrl = s_cbuf;
+  for (int i = threadIdx.x; i < nk; i += blockDim.x) s_knots[i] = gk[i];
+  for (int i = threadIdx.x; i < n * kD; i += blockDim.x) s_ctrl[i] = gc[i];
+#endif
+  if (threadIdx.x < kD) {
+    const double am = a.amax[static_cast<size_t>(b) * kD + threadIdx.x];
+    const double vm = a.vmax[static_cast<size_t>(b) * kD + threadIdx.x];
+    s_aS[threadIdx.x] = am * safety;
+    const double vs = vm * safety;
+    s_vS2[threadIdx.x] = vs * vs;
+  }
+  __syncthreads();  // the barrier is initialised, the limits are written
+#if TPB_SL_BULK_IN
+  bulk::mbar_wait(&s_bar, 0);  // the tables have landed
+#endif
   const int idx0 = blockIdx.x * kSampleThreads;
   const int idx = idx0 + threadIdx.x;
   const bool live = idx < dm.N;
@@ -260,10 +301,27 @@ k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
     a.b_raw_sdd_min[o] = smin;
     a.b_at0[o] = fabs(sd2max - sd2zero) < kTiny;
   }
-  __syncthreads();
-  // coalesced copy-out of this CTA's rows [idx0, idx0 + cnt)
+  // copy-out of this CTA's rows [idx0, idx0 + cnt): three contiguous runs
   const int cnt = min(kSampleThreads, dm.N - idx0);
   const size_t g0 = (static_cast<size_t>(b) * dm.N + idx0) * kD;
+#if TPB_SL_BULK_OUT
+  const bool vec = ((cnt * kD) & 1) == 0 && bulk::aligned16(a.q + g0) &&
+                   bulk::aligned16(a.dq + g0) && bulk::aligned16(a.ddq + g0);
+  if (vec) {
+    bulk::fence_async_shared();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint32_t bytes = static_cast<uint32_t>(cnt * kD) * 8u;
+      bulk::bulk_store(a.q + g0, s_out, bytes);
+      bulk::bulk_store(a.dq + g0, s_out + kSampleThreads * kD, bytes);
+      bulk::bulk_store(a.ddq + g0, s_out + 2 * kSampleThreads * kD, bytes);
+      bulk::bulk_commit();
+      bulk::bulk_wait_read<0>();  // shared memory stays valid until the copies have read it
+    }
+    return;
+  }
+#endif
+  __syncthreads();
   for (int k = threadIdx.x; k < cnt * kD; k += kSampleThreads) {
     a.q[g0 + k] = s_out[k];
     a.dq[g0 + k] = s_out[kSampleThreads * kD + k];
@@ -461,15 +519,31 @@ constexpr int kResampleThreads = 224;
 // are erased in front (row i is grid row i + grid_skip, so that the times keep the
 // bits of the grid they were first computed on), and with kSkip row 0's lower-index
 // scan starts at v.first_from[b] and row i > 0 is sample keep[b][keep_base + i - 1].
+//
+// The three [32][D] tiles of a warp leave shared memory as bulk asynchronous copies
+// (cp.async.bulk.global.shared::cta, issued by lane 0) instead of a per-lane copy loop.
+// A bulk copy needs 16-byte aligned addresses on both sides; rows are D * 8 bytes, so for
+// odd D every other row starts 8 bytes off.  The tile is therefore written into shared
+// memory with the same 8-byte offset the destination has (`shift`): the head element (if
+// any) and a tail element are stored by lane 0 directly, everything between them is one
+// aligned bulk copy per array.  TPB_RESAMPLE_BULK=0 builds the per-lane loop (A/B).
+#ifndef TPB_RESAMPLE_BULK
+#define TPB_RESAMPLE_BULK 1
+#endif
+// doubles of one warp's tile region: 3 x (32 x D + 2 for the shift), kept even
+__host__ __device__ inline int resample_tile_doubles(int D) { return 3 * ((32 * D + 3) & ~1); }
+
 template <bool kSmemTime, bool kSkip>
 __global__ void __launch_bounds__(kResampleThreads)
 k_resample_fill(Dims dm, DeviceArrays a, ResampleView v, const int32_t* keep, double start_sec,
                 double dt) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
   const int stride = dm.N, D = dm.D;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int plane = (32 * D + 3) & ~1;                      // one array's tile, even
   double* s_time = smem;                                    // [N] (kSmemTime)
-  double* s_tile = smem + (kSmemTime ? stride : 0) + warp * 3 * 32 * D;  // [3][32][D] per warp
+  // [3][plane] per warp, 16-byte aligned
+  double* s_tile = smem + (kSmemTime ? ((stride + 1) & ~1) : 0) + warp * 3 * plane;
   for (int b = blockIdx.x; b < dm.B; b += gridDim.x) {
     const int M = a.r_count[b];
     if (M == 0) continue;  // uniform per CTA
@@ -490,9 +564,24 @@ k_resample_fill(Dims dm, DeviceArrays a, ResampleView v, const int32_t* keep, do
     for (int base = warp * 32; base < M; base += kResampleThreads) {
       const int i = base + lane;
       const bool live = i < M;
+      // rows [base, base + cnt) of this path are contiguous in the packed arrays
+      const int64_t wrow = row0 + base;
+      const size_t g0 = static_cast<size_t>(wrow) * D;
+      // 8-byte offset of each destination from a 16-byte boundary (caller-provided arrays
+      // of tpb_resample_uniform_noalloc may start anywhere on an 8-byte boundary)
+      auto off8 = [&](const double* base) {
+        return TPB_RESAMPLE_BULK
+                   ? static_cast<int>((reinterpret_cast<uintptr_t>(base + g0) >> 3) & 1)
+                   : 0;
+      };
+      const int shp = off8(a.r_pos), shv = off8(a.r_vel), sha = off8(a.r_acc);
+      // part 1 (per row): the bracketing samples and the scalar outputs
+      bool sample_row = false;
+      int li = 0, ui = 0;
+      double at = 0.0, sdl = 0.0, sdu = 0.0, sddl = 0.0, sddu = 0.0;
       if (live) {
         const int64_t row = row0 + i;
-        const bool sample_row = kSkip && i > 0;
+        sample_row = kSkip && i > 0;
         const int src = sample_row ? keep[o + kbase + i - 1] : 0;
         const double t = sample_row ? tp[src] : (kSkip ? t0 : t0 + dt * (i + grid_skip));
         // TimeAtPathSamplesLowerIndex (:686-695): first index with time[index+1] > t,
@@ -507,18 +596,30 @@ k_resample_fill(Dims dm, DeviceArrays a, ResampleView v, const int32_t* keep, do
             lo = mid + 1;
           }
         }
-        const int li = sample_row ? src : lo;
-        const int ui = sample_row ? src : min(N - 1, li + 1);
+        li = sample_row ? src : lo;
+        ui = sample_row ? src : min(N - 1, li + 1);
         const double tl = tp[li], tu = tp[ui];
-        const double at = (fabs(tu - tl) < DBL_EPSILON) ? 0.5 : (t - tl) / (tu - tl);
-        const double sdl = a.sd[o + li], sdu = a.sd[o + ui];
-        const double sddl = a.sdd[o + li], sddu = a.sdd[o + ui];
+        at = (fabs(tu - tl) < DBL_EPSILON) ? 0.5 : (t - tl) / (tu - tl);
+        sdl = a.sd[o + li];
+        sdu = a.sd[o + ui];
+        sddl = a.sdd[o + li];
+        sddu = a.sdd[o + ui];
         if (row < dm.r_cap) {
           a.r_time[row] = t;
           a.r_s[row] = sample_row ? a.s[o + li] : lerp(at, a.s[o + li], a.s[o + ui]);
           a.r_sd[row] = sample_row ? sdl : lerp(at, sdl, sdu);
           a.r_sdd[row] = sample_row ? sddl : lerp(at, sddl, sddu);
         }
+      }
+#if TPB_RESAMPLE_BULK
+      // the bulk copies of this warp's previous pass must have read the tile before it is
+      // rewritten; waiting here (not right after issuing them) lets the searches and loads
+      // above overlap them
+      if (lane == 0) bulk::bulk_wait_read<0>();
+      __syncwarp();
+#endif
+      // part 2 (per row and dof): the tile
+      if (live) {
         const bool last = (i == M - 1);
         const double sdl2 = sdl * sdl, sdu2 = sdu * sdu;  // eigenmath::Square
         for (int d = 0; d < D; ++d) {
@@ -540,25 +641,47 @@ k_resample_fill(Dims dm, DeviceArrays a, ResampleView v, const int32_t* keep, do
             vel = sample_row ? vl : lerp(at, vl, vu);
             acc = sample_row ? al : clampa(lerp(at, al, au), am);
           }
-          s_tile[lane * D + d] = pos;
-          s_tile[32 * D + lane * D + d] = vel;
-          s_tile[64 * D + lane * D + d] = acc;
+          s_tile[shp + lane * D + d] = pos;
+          s_tile[plane + shv + lane * D + d] = vel;
+          s_tile[2 * plane + sha + lane * D + d] = acc;
         }
       }
-      __syncwarp();
-      // rows [base, base + cnt) of this path are contiguous in the packed arrays
-      const int64_t wrow = row0 + base;
       int cnt = min(32, M - base);
       if (wrow + cnt > dm.r_cap) cnt = (wrow < dm.r_cap) ? static_cast<int>(dm.r_cap - wrow) : 0;
-      const size_t g0 = static_cast<size_t>(wrow) * D;
-      for (int k = lane; k < cnt * D; k += 32) {
+      const int total = cnt * D;
+#if TPB_RESAMPLE_BULK
+      // the tile's ordinary stores become visible to the async proxy, then lane 0 copies
+      bulk::fence_async_shared();
+      __syncwarp();
+      if (lane == 0 && total > 0) {
+        double* dst[3] = {a.r_pos + g0, a.r_vel + g0, a.r_acc + g0};
+        const int shifts[3] = {shp, shv, sha};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const int head = shifts[k];                // elements before the aligned part
+          const int body = (total - head) & ~1;      // even number of doubles
+          const double* src = s_tile + k * plane + head;
+          if (head) dst[k][0] = src[0];
+          if (body > 0)
+            bulk::bulk_store(dst[k] + head, src + head, static_cast<uint32_t>(body) * 8u);
+          if (head + body < total) dst[k][total - 1] = src[total - 1];
+        }
+        bulk::bulk_commit();
+      }
+#else
+      __syncwarp();
+      for (int k = lane; k < total; k += 32) {
         a.r_pos[g0 + k] = s_tile[k];
-        a.r_vel[g0 + k] = s_tile[32 * D + k];
-        a.r_acc[g0 + k] = s_tile[64 * D + k];
+        a.r_vel[g0 + k] = s_tile[plane + k];
+        a.r_acc[g0 + k] = s_tile[2 * plane + k];
       }
       __syncwarp();
+#endif
     }
   }
+#if TPB_RESAMPLE_BULK
+  if (lane == 0) bulk::bulk_wait_read<0>();  // shared memory stays valid until then
+#endif
 }
 
 __global__ void k_fill_f64(double* p, double v, int n) {
@@ -597,7 +720,8 @@ int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safet
   const size_t tables =
       sizeof(double) * (static_cast<size_t>(d.max_points) + 3 + static_cast<size_t>(d.max_points) * d.D + 2 * d.D);
   const dim3 grid = path_grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
-  const size_t smem = tables + sizeof(double) * 3 * kSampleThreads * d.D;
+  const size_t smem = sizeof(double) * (sample_limit_table_doubles(d.max_points, d.D) +
+                                        static_cast<size_t>(3) * kSampleThreads * d.D);
   if (d.D <= 8 && smem <= 48 * 1024) {
 #define TPB_SL(K) \
   case K: k_joint_sample_limit<K><<<grid, kSampleThreads, smem, st>>>(d, a, safety); break
@@ -613,12 +737,12 @@ int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safet
 
 // C <= 12: rows in registers, kC = C rounded up to even.  Above that the fully
 // predicated candidate tests (2*kC candidates x kC rows) cost more than the local-memory
-// kernel's early exits (measured, profiles/r1_summary.md v9).  TPB_GENERIC_LIMIT_LOCAL=1
-// keeps the local-memory kernel for every C (the parity tests compare the two).
+// kernel's early exits (measured, profiles/r1_summary.md v9).  TPB_VARIANT_GENERIC_LIMIT_LOCAL
+// (tpb_set_kernel_variant) keeps the local-memory kernel for every C (the parity tests
+// compare the two).
 int launch_generic_limit(const Dims& d, const DeviceArrays& a, cudaStream_t st) {
   const dim3 grid = path_grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
-  const char* env = std::getenv("TPB_GENERIC_LIMIT_LOCAL");
-  const bool local = env != nullptr && env[0] == '1';
+  const bool local = (d.variants >> TPB_VARIANT_GENERIC_LIMIT_LOCAL) & 1u;
   const int kc = local ? 99 : (d.C + 1) / 2 * 2;
   switch (kc) {
     case 2: k_generic_limit_reg<2><<<grid, kSampleThreads, 0, st>>>(d, a); break;
@@ -642,11 +766,8 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
   };
   const int blocks = (d.B + kWarpsPerBlock - 1) / kWarpsPerBlock;
   const bool joint = mode == Mode::kJoint;
-  // TPB_INTEGRATE=warp selects the one-path-per-warp kernel (read once).
-  static const bool use_pair = []() {
-    const char* e = std::getenv("TPB_INTEGRATE");
-    return !(e && std::strcmp(e, "warp") == 0);
-  }();
+  // TPB_VARIANT_INTEGRATE_WARP selects the one-path-per-warp kernel
+  const bool use_pair = ((d.variants >> TPB_VARIANT_INTEGRATE_WARP) & 1u) == 0;
   if (joint && d.D <= 8 && use_pair) {
     // setup and finalize one warp per path, the sweeps two paths per warp
     const int threads = kWarpsPerBlock * 32;
@@ -672,11 +793,10 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
     return 3;
   }
   // Cartesian paths with 6 or 7 dofs: joint rows + the two speed rows on the padding
-  // lanes (Joint8Policy<., true>); TPB_CART_GENERIC=1 keeps the generic rows-in-shared-
+  // lanes (Joint8Policy<., true>); TPB_VARIANT_CART_GENERIC keeps the generic rows-in-shared-
   // memory solver (the parity tests compare the two)
-  const char* cg = std::getenv("TPB_CART_GENERIC");
   if (mode == Mode::kCartesian && (d.D == 6 || d.D == 7) && d.C == 2 * d.D + 2 &&
-      !(cg != nullptr && cg[0] == '1')) {
+      ((d.variants >> TPB_VARIANT_CART_GENERIC) & 1u) == 0) {
     const int threads = kWarpsPerBlock * 32;
     const int per_block = kPairWarpsPerBlock * 2;
     const int pblocks = (d.B + per_block - 1) / per_block;
@@ -721,8 +841,8 @@ int launch_resample_rows(const Dims& d, const DeviceArrays& a, const ResampleVie
                          const int32_t* keep, double start_sec, double dt, int num_sms,
                          cudaStream_t st, bool skip, bool continued) {
   k_scan_offsets<<<1, 1024, 0, st>>>(d.B, a.r_count, a.r_offset, continued ? 1 : 0);
-  const size_t tile = sizeof(double) * (kResampleThreads / 32) * 3 * 32 * d.D;
-  const size_t with_time = tile + sizeof(double) * d.N;
+  const size_t tile = sizeof(double) * (kResampleThreads / 32) * resample_tile_doubles(d.D);
+  const size_t with_time = tile + sizeof(double) * ((d.N + 1) & ~1);
   const int grid = std::min(d.B, num_sms * 16);
   if (with_time <= 160 * 1024) {
     // > 48 KB of dynamic shared memory is opt-in (per device, so set it every time)

@@ -187,60 +187,31 @@ class TimeOptimalPathProfile {
     return tp::OkStatus();
   }
 
-  // Result queries on the downloaded profile (:1497-1668); O(log N) host look-ups.
+  // Result queries (:1497-1668) run on the device (tpb_query_profile, one query of this
+  // one profile per call; TimeOptimalPathProfileBatch / the C ABI take whole grids).
   int GetPreviousIndex(Scalar t) const {
-    if (state_ != kProblemSolved || t < time_[0]) return -1;
-    if (t > time_[num_samples_ - 1]) return num_samples_ - 1;
-    return SampleIndexFromTime(t);
+    if (state_ != kProblemSolved) return -1;
+    int32_t k = -1;
+    if (tpb_query_profile(e_, 1, &t, nullptr, nullptr, nullptr, &k, nullptr, nullptr, nullptr,
+                          nullptr, nullptr, 0) != TPB_OK)
+      return -1;
+    return k;
   }
   bool GetPreviousDiscreteValues(Scalar t, Scalar* sk, Scalar* sdk, Scalar* sddk, Scalar* tk) const {
-    const int k = GetPreviousIndex(t);
-    if (k < 0) return false;
-    *sk = s_[k];
-    *sdk = sd_[k];
-    *sddk = sdd_[k];
-    *tk = time_[k];
-    return true;
+    if (state_ != kProblemSolved) return false;
+    int32_t st = 3;
+    if (tpb_query_profile(e_, 1, &t, nullptr, nullptr, nullptr, nullptr, sk, sdk, sddk, tk, &st,
+                          0) != TPB_OK)
+      return false;
+    return (st & 2) == 0;
   }
   bool GetPathParameterAndDerivatives(Scalar t, Scalar* s, Scalar* sd, Scalar* sdd) const {
     if (state_ != kProblemSolved) return false;
-    const int N = num_samples_;
-    const Scalar ds_ = (s_end_ - s_start_) / (N - 1), inv_ds = Scalar(1) / ds_;
-    if (t <= time_[0]) {
-      *s = s_start_;
-      *sd = sd_[0];
-      *sdd = 0.5 * inv_ds * (sd2_[1] - sd2_[0]);
-      return true;
-    }
-    if (t >= time_[N - 1]) {
-      *s = s_end_;
-      *sd = sd_[N - 1];
-      *sdd = 0.0;
-      return true;
-    }
-    const int k = SampleIndexFromTime(t);
-    if (time_[k] == time_[k + 1]) {
-      *s = s_[k + 1];
-      *sd = sd_[k + 1];
-      *sdd = 0.5 * inv_ds * (sd2_[k + 1] - sd2_[k]);
-      return true;
-    }
-    const Scalar dt = t - time_[k];
-    if (k > N - 2) return false;
-    const Scalar sda = sd_[k], sdb = sd_[k + 1], sd2a = sd2_[k], sd2b = sd2_[k + 1];
-    if (sda > 0 || sdb > 0) {
-      Scalar ds = sda * dt + dt * dt * 0.25 * inv_ds * (sd2b - sd2a);
-      if (ds > ds_) ds = ds_;
-      if (dt < 0 || ds < 0) return false;
-      *s = std::min(s_[k] + ds, s_[k + 1]);
-      *sd = std::sqrt(sd2a + ds * inv_ds * (sd2b - sd2a));
-      *sdd = 0.5 * inv_ds * (sd2b - sd2a);
-    } else {
-      *s = s_[k] + (s_[k + 1] - s_[k]) * dt / (time_[k + 1] - time_[k]);
-      *sd = 0.0;
-      *sdd = 0.0;
-    }
-    return true;
+    int32_t st = 3;
+    if (tpb_query_profile(e_, 1, &t, s, sd, sdd, nullptr, nullptr, nullptr, nullptr, nullptr,
+                          &st, 0) != TPB_OK)
+      return false;
+    return (st & 1) == 0;
   }
 
   // FindMaxSd2Simplex (:1149-1363) for one constraint table, on the device.
@@ -275,27 +246,6 @@ class TimeOptimalPathProfile {
   static int& Device() {
     static int d = 0;
     return d;
-  }
-  // SampleIndexFromTime (:1497-1524)
-  int SampleIndexFromTime(Scalar t) const {
-    const int N = num_samples_;
-    if (t <= time_[0]) return 0;
-    if (t >= time_[N - 1]) return N - 2;
-    int low = 0;
-    while ((time_[low] == time_[low + 1]) && (low < N - 2)) low++;
-    int high = N - 1;
-    while ((time_[high] == time_[high - 1]) && (high >= low)) high--;
-    int mid = (low + high) / 2;
-    while (t < time_[mid] || t >= time_[mid + 1]) {
-      if (t < time_[mid]) {
-        high = mid;
-      } else {
-        low = mid;
-      }
-      mid = (low + high) / 2;
-    }
-    while ((time_[mid] == time_[mid + 1]) && (mid < N - 1)) mid++;
-    return mid;
   }
 
   tpb_engine* e_ = nullptr;
