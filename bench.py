@@ -42,14 +42,20 @@ WORKLOAD = ("cfg2: 4096 synthetic 7-DoF joint-spline paths x 2048 samples per GP
             "time-optimal timing + 4 ms uniform resampling")
 
 
+#: the sources of the kernels whose ncu counters bench.py reads (profiles/tools/ops_from_raw.py
+#: hashes the same list)
+HOT_KERNEL_SOURCES = ("tpb_kernels.cu", "tpb_integrate.cuh", "tpb_integrate_pair.cuh",
+                      "tpb_joint_limit.cuh", "tpb_row_limit.cuh", "tpb_solver.cuh", "tpb_device.cuh",
+                      "tpb_bulk.cuh", "tpb_fit.cuh")
+
+
 def _csrc_hash():
     """Hash of the CUDA sources; profiles/fp64_ops.json and traffic.json carry the hash of
     the build they were captured from ("_csrc_hash"), so stale counters are visible."""
-    import glob
     import hashlib
     h = hashlib.sha256()
-    for f in sorted(glob.glob(os.path.join(ROOT, "x-edr-trajectory-planning_b200", "csrc", "*.cu*"))):
-        with open(f, "rb") as fh:
+    for name in HOT_KERNEL_SOURCES:
+        with open(os.path.join(ROOT, "x-edr-trajectory-planning_b200", "csrc", name), "rb") as fh:
             h.update(fh.read())
     return h.hexdigest()[:16]
 
@@ -499,6 +505,9 @@ def run_ours(args):
     planner = run_planner_leg(pkg, torch, dev, stream, local_rank, d_wp, d_vmax, d_amax, B, D, W,
                               max_over_ranks, barrier, world, args)
 
+    # ---- BASELINE config 1: one path, latency ----
+    cfg1 = run_cfg1_leg(pkg, local_rank, rank, world, args)
+
     # ---- BASELINE config 4: 65,536 paths in total, strong-scaled over the ranks ----
     cfg4 = run_cfg4_leg(pkg, torch, dev, stream, local_rank, rank, world, max_over_ranks,
                         barrier, args)
@@ -561,7 +570,7 @@ def run_ours(args):
         spline_compact = None
         if spline:
             poly = {k: v for k, v in spline.items()
-                    if isinstance(v, dict) and "_" in k and k.count("_") == 1}
+                    if isinstance(v, dict) and "frac_of_peak" in v and k.count("_") == 1}
             head = spline["p3_d7"]
             worst = min(poly, key=lambda k: poly[k]["frac_of_peak"])
             spline_compact = {
@@ -571,7 +580,8 @@ def run_ours(args):
                 "frac": head["frac_of_peak"], "worst_config": worst,
                 "worst_frac": poly[worst]["frac_of_peak"],
                 "shuffled_u_frac": spline.get("p3_d7_shuffled", {}).get("frac_of_peak"),
-                "exact_mode_frac": spline.get("p3_d7_exact", {}).get("frac_of_peak")}
+                "exact_mode_frac": spline.get("p3_d7_exact", {}).get("frac_of_peak"),
+                "cpu_baseline": spline.get("cpu_baseline")}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -579,7 +589,7 @@ def run_ours(args):
             "data": "synthetic", "config": _config(),
             "spline_eval": spline_compact,
             "roofline": roofline, "cpu_baseline": cpu_baseline, "parity": parity, "e2e": e2e,
-            "cfg4": cfg4,
+            "cfg4": cfg4, "cfg1": cfg1,
             "gpu_launches": int(launches), "clocks": clock_info,
             "stage_ms": stage_ms, "paths_ok": n_ok, "resampled_rows_per_gpu": total_rows,
             "mean_duration_s": float(np.nanmean(all_dur)),
@@ -601,6 +611,51 @@ def run_ours(args):
     eng.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_cfg1_leg(pkg, local_rank, rank, world, args):
+    """BASELINE config 1, the reference's own test-sized workload: ONE 7-DoF joint-space path
+    (10 waypoints ~ U(-pi, pi)^7, degree-2 spline as the reference fits it, v_max 1, a_max 2),
+    N = 1000 path samples, 4 ms resampling, whole path in one window.  Latency of one call:
+    the host C++ class with a batch of one (PathTimingTrajectoryBatch::Plan on the GPU,
+    host buffers in and out) next to the reference's own object code on one host thread."""
+    if rank != 0 or world != 1:
+        return None
+    rng = np.random.default_rng(1)
+    D, W, N = NUM_DOFS, 10, 1000
+    wp = rng.uniform(-np.pi, np.pi, (1, W, D))
+    vmax, amax = np.full((1, D), 1.0), np.full((1, D), 2.0)
+    hb = pkg.HostBatch(D, N, int(round(TIME_STEP * 1e9)), 1, W, 65536, devices=(local_rank,))
+    lat = []
+    for i in range(25):
+        t0 = time.perf_counter()
+        rows = hb.plan(wp, vmax, amax, want="trajectory")
+        lat.append(time.perf_counter() - t0)
+    lat = np.array(lat[5:]) * 1e6
+    dur = float(hb.array("duration")[0])
+    hb.close()
+    out = {"workload": "cfg1: 1 path, 7 dof, 10 waypoints, N = 1000, 4 ms resampling",
+           "gpu_us_best": float(lat.min()), "gpu_us_median": float(np.median(lat)),
+           "rows": int(rows), "duration_s": dur,
+           "api": "PathTimingTrajectoryBatch::Plan, batch of one, host buffers in / out"}
+    if not args.no_cpu_baseline:
+        po, impl, kind, _ = _cpu_setup()
+        if impl == "ref":
+            saved = _quiet_stderr()
+            try:
+                cl = []
+                for i in range(25):
+                    t0 = time.perf_counter()
+                    r = po.plan_joint_batch_ref(wp, vmax, amax, N, dt=TIME_STEP, threads=1)
+                    cl.append(time.perf_counter() - t0)
+            finally:
+                os.dup2(saved, 2)
+            cl = np.array(cl[5:]) * 1e6
+            out.update(cpu_us_best=float(cl.min()), cpu_us_median=float(np.median(cl)),
+                       cpu_kind="reference (object code, 1 thread)",
+                       duration_equal=bool(r["duration"][0] == dur),
+                       rows_equal=bool(r["rows"][0] == rows))
+    return out
 
 
 CFG4_PATHS = 65536
@@ -1032,6 +1087,36 @@ def run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, wor
                                               "hbm_gbs_per_gpu": gbs, "frac_of_peak": gbs / peak,
                                               "bytes_per_eval": 3 * D * 8 + 8}
                 del d_u
+    if world == 1 and not args.no_cpu_baseline:
+        # CPU baseline of cfg3: the reference's own BSplineXd::EvalCurveAndDerivatives object
+        # code, one call per parameter, degree 3, 7 dofs, 2 derivatives, the same splines
+        po, impl, kind, cores = _cpu_setup()
+        if impl == "ref":
+            knots, ctrl = pkg.workloads.dense_splines(8 * cores, 3, 7, npts, 8.0)
+            u = np.tile(np.linspace(0.0, 8.0, E), (8 * cores, 1))
+            t0 = time.perf_counter()
+            ref1, _ = po.spline_eval_batch_ref(knots[:8], ctrl[:8], 3, 2, u[:8], threads=1)
+            t1 = time.perf_counter()
+            po.spline_eval_batch_ref(knots, ctrl, 3, 2, u, threads=cores)
+            t2 = time.perf_counter()
+            # parity of the device evaluation with it, on the first 8 splines
+            d_k = torch.from_numpy(knots[:8]).to(dev)
+            d_c = torch.from_numpy(ctrl[:8]).to(dev)
+            d_u = torch.from_numpy(u[:8]).to(dev)
+            o8 = torch.empty((8, E, 3, 7), dtype=torch.float64, device=dev)
+            err = {}
+            for mode, name in ((1, "exact"), (0, "polynomial")):
+                pkg.spline_eval_device(d_k, d_c, 3, 2, o8, u=d_u, exact=mode,
+                                       stream=stream.cuda_stream)
+                torch.cuda.synchronize()
+                err[name] = float(np.max(np.abs(o8.cpu().numpy() - ref1)))
+            res["cpu_baseline"] = {
+                "kind": "reference (BSplineXd::EvalCurveAndDerivatives object code)",
+                "config": "p3_d7, 2 derivatives", "cores": cores,
+                "single_thread_evals_per_s": 8 * E / (t1 - t0),
+                "all_cores_evals_per_s": 8 * cores * E / (t2 - t1),
+                "max_abs_err_vs_reference": err,
+                "tolerance": "1e-12 absolute (BASELINE.json); exact mode is bit-identical"}
     res["bytes_per_eval"] = "3*dim*8 written (implicit parameter grid, tables in smem)"
     res["modes"] = ("pP_dD: per-span polynomial form (<= 1e-12 of the reference), tiles leave shared "
                     "memory as bulk async copies (UBLKCP); pP_dD_threadstores: the same with per-"

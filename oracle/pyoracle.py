@@ -307,6 +307,10 @@ def _register_ref_planner(R):
         f = getattr(R, "tpref_planner_" + name)
         f.restype = None
         f.argtypes = [vp] + args
+    R.tpref_spline_eval_batch.restype = C.c_int
+    R.tpref_spline_eval_batch.argtypes = [C.c_int] * 4 + [c_double_p, c_double_p, C.c_int,
+                                                          c_double_p, C.c_int, C.c_int,
+                                                          c_double_p, i32p]
     R.tpref_plan_joint_batch.restype = None
     R.tpref_plan_joint_batch.argtypes = [
         C.c_int, C.c_int, C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, C.c_double,
@@ -738,6 +742,23 @@ def plan_joint_ref(waypoints, vmax, amax, N, rounding=0.2, safety=0.8, delta=-1.
                vel=w["w_vel"], acc=w["w_acc"], cons=p.constraints(), spline=p.spline())
     p.close()
     return res
+
+
+def spline_eval_batch_ref(knots, ctrl, degree, nder, u, threads=1):
+    """BASELINE cfg3 by the reference's own BSplineXd::EvalCurveAndDerivatives object code:
+    knots [S][n+degree+1], ctrl [S][n][D], u [S][E] -> (out [S][E][nder+1][D], status [S][E])."""
+    knots = np.ascontiguousarray(knots, np.float64)
+    ctrl = np.ascontiguousarray(ctrl, np.float64)
+    u = np.ascontiguousarray(u, np.float64)
+    S, n, D = ctrl.shape
+    E = u.shape[1]
+    out = np.full((S, E, nder + 1, D), np.nan)
+    status = np.zeros((S, E), np.int32)
+    rc = ref().tpref_spline_eval_batch(S, degree, n, D, _dp(knots), _dp(ctrl), E, _dp(u), nder,
+                                       int(threads), _dp(out),
+                                       status.ctypes.data_as(C.POINTER(C.c_int32)))
+    assert rc == 0, rc
+    return out, status
 
 
 def plan_joint_batch_ref(waypoints, vmax, amax, N, dt=0.004, rounding=0.2, safety=0.8,

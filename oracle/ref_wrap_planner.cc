@@ -309,6 +309,54 @@ void tpref_planner_spline(void* hv, int* counts, double* knots, int knot_cap, do
     for (int d = 0; d < h->D; ++d) points[static_cast<size_t>(i) * h->D + d] = cp[i][d];
 }
 
+// BASELINE cfg3 on the host: dense evaluation with derivatives by the reference's own
+// BSplineXd (splines/bspline.h:539-568 EvalCurveAndDerivatives over BSplineBase::KnotSpan
+// / UpdateBasisAndDerivatives, bspline_base.cc:218-348), one parameter per call as the
+// reference's API has it; splines are spread over `nthreads` host threads.
+//   knots [S][n + degree + 1], ctrl [S][n][D], u [S][E], out [S][E][nder + 1][D],
+//   status [S][E] (absl code per evaluation; may be NULL).  Returns an absl code.
+int tpref_spline_eval_batch(int S, int degree, int n, int D, const double* knots,
+                            const double* ctrl, int E, const double* u, int nder, int nthreads,
+                            double* out, int32_t* status) {
+  const int nk = n + degree + 1;
+  std::atomic<int> next{0};
+  std::atomic<int> first_error{0};
+  auto worker = [&]() {
+    trajectory_planning::BSplineXd spline;
+    std::vector<VectorXd> values(nder + 1, VectorXd(D));
+    for (;;) {
+      const int s = next.fetch_add(1);
+      if (s >= S) break;
+      const std::vector<VectorXd> pts = Rows(ctrl + static_cast<size_t>(s) * n * D, n, D);
+      const std::vector<double> kn(knots + static_cast<size_t>(s) * nk,
+                                   knots + static_cast<size_t>(s + 1) * nk);
+      absl::Status st = spline.Init(degree, pts, kn);
+      if (!st.ok()) {
+        int expected = 0;
+        first_error.compare_exchange_strong(expected, Code(st));
+        continue;
+      }
+      for (int e = 0; e < E; ++e) {
+        const size_t flat = static_cast<size_t>(s) * E + e;
+        st = spline.EvalCurveAndDerivatives(u[flat], absl::MakeSpan(values));
+        if (status != nullptr) status[flat] = Code(st);
+        if (!st.ok()) continue;
+        double* o = out + flat * (nder + 1) * D;
+        for (int k = 0; k <= nder; ++k)
+          for (int d = 0; d < D; ++d) o[k * D + d] = values[k][d];
+      }
+    }
+  };
+  if (nthreads <= 1) {
+    worker();
+  } else {
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nthreads; ++t) pool.emplace_back(worker);
+    for (auto& t : pool) t.join();
+  }
+  return first_error.load();
+}
+
 // BASELINE cfg2 / cfg4 on the host: B independent fresh joint paths, each planned
 // from its waypoints to its resampled trajectory by the reference's own classes
 // (SetWaypoints -> Plan: SamplePath, ConstraintSetup, OptimizePathParameter,

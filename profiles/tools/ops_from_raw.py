@@ -2,7 +2,9 @@
 """fp64_ops.json / traffic.json entries from an `ncu --page raw --csv` export of one
 `--set full` capture (first launch of every kernel name counts).
   ncu -i cap.ncu-rep --page raw --csv > raw.csv
-  python profiles/tools/ops_from_raw.py raw.csv <source note>  ->  prints both JSON fragments"""
+  python profiles/tools/ops_from_raw.py raw.csv <source note> [--write]
+  -> prints both JSON fragments, or writes profiles/fp64_ops.json and traffic.json (with the
+     hash of csrc/ so that bench.py can tell when they are stale)"""
 import csv
 import json
 import sys
@@ -46,5 +48,24 @@ for r in rows[2:]:
     rd, wr = gb("dram__bytes_read.sum"), gb("dram__bytes_write.sum")
     traffic[key] = {"dram_bytes_per_launch": int(rd + wr), "read": rd, "write": wr}
 note = sys.argv[2] if len(sys.argv) > 2 else ""
-print(json.dumps({"_source": note, **ops}, indent=1))
-print(json.dumps(traffic, indent=1))
+# the hash of the CUDA sources the capture was taken from (bench.py prints "stale" when
+# the tree's differs)
+import hashlib
+import os
+root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+HOT_KERNEL_SOURCES = ("tpb_kernels.cu", "tpb_integrate.cuh", "tpb_integrate_pair.cuh",
+                      "tpb_joint_limit.cuh", "tpb_row_limit.cuh", "tpb_solver.cuh", "tpb_device.cuh",
+                      "tpb_bulk.cuh", "tpb_fit.cuh")  # as in bench.py
+hsh = hashlib.sha256()
+for f in HOT_KERNEL_SOURCES:
+    hsh.update(open(os.path.join(root, "x-edr-trajectory-planning_b200", "csrc", f), "rb").read())
+digest = hsh.hexdigest()[:16]
+if len(sys.argv) > 3 and sys.argv[3] == "--write":
+    with open(os.path.join(root, "profiles", "fp64_ops.json"), "w") as f:
+        json.dump({"_source": note, "_csrc_hash": digest, **ops}, f, indent=1)
+    with open(os.path.join(root, "profiles", "traffic.json"), "w") as f:
+        json.dump({"_source": note, "_csrc_hash": digest, **traffic}, f, indent=1)
+    print("wrote profiles/fp64_ops.json and profiles/traffic.json, csrc hash", digest)
+else:
+    print(json.dumps({"_source": note, "_csrc_hash": digest, **ops}, indent=1))
+    print(json.dumps({"_csrc_hash": digest, **traffic}, indent=1))

@@ -413,3 +413,30 @@ def test_cfg2_full_size_properties(pkg, po):
         assert np.array_equal(res["TIME"][b], sub["TIME"][i])
     exact = _check_against_oracle(po, sub, wp[pick], vmax[pick], amax[pick], N, dt=dt)
     assert exact == len(pick)
+
+
+def test_resample_with_more_path_samples_than_shared_memory_holds(pkg, po):
+    """N = 32,768 path samples: the time stamps of a path (256 KB) do not fit shared memory,
+    so the resampling searches them in global memory (k_resample_fill<false, .>); every
+    array still equals the oracle bit for bit."""
+    B, W, D, N = 2, 5, 7, 32768
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=41)
+    res = _run_engine(pkg, wp, vmax, amax, N)
+    _check_against_oracle(po, res, wp, vmax, amax, N)
+    # and with the skipping time sampling
+    eng = pkg.Engine(max_paths=B, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=B * (N + 1))
+    eng.set_joint_waypoints(wp)
+    eng.set_joint_limits(vmax, amax)
+    eng.sample_paths()
+    eng.optimize()
+    total = eng.resample(0.0, 0.004, skip=True)
+    off = eng.get(pkg.ARR.R_OFFSET)
+    pos, t = eng.get(pkg.ARR.R_POS), eng.get(pkg.ARR.R_TIME)
+    for b in range(B):
+        o = po.plan_joint(wp[b], vmax[b], amax[b], N, dt=0.004, M_cap=N + 1, skip=True)
+        assert o["ok"] and off[b + 1] - off[b] == o["M"]
+        assert pos[off[b]:off[b + 1]].tobytes() == o["r_pos"].tobytes()
+        assert t[off[b]:off[b + 1]].tobytes() == o["r_t"].tobytes()
+    assert total == off[-1]
+    eng.close()

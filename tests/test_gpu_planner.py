@@ -291,3 +291,20 @@ def test_batch_of_cartesian_paths():
                                            400 * MS, 16 * N)
     assert n["windows"] >= 2 * B
     assert all(pl.target_reached for pl in planners)
+
+
+@pytest.mark.parametrize("D,skip", [(12, False), (16, False), (12, True)])
+def test_replanning_many_dofs_with_the_default_capacity(D, skip):
+    """num_dofs 10..16 with the host classes' default path-sample capacity of 64 * N: the
+    planner resamples views of P_cap samples, so the time stamps do not fit shared memory
+    and the row tile alone exceeds 48 KB (k_resample_fill<false, .> with its opt-in to
+    large dynamic shared memory)."""
+    B, W, N = 3, 4, 160
+    wp, vmax, amax = pkg.workloads.joint_paths(B, W, D, seed=70 + D)
+    ends = [orc.joint_fit(wp[b], 0.2)[1][-1] for b in range(B)]
+    delta = min(ends) / (N - 1) / 2.5
+    eng, planners, stats = run_replanning(wp, vmax, amax, N, delta, 0.004, skip, 750 * MS, 200 * MS,
+                                          P_cap=64 * N)
+    assert stats["windows"] >= 2 * B
+    assert all(pl.target_reached for pl in planners)
+    eng.close()

@@ -300,3 +300,27 @@ def test_switch_to_new_waypoint_path(skip):
     assert port.target_reached
     np.testing.assert_allclose(tr["r_pos"][-1], new_wp[-1], atol=1e-10)
 
+
+
+@pytest.mark.parametrize("degree", [1, 2, 3, 4, 5])
+def test_spline_evaluation_equals_reference_object_code(degree):
+    """Stage A (KnotSpan, UpdateBasisAndDerivatives, EvalCurveAndDerivatives): the port's
+    values and derivatives of every order up to min(degree, 3) equal the reference's
+    BSplineXd bit for bit -- uniform grid, the knots themselves, both ends, shuffled
+    parameters, out-of-range parameters (kOutOfRange, output untouched)."""
+    rng = np.random.default_rng(degree)
+    S, n, D, E = 3, 12 + degree, 5, 400
+    nder = min(degree, 3)
+    knots = np.stack([orc.make_uniform_knots(n, degree, 0.0, 1.0) * s for s in (1.0, 8.0, 0.37)])
+    ctrl = rng.uniform(-np.pi, np.pi, (S, n, D))
+    u = np.stack([np.concatenate([np.linspace(k[0], k[-1], E - 2 * len(k) - 4), k, k[::-1],
+                                  [k[0] - 0.1, k[-1] + 1e-9, np.nextafter(k[-1], 0), k[0]]])
+                  for k in knots])
+    u[1] = rng.permutation(u[1])
+    ref_out, ref_st = orc.spline_eval_batch_ref(knots, ctrl, degree, nder, u, threads=2)
+    for s in range(S):
+        st, out = orc.eval_curve_ders(knots[s], ctrl[s], degree, nder, u[s])
+        assert np.array_equal(np.asarray(st), ref_st[s])
+        ok = ref_st[s] == 0
+        assert (~ok).sum() == 2 and (ref_st[s][~ok] == 11).all()
+        same_bits(np.asarray(out)[ok], ref_out[s][ok], f"degree {degree} spline {s}")

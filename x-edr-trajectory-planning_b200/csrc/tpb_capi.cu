@@ -11,6 +11,7 @@
 
 #include "tpb_device.cuh"
 #include "tpb_engine.h"
+#include "tpb_nvtx.h"
 
 namespace tpb {
 int launch_spline_eval(const tpb_spline_eval_desc& d, cudaStream_t st, std::string* err);
@@ -757,6 +758,7 @@ static int32_t resample_impl(tpb_engine* e, double start_sec, double time_step_s
 // free) and resampled on a third stream in chunk order (the continued offset scan).
 int32_t tpb_plan_joint_device(tpb_engine* e, double start_sec, double time_step_sec,
                               int32_t num_chunks, int64_t* total_samples) {
+  TPB_NVTX("tpb_plan_joint_device");
   if (e == nullptr) return TPB_INVALID_ARGUMENT;
   auto& d = e->dims;
   if (e->mode != Mode::kJoint || !e->have_waypoints)
@@ -835,6 +837,7 @@ int32_t tpb_plan_joint_device(tpb_engine* e, double start_sec, double time_step_
 }
 
 int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
+  TPB_NVTX("tpb_plan_joint_host");
   if (e == nullptr || io == nullptr) return TPB_INVALID_ARGUMENT;
   int32_t rc;
   if ((rc = tpb_set_joint_waypoints(e, io->num_paths, io->num_waypoints, io->waypoints, 0))) return rc;
@@ -861,7 +864,16 @@ int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
   int bounds[tpb_engine::kMaxChunks + 1];
   int nchunks = 0;
   bounds[0] = 0;
-  if (((want_rows && any_out) || any_profile) && d.B >= 1024) {
+  // How finely to cut depends on how much leaves the GPU: the sweeps of a small chunk take
+  // about as long as those of the whole batch (they are latency-bound), so chunks only pay
+  // when the copies they hide are long.  Bytes per trajectory row the caller asked for:
+  const int row_bytes =
+      want_rows ? 8 * (d.D * ((io->r_pos != nullptr) + (io->r_vel != nullptr) + (io->r_acc != nullptr)) +
+                       (io->r_s != nullptr) + (io->r_sd != nullptr) + (io->r_sdd != nullptr) +
+                       (io->r_time != nullptr))
+                : 0;
+  if (row_bytes >= 120 && d.B >= 1024) {
+    // most of the trajectory: small first chunks (their compute time is exposed), doubling
     int size = std::max(128, d.B / 16);
     while (bounds[nchunks] < d.B && nchunks < tpb_engine::kMaxChunks - 1) {
       const int next = std::min(d.B, bounds[nchunks] + size);
@@ -869,9 +881,14 @@ int32_t tpb_plan_joint_host(tpb_engine* e, tpb_plan_io* io) {
       if (nchunks >= 2) size *= 2;
     }
     if (bounds[nchunks] < d.B) bounds[++nchunks] = d.B;
+  } else if (row_bytes >= 40 && d.B >= 2048) {
+    // one array of rows (positions only): two halves
+    bounds[++nchunks] = d.B / 2;
+    bounds[++nchunks] = d.B;
   } else {
     bounds[++nchunks] = d.B;
   }
+  (void)any_profile;
   if (nchunks > 1) {
     if (e->copy_stream == nullptr)
       TPB_CUDA(e, cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
@@ -1156,6 +1173,7 @@ int32_t tpb_planner_set_kinematics(tpb_engine* e, int32_t model) {
 
 int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
                          int64_t* total_samples) {
+  TPB_NVTX("tpb_planner_plan");
   if (e == nullptr) return TPB_INVALID_ARGUMENT;
   auto& d = e->dims;
   if ((e->mode != Mode::kJoint && e->mode != Mode::kCartesian) || !e->have_waypoints)
@@ -1292,6 +1310,7 @@ int32_t tpb_query_profile(tpb_engine* e, int32_t queries_per_path, const double*
                           double* s, double* sd, double* sdd, int32_t* previous_index,
                           double* sk, double* sdk, double* sddk, double* tk, int32_t* status,
                           int32_t on_device) {
+  TPB_NVTX("tpb_query_profile");
   if (e == nullptr || time_sec == nullptr) return TPB_INVALID_ARGUMENT;
   auto& d = e->dims;
   if (!e->optimized) return fail(e, TPB_FAILED_PRECONDITION, "Error, solution not yet calculated!");

@@ -22,6 +22,7 @@
 #include "tpb_integrate.cuh"
 #include "tpb_integrate_pair.cuh"
 #include "tpb_joint_limit.cuh"
+#include "tpb_nvtx.h"
 #include "tpb_row_limit.cuh"
 #include "tpb_solver.cuh"
 
@@ -526,9 +527,14 @@ constexpr int kResampleThreads = 224;
 // odd D every other row starts 8 bytes off.  The tile is therefore written into shared
 // memory with the same 8-byte offset the destination has (`shift`): the head element (if
 // any) and a tail element are stored by lane 0 directly, everything between them is one
-// aligned bulk copy per array.  TPB_RESAMPLE_BULK=0 builds the per-lane loop (A/B).
+// aligned bulk copy per array.
+// MEASURED AND NOT ADOPTED (profiles/r2_summary.md): with the bulk copies the kernel takes
+// 1.197 ms against 1.121 ms for the per-lane copy loop on the cfg2 batch -- its limit is the
+// L1 data pipe of the row gathers, which the copy-out does not touch, and lane 0's three
+// issue sequences per pass serialise a warp that otherwise stores with 32 lanes.  The code
+// stays behind TPB_RESAMPLE_BULK=1 for that A/B; the default build uses the copy loop.
 #ifndef TPB_RESAMPLE_BULK
-#define TPB_RESAMPLE_BULK 1
+#define TPB_RESAMPLE_BULK 0
 #endif
 // doubles of one warp's tile region: 3 x (32 x D + 2 for the shift), kept even
 __host__ __device__ inline int resample_tile_doubles(int D) { return 3 * ((32 * D + 3) & ~1); }
@@ -710,6 +716,7 @@ int launch_fill_i32(int32_t* p, int32_t v, int n, cudaStream_t st) {
 
 int launch_joint_fit(const Dims& d, const DeviceArrays& a, double rounding, bool auto_delta,
                      cudaStream_t st) {
+  TPB_NVTX("tpb:joint_fit");
   const int threads = 64;
   k_joint_fit<<<(d.B + threads - 1) / threads, threads, 0, st>>>(d, a, rounding, auto_delta);
   return 1;
@@ -717,6 +724,7 @@ int launch_joint_fit(const Dims& d, const DeviceArrays& a, double rounding, bool
 
 int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safety,
                               cudaStream_t st) {
+  TPB_NVTX("tpb:sample_path+limit_curve");
   const size_t tables =
       sizeof(double) * (static_cast<size_t>(d.max_points) + 3 + static_cast<size_t>(d.max_points) * d.D + 2 * d.D);
   const dim3 grid = path_grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
@@ -741,6 +749,7 @@ int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safet
 // (tpb_set_kernel_variant) keeps the local-memory kernel for every C (the parity tests
 // compare the two).
 int launch_generic_limit(const Dims& d, const DeviceArrays& a, cudaStream_t st) {
+  TPB_NVTX("tpb:limit_curve");
   const dim3 grid = path_grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
   const bool local = (d.variants >> TPB_VARIANT_GENERIC_LIMIT_LOCAL) & 1u;
   const int kc = local ? 99 : (d.C + 1) / 2 * 2;
@@ -758,6 +767,7 @@ int launch_generic_limit(const Dims& d, const DeviceArrays& a, cudaStream_t st) 
 
 int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double safety,
                      int max_loops, cudaStream_t st, cudaEvent_t* phase_events) {
+  TPB_NVTX("tpb:optimize_path_parameter");
   // phase_events (4, optional): recorded before setup, before the sweeps, after
   // the sweeps and after finalize; a single-kernel path records the inner two
   // around the whole kernel as well
@@ -840,6 +850,7 @@ int launch_integrate(const Dims& d, const DeviceArrays& a, Mode mode, double saf
 int launch_resample_rows(const Dims& d, const DeviceArrays& a, const ResampleView& v,
                          const int32_t* keep, double start_sec, double dt, int num_sms,
                          cudaStream_t st, bool skip, bool continued) {
+  TPB_NVTX("tpb:resample_rows");
   k_scan_offsets<<<1, 1024, 0, st>>>(d.B, a.r_count, a.r_offset, continued ? 1 : 0);
   const size_t tile = sizeof(double) * (kResampleThreads / 32) * resample_tile_doubles(d.D);
   const size_t with_time = tile + sizeof(double) * ((d.N + 1) & ~1);
@@ -870,6 +881,7 @@ int launch_resample_rows(const Dims& d, const DeviceArrays& a, const ResampleVie
 
 int launch_resample(const Dims& d, const DeviceArrays& a, double start_sec, double dt,
                     int num_sms, cudaStream_t st, bool continued, bool skip) {
+  TPB_NVTX("tpb:resample");
   const int threads = 128;
   // the kept-sample lists of the skipping method live in the boundary passes' scratch
   int32_t* keep = reinterpret_cast<int32_t*>(a.fix_val);
