@@ -161,7 +161,7 @@ typedef struct {
   int32_t num_dofs;        /* D (JointPathOptions::num_dofs); 0 for constraint-only use */
   int32_t max_waypoints;   /* per path; 0 for constraint-only use */
   int32_t num_samples;     /* N (num_path_samples) */
-  int32_t max_constraints; /* C capacity for tpb_set_constraints; 0 -> 2*D only */
+  int32_t max_constraints; /* C capacity for tpb_set_constraints (<= 64); 0 -> 2*D only */
   int64_t max_time_samples_total; /* capacity of the packed resampled output; 0 -> none */
   int32_t cartesian;       /* != 0: allocate the Cartesian-path buffers (needs num_dofs > 0;
                               the constraint capacity is raised to 2*D + 2) */

@@ -85,7 +85,8 @@ def test_line_scalar_scenarios(pkg, po):
 
 
 @pytest.mark.parametrize("N,C", [(64, 2), (200, 6), (333, 14), (128, 32), (2, 3), (3, 4),
-                                 (300, 9), (150, 12), (100, 16), (90, 17), (257, 1)])
+                                 (300, 9), (150, 12), (100, 16), (90, 17), (257, 1),
+                                 (80, 33), (60, 50), (48, 64)])
 def test_random_problems(pkg, po, N, C):
     rng = np.random.default_rng(100 * N + C)
     B = 24
@@ -97,6 +98,33 @@ def test_random_problems(pkg, po, N, C):
     t0 = rng.uniform(0, 10, B)
     res = _solve_batch(pkg, cons, s0, s1, sd0, sdd0, t0)
     _compare(po, res, cons, s0, s1, sd0, sdd0, t0)
+
+
+def test_find_max_sd2_random_sizes_2_to_50(pkg, po):
+    """FindMaxSd2Random (time_optimal_path_timing_test.cc:703-736): random LPs with 2..50
+    rows, A, B ~ U(-100, 100), lower ~ U(-10, 0), upper ~ U(0, 10).  One LP per path (the
+    same rows at both samples of an N = 2 problem, so the boundary passes leave the limit
+    curve as computed): sd2_max and sd2_max_for_sdd0 equal the oracle's FindMaxSd2Simplex
+    (== the reference's object code, tests/test_oracle_vs_ref.py) bit for bit and its brute
+    force within 1e-8."""
+    rng = np.random.default_rng(703)
+    for C in list(range(2, 51, 3)) + [50]:
+        B = 40
+        rows = np.stack([rng.uniform(-100, 100, (B, C)), rng.uniform(-100, 100, (B, C)),
+                         rng.uniform(-10, 0, (B, C)), rng.uniform(0, 10, (B, C))], -1)
+        cons = np.ascontiguousarray(np.repeat(rows[:, None], 2, axis=1))  # [B][2][C][4]
+        eng = pkg.Engine(max_paths=B, num_samples=2, max_constraints=C)
+        eng.set_constraints(cons, np.zeros(B), np.ones(B))
+        eng.optimize()
+        sd2max = eng.get(pkg.ARR.B_SD2_MAX)[:, 0]
+        sd2zero = eng.get(pkg.ARR.B_SD2_ZERO)[:, 0]
+        eng.close()
+        for b in range(B):
+            a = po.find_max_sd2(rows[b], "port")
+            assert (sd2max[b], sd2zero[b]) == (a[0], a[2]), (C, b)
+            if po.have_ref():
+                c = po.find_max_sd2(rows[b], "ref_brute")
+                assert abs(sd2max[b] - c[0]) <= 1e-8
 
 
 @pytest.mark.parametrize("C", [4, 7, 10, 16])

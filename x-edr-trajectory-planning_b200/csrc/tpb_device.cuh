@@ -22,7 +22,9 @@ enum : uint8_t { kNone = 0, kSource = 1, kSink = 2, kTrajectory = 4 };
 // ConstraintType (time_optimal_path_timing.h:268)
 enum : int { kUpper = 1, kLower = 2 };
 
-constexpr int kMaxRows = 32;    // constraint rows per sample handled by the kernels
+// constraint rows per sample handled by the kernels (the reference has no limit; its own
+// LP test runs 2..50 rows, time_optimal_path_timing_test.cc:703-736)
+constexpr int kMaxRows = 64;
 constexpr int kMaxDofs = 16;    // joint dofs (2*D rows <= kMaxRows)
 constexpr int kMaxDegree = 5;   // dense spline evaluator
 

@@ -16,7 +16,7 @@
 //                  prefetched one step ahead of the sweep; the 2D velocity rows
 //                  have A == 0, so they never yield a candidate and their validity
 //                  does not depend on the candidate (tested once per call).
-//   GenericPolicy  explicit constraint tables (C <= 32) and joint paths with
+//   GenericPolicy  explicit constraint tables (C <= kMaxRows = 64) and joint paths with
 //                  D > 8: rows of the current sample staged per warp in shared
 //                  memory, lane j owns candidate (row j/2, bound j&1).
 //
@@ -79,9 +79,9 @@ struct GenericPolicy {
   __device__ bool valid(Rows r, double sddv, double sd2v) {
     stage(r.idx);
     bool bad = false;
-    if (lane < C) {
-      const double v = sA[lane] * sddv + sB[lane] * sd2v;
-      bad = (v + kTiny < sLo[lane]) || (v - kTiny > sHi[lane]);
+    for (int r = lane; r < C; r += 32) {  // C <= kMaxRows = 64: up to two rows per lane
+      const double v = sA[r] * sddv + sB[r] * sd2v;
+      bad = bad || (v + kTiny < sLo[r]) || (v - kTiny > sHi[r]);
     }
     return __ballot_sync(kFullMask, bad) == 0u;
   }
