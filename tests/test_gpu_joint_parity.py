@@ -6,6 +6,8 @@ build uses the oracle's operation order without FMA contraction, the
 intermediate arrays are in fact expected to be bit-identical; that stronger
 property is asserted where it holds by construction.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -413,6 +415,17 @@ def test_cfg2_full_size_properties(pkg, po):
         assert np.array_equal(res["TIME"][b], sub["TIME"][i])
     exact = _check_against_oracle(po, sub, wp[pick], vmax[pick], amax[pick], N, dt=dt)
     assert exact == len(pick)
+    # ALL 4,096 paths against the reference's own object code (TimeableJointSplinePath +
+    # PathTimingTrajectory compiled verbatim into oracle/_ref, all host threads): status,
+    # duration, row count, the profile's time stamps and every resampled position, bit for bit
+    if po.have_ref():
+        ref = po.plan_joint_batch_ref(wp, vmax, amax, N, dt=dt, threads=os.cpu_count() or 1,
+                                      r_offset=off, want_time=True)
+        assert np.array_equal(ref["status"] == 0, res["STATUS"] == 0)
+        assert ref["duration"].tobytes() == res["DURATION"].tobytes()
+        assert np.array_equal(ref["rows"], rows)
+        assert ref["time"].tobytes() == res["TIME"].tobytes()
+        assert ref["r_pos"].tobytes() == res["R_POS"][:total].tobytes()
 
 
 def test_resample_with_more_path_samples_than_shared_memory_holds(pkg, po):
