@@ -31,13 +31,21 @@ __device__ __forceinline__ bool lp_is_optimal(const double* A, const double* B, 
 __device__ inline void lp_max_sd2(const double* A, const double* B, const double* LO,
                                   const double* HI, int C, double& sd2max,
                                   double& sddmax, double& sd2zero) {
+  static_assert(kMaxRows <= 64, "in_set holds 128 slots");
   int act_row[2 * kMaxRows + 2];
   int act_type[2 * kMaxRows + 2];
   double act_slope[2 * kMaxRows + 2];
   int nact = 0;
   sd2max = 0;
   sddmax = 0;
-  unsigned long long in_set = (C >= 32) ? ~0ull : ((1ull << (2 * C)) - 1ull);
+  // slots 0..63 in in_set[0], 64..127 in in_set[1] (C <= kMaxRows = 64)
+  unsigned long long in_set[2];
+  in_set[0] = (C >= 32) ? ~0ull : ((1ull << (2 * C)) - 1ull);
+  in_set[1] = (C <= 32) ? 0ull : ((C >= 64) ? ~0ull : ((1ull << (2 * C - 64)) - 1ull));
+  auto drop = [&](int row, int type) {
+    const int slot = 2 * row + (type == kLower ? 1 : 0);
+    in_set[slot >> 6] &= ~(1ull << (slot & 63));
+  };
 
   // Step 2: walk along sdd = 0.
   double sd2 = DBL_MAX;
@@ -97,7 +105,7 @@ __device__ inline void lp_max_sd2(const double* A, const double* B, const double
     }
   }
   for (int l = 0; l < nact; ++l) {
-    in_set &= ~(1ull << (2 * act_row[l] + (act_type[l] == kLower ? 1 : 0)));
+    drop(act_row[l], act_type[l]);
   }
 
   for (int loop = 0; loop < C; ++loop) {
@@ -114,9 +122,16 @@ __device__ inline void lp_max_sd2(const double* A, const double* B, const double
     // Step 4: next vertex along sdd = a + b * sd2.
     nact = 0;
     double next_sd2 = DBL_MAX, next_sdd = 0.0;
-    unsigned long long m = in_set;
-    while (m) {
-      const int e = __ffsll(static_cast<long long>(m)) - 1;
+    unsigned long long m = in_set[0];
+    int word = 0;
+    for (;;) {
+      if (m == 0ull) {
+        if (word == 1 || C <= 32) break;
+        word = 1;
+        m = in_set[1];
+        continue;
+      }
+      const int e = 64 * word + __ffsll(static_cast<long long>(m)) - 1;
       m &= m - 1;
       const int ci = e >> 1;
       const bool is_lower = e & 1;
@@ -168,7 +183,7 @@ __device__ inline void lp_max_sd2(const double* A, const double* B, const double
     }
     --nact;
     for (int l = 0; l < nact; ++l) {
-      in_set &= ~(1ull << (2 * act_row[l] + (act_type[l] == kLower ? 1 : 0)));
+      drop(act_row[l], act_type[l]);
     }
     sd2 = next_sd2;
     sdd = next_sdd;
