@@ -176,6 +176,9 @@ def lib():
             getattr(L, fn).argtypes = [c_double_p] * n
             getattr(L, fn).restype = None
         L.orc_quat_power.argtypes = [c_double_p, C.c_double, c_double_p]
+        L.orc_quat_power_derivative.argtypes = [c_double_p, C.c_double, c_double_p]
+        L.orc_quat_eval_curve_derivative.argtypes = [c_double_p, C.c_int, c_double_p, C.c_int,
+                                                     C.c_double, c_double_p, c_double_p]
         L.orc_quat_eval_curve.restype = C.c_int
         L.orc_quat_eval_curve.argtypes = [c_double_p, C.c_int, c_double_p, C.c_int,
                                           C.c_double, c_double_p]
@@ -311,6 +314,32 @@ def _register_ref_planner(R):
     R.tpref_spline_eval_batch.argtypes = [C.c_int] * 4 + [c_double_p, c_double_p, C.c_int,
                                                           c_double_p, C.c_int, C.c_int,
                                                           c_double_p, i32p]
+    # Cartesian path (splines/bsplineq.cc, timeable_path_cartesian_spline.cc verbatim)
+    for name in ("log", "exp"):
+        f = getattr(R, "tpref_quat_" + name)
+        f.restype, f.argtypes = None, [c_double_p, c_double_p]
+    for name in ("power", "power_derivative"):
+        f = getattr(R, "tpref_quat_" + name)
+        f.restype, f.argtypes = None, [c_double_p, C.c_double, c_double_p]
+    R.tpref_bsplineq_eval.restype = C.c_int
+    R.tpref_bsplineq_eval.argtypes = [C.c_int, C.c_int, c_double_p, C.c_int, c_double_p, C.c_int,
+                                      c_double_p, c_double_p, c_double_p, i32p]
+    R.tpref_pose_polyline_to_bspline3.restype = C.c_int
+    R.tpref_pose_polyline_to_bspline3.argtypes = [c_double_p, C.c_int, C.c_double, C.c_double,
+                                                  c_double_p, C.c_int]
+    R.tpref_planner_set_cartesian.restype = None
+    R.tpref_planner_set_cartesian.argtypes = [vp, C.c_double, C.c_double, C.c_double, vp, vp]
+    R.tpref_planner_set_cart_waypoints.restype = C.c_int
+    R.tpref_planner_set_cart_waypoints.argtypes = [vp, C.c_int, c_double_p, c_double_p]
+    R.tpref_planner_cart_switch.restype = C.c_int
+    R.tpref_planner_cart_switch.argtypes = [vp, C.c_double, C.c_int, c_double_p, c_double_p]
+    for name in ("pose_points", "ik_positions"):
+        f = getattr(R, "tpref_planner_cart_" + name)
+        f.restype, f.argtypes = C.c_int, [vp, c_double_p, C.c_int]
+    R.tpref_planner_cart_targets.restype = C.c_int
+    R.tpref_planner_cart_targets.argtypes = [vp, c_double_p, c_double_p, C.c_int]
+    R.tpref_planner_cart_sample.restype = C.c_int
+    R.tpref_planner_cart_sample.argtypes = [vp, C.c_double]
     R.tpref_plan_joint_batch.restype = None
     R.tpref_plan_joint_batch.argtypes = [
         C.c_int, C.c_int, C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, C.c_double,
@@ -625,23 +654,43 @@ class RefPlanner:
 
     def __init__(self, waypoints, vmax, amax, N, delta, dt, rounding=0.2, safety=0.8, skip=False,
                  max_planning_iterations=200, initial_velocity=None,
-                 max_initial_velocity_error=1e-4):
+                 max_initial_velocity_error=1e-4, pose_waypoints=None,
+                 translation_rounding=0.05, max_trans_vel=0.5, max_rot_vel=0.25,
+                 ik_fn=None, jacobian_fn=None):
+        """pose_waypoints [W][7] (tx,ty,tz,qx,qy,qz,qw): a TimeableCartesianSplinePath
+        (`waypoints` are then the joint waypoints, `rounding` the rotation rounding) whose
+        PathIKFunc / JacobianFunc are the C functions ik_fn / jacobian_fn (default: the
+        reference test's fake kinematics as restated in oracle/tp_oracle_cart.c -- user
+        callbacks, not part of the path)."""
         wp = np.ascontiguousarray(waypoints, np.float64)
         self.W, self.D = wp.shape
         self.N = N
+        self.cart = pose_waypoints is not None
         dt_ns = int(round(dt * 1e9))
         assert dt_ns * 1e-9 == dt or abs(dt_ns / 1e9 - dt) == 0.0, "dt must be whole ns"
         self._h = ref().tpref_planner_create(N, self.D, rounding, safety, float(delta), dt_ns,
                                              1 if skip else 0, max_planning_iterations,
                                              max_initial_velocity_error)
         R = ref()
+        if self.cart:
+            assert self.D == 7 or (ik_fn is not None and jacobian_fn is not None)
+            ik = ik_fn if ik_fn is not None else C.cast(lib().orc_fake_ik, C.c_void_p)
+            jac = jacobian_fn if jacobian_fn is not None else C.cast(lib().orc_fake_jacobian,
+                                                                    C.c_void_p)
+            self._callbacks = (ik_fn, jacobian_fn)  # keep ctypes callbacks alive
+            R.tpref_planner_set_cartesian(self._h, float(translation_rounding),
+                                          float(max_trans_vel), float(max_rot_vel), ik, jac)
         st = R.tpref_planner_set_limits(self._h, _dp(np.ascontiguousarray(vmax, np.float64)),
                                         _dp(np.ascontiguousarray(amax, np.float64)))
         assert st == 0, st
         if initial_velocity is not None:
             iv = np.ascontiguousarray(initial_velocity, np.float64)
             R.tpref_planner_set_initial_velocity(self._h, _dp(iv))
-        self.set_status = R.tpref_planner_set_waypoints(self._h, self.W, _dp(wp))
+        if self.cart:
+            pw = np.ascontiguousarray(pose_waypoints, np.float64)
+            self.set_status = R.tpref_planner_set_cart_waypoints(self._h, self.W, _dp(pw), _dp(wp))
+        else:
+            self.set_status = R.tpref_planner_set_waypoints(self._h, self.W, _dp(wp))
 
     def close(self):
         if self._h:
@@ -661,14 +710,40 @@ class RefPlanner:
     def plan(self, start_ns, horizon_ns):
         return ref().tpref_planner_plan(self._h, int(start_ns), int(horizon_ns))
 
-    def switch(self, keep_path_until, waypoints, initial_velocity=None):
+    def switch(self, keep_path_until, waypoints, initial_velocity=None, pose_waypoints=None):
         wp = np.ascontiguousarray(waypoints, np.float64)
-        st = ref().tpref_planner_switch(self._h, float(keep_path_until), wp.shape[0], _dp(wp))
+        if self.cart:
+            pw = np.ascontiguousarray(pose_waypoints, np.float64)
+            st = ref().tpref_planner_cart_switch(self._h, float(keep_path_until), wp.shape[0],
+                                                 _dp(pw), _dp(wp))
+        else:
+            st = ref().tpref_planner_switch(self._h, float(keep_path_until), wp.shape[0],
+                                            _dp(wp))
         if initial_velocity is not None:
             iv = np.ascontiguousarray(initial_velocity, np.float64)
             st2 = ref().tpref_planner_set_initial_velocity(self._h, _dp(iv))
             st = st or st2
         return st
+
+    # Cartesian path only
+    def pose_points(self):
+        out = np.zeros((4096, 7))
+        n = ref().tpref_planner_cart_pose_points(self._h, _dp(out), 4096)
+        return out[:n].copy()
+
+    def ik_positions(self):
+        out = np.zeros((1 << 16, self.D))
+        n = ref().tpref_planner_cart_ik_positions(self._h, _dp(out), 1 << 16)
+        return out[:n].copy()
+
+    def targets(self):
+        pt, jt = np.zeros((1 << 16, 7)), np.zeros((1 << 16, self.D))
+        n = ref().tpref_planner_cart_targets(self._h, _dp(pt), _dp(jt), 1 << 16)
+        return pt[:n].copy(), jt[:n].copy()
+
+    def sample(self, path_start):
+        """SamplePath(path_start) + ConstraintSetup() on the path alone."""
+        return ref().tpref_planner_cart_sample(self._h, float(path_start))
 
     def stop_parameter(self, time_ns):
         out = C.c_double(float("nan"))
@@ -717,7 +792,7 @@ class RefPlanner:
         return o
 
     def constraints(self):
-        c = np.zeros((self.N, 2 * self.D, 4))
+        c = np.zeros((self.N, 2 * self.D + (2 if self.cart else 0), 4))
         ref().tpref_planner_constraints(self._h, _dp(c))
         return c
 
@@ -954,6 +1029,21 @@ def quat_power(q, power):
     return out
 
 
+def quat_power_derivative(q, power):
+    out = np.zeros(4)
+    lib().orc_quat_power_derivative(_dp(_q(q)), float(power), _dp(out))
+    return out
+
+
+def quat_eval_curve_derivative(knots, quats, degree, u):
+    """BSplineQ::EvalCurveAndDerivative; returns (status, q, dq/du)."""
+    knots, quats = _q(knots), _q(quats)
+    out, dout = np.zeros(4), np.zeros(4)
+    st = lib().orc_quat_eval_curve_derivative(_dp(knots), len(knots), _dp(quats), degree, float(u),
+                                          _dp(out), _dp(dout))
+    return st, out, dout
+
+
 def quat_eval_curve(knots, quats, degree, u):
     """BSplineQ::EvalCurve; quats [n][4] in (x, y, z, w) order."""
     knots, quats = _q(knots), _q(quats)
@@ -961,6 +1051,40 @@ def quat_eval_curve(knots, quats, degree, u):
     st = lib().orc_quat_eval_curve(_dp(knots), len(knots), _dp(quats), degree, float(u),
                                    _dp(out))
     return st, out
+
+
+def quat_ref(kind, q, power=None):
+    """bsplineq_details::QuatLog / QuatExp / QuatPower / QuatPowerDerivative, reference
+    object code (kind: "log", "exp", "power", "power_derivative")."""
+    out = np.zeros(4)
+    f = getattr(ref(), "tpref_quat_" + kind)
+    if power is None:
+        f(_dp(_q(q)), _dp(out))
+    else:
+        f(_dp(_q(q)), float(power), _dp(out))
+    return out
+
+
+def bsplineq_eval_ref(knots, quats, degree, us, derivative=False):
+    """BSplineQ::EvalCurve / EvalCurveAndDerivative, reference object code.  Returns
+    (status [M], q [M][4], dq [M][4] or None)."""
+    knots, quats, us = _q(knots), _q(quats), _q(np.atleast_1d(us))
+    M = len(us)
+    q, dq, st = np.zeros((M, 4)), np.zeros((M, 4)), np.zeros(M, np.int32)
+    rc = ref().tpref_bsplineq_eval(degree, len(knots), _dp(knots), quats.shape[0], _dp(quats), M,
+                                   _dp(us), _dp(q), _dp(dq) if derivative else None,
+                                   st.ctypes.data_as(C.POINTER(C.c_int32)))
+    assert rc == 0, rc
+    return st, q, (dq if derivative else None)
+
+
+def pose_polyline_to_bspline3_ref(corners, translation_radius, rotational_radius):
+    corners = _q(corners)
+    W = corners.shape[0]
+    out = np.zeros((max(3 * W - 2, 4) + 4, 7))
+    n = ref().tpref_pose_polyline_to_bspline3(_dp(corners), W, float(translation_radius),
+                                              float(rotational_radius), _dp(out), out.shape[0])
+    return out[:n]
 
 
 def pose_polyline_to_bspline3(corners, translation_radius, rotational_radius):

@@ -39,6 +39,7 @@
 #define private public
 #define protected public
 #include "trajectory_planning/path_timing_trajectory.h"
+#include "trajectory_planning/timeable_path_cartesian_spline.h"
 #include "trajectory_planning/timeable_path_joint_spline.h"
 #undef private
 #undef protected
@@ -47,7 +48,19 @@ using eigenmath::VectorXd;
 using trajectory_planning::JointPathOptions;
 using trajectory_planning::PathTimingTrajectory;
 using trajectory_planning::PathTimingTrajectoryOptions;
+using trajectory_planning::CartesianPathOptions;
+using trajectory_planning::TimeableCartesianSplinePath;
 using trajectory_planning::TimeableJointSplinePath;
+using trajectory_planning::TimeablePath;
+
+// The user callbacks of a Cartesian path (CartesianPathOptions::PathIKFunc /
+// JacobianFunc, timeable_path_cartesian_spline.h:33-41) as plain C functions over
+// packed arrays: poses are (tx, ty, tz, qx, qy, qz, qw), the Jacobian is 6 x D row-major.
+extern "C" {
+typedef void (*tpref_ik_fn)(const double* pose_targets, const double* joint_targets, int M,
+                            double* ik);
+typedef void (*tpref_jacobian_fn)(const double* joints, double* jacobian);
+}
 
 namespace {
 
@@ -90,8 +103,20 @@ struct Planner {
   int N = 0, D = 0;
   double rounding = 0.2, safety = 0.8, delta = -1.0;
   std::vector<double> vmax, amax, init_vel;
-  std::shared_ptr<TimeableJointSplinePath> path;
+  std::shared_ptr<TimeableJointSplinePath> path;      // joint path, or
+  std::shared_ptr<TimeableCartesianSplinePath> cart;  // Cartesian path
   std::unique_ptr<PathTimingTrajectory> planner;
+  // Cartesian path only
+  double translation_rounding = 0.05, max_translational_velocity = 0.0,
+         max_rotational_velocity = 0.0;
+  tpref_ik_fn ik = nullptr;
+  tpref_jacobian_fn jacobian = nullptr;
+  TimeablePath* any() const {
+    return path ? static_cast<TimeablePath*>(path.get()) : static_cast<TimeablePath*>(cart.get());
+  }
+  const std::vector<double>* knots() const {
+    return path ? &path->knots_ : (cart ? &cart->knots_ : nullptr);
+  }
 };
 
 }  // namespace
@@ -123,10 +148,10 @@ int tpref_planner_set_limits(void* hv, const double* vmax, const double* amax) {
   auto* h = static_cast<Planner*>(hv);
   h->vmax.assign(vmax, vmax + h->D);
   h->amax.assign(amax, amax + h->D);
-  if (h->path == nullptr) return 0;
-  absl::Status st = h->path->SetMaxJointVelocity(h->vmax);
+  if (h->any() == nullptr) return 0;
+  absl::Status st = h->any()->SetMaxJointVelocity(h->vmax);
   if (!st.ok()) return Code(st);
-  return Code(h->path->SetMaxJointAcceleration(h->amax));
+  return Code(h->any()->SetMaxJointAcceleration(h->amax));
 }
 
 // TimeableJointSplinePath::SetWaypoints (+ SetPath on the first call).
@@ -157,8 +182,8 @@ int tpref_planner_set_waypoints(void* hv, int W, const double* waypoints) {
 int tpref_planner_set_initial_velocity(void* hv, const double* velocity) {
   auto* h = static_cast<Planner*>(hv);
   h->init_vel.assign(velocity, velocity + h->D);
-  if (h->path == nullptr) return 0;
-  return Code(h->path->SetInitialVelocity(h->init_vel));
+  if (h->any() == nullptr) return 0;
+  return Code(h->any()->SetInitialVelocity(h->init_vel));
 }
 
 // PathTimingTrajectory::Plan(start, horizon)
@@ -195,7 +220,7 @@ void tpref_planner_state(void* hv, int64_t* out) {
   out[2] = absl::ToUnixNanos(p.final_decel_start_);
   out[3] = p.planned_to_end_ ? 1 : 0;
   out[4] = p.target_reached_ ? 1 : 0;
-  out[5] = h->path ? static_cast<int64_t>(h->path->GetState()) : -1;
+  out[5] = h->any() ? static_cast<int64_t>(h->any()->GetState()) : -1;
   out[6] = p.initial_plan_ ? 1 : 0;
   out[7] = static_cast<int64_t>(p.time_.size());
   out[8] = static_cast<int64_t>(p.time_at_path_samples_.size());
@@ -207,8 +232,8 @@ void tpref_planner_state(void* hv, int64_t* out) {
 void tpref_planner_scalars(void* hv, double* out) {
   auto* h = static_cast<Planner*>(hv);
   out[0] = h->delta;
-  out[1] = (h->path && !h->path->knots_.empty()) ? h->path->knots_.back()
-                                                 : std::numeric_limits<double>::quiet_NaN();
+  out[1] = (h->knots() && !h->knots()->empty()) ? h->knots()->back()
+                                                : std::numeric_limits<double>::quiet_NaN();
   out[2] = h->planner->path_horizon_;
   out[3] = h->planner->path_start_;
 }
@@ -256,14 +281,14 @@ void tpref_planner_path_samples(void* hv, double* time, double* s, double* sd, d
 void tpref_planner_window(void* hv, double* q, double* dq, double* ddq, double* time, double* s,
                           double* sd, double* sdd) {
   auto* h = static_cast<Planner*>(hv);
-  if (h->path == nullptr) return;
+  if (h->any() == nullptr) return;
   const size_t N = static_cast<size_t>(h->N), D = static_cast<size_t>(h->D);
   const auto& prof = h->planner->profile_;
   for (size_t i = 0; i < N; ++i) {
     for (size_t d = 0; d < D; ++d) {
-      if (q) q[i * D + d] = h->path->GetPathPositionAt(i)[d];
-      if (dq) dq[i * D + d] = h->path->GetFirstPathDerivativeAt(i)[d];
-      if (ddq) ddq[i * D + d] = h->path->GetSecondPathDerivativeAt(i)[d];
+      if (q) q[i * D + d] = h->any()->GetPathPositionAt(i)[d];
+      if (dq) dq[i * D + d] = h->any()->GetFirstPathDerivativeAt(i)[d];
+      if (ddq) ddq[i * D + d] = h->any()->GetSecondPathDerivativeAt(i)[d];
     }
   }
   if (prof.GetTimeSamples().size() == static_cast<std::ptrdiff_t>(N)) {
@@ -276,12 +301,13 @@ void tpref_planner_window(void* hv, double* q, double* dq, double* ddq, double* 
   }
 }
 
-// ConstraintSetup's rows of the last window, [N][2D][4] = (A, B, lower, upper)
+// ConstraintSetup's rows of the last window, [N][C][4] = (A, B, lower, upper); C = 2D for
+// a joint path, 2D + 2 for a Cartesian one
 void tpref_planner_constraints(void* hv, double* cons) {
   auto* h = static_cast<Planner*>(hv);
-  if (h->path == nullptr) return;
-  const auto& c = h->path->GetConstraints();
-  const size_t C = 2 * static_cast<size_t>(h->D);
+  if (h->any() == nullptr) return;
+  const auto& c = h->any()->GetConstraints();
+  const size_t C = h->any()->NumConstraints();
   for (size_t i = 0; i < c.size(); ++i) {
     for (size_t r = 0; r < C; ++r) {
       double* row = cons + (i * C + r) * 4;
@@ -299,9 +325,10 @@ void tpref_planner_spline(void* hv, int* counts, double* knots, int knot_cap, do
                           int point_cap) {
   auto* h = static_cast<Planner*>(hv);
   counts[0] = counts[1] = 0;
-  if (h->path == nullptr) return;
-  const auto kv = h->path->spline_.GetKnotVector();
-  const auto cp = h->path->spline_.GetControlPoints();
+  if (h->any() == nullptr) return;
+  auto& spline = h->path ? h->path->spline_ : h->cart->joint_spline_;
+  const auto kv = spline.GetKnotVector();
+  const auto cp = spline.GetControlPoints();
   counts[0] = static_cast<int>(kv.size());
   counts[1] = static_cast<int>(cp.size());
   for (int i = 0; i < counts[0] && i < knot_cap; ++i) knots[i] = kv[i];
@@ -428,6 +455,226 @@ void tpref_plan_joint_batch(int B, int N, int D, int W, const double* waypoints,
   std::vector<std::thread> pool;
   for (int t = 0; t < nthreads; ++t) pool.emplace_back(worker);
   for (auto& t : pool) t.join();
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Cartesian path (BASELINE config 5): splines/bsplineq.cc and
+// timeable_path_cartesian_spline.cc compiled VERBATIM; pins oracle/tp_oracle_cart.c
+// and the Cartesian branch of tp_oracle_windows.c.
+// ---------------------------------------------------------------------------
+#include "eigenmath/pose3.h"
+#include "trajectory_planning/splines/bsplineq.h"
+#include "trajectory_planning/splines/spline_utils.h"
+
+namespace {
+
+using eigenmath::Pose3d;
+using eigenmath::Quaterniond;
+using eigenmath::Vector3d;
+
+Quaterniond QuatOf(const double* q) { return Quaterniond(q[3], q[0], q[1], q[2]); }
+void PutQuat(const Quaterniond& q, double* out) {
+  out[0] = q.x();
+  out[1] = q.y();
+  out[2] = q.z();
+  out[3] = q.w();
+}
+Pose3d PoseOf(const double* p) { return Pose3d(QuatOf(p + 3), Vector3d(p[0], p[1], p[2])); }
+void PutPose(const Pose3d& p, double* out) {
+  out[0] = p.translation()[0];
+  out[1] = p.translation()[1];
+  out[2] = p.translation()[2];
+  PutQuat(p.quaternion(), out + 3);
+}
+std::vector<Pose3d> Poses(const double* p, int n) {
+  std::vector<Pose3d> v;
+  v.reserve(n);
+  for (int i = 0; i < n; ++i) v.push_back(PoseOf(p + 7 * static_cast<size_t>(i)));
+  return v;
+}
+
+CartesianPathOptions CartOptions(const Planner* h, int N, double delta) {
+  CartesianPathOptions o;
+  o.set_num_dofs(h->D).set_num_path_samples(N).set_rounding(h->rounding);
+  o.set_constraint_safety(h->safety).set_delta_parameter(delta);
+  o.set_translation_rounding(h->translation_rounding);
+  const int D = h->D;
+  const tpref_ik_fn ik = h->ik;
+  const tpref_jacobian_fn jac = h->jacobian;
+  o.set_path_ik_func([ik, D](const VectorXd&, const std::vector<Pose3d>& pose,
+                             const std::vector<VectorXd>& joint,
+                             std::vector<VectorXd>* solution) -> absl::Status {
+    const size_t M = pose.size();
+    std::vector<double> pt(7 * M), jt(D * M), out(D * M);
+    for (size_t i = 0; i < M; ++i) {
+      PutPose(pose[i], pt.data() + 7 * i);
+      for (int d = 0; d < D; ++d) jt[i * D + d] = joint[i][d];
+    }
+    ik(pt.data(), jt.data(), static_cast<int>(M), out.data());
+    solution->resize(M);
+    for (size_t i = 0; i < M; ++i) {
+      (*solution)[i].resize(D);
+      for (int d = 0; d < D; ++d) (*solution)[i][d] = out[i * D + d];
+    }
+    return absl::OkStatus();
+  });
+  o.set_jacobian_func([jac, D](const VectorXd& joints, eigenmath::Matrix6Xd* J) -> absl::Status {
+    std::vector<double> q(D), m(6 * static_cast<size_t>(D));
+    for (int d = 0; d < D; ++d) q[d] = joints[d];
+    jac(q.data(), m.data());
+    for (int r = 0; r < 6; ++r)
+      for (int d = 0; d < D; ++d) (*J)(r, d) = m[static_cast<size_t>(r) * D + d];
+    return absl::OkStatus();
+  });
+  return o;
+}
+
+}  // namespace
+
+extern "C" {
+
+// bsplineq_details (splines/bsplineq.cc:112-160); quaternions are (x, y, z, w)
+void tpref_quat_log(const double* q, double* out) {
+  PutQuat(trajectory_planning::bsplineq_details::QuatLog(QuatOf(q)), out);
+}
+void tpref_quat_exp(const double* q, double* out) {
+  PutQuat(trajectory_planning::bsplineq_details::QuatExp(QuatOf(q)), out);
+}
+void tpref_quat_power(const double* q, double power, double* out) {
+  PutQuat(trajectory_planning::bsplineq_details::QuatPower(QuatOf(q), power), out);
+}
+void tpref_quat_power_derivative(const double* q, double power, double* out) {
+  PutQuat(trajectory_planning::bsplineq_details::QuatPowerDerivative(QuatOf(q), power), out);
+}
+
+// BSplineQ::Init + EvalCurve (dq_out == NULL) or EvalCurveAndDerivative at M parameters.
+// status [M]: absl::StatusCode of each evaluation.  Returns Init's code.
+int tpref_bsplineq_eval(int degree, int num_knots, const double* knots, int num_points,
+                        const double* quats, int M, const double* u, double* q_out,
+                        double* dq_out, int* status) {
+  std::vector<Quaterniond> pts;
+  for (int i = 0; i < num_points; ++i) pts.push_back(QuatOf(quats + 4 * static_cast<size_t>(i)));
+  trajectory_planning::BSplineQ spline;
+  absl::Status st = spline.Init(degree, pts, absl::MakeConstSpan(knots, num_knots));
+  if (!st.ok()) return Code(st);
+  for (int i = 0; i < M; ++i) {
+    Quaterniond q, dq;
+    st = dq_out ? spline.EvalCurveAndDerivative(u[i], q, dq) : spline.EvalCurve(u[i], q);
+    status[i] = Code(st);
+    PutQuat(q, q_out + 4 * static_cast<size_t>(i));
+    if (dq_out) PutQuat(dq, dq_out + 4 * static_cast<size_t>(i));
+  }
+  return 0;
+}
+
+// PolyLineToBspline3Waypoints for poses (splines/spline_utils.cc); returns the number
+// of control points written to out [cap][7].
+int tpref_pose_polyline_to_bspline3(const double* corners, int W, double translation_radius,
+                                    double rotational_radius, double* out, int cap) {
+  std::vector<Pose3d> ctrl;
+  trajectory_planning::PolyLineToBspline3Waypoints(Poses(corners, W), translation_radius,
+                                                   rotational_radius, &ctrl);
+  for (size_t i = 0; i < ctrl.size() && static_cast<int>(i) < cap; ++i) PutPose(ctrl[i], out + 7 * i);
+  return static_cast<int>(ctrl.size());
+}
+
+// Make the planner of tpref_planner_create plan over a TimeableCartesianSplinePath;
+// call before the first tpref_planner_set_cart_waypoints.  `rounding` of
+// tpref_planner_create is the rotation rounding.
+void tpref_planner_set_cartesian(void* hv, double translation_rounding,
+                                 double max_translational_velocity,
+                                 double max_rotational_velocity, tpref_ik_fn ik,
+                                 tpref_jacobian_fn jacobian) {
+  auto* h = static_cast<Planner*>(hv);
+  h->translation_rounding = translation_rounding;
+  h->max_translational_velocity = max_translational_velocity;
+  h->max_rotational_velocity = max_rotational_velocity;
+  h->ik = ik;
+  h->jacobian = jacobian;
+}
+
+// TimeableCartesianSplinePath::SetWaypoints (+ SetPath on the first call); poses [W][7]
+int tpref_planner_set_cart_waypoints(void* hv, int W, const double* pose_waypoints,
+                                     const double* joint_waypoints) {
+  auto* h = static_cast<Planner*>(hv);
+  const std::vector<VectorXd> jw = Rows(joint_waypoints, W, h->D);
+  const std::vector<Pose3d> pw = Poses(pose_waypoints, W);
+  if (h->cart == nullptr) {
+    if (!(h->delta > 0)) {  // one planning window: delta = knots.back() / (N - 1)
+      TimeableCartesianSplinePath tmp(CartOptions(h, 3, 1.0));
+      absl::Status st = tmp.SetWaypoints(pw, jw);
+      if (!st.ok()) return Code(st);
+      h->delta = tmp.knots_.back() / (h->N - 1);
+    }
+    h->cart = std::make_shared<TimeableCartesianSplinePath>(CartOptions(h, h->N, h->delta));
+    absl::Status st = h->cart->SetMaxJointVelocity(h->vmax);
+    if (st.ok()) st = h->cart->SetMaxJointAcceleration(h->amax);
+    if (st.ok())
+      st = h->cart->SetMaxCartesianVelocity(h->max_translational_velocity,
+                                            h->max_rotational_velocity);
+    if (st.ok()) st = h->planner->SetPath(h->cart);
+    if (!st.ok()) return Code(st);
+  }
+  absl::Status st = h->cart->SetWaypoints(pw, jw);
+  if (!st.ok()) return Code(st);
+  return Code(h->cart->SetInitialVelocity(h->init_vel));
+}
+
+// TimeableCartesianSplinePath::SwitchToWaypointPath
+int tpref_planner_cart_switch(void* hv, double keep_path_until, int W,
+                              const double* pose_waypoints, const double* joint_waypoints) {
+  auto* h = static_cast<Planner*>(hv);
+  if (h->cart == nullptr) return static_cast<int>(absl::StatusCode::kFailedPrecondition);
+  return Code(h->cart->SwitchToWaypointPath(keep_path_until, Poses(pose_waypoints, W),
+                                            Rows(joint_waypoints, W, h->D)));
+}
+
+// Control points of the translation / rotation splines as poses [cap][7]; returns their
+// number (the knots and the joint control points: tpref_planner_spline).
+int tpref_planner_cart_pose_points(void* hv, double* out, int cap) {
+  auto* h = static_cast<Planner*>(hv);
+  if (h->cart == nullptr) return 0;
+  const auto tp = h->cart->translation_spline_.GetControlPoints();
+  const auto rp = h->cart->rotation_spline_.GetControlPoints();
+  for (size_t i = 0; i < tp.size() && static_cast<int>(i) < cap; ++i)
+    PutPose(Pose3d(rp[i], tp[i]), out + 7 * i);
+  return static_cast<int>(tp.size());
+}
+
+// The IK solution cache path_ik_positions_ [cap][D]; returns its length.
+int tpref_planner_cart_ik_positions(void* hv, double* out, int cap) {
+  auto* h = static_cast<Planner*>(hv);
+  if (h->cart == nullptr) return 0;
+  const auto& ik = h->cart->path_ik_positions_;
+  for (size_t i = 0; i < ik.size() && static_cast<int>(i) < cap; ++i)
+    for (int d = 0; d < h->D; ++d) out[i * h->D + d] = ik[i][d];
+  return static_cast<int>(ik.size());
+}
+
+// The targets handed to the last PathIKFunc call: poses [cap][7], joints [cap][D];
+// returns their number.
+int tpref_planner_cart_targets(void* hv, double* pose_out, double* joint_out, int cap) {
+  auto* h = static_cast<Planner*>(hv);
+  if (h->cart == nullptr) return 0;
+  const auto& pt = h->cart->sampled_pose_targets_;
+  const auto& jt = h->cart->sampled_joint_targets_;
+  for (size_t i = 0; i < pt.size() && static_cast<int>(i) < cap; ++i) {
+    if (pose_out) PutPose(pt[i], pose_out + 7 * i);
+    if (joint_out)
+      for (int d = 0; d < h->D; ++d) joint_out[i * h->D + d] = jt[i][d];
+  }
+  return static_cast<int>(pt.size());
+}
+
+// One call of the path alone (no planner): SamplePath(path_start) + ConstraintSetup().
+int tpref_planner_cart_sample(void* hv, double path_start) {
+  auto* h = static_cast<Planner*>(hv);
+  if (h->cart == nullptr) return static_cast<int>(absl::StatusCode::kFailedPrecondition);
+  absl::Status st = h->cart->SamplePath(path_start);
+  if (!st.ok()) return Code(st);
+  return Code(h->cart->ConstraintSetup());
 }
 
 }  // extern "C"

@@ -21,6 +21,7 @@ inline CheckSink CheckFail(bool ok, const char* what) {
 }  // namespace oracle_shim
 
 #define CHECK(cond) ::oracle_shim::CheckFail(static_cast<bool>(cond), #cond)
+#define CHECK_OK(status) CHECK((status).ok())
 #define CHECK_EQ(a, b) CHECK((a) == (b))
 #define CHECK_NE(a, b) CHECK((a) != (b))
 #define CHECK_LE(a, b) CHECK((a) <= (b))

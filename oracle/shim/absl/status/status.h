@@ -41,6 +41,8 @@ class Status {
   Status(StatusCode code, std::string msg)
       : code_(code), msg_(std::move(msg)) {}
   bool ok() const { return code_ == StatusCode::kOk; }
+  void IgnoreError() const {}
+  std::string ToString() const { return ok() ? std::string("OK") : msg_; }
   StatusCode code() const { return code_; }
   const std::string& message() const { return msg_; }
 
@@ -67,6 +69,9 @@ inline Status OutOfRangeError(std::string m) {
 }
 inline Status UnimplementedError(std::string m) {
   return Status(StatusCode::kUnimplemented, std::move(m));
+}
+inline Status AbortedError(std::string m) {
+  return Status(StatusCode::kAborted, std::move(m));
 }
 
 // The reference .cc calls absl::StrCat without including str_cat.h directly.

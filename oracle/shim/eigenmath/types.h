@@ -17,6 +17,8 @@ using MatrixXd = Eigen::MatrixXd;
 using Vector2d = Eigen::Vector2d;
 using Vector3d = Eigen::Vector3d;
 using Quaterniond = Eigen::Quaterniond;
+using Vector6d = Eigen::Vector6d;
+using Matrix6Xd = Eigen::Matrix6Xd;
 
 // VectorNd is Eigen's dynamic vector with a fixed maximum capacity; the capacity
 // (un-vendored) only bounds BSplineNd's point size, which nothing here instantiates.

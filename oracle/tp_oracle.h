@@ -156,6 +156,10 @@ void orc_quat_exp(const double* q, double* out);
 void orc_quat_power(const double* q, double power, double* out);
 int orc_quat_eval_curve(const double* knots, int num_knots, const double* quats,
                         int degree, double u, double* out);
+void orc_quat_power_derivative(const double* q, double power, double* out);
+/* BSplineQ::EvalCurveAndDerivative (splines/bsplineq.cc:246-307) */
+int orc_quat_eval_curve_derivative(const double* knots, int num_knots, const double* quats,
+                                   int degree, double u, double* out, double* dout);
 int orc_pose_polyline_to_bspline3(const double* corners, int W, double translation_radius,
                                   double rotational_radius, double* out);
 int orc_cart_fit(const double* pose_wp, const double* joint_wp, int W, int dim,

@@ -197,6 +197,74 @@ int orc_quat_eval_curve(const double* knots, int num_knots, const double* quats,
   return 0;
 }
 
+/* QuatPowerDerivative, splines/bsplineq.cc:148-160: exp(p log q) * log q */
+void orc_quat_power_derivative(const double* q, double power, double* out) {
+  double in[4] = {q[0], q[1], q[2], q[3]};
+  normalize_if_necessary_positive_real(in);
+  double lg[4], sc[4], ex[4];
+  orc_quat_log(in, lg);
+  for (int i = 0; i < 4; ++i) sc[i] = lg[i] * power;
+  orc_quat_exp(sc, ex);
+  orc_quat_mul(ex, lg, out);
+}
+
+/* BSplineQ::EvalCurveAndDerivative, splines/bsplineq.cc:246-307 with
+ * UpdateCumulativeBasisAndDerivative (:319-333).  The value is
+ * points[span - p] * (prod_k QuatPower(rel_k, Bc_k)) WITHOUT the final normalisation of
+ * EvalCurve (only the sign flip + normalize when w < 0).  Returns 0 or 11. */
+int orc_quat_eval_curve_derivative(const double* knots, int num_knots, const double* quats,
+                                   int degree, double u, double* out, double* dout) {
+  if (u < knots[0] || u > knots[num_knots - 1]) return 11;
+  const int span = orc_knot_span(knots, num_knots, degree, u);
+  double ders[2 * 16], cum[16], dcum[16];
+  orc_basis_ders(knots, span, degree, 1, u, ders);
+  const double* b0 = ders;
+  const double* b1 = ders + (degree + 1);
+  cum[degree - 1] = b0[degree];
+  dcum[degree - 1] = b1[degree];
+  for (int i = degree - 2; i >= 0; --i) {
+    cum[i] = cum[i + 1] + b0[i + 1];
+    dcum[i] = dcum[i + 1] + b1[i + 1];
+  }
+  double pw[17][4]; /* quat_powers_: [0] = identity */
+  double rel[16][4];
+  pw[0][0] = pw[0][1] = pw[0][2] = 0.0;
+  pw[0][3] = 1.0;
+  for (int k = 0; k < degree; ++k) {
+    double inv[4], f[4];
+    quat_inverse(quats + 4 * (span - degree + k), inv);
+    orc_quat_mul(inv, quats + 4 * (span - degree + k + 1), rel[k]);
+    orc_quat_power(rel[k], cum[k], f);
+    orc_quat_mul(pw[k], f, pw[k + 1]);
+  }
+  double q[4], d[4] = {0.0, 0.0, 0.0, 0.0};
+  orc_quat_mul(quats + 4 * (span - degree), pw[degree], q);
+  for (int k = 0; k < degree; ++k) {
+    double dk[4], inv[4], t1[4], t2[4], t3[4];
+    orc_quat_power_derivative(rel[k], cum[k], dk);
+    for (int i = 0; i < 4; ++i) dk[i] *= dcum[k];
+    orc_quat_mul(pw[k], dk, t1);
+    quat_inverse(pw[k + 1], inv);
+    orc_quat_mul(t1, inv, t2);
+    orc_quat_mul(t2, pw[degree], t3);
+    for (int i = 0; i < 4; ++i) d[i] += t3[i];
+  }
+  double dd[4];
+  orc_quat_mul(quats + 4 * (span - degree), d, dd);
+  if (q[3] < 0) {
+    for (int i = 0; i < 4; ++i) q[i] *= -1.0;
+    const double z = sq_norm4(q);
+    if (z > 0) {
+      const double n = sqrt(z);
+      for (int i = 0; i < 4; ++i) q[i] /= n;
+    }
+    for (int i = 0; i < 4; ++i) dd[i] *= -1.0;
+  }
+  memcpy(out, q, sizeof(q));
+  memcpy(dout, dd, sizeof(dd));
+  return 0;
+}
+
 /* ---------------------------------------------------------------- poses */
 static void pose_identity(double* p) {
   p[0] = p[1] = p[2] = 0.0;
