@@ -582,6 +582,16 @@ def run_ours(args):
                 "shuffled_u_frac": spline.get("p3_d7_shuffled", {}).get("frac_of_peak"),
                 "exact_mode_frac": spline.get("p3_d7_exact", {}).get("frac_of_peak"),
                 "cpu_baseline": spline.get("cpu_baseline")}
+        cfg5 = None
+        if cartesian:
+            cb = cartesian.get("cpu_baseline") or {}
+            cfg5 = {"workload": "4096 Cartesian paths (W = 5 poses, N = 1000) per GPU, device "
+                                "kinematics, no resampling",
+                    "paths_per_s": cartesian["paths_per_s"], "ms": cartesian["ms"],
+                    "cpu_single_thread_paths_per_s": cb.get("single_thread_paths_per_s"),
+                    "cpu_all_cores_paths_per_s": cb.get("all_cores_paths_per_s"),
+                    "cpu_cores": cb.get("cores"), "cpu_kind": cb.get("kind"),
+                    "max_rel_duration_err": cb.get("max_rel_duration_err")}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -589,7 +599,7 @@ def run_ours(args):
             "data": "synthetic", "config": _config(),
             "spline_eval": spline_compact,
             "roofline": roofline, "cpu_baseline": cpu_baseline, "parity": parity, "e2e": e2e,
-            "cfg4": cfg4, "cfg1": cfg1,
+            "cfg4": cfg4, "cfg1": cfg1, "cfg5": cfg5,
             "gpu_launches": int(launches), "clocks": clock_info,
             "stage_ms": stage_ms, "paths_ok": n_ok, "resampled_rows_per_gpu": total_rows,
             "mean_duration_s": float(np.nanmean(all_dur)),
@@ -1015,10 +1025,40 @@ def run_cartesian_leg(pkg, torch, dev, stream, local_rank, max_over_ranks, barri
     status = eng.get(pkg.ARR.STATUS)
     dur = eng.get(pkg.ARR.DURATION)
     eng.close()
-    return {"paths_per_s": world * B / (ms / 1e3), "ms": ms, "paths_per_gpu": B,
-            "num_samples": N, "num_waypoints": W, "rows_per_sample": 16,
-            "kinematics": "TPB_KIN_FAKE7 (reference test's fake robot) on the device",
-            "paths_ok": int((status == 0).sum()), "mean_duration_s": float(np.nanmean(dur))}
+    out = {"paths_per_s": world * B / (ms / 1e3), "ms": ms, "paths_per_gpu": B,
+           "num_samples": N, "num_waypoints": W, "rows_per_sample": 16,
+           "kinematics": "TPB_KIN_FAKE7 (reference test's fake robot) on the device",
+           "paths_ok": int((status == 0).sum()), "mean_duration_s": float(np.nanmean(dur))}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # the reference's own TimeableCartesianSplinePath + PathTimingTrajectory object code
+        # (oracle/_ref) on a bounded sample of the same paths; its PathIKFunc / JacobianFunc
+        # are the same fake robot as host callbacks
+        po, impl, kind, cores = _cpu_setup()
+        if impl == "ref":
+            n1, nall = 64, min(B, 64 * cores)
+            t0 = time.perf_counter()
+            r1 = po.plan_cart_batch_ref(pw[:n1], jw[:n1], vm[:n1], am[:n1], N, dt=TIME_STEP,
+                                        threads=1)
+            t1 = time.perf_counter()
+            ra = po.plan_cart_batch_ref(pw[:nall], jw[:nall], vm[:nall], am[:nall], N,
+                                        dt=TIME_STEP, threads=cores)
+            t2 = time.perf_counter()
+            both = (ra["status"] == 0) & (status[:nall] == 0)
+            rel = np.abs(dur[:nall][both] - ra["duration"][both]) / ra["duration"][both]
+            out["cpu_baseline"] = {
+                "kind": kind, "cores": cores,
+                "single_thread_paths_per_s": n1 / (t1 - t0),
+                "all_cores_paths_per_s": nall / (t2 - t1),
+                "sample": f"{n1} paths on one thread, {nall} on {cores} (reference object code "
+                          "of bsplineq.cc / timeable_path_cartesian_spline.cc / "
+                          "path_timing_trajectory.cc incl. resampling)",
+                "paths_compared": int(both.sum()),
+                "status_equal": bool(((ra["status"] == 0) == (status[:nall] == 0)).all()),
+                "max_rel_duration_err": float(rel.max()) if rel.size else None,
+                "tolerance": "1e-6 relative on T_total (BASELINE.json); device kinematics "
+                             "differ from the host callbacks by libm rounding",
+                "single_thread_status_ok": int((r1["status"] == 0).sum())}
+    return out
 
 
 def run_spline_sweep(pkg, torch, dev, stream, peak, max_over_ranks, barrier, world, args):

@@ -370,10 +370,28 @@ int32_t tpb_planner_reset(tpb_engine* e, int32_t path_sample_capacity, double ti
  * TimeableCartesianSplinePath::SamplePath (targets at the IK indices of the window,
  * path IK, finite differences; timeable_path_cartesian_spline.cc:464-549) and
  * ConstraintSetup (:551-595) on the device with the built-in kinematics `model`
- * (TPB_KIN_FAKE7).  With TPB_KIN_HOST (the default; a user PathIKFunc warm-started
- * from the previous window) tpb_planner_plan returns kUnimplemented for Cartesian
- * paths and the caller plans window by window through tpb_cart_*. */
+ * (TPB_KIN_FAKE7).  With TPB_KIN_HOST (the default) the kinematics are the user's:
+ * tpb_planner_set_host_kinematics. */
 int32_t tpb_planner_set_kinematics(tpb_engine* e, int32_t model);
+/* CartesianPathOptions::PathIKFunc / JacobianFunc (timeable_path_cartesian_spline.h:33-41)
+ * as C callbacks, for Cartesian paths behind the planner.  Every planning window the
+ * targets of the IK indices not solved yet come back to the host, `ik` is called once per
+ * active path with them -- initial_value [D] is the last solution of the previous window
+ * (the first joint target for a fresh path, :503-506); pose_targets [num_samples][7] as
+ * (tx,ty,tz,qx,qy,qz,qw), joint_targets / solution [num_samples][D]; solution[0] belongs
+ * to initial_value's index and is dropped, the rest extends the path's IK cache
+ * (path_ik_positions_, :509-513) -- then `jacobian` once per path sample (jacobian
+ * [6][D] row-major, rows 0-2 linear, 3-5 angular), and positions and Jacobians go back
+ * to the device for the finite differences, ConstraintSetup and the timing.  A callback
+ * returns TPB_OK or a tpb_status, which tpb_planner_plan then returns (the reference
+ * returns the PathIKFunc's status from Plan).  The cache is dropped by tpb_planner_reset. */
+typedef int32_t (*tpb_path_ik_fn)(void* user, int32_t path, const double* initial_value,
+                                  int32_t num_samples, const double* pose_targets,
+                                  const double* joint_targets, double* solution);
+typedef int32_t (*tpb_jacobian_fn)(void* user, int32_t path, const double* joint_positions,
+                                   double* jacobian);
+int32_t tpb_planner_set_host_kinematics(tpb_engine* e, tpb_path_ik_fn ik,
+                                        tpb_jacobian_fn jacobian, void* user);
 int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
                          int64_t* total_samples);
 /* New waypoints were set (tpb_set_joint_waypoints) on a planner that keeps its plan:

@@ -340,6 +340,11 @@ def _register_ref_planner(R):
     R.tpref_planner_cart_targets.argtypes = [vp, c_double_p, c_double_p, C.c_int]
     R.tpref_planner_cart_sample.restype = C.c_int
     R.tpref_planner_cart_sample.argtypes = [vp, C.c_double]
+    R.tpref_plan_cart_batch.restype = None
+    R.tpref_plan_cart_batch.argtypes = [
+        C.c_int, C.c_int, C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, c_double_p,
+        C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_int, C.c_int,
+        vp, vp, i32p, c_double_p, i32p, c_double_p]
     R.tpref_plan_joint_batch.restype = None
     R.tpref_plan_joint_batch.argtypes = [
         C.c_int, C.c_int, C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, C.c_double,
@@ -862,6 +867,35 @@ def plan_joint_batch_ref(waypoints, vmax, amax, N, dt=0.004, rounding=0.2, safet
     out = dict(status=status, duration=duration, rows=rows)
     if r_pos is not None:
         out["r_pos"] = r_pos
+    if ptime is not None:
+        out["time"] = ptime
+    return out
+
+
+def plan_cart_batch_ref(pose_waypoints, joint_waypoints, vmax, amax, N, dt=0.004,
+                        rotation_rounding=0.2, translation_rounding=0.05, safety=0.8,
+                        max_trans_vel=0.5, max_rot_vel=0.25, skip=False, threads=1,
+                        want_time=False):
+    """B fresh Cartesian paths (7 dofs, the reference test's fake kinematics as the user
+    callbacks) through the reference's own classes on `threads` host threads
+    (tpref_plan_cart_batch).  Returns status [B] (absl codes), duration [B], rows [B]."""
+    pw = np.ascontiguousarray(pose_waypoints, np.float64)
+    jw = np.ascontiguousarray(joint_waypoints, np.float64)
+    B, W, D = jw.shape
+    assert D == 7 and pw.shape == (B, W, 7)
+    vmax = np.ascontiguousarray(vmax, np.float64)
+    amax = np.ascontiguousarray(amax, np.float64)
+    status, rows = np.zeros(B, np.int32), np.zeros(B, np.int32)
+    duration = np.zeros(B)
+    ptime = np.full((B, N), np.nan) if want_time else None
+    i32 = lambda a: a.ctypes.data_as(C.POINTER(C.c_int32))
+    ref().tpref_plan_cart_batch(
+        B, N, D, W, _dp(pw), _dp(jw), _dp(vmax), _dp(amax), rotation_rounding,
+        translation_rounding, safety, max_trans_vel, max_rot_vel, int(round(dt * 1e9)),
+        1 if skip else 0, int(threads), C.cast(lib().orc_fake_ik, C.c_void_p),
+        C.cast(lib().orc_fake_jacobian, C.c_void_p), i32(status), _dp(duration), i32(rows),
+        _dp(ptime))
+    out = dict(status=status, duration=duration, rows=rows)
     if ptime is not None:
         out["time"] = ptime
     return out

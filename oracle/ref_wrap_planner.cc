@@ -678,3 +678,84 @@ int tpref_planner_cart_sample(void* hv, double path_start) {
 }
 
 }  // extern "C"
+
+extern "C" {
+
+// BASELINE cfg5 on the host: B independent fresh Cartesian paths (D dofs, W pose + joint
+// waypoints each), planned by the reference's own classes (SetWaypoints -> Plan:
+// SamplePath with the PathIKFunc, ConstraintSetup with the JacobianFunc,
+// OptimizePathParameter, ResampleTrajectory), the whole path in one window, on
+// `nthreads` host threads; same conventions as tpref_plan_joint_batch.
+//   pose_waypoints [B][W][7], joint_waypoints [B][W][D], vmax / amax [B][D]
+//   status [B] absl code, duration [B] (NaN on failure), rows [B];
+//   optional prof_time [B][N]
+void tpref_plan_cart_batch(int B, int N, int D, int W, const double* pose_waypoints,
+                           const double* joint_waypoints, const double* vmax,
+                           const double* amax, double rotation_rounding,
+                           double translation_rounding, double safety,
+                           double max_translational_velocity, double max_rotational_velocity,
+                           int64_t dt_ns, int skip_method, int nthreads, tpref_ik_fn ik,
+                           tpref_jacobian_fn jacobian, int32_t* status, double* duration,
+                           int32_t* rows, double* prof_time) {
+  Planner proto;
+  proto.D = D;
+  proto.rounding = rotation_rounding;
+  proto.safety = safety;
+  proto.translation_rounding = translation_rounding;
+  proto.ik = ik;
+  proto.jacobian = jacobian;
+  std::atomic<int> next{0};
+  auto worker = [&]() {
+    PathTimingTrajectory planner(PlannerOptions(N, D, dt_ns, skip_method, 0, 0.0));
+    for (;;) {
+      const int b = next.fetch_add(1);
+      if (b >= B) break;
+      status[b] = 0;
+      duration[b] = std::numeric_limits<double>::quiet_NaN();
+      rows[b] = 0;
+      const std::vector<VectorXd> jw = Rows(joint_waypoints + static_cast<size_t>(b) * W * D, W, D);
+      const std::vector<Pose3d> pw = Poses(pose_waypoints + static_cast<size_t>(b) * W * 7, W);
+      std::shared_ptr<TimeableCartesianSplinePath> path;
+      double kend = 0.0;
+      absl::Status st;
+      {
+        TimeableCartesianSplinePath tmp(CartOptions(&proto, 3, 1.0));
+        st = tmp.SetWaypoints(pw, jw);
+        if (st.ok()) kend = tmp.knots_.back();
+      }
+      if (st.ok()) {
+        path = std::make_shared<TimeableCartesianSplinePath>(
+            CartOptions(&proto, N, kend / (N - 1)));
+        st = path->SetMaxJointVelocity(absl::MakeConstSpan(vmax + static_cast<size_t>(b) * D, D));
+      }
+      if (st.ok())
+        st = path->SetMaxJointAcceleration(
+            absl::MakeConstSpan(amax + static_cast<size_t>(b) * D, D));
+      if (st.ok())
+        st = path->SetMaxCartesianVelocity(max_translational_velocity, max_rotational_velocity);
+      if (st.ok()) {
+        planner.Reset();
+        st = planner.SetPath(path);
+      }
+      if (st.ok()) st = path->SetWaypoints(pw, jw);
+      if (st.ok()) st = planner.Plan(absl::FromUnixNanos(0), absl::Seconds(1));
+      status[b] = Code(st);
+      if (!st.ok()) continue;
+      duration[b] = planner.profile_.GetTotalDuration();
+      rows[b] = static_cast<int32_t>(planner.GetTime().size());
+      if (prof_time != nullptr) {
+        for (int i = 0; i < N; ++i)
+          prof_time[static_cast<size_t>(b) * N + i] = planner.profile_.GetTimeSamples()[i];
+      }
+    }
+  };
+  if (nthreads <= 1) {
+    worker();
+    return;
+  }
+  std::vector<std::thread> pool;
+  for (int t = 0; t < nthreads; ++t) pool.emplace_back(worker);
+  for (auto& t : pool) t.join();
+}
+
+}  // extern "C"

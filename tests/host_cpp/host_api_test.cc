@@ -527,11 +527,34 @@ int main() {
     }
     // the reference's 5-waypoint Cartesian scenario (path_timing_trajectory_test.cc:695-757):
     // default delta 0.005, Plan() every 200 ms with a 750 ms horizon until the end; with
-    // device kinematics every window is sampled and timed on the device
-    {
+    // device kinematics every window is sampled and timed on the device; with the user's
+    // PathIKFunc / JacobianFunc every window's new IK indices go through the callbacks,
+    // warm-started from the previous window (timeable_path_cartesian_spline.cc:464-549)
+    for (int mode = 0; mode < 2; ++mode) {
       constexpr size_t kSamples = 1000;
+      int ik_calls = 0, ik_samples = 0;
+      bool warm_start_ok = true;
+      VectorXd last_solution;
       CartesianPathOptions opt;
-      opt.set_num_dofs(kFakeDofs).set_num_path_samples(kSamples).set_device_kinematics(TPB_KIN_FAKE7);
+      opt.set_num_dofs(kFakeDofs).set_num_path_samples(kSamples);
+      if (mode == 0) {
+        opt.set_device_kinematics(TPB_KIN_FAKE7);
+      } else {
+        opt.set_jacobian_func(FakeJacobian);
+        opt.set_path_ik_func([&](const VectorXd& initial_value, const std::vector<tp::Pose3d>& pose,
+                                 const std::vector<VectorXd>& joint, std::vector<VectorXd>* solution) {
+          // the warm start of a later window is the last solution of the previous one
+          if (ik_calls > 0 && last_solution.size() == initial_value.size()) {
+            for (size_t d = 0; d < initial_value.size(); ++d)
+              warm_start_ok = warm_start_ok && initial_value[d] == last_solution[d];
+          }
+          const tp::Status st = FakePathIK(initial_value, pose, joint, solution);
+          ++ik_calls;
+          ik_samples += static_cast<int>(pose.size());
+          if (!solution->empty()) last_solution = solution->back();
+          return st;
+        });
+      }
       auto cpath = std::make_shared<TimeableCartesianSplinePath>(opt);
       PathTimingTrajectory planner(PathTimingTrajectoryOptions()
                                        .SetTimeStep(tp::Milliseconds(4))
@@ -567,7 +590,14 @@ int main() {
       EXPECT(planner.IsTrajectoryAtEnd() && windows >= 3);
       EXPECT(cpath->GetState() == TimeablePath::State::kPathWasSampled);
       EXPECT(cpath->GetConstraints().size() == kSamples);
-      printf(",\"replanning\": {\n\"loops\": %d, \"windows\": %d,\n", loops, windows);
+      if (mode == 1) {
+        // one IK call per planning window, each on the indices the cache does not hold yet
+        // plus the re-evaluated first one; never the whole window again
+        EXPECT(ik_calls == windows && warm_start_ok);
+        EXPECT(ik_samples < windows * static_cast<int>(kSamples + 1) && ik_samples > static_cast<int>(kSamples));
+      }
+      printf(",\"%s\": {\n\"loops\": %d, \"windows\": %d, \"ik_calls\": %d, \"ik_samples\": %d,\n",
+             mode == 0 ? "replanning" : "replanning_host_callbacks", loops, windows, ik_calls, ik_samples);
       PrintArray("end_times", end_times);
       PrintArray("time", planner.GetTime());
       PrintArray("positions", Flatten(planner.GetPositions()));

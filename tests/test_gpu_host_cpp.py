@@ -277,12 +277,16 @@ def test_trajectory_buffer_matches_oracle(result, po):
     assert r["stop_halfway_num_samples"] == h.num_samples
 
 
-def test_cartesian_replanning_matches_oracle(result, po):
+@pytest.mark.parametrize("key", ["replanning", "replanning_host_callbacks"])
+def test_cartesian_replanning_matches_oracle(result, po, key):
     """The reference's 5-waypoint Cartesian re-planning scenario
-    (path_timing_trajectory_test.cc:695-757) through the host classes with device
-    kinematics (all windows on the device), against the oracle planner's loop."""
+    (path_timing_trajectory_test.cc:695-757) through the host classes, against the oracle
+    planner's loop (== the reference's object code, tests/test_oracle_vs_ref_cart.py):
+    with device kinematics (all windows on the device) and with the user's PathIKFunc /
+    JacobianFunc as host callbacks driven window by window from tpb_planner_plan (the IK
+    cache grows by the new indices only, timeable_path_cartesian_spline.cc:464-549)."""
     import test_oracle_windows as TW
-    r = result["cartesian"]["replanning"]
+    r = result["cartesian"][key]
     pl = TW.make_cart(TW.CART_WAYPOINTS)
     start, loops, windows, end_times = 0, 0, 0, []
     while not pl.target_reached:
@@ -302,3 +306,16 @@ def test_cartesian_replanning_matches_oracle(result, po):
     assert np.max(np.abs(pos[:m] - tr["r_pos"][:m])) <= 1e-9
     assert np.max(np.abs(vel[:m] - tr["r_vel"][:m])) <= 1e-6
     assert np.max(np.abs(pos[-1] - TW.CART_WAYPOINTS[-1])) <= 1e-9 and (vel[-1] == 0).all()
+    if key == "replanning_host_callbacks":
+        assert r["ik_calls"] == windows
+        assert 1001 < r["ik_samples"] < 1001 * windows
+        if po.have_ref():
+            # every IK index is solved once (+ the re-evaluated first sample of each call):
+            # the reference's own path_ik_positions_ cache after the same loop
+            import test_oracle_vs_ref_cart as TC
+            _, ref = TC.cart_pair(TW.CART_WAYPOINTS)
+            start = 0
+            while not ref.state()["target_reached"]:
+                assert ref.plan(start, TW.HORIZON) == 0
+                start = min(ref.state()["end_time"], start + TW.REPLAN)
+            assert r["ik_samples"] == len(ref.ik_positions()) + windows

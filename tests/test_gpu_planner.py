@@ -208,7 +208,7 @@ def test_initial_velocity():
 
 # ---- Cartesian paths behind the planner (device kinematics TPB_KIN_FAKE7) -------------
 def run_cart_replanning(pose_wp, joint_wp, N, delta, dt, skip, horizon, replan, P_cap,
-                        max_calls=600):
+                        max_calls=600, host_callbacks=None):
     """Like run_replanning for TimeableCartesianSplinePath with the reference test's fake
     kinematics on the device.  The device evaluates sin/cos/atan2 of the quaternion
     spline and of the fake IK with its own libm, so values are compared within the
@@ -223,10 +223,13 @@ def run_cart_replanning(pose_wp, joint_wp, N, delta, dt, skip, horizon, replan, 
     eng.set_joint_limits(vmax, amax)
     eng.set_sampling(np.full(B, delta))
     eng.planner_reset(P_cap, dt, skip=skip, max_initial_velocity_error=1e-2)
-    with pytest.raises(pkg.TpbError) as ei:  # host kinematics: one window at a time
+    with pytest.raises(pkg.TpbError) as ei:  # neither callbacks nor a device model yet
         eng.planner_plan(0, horizon)
-    assert ei.value.code == 12
-    eng.planner_set_kinematics(1)
+    assert ei.value.code == 9
+    if host_callbacks is None:
+        eng.planner_set_kinematics(1)
+    else:
+        eng.planner_set_host_kinematics(*host_callbacks)
     planners = [orc.Planner(joint_wp[b], vmax[b], amax[b], N, delta, dt, skip=skip, P_cap=P_cap,
                             pose_waypoints=pose_wp[b], max_initial_velocity_error=1e-2)
                 for b in range(B)]
@@ -277,6 +280,78 @@ def test_reference_cartesian_replanning(skip):
     np.testing.assert_allclose(rows["r_pos"][-1], TW.CART_WAYPOINTS[-1], atol=1e-9)
     np.testing.assert_array_equal(rows["r_vel"][-1], 0.0)
     assert np.all(np.abs(rows["r_vel"]) <= 1.0 + 1e-9) and np.all(np.abs(rows["r_acc"]) <= 2.0 + 1e-9)
+
+
+class CountingFakeKinematics:
+    """The reference test's FakePathIK / FakeJacobian (the oracle's C restatement) as the
+    user's host callbacks; records what tpb_planner_plan asks for."""
+
+    def __init__(self, B):
+        self.calls = np.zeros(B, int)
+        self.samples = np.zeros(B, int)
+        self.last = [None] * B
+        self.warm_ok = True
+
+    def path_ik(self, path, initial, pose_targets, joint_targets):
+        if self.calls[path] > 0:  # warm start = last solution of the previous window
+            self.warm_ok = self.warm_ok and np.array_equal(initial, self.last[path])
+        else:                     # fresh path: the first joint target (:503-505)
+            self.warm_ok = self.warm_ok and np.array_equal(initial, joint_targets[0])
+        sol = orc.fake_ik(pose_targets, joint_targets)
+        self.calls[path] += 1
+        self.samples[path] += len(sol)
+        self.last[path] = sol[-1].copy()
+        return sol
+
+    def jacobian(self, path, q):
+        return orc.fake_jacobian(q)
+
+
+@pytest.mark.parametrize("skip", [False, True])
+def test_cartesian_replanning_with_user_kinematics(skip):
+    """a user PathIKFunc / JacobianFunc over several planning windows
+    (timeable_path_cartesian_spline.cc:464-549 with path_start > 0 and the IK cache
+    :504-517), driven from tpb_planner_plan: the reference's 5-waypoint scenario
+    (path_timing_trajectory_test.cc:695-757) equals the oracle after every Plan() (within
+    the tolerances of run_cart_replanning: the targets handed to the callbacks come from
+    the device's quaternion spline, i.e. CUDA's sin / cos / atan2); the IK is asked once
+    per window, for the indices it has not solved yet, warm-started from the last one."""
+    import test_oracle_windows as TW
+    joint = TW.CART_WAYPOINTS[None]
+    pose = np.stack([TW.fake_fk_pose(q) for q in TW.CART_WAYPOINTS])[None]
+    kin = CountingFakeKinematics(1)
+    eng, planners, n = run_cart_replanning(pose, joint, 1000, 0.005, 0.004, skip, 750 * MS,
+                                           200 * MS, 16384,
+                                           host_callbacks=(kin.path_ik, kin.jacobian))
+    assert n["windows"] >= 3 and planners[0].target_reached
+    assert kin.warm_ok and kin.calls[0] == n["windows"]
+    assert 1001 < kin.samples[0] < 1001 * n["windows"]
+
+
+def test_batch_of_cartesian_paths_with_user_kinematics():
+    """Eight Cartesian paths in lockstep, user kinematics: per-path IK caches."""
+    B = 8
+    pose_wp, joint_wp, _, _ = pkg.workloads.cart_paths(B, 5, seed=5300)
+    N = 256
+    knot_end = max(orc.plan_cart_fake(pose_wp[b], joint_wp[b], np.ones(7), np.full(7, 2.0),
+                                      64)["knot_end"] for b in range(B))
+    delta = knot_end / (N - 1) / 2.5
+    kin = CountingFakeKinematics(B)
+    eng, planners, n = run_cart_replanning(pose_wp, joint_wp, N, delta, 0.008, False, 1000 * MS,
+                                           400 * MS, 16 * N,
+                                           host_callbacks=(kin.path_ik, kin.jacobian))
+    assert n["windows"] >= 2 * B and all(pl.target_reached for pl in planners)
+    assert kin.warm_ok and kin.calls.sum() == n["windows"]
+    # a failing PathIKFunc ends the call with its status
+    eng.planner_reset(16 * N, 0.008, max_initial_velocity_error=1e-2)
+
+    def bad_ik(path, initial, pose_targets, joint_targets):
+        raise RuntimeError("no solution")
+
+    eng.planner_set_host_kinematics(bad_ik, kin.jacobian)
+    with pytest.raises(pkg.TpbError) as ei:
+        eng.planner_plan(0, 1000 * MS)
+    assert ei.value.code == 13 and "PathIKFunc" in str(ei.value)
 
 
 def test_batch_of_cartesian_paths():

@@ -97,6 +97,12 @@ def lib_path() -> str:
     return _LIB
 
 
+_dptr = C.POINTER(C.c_double)
+# tpb_path_ik_fn / tpb_jacobian_fn (include/tpb.h)
+PATH_IK_FN = C.CFUNCTYPE(C.c_int32, C.c_void_p, C.c_int32, _dptr, C.c_int32, _dptr, _dptr, _dptr)
+JACOBIAN_FN = C.CFUNCTYPE(C.c_int32, C.c_void_p, C.c_int32, _dptr, _dptr)
+
+
 def lib():
     """Load libtpb.so; raises if it has not been built (no fallback)."""
     global _lib
@@ -178,6 +184,8 @@ def lib():
         L.tpb_planner_set_initial_velocity.argtypes = [vp, vp, i32]
         L.tpb_planner_set_kinematics.restype = i32
         L.tpb_planner_set_kinematics.argtypes = [vp, i32]
+        L.tpb_planner_set_host_kinematics.restype = i32
+        L.tpb_planner_set_host_kinematics.argtypes = [vp, PATH_IK_FN, JACOBIAN_FN, vp]
         L.tpb_planner_plan.restype = i32
         L.tpb_planner_plan.argtypes = [vp, C.c_int64, C.c_int64, C.POINTER(C.c_int64)]
         L.tpb_path_stop_parameter.restype = i32
@@ -513,6 +521,35 @@ class Engine:
 
     def planner_set_kinematics(self, model=1):
         self._ck(lib().tpb_planner_set_kinematics(self._h, int(model)))
+
+    def planner_set_host_kinematics(self, path_ik, jacobian):
+        """tpb_planner_set_host_kinematics: the user's PathIKFunc / JacobianFunc for
+        Cartesian paths behind the planner, as Python callables
+            path_ik(path, initial_value [D], pose_targets [M][7], joint_targets [M][D])
+                -> solution [M][D]   (raise to fail the plan)
+            jacobian(path, joint_positions [D]) -> [6][D]
+        called on the host once per planning window / path sample."""
+        D = self.D
+
+        def ik_thunk(_user, path, initial, M, pt, jt, sol):
+            try:
+                out = path_ik(path, np.ctypeslib.as_array(initial, (D,)),
+                              np.ctypeslib.as_array(pt, (M, 7)), np.ctypeslib.as_array(jt, (M, D)))
+                np.ctypeslib.as_array(sol, (M, D))[:] = out
+                return 0
+            except Exception:  # noqa: BLE001 -- a status for the C caller
+                return 13
+
+        def jac_thunk(_user, path, q, out):
+            try:
+                np.ctypeslib.as_array(out, (6, D))[:] = jacobian(path, np.ctypeslib.as_array(q, (D,)))
+                return 0
+            except Exception:  # noqa: BLE001
+                return 13
+
+        self._host_kinematics = (PATH_IK_FN(ik_thunk), JACOBIAN_FN(jac_thunk))  # keep alive
+        self._ck(lib().tpb_planner_set_host_kinematics(self._h, self._host_kinematics[0],
+                                                       self._host_kinematics[1], None))
 
     def planner_plan(self, start_ns, horizon_ns, want_total=True):
         """tpb_planner_plan: PathTimingTrajectory::Plan(start, horizon) for every path

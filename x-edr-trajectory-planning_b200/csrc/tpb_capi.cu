@@ -61,6 +61,14 @@ struct tpb_engine {
   std::vector<void*> w_big;  // the P_cap-sized arrays (reallocated when the capacity grows)
   bool planner_ready = false;
   int planner_kinematics = TPB_KIN_HOST;  // device kinematics of Cartesian planner windows
+  // user kinematics of Cartesian planner windows (tpb_planner_set_host_kinematics) and the
+  // reference's path_ik_positions_ cache, one per path: [ik index][D]
+  tpb_path_ik_fn host_ik = nullptr;
+  tpb_jacobian_fn host_jacobian = nullptr;
+  void* host_user = nullptr;
+  std::vector<std::vector<double>> ik_cache;
+  std::vector<double> hk_pose, hk_joint, hk_start, hk_delta, hk_q, hk_jac, hk_solution;
+  std::vector<int32_t> hk_active;
   int32_t* any_active_host = nullptr;  // pinned
   // tpb_switch_to_waypoint_path staging: [Bmax] / [Bmax][Wmax][D]
   double *sw_keep = nullptr, *sw_wp = nullptr;
@@ -1130,6 +1138,7 @@ int32_t tpb_planner_reset(tpb_engine* e, int32_t path_sample_capacity, double ti
   TPB_CUDA(e, cudaMemsetAsync(e->a.r_offset, 0, sizeof(int64_t) * (d.B + 1), e->stream));
   e->launches += tpb::launch_planner_reset(d, w, e->stream);
   TPB_CUDA(e, cudaGetLastError());
+  for (auto& c : e->ik_cache) c.clear();  // TimeableCartesianSplinePath::Reset / SetWaypoints
   e->planner_ready = true;
   e->resampled = true;  // zero rows so far
   return TPB_OK;
@@ -1171,6 +1180,96 @@ int32_t tpb_planner_set_kinematics(tpb_engine* e, int32_t model) {
   return TPB_OK;
 }
 
+namespace {
+
+// One planning window of Cartesian paths with user kinematics: SamplePath's IK part
+// (timeable_path_cartesian_spline.cc:464-549) and the Jacobians of ConstraintSetup
+// (:551-595) on the host.  The device has just written the window's N + 1 pose / joint
+// targets (IK indices PathIkIndex(path_start) - 1 ... + N - 1).  Per active path: the
+// targets of the IK indices not solved yet go to the PathIKFunc, warm-started from the
+// last cached solution (:503-506); its solutions but the first extend the cache
+// (:512-513); the window's positions are the cache entries of its indices (:527-540);
+// the JacobianFunc is evaluated at each of them.  Positions and Jacobians go back to
+// the device (TPB_ARR_Q, the Jacobian table), which does the rest.
+int32_t host_kinematics_window(tpb_engine* e) {
+  const auto& d = e->dims;
+  const size_t B = d.B, N = d.N, D = d.D;
+  e->hk_active.resize(B);
+  e->hk_start.resize(B);
+  e->hk_delta.resize(B);
+  e->hk_pose.resize(B * (N + 1) * 7);
+  e->hk_joint.resize(B * (N + 1) * D);
+  e->hk_q.resize(N * D);
+  e->hk_jac.resize(N * 6 * D);
+  if (e->ik_cache.size() < B) e->ik_cache.resize(B);
+  auto d2h = [&](void* dst, const void* src, size_t bytes) {
+    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, e->stream);
+  };
+  TPB_CUDA(e, d2h(e->hk_active.data(), e->w.active, B * sizeof(int32_t)));
+  TPB_CUDA(e, d2h(e->hk_start.data(), e->a.path_start, B * sizeof(double)));
+  TPB_CUDA(e, d2h(e->hk_delta.data(), e->a.delta, B * sizeof(double)));
+  TPB_CUDA(e, d2h(e->hk_pose.data(), e->a.pose_targets, e->hk_pose.size() * sizeof(double)));
+  TPB_CUDA(e, d2h(e->hk_joint.data(), e->a.joint_targets, e->hk_joint.size() * sizeof(double)));
+  TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+  for (size_t b = 0; b < B; ++b) {
+    if (e->hk_active[b] == 0) continue;
+    std::vector<double>& cache = e->ik_cache[b];
+    const double delta = e->hk_delta[b];
+    // PathIkIndex (:671-674)
+    const int start_index = static_cast<int>(std::round(e->hk_start[b] / delta));
+    const double path_horizon = e->hk_start[b] + delta * static_cast<double>(N - 1);
+    const int horizon_index = static_cast<int>(std::round(path_horizon / delta));
+    const int current_upper = static_cast<int>(cache.size() / D) - 1;
+    if (horizon_index - start_index != static_cast<int>(N) - 1 || current_upper < start_index - 1)
+      return fail(e, TPB_INTERNAL, "IK index range of the window does not follow the cache");
+    if (horizon_index >= current_upper) {
+      const int num_new = horizon_index - current_upper + 1;
+      const size_t slot = static_cast<size_t>(current_upper - (start_index - 1));
+      const double* pt = e->hk_pose.data() + (b * (N + 1) + slot) * 7;
+      const double* jt = e->hk_joint.data() + (b * (N + 1) + slot) * D;
+      const double* initial =
+          current_upper > 0 ? cache.data() + static_cast<size_t>(current_upper) * D : jt;
+      e->hk_solution.assign(static_cast<size_t>(num_new) * D, 0.0);
+      const int32_t rc = e->host_ik(e->host_user, static_cast<int32_t>(b), initial, num_new, pt,
+                                    jt, e->hk_solution.data());
+      // partial solutions are kept like the reference keeps them (:509-513)
+      cache.insert(cache.end(), e->hk_solution.begin() + D, e->hk_solution.end());
+      if (rc != TPB_OK)
+        return fail(e, rc, "PathIKFunc failed for path " + std::to_string(b));
+    }
+    const double* win = cache.data() + static_cast<size_t>(start_index) * D;
+    TPB_CUDA(e, cudaMemcpyAsync(e->a.q + b * N * D, win, N * D * sizeof(double),
+                                cudaMemcpyHostToDevice, e->stream));
+    for (size_t i = 0; i < N; ++i) {
+      const int32_t rc = e->host_jacobian(e->host_user, static_cast<int32_t>(b), win + i * D,
+                                          e->hk_jac.data() + i * 6 * D);
+      if (rc != TPB_OK)
+        return fail(e, rc, "JacobianFunc failed for path " + std::to_string(b));
+    }
+    TPB_CUDA(e, cudaMemcpyAsync(e->a.jac + b * N * 6 * D, e->hk_jac.data(),
+                                N * 6 * D * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    // the staging vectors are reused by the next path
+    TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+  }
+  return TPB_OK;
+}
+
+}  // namespace
+
+int32_t tpb_planner_set_host_kinematics(tpb_engine* e, tpb_path_ik_fn ik, tpb_jacobian_fn jacobian,
+                                        void* user) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  if (e->mode != Mode::kCartesian)
+    return fail(e, TPB_FAILED_PRECONDITION, "engine was not created for Cartesian paths");
+  if (ik == nullptr || jacobian == nullptr)
+    return fail(e, TPB_INVALID_ARGUMENT, "PathIKFunc / JacobianFunc is null");
+  e->host_ik = ik;
+  e->host_jacobian = jacobian;
+  e->host_user = user;
+  e->planner_kinematics = TPB_KIN_HOST;
+  return TPB_OK;
+}
+
 int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
                          int64_t* total_samples) {
   TPB_NVTX("tpb_planner_plan");
@@ -1180,13 +1279,15 @@ int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
     return fail(e, TPB_FAILED_PRECONDITION, "No path set.");
   if (!e->have_limits) return fail(e, TPB_FAILED_PRECONDITION, "joint limits not set");
   const bool cart = e->mode == Mode::kCartesian;
+  const bool host_kinematics = cart && e->planner_kinematics == TPB_KIN_HOST;
   if (cart) {
-    // windows beyond the first need IK solutions the device can produce itself; with
-    // a host PathIKFunc the caller plans window by window (tpb_cart_*)
-    if (e->planner_kinematics != TPB_KIN_FAKE7 || d.D != 7)
-      return fail(e, TPB_UNIMPLEMENTED,
-                  "moving-horizon planning of Cartesian paths needs built-in device kinematics "
-                  "(tpb_planner_set_kinematics)");
+    if (host_kinematics && (e->host_ik == nullptr || e->host_jacobian == nullptr))
+      return fail(e, TPB_FAILED_PRECONDITION,
+                  "Cartesian paths behind the planner need kinematics: "
+                  "tpb_planner_set_host_kinematics (user PathIKFunc / JacobianFunc) or "
+                  "tpb_planner_set_kinematics (built-in device model)");
+    if (!host_kinematics && (e->planner_kinematics != TPB_KIN_FAKE7 || d.D != 7))
+      return fail(e, TPB_INVALID_ARGUMENT, "unknown kinematics model for this dof count");
     if (!(e->max_trans_vel > 0) || !(e->max_rot_vel > 0))
       return fail(e, TPB_FAILED_PRECONDITION, "Cartesian velocity limits not set");
   }
@@ -1207,6 +1308,8 @@ int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
   e->launches += tpb::launch_plan_begin(d, e->a, w, o, start_ns, horizon_ns, e->stream);
   int32_t more = 0;
   TPB_CUDA(e, read_flag(&more));
+  if (host_kinematics && e->a.jac == nullptr)  // the Jacobian table of the host callbacks
+    TPB_CUDA(e, dev_alloc(e, &e->a.jac, static_cast<size_t>(d.Bmax) * d.N * 6 * d.D));
   tpb::DeviceArrays am = e->a;  // the stage kernels, masked to the paths that plan a window
   am.active = w.active;
   const int max_solver_loops = std::max(100, 10 * d.N);  // (:399-401)
@@ -1214,7 +1317,13 @@ int32_t tpb_planner_plan(tpb_engine* e, int64_t start_ns, int64_t horizon_ns,
     if (window > o.max_planning_iterations + 1)
       return fail(e, TPB_INTERNAL, "planning loop did not terminate");
     e->launches += tpb::launch_window_begin(d, e->a, w, start_ns, horizon_ns, e->stream);
-    if (cart) {  // SamplePath (targets, path IK, finite differences) + ConstraintSetup
+    if (cart && host_kinematics) {
+      e->launches += tpb::launch_cart_sample_targets(d, am, e->stream);
+      const int32_t rc = host_kinematics_window(e);  // user PathIKFunc / JacobianFunc
+      if (rc != TPB_OK) return rc;
+      e->launches += tpb::launch_cart_constraints(d, am, e->safety, e->max_trans_vel,
+                                                  e->max_rot_vel, TPB_KIN_HOST, true, e->stream);
+    } else if (cart) {  // SamplePath (targets, path IK, finite differences) + ConstraintSetup
       e->launches += tpb::launch_cart_sample_targets(d, am, e->stream);
       e->launches += tpb::launch_cart_ik_builtin(d, am, e->planner_kinematics, e->stream);
       e->launches += tpb::launch_cart_constraints(d, am, e->safety, e->max_trans_vel,

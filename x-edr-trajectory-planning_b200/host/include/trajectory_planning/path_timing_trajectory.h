@@ -132,7 +132,11 @@ class PathTimingTrajectory : public TrajectoryPlanner {
     }
     int64_t total = 0;
     rc = tpb_planner_plan(e, start.ns, time_horizon.ns, &total);
-    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
+    if (rc != TPB_OK) {
+      // a failing PathIKFunc / JacobianFunc ends Plan with its own Status (.cc:518-525)
+      if (auto st = path_->TakeCallbackStatus(); !st.ok()) return st;
+      return tp::FromCode(rc, tpb_last_error(e));
+    }
     // the planner's state after the call
     int32_t status = TPB_PATH_NOT_RUN, loops = 0, to_end = 0, reached = 0, rows_mode = 0;
     int64_t start_ns = 0, end_ns = 0, decel_ns = 0;

@@ -97,6 +97,8 @@ class TimeablePath {
   virtual bool SupportsDevicePlanner() const { return false; }
   virtual tp::Status BeforeDevicePlan() { return tp::OkStatus(); }
   virtual tp::Status AfterDevicePlan(bool /*window_was_sampled*/) { return tp::OkStatus(); }
+  // the Status a user callback returned during the device plan (Ok if none failed)
+  virtual tp::Status TakeCallbackStatus() { return tp::OkStatus(); }
 };
 
 inline constexpr const char* ToString(const TimeablePath::State state) {

@@ -290,11 +290,18 @@ class TimeableCartesianSplinePath : public TimeablePath {
   }
   const std::vector<TimeOptimalPathProfile::Constraint>& GetConstraints() const override { return constraints_; }
 
-  // Device planner hooks (timeable_path.h).  With built-in device kinematics the IK
-  // solution at an IK index does not depend on a warm start from the previous window,
-  // so PathTimingTrajectory plans all windows on the device (tpb_planner_plan); with
-  // host callbacks it plans one window at a time through SamplePath / ConstraintSetup.
-  bool SupportsDevicePlanner() const override { return options_.device_kinematics() != TPB_KIN_HOST; }
+  // Device planner hooks (timeable_path.h): PathTimingTrajectory plans all windows
+  // through tpb_planner_plan.  With built-in device kinematics nothing leaves the GPU;
+  // with the user's PathIKFunc / JacobianFunc every window's new targets come back to
+  // the host, the callbacks run (warm-started from the previous window's last solution,
+  // .cc:503-517) and positions + Jacobians return to the device
+  // (tpb_planner_set_host_kinematics).
+  bool SupportsDevicePlanner() const override { return true; }
+  tp::Status TakeCallbackStatus() override {
+    tp::Status st = callback_status_;
+    callback_status_ = tp::OkStatus();
+    return st;
+  }
   tp::Status BeforeDevicePlan() override {
     if (!e_ || joint_waypoints_.empty()) return tp::FailedPreconditionError("No path set");
     int32_t rc = tpb_set_joint_limits(e_, max_joint_velocity_.data(), max_joint_acceleration_.data(), 0, 0);
@@ -305,8 +312,68 @@ class TimeableCartesianSplinePath : public TimeablePath {
       rc = tpb_set_cart_options(e_, options_.translation_rounding(), max_translational_velocity_,
                                 max_rotational_velocity_);
     }
-    if (rc == TPB_OK) rc = tpb_planner_set_kinematics(e_, options_.device_kinematics());
+    if (rc == TPB_OK) {
+      rc = options_.device_kinematics() != TPB_KIN_HOST
+               ? tpb_planner_set_kinematics(e_, options_.device_kinematics())
+               : tpb_planner_set_host_kinematics(e_, &PathIkThunk, &JacobianThunk, this);
+    }
+    callback_status_ = tp::OkStatus();
     return rc == TPB_OK ? tp::OkStatus() : tp::FromCode(rc, tpb_last_error(e_));
+  }
+  // tpb_path_ik_fn: the user's PathIKFunc on one window's new targets
+  static int32_t PathIkThunk(void* user, int32_t /*path*/, const double* initial_value,
+                             int32_t num_samples, const double* pose_targets,
+                             const double* joint_targets, double* solution) {
+    auto* self = static_cast<TimeableCartesianSplinePath*>(user);
+    const size_t D = self->options_.num_dofs(), M = static_cast<size_t>(num_samples);
+    self->sampled_pose_targets_.resize(M);
+    self->sampled_joint_targets_.resize(M);
+    for (size_t m = 0; m < M; ++m) {
+      const double* p = pose_targets + m * 7;
+      self->sampled_pose_targets_[m] =
+          tp::Pose3d(tp::Quaterniond(p[6], p[3], p[4], p[5]), tp::Vector3d(p[0], p[1], p[2]));
+      self->sampled_joint_targets_[m] = tp::VectorXd(joint_targets + m * D, D);
+    }
+    self->new_ik_path_.clear();
+    const tp::Status st = self->path_ik_func_(tp::VectorXd(initial_value, D), self->sampled_pose_targets_,
+                                              self->sampled_joint_targets_, &self->new_ik_path_);
+    for (size_t m = 0; m < M && m < self->new_ik_path_.size(); ++m) {
+      if (self->new_ik_path_[m].size() != D) {
+        self->callback_status_ = tp::InternalError("path IK sample has wrong size");
+        return TPB_INTERNAL;
+      }
+      std::copy(self->new_ik_path_[m].begin(), self->new_ik_path_[m].end(), solution + m * D);
+    }
+    if (!st.ok()) {
+      self->callback_status_ = st;
+      return static_cast<int32_t>(st.code());
+    }
+    if (self->new_ik_path_.size() != M) {
+      self->callback_status_ =
+          tp::InternalError("path IK returned " + std::to_string(self->new_ik_path_.size()) +
+                            " samples for " + std::to_string(M) + " targets");
+      return TPB_INTERNAL;
+    }
+    return TPB_OK;
+  }
+  // tpb_jacobian_fn: the user's JacobianFunc at one path sample
+  static int32_t JacobianThunk(void* user, int32_t /*path*/, const double* joint_positions,
+                               double* jacobian_out) {
+    auto* self = static_cast<TimeableCartesianSplinePath*>(user);
+    const size_t D = self->options_.num_dofs();
+    tp::Matrix6Xd jacobian(6, D);
+    jacobian.setZero();
+    const tp::Status st = self->jacobian_func_(tp::VectorXd(joint_positions, D), &jacobian);
+    if (!st.ok()) {
+      self->callback_status_ = st;
+      return static_cast<int32_t>(st.code());
+    }
+    if (jacobian.cols() != D) {
+      self->callback_status_ = tp::InternalError("Jacobian has wrong number of columns");
+      return TPB_INTERNAL;
+    }
+    std::copy(jacobian.data(), jacobian.data() + 6 * D, jacobian_out);
+    return TPB_OK;
   }
   tp::Status AfterDevicePlan(bool window_was_sampled) override {
     if (!window_was_sampled) return tp::OkStatus();
@@ -471,6 +538,7 @@ class TimeableCartesianSplinePath : public TimeablePath {
   double max_translational_velocity_ = 0.0, max_rotational_velocity_ = 0.0;
   CartesianPathOptions::PathIKFunc path_ik_func_;
   CartesianPathOptions::JacobianFunc jacobian_func_;
+  tp::Status callback_status_;  // what a user callback returned inside tpb_planner_plan
   double parameter_start_ = -1.0, parameter_end_ = -1.0;
 };
 
