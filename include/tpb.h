@@ -558,6 +558,35 @@ int32_t tpb_spline_eval_device(const tpb_spline_eval_desc* d, void* cuda_stream)
 /* Same with host pointers (allocates, copies in, evaluates, copies out). */
 int32_t tpb_spline_eval_host(const tpb_spline_eval_desc* d, int32_t device);
 
+/* ---- stage A stand-alone: quaternion B-spline evaluation ------------------- */
+/* BSplineQ::EvalCurve (splines/bsplineq.cc:223-244; dout == NULL) or
+ * BSplineQ::EvalCurveAndDerivative (:246-307; dout != NULL) for num_splines quaternion
+ * splines that share degree (1..5) and num_points, evals_per_spline parameters each;
+ * u == NULL: implicit grid u0[s] + i * du[s].  Quaternions are (x, y, z, w).
+ * out / dout: [num_splines][evals_per_spline][4] -- the curve value (normalised with a
+ * non-negative real part for EvalCurve; the un-normalised product, sign-flipped when its
+ * real part is negative, for EvalCurveAndDerivative, as in the reference) and d/du.
+ * status (may be NULL): 0 or kOutOfRange (11) when u is outside the knot range (the
+ * output rows are then left untouched).  Values agree with the reference to the
+ * accuracy of the device's log / atan2 / sin / cos / exp (<= 1e-12 absolute). */
+typedef struct {
+  int32_t degree, num_points;
+  int32_t num_splines;
+  int64_t evals_per_spline;
+  const double* knots; /* [num_splines][num_points + degree + 1] */
+  const double* quats; /* [num_splines][num_points][4] */
+  const double* u;     /* [num_splines][evals_per_spline] or NULL */
+  const double* u0;    /* [num_splines] (grid mode) */
+  const double* du;    /* [num_splines] (grid mode) */
+  double* out;
+  double* dout;
+  int32_t* status;
+} tpb_quat_spline_eval_desc;
+/* All pointers are device pointers; cuda_stream may be NULL (default stream). */
+int32_t tpb_quat_spline_eval_device(const tpb_quat_spline_eval_desc* d, void* cuda_stream);
+/* Same with host pointers (allocates, copies in, evaluates, copies out). */
+int32_t tpb_quat_spline_eval_host(const tpb_quat_spline_eval_desc* d, int32_t device);
+
 /* Diagnostics: the FP64 FMA rate of `device` in TFLOP/s (2 flops per FMA), measured
  * with eight independent FMA chains per thread -- the denominator bench.py reports the
  * limit-curve and phase-plane kernels' FP64 FLOP/s against. */

@@ -51,3 +51,13 @@ print("kernel span (cycles): %.0f; last start %.0f" % ((start + tot).max(), star
 worst = np.argsort(-tot)[:5]
 for b in worst:
     print("path", b, "phases", ph[b].astype(int).tolist(), "loops", int(dbg[b, 7]))
+steps = dbg[:, 16]
+print("extremal steps per path: mean %.0f p50 %.0f p90 %.0f p99 %.0f max %.0f" % (
+    steps.mean(), np.percentile(steps, 50), np.percentile(steps, 90), np.percentile(steps, 99), steps.max()))
+pair = np.maximum(steps[0::2], steps[1::2])
+print("max over the two paths of a warp (k_optimize_pair): mean %.0f p90 %.0f p99 %.0f max %.0f" % (
+    pair.mean(), np.percentile(pair, 90), np.percentile(pair, 99), pair.max()))
+srt = np.sort(steps)
+pair_sorted = np.maximum(srt[0::2], srt[1::2])
+print("the same with paths paired by step count: mean %.0f max %.0f" % (pair_sorted.mean(), pair_sorted.max()))
+np.save(os.path.join(ROOT, "gpurun_out", "phase_dbg.npy"), dbg)

@@ -12,7 +12,8 @@ The directory name contains hyphens, so import it through
 """
 from .binding import (  # noqa: F401
     ARR, PATH_OK, Engine, TpbError, lib, lib_path, rescale_to_stop_device, rescale_to_stop_host,
-    spline_eval_device, spline_eval_host, TrajectoryBufferBatch, TrajectoryBufferView, SKIP_INDEX,
+    spline_eval_device, spline_eval_host, quat_spline_eval_device, quat_spline_eval_host,
+    TrajectoryBufferBatch, TrajectoryBufferView, SKIP_INDEX,
     time_from_sec_ns, time_to_sec, measure_fp64_fma_peak, resample_uniform_noalloc, MultiEngine, shard_range, HostBatch,
 )
 from . import workloads  # noqa: F401

@@ -184,6 +184,10 @@ def lib():
         L.tpb_planner_set_initial_velocity.argtypes = [vp, vp, i32]
         L.tpb_planner_set_kinematics.restype = i32
         L.tpb_planner_set_kinematics.argtypes = [vp, i32]
+        L.tpb_quat_spline_eval_host.restype = i32
+        L.tpb_quat_spline_eval_host.argtypes = [vp, i32]
+        L.tpb_quat_spline_eval_device.restype = i32
+        L.tpb_quat_spline_eval_device.argtypes = [vp, vp]
         L.tpb_planner_set_host_kinematics.restype = i32
         L.tpb_planner_set_host_kinematics.argtypes = [vp, PATH_IK_FN, JACOBIAN_FN, vp]
         L.tpb_planner_plan.restype = i32
@@ -675,6 +679,49 @@ def spline_eval_device(knots, ctrl, degree, nder, out, u=None, u0=None, du=None,
     rc = lib().tpb_spline_eval_device(C.byref(d), stream)
     if rc != 0:
         raise TpbError(rc, "tpb_spline_eval_device")
+
+
+class _QuatSplineDesc(C.Structure):
+    _fields_ = [("degree", C.c_int32), ("num_points", C.c_int32), ("num_splines", C.c_int32),
+                ("evals_per_spline", C.c_int64), ("knots", C.c_void_p), ("quats", C.c_void_p),
+                ("u", C.c_void_p), ("u0", C.c_void_p), ("du", C.c_void_p), ("out", C.c_void_p),
+                ("dout", C.c_void_p), ("status", C.c_void_p)]
+
+
+def quat_spline_eval_host(knots, quats, degree, u=None, u0=None, du=None, evals=None,
+                          derivative=False, device=0):
+    """tpb_quat_spline_eval_host: BSplineQ::EvalCurve (derivative=False) or
+    EvalCurveAndDerivative for knots [S][n+p+1], quats [S][n][4] (x, y, z, w); u [S][E] or
+    the grid u0[s] + i * du[s].  Returns (q [S][E][4], dq or None, status [S][E])."""
+    knots, quats = _f64(knots), _f64(quats)
+    S, n, _ = quats.shape
+    if u is not None:
+        u = _f64(u)
+        evals = u.shape[1]
+    else:
+        u0, du = _f64(u0), _f64(du)
+    out = np.full((S, evals, 4), np.nan)
+    dout = np.full((S, evals, 4), np.nan) if derivative else None
+    status = np.zeros((S, evals), np.int32)
+    d = _QuatSplineDesc(degree, n, S, evals, _addr(knots), _addr(quats), _addr(u), _addr(u0),
+                        _addr(du), _addr(out), _addr(dout), _addr(status))
+    rc = lib().tpb_quat_spline_eval_host(C.byref(d), device)
+    if rc != 0:
+        raise TpbError(rc, "tpb_quat_spline_eval_host")
+    return out, dout, status
+
+
+def quat_spline_eval_device(knots, quats, degree, out, dout=None, u=None, u0=None, du=None,
+                            evals=None, status=None, stream=None):
+    """tpb_quat_spline_eval_device on torch CUDA tensors (asynchronous on `stream`)."""
+    S, n, _ = quats.shape
+    if u is not None:
+        evals = u.shape[1]
+    d = _QuatSplineDesc(degree, n, S, evals, _addr(knots), _addr(quats), _addr(u), _addr(u0),
+                        _addr(du), _addr(out), _addr(dout), _addr(status))
+    rc = lib().tpb_quat_spline_eval_device(C.byref(d), stream)
+    if rc != 0:
+        raise TpbError(rc, "tpb_quat_spline_eval_device")
 
 
 def _addr(x):
