@@ -615,6 +615,37 @@ int main() {
     PrintArray("pose_waypoints", pflat, false);
     printf("},\n");
   }
+  // ---- more waypoints than the path's engine was created for: the engine is re-created
+  // (possibly at the same address) and the planner starts from an empty plan on it
+  {
+    constexpr size_t kN = 200;
+    auto path = std::make_shared<TimeableJointSplinePath>(
+        JointPathOptions().set_num_dofs(3).set_num_path_samples(kN));
+    PathTimingTrajectory planner(PathTimingTrajectoryOptions()
+                                     .SetTimeStep(tp::Milliseconds(4))
+                                     .SetNumDofs(3)
+                                     .SetNumPathSamples(kN));
+    EXPECT(planner.SetPath(path).ok());
+    VectorXd vmax = VectorXd::Constant(3, 1.0), amax = VectorXd::Constant(3, 2.0);
+    EXPECT(path->SetMaxJointVelocity(ToSpan(vmax)).ok());
+    EXPECT(path->SetMaxJointAcceleration(ToSpan(amax)).ok());
+    std::vector<VectorXd> few = {VectorXd{0.0, 0.0, 0.0}, VectorXd{0.5, 0.2, -0.1}, VectorXd{0.1, 0.4, 0.3}};
+    EXPECT(path->SetWaypoints(few).ok());
+    EXPECT(planner.Plan(TimeFromSec(0.0), tp::Seconds(1000)).ok());
+    const uint64_t generation = path->DeviceEngineGeneration();
+    std::vector<VectorXd> many;
+    for (int i = 0; i < 40; ++i) {
+      many.push_back(VectorXd{0.1 * std::sin(0.7 * i), 0.05 * i, 0.1 * std::cos(0.3 * i)});
+    }
+    EXPECT(path->SetWaypoints(many).ok());
+    EXPECT(path->DeviceEngineGeneration() == generation + 1);
+    const tp::Status st = planner.Plan(TimeFromSec(0.0), tp::Seconds(1000));
+    EXPECT(st.ok());
+    if (!st.ok()) fprintf(stderr, "Plan on a re-created engine: %s\n", st.message().c_str());
+    EXPECT(planner.IsTrajectoryAtEnd() && !planner.GetPositions().empty());
+    const auto& last = planner.GetPositions().back();
+    for (int d = 0; d < 3; ++d) EXPECT(std::abs(last[d] - many.back()[d]) <= 1e-9);
+  }
   // ---- batched front-end
   {
     const int B = 5, W = 4, D = 3, N = 256;

@@ -236,6 +236,10 @@ int32_t tpb_create(const tpb_config* cfg, tpb_engine** out) {
   if (cfg->num_dofs > 0 && cfg->max_waypoints < 1) return TPB_INVALID_ARGUMENT;
   // CHECK(options_.num_path_samples() >= 3), timeable_path_joint_spline.cc:45
   if (cfg->num_dofs > 0 && cfg->num_samples < 3) return TPB_INVALID_ARGUMENT;
+  if (cfg->cartesian) {
+    if (cfg->num_dofs < 1) return TPB_INVALID_ARGUMENT;
+    if (2 * cfg->num_dofs + 2 > tpb::kMaxRows) return TPB_OUT_OF_RANGE;
+  }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     cudaGetLastError();
@@ -256,11 +260,7 @@ int32_t tpb_create(const tpb_config* cfg, tpb_engine** out) {
   d.max_points = (d.D > 0) ? std::max(3 * d.Wmax - 2, 4) : 0;
   d.N = cfg->num_samples;
   d.Cmax = cfg->max_constraints;
-  if (cfg->cartesian) {
-    if (cfg->num_dofs < 1) return TPB_INVALID_ARGUMENT;
-    if (2 * cfg->num_dofs + 2 > tpb::kMaxRows) return TPB_OUT_OF_RANGE;
-    d.Cmax = std::max(d.Cmax, 2 * cfg->num_dofs + 2);
-  }
+  if (cfg->cartesian) d.Cmax = std::max(d.Cmax, 2 * cfg->num_dofs + 2);
   d.r_cap = (d.D > 0) ? cfg->max_time_samples_total : 0;
   const size_t B = d.Bmax, N = d.N, D = d.D;
   auto& a = e->a;

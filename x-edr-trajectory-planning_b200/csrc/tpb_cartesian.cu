@@ -142,7 +142,7 @@ __global__ void k_cart_fit(Dims dm, DeviceArrays a, double rotation_rounding,
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= dm.B) return;
   const int D = dm.D;
-  const int W = a.num_wp[b];
+  const int W = min(max(a.num_wp[b], 1), dm.Wmax);  // see k_joint_fit
   const double* jwp = a.waypoints + static_cast<size_t>(b) * dm.Wmax * D;
   const double* pwp = a.pose_wp + static_cast<size_t>(b) * dm.Wmax * 7;
   double* jc = a.ctrl + static_cast<size_t>(b) * dm.max_points * D;

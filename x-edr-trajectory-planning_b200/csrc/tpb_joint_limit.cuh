@@ -31,6 +31,28 @@
 // (bound -hX < 0 over B >= 0) can never become active either.
 #pragma once
 
+// Code size: k_joint_sample_limit<7> is 60+ KB of straight-line code against a 32 KB
+// instruction cache level, and a third of its stall samples are instruction fetch
+// (profiles/r2_summary.md).  Measured variants (cfg2, ms per launch):
+//   TPB_SL_ROLL_W 0  everything unrolled                       67.7 KB, 122 regs  1.402
+//   TPB_SL_ROLL_W 1  the two bounds of a row share one copy of
+//                    the candidate test in FindSddMax / Min    62.0 KB, 124 regs  1.296  <- default
+//   TPB_SL_ROLL_W 2  + the same in the LP's vertex scan        60.5 KB, 128 regs  1.390
+//   TPB_SL_ROLL_W 3  + entry() not inlined                     59.6 KB, 128 regs  1.397
+//   TPB_SL_ROLL_ROWS 1  per-row loops not unrolled, rows in
+//                    local memory                              33.2 KB,  90 regs  1.616
+#ifndef TPB_SL_ROLL_W
+#define TPB_SL_ROLL_W 1
+#endif
+#ifndef TPB_SL_ROLL_ROWS
+#define TPB_SL_ROLL_ROWS 0
+#endif
+#if TPB_SL_ROLL_ROWS
+#define TPB_ROW_LOOP _Pragma("unroll 1")
+#else
+#define TPB_ROW_LOOP _Pragma("unroll")
+#endif
+
 #include "tpb_device.cuh"
 
 namespace tpb {
@@ -71,6 +93,9 @@ struct JointLimit {
 
   template <int kN>
   __device__ __forceinline__ static double sel(const double (&x)[kN], int i) {
+#if TPB_SL_ROLL_ROWS
+    return x[i];
+#endif
     double r = x[0];
 #pragma unroll
     for (int k = 1; k < kN; ++k) r = (i == k) ? x[k] : r;
@@ -78,7 +103,11 @@ struct JointLimit {
   }
 
   // row data by slot (slow paths only)
+#if TPB_SL_ROLL_W > 2
+  __device__ __noinline__ LpEntry entry(int slot) const {
+#else
   __device__ LpEntry entry(int slot) const {
+#endif
     const int row = slot >> 1;
     const bool lower = slot & 1;
     LpEntry e;
@@ -106,9 +135,9 @@ struct JointLimit {
 
   // (with kX > 0 the caller sets Bv[kD ..] before this)
   __device__ __forceinline__ void prepare() {
-#pragma unroll
+    TPB_ROW_LOOP
     for (int d = 0; d < kD; ++d) Bv[d] = A[d] * A[d];
-#pragma unroll
+    TPB_ROW_LOOP
     for (int d = 0; d < kV; ++d) {
       // only used where Bv >= kTiny (rows with |Bc| < kTiny are skipped)
       invBv[d] = 1.0 / ((Bv[d] < kTiny) ? 1.0 : Bv[d]);
@@ -128,7 +157,7 @@ struct JointLimit {
     last.slot = 0;
 
     // Step 2: walk along sdd = 0.
-#pragma unroll
+    TPB_ROW_LOOP
     for (int d = 0; d < kD; ++d) {
       const double Bi = B[d];
       const bool up = Bi > kTiny, dn = Bi < -kTiny;
@@ -147,7 +176,7 @@ struct JointLimit {
         last.slot = slot;
       }
     }
-#pragma unroll
+    TPB_ROW_LOOP
     for (int d = 0; d < kV; ++d) {
       const double Bi = Bv[d];
       const double tmp = vhi(d) * invBv[d];
@@ -215,14 +244,18 @@ struct JointLimit {
       // Step 4: next vertex along sdd = a + b * sd2.
       act = 0u;
       double next_sd2 = DBL_MAX, next_sdd = 0.0;
-#pragma unroll
+      TPB_ROW_LOOP
       for (int d = 0; d < kD; ++d) {
         const double Ac = A[d];
         const double Bc = Ac * b + B[d];
         const bool usable = !(fabs(Bc) < kTiny);
         const double invB = 1.0 / (usable ? Bc : 1.0);
         const double Aca = Ac * a;
+#if TPB_SL_ROLL_W > 1 || TPB_SL_ROLL_ROWS
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
         for (int w = 0; w < 2; ++w) {  // upper slot first, then lower (slot order)
           const int slot = 2 * d + w;
           const double bound = w ? -aS[d] : aS[d];
@@ -240,7 +273,7 @@ struct JointLimit {
         }
       }
       const double zb = 0.0 * b, za = 0.0 * a;
-#pragma unroll
+      TPB_ROW_LOOP
       for (int d = 0; d < kV; ++d) {
         const double Bc = zb + Bv[d];
         const bool usable = !(fabs(Bc) < kTiny);
@@ -330,11 +363,15 @@ struct JointLimit {
       vbad = vbad || (w + kTiny < vlo(d)) || (w - kTiny > vhi(d));
     }
     double mx = -DBL_MAX, mn = DBL_MAX;
-#pragma unroll
+    TPB_ROW_LOOP
     for (int i = 0; i < kD; ++i) {
       const double Ai = A[i];
       const bool has = !is_tiny(Ai);
+#if TPB_SL_ROLL_W || TPB_SL_ROLL_ROWS
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
       for (int w = 0; w < 2; ++w) {
         const double cand = ((w == 0 ? -aS[i] : aS[i]) - Bs[i]) / (has ? Ai : 1.0);
         // velocity rows: 0*cand + B*sd2 is NaN (passes) for a non-finite candidate

@@ -37,7 +37,9 @@ __global__ void k_joint_fit(Dims dm, DeviceArrays a, double rounding, bool auto_
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= dm.B) return;
   const int D = dm.D;
-  const int W = a.num_wp[b];
+  // counts that arrive in device memory cannot be range-checked by the host: clamped, so
+  // that a bad one stays inside this path's slabs
+  const int W = min(max(a.num_wp[b], 1), dm.Wmax);
   const double* wp = a.waypoints + static_cast<size_t>(b) * dm.Wmax * D;
   double* c = a.ctrl + static_cast<size_t>(b) * dm.max_points * D;
   double* kn = a.knots + static_cast<size_t>(b) * (dm.max_points + 3);
@@ -169,6 +171,10 @@ k_joint_sample_limit_any(Dims dm, DeviceArrays a, double safety) {
 // each CTA writes its 128 consecutive [sample][D] rows as contiguous runs.
 // 4 CTAs/SM (<= 128 registers: 124 used, no spills) measured best: 1.42 ms against 1.54 ms
 // unconstrained (140 registers, 3 CTAs/SM) and 1.46 ms at 5 CTAs/SM (96 registers, spills)
+// 1: __syncthreads() between the sampling, LP and FindSdd phases (A/B: instruction cache)
+#ifndef TPB_SL_PHASE_SYNC
+#define TPB_SL_PHASE_SYNC 0
+#endif
 #ifndef TPB_SL_MINBLOCKS
 #define TPB_SL_MINBLOCKS 4
 #endif
@@ -292,8 +298,16 @@ k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
     // ConstraintSetup (:320-343) + CalculateBoundary's per-sample part
     // (time_optimal_path_timing.cc:1366-1377); rows never leave the registers.
     J.prepare();
-    double sd2max, sddmax, sd2zero, smax, smin;
-    J.lp(sd2max, sddmax, sd2zero);
+  }
+#if TPB_SL_PHASE_SYNC
+  __syncthreads();  // the CTA's warps enter the LP together (one region of code at a time)
+#endif
+  double sd2max = 0.0, sddmax = 0.0, sd2zero = 0.0, smax = 0.0, smin = 0.0;
+  if (live) J.lp(sd2max, sddmax, sd2zero);
+#if TPB_SL_PHASE_SYNC
+  __syncthreads();
+#endif
+  if (live) {
     J.sdd_min_max(sd2max, smax, smin);
     const size_t o = static_cast<size_t>(b) * dm.N + idx;
     a.b_raw_sd2_max[o] = sd2max;

@@ -109,9 +109,13 @@ class PathTimingTrajectory : public TrajectoryPlanner {
     int32_t rc = TPB_OK;
     if (state == TimeablePath::State::kNewPath) {
       const tp::VectorXd& v0 = path_->GetInitialVelocity();
-      if (initial_plan_ && device_planner_ == e) {
+      const bool same_engine =
+          device_planner_ == e && device_planner_generation_ == path_->DeviceEngineGeneration();
+      if (initial_plan_ && same_engine) {
         rc = tpb_planner_new_path(e, v0.data(), 0);  // the plan so far stays (no Reset())
       } else {
+        // a new engine (more waypoints than the old one held) starts from an empty plan
+        if (initial_plan_) initial_plan_ = false;
         const size_t cap = path_sample_capacity_ ? path_sample_capacity_ : 64 * options_.GetNumPathSamples();
         rc = tpb_planner_reset(e, static_cast<int32_t>(cap), time_step_sec_, skipping ? 1 : 0,
                                options_.GetMaxPlanningIterations(),
@@ -119,10 +123,11 @@ class PathTimingTrajectory : public TrajectoryPlanner {
       }
       if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
       device_planner_ = e;
+      device_planner_generation_ = path_->DeviceEngineGeneration();
     } else if (state == TimeablePath::State::kModifiedPath) {
       // SwitchToWaypointPath marked the path on the device; the initial velocity set
       // since (SetInitialVelocity) goes to the planner now (.cc:352-385)
-      if (device_planner_ != e) {
+      if (device_planner_ != e || device_planner_generation_ != path_->DeviceEngineGeneration()) {
         return tp::FailedPreconditionError("the path was modified, but never planned by this planner");
       }
       rc = tpb_planner_set_initial_velocity(e, path_->GetInitialVelocity().data(), 0);
@@ -516,6 +521,7 @@ class PathTimingTrajectory : public TrajectoryPlanner {
   std::vector<double> time_at_path_samples_;
   size_t path_sample_capacity_ = 0;
   tpb_engine* device_planner_ = nullptr;  // the engine that holds this planner's state
+  uint64_t device_planner_generation_ = 0;
   int last_plan_windows_ = 0;
   int last_extremal_ = 0;  // of the window held by the engine (PlanOneWindow)
 };

@@ -4,6 +4,7 @@
 #ifndef TRAJECTORY_PLANNING_TIMEABLE_PATH_H_
 #define TRAJECTORY_PLANNING_TIMEABLE_PATH_H_
 
+#include <cstdint>
 #include <type_traits>
 #include <vector>
 
@@ -97,6 +98,10 @@ class TimeablePath {
   virtual bool SupportsDevicePlanner() const { return false; }
   virtual tp::Status BeforeDevicePlan() { return tp::OkStatus(); }
   virtual tp::Status AfterDevicePlan(bool /*window_was_sampled*/) { return tp::OkStatus(); }
+  // Counts the engines DeviceEngine() has returned over the object's life: a planner that
+  // keeps state on an engine tells a re-created engine from the one it planned on even
+  // when the allocator hands the same address back.
+  virtual uint64_t DeviceEngineGeneration() const { return 0; }
   // the Status a user callback returned during the device plan (Ok if none failed)
   virtual tp::Status TakeCallbackStatus() { return tp::OkStatus(); }
 };

@@ -438,6 +438,7 @@ class TimeableCartesianSplinePath : public TimeablePath {
   const std::vector<tp::VectorXd>& GetJointControlPoints() const { return joint_control_points_; }
   const std::vector<double>& GetKnots() const { return knots_; }
   tpb_engine* DeviceEngine() override { return e_; }
+  uint64_t DeviceEngineGeneration() const override { return engine_generation_; }
 
  private:
   // FitSplineToWaypoints (.cc:396-462) on the device.
@@ -460,6 +461,7 @@ class TimeableCartesianSplinePath : public TimeablePath {
         return tp::FromCode(rc, "tpb_create failed (no CUDA device; there is no CPU fallback)");
       }
       wcap_ = cfg.max_waypoints;
+      ++engine_generation_;
     }
     std::vector<double> jflat(static_cast<size_t>(wcap_) * D, 0.0), pflat(static_cast<size_t>(wcap_) * 7, 0.0);
     for (int w = 0; w < W; ++w) {
@@ -525,6 +527,7 @@ class TimeableCartesianSplinePath : public TimeablePath {
   int device_ = 0;
   tpb_engine* e_ = nullptr;
   int wcap_ = 0;
+  uint64_t engine_generation_ = 0;
   State path_state_ = State::kNoPath;
   std::vector<tp::VectorXd> joint_waypoints_, joint_control_points_;
   std::vector<tp::Pose3d> pose_waypoints_, pose_control_points_;

@@ -70,6 +70,7 @@ class TimeableJointSplinePath : public TimeablePath {
         return tp::FromCode(rc, "tpb_create failed (no CUDA device; there is no CPU fallback)");
       }
       wcap_ = cfg.max_waypoints;
+      ++engine_generation_;
     }
     std::vector<double> flat(static_cast<size_t>(wcap_) * D, 0.0);
     for (int w = 0; w < W; ++w) std::copy(waypoints_[w].begin(), waypoints_[w].end(), flat.begin() + w * D);
@@ -285,6 +286,7 @@ class TimeableJointSplinePath : public TimeablePath {
   const std::vector<double>& GetKnots() const { return knots_; }
   tpb_engine* engine() { return e_; }
   tpb_engine* DeviceEngine() override { return e_; }
+  uint64_t DeviceEngineGeneration() const override { return engine_generation_; }
 
  private:
   static constexpr int kSplineOrder = 2;  // .h:89
@@ -293,6 +295,7 @@ class TimeableJointSplinePath : public TimeablePath {
   int device_ = 0;
   tpb_engine* e_ = nullptr;
   int wcap_ = 0;
+  uint64_t engine_generation_ = 0;
   State path_state_ = State::kNoPath;
   std::vector<tp::VectorXd> waypoints_, control_points_;
   std::vector<tp::VectorXd> path_position_, first_path_derivative_, second_path_derivative_;
