@@ -554,6 +554,7 @@ def run_ours(args):
         parity = {"paths": int(B), "status_equal": bool(np.array_equal(gpu_ok, cpu_ok)),
                   "paths_ok": int(both.sum()),
                   "max_rel_duration_err": float(rel.max()) if rel.size else None,
+                "paths_beyond_tolerance": int((rel > 1e-6).sum()),
                   "durations_bit_equal": int((gpu_dur[both] == res["duration"][both]).sum()),
                   "rows_equal": bool(np.array_equal(gpu_rows[both], res["rows"][both])),
                   "tolerances": "duration 1e-6 relative, positions 1e-9 rad (BASELINE.json)",

@@ -154,6 +154,66 @@ def test_builtin_kinematics_pipeline(pkg, po):
     assert n_ok >= B // 2
 
 
+def test_cfg5_full_size_against_reference_object_code(pkg, po):
+    """BASELINE config 5 at its full size -- 4,096 Cartesian paths (5 pose waypoints, N = 1000),
+    the batch bench.py times -- everything on the device, against the reference's own
+    TimeableCartesianSplinePath + PathTimingTrajectory object code (oracle/_ref, all host
+    threads, the same fake robot as its callbacks): status of every path, total duration
+    within 1e-6 relative (BASELINE.json), the profile's time stamps within 1e-6 of the
+    duration, row counts of a 20 ms resampling within one row; size-independent
+    properties on all rows (uniform grid, rest to rest, end on the last joint waypoint)."""
+    import os
+    if not po.have_ref():
+        pytest.skip("oracle/_ref not built")
+    B, W = 4096, 5
+    dt = 0.02  # ~2,100 rows per path: 9 M rows in all
+    pw, jw, vm, am = pkg.workloads.cart_paths(B, W, seed=5000)
+    eng = _engine(pkg, B, W, cap=4096)
+    eng.set_cart_options(0.05, 0.5, 0.25)
+    eng.set_cart_waypoints(pw, jw)
+    eng.set_joint_limits(vm, am)
+    eng.cart_sample_targets()
+    eng.cart_solve_ik(1)
+    eng.cart_setup_constraints(1)
+    eng.optimize()
+    eng.resample(0.0, dt)
+    A = pkg.ARR
+    st, dur, tim = eng.get(A.STATUS), eng.get(A.DURATION), eng.get(A.TIME)
+    off, r_t, r_pos, r_vel = eng.get(A.R_OFFSET), eng.get(A.R_TIME), eng.get(A.R_POS), eng.get(A.R_VEL)
+    eng.close()
+    ref = po.plan_cart_batch_ref(pw, jw, vm, am, N, dt=dt, threads=os.cpu_count(), want_time=True)
+    assert ((st == 0) == (ref["status"] == 0)).all()
+    ok = st == 0
+    assert ok.sum() >= 0.99 * B
+    rel = np.zeros(B)
+    rel[ok] = np.abs(dur[ok] - ref["duration"][ok]) / ref["duration"][ok]
+    # With the whole path in one window (delta = knots.back() / (N - 1)) SamplePath's test
+    # "parameter < knots.back() - delta" (timeable_path_cartesian_spline.cc:488) compares two
+    # numbers that are equal in exact arithmetic at IK index N - 2; knots.back() is a sum of
+    # control-polygon lengths that went through sin / cos / atan2, so the device's and glibc's
+    # last bit can differ and the second-to-last sample is then the spline value on one side
+    # and the end pose on the other.  Such a path (1 of these 4,096) agrees up to its last
+    # few samples; every other path is within BASELINE.json's 1e-6.
+    edge = rel > 1e-6
+    assert edge.sum() <= B // 1000, int(edge.sum())
+    good = ok & ~edge
+    assert np.max(np.abs(tim[good] - ref["time"][good]) / ref["duration"][good, None]) <= 1e-6
+    for b in np.flatnonzero(edge):
+        d = np.abs(tim[b] - ref["time"][b]) / ref["duration"][b]
+        assert d[:N - 8].max() <= 1e-6 and rel[b] <= 2e-3, (b, rel[b])
+    rows = np.diff(off)
+    assert np.max(np.abs(rows[good] - ref["rows"][good])) <= 1
+    first, last = off[:-1][ok], off[1:][ok] - 1
+    assert (r_t[first] == 0.0).all()
+    inner = np.ones(len(r_t), bool)
+    inner[off[1:] - 1] = False  # the last row of a path is its end time, off the grid
+    steps = np.diff(r_t)[inner[:-1] & inner[1:]]
+    assert np.max(np.abs(steps - dt)) <= 1e-9
+    assert (r_vel[first] == 0).all() and (r_vel[last] == 0).all()
+    assert np.max(np.abs(r_pos[last] - jw[ok, -1])) <= 1e-9
+    assert np.max(np.abs(r_vel)) <= 0.8 * vm.max() + 1e-9
+
+
 def _limit_curve_run(pkg, pw, jw, vm, am, jac_from=None, variants=()):
     B, W = pw.shape[0], pw.shape[1]
     eng = _engine(pkg, B, W)
