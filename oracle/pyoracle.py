@@ -591,7 +591,7 @@ class Planner:
         cart = {}
         if pose_waypoints is not None:
             self._pose_wp = np.ascontiguousarray(pose_waypoints, np.float64)
-            self._pose_ctrl = np.zeros((n, 7))
+            self._pose_ctrl = np.zeros((cap - 3, 7))
             cart = dict(cart=1, translation_rounding=translation_rounding,
                         max_translational_velocity=max_translational_velocity,
                         max_rotational_velocity=max_rotational_velocity,
@@ -614,11 +614,19 @@ class Planner:
         """Plan(start, horizon); returns the ORC_* status."""
         return lib().orc_planner_plan(C.byref(self.c), int(start_ns), int(horizon_ns))
 
-    def switch(self, keep_path_until, waypoints, initial_velocity=None):
+    def switch(self, keep_path_until, waypoints, initial_velocity=None, pose_waypoints=None):
         """SwitchToWaypointPath (+ SetInitialVelocity); returns the absl status code."""
         wp = np.ascontiguousarray(waypoints, np.float64)
         if initial_velocity is not None:
             self._keep["initial_velocity"][:] = initial_velocity
+        if pose_waypoints is not None:
+            pw = np.ascontiguousarray(pose_waypoints, np.float64)
+            L = lib()
+            L.orc_planner_cart_switch.restype = C.c_int
+            L.orc_planner_cart_switch.argtypes = [C.POINTER(_Planner), C.c_double, c_double_p,
+                                                  c_double_p, C.c_int]
+            return L.orc_planner_cart_switch(C.byref(self.c), float(keep_path_until), _dp(pw),
+                                             _dp(wp), wp.shape[0])
         return lib().orc_planner_switch(C.byref(self.c), float(keep_path_until), _dp(wp),
                                         wp.shape[0])
 

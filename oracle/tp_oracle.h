@@ -316,6 +316,13 @@ int orc_planner_plan(orc_planner* p, int64_t start_ns, int64_t horizon_ns);
 /* SwitchToWaypointPath on the planner's path (SetInitialVelocity = write through the
  * initial_velocity pointer); returns an absl::StatusCode number. */
 int orc_planner_switch(orc_planner* p, double keep_path_until, const double* waypoints, int W);
+/* TimeableCartesianSplinePath::SwitchToWaypointPath (timeable_path_cartesian_spline.cc:183-296);
+ * pose_ctrl [joint->knot_capacity - 3][7].  tp_oracle_cart.c */
+int orc_cart_switch(orc_spline* joint, double* pose_ctrl, double keep_path_until,
+                    const double* pose_waypoints, const double* joint_waypoints, int W,
+                    double translation_rounding, double rotation_rounding);
+int orc_planner_cart_switch(orc_planner* p, double keep_path_until, const double* pose_waypoints,
+                            const double* joint_waypoints, int W);
 
 #ifdef __cplusplus
 }

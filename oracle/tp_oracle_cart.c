@@ -638,3 +638,216 @@ int orc_plan_cart_fake(const orc_cart_cfg* cfg, const double* pose_wp, const dou
   free(cons);
   return st;
 }
+
+/* ---------------------------------------------------------------- online re-planning
+ * TimeableCartesianSplinePath::SwitchToWaypointPath (timeable_path_cartesian_spline.cc:
+ * 183-296) over the joint, translation and rotation splines:
+ *   BSplineQ::InsertKnotAndUpdateControlPoints (degree <= 2: slerp of neighbouring control
+ *     quaternions, splines/bsplineq.cc:355-431), TruncateSplineAt (:497-519),
+ *     ExtendWithControlPoints (:521-587)
+ *   BSplineT<Vector3d / VectorXd>::TruncateSplineAt / ExtendWithControlPoints: orc_spline_*
+ *     (tp_oracle_switch.c; closed-form knot insertion where the reference solves a small
+ *     system by QR -- same curve, control points to rounding, see that file's header)
+ * The three splines keep knot vectors of their own in the reference; they stay equal, so one
+ * is kept here (the joint spline's) and the other two work on copies of it. */
+static void quat_slerp(const double* a, double t, const double* b, double* out) {
+  const double one = 1.0 - DBL_EPSILON;
+  const double d = a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3];
+  const double abs_d = fabs(d);
+  double scale0, scale1;
+  if (abs_d >= one) {
+    scale0 = 1.0 - t;
+    scale1 = t;
+  } else {
+    const double theta = acos(abs_d);
+    const double sin_theta = sin(theta);
+    scale0 = sin((1.0 - t) * theta) / sin_theta;
+    scale1 = sin(t * theta) / sin_theta;
+  }
+  if (d < 0.0) scale1 = -scale1;
+  for (int i = 0; i < 4; ++i) out[i] = scale0 * a[i] + scale1 * b[i];
+}
+
+typedef struct {
+  int knot_capacity, num_knots, num_points;
+  double* knots; /* [knot_capacity] */
+  double* quats; /* [knot_capacity - 3][4] */
+} qspline;
+
+/* one insertion, degree 2 (bsplineq.cc:355-431) */
+static void qspline_insert_knot(qspline* s, double knot) {
+  const int p = 2;
+  double scratch[2][4];
+  const int span = orc_knot_span(s->knots, s->num_knots, p, knot);
+  for (int i = 0; i < p; ++i) {
+    const int k = span + i - p + 1;
+    const double alpha = (knot - s->knots[k]) / (s->knots[k + p] - s->knots[k]);
+    quat_slerp(s->quats + 4 * (k - 1), alpha, s->quats + 4 * k, scratch[i]);
+  }
+  memmove(s->knots + span + 2, s->knots + span + 1,
+          sizeof(double) * (size_t)(s->num_knots - span - 1));
+  s->knots[span + 1] = knot;
+  s->num_knots += 1;
+  /* copy_backward(points + span, points + old_count, points + old_count + 1) */
+  memmove(s->quats + 4 * (span + 1), s->quats + 4 * span,
+          sizeof(double) * 4 * (size_t)(s->num_points - span));
+  s->num_points += 1;
+  memcpy(s->quats + 4 * (span - p + 1), scratch, sizeof(scratch));
+}
+
+static int qspline_truncate(qspline* s, double u_end) {
+  const int p = 2;
+  if (s->num_knots == 0) return 0;
+  if (u_end >= s->knots[s->num_knots - 1]) return 0;
+  if (u_end <= s->knots[0]) {
+    s->num_knots = 0;
+    s->num_points = 0;
+    return 0;
+  }
+  /* CanInsertKnot (bspline_base.cc:166-195) */
+  if (s->num_knots + p + 1 > s->knot_capacity) return 9;
+  for (int i = 0; i < p + 1; ++i) qspline_insert_knot(s, u_end);
+  const int span = orc_knot_span(s->knots, s->num_knots, p, u_end);
+  s->num_knots = span + 1;
+  s->num_points = s->num_knots - p - 1;
+  return 0;
+}
+
+static int qspline_extend(qspline* s, const double* quats, int n) {
+  const int p = 2;
+  const int new_num_points = s->num_points + n;
+  const int added_knots = (n + 1 + p + 1) - 2 * p;
+  const int new_num_knots = s->num_knots + added_knots;
+  if (new_num_points > s->knot_capacity - p - 1) return 9;
+  if (new_num_knots > s->knot_capacity) return 9;
+  if (n < 2) return 12;
+  const double u_join = s->knots[s->num_knots - 1];
+  double quat_join[4] = {0, 0, 0, 1};
+  orc_quat_eval_curve(s->knots, s->num_knots, s->quats, p, u_join, quat_join); /* IgnoreError */
+  const double old_knot_range = s->knots[s->num_knots - 1] - s->knots[0];
+  const int old_inner = s->num_knots - 2 * p - 1;
+  const int new_inner = new_num_knots - 2 * p - 1;
+  const double new_knot_range = (old_knot_range * new_inner) / old_inner;
+  const int start = s->num_knots - p - 1;
+  const int size = (new_num_knots - p) - start;
+  {
+    const double low = old_knot_range, high = new_knot_range;
+    const int size1 = (size == 1) ? 1 : size - 1;
+    const double step = (size == 1) ? 0.0 : (high - low) / (double)(size - 1);
+    for (int i = 0; i < size; ++i) s->knots[start + i] = (i == size1) ? high : low + (double)i * step;
+  }
+  for (int i = 0; i < p + 1; ++i) s->knots[new_num_knots - p - 1 + i] = s->knots[0] + new_knot_range;
+  s->num_knots = new_num_knots;
+  const int imod = s->num_points - 1;
+  const int span = orc_knot_span(s->knots, s->num_knots, p, u_join);
+  double basis[3];
+  orc_basis(s->knots, span, p, u_join, basis);
+  const double cum0 = basis[2] + basis[1]; /* cumulative_basis_[0] (:309-317) */
+  if (!(cum0 > 0.0)) return 13;            /* CHECK_GT in the reference */
+  double inv[4], rel[4], lg[4], ex[4], np_[4];
+  quat_inverse(s->quats + 4 * (imod - 1), inv);
+  orc_quat_mul(inv, quat_join, rel);
+  orc_quat_log(rel, lg);
+  for (int i = 0; i < 4; ++i) lg[i] /= cum0;
+  if (lg[3] < 0) {
+    for (int i = 0; i < 4; ++i) lg[i] *= -1.0;
+  }
+  orc_quat_exp(lg, ex);
+  orc_quat_mul(s->quats + 4 * (imod - 1), ex, np_);
+  memcpy(s->quats + 4 * imod, np_, sizeof(np_));
+  memcpy(s->quats + 4 * s->num_points, quats, sizeof(double) * 4 * (size_t)n);
+  s->num_points = new_num_points;
+  return 0;
+}
+
+/* joint: the joint spline (knots + joint control points); pose_ctrl [knot_capacity - 3][7]:
+ * control points of the translation / rotation splines.  Returns an absl::StatusCode number.
+ * Scratch is sized for ORC_MAX_SWITCH_WAYPOINTS new waypoints and joint->knot_capacity. */
+int orc_cart_switch(orc_spline* joint, double* pose_ctrl, double keep_path_until,
+                    const double* pose_waypoints, const double* joint_waypoints, int W,
+                    double translation_rounding, double rotation_rounding) {
+  const int D = joint->dim, cap = joint->knot_capacity, pcap = cap - 3;
+  if (W > ORC_MAX_SWITCH_WAYPOINTS) return 3;
+  double* tk = (double*)malloc(sizeof(double) * (size_t)cap * 2);
+  double* rk = tk + cap;
+  double* tp = (double*)malloc(sizeof(double) * (size_t)pcap * 7);
+  double* rq = tp + (size_t)pcap * 3;
+  memcpy(tk, joint->knots, sizeof(double) * (size_t)cap);
+  memcpy(rk, joint->knots, sizeof(double) * (size_t)cap);
+  for (int i = 0; i < joint->num_points; ++i) {
+    memcpy(tp + 3 * i, pose_ctrl + 7 * i, sizeof(double) * 3);
+    memcpy(rq + 4 * i, pose_ctrl + 7 * i + 3, sizeof(double) * 4);
+  }
+  orc_spline ts = {2, 3, cap, joint->num_knots, joint->num_points, tk, tp};
+  qspline rs = {cap, joint->num_knots, joint->num_points, rk, rq};
+  int st = orc_spline_truncate(joint, keep_path_until);
+  if (st == 0) st = qspline_truncate(&rs, keep_path_until);
+  if (st == 0) st = orc_spline_truncate(&ts, keep_path_until);
+  double jsw[64], qsw[4] = {0, 0, 0, 1}, tsw[3] = {0, 0, 0};
+  if (st == 0 && joint->num_knots == 0) st = 11; /* EvalCurve on a cleared curve */
+  if (st == 0)
+    st = orc_eval_curve(joint->knots, joint->num_knots, joint->points, D, 2, keep_path_until, jsw);
+  if (st == 0) st = orc_quat_eval_curve(rs.knots, rs.num_knots, rs.quats, 2, keep_path_until, qsw);
+  if (st == 0) st = orc_eval_curve(ts.knots, ts.num_knots, ts.points, 3, 2, keep_path_until, tsw);
+  double jproj[64], tproj[3], jdist = 0, jt = 0, tdist = 0, tt = 0;
+  int jidx = 0, tidx = 0;
+  if (st == 0)
+    st = orc_project_point_on_path(joint_waypoints, W, D, jsw, &jidx, &jdist, &jt, jproj);
+  double twp[ORC_MAX_SWITCH_WAYPOINTS * 3];
+  for (int i = 0; i < W; ++i) memcpy(twp + 3 * i, pose_waypoints + 7 * i, sizeof(double) * 3);
+  if (st == 0) st = orc_project_point_on_path(twp, W, 3, tsw, &tidx, &tdist, &tt, tproj);
+  double njw[(ORC_MAX_SWITCH_WAYPOINTS + 1) * 64], npw[(ORC_MAX_SWITCH_WAYPOINTS + 1) * 7];
+  int n = 0;
+  if (st == 0) {
+    double linf = 0.0;
+    for (int d = 0; d < 3; ++d) {
+      const double e = fabs(tsw[d] - tproj[d]);
+      if (e > linf) linf = e;
+    }
+    if (linf > 1e-3) { /* kEpsilon */
+      if (tidx + 1 >= W) {
+        st = 3; /* the reference would read pose_waypoints[W] */
+      } else {
+        memcpy(njw, jproj, sizeof(double) * (size_t)D);
+        memcpy(npw, tproj, sizeof(double) * 3);
+        quat_slerp(pose_waypoints + 7 * tidx + 3, tt, pose_waypoints + 7 * (tidx + 1) + 3, npw + 3);
+        n = 1;
+      }
+    }
+  }
+  if (st == 0) {
+    const int first = (tt >= 0) ? tidx + 1 : tidx;
+    for (int i = first; i < W; ++i) {
+      memcpy(njw + (size_t)n * D, joint_waypoints + (size_t)i * D, sizeof(double) * (size_t)D);
+      memcpy(npw + (size_t)n * 7, pose_waypoints + (size_t)i * 7, sizeof(double) * 7);
+      ++n;
+    }
+    if (n == 0) st = 3; /* the reference would index an empty vector */
+  }
+  if (st == 0) {
+    const int ncmax = (n == 1) ? 4 : 3 * n - 2;
+    double* jc = (double*)malloc(sizeof(double) * (size_t)ncmax * (D + 7 + 3 + 4));
+    double* pc = jc + (size_t)ncmax * D;
+    double* tc = pc + (size_t)ncmax * 7;
+    double* qc = tc + (size_t)ncmax * 3;
+    const int nc = orc_polyline_to_bspline3(njw, n, D, rotation_rounding, jc);
+    orc_pose_polyline_to_bspline3(npw, n, translation_rounding, rotation_rounding, pc);
+    for (int i = 0; i < nc; ++i) {
+      memcpy(tc + 3 * i, pc + 7 * i, sizeof(double) * 3);
+      memcpy(qc + 4 * i, pc + 7 * i + 3, sizeof(double) * 4);
+    }
+    st = orc_spline_extend(joint, jc, nc);
+    if (st == 0) st = orc_spline_extend(&ts, tc, nc);
+    if (st == 0) st = qspline_extend(&rs, qc, nc);
+    free(jc);
+  }
+  /* the splines' control points as they stand, also after a failure */
+  const int np_out = (ts.num_points > rs.num_points) ? ts.num_points : rs.num_points;
+  for (int i = 0; i < np_out && i < pcap; ++i) {
+    if (i < ts.num_points) memcpy(pose_ctrl + 7 * i, tp + 3 * i, sizeof(double) * 3);
+    if (i < rs.num_points) memcpy(pose_ctrl + 7 * i + 3, rq + 4 * i, sizeof(double) * 4);
+  }
+  free(tk);
+  free(tp);
+  return st;
+}

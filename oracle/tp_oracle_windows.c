@@ -367,6 +367,19 @@ int orc_planner_plan(orc_planner* p, int64_t start, int64_t horizon) {
   return ORC_OK;
 }
 
+/* TimeableCartesianSplinePath::SwitchToWaypointPath on the planner's path (cart != 0;
+ * pose_ctrl must hold spline.knot_capacity - 3 rows).  The IK cache the reference trims
+ * (:188-192) does not exist here: the fake IK does not depend on its warm start. */
+int orc_planner_cart_switch(orc_planner* p, double keep_path_until, const double* pose_waypoints,
+                            const double* joint_waypoints, int W) {
+  p->sampled = 2; /* kModifiedPath */
+  const int st = orc_cart_switch(&p->spline, p->pose_ctrl, keep_path_until, pose_waypoints,
+                                 joint_waypoints, W, p->translation_rounding, p->rounding);
+  if (p->spline.num_knots > 0) p->knot_end = p->spline.knots[p->spline.num_knots - 1];
+  p->num_points = p->spline.num_points;
+  return st;
+}
+
 int orc_planner_switch(orc_planner* p, double keep_path_until, const double* waypoints, int W) {
   double new_ctrl[(3 * (ORC_MAX_SWITCH_WAYPOINTS + 1)) * 64];
   int n = 0;

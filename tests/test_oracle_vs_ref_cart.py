@@ -257,3 +257,109 @@ def test_random_cartesian_paths_long_horizon(seed):
     h = 3600 * 1000 * MS
     check_equal(port, ref, port.plan(0, h), ref.plan(0, h))
     assert port.target_reached
+
+
+# ---------------------------------------------------------------- online re-planning
+@pytest.mark.parametrize("skip", [False, True])
+def test_switch_to_new_cartesian_waypoint_path(skip):
+    """SwitchToNewCartesianWaypointPathWorks (_test.cc:764-920): plan until the motion is
+    fast, switch all three splines at the stop parameter with the current velocity, plan
+    to the end.  The joint and the translation spline are truncated through the shim's
+    restatement of Eigen's QR in the reference and through the closed form in the port
+    (knots bit for bit, control points 1e-12); the rotation spline's knot insertion is
+    slerp on both sides."""
+    joint = CART_WAYPOINTS
+    port, ref = cart_pair(joint, skip=skip)
+    start, tr = 0, None
+    for _ in range(200):
+        check_equal(port, ref, port.plan(start, HORIZON), ref.plan(start, HORIZON))
+        tr = port.trajectory()
+        start = min(port.end_time, max(start + REPLAN, port.start_time))
+        v = np.max(np.abs(tr["r_vel"][0]))
+        if v > 0.3 * 0.25:  # kFractionToStopAt of the smallest limit
+            break
+    assert not port.target_reached
+    new_joint = np.array([[-1.0] * 7, [1.0] * 7])
+    new_pose = np.stack([fake_fk_pose(q) for q in new_joint])
+    st_r, par = ref.stop_parameter(start)
+    assert st_r == 0
+    v0 = np.array([np.interp(start / 1e9, tr["r_t"], tr["r_vel"][:, d]) for d in range(7)])
+    assert port.switch(par, new_joint, initial_velocity=v0, pose_waypoints=new_pose) == 0
+    assert ref.switch(par, new_joint, initial_velocity=v0, pose_waypoints=new_pose) == 0
+    (kp, pp), (kr, pr) = port.spline(), ref.spline()
+    same_bits(kp, kr, "knots after the switch")
+    assert pp.shape == pr.shape
+    np.testing.assert_allclose(pp, pr, rtol=0, atol=1e-12)
+    poses_r = ref.pose_points()
+    poses_p = port._pose_ctrl[:len(poses_r)]
+    np.testing.assert_allclose(poses_p[:, :3], poses_r[:, :3], rtol=0, atol=1e-12)
+    np.testing.assert_allclose(poses_p[:, 3:], poses_r[:, 3:], rtol=0, atol=1e-12)
+    assert ref.state()["path_state"] == 2 and port.sampled == 2  # kModifiedPath
+    for _ in range(400):
+        st_p, st_r = port.plan(start, HORIZON), ref.plan(start, HORIZON)
+        assert st_p == orc.ORC_OK and st_r == 0
+        s = ref.state()
+        assert (port.len, port.target_reached) == (s["len"], s["target_reached"])
+        assert abs(port.M - s["M"]) <= 1 and abs(port.end_time - s["end_time"]) <= 4 * MS
+        tp, trr = port.trajectory(), ref.trajectory()
+        m = min(len(tp["r_t"]), len(trr["r_t"])) - 1
+        np.testing.assert_allclose(tp["r_t"][:m], trr["r_t"][:m], rtol=1e-6, atol=1e-9)
+        np.testing.assert_allclose(tp["r_pos"][:m], trr["r_pos"][:m], rtol=0, atol=1e-8)
+        start = min(port.end_time, max(start + REPLAN, port.start_time))
+        if port.target_reached:
+            break
+    assert port.target_reached
+    np.testing.assert_allclose(tp["r_pos"][-1], new_joint[-1], atol=1e-9)
+
+
+def test_cartesian_switch_geometry_random():
+    """Seeded switches on fresh fits: truncation points inside the path, two to five new
+    waypoints, repeated switches until the knot capacity is exhausted -- status and knots bit
+    for bit, control points of the joint and the translation spline within 1e-11 (QR in the
+    reference, closed form in the port).  The rotation spline agrees to 1e-9 except where the
+    reference's own end-point correction is decided by rounding noise:
+    BSplineQ::ExtendWithControlPoints negates the whole logarithm of a relative rotation when
+    its real part -- 0.5 log |q|^2 / B, i.e. +-1e-16 for a unit quaternion -- is negative
+    (bsplineq.cc:573-577), which turns the correction into its inverse.  Port and reference
+    then pick the two alternatives whenever their inputs differ in the last bit (they do
+    after the first switch, through the translation spline); the test recognises that case
+    (relative rotations inverse to each other) and ends the trial there."""
+    rng = np.random.default_rng(11)
+    checked = flipped = 0
+    for trial in range(12):
+        W = int(rng.integers(2, 5))
+        joint = rng.uniform(-0.8, 0.8, (W, 7))
+        port, ref = cart_pair(joint, N=100, delta=0.01)
+        for rep in range(8):
+            kn, _ = ref.spline()
+            keep = float(rng.uniform(0.15, 0.9) * kn[-1])
+            Wn = int(rng.integers(2, 6))
+            nj = rng.uniform(-0.8, 0.8, (Wn, 7))
+            npz = np.stack([fake_fk_pose(q) for q in nj])
+            st_p = port.switch(keep, nj, pose_waypoints=npz)
+            st_r = ref.switch(keep, nj, pose_waypoints=npz)
+            assert st_p == st_r, (trial, rep, st_p, st_r)
+            if st_p != 0:
+                assert st_p == 9  # kFailedPrecondition: capacity
+                break
+            (kp, pp), (kr, pr) = port.spline(), ref.spline()
+            same_bits(kp, kr, ("knots", trial, rep))
+            np.testing.assert_allclose(pp, pr, rtol=0, atol=1e-11)
+            poses_r = ref.pose_points()
+            poses_p = port._pose_ctrl[:len(poses_r)]
+            assert len(poses_r) == len(pr)
+            np.testing.assert_allclose(poses_p[:, :3], poses_r[:, :3], rtol=0, atol=1e-11)
+            np.testing.assert_allclose(np.linalg.norm(poses_r[:, 3:], axis=1), 1.0, atol=1e-9)
+            bad = np.flatnonzero(np.abs(poses_p[:, 3:] - poses_r[:, 3:]).max(axis=1) > 1e-9)
+            checked += 1
+            if bad.size:
+                r = bad[0]  # the corrected end point of the kept part
+                assert bad.size == 1 and r >= 1
+                inv = lambda q: np.array([-q[0], -q[1], -q[2], q[3]])
+                rel_p = orc.quat_mul(inv(poses_p[r - 1, 3:]), poses_p[r, 3:])
+                rel_r = orc.quat_mul(inv(poses_r[r - 1, 3:]), poses_r[r, 3:])
+                both = orc.quat_mul(rel_p, rel_r)
+                assert np.max(np.abs(both[:3])) <= 1e-8 and abs(abs(both[3]) - 1.0) <= 1e-8
+                flipped += 1
+                break
+    assert checked >= 30 and flipped <= checked // 4
