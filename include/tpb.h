@@ -427,6 +427,21 @@ int32_t tpb_planner_set_initial_velocity(tpb_engine* e, const double* initial_ve
 int32_t tpb_switch_to_waypoint_path(tpb_engine* e, const double* keep_path_until,
                                     const int32_t* num_waypoints, const double* waypoints,
                                     const double* initial_velocity, int32_t on_device);
+/* TimeableCartesianSplinePath::SwitchToWaypointPath (timeable_path_cartesian_spline.cc:
+ * 183-296), same conventions: the joint, translation and rotation splines are truncated at
+ * keep_path_until[b] (the rotation spline's knot insertion is slerp of neighbouring control
+ * quaternions, splines/bsplineq.cc:355-431, 497-519), the switching joint position and
+ * translation are projected onto the new waypoints, the rotation of the projected first
+ * waypoint is the slerp of the two pose waypoints around it, the three control polygons are
+ * appended (BSplineQ::ExtendWithControlPoints :521-587 for the rotations) and the path
+ * becomes kModifiedPath.  pose_waypoints [B][max_waypoints][7] (tx,ty,tz,qx,qy,qz,qw),
+ * joint_waypoints [B][max_waypoints][num_dofs].  With user kinematics
+ * (tpb_planner_set_host_kinematics) the IK caches are cut at PathIkIndex(keep_path_until)
+ * like the reference's (:188-192).  Per-path status in TPB_ARR_SWITCH_STATUS. */
+int32_t tpb_switch_to_cart_waypoint_path(tpb_engine* e, const double* keep_path_until,
+                                         const int32_t* num_waypoints, const double* pose_waypoints,
+                                         const double* joint_waypoints,
+                                         const double* initial_velocity, int32_t on_device);
 
 /* Whole pipeline for a batch of fresh joint paths with HOST buffers in and out:
  * set waypoints+limits, sample, optimize, resample, copy back durations,

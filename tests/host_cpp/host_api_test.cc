@@ -604,6 +604,111 @@ int main() {
       PrintArray("velocities", Flatten(planner.GetVelocities()), false);
       printf("}\n");
     }
+    // SwitchToNewCartesianWaypointPathWorks (path_timing_trajectory_test.cc:764-920): plan
+    // until the motion is fast, switch the three splines to new waypoints at the stop
+    // parameter with the current velocity, plan to the end -- with device kinematics and
+    // with the user's callbacks (whose IK cache is cut at the switching index)
+    for (int mode = 0; mode < 2; ++mode) {
+      constexpr size_t kSamples = 1000;
+      int ik_calls = 0;
+      CartesianPathOptions opt;
+      opt.set_num_dofs(kFakeDofs).set_num_path_samples(kSamples).set_delta_parameter(0.005);
+      if (mode == 0) {
+        opt.set_device_kinematics(TPB_KIN_FAKE7);
+      } else {
+        opt.set_jacobian_func(FakeJacobian);
+        opt.set_path_ik_func([&](const VectorXd& initial_value, const std::vector<tp::Pose3d>& pose,
+                                 const std::vector<VectorXd>& joint, std::vector<VectorXd>* solution) {
+          ++ik_calls;
+          return FakePathIK(initial_value, pose, joint, solution);
+        });
+      }
+      auto cpath = std::make_shared<TimeableCartesianSplinePath>(opt);
+      PathTimingTrajectory planner(PathTimingTrajectoryOptions()
+                                       .SetTimeStep(tp::Milliseconds(4))
+                                       .SetNumDofs(kFakeDofs)
+                                       .SetNumPathSamples(kSamples)
+                                       .SetMaxInitialVelocityError(1e-2));
+      EXPECT(planner.SetPath(cpath).ok());
+      const std::vector<VectorXd> joints = {VectorXd{1.0, 0, 0, 0, 0, 0, 0}, VectorXd{0, 1.0, 0, 0, 0, 0, 0},
+                                            VectorXd{0, 0, 0, 1.0, 0, 0, 0}, VectorXd{0, 0, 0, 0, 1.0, 0, 0},
+                                            VectorXd{0, 0, 0, 0, 0, 0, 1.0}};
+      std::vector<tp::Pose3d> poses;
+      for (const auto& j : joints) poses.push_back(FakeFK(j));
+      EXPECT(cpath->SetWaypoints(poses, joints).ok());
+      VectorXd vmax = VectorXd::Constant(kFakeDofs, 1.0), amax = VectorXd::Constant(kFakeDofs, 2.0);
+      EXPECT(cpath->SetMaxJointVelocity(ToSpan(vmax)).ok());
+      EXPECT(cpath->SetMaxJointAcceleration(ToSpan(amax)).ok());
+      EXPECT(cpath->SetMaxCartesianVelocity(0.5, 0.25).ok());
+      tp::Time start_time = TimeFromSec(0.0);
+      int first_calls = 0;
+      for (; first_calls < 200; ++first_calls) {
+        const tp::Status st = planner.Plan(start_time, tp::Milliseconds(750));
+        EXPECT(st.ok());
+        if (!st.ok()) break;
+        start_time = planner.GetNextPlanStartTime(start_time + tp::Milliseconds(200));
+        double fastest = 0.0;
+        for (size_t d = 0; d < kFakeDofs; ++d) {
+          fastest = std::max(fastest, std::abs(planner.GetVelocities().front()[d]));
+        }
+        if (fastest > 0.3 * 0.25) break;
+      }
+      EXPECT(!planner.IsTrajectoryAtEnd());
+      const std::vector<VectorXd> new_joints = {VectorXd::Constant(kFakeDofs, -1.0),
+                                                VectorXd::Constant(kFakeDofs, 1.0)};
+      std::vector<tp::Pose3d> new_poses;
+      for (const auto& j : new_joints) new_poses.push_back(FakeFK(j));
+      auto stop = planner.GetPathStopParameter(start_time);
+      EXPECT(stop.ok());
+      const double stop_parameter = stop.ok() ? *stop : 0.0;
+      VectorXd v0(kFakeDofs);
+      {
+        const auto& t = planner.GetTime();
+        const double ts = TimeToSec(start_time);
+        size_t hi = 1;
+        while (hi + 1 < t.size() && t[hi] < ts) ++hi;
+        const double w = (ts - t[hi - 1]) / (t[hi] - t[hi - 1]);
+        for (size_t d = 0; d < kFakeDofs; ++d) {
+          v0[d] = planner.GetVelocities()[hi - 1][d] +
+                  w * (planner.GetVelocities()[hi][d] - planner.GetVelocities()[hi - 1][d]);
+        }
+      }
+      EXPECT(cpath->SwitchToWaypointPath(stop_parameter, new_poses, std::vector<VectorXd>{new_joints[0]}).code() ==
+             tp::StatusCode::kInvalidArgument);
+      const tp::Status sw = cpath->SwitchToWaypointPath(stop_parameter, new_poses, new_joints);
+      EXPECT(sw.ok());
+      if (!sw.ok()) fprintf(stderr, "Cartesian switch (mode %d): %s\n", mode, sw.message().c_str());
+      EXPECT(cpath->GetState() == TimeablePath::State::kModifiedPath);
+      EXPECT(cpath->SetInitialVelocity(ToSpan(v0)).ok());
+      const std::vector<double> knots_after = cpath->GetKnots();
+      const int ik_calls_before = ik_calls;
+      int second_calls = 0;
+      for (; !planner.IsTrajectoryAtEnd() && second_calls < 400; ++second_calls) {
+        const tp::Status st = planner.Plan(start_time, tp::Milliseconds(750));
+        EXPECT(st.ok());
+        if (!st.ok()) {
+          fprintf(stderr, "Cartesian Plan after switch %d (mode %d): %s\n", second_calls, mode,
+                  st.message().c_str());
+          break;
+        }
+        start_time = planner.GetNextPlanStartTime(start_time + tp::Milliseconds(200));
+      }
+      EXPECT(planner.IsTrajectoryAtEnd());
+      EXPECT(mode == 0 || ik_calls > ik_calls_before);
+      if (!planner.GetPositions().empty()) {
+        for (size_t d = 0; d < kFakeDofs; ++d) {
+          EXPECT(std::abs(planner.GetPositions().back()[d] - new_joints.back()[d]) < 1e-8);
+          EXPECT(std::abs(planner.GetVelocities().back()[d]) < 1e-10);
+        }
+      }
+      printf(",\"%s\": {\n\"first_calls\": %d, \"second_calls\": %d, \"stop_parameter\": %.17g,\n",
+             mode == 0 ? "switch" : "switch_host_callbacks", first_calls, second_calls, stop_parameter);
+      PrintArray("initial_velocity", std::vector<double>(v0.begin(), v0.end()));
+      PrintArray("knots_after_switch", knots_after);
+      PrintArray("time", planner.GetTime());
+      PrintArray("positions", Flatten(planner.GetPositions()), false);
+      printf("}\n");
+    }
     std::vector<double> jflat, pflat;
     for (size_t w = 0; w < jw.size(); ++w) {
       jflat.insert(jflat.end(), jw[w].begin(), jw[w].end());

@@ -319,3 +319,45 @@ def test_cartesian_replanning_matches_oracle(result, po, key):
                 assert ref.plan(start, TW.HORIZON) == 0
                 start = min(ref.state()["end_time"], start + TW.REPLAN)
             assert r["ik_samples"] == len(ref.ik_positions()) + windows
+
+
+@pytest.mark.parametrize("key", ["switch", "switch_host_callbacks"])
+def test_cartesian_switch_matches_oracle(result, po, key):
+    """SwitchToNewCartesianWaypointPathWorks (path_timing_trajectory_test.cc:764-920) through
+    the host classes -- device kinematics and the user's callbacks -- against the oracle
+    planner driven through the same sequence (== the reference's object code,
+    tests/test_oracle_vs_ref_cart.py): stop parameter, knots after the switch, number of
+    Plan() calls on both sides of the switch, the final trajectory."""
+    import test_oracle_windows as TW
+    r = result["cartesian"][key]
+    pl = TW.make_cart(TW.CART_WAYPOINTS)
+    start, tr = 0, None
+    for first_calls in range(200):
+        assert pl.plan(start, TW.HORIZON) == po.ORC_OK
+        tr = pl.trajectory()
+        start = min(pl.end_time, max(start + TW.REPLAN, pl.start_time))
+        if np.max(np.abs(tr["r_vel"][0])) > 0.3 * 0.25:
+            break
+    assert r["first_calls"] == first_calls
+    sp = po.path_stop_parameter(tr["r_t"], tr["r_s"], tr["r_vel"], tr["r_acc"], np.full(7, 2.0), start / 1e9)
+    assert sp["status"] == 0 and abs(r["stop_parameter"] - sp["parameter"]) <= 1e-9
+    v0 = np.array([np.interp(start / 1e9, tr["r_t"], tr["r_vel"][:, d]) for d in range(7)])
+    assert np.max(np.abs(np.array(r["initial_velocity"]) - v0)) <= 1e-7
+    new_joint = np.array([[-1.0] * 7, [1.0] * 7])
+    new_pose = np.stack([TW.fake_fk_pose(q) for q in new_joint])
+    assert pl.switch(sp["parameter"], new_joint, initial_velocity=v0, pose_waypoints=new_pose) == 0
+    k, _ = pl.spline()
+    assert np.max(np.abs(np.array(r["knots_after_switch"]) - k)) <= 1e-9 * k[-1]
+    for second_calls in range(1, 401):
+        assert pl.plan(start, TW.HORIZON) == po.ORC_OK
+        start = min(pl.end_time, max(start + TW.REPLAN, pl.start_time))
+        if pl.target_reached:
+            break
+    assert r["second_calls"] == second_calls
+    tr = pl.trajectory()
+    t = np.array(r["time"])
+    pos = np.array(r["positions"]).reshape(-1, 7)
+    assert abs(len(t) - len(tr["r_t"])) <= 1
+    m = min(len(t), len(tr["r_t"])) - 1
+    assert np.max(np.abs(pos[:m] - tr["r_pos"][:m])) <= 1e-7
+    assert np.max(np.abs(pos[-1] - new_joint[-1])) <= 1e-8

@@ -130,3 +130,146 @@ def test_switch_and_replan_matches_oracle(skip):
     P.compare_path_samples(eng, planners)
     for b, pl in enumerate(planners[:-1]):
         np.testing.assert_allclose(pl.trajectory()["r_pos"][-1], new_wp[b, 1], atol=1e-10)
+
+
+# ---- Cartesian paths (TimeableCartesianSplinePath::SwitchToWaypointPath) ----------------
+def device_cart_splines(eng):
+    n = eng.get(ARR.NUM_POINTS)
+    ctrl, knots, pose = eng.get(ARR.CTRL), eng.get(ARR.KNOTS), eng.get(ARR.POSE_CTRL)
+    return [(knots[b, :n[b] + 3].copy(), ctrl[b, :n[b]].copy(), pose[b, :n[b]].copy())
+            for b in range(len(n))]
+
+
+def fake_fk(q):
+    return np.concatenate([q[:3], orc.exp_so3(q[3:6])])
+
+
+def test_cartesian_switch_matches_oracle_per_path():
+    """Batched switches of Cartesian paths against the oracle (== the reference's object code
+    up to its rounding-decided end-point sign, tests/test_oracle_vs_ref_cart.py): status
+    exact; knots, joint, translation and rotation control points within 1e-12 (the device's
+    acos / sin / cos / atan2 in slerp and the pose corner offsets).  A path whose rotation
+    end-point correction falls on the other side of that sign is recognised and dropped."""
+    B, W, D = 12, 5, 7
+    rng = np.random.default_rng(31)
+    joint = rng.uniform(-0.8, 0.8, (B, W, D))
+    pose = np.stack([np.stack([fake_fk(q) for q in joint[b]]) for b in range(B)])
+    eng = pkg.Engine(max_paths=B, num_samples=64, num_dofs=D, max_waypoints=W, cartesian=True)
+    eng.set_cart_options(0.05, 0.5, 0.25)
+    eng.set_cart_waypoints(pose, joint)
+    vm, am = np.ones((B, D)), np.full((B, D), 2.0)
+    planners = [orc.Planner(joint[b], vm[b], am[b], 64, 0.01, 0.004, pose_waypoints=pose[b])
+                for b in range(B)]
+    alive = np.ones(B, bool)
+    seen, compared = set(), 0
+    for round_ in range(8):
+        kend = np.array([pl.spline()[0][-1] for pl in planners])
+        keep = rng.uniform(0.2, 0.9, B) * kend
+        keep[1] = kend[1] + 1.0  # nothing to truncate: the join is the old end
+        nj = rng.uniform(-0.8, 0.8, (B, W, D))
+        num = rng.integers(2, W + 1, size=B).astype(np.int32)
+        num[3] = 0  # untouched
+        npz = np.stack([np.stack([fake_fk(q) for q in nj[b]]) for b in range(B)])
+        status = eng.switch_to_cart_waypoint_path(keep, npz, nj, num_waypoints=num)
+        got = device_cart_splines(eng)
+        for b, pl in enumerate(planners):
+            expect = 0 if num[b] <= 0 else pl.switch(keep[b], nj[b, :num[b]],
+                                                     pose_waypoints=npz[b, :num[b]])
+            if not alive[b]:
+                continue
+            assert status[b] == expect, (round_, b, status[b], expect)
+            seen.add(int(expect))
+            if expect != 0:
+                alive[b] = False  # partially modified splines: not compared further
+                continue
+            k, p = pl.spline()
+            pc = pl._pose_ctrl[:len(p)]
+            assert got[b][0].shape == k.shape
+            np.testing.assert_allclose(got[b][0], k, rtol=1e-13, atol=0)
+            np.testing.assert_allclose(got[b][1], p, rtol=0, atol=1e-12)
+            np.testing.assert_allclose(got[b][2][:, :3], pc[:, :3], rtol=0, atol=1e-12)
+            bad = np.flatnonzero(np.abs(got[b][2][:, 3:] - pc[:, 3:]).max(axis=1) > 1e-11)
+            if bad.size:  # the reference's sign of +-1e-16 (bsplineq.cc:575-577)
+                assert bad.size == 1
+                alive[b] = False
+                continue
+            compared += 1
+    assert 0 in seen and compared >= 40
+
+
+@pytest.mark.parametrize("skip", [False, True])
+def test_cartesian_switch_and_replan(skip):
+    """SwitchToNewCartesianWaypointPathWorks (path_timing_trajectory_test.cc:764-920) on the
+    device with the built-in kinematics: plan until the motion is fast, switch at the stop
+    parameter with the current velocity, plan to the end -- against the oracle planner within
+    the tolerances of the Cartesian planner tests (device libm)."""
+    import test_oracle_windows as TW
+    N, dt, delta = 1000, 0.004, 0.005
+    joint = TW.CART_WAYPOINTS[None]
+    pose = np.stack([TW.fake_fk_pose(q) for q in TW.CART_WAYPOINTS])[None]
+    W, D = joint.shape[1], 7
+    vm, am = np.ones((1, D)), np.full((1, D), 2.0)
+    eng = pkg.Engine(max_paths=1, num_samples=N, num_dofs=D, max_waypoints=W,
+                     max_time_samples_total=60000, cartesian=True)
+    eng.set_cart_options(0.05, 0.5, 0.25)
+    eng.set_cart_waypoints(pose, joint)
+    eng.set_joint_limits(vm, am)
+    eng.set_sampling(np.full(1, delta))
+    eng.planner_reset(16384, dt, skip=skip, max_initial_velocity_error=1e-2)
+    eng.planner_set_kinematics(1)
+    pl = orc.Planner(joint[0], vm[0], am[0], N, delta, dt, skip=skip, P_cap=16384,
+                     pose_waypoints=pose[0], max_initial_velocity_error=1e-2)
+
+    def compare(tag):
+        st = P.device_state(eng)
+        off, rows = P.device_rows(eng)
+        assert st["len"][0] == pl.len and st["target_reached"][0] == pl.target_reached, tag
+        tr = pl.trajectory()
+        M = off[1] - off[0]
+        assert abs(M - pl.M) <= 1, tag
+        m = min(M, pl.M) - 1
+        if m > 0:
+            assert np.max(np.abs(rows["r_t"][:m] - tr["r_t"][:m])) <= 1e-9, tag
+            assert np.max(np.abs(rows["r_pos"][:m] - tr["r_pos"][:m])) <= 1e-8, tag
+        return tr
+
+    start, tr = 0, None
+    for call in range(200):
+        assert pl.plan(start, 750 * MS) == orc.ORC_OK
+        eng.planner_plan(start, 750 * MS)
+        tr = compare(f"before switch {call}")
+        start = min(pl.end_time, max(start + 200 * MS, pl.start_time))
+        if np.max(np.abs(tr["r_vel"][0])) > 0.3 * 0.25:
+            break
+    assert not pl.target_reached
+    stop = eng.path_stop_parameter(start / 1e9)
+    o = orc.path_stop_parameter(tr["r_t"], tr["r_s"], tr["r_vel"], tr["r_acc"], am[0], start / 1e9)
+    assert abs(stop["parameter"][0] - o["parameter"]) <= 1e-9
+    new_joint = np.zeros((1, W, D))
+    new_joint[0, 0], new_joint[0, 1] = -1.0, 1.0
+    new_pose = np.zeros((1, W, 7))
+    new_pose[0, :, 6] = 1.0
+    new_pose[0, :2] = [TW.fake_fk_pose(q) for q in new_joint[0, :2]]
+    v0 = np.array([[np.interp(start / 1e9, tr["r_t"], tr["r_vel"][:, d]) for d in range(D)]])
+    status = eng.switch_to_cart_waypoint_path(np.array([o["parameter"]]), new_pose, new_joint,
+                                              num_waypoints=np.array([2], np.int32),
+                                              initial_velocity=v0)
+    assert status[0] == 0
+    assert pl.switch(o["parameter"], new_joint[0, :2], initial_velocity=v0[0],
+                     pose_waypoints=new_pose[0, :2]) == 0
+    k, p = pl.spline()
+    got = device_cart_splines(eng)[0]
+    np.testing.assert_allclose(got[0], k, rtol=1e-13, atol=0)
+    np.testing.assert_allclose(got[1], p, rtol=0, atol=1e-11)
+    np.testing.assert_allclose(got[2], pl._pose_ctrl[:len(p)], rtol=0, atol=1e-11)
+    for call in range(400):
+        assert pl.plan(start, 750 * MS) == orc.ORC_OK
+        eng.planner_plan(start, 750 * MS)
+        compare(f"after switch {call}")
+        start = min(pl.end_time, max(start + 200 * MS, pl.start_time))
+        if pl.target_reached:
+            break
+    assert pl.target_reached
+    _, rows = P.device_rows(eng)
+    np.testing.assert_allclose(rows["r_pos"][-1], new_joint[0, 1], atol=1e-9)
+    np.testing.assert_array_equal(rows["r_vel"][-1], 0.0)

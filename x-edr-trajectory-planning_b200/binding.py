@@ -176,6 +176,8 @@ def lib():
         L.tpb_resample_skipping.argtypes = [vp, C.c_double, C.c_double, C.POINTER(C.c_int64)]
         L.tpb_switch_to_waypoint_path.restype = i32
         L.tpb_switch_to_waypoint_path.argtypes = [vp, vp, vp, vp, vp, i32]
+        L.tpb_switch_to_cart_waypoint_path.restype = i32
+        L.tpb_switch_to_cart_waypoint_path.argtypes = [vp, vp, vp, vp, vp, vp, i32]
         L.tpb_planner_reset.restype = i32
         L.tpb_planner_reset.argtypes = [vp, i32, C.c_double, i32, i32, C.c_double, vp, i32]
         L.tpb_planner_new_path.restype = i32
@@ -501,6 +503,21 @@ class Engine:
                                                    _ptr(wp)[0], _ptr(v0)[0], dev))
         return self.get(ARR.SWITCH_STATUS)
 
+    def switch_to_cart_waypoint_path(self, keep_path_until, pose_waypoints, joint_waypoints,
+                                     num_waypoints=None, initial_velocity=None):
+        """tpb_switch_to_cart_waypoint_path: TimeableCartesianSplinePath::SwitchToWaypointPath
+        for every path of the batch.  Returns the per-path status codes."""
+        keep = _f64(keep_path_until)
+        pw, jw = _f64(pose_waypoints), _f64(joint_waypoints)
+        assert tuple(pw.shape[1:]) == (self.Wmax, 7) and tuple(jw.shape[1:]) == (self.Wmax, self.D)
+        if num_waypoints is not None and not hasattr(num_waypoints, "data_ptr"):
+            num_waypoints = np.ascontiguousarray(num_waypoints, np.int32)
+        v0 = _f64(initial_velocity)
+        pk, dev = _ptr(keep)
+        self._ck(lib().tpb_switch_to_cart_waypoint_path(self._h, pk, _ptr(num_waypoints)[0],
+                                                        _ptr(pw)[0], _ptr(jw)[0], _ptr(v0)[0], dev))
+        return self.get(ARR.SWITCH_STATUS)
+
     def planner_reset(self, path_sample_capacity, time_step_sec, skip=False,
                       max_planning_iterations=200, max_initial_velocity_error=1e-4,
                       initial_velocity=None):
@@ -620,7 +637,7 @@ class Engine:
         if what == ARR.KNOTS:
             return out.reshape(B, -1)
         if what == ARR.POSE_CTRL:
-            return out.reshape(B, self.max_points, 7)
+            return out.reshape(B, -1, 7)  # grows with the first switch, like CTRL
         if what == ARR.POSE_TARGETS:
             return out.reshape(B, N + 1, 7)
         if what == ARR.JOINT_TARGETS:

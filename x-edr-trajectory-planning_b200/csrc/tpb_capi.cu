@@ -71,7 +71,7 @@ struct tpb_engine {
   std::vector<int32_t> hk_active;
   int32_t* any_active_host = nullptr;  // pinned
   // tpb_switch_to_waypoint_path staging: [Bmax] / [Bmax][Wmax][D]
-  double *sw_keep = nullptr, *sw_wp = nullptr;
+  double *sw_keep = nullptr, *sw_wp = nullptr, *sw_pose = nullptr;
   int32_t *sw_num = nullptr, *sw_status = nullptr, *sw_modified = nullptr;
   std::vector<void*> spline_big;  // ctrl / knots of the reference's knot capacity
   void* query_scratch = nullptr;  // tpb_query_profile with host arrays
@@ -1072,6 +1072,90 @@ int32_t tpb_switch_to_waypoint_path(tpb_engine* e, const double* keep_path_until
   }
   TPB_CUDA(e, cudaGetLastError());
   e->sampled = e->optimized = false;  // the sampled window belongs to the old spline
+  return TPB_OK;
+}
+
+int32_t tpb_switch_to_cart_waypoint_path(tpb_engine* e, const double* keep_path_until,
+                                         const int32_t* num_waypoints, const double* pose_waypoints,
+                                         const double* joint_waypoints,
+                                         const double* initial_velocity, int32_t on_device) {
+  if (e == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (e->mode != Mode::kCartesian || !e->have_waypoints)
+    return fail(e, TPB_FAILED_PRECONDITION, "No path set");
+  if (keep_path_until == nullptr || pose_waypoints == nullptr || joint_waypoints == nullptr)
+    return fail(e, TPB_INVALID_ARGUMENT, "keep_path_until / waypoints are null");
+  cudaSetDevice(e->device);
+  const size_t Bm = d.Bmax, D = d.D;
+  // the spline arrays grow once to the reference's knot capacity
+  // (timeable_path_cartesian_spline.cc:404-413)
+  const int cap_points = std::max(2 * (std::max(3 * d.Wmax - 2, 4) + 3), 100) - 3;
+  if (d.max_points < cap_points) {
+    double *ctrl = nullptr, *knots = nullptr, *pose = nullptr;
+    TPB_CUDA(e, cudaMalloc(reinterpret_cast<void**>(&ctrl), sizeof(double) * Bm * cap_points * D + 16));
+    e->spline_big.push_back(ctrl);
+    TPB_CUDA(e, cudaMalloc(reinterpret_cast<void**>(&knots), sizeof(double) * Bm * (cap_points + 3) + 16));
+    e->spline_big.push_back(knots);
+    TPB_CUDA(e, cudaMalloc(reinterpret_cast<void**>(&pose), sizeof(double) * Bm * cap_points * 7 + 16));
+    e->spline_big.push_back(pose);
+    e->launches += tpb::launch_restride_spline(d.B, d.D, d.max_points, cap_points, e->a.ctrl,
+                                               e->a.knots, ctrl, knots, e->stream);
+    e->launches += tpb::launch_restride_rows(d.B, 7, d.max_points, cap_points, e->a.pose_ctrl, pose,
+                                             e->stream);
+    e->a.ctrl = ctrl;  // the smaller arrays stay allocated until tpb_destroy
+    e->a.knots = knots;
+    e->a.pose_ctrl = pose;
+    d.max_points = cap_points;
+  }
+  if (e->sw_keep == nullptr) {
+    TPB_CUDA(e, dev_alloc(e, &e->sw_keep, Bm));
+    TPB_CUDA(e, dev_alloc(e, &e->sw_num, Bm));
+    TPB_CUDA(e, dev_alloc(e, &e->sw_status, Bm));
+    TPB_CUDA(e, dev_alloc(e, &e->sw_modified, Bm));
+    TPB_CUDA(e, dev_alloc(e, &e->sw_wp, Bm * d.Wmax * D));
+  }
+  if (e->sw_pose == nullptr) TPB_CUDA(e, dev_alloc(e, &e->sw_pose, Bm * d.Wmax * 7));
+  TPB_CUDA(e, copy_in(e, e->sw_keep, keep_path_until, sizeof(double) * d.B, on_device));
+  TPB_CUDA(e, copy_in(e, e->sw_wp, joint_waypoints, sizeof(double) * d.B * d.Wmax * D, on_device));
+  TPB_CUDA(e, copy_in(e, e->sw_pose, pose_waypoints, sizeof(double) * d.B * d.Wmax * 7, on_device));
+  if (num_waypoints != nullptr)
+    TPB_CUDA(e, copy_in(e, e->sw_num, num_waypoints, sizeof(int32_t) * d.B, on_device));
+  tpb::SwitchArgs s;
+  s.keep_path_until = e->sw_keep;
+  s.num_waypoints = num_waypoints ? e->sw_num : nullptr;
+  s.waypoints = e->sw_wp;
+  s.pose_waypoints = e->sw_pose;
+  s.max_waypoints = d.Wmax;
+  s.status = e->sw_status;
+  s.modified = e->sw_modified;
+  e->launches += tpb::launch_cart_switch(d, e->a, s, e->rounding, e->translation_rounding, e->stream);
+  if (e->planner_ready) {
+    e->launches += tpb::launch_planner_mark_modified(d, e->w, e->sw_modified, e->stream);
+    if (initial_velocity != nullptr)
+      TPB_CUDA(e, copy_in(e, e->w.init_vel, initial_velocity, sizeof(double) * d.B * D, on_device));
+  }
+  TPB_CUDA(e, cudaGetLastError());
+  // the IK solutions beyond the kept part belong to the old path (:188-192): the caches of
+  // user kinematics (tpb_planner_set_host_kinematics) are cut at PathIkIndex(keep_path_until)
+  if (!e->ik_cache.empty()) {
+    std::vector<double> keep(d.B), delta(d.B);
+    std::vector<int32_t> modified(d.B);
+    TPB_CUDA(e, cudaMemcpyAsync(keep.data(), e->sw_keep, sizeof(double) * d.B, cudaMemcpyDeviceToHost,
+                                e->stream));
+    TPB_CUDA(e, cudaMemcpyAsync(delta.data(), e->a.delta, sizeof(double) * d.B, cudaMemcpyDeviceToHost,
+                                e->stream));
+    TPB_CUDA(e, cudaMemcpyAsync(modified.data(), e->sw_modified, sizeof(int32_t) * d.B,
+                                cudaMemcpyDeviceToHost, e->stream));
+    TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+    for (int b = 0; b < d.B && b < static_cast<int>(e->ik_cache.size()); ++b) {
+      if (modified[b] == 0) continue;
+      const long ik_index = std::lround(keep[b] / delta[b]);  // PathIkIndex (:671-674)
+      auto& cache = e->ik_cache[b];
+      if (ik_index >= 0 && static_cast<size_t>(ik_index) < cache.size() / D)
+        cache.resize(static_cast<size_t>(ik_index + 1) * D);
+    }
+  }
+  e->sampled = e->optimized = false;  // the sampled window belongs to the old splines
   return TPB_OK;
 }
 

@@ -20,6 +20,7 @@
 // warm-start semantics: the host layer downloads the targets, runs the user's
 // callbacks and uploads joint positions / Jacobians (tpb_cart_set_ik_positions,
 // tpb_cart_setup_constraints); everything else stays on the device.
+#include <cfloat>
 #include <cstdlib>
 
 #include "tpb_engine.h"
@@ -167,9 +168,269 @@ __global__ void k_cart_fit(Dims dm, DeviceArrays a, double rotation_rounding,
   const double scale = weighted * kPathParameterPerPolygonLength;
   for (int i = 0; i < nk; ++i) kn[i] *= scale;
   a.num_points[b] = n;
+  a.knot_cap[b] = max(2 * nk, 100);  // timeable_path_cartesian_spline.cc:404-413
   const double kend = kn[nk - 1];
   a.knot_end[b] = kend;
   a.delta[b] = auto_delta ? kend / (dm.N - 1) : a.delta_in[b];
+}
+
+// ---------------------------------------------------------------------------
+// TimeableCartesianSplinePath::SwitchToWaypointPath (timeable_path_cartesian_spline.cc:
+// 183-296), one thread per path, in place on the path's knots[] / ctrl[] / pose_ctrl[]
+// (which hold the reference's knot capacity by now).  The joint, translation and rotation
+// splines keep equal knot vectors in the reference, so one insertion step serves all
+// three: lerp for the two vector splines (bspline.h:244-278, the closed form, see
+// tpb_switch.cu), slerp for the quaternions (bsplineq.cc:355-431).
+// ---------------------------------------------------------------------------
+enum : int32_t { kSwOk = 0, kSwInvalidArgument = 3, kSwFailedPrecondition = 9, kSwOutOfRange = 11,
+                 kSwInternal = 13 };
+
+__device__ int span2(const double* knots, int num_knots, double u) {
+  if (u == knots[num_knots - 1]) return num_knots - 4;  // num_points - 1
+  int lo = 2, hi = num_knots - 2;
+  while (lo < hi) {
+    const int mid = lo + ((hi - lo) >> 1);
+    if (knots[mid] <= u) {
+      lo = mid + 1;
+    } else {
+      hi = mid;
+    }
+  }
+  return lo - 1;
+}
+
+__device__ void cart_insert_knot(double* knots, double* pts, double* pose, int D, int& num_knots,
+                                 int& num_points, double knot) {
+  double sj[2][kMaxDofs], sp[2][7];
+  const int span = span2(knots, num_knots, knot);
+  for (int i = 0; i < 2; ++i) {
+    const int k = span + i - 1;
+    const double alpha = (knot - knots[k]) / (knots[k + 2] - knots[k]);
+    for (int d = 0; d < D; ++d) sj[i][d] = alpha * pts[k * D + d] + (1.0 - alpha) * pts[(k - 1) * D + d];
+    for (int d = 0; d < 3; ++d) sp[i][d] = alpha * pose[k * 7 + d] + (1.0 - alpha) * pose[(k - 1) * 7 + d];
+    store_quat(sp[i] + 3, qslerp(load_quat(pose + (k - 1) * 7 + 3), alpha, load_quat(pose + k * 7 + 3)));
+  }
+  for (int i = num_points - 1; i >= span; --i) {  // copy_backward
+    for (int d = 0; d < D; ++d) pts[(i + 1) * D + d] = pts[i * D + d];
+    for (int d = 0; d < 7; ++d) pose[(i + 1) * 7 + d] = pose[i * 7 + d];
+  }
+  for (int i = 0; i < 2; ++i) {
+    for (int d = 0; d < D; ++d) pts[(span - 1 + i) * D + d] = sj[i][d];
+    for (int d = 0; d < 7; ++d) pose[(span - 1 + i) * 7 + d] = sp[i][d];
+  }
+  for (int i = num_knots - 1; i >= span + 1; --i) knots[i + 1] = knots[i];
+  knots[span + 1] = knot;
+  num_knots += 1;
+  num_points += 1;
+}
+
+// ProjectPointOnPath (path_tools.h:59-104) over rows `stride` doubles apart
+__device__ void project_on_polyline(const double* wps, int stride, int W, int dim, const double* point,
+                                    int* index, double* line_parameter, double* projected) {
+  *index = 0;
+  *line_parameter = 0.0;
+  if (W == 1) {
+    for (int d = 0; d < dim; ++d) projected[d] = wps[d];
+    return;
+  }
+  double best = DBL_MAX;
+  for (int i = 0; i < W - 1; ++i) {
+    const double* p0 = wps + i * stride;
+    const double* p1 = p0 + stride;
+    double ab2 = 0.0, dot = 0.0;
+    for (int d = 0; d < dim; ++d) {
+      ab2 += (p1[d] - p0[d]) * (p1[d] - p0[d]);
+      dot += (point[d] - p0[d]) * (p1[d] - p0[d]);
+    }
+    double t = (ab2 > 0.0) ? dot / ab2 : 0.0;
+    t = (t < 0.0) ? 0.0 : ((t > 1.0) ? 1.0 : t);
+    double sum = 0.0;
+    for (int d = 0; d < dim; ++d) {
+      const double e = p0[d] + t * (p1[d] - p0[d]) - point[d];
+      sum += e * e;
+    }
+    const double dist = sqrt(sum);
+    if (dist < best) {
+      best = dist;
+      *line_parameter = t;
+      *index = i;
+    }
+  }
+  const double* p0 = wps + *index * stride;
+  for (int d = 0; d < dim; ++d) projected[d] = p0[d] + *line_parameter * (p0[stride + d] - p0[d]);
+}
+
+__global__ void k_cart_switch(Dims dm, DeviceArrays a, SwitchArgs s, double rotation_rounding,
+                              double translation_rounding) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= dm.B) return;
+  const int D = dm.D;
+  const int W = s.num_waypoints ? s.num_waypoints[b] : s.max_waypoints;
+  if (W <= 0) {  // this path keeps its splines
+    s.status[b] = kSwOk;
+    s.modified[b] = 0;
+    return;
+  }
+  s.modified[b] = 1;  // kModifiedPath, also when the switch fails (:194)
+  double* knots = a.knots + static_cast<size_t>(b) * (dm.max_points + 3);
+  double* pts = a.ctrl + static_cast<size_t>(b) * dm.max_points * D;
+  double* pose = a.pose_ctrl + static_cast<size_t>(b) * dm.max_points * 7;
+  const double* jw = s.waypoints + static_cast<size_t>(b) * s.max_waypoints * D;
+  const double* pw = s.pose_waypoints + static_cast<size_t>(b) * s.max_waypoints * 7;
+  double* jlist = a.waypoints + static_cast<size_t>(b) * dm.Wmax * D;  // new waypoint lists
+  double* plist = a.pose_wp + static_cast<size_t>(b) * dm.Wmax * 7;
+  const int cap = a.knot_cap[b];
+  int num_points = a.num_points[b];
+  int num_knots = (num_points > 0) ? num_points + 3 : 0;
+  const double keep = s.keep_path_until[b];
+  int32_t st = kSwOk;
+
+  // ---- TruncateSplineAt of the three splines (bspline.h:402-427, bsplineq.cc:497-519)
+  if (num_knots > 0 && !(keep >= knots[num_knots - 1])) {
+    if (keep <= knots[0]) {
+      num_knots = 0;
+      num_points = 0;
+    } else if (num_knots + 3 > cap) {
+      st = kSwFailedPrecondition;  // CanInsertKnot (bspline_base.cc:166-195)
+    } else {
+      for (int i = 0; i < 3; ++i) cart_insert_knot(knots, pts, pose, D, num_knots, num_points, keep);
+      const int span = span2(knots, num_knots, keep);
+      num_knots = span + 1;
+      num_points = num_knots - 3;
+    }
+  }
+  // ---- EvalCurve(keep_path_until) of the joint and the translation spline (:203-212; the
+  // rotation's value is not used afterwards and its range check is the same)
+  double jsw[kMaxDofs], tsw[3];
+  if (st == kSwOk) {
+    if (num_knots == 0 || keep < knots[0] || keep > knots[num_knots - 1]) {
+      st = kSwOutOfRange;
+    } else {
+      const int span = span2(knots, num_knots, keep);
+      double basis[3];
+      basis_funs<2>(knots, span, keep, basis);
+      for (int d = 0; d < D; ++d) jsw[d] = 0.0;
+      for (int d = 0; d < 3; ++d) tsw[d] = 0.0;
+      for (int i = 0; i <= 2; ++i) {
+        for (int d = 0; d < D; ++d) jsw[d] += basis[i] * pts[(span - 2 + i) * D + d];
+        for (int d = 0; d < 3; ++d) tsw[d] += basis[i] * pose[(span - 2 + i) * 7 + d];
+      }
+    }
+  }
+  if (st == kSwOk) {
+    int jidx, tidx;
+    double jt, tt, jproj[kMaxDofs], tproj[3];
+    project_on_polyline(jw, D, W, D, jsw, &jidx, &jt, jproj);
+    project_on_polyline(pw, 7, W, 3, tsw, &tidx, &tt, tproj);
+    // ---- the new waypoint lists (:238-276)
+    int n = 0;
+    double linf = 0.0;
+    for (int d = 0; d < 3; ++d) linf = fmax(linf, fabs(tsw[d] - tproj[d]));
+    if (linf > 1e-3) {
+      if (tidx + 1 >= W) {
+        st = kSwInvalidArgument;  // the reference would read pose_waypoints[W]
+      } else {
+        for (int d = 0; d < D; ++d) jlist[d] = jproj[d];
+        for (int d = 0; d < 3; ++d) plist[d] = tproj[d];
+        store_quat(plist + 3, qslerp(load_quat(pw + tidx * 7 + 3), tt, load_quat(pw + (tidx + 1) * 7 + 3)));
+        n = 1;
+      }
+    }
+    if (st == kSwOk) {
+      const int first = (tt >= 0) ? tidx + 1 : tidx;
+      for (int i = first; i < W; ++i) {
+        for (int d = 0; d < D; ++d) jlist[n * D + d] = jw[i * D + d];
+        for (int d = 0; d < 7; ++d) plist[n * 7 + d] = pw[i * 7 + d];
+        ++n;
+      }
+      // ---- control polygons + ExtendWithControlPoints of the three splines
+      // (bspline.h:429-511, bsplineq.cc:521-587)
+      const int nc = (n == 1) ? 4 : 3 * n - 2;
+      const int new_num_points = num_points + nc;
+      const int new_num_knots = num_knots + (nc + 4) - 4;
+      if (n == 0) {
+        st = kSwInvalidArgument;  // the reference would index an empty vector
+      } else if (num_knots < 6 || new_num_points > cap - 3 || new_num_knots > cap) {
+        st = kSwFailedPrecondition;
+      } else {
+        polyline_to_bspline3(jlist, n, D, rotation_rounding, pts + num_points * D);
+        pose_polyline_to_bspline3(plist, n, translation_rounding, rotation_rounding,
+                                  pose + num_points * 7);
+        const double u_join = knots[num_knots - 1];
+        // the rotation curve's value at the join, on the truncated spline (:548-549)
+        Quat q_join;
+        {
+          double basis[3];
+          const int span = span2(knots, num_knots, u_join);
+          basis_funs<2>(knots, span, u_join, basis);
+          const double c1 = basis[2], c0 = c1 + basis[1];
+          const Quat p0 = load_quat(pose + (span - 2) * 7 + 3);
+          const Quat p1 = load_quat(pose + (span - 1) * 7 + 3);
+          const Quat p2 = load_quat(pose + span * 7 + 3);
+          q_join = qmul(qmul(p0, qpow(qmul(qinv(p0), p1), c0)), qpow(qmul(qinv(p1), p2), c1));
+          normalize_positive_real(q_join);
+        }
+        const double old_knot_range = knots[num_knots - 1] - knots[0];
+        const int old_inner = num_knots - 5;
+        const int new_inner = new_num_knots - 5;
+        const double new_knot_range = (old_knot_range * new_inner) / old_inner;
+        const int start = num_knots - 3;
+        const int size = (new_num_knots - 2) - start;
+        {  // Eigen's setLinSpaced(size, low, high) for |high| >= |low|
+          const double low = old_knot_range, high = new_knot_range;
+          const int size1 = (size == 1) ? 1 : size - 1;
+          const double step = (size == 1) ? 0.0 : (high - low) / static_cast<double>(size - 1);
+          for (int i = 0; i < size; ++i) {
+            knots[start + i] = (i == size1) ? high : low + static_cast<double>(i) * step;
+          }
+        }
+        for (int i = 0; i < 3; ++i) knots[new_num_knots - 3 + i] = knots[0] + new_knot_range;
+        // the old end points move so that the curves keep their values at the join
+        const int join_span = span2(knots, new_num_knots, u_join);
+        const int mod = num_points - 1;
+        double basis[3];
+        basis_funs<2>(knots, join_span, u_join, basis);
+        const double cum0 = basis[2] + basis[1];
+        if (!(basis[1] > 0) || !(cum0 > 0.0)) {
+          st = kSwInternal;
+        } else {
+          for (int d = 0; d < D; ++d) {
+            pts[mod * D + d] = 1.0 / (basis[1]) * (pts[mod * D + d] - basis[0] * pts[(mod - 1) * D + d]);
+          }
+          for (int d = 0; d < 3; ++d) {
+            pose[mod * 7 + d] = 1.0 / (basis[1]) * (pose[mod * 7 + d] - basis[0] * pose[(mod - 1) * 7 + d]);
+          }
+          const Quat pm = load_quat(pose + (mod - 1) * 7 + 3);
+          Quat lg = qlog(qmul(qinv(pm), q_join));
+          lg.x /= cum0;
+          lg.y /= cum0;
+          lg.z /= cum0;
+          lg.w /= cum0;
+          if (lg.w < 0) {  // (sic, :575-577: the whole logarithm is negated)
+            lg.x *= -1.0;
+            lg.y *= -1.0;
+            lg.z *= -1.0;
+            lg.w *= -1.0;
+          }
+          store_quat(pose + mod * 7 + 3, qmul(pm, qexp(lg)));
+        }
+        num_knots = new_num_knots;
+        num_points = new_num_points;
+      }
+    }
+  }
+  a.num_points[b] = num_points;
+  if (num_knots > 0) a.knot_end[b] = knots[num_knots - 1];
+  s.status[b] = st;
+}
+
+// [B][old_rows][width] -> [B][new_rows][width]
+__global__ void k_restride_rows(int width, int old_rows, int new_rows, const double* __restrict__ in,
+                                double* __restrict__ out) {
+  const int b = blockIdx.x;
+  for (int i = threadIdx.x; i < old_rows * width; i += blockDim.x) {
+    out[static_cast<size_t>(b) * new_rows * width + i] = in[static_cast<size_t>(b) * old_rows * width + i];
+  }
 }
 
 constexpr int kCartThreads = 128;
@@ -523,6 +784,18 @@ int launch_cart_fit(const Dims& d, const DeviceArrays& a, double rotation_roundi
   const int threads = 64;
   k_cart_fit<<<(d.B + threads - 1) / threads, threads, 0, st>>>(d, a, rotation_rounding,
                                                                 translation_rounding, auto_delta);
+  return 1;
+}
+
+int launch_cart_switch(const Dims& d, const DeviceArrays& a, const SwitchArgs& s,
+                       double rotation_rounding, double translation_rounding, cudaStream_t st) {
+  k_cart_switch<<<(d.B + 63) / 64, 64, 0, st>>>(d, a, s, rotation_rounding, translation_rounding);
+  return 1;
+}
+
+int launch_restride_rows(int B, int width, int old_rows, int new_rows, const double* in, double* out,
+                         cudaStream_t st) {
+  k_restride_rows<<<B, 128, 0, st>>>(width, old_rows, new_rows, in, out);
   return 1;
 }
 

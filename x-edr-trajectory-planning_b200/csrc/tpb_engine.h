@@ -213,12 +213,17 @@ struct SwitchArgs {
   const double* keep_path_until = nullptr;  // [B]
   const int32_t* num_waypoints = nullptr;   // [B] or nullptr (max_waypoints each); <= 0: path untouched
   const double* waypoints = nullptr;        // [B][max_waypoints][D]
+  const double* pose_waypoints = nullptr;   // [B][max_waypoints][7] (Cartesian paths)
   int max_waypoints = 0;                    // <= Dims::Wmax
   int32_t* status = nullptr;                // [B] absl::StatusCode numbers
   int32_t* modified = nullptr;              // [B] 1: the path is TimeablePath::State::kModifiedPath now
 };
 int launch_joint_switch(const Dims& d, const DeviceArrays& a, const SwitchArgs& s, double rounding,
                         cudaStream_t st);
+int launch_cart_switch(const Dims& d, const DeviceArrays& a, const SwitchArgs& s,
+                       double rotation_rounding, double translation_rounding, cudaStream_t st);
+int launch_restride_rows(int B, int width, int old_rows, int new_rows, const double* in, double* out,
+                         cudaStream_t st);
 int launch_restride_spline(int B, int D, int old_points, int new_points, const double* ctrl_in,
                            const double* knots_in, double* ctrl_out, double* knots_out,
                            cudaStream_t st);

@@ -153,6 +153,26 @@ __device__ __forceinline__ Quat qpow(Quat q, double power) {
 
 __device__ __forceinline__ Quat load_quat(const double* p) { return Quat{p[0], p[1], p[2], p[3]}; }
 
+// Eigen QuaternionBase::slerp(t, other)
+__device__ __forceinline__ Quat qslerp(const Quat& a, double t, const Quat& b) {
+  const double one = 1.0 - 2.220446049250313e-16;
+  const double d = a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+  const double abs_d = fabs(d);
+  double scale0, scale1;
+  if (abs_d >= one) {
+    scale0 = 1.0 - t;
+    scale1 = t;
+  } else {
+    const double theta = acos(abs_d);
+    const double sin_theta = sin(theta);
+    scale0 = sin((1.0 - t) * theta) / sin_theta;
+    scale1 = sin(t * theta) / sin_theta;
+  }
+  if (d < 0.0) scale1 = -scale1;
+  return Quat{scale0 * a.x + scale1 * b.x, scale0 * a.y + scale1 * b.y,
+              scale0 * a.z + scale1 * b.z, scale0 * a.w + scale1 * b.w};
+}
+
 // QuatPowerDerivative, splines/bsplineq.cc:148-160: exp(p log q) * log q
 __device__ __forceinline__ Quat qpow_derivative(Quat q, double power) {
   normalize_positive_real(q);

@@ -13,9 +13,8 @@
 // uploads the 6 x D matrices.  Extension: set_device_kinematics(TPB_KIN_FAKE7)
 // selects a built-in device model instead, then nothing leaves the GPU.
 //
-// Scope: fresh paths planned from path_start = 0 in one window.  The growing
-// path_ik_positions_ buffer across windows and SwitchToWaypointPath (online
-// replanning) return kUnimplemented.
+// Scope: the reference's whole class -- fresh paths, several planning windows per path with
+// the growing path_ik_positions_ cache, SwitchToWaypointPath (online replanning).
 #ifndef TRAJECTORY_PLANNING_TIMEABLE_PATH_CARTESIAN_SPLINE_H_
 #define TRAJECTORY_PLANNING_TIMEABLE_PATH_CARTESIAN_SPLINE_H_
 
@@ -111,8 +110,59 @@ class TimeableCartesianSplinePath : public TimeablePath {
     return FitSplineToWaypoints();
   }
 
-  tp::Status SwitchToWaypointPath(double, tp::Span<const tp::Pose3d>, tp::Span<const tp::VectorXd>) {
-    return tp::UnimplementedError("SwitchToWaypointPath: online replanning is outside the hot path");
+  // SwitchToWaypointPath (.cc:183-296) on the device (tpb_switch_to_cart_waypoint_path): the
+  // joint, translation and rotation splines are truncated at keep_path_until, the switching
+  // position is projected onto the new waypoints, their control polygons are appended.  The
+  // path is kModifiedPath afterwards (also when the switch fails, as in the reference).
+  tp::Status SwitchToWaypointPath(const double keep_path_until, tp::Span<const tp::Pose3d> pose_waypoints,
+                                  tp::Span<const tp::VectorXd> joint_waypoints) {
+    // erase the obsolete part of the IK solution (.cc:188-192)
+    if (const int ik_index = PathIkIndex(keep_path_until);
+        ik_index >= 0 && static_cast<size_t>(ik_index) < path_ik_positions_.size()) {
+      path_ik_positions_.resize(ik_index + 1);
+    }
+    if (joint_waypoints.size() != pose_waypoints.size()) {
+      return tp::InvalidArgumentError("'joint_waypoints' and 'pose_waypoints' have different sizes.");
+    }
+    path_state_ = State::kModifiedPath;
+    if (!e_ || joint_waypoints_.empty()) return tp::FailedPreconditionError("Spline is empty or invalid.");
+    if (joint_waypoints.empty()) return tp::InvalidArgumentError("No waypoints.");
+    const int W = static_cast<int>(joint_waypoints.size()), D = static_cast<int>(options_.num_dofs());
+    for (const auto& wp : joint_waypoints) {
+      if (static_cast<int>(wp.size()) != D) {
+        return tp::InvalidArgumentError("Invalid number of joints: waypoint.size: " + std::to_string(wp.size()));
+      }
+    }
+    if (W > wcap_) {
+      return {tp::StatusCode::kResourceExhausted,
+              "more waypoints than the engine was created for (" + std::to_string(wcap_) + ")"};
+    }
+    std::vector<double> jflat(static_cast<size_t>(wcap_) * D, 0.0), pflat(static_cast<size_t>(wcap_) * 7, 0.0);
+    for (int w = 0; w < W; ++w) {
+      std::copy(joint_waypoints[w].begin(), joint_waypoints[w].end(), jflat.begin() + static_cast<size_t>(w) * D);
+      double* o = &pflat[static_cast<size_t>(w) * 7];
+      for (int k = 0; k < 3; ++k) o[k] = pose_waypoints[w].translation()[k];
+      for (int k = 0; k < 4; ++k) o[3 + k] = pose_waypoints[w].quaternion().coeffs()[k];
+    }
+    const int32_t nw = W;
+    int32_t rc = tpb_set_path_options(e_, options_.constraint_safety(), options_.rounding());
+    if (rc == TPB_OK) {
+      rc = tpb_set_cart_options(e_, options_.translation_rounding(),
+                                max_translational_velocity_ > 0 ? max_translational_velocity_ : 1.0,
+                                max_rotational_velocity_ > 0 ? max_rotational_velocity_ : 1.0);
+    }
+    // SetInitialVelocity may follow (the reference's order); PathTimingTrajectory hands the
+    // path's initial velocity to the planner before the next Plan()
+    if (rc == TPB_OK) {
+      rc = tpb_switch_to_cart_waypoint_path(e_, &keep_path_until, &nw, pflat.data(), jflat.data(), nullptr, 0);
+    }
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+    int32_t status = 0;
+    rc = tpb_get(e_, TPB_ARR_SWITCH_STATUS, &status, sizeof(status), 0);
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+    if (auto st = DownloadSplines(); !st.ok()) return st;
+    if (status != 0) return tp::FromCode(status, "SwitchToWaypointPath failed (truncate / project / extend)");
+    return tp::OkStatus();
   }
 
   // SetMaxCartesianVelocity (.cc:352-366)
@@ -481,19 +531,33 @@ class TimeableCartesianSplinePath : public TimeablePath {
     const double delta = options_.delta_parameter();
     rc = tpb_set_sampling(e_, &delta, 0);
     if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
-    const int n = (W == 1) ? 4 : 3 * W - 2;
-    const int max_points = std::max(3 * wcap_ - 2, 4);
-    std::vector<double> kn(max_points + 3), jc(static_cast<size_t>(max_points) * D),
-        pc(static_cast<size_t>(max_points) * 7);
-    tpb_get(e_, TPB_ARR_KNOTS, kn.data(), kn.size() * sizeof(double), 0);
-    tpb_get(e_, TPB_ARR_CTRL, jc.data(), jc.size() * sizeof(double), 0);
-    tpb_get(e_, TPB_ARR_POSE_CTRL, pc.data(), pc.size() * sizeof(double), 0);
-    knots_.assign(kn.begin(), kn.begin() + n + 3);
+    return DownloadSplines();
+  }
+
+  // host copies of the knots and of the three splines' control points (their device arrays
+  // grow to the reference's knot capacity with the first switch)
+  tp::Status DownloadSplines() {
+    const size_t D = options_.num_dofs();
+    int32_t n = 0;
+    int32_t rc = tpb_get(e_, TPB_ARR_NUM_POINTS, &n, sizeof(n), 0);
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+    std::vector<double> buf[3];
+    const tpb_array what[3] = {TPB_ARR_KNOTS, TPB_ARR_CTRL, TPB_ARR_POSE_CTRL};
+    for (int k = 0; k < 3; ++k) {
+      void* ptr = nullptr;
+      size_t bytes = 0;
+      rc = tpb_devptr(e_, what[k], &ptr, &bytes);
+      if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+      buf[k].resize(bytes / sizeof(double));
+      rc = tpb_get(e_, what[k], buf[k].data(), bytes, 0);
+      if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+    }
+    knots_.assign(buf[0].begin(), buf[0].begin() + (n > 0 ? n + 3 : 0));
     joint_control_points_.assign(n, tp::VectorXd(D));
     pose_control_points_.resize(n);
     for (int i = 0; i < n; ++i) {
-      joint_control_points_[i] = tp::VectorXd(&jc[static_cast<size_t>(i) * D], D);
-      const double* p = &pc[static_cast<size_t>(i) * 7];
+      joint_control_points_[i] = tp::VectorXd(&buf[1][static_cast<size_t>(i) * D], D);
+      const double* p = &buf[2][static_cast<size_t>(i) * 7];
       pose_control_points_[i] =
           tp::Pose3d(tp::Quaterniond(p[6], p[3], p[4], p[5]), tp::Vector3d(p[0], p[1], p[2]));
     }

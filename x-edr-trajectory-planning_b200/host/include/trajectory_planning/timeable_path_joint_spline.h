@@ -3,8 +3,8 @@
 // public methods and state machine; spline fitting, path sampling, constraint
 // rows and the limit curve run on the GPU (tpb_set_joint_waypoints /
 // tpb_sample_paths).  One object = a batch of one path on its own engine.
-// SwitchToWaypointPath (online replanning) is not part of the hot path
-//  and returns kUnimplemented.
+// SwitchToWaypointPath (online replanning) runs on the device too
+// (tpb_switch_to_waypoint_path).
 #ifndef TRAJECTORY_PLANNING_TIMEABLE_PATH_JOINT_SPLINE_H_
 #define TRAJECTORY_PLANNING_TIMEABLE_PATH_JOINT_SPLINE_H_
 
