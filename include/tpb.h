@@ -265,6 +265,14 @@ int32_t tpb_time_phases(tpb_engine* e, int32_t on);
 int32_t tpb_last_phase_ms(tpb_engine* e, double* ms3);
 
 /* ---- queries on the solved profiles ------------------------------ */
+/* TimeOptimalPathProfile::SolutionSatisfiesConstraints (time_optimal_path_timing.cc:492-518)
+ * for every path of the batch, on the device: violations[b] = number of (sample, row) pairs
+ * whose value A * sdd + B * sd^2 leaves [lower, upper] by more than kTiny (0 = the reference's
+ * OkStatus, > 0 = its kNotFound "Number of constraint violations: n"), -1 for a path without
+ * a valid solution (its kFailedPrecondition).  Joint paths use the rows ConstraintSetup would
+ * build from q', q''; explicit-row and Cartesian problems the stored rows. */
+int32_t tpb_count_violations(tpb_engine* e, int32_t* violations, int32_t on_device);
+
 /* TimeOptimalPathProfile::GetPathParameterAndDerivatives, SampleIndexFromTime,
  * GetPreviousIndex and GetPreviousDiscreteValues (time_optimal_path_timing.cc:
  * 1497-1668) for queries_per_path times per path, on the device, after tpb_optimize

@@ -132,3 +132,48 @@ def test_queries_on_joint_path_profiles(pkg, po):
     assert ei.value.code == 9
     fresh.close()
     eng.close()
+
+
+def test_solution_satisfies_constraints_on_the_device(pkg, po):
+    """tpb_count_violations = TimeOptimalPathProfile::SolutionSatisfiesConstraints
+    (time_optimal_path_timing.cc:492-518) for a batch: explicit rows (with a path that has
+    no solution) and joint paths (rows synthesised from q', q''), against the oracle's
+    count (the reference's loop restated)."""
+    rng = np.random.default_rng(5)
+    B, N, C = 12, 120, 6
+    cons = np.stack([pkg.workloads.random_constraints(rng, N, C) for _ in range(B)])
+    s0 = np.zeros(B)
+    s1 = rng.uniform(0.5, 4.0, B)
+    s1[3] = -1.0  # setup failure: no valid solution for this path
+    eng = pkg.Engine(max_paths=B, num_samples=N, max_constraints=C)
+    eng.set_constraints(cons, s0, s1)
+    eng.optimize()
+    got = eng.count_violations()
+    st, sd2, sdd = eng.get(pkg.ARR.STATUS), eng.get(pkg.ARR.SD2), eng.get(pkg.ARR.SDD)
+    for b in range(B):
+        if st[b] != 0:
+            assert got[b] == -1
+        else:
+            assert got[b] == po.count_violations(cons[b], sd2[b], sdd[b]), b
+    assert got[3] == -1 and (got[st == 0] >= 0).all()
+    eng.close()
+    # joint paths: the rows ConstraintSetup would build; tighter limits -> violations
+    Bj, W, D, Nj = 6, 6, 7, 256
+    wp, vm, am = pkg.workloads.joint_paths(Bj, W, D, seed=77)
+    eng = pkg.Engine(max_paths=Bj, num_samples=Nj, num_dofs=D, max_waypoints=W)
+    eng.set_joint_limits(vm, am)
+    eng.set_joint_waypoints(wp)
+    eng.sample_paths()
+    eng.optimize()
+    got = eng.count_violations()
+    dq, ddq = eng.get(pkg.ARR.DQ), eng.get(pkg.ARR.DDQ)
+    sd2, sdd = eng.get(pkg.ARR.SD2), eng.get(pkg.ARR.SDD)
+    for b in range(Bj):
+        rows = po.joint_constraints(dq[b], ddq[b], vm[b], am[b], 0.8)
+        assert got[b] == po.count_violations(rows, sd2[b], sdd[b]) == 0
+    # new limits invalidate the solution: the audit refuses like the reference does
+    eng.set_joint_limits(0.5 * vm, 0.5 * am)
+    with pytest.raises(pkg.TpbError) as ei:
+        eng.count_violations()
+    assert ei.value.code == 9
+    eng.close()

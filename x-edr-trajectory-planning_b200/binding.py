@@ -190,6 +190,8 @@ def lib():
         L.tpb_quat_spline_eval_host.argtypes = [vp, i32]
         L.tpb_quat_spline_eval_device.restype = i32
         L.tpb_quat_spline_eval_device.argtypes = [vp, vp]
+        L.tpb_count_violations.restype = i32
+        L.tpb_count_violations.argtypes = [vp, vp, i32]
         L.tpb_planner_set_host_kinematics.restype = i32
         L.tpb_planner_set_host_kinematics.argtypes = [vp, PATH_IK_FN, JACOBIAN_FN, vp]
         L.tpb_planner_plan.restype = i32
@@ -542,6 +544,12 @@ class Engine:
 
     def planner_set_kinematics(self, model=1):
         self._ck(lib().tpb_planner_set_kinematics(self._h, int(model)))
+
+    def count_violations(self):
+        """tpb_count_violations: SolutionSatisfiesConstraints per path (-1: no solution)."""
+        out = np.zeros(self.B, np.int32)
+        self._ck(lib().tpb_count_violations(self._h, out.ctypes.data, 0))
+        return out
 
     def planner_set_host_kinematics(self, path_ik, jacobian):
         """tpb_planner_set_host_kinematics: the user's PathIKFunc / JacobianFunc for

@@ -1499,6 +1499,35 @@ int32_t tpb_devptr(tpb_engine* e, tpb_array what, void** ptr, size_t* bytes) {
 }
 
 // ---------------------------------------------------------------- profile queries (A16)
+int32_t tpb_count_violations(tpb_engine* e, int32_t* violations, int32_t on_device) {
+  if (e == nullptr || violations == nullptr) return TPB_INVALID_ARGUMENT;
+  auto& d = e->dims;
+  if (!e->optimized) return fail(e, TPB_FAILED_PRECONDITION, "No valid solution.");
+  cudaSetDevice(e->device);
+  int32_t* out = violations;
+  if (!on_device) {
+    const size_t need = sizeof(int32_t) * static_cast<size_t>(d.B);
+    if (need > e->query_scratch_bytes) {
+      TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+      if (e->query_scratch) cudaFree(e->query_scratch);
+      e->query_scratch = nullptr;
+      e->query_scratch_bytes = 0;
+      TPB_CUDA(e, cudaMalloc(&e->query_scratch, need + 16));
+      e->query_scratch_bytes = need;
+    }
+    out = static_cast<int32_t*>(e->query_scratch);
+  }
+  e->launches += tpb::launch_count_violations(d, e->a, e->mode == Mode::kJoint, e->safety, out,
+                                              e->stream);
+  TPB_CUDA(e, cudaGetLastError());
+  if (!on_device) {
+    TPB_CUDA(e, cudaMemcpyAsync(violations, out, sizeof(int32_t) * d.B, cudaMemcpyDeviceToHost,
+                                e->stream));
+    TPB_CUDA(e, cudaStreamSynchronize(e->stream));
+  }
+  return TPB_OK;
+}
+
 int32_t tpb_query_profile(tpb_engine* e, int32_t queries_per_path, const double* time_sec,
                           double* s, double* sd, double* sdd, int32_t* previous_index,
                           double* sk, double* sdk, double* sddk, double* tk, int32_t* status,

@@ -163,6 +163,8 @@ struct ProfileQueryArgs {
 };
 int launch_profile_query(const struct Dims& d, const struct DeviceArrays& a,
                          const ProfileQueryArgs& p, cudaStream_t st);
+int launch_count_violations(const struct Dims& d, const struct DeviceArrays& a, bool joint,
+                            double safety, int32_t* count, cudaStream_t st);
 
 // ---- kernel launchers (tpb_kernels.cu); each returns the number of kernels
 // it launched.

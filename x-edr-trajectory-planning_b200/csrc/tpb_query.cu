@@ -130,7 +130,54 @@ k_profile_query(Dims dm, DeviceArrays a, ProfileQueryArgs p) {
   if (p.status) p.status[out] = st;
 }
 
+// TimeOptimalPathProfile::SolutionSatisfiesConstraints (:492-518) for every path: the
+// number of (sample, row) pairs whose value A sdd + B sd^2 lies outside [lower, upper] by
+// more than kTiny.  One warp per path, lanes over samples; joint paths synthesise their
+// 2 D rows from q', q'' as ConstraintSetup does (timeable_path_joint_spline.cc:320-343),
+// everything else reads the stored rows.
+__global__ void __launch_bounds__(128)
+k_count_violations(Dims dm, DeviceArrays a, bool joint, double safety, int32_t* count) {
+  const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (b >= dm.B) return;  // uniform per warp
+  const int N = dm.N, D = dm.D, C = dm.C;
+  const size_t o = static_cast<size_t>(b) * N;
+  int bad = 0;
+  if (a.status[b] == TPB_PATH_OK) {
+    for (int i = lane; i < N; i += 32) {
+      const double sddv = a.sdd[o + i], sd2v = a.sd2[o + i];
+      if (joint) {
+        for (int d = 0; d < D; ++d) {
+          const double q1 = a.dq[(o + i) * D + d], q2 = a.ddq[(o + i) * D + d];
+          const double am = a.amax[static_cast<size_t>(b) * D + d] * safety;
+          const double vs = a.vmax[static_cast<size_t>(b) * D + d] * safety;
+          const double v = q1 * sddv + q2 * sd2v;
+          bad += ((v + kTiny < -am) || (v - kTiny > am)) ? 1 : 0;
+          const double w = 0.0 * sddv + (q1 * q1) * sd2v;
+          bad += ((w + kTiny < 0.0) || (w - kTiny > vs * vs)) ? 1 : 0;
+        }
+      } else {
+        const double* c = a.cons + (o + i) * C * 4;
+        for (int r = 0; r < C; ++r) {
+          const double v = c[r * 4 + 0] * sddv + c[r * 4 + 1] * sd2v;
+          bad += ((v + kTiny < c[r * 4 + 2]) || (v - kTiny > c[r * 4 + 3])) ? 1 : 0;
+        }
+      }
+    }
+  } else {
+    bad = -1;  // "No valid solution." (kFailedPrecondition in the reference)
+  }
+  for (int s = 16; s > 0; s >>= 1) bad += __shfl_xor_sync(kFullMask, bad, s);
+  if (lane == 0) count[b] = (a.status[b] == TPB_PATH_OK) ? bad : -1;
+}
+
 }  // namespace
+
+int launch_count_violations(const Dims& d, const DeviceArrays& a, bool joint, double safety,
+                            int32_t* count, cudaStream_t st) {
+  k_count_violations<<<(d.B + 3) / 4, 128, 0, st>>>(d, a, joint, safety, count);
+  return 1;
+}
 
 int launch_profile_query(const Dims& d, const DeviceArrays& a, const ProfileQueryArgs& p,
                          cudaStream_t st) {

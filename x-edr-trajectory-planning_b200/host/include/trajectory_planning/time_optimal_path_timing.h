@@ -169,18 +169,14 @@ class TimeOptimalPathProfile {
 
   Scalar GetMaxTimeIncrement() const { return state_ == kProblemSolved ? dt_max_ : -1; }
 
-  // SolutionSatisfiesConstraints (:492-518): audit of the downloaded solution.
+  // SolutionSatisfiesConstraints (:492-518): the audit runs on the device
+  // (tpb_count_violations).
   tp::Status SolutionSatisfiesConstraints() {
     if (state_ != kProblemSolved) return tp::FailedPreconditionError("No valid solution.");
-    constexpr Scalar kTiny = std::numeric_limits<Scalar>::epsilon() * 1e5;
-    int violations = 0;
-    for (int i = 0; i < num_samples_; ++i) {
-      for (int r = 0; r < num_constraints_; ++r) {
-        const double* c = &constraints_[(static_cast<size_t>(i) * num_constraints_ + r) * 4];
-        const Scalar v = c[0] * sdd_[i] + c[1] * sd2_[i];
-        if ((v + kTiny < c[2]) || (v - kTiny > c[3])) ++violations;
-      }
-    }
+    int32_t violations = -1;
+    const int32_t rc = tpb_count_violations(e_, &violations, 0);
+    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e_));
+    if (violations < 0) return tp::FailedPreconditionError("No valid solution.");
     if (violations > 0) {
       return tp::NotFoundError("Number of constraint violations: " + std::to_string(violations));
     }
