@@ -88,8 +88,11 @@ class PathTimingTrajectory : public TrajectoryPlanner {
   // Plan (.cc:579-684)
   tp::Status Plan(tp::Time start, tp::Duration time_horizon) override {
     if (path_ == nullptr) return {tp::StatusCode::kFailedPrecondition, "No path set."};
-    if (path_->SupportsDevicePlanner()) return PlanOnDevice(start, time_horizon);
-    return PlanOneWindow(start, time_horizon);
+    if (!path_->SupportsDevicePlanner()) {
+      return tp::UnimplementedError(
+          "only device-backed paths (TimeableJointSplinePath, TimeableCartesianSplinePath) are timed");
+    }
+    return PlanOnDevice(start, time_horizon);
   }
 
   // Extension: capacity (in path samples) of the spliced *_at_path_samples_ arrays on
@@ -214,155 +217,7 @@ class PathTimingTrajectory : public TrajectoryPlanner {
     return tp::OkStatus();
   }
 
-  // Plan (.cc:579-684) for paths sampled through host callbacks: one planning window.
-  tp::Status PlanOneWindow(tp::Time start, tp::Duration time_horizon) {
-    const double start_sec = TimeToSec(start);
-    // HandleTimeArguments (.cc:502-538)
-    if (initial_plan_ && start > end_time_ + tp::Seconds(time_step_sec_)) {
-      return {tp::StatusCode::kOutOfRange, "start > end of previous plan"};
-    }
-    if (!initial_plan_) {
-      start_time_ = start;
-      end_time_ = start;
-      path_start_ = 0.0;
-    } else {
-      if (start > end_time_) return tp::InvalidArgumentError("Start time must be < end time");
-      if (start < start_time_) return tp::InvalidArgumentError("Start time must be >= previous start time");
-      start_time_ = start;
-    }
-    // UpdatePathTrackingStatus (.cc:477-500)
-    target_reached_ = false;
-    planned_to_end_ = false;
-    const auto state = path_->GetState();
-    const bool fresh = state == TimeablePath::State::kNewPath || state == TimeablePath::State::kModifiedPath;
-    if (!initial_plan_) {
-      path_horizon_ = 0;
-      path_start_ = 0;
-    } else {
-      planned_to_end_ = path_->CloseToEnd(path_horizon_);
-      if (planned_to_end_) {
-        if (!fresh) {
-          target_reached_ = true;
-        } else {
-          path_horizon_ = path_start_ = 0.0;
-          planned_to_end_ = false;
-        }
-      }
-    }
-    const bool planned_enough = !fresh && (final_decel_start_ >= start + time_horizon);
-    if (!time_.empty() && planned_enough) {
-      EraseTrajectoryBefore(start);
-      return tp::OkStatus();
-    }
-    if (planned_to_end_) {
-      // the loop at .cc:628 does not run: GetTimeOffsetAfter (.cc:289-305), then the
-      // trajectory is resampled from the new start (.cc:660)
-      if (time_.empty()) return tp::FailedPreconditionError("No samples yet.");
-      if (start_sec < time_.front()) return {tp::StatusCode::kOutOfRange, "time < start_time."};
-      if (!(time_.back() > start_sec)) return tp::InternalError("time >= end_time_");
-      tpb_engine* held = path_->DeviceEngine();
-      if (held == nullptr) return tp::InternalError("path has no device engine");
-      return ResampleAndFinish(held, start_sec);
-    }
-    if (state != TimeablePath::State::kNewPath) {
-      return tp::UnimplementedError(
-          "moving-horizon re-planning of a partially planned path is outside the hot path");
-    }
-    if (path_->DeviceEngine() == nullptr) {
-      return tp::UnimplementedError(
-          "only device-backed paths (TimeableJointSplinePath, TimeableCartesianSplinePath) are timed");
-    }
-    if (time_horizon.ns <= 0) return tp::InvalidArgumentError("Duration must be positive");
-
-    // ---- ComputeTimingProfile (.cc:307-475), kNewPath branch
-    path_start_ = 0.0;
-    path_start_velocity_ = 0.0;
-    path_start_acceleration_ = 0.0;
-    path_time_start_ = start_sec;
-    const int N = path_->GetNumPathSamples();
-    path_horizon_ = path_start_ + path_->GetPathSamplingDistance() * (N - 1);
-    if (auto st = path_->SamplePath(path_start_); !st.ok()) return st;
-    if (auto st = path_->ConstraintSetup(); !st.ok()) return st;
-    {  // initial-velocity projection onto the path tangent (.cc:352-385)
-      const tp::VectorXd& d0 = path_->GetFirstPathDerivativeAt(0);
-      const tp::VectorXd& v0 = path_->GetInitialVelocity();
-      double sq = 0.0, dot = 0.0;
-      for (size_t i = 0; i < d0.size(); ++i) {
-        sq += d0[i] * d0[i];
-        dot += v0[i] * d0[i];
-      }
-      if (sq > 100 * std::numeric_limits<double>::epsilon()) {
-        path_start_velocity_ = std::max(dot / sq, 0.0);
-      }
-      double err = 0.0;
-      for (size_t i = 0; i < d0.size(); ++i) {
-        err = std::max(err, std::abs(d0[i] * path_start_velocity_ - v0[i]));
-      }
-      if (err > options_.GetMaxInitialVelocityError()) {
-        return tp::InvalidArgumentError(
-            "Could not satisfy initial velocity (probably not parallel to initial tangent): error = " +
-            std::to_string(err));
-      }
-    }
-    // the Cartesian path creates its engine state in SamplePath / ConstraintSetup
-    tpb_engine* e = path_->DeviceEngine();
-    if (e == nullptr) return tp::InternalError("path has no device engine after SamplePath");
-    const int max_solver_loops = static_cast<int>(std::max<size_t>(100, 10 * options_.GetNumPathSamples()));
-    int32_t rc = tpb_optimize(e, &path_start_velocity_, &path_start_acceleration_, &path_time_start_,
-                              max_solver_loops, 0);
-    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
-    int32_t status = TPB_PATH_NOT_RUN, last_extremal = 0;
-    tpb_get(e, TPB_ARR_STATUS, &status, sizeof(status), 0);
-    if (status == TPB_PATH_FAIL_SETUP) {
-      return {tp::StatusCode::kInternal, "Error setting up optimization problem"};
-    }
-    if (status != TPB_PATH_OK) return {tp::StatusCode::kInternal, "Error optimizing path parameter"};
-    tpb_get(e, TPB_ARR_LAST_EXTREMAL, &last_extremal, sizeof(last_extremal), 0);
-    time_at_path_samples_.resize(N);
-    tpb_get(e, TPB_ARR_TIME, time_at_path_samples_.data(), sizeof(double) * N, 0);
-
-    // ---- loop bookkeeping of Plan (.cc:635-658), first iteration
-    const int decel_start = std::max(last_extremal, static_cast<int>(options_.GetNumPathSamples() / 2));
-    final_decel_start_ = TimeFromSec(time_at_path_samples_[decel_start]);
-    planned_to_end_ = path_->CloseToEnd(path_horizon_);
-    const bool time_horizon_reached =
-        (time_at_path_samples_[N - 1] - start_sec) > static_cast<double>(time_horizon.ns) / 1e9;
-    if (!planned_to_end_ && !time_horizon_reached) {
-      return tp::UnimplementedError(
-          "path needs more than one planning window (increase num_path_samples * delta_parameter)");
-    }
-
-    last_extremal_ = last_extremal;
-    return ResampleAndFinish(e, start_sec);
-  }
-
-  // ResampleTrajectory (.cc:697-707, 755-783) on the device and the end of Plan
-  // (.cc:660-676), for the single window held by the engine.
-  tp::Status ResampleAndFinish(tpb_engine* e, double start_sec) {
-    int64_t total = 0;
-    const bool skipping = options_.GetTimeSamplingMethod() ==
-                          PathTimingTrajectoryOptions::TimeSamplingMethod::kSkipSamplesCloserThanTimeStep;
-    const int32_t rc = skipping ? tpb_resample_skipping(e, start_sec, time_step_sec_, &total)
-                                : tpb_resample(e, start_sec, time_step_sec_, &total);
-    if (rc != TPB_OK) return tp::FromCode(rc, tpb_last_error(e));
-    if (auto st = DownloadTrajectory(e, total); !st.ok()) return st;
-
-    initial_plan_ = true;
-    if (!time_.empty()) {
-      end_time_ = TimeFromSec(time_.back());
-      ClampToTimeStepMultiple(&end_time_);
-      final_decel_start_ = TimeFromSec(time_at_path_samples_[last_extremal_]);
-      ClampToTimeStepMultiple(&final_decel_start_);
-    } else {
-      end_time_ = start_time_;
-      final_decel_start_ = end_time_;
-    }
-    target_reached_ = planned_to_end_;
-    return tp::OkStatus();
-  }
-
  public:
-  size_t NumTimeSamples() const { return time_.size(); }
   // Extension: planning windows computed by the last Plan() (device planner).
   int LastPlanWindows() const { return last_plan_windows_; }
   tp::Time GetFinalDecelStart() const { return final_decel_start_; }
@@ -409,109 +264,6 @@ class PathTimingTrajectory : public TrajectoryPlanner {
   }
 
  private:
-  // ClampToTimeStepMultiple (.cc:229-233)
-  void ClampToTimeStepMultiple(tp::Time* time) const {
-    const int64_t loop_multiple = static_cast<int64_t>(std::round(TimeToSec(*time) / time_step_sec_));
-    *time = TimeFromSec(loop_multiple * time_step_sec_);
-  }
-  // GetMinTimeDeltaToKeep (.cc:893-900)
-  double GetMinTimeDeltaToKeep() const { return 0.95 * time_step_sec_; }
-
-  struct InterpolationResult {
-    tp::VectorXd position, velocity, acceleration;
-    double path_parameter = 0, path_parameter_derivative = 0, second_path_parameter_derivative = 0;
-  };
-  // InterpolateAtTime (.cc:709-753) on the path samples held by the device engine
-  // (bookkeeping for EraseTrajectoryBefore; the bulk interpolation of Plan() runs
-  // on the device).
-  InterpolationResult InterpolateAtTime(double time_sec) const {
-    InterpolationResult r;
-    tpb_engine* e = path_->DeviceEngine();
-    const size_t N = time_at_path_samples_.size(), D = options_.GetNumDofs();
-    size_t li = N - 1;  // TimeAtPathSamplesLowerIndex (.cc:686-695)
-    for (size_t i = 0; i + 1 < N; ++i) {
-      if (time_at_path_samples_[i + 1] > time_sec) {
-        li = i;
-        break;
-      }
-    }
-    const size_t ui = std::min(N - 1, li + 1);
-    const double tl = time_at_path_samples_[li], tu = time_at_path_samples_[ui];
-    const double at = std::abs(tu - tl) < std::numeric_limits<double>::epsilon()
-                          ? 0.5
-                          : (time_sec - tl) / (tu - tl);
-    std::vector<double> s(N), sd(N), sdd(N), q(N * D), dq(N * D), ddq(N * D);
-    tpb_get(e, TPB_ARR_S, s.data(), N * sizeof(double), 0);
-    tpb_get(e, TPB_ARR_SD, sd.data(), N * sizeof(double), 0);
-    tpb_get(e, TPB_ARR_SDD, sdd.data(), N * sizeof(double), 0);
-    tpb_get(e, TPB_ARR_Q, q.data(), N * D * sizeof(double), 0);
-    tpb_get(e, TPB_ARR_DQ, dq.data(), N * D * sizeof(double), 0);
-    tpb_get(e, TPB_ARR_DDQ, ddq.data(), N * D * sizeof(double), 0);
-    auto lerp = [at](double x, double y) { return x + at * (y - x); };
-    const auto& amax = path_->GetMaxJointAcceleration();
-    auto clamp = [](double v, double lim) {
-      v = (v < -lim) ? -lim : v;
-      return (lim < v) ? lim : v;
-    };
-    r.position = tp::VectorXd(D);
-    r.velocity = tp::VectorXd(D);
-    r.acceleration = tp::VectorXd(D);
-    for (size_t d = 0; d < D; ++d) {
-      const double vl = dq[li * D + d] * sd[li], vu = dq[ui * D + d] * sd[ui];
-      const double al = clamp(dq[li * D + d] * sdd[li] + ddq[li * D + d] * (sd[li] * sd[li]), amax[d]);
-      const double au = clamp(dq[ui * D + d] * sdd[ui] + ddq[ui * D + d] * (sd[ui] * sd[ui]), amax[d]);
-      r.position[d] = lerp(q[li * D + d], q[ui * D + d]);
-      r.velocity[d] = lerp(vl, vu);
-      r.acceleration[d] = clamp(lerp(al, au), amax[d]);
-    }
-    r.path_parameter = lerp(s[li], s[ui]);
-    r.path_parameter_derivative = lerp(sd[li], sd[ui]);
-    r.second_path_parameter_derivative = lerp(sdd[li], sdd[ui]);
-    return r;
-  }
-
-  // EraseTrajectoryBefore (.cc:540-577)
-  void EraseTrajectoryBefore(tp::Time time) {
-    const double time_sec = TimeToSec(time);
-    if (time_.empty() || time_sec < time_.front()) return;
-    if (options_.GetTimeSamplingMethod() ==
-        PathTimingTrajectoryOptions::TimeSamplingMethod::kSkipSamplesCloserThanTimeStep) {
-      // number of samples with a timestamp < time_sec
-      const int below = static_cast<int>(std::lower_bound(time_.begin(), time_.end(), time_sec) - time_.begin());
-      const InterpolationResult v = InterpolateAtTime(time_sec);
-      const int until = (below < static_cast<int>(time_.size()) &&
-                         time_[below] < time_sec + GetMinTimeDeltaToKeep())
-                            ? below
-                            : below - 1;
-      auto erase_n = [until](auto& vec) { vec.erase(vec.begin(), vec.begin() + std::max(until, 0)); };
-      erase_n(time_);
-      erase_n(path_parameter_);
-      erase_n(path_parameter_derivative_);
-      erase_n(second_path_parameter_derivative_);
-      erase_n(positions_);
-      erase_n(velocities_);
-      erase_n(accelerations_);
-      time_.front() = time_sec;  // fix the first sample
-      positions_.front() = v.position;
-      velocities_.front() = v.velocity;
-      accelerations_.front() = v.acceleration;
-      path_parameter_.front() = v.path_parameter;
-      path_parameter_derivative_.front() = v.path_parameter_derivative;
-      second_path_parameter_derivative_.front() = v.second_path_parameter_derivative;
-      return;
-    }
-    const int offset = std::min<int>(static_cast<int>(std::round((time_sec - time_.front()) / time_step_sec_)),
-                                     static_cast<int>(time_.size()) - 1);
-    auto erase = [offset](auto& v) { v.erase(v.begin(), v.begin() + offset); };
-    erase(time_);
-    erase(path_parameter_);
-    erase(path_parameter_derivative_);
-    erase(second_path_parameter_derivative_);
-    erase(positions_);
-    erase(velocities_);
-    erase(accelerations_);
-  }
-
   const PathTimingTrajectoryOptions options_;
   const double time_step_sec_;
   tp::Time final_decel_start_;
@@ -523,7 +275,6 @@ class PathTimingTrajectory : public TrajectoryPlanner {
   tpb_engine* device_planner_ = nullptr;  // the engine that holds this planner's state
   uint64_t device_planner_generation_ = 0;
   int last_plan_windows_ = 0;
-  int last_extremal_ = 0;  // of the window held by the engine (PlanOneWindow)
 };
 
 }  // namespace trajectory_planning
