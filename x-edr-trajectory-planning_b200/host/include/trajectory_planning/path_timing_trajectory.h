@@ -1,8 +1,9 @@
 // Host-side mirror of PathTimingTrajectory
 // (trajectory_planning/path_timing_trajectory.h:33-186, .cc:206-902).
 //
-// Plan() runs on the device.  For a TimeableJointSplinePath the whole
-// PathTimingTrajectory::Plan state machine lives there (tpb_planner_plan:
+// Plan() runs on the device.  For a TimeableJointSplinePath and a
+// TimeableCartesianSplinePath the whole PathTimingTrajectory::Plan state machine lives
+// there (tpb_planner_plan:
 // HandleTimeArguments, the moving-horizon loop over ComputeTimingProfile .cc:307-475
 // with splicing of the path samples, the "already planned enough" erase, both time
 // sampling methods); this class keeps the options, maps the per-path status back to
@@ -10,11 +11,9 @@
 // TrajectoryPlanner vectors.  Re-planning with a shifted start time (Plan() called
 // again while the previous trajectory is being executed) works as in the reference.
 //
-// Paths whose samples come from host callbacks (TimeableCartesianSplinePath with
-// user PathIKFunc / JacobianFunc) are planned one window at a time from here
-// (PlanOneWindow): a fresh path (State::kNewPath) whose planning loop needs a single
-// window, plus the "already planned enough" re-entry (.cc:590-601).
-// GetPathStopParameter runs on the device for both.
+// A Cartesian path's user PathIKFunc / JacobianFunc are called back from inside
+// tpb_planner_plan, once per planning window (tpb_planner_set_host_kinematics).
+// GetPathStopParameter runs on the device.
 #ifndef TRAJECTORY_PLANNING_PATH_TIMING_TRAJECTORY_H_
 #define TRAJECTORY_PLANNING_PATH_TIMING_TRAJECTORY_H_
 
