@@ -124,6 +124,14 @@ k_joint_fit(Dims dm, DeviceArrays a, double rounding, bool auto_delta) {
 // ===========================================================================
 
 constexpr int kSampleThreads = 128;
+// CTA size of k_joint_sample_limit<D>: the staging of the path's tables and the limits is
+// per CTA, so larger CTAs do it less often.  Measured (cfg2, ms per launch, same 16 warps /
+// SM): 64 threads x 8 CTAs/SM 1.321, 128 x 4 1.297, 192 x 2 (138 registers) 1.470,
+// **256 x 2 1.228**, 512 x 1 3.864.
+#ifndef TPB_JOINT_SAMPLE_THREADS
+#define TPB_JOINT_SAMPLE_THREADS 256
+#endif
+constexpr int kJointSampleThreads = TPB_JOINT_SAMPLE_THREADS;
 
 // Any D <= kMaxDofs: rows in thread-local arrays, generic LP (used for D > 8).
 __global__ void __launch_bounds__(kSampleThreads)
@@ -225,7 +233,7 @@ k_joint_sample_limit_any(Dims dm, DeviceArrays a, double safety) {
 #define TPB_SL_PHASE_SYNC 0
 #endif
 #ifndef TPB_SL_MINBLOCKS
-#define TPB_SL_MINBLOCKS 4
+#define TPB_SL_MINBLOCKS (512 / TPB_JOINT_SAMPLE_THREADS)
 #endif
 //
 // Staging: the path's knot vector and control points are contiguous runs in HBM and come
@@ -233,7 +241,7 @@ k_joint_sample_limit_any(Dims dm, DeviceArrays a, double safety) {
 // counted on an mbarrier), issued by thread 0 while the other threads compute the scaled
 // limits; a run that does not start on a 16-byte boundary is fetched from the boundary
 // before it (the extra 8 bytes belong to the neighbouring path's row) and addressed with an
-// offset.  The three [128][kD] output tiles leave as bulk copies when their HBM address is
+// offset.  The three [256][kD] output tiles leave as bulk copies when their HBM address is
 // 16-byte aligned (always for even N).  TPB_SL_BULK_IN / TPB_SL_BULK_OUT = 0 build the
 // per-thread loops (A/B; profiles/r2_summary.md).
 #ifndef TPB_SL_BULK_IN
@@ -248,7 +256,7 @@ __host__ __device__ inline int sample_limit_table_doubles(int max_points, int D)
 }
 
 template <int kD>
-__global__ void __launch_bounds__(kSampleThreads, TPB_SL_MINBLOCKS)
+__global__ void __launch_bounds__(kJointSampleThreads, TPB_SL_MINBLOCKS)
 k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
   extern __shared__ __align__(16) double smem[];
   __shared__ __align__(8) uint64_t s_bar;
@@ -295,7 +303,7 @@ k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
 #if TPB_SL_BULK_IN
   bulk::mbar_wait(&s_bar, 0);  // the tables have landed
 #endif
-  const int idx0 = blockIdx.x * kSampleThreads;
+  const int idx0 = blockIdx.x * kJointSampleThreads;
   const int idx = idx0 + threadIdx.x;
   const bool live = idx < dm.N;
 
@@ -309,8 +317,8 @@ k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
     const double parameter = path_start + idx * delta;
     const double k0 = s_knots[0], k1 = s_knots[nk - 1];
     double* o0 = s_out + threadIdx.x * kD;
-    double* o1 = o0 + kSampleThreads * kD;
-    double* o2 = o1 + kSampleThreads * kD;
+    double* o1 = o0 + kJointSampleThreads * kD;
+    double* o2 = o1 + kJointSampleThreads * kD;
     if (parameter < k1 + delta) {
       const double u = (parameter < k0) ? k0 : ((k1 < parameter) ? k1 : parameter);
       const int span = knot_span(s_knots, nk, 2, u);
@@ -366,7 +374,7 @@ k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
     a.b_at0[o] = fabs(sd2max - sd2zero) < kTiny;
   }
   // copy-out of this CTA's rows [idx0, idx0 + cnt): three contiguous runs
-  const int cnt = min(kSampleThreads, dm.N - idx0);
+  const int cnt = min(kJointSampleThreads, dm.N - idx0);
   const size_t g0 = (static_cast<size_t>(b) * dm.N + idx0) * kD;
 #if TPB_SL_BULK_OUT
   const bool vec = ((cnt * kD) & 1) == 0 && bulk::aligned16(a.q + g0) &&
@@ -377,8 +385,8 @@ k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
     if (threadIdx.x == 0) {
       const uint32_t bytes = static_cast<uint32_t>(cnt * kD) * 8u;
       bulk::bulk_store(a.q + g0, s_out, bytes);
-      bulk::bulk_store(a.dq + g0, s_out + kSampleThreads * kD, bytes);
-      bulk::bulk_store(a.ddq + g0, s_out + 2 * kSampleThreads * kD, bytes);
+      bulk::bulk_store(a.dq + g0, s_out + kJointSampleThreads * kD, bytes);
+      bulk::bulk_store(a.ddq + g0, s_out + 2 * kJointSampleThreads * kD, bytes);
       bulk::bulk_commit();
       bulk::bulk_wait_read<0>();  // shared memory stays valid until the copies have read it
     }
@@ -386,10 +394,10 @@ k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
   }
 #endif
   __syncthreads();
-  for (int k = threadIdx.x; k < cnt * kD; k += kSampleThreads) {
+  for (int k = threadIdx.x; k < cnt * kD; k += kJointSampleThreads) {
     a.q[g0 + k] = s_out[k];
-    a.dq[g0 + k] = s_out[kSampleThreads * kD + k];
-    a.ddq[g0 + k] = s_out[2 * kSampleThreads * kD + k];
+    a.dq[g0 + k] = s_out[kJointSampleThreads * kD + k];
+    a.ddq[g0 + k] = s_out[2 * kJointSampleThreads * kD + k];
   }
 }
 
@@ -791,17 +799,25 @@ int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safet
   TPB_NVTX("tpb:sample_path+limit_curve");
   const size_t tables =
       sizeof(double) * (static_cast<size_t>(d.max_points) + 3 + static_cast<size_t>(d.max_points) * d.D + 2 * d.D);
-  const dim3 grid = path_grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
   const size_t smem = sizeof(double) * (sample_limit_table_doubles(d.max_points, d.D) +
-                                        static_cast<size_t>(3) * kSampleThreads * d.D);
-  if (d.D <= 8 && smem <= 48 * 1024) {
-#define TPB_SL(K) \
-  case K: k_joint_sample_limit<K><<<grid, kSampleThreads, smem, st>>>(d, a, safety); break
+                                        static_cast<size_t>(3) * kJointSampleThreads * d.D);
+  if (d.D <= 8 && smem <= 96 * 1024) {
+    const dim3 grid = path_grid((d.N + kJointSampleThreads - 1) / kJointSampleThreads, d.B);
+    // more than 48 KB of dynamic shared memory needs the opt-in (8 dofs, or the spline at
+    // the reference's knot capacity after a switch)
+#define TPB_SL(K)                                                                          \
+  case K:                                                                                  \
+    if (smem > 48 * 1024)                                                                  \
+      cudaFuncSetAttribute(k_joint_sample_limit<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                           96 * 1024);                                                     \
+    k_joint_sample_limit<K><<<grid, kJointSampleThreads, smem, st>>>(d, a, safety);        \
+    break
     switch (d.D) {
       TPB_SL(1); TPB_SL(2); TPB_SL(3); TPB_SL(4); TPB_SL(5); TPB_SL(6); TPB_SL(7); TPB_SL(8);
     }
 #undef TPB_SL
   } else {
+    const dim3 grid = path_grid((d.N + kSampleThreads - 1) / kSampleThreads, d.B);
     k_joint_sample_limit_any<<<grid, kSampleThreads, tables, st>>>(d, a, safety);
   }
   return 1;
