@@ -228,9 +228,11 @@ k_joint_sample_limit_any(Dims dm, DeviceArrays a, double safety) {
 // each CTA writes its 128 consecutive [sample][D] rows as contiguous runs.
 // 4 CTAs/SM (<= 128 registers: 124 used, no spills) measured best: 1.42 ms against 1.54 ms
 // unconstrained (140 registers, 3 CTAs/SM) and 1.46 ms at 5 CTAs/SM (96 registers, spills)
-// 1: __syncthreads() between the sampling, LP and FindSdd phases (A/B: instruction cache)
-#ifndef TPB_SL_PHASE_SYNC
-#define TPB_SL_PHASE_SYNC 0
+// tiles of 256 samples a CTA works through with one staging of the path's tables.  Measured
+// (cfg2, ms per launch): 1 tile 1.202, 2 tiles 1.293, 4 tiles 1.406 (128 registers with
+// spills, and half / a quarter of the CTAs to balance the SMs with).
+#ifndef TPB_SL_TILES
+#define TPB_SL_TILES 1
 #endif
 #ifndef TPB_SL_MINBLOCKS
 #define TPB_SL_MINBLOCKS (512 / TPB_JOINT_SAMPLE_THREADS)
@@ -303,102 +305,118 @@ k_joint_sample_limit(Dims dm, DeviceArrays a, double safety) {
 #if TPB_SL_BULK_IN
   bulk::mbar_wait(&s_bar, 0);  // the tables have landed
 #endif
-  const int idx0 = blockIdx.x * kJointSampleThreads;
-  const int idx = idx0 + threadIdx.x;
-  const bool live = idx < dm.N;
-
+  // From here on the warps are independent: warp w of tile t owns samples
+  // [tile * 256 + 32 w, + 32), its own three [32][kD] output tiles in shared memory, and
+  // sends them off itself (three bulk copies issued by lane 0) -- no CTA barrier, a warp
+  // whose samples need more simplex iterations holds nobody up.
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double* wq = s_out + warp * (3 * 32 * kD);  // this warp's q / q' / q'' tiles
+  double* wdq = wq + 32 * kD;
+  double* wddq = wdq + 32 * kD;
   JointLimit<kD> J;
   J.aS = s_aS;
   J.vS2 = s_vS2;
-  if (live) {
-    // SamplePath, timeable_path_joint_spline.cc:294-318.
-    const double delta = a.delta[b];
-    const double path_start = a.path_start[b];
-    const double parameter = path_start + idx * delta;
-    const double k0 = s_knots[0], k1 = s_knots[nk - 1];
-    double* o0 = s_out + threadIdx.x * kD;
-    double* o1 = o0 + kJointSampleThreads * kD;
-    double* o2 = o1 + kJointSampleThreads * kD;
-    if (parameter < k1 + delta) {
-      const double u = (parameter < k0) ? k0 : ((k1 < parameter) ? k1 : parameter);
-      const int span = knot_span(s_knots, nk, 2, u);
-      double ders[3][3];
-      basis_ders<2, 2>(s_knots, span, u, ders);
-      // EvalCurveAndDerivatives, splines/bspline.h:561-566.
-      const double* P0 = s_ctrl + (span - 2) * kD;
-#pragma unroll
-      for (int d = 0; d < kD; ++d) {
-        double v0 = 0.0, v1 = 0.0, v2 = 0.0;
-#pragma unroll
-        for (int j = 0; j <= 2; ++j) {
-          const double Pj = P0[j * kD + d];
-          v0 += ders[0][j] * Pj;
-          v1 += ders[1][j] * Pj;
-          v2 += ders[2][j] * Pj;
-        }
-        o0[d] = v0;
-        o1[d] = v1;
-        o2[d] = v2;
-        J.A[d] = v1;
-        J.B[d] = v2;
-      }
-    } else {
-#pragma unroll
-      for (int d = 0; d < kD; ++d) {
-        o0[d] = s_ctrl[(n - 1) * kD + d];
-        o1[d] = 0.0;
-        o2[d] = 0.0;
-        J.A[d] = 0.0;
-        J.B[d] = 0.0;
-      }
-    }
-    // ConstraintSetup (:320-343) + CalculateBoundary's per-sample part
-    // (time_optimal_path_timing.cc:1366-1377); rows never leave the registers.
-    J.prepare();
-  }
-#if TPB_SL_PHASE_SYNC
-  __syncthreads();  // the CTA's warps enter the LP together (one region of code at a time)
-#endif
-  double sd2max = 0.0, sddmax = 0.0, sd2zero = 0.0, smax = 0.0, smin = 0.0;
-  if (live) J.lp(sd2max, sddmax, sd2zero);
-#if TPB_SL_PHASE_SYNC
-  __syncthreads();
-#endif
-  if (live) {
-    J.sdd_min_max(sd2max, smax, smin);
-    const size_t o = static_cast<size_t>(b) * dm.N + idx;
-    a.b_raw_sd2_max[o] = sd2max;
-    a.b_sd2_zero[o] = sd2zero;
-    a.b_raw_sdd_max[o] = smax;
-    a.b_raw_sdd_min[o] = smin;
-    a.b_at0[o] = fabs(sd2max - sd2zero) < kTiny;
-  }
-  // copy-out of this CTA's rows [idx0, idx0 + cnt): three contiguous runs
-  const int cnt = min(kJointSampleThreads, dm.N - idx0);
-  const size_t g0 = (static_cast<size_t>(b) * dm.N + idx0) * kD;
+  const double delta = a.delta[b];
+  const double path_start = a.path_start[b];
+  const double k0 = s_knots[0], k1 = s_knots[nk - 1];
 #if TPB_SL_BULK_OUT
-  const bool vec = ((cnt * kD) & 1) == 0 && bulk::aligned16(a.q + g0) &&
-                   bulk::aligned16(a.dq + g0) && bulk::aligned16(a.ddq + g0);
-  if (vec) {
-    bulk::fence_async_shared();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      const uint32_t bytes = static_cast<uint32_t>(cnt * kD) * 8u;
-      bulk::bulk_store(a.q + g0, s_out, bytes);
-      bulk::bulk_store(a.dq + g0, s_out + kJointSampleThreads * kD, bytes);
-      bulk::bulk_store(a.ddq + g0, s_out + 2 * kJointSampleThreads * kD, bytes);
-      bulk::bulk_commit();
-      bulk::bulk_wait_read<0>();  // shared memory stays valid until the copies have read it
-    }
-    return;
-  }
+  bool pending = false;  // lane 0: bulk copies of the previous tile may still read the tiles
 #endif
-  __syncthreads();
-  for (int k = threadIdx.x; k < cnt * kD; k += kJointSampleThreads) {
-    a.q[g0 + k] = s_out[k];
-    a.dq[g0 + k] = s_out[kJointSampleThreads * kD + k];
-    a.ddq[g0 + k] = s_out[2 * kJointSampleThreads * kD + k];
+  for (int t = 0; t < TPB_SL_TILES; ++t) {
+    const int idx0 = (blockIdx.x * TPB_SL_TILES + t) * kJointSampleThreads + warp * 32;
+    if (idx0 >= dm.N) break;  // uniform per warp
+    const int idx = idx0 + lane;
+    const bool live = idx < dm.N;
+#if TPB_SL_BULK_OUT
+    if (TPB_SL_TILES > 1) {
+      if (pending) bulk::bulk_wait_read<0>();
+      __syncwarp();
+    }
+#endif
+    if (live) {
+      // SamplePath, timeable_path_joint_spline.cc:294-318.
+      const double parameter = path_start + idx * delta;
+      double* o0 = wq + lane * kD;
+      double* o1 = wdq + lane * kD;
+      double* o2 = wddq + lane * kD;
+      if (parameter < k1 + delta) {
+        const double u = (parameter < k0) ? k0 : ((k1 < parameter) ? k1 : parameter);
+        const int span = knot_span(s_knots, nk, 2, u);
+        double ders[3][3];
+        basis_ders<2, 2>(s_knots, span, u, ders);
+        // EvalCurveAndDerivatives, splines/bspline.h:561-566.
+        const double* P0 = s_ctrl + (span - 2) * kD;
+#pragma unroll
+        for (int d = 0; d < kD; ++d) {
+          double v0 = 0.0, v1 = 0.0, v2 = 0.0;
+#pragma unroll
+          for (int j = 0; j <= 2; ++j) {
+            const double Pj = P0[j * kD + d];
+            v0 += ders[0][j] * Pj;
+            v1 += ders[1][j] * Pj;
+            v2 += ders[2][j] * Pj;
+          }
+          o0[d] = v0;
+          o1[d] = v1;
+          o2[d] = v2;
+          J.A[d] = v1;
+          J.B[d] = v2;
+        }
+      } else {
+#pragma unroll
+        for (int d = 0; d < kD; ++d) {
+          o0[d] = s_ctrl[(n - 1) * kD + d];
+          o1[d] = 0.0;
+          o2[d] = 0.0;
+          J.A[d] = 0.0;
+          J.B[d] = 0.0;
+        }
+      }
+      // ConstraintSetup (:320-343) + CalculateBoundary's per-sample part
+      // (time_optimal_path_timing.cc:1366-1377); rows never leave the registers.
+      J.prepare();
+      double sd2max, sddmax, sd2zero, smax, smin;
+      J.lp(sd2max, sddmax, sd2zero);
+      J.sdd_min_max(sd2max, smax, smin);
+      const size_t o = static_cast<size_t>(b) * dm.N + idx;
+      a.b_raw_sd2_max[o] = sd2max;
+      a.b_sd2_zero[o] = sd2zero;
+      a.b_raw_sdd_max[o] = smax;
+      a.b_raw_sdd_min[o] = smin;
+      a.b_at0[o] = fabs(sd2max - sd2zero) < kTiny;
+    }
+    // copy-out of this warp's rows [idx0, idx0 + cnt): three contiguous runs
+    const int cnt = min(32, dm.N - idx0);
+    const size_t g0 = (static_cast<size_t>(b) * dm.N + idx0) * kD;
+#if TPB_SL_BULK_OUT
+    const bool vec = ((cnt * kD) & 1) == 0 && bulk::aligned16(a.q + g0) &&
+                     bulk::aligned16(a.dq + g0) && bulk::aligned16(a.ddq + g0);
+    if (vec) {
+      bulk::fence_async_shared();
+      __syncwarp();
+      if (lane == 0) {
+        const uint32_t bytes = static_cast<uint32_t>(cnt * kD) * 8u;
+        bulk::bulk_store(a.q + g0, wq, bytes);
+        bulk::bulk_store(a.dq + g0, wdq, bytes);
+        bulk::bulk_store(a.ddq + g0, wddq, bytes);
+        bulk::bulk_commit();
+        pending = true;
+      }
+      continue;
+    }
+#endif
+    __syncwarp();
+    for (int k = lane; k < cnt * kD; k += 32) {
+      a.q[g0 + k] = wq[k];
+      a.dq[g0 + k] = wdq[k];
+      a.ddq[g0 + k] = wddq[k];
+    }
+    __syncwarp();
   }
+#if TPB_SL_BULK_OUT
+  // shared memory stays valid until the copies have read it
+  if (pending) bulk::bulk_wait_read<0>();
+#endif
 }
 
 __global__ void __launch_bounds__(kSampleThreads)
@@ -802,7 +820,8 @@ int launch_joint_sample_limit(const Dims& d, const DeviceArrays& a, double safet
   const size_t smem = sizeof(double) * (sample_limit_table_doubles(d.max_points, d.D) +
                                         static_cast<size_t>(3) * kJointSampleThreads * d.D);
   if (d.D <= 8 && smem <= 96 * 1024) {
-    const dim3 grid = path_grid((d.N + kJointSampleThreads - 1) / kJointSampleThreads, d.B);
+    const int per_cta = kJointSampleThreads * TPB_SL_TILES;
+    const dim3 grid = path_grid((d.N + per_cta - 1) / per_cta, d.B);
     // more than 48 KB of dynamic shared memory needs the opt-in (8 dofs, or the spline at
     // the reference's knot capacity after a switch)
 #define TPB_SL(K)                                                                          \
