@@ -238,6 +238,72 @@ int main() {
     printf("\"loops\": %d, \"windows\": %d, \"final_decel_start_ns\": %lld},\n", loops, windows,
            static_cast<long long>(planner2.GetFinalDecelStart().ns));
   }
+  // ---- ResetAndReplan (path_timing_trajectory_test.cc:440-563): plan to the end while
+  // collecting every window's rows in a TrajectoryBuffer, Reset(), set the same waypoints
+  // again, plan to the end again -- both buffers hold the same rows; both sampling methods
+  for (int method = 0; method < 2; ++method) {
+    std::vector<VectorXd> wps = {VectorXd{1, 2, 3}, VectorXd{-1, -2, -3}, VectorXd{0.5, 1.0, 1.5}};
+    VectorXd vmax = VectorXd::Constant(kNDof, 1.0), amax = VectorXd::Constant(kNDof, 2.0);
+    auto path3 = std::make_shared<TimeableJointSplinePath>(
+        JointPathOptions().set_num_dofs(kNDof).set_num_path_samples(kNumSamples));
+    PathTimingTrajectory planner3(
+        PathTimingTrajectoryOptions()
+            .SetTimeStep(tp::Milliseconds(4))
+            .SetNumDofs(kNDof)
+            .SetNumPathSamples(kNumSamples)
+            .SetTimeSamplingMethod(method == 0
+                                       ? PathTimingTrajectoryOptions::TimeSamplingMethod::kUniformlyInTime
+                                       : PathTimingTrajectoryOptions::TimeSamplingMethod::
+                                             kSkipSamplesCloserThanTimeStep));
+    EXPECT(planner3.SetPath(path3).ok());
+    EXPECT(path3->SetWaypoints(wps).ok());
+    path3->SetMaxJointVelocity(ToSpan(vmax));
+    path3->SetMaxJointAcceleration(ToSpan(amax));
+    auto plan_to_end = [&](TrajectoryBuffer& buffer) {
+      tp::Time start_time = TimeFromSec(0.0);
+      int loops = 0;
+      for (; !planner3.IsTrajectoryAtEnd() && loops < 500; ++loops) {
+        const tp::Status st = planner3.Plan(start_time, tp::Milliseconds(750));
+        EXPECT(st.ok());
+        if (!st.ok()) break;
+        EXPECT(planner3.GetPositions().size() == planner3.GetVelocities().size());
+        EXPECT(planner3.GetPositions().size() == planner3.GetAccelerations().size());
+        EXPECT(buffer
+                   .InsertSegment(planner3.GetTime(), planner3.GetPositions(),
+                                  planner3.GetVelocities(), planner3.GetAccelerations())
+                   .ok());
+        start_time = planner3.GetNextPlanStartTime(start_time + tp::Milliseconds(200));
+      }
+      return loops;
+    };
+    auto first = TrajectoryBuffer::Create();
+    auto second = TrajectoryBuffer::Create();
+    EXPECT(first.ok() && second.ok());
+    const int loops1 = plan_to_end(**first);
+    EXPECT(planner3.IsTrajectoryAtEnd());
+    planner3.Reset();
+    EXPECT(!planner3.IsTrajectoryAtEnd());
+    EXPECT(planner3.GetNumTimeSamples() == 0);
+    EXPECT(path3->SetWaypoints(wps).ok());
+    const int loops2 = plan_to_end(**second);
+    EXPECT(planner3.IsTrajectoryAtEnd());
+    EXPECT(loops1 == loops2 && loops1 >= 3);
+    const size_t rows = (*first)->GetNumSamples();
+    EXPECT(rows > 100 && rows == (*second)->GetNumSamples());
+    bool same = rows == (*second)->GetNumSamples();
+    for (size_t i = 0; same && i < rows; ++i) {
+      same = (*first)->GetTimes()[i] == (*second)->GetTimes()[i] &&
+             (*first)->GetPositions()[i] == (*second)->GetPositions()[i] &&
+             (*first)->GetVelocities()[i] == (*second)->GetVelocities()[i] &&
+             (*first)->GetAccelerations()[i] == (*second)->GetAccelerations()[i];
+    }
+    EXPECT(same);
+    printf("\"%s\": {\n", method == 0 ? "reset_and_replan" : "reset_and_replan_skip");
+    PrintArray("time", std::vector<double>((*second)->GetTimes().begin(), (*second)->GetTimes().end()));
+    PrintArray("positions", Flatten(std::vector<VectorXd>((*second)->GetPositions().begin(),
+                                                          (*second)->GetPositions().end())));
+    printf("\"loops\": %d, \"rows\": %zu, \"same\": %d},\n", loops2, rows, same ? 1 : 0);
+  }
   // ---- SwitchToNewJointWaypointPathWorks (path_timing_trajectory_test.cc:299-436):
   // plan until the motion is fast, switch to new waypoints at the stop parameter with the
   // current velocity as the initial velocity, plan to the end of the new path

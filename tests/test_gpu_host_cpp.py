@@ -191,6 +191,32 @@ def test_moving_horizon_replanning_matches_oracle(result, po, key, skip):
     assert r["final_decel_start_ns"] == pl.final_decel_start
 
 
+@pytest.mark.parametrize("key,skip", [("reset_and_replan", False), ("reset_and_replan_skip", True)])
+def test_reset_and_replan_matches_oracle(result, po, key, skip):
+    """ResetAndReplan (path_timing_trajectory_test.cc:440-563): the host classes plan to the
+    end into a TrajectoryBuffer, Reset(), and plan again -- the C++ side checks both buffers
+    are equal; here the second one is compared bit for bit with the oracle's planner and
+    the oracle's TrajectoryBuffer driven the same way."""
+    r = result[key]
+    assert r["same"] == 1
+    wp = np.array([[1.0, 2, 3], [-1, -2, -3], [0.5, 1.0, 1.5]])
+    pl = po.Planner(wp, np.ones(3), np.full(3, 2.0), 1000, 0.005, 0.004, skip=skip,
+                    max_initial_velocity_error=1e-2)
+    buf = po.TrajectoryBuffer(3)
+    start, loops = 0, 0
+    while not pl.target_reached:
+        assert pl.plan(start, 750_000_000) == po.ORC_OK
+        tr = pl.trajectory()
+        assert buf.insert_segment(tr["r_t"], tr["r_pos"], tr["r_vel"], tr["r_acc"]) == 0
+        # GetNextPlanStartTime (path_timing_trajectory.cc:870-872)
+        start = min(pl.end_time, max(start + 200_000_000, pl.start_time))
+        loops += 1
+    assert r["loops"] == loops and r["rows"] == buf.num_samples
+    t, p, _, _ = buf.rows()
+    assert np.array_equal(np.array(r["time"]), t)
+    assert np.array_equal(np.array(r["positions"]).reshape(-1, 3), p)
+
+
 def test_switch_to_waypoint_path_matches_oracle(result, po):
     """host SwitchToWaypointPath + re-planning of the modified path
     (SwitchToNewJointWaypointPathWorks, path_timing_trajectory_test.cc:299-436) against the
